@@ -1,0 +1,289 @@
+"""
+ctypes binding of the C ABI declared in include/atooms_b200.h.
+
+`load()` returns the product library (hand-written CUDA, sm_100a).  There is
+no CPU fallback: if the shared object is missing or no GPU is usable the
+call raises.  `Library(path)` binds any shared object exporting the ABI; the
+test-suite uses it to drive the CPU oracle through the very same wrapper.
+"""
+import ctypes
+import os
+
+import numpy
+
+__all__ = ['Library', 'Engine', 'load', 'library_path', 'B2Error',
+           'FP32', 'FP64', 'ENERGY', 'FORCES', 'VIRIAL', 'STRESS', 'MIN_SD', 'MIN_FIRE',
+           'SYMBOLS']
+
+ABI_VERSION = 1
+FP32, FP64 = 32, 64
+ENERGY, FORCES, VIRIAL, STRESS = 1, 2, 4, 8
+MIN_SD, MIN_FIRE = 0, 1
+T_KINETIC, T_POTENTIAL, T_VIRIAL, T_FNORM2, T_PX, T_PY, T_PZ, T_MASS, T_MSD, T_LEN = \
+    0, 1, 2, 3, 4, 5, 6, 7, 8, 16
+S_STEPS, S_REBUILDS, S_LAUNCHES, S_MAX_NEIGH, S_NEIGH_CAP, S_LIST_MODE, S_NCELLS, S_LEN = \
+    0, 1, 2, 3, 4, 5, 6, 16
+
+_ERRORS = {-1: ValueError, -5: NotImplementedError}
+
+_c_dp = ctypes.POINTER(ctypes.c_double)
+_c_ip = ctypes.POINTER(ctypes.c_int32)
+_c_lp = ctypes.POINTER(ctypes.c_int64)
+_vp = ctypes.c_void_p
+_i64 = ctypes.c_int64
+_int = ctypes.c_int
+_dbl = ctypes.c_double
+
+# name -> (restype, argtypes); the single source of truth for the loader and
+# for the "every declared symbol is exported" test.
+SYMBOLS = {
+    'b2_abi_version': (_int, []),
+    'b2_backend_name': (ctypes.c_char_p, []),
+    'b2_last_error': (ctypes.c_char_p, [_vp]),
+    'b2_create': (_int, [_int, _int, ctypes.POINTER(_vp)]),
+    'b2_destroy': (_int, [_vp]),
+    'b2_set_stream': (_int, [_vp, _vp]),
+    'b2_set_box': (_int, [_vp, _c_dp, _c_dp]),
+    'b2_set_pair_table': (_int, [_vp, _int, _c_dp, _c_dp, _c_dp, _int]),
+    'b2_set_skin': (_int, [_vp, _dbl]),
+    'b2_upload': (_int, [_vp, _i64, _c_dp, _c_dp, _c_ip, _c_dp]),
+    'b2_update': (_int, [_vp, _c_dp, _c_dp]),
+    'b2_download': (_int, [_vp, _c_dp, _c_dp, _c_ip]),
+    'b2_scale_velocities': (_int, [_vp, _dbl]),
+    'b2_mark_reference': (_int, [_vp]),
+    'b2_compute': (_int, [_vp, _int, _c_dp, _c_dp, _c_dp, _c_dp, _c_dp, _c_dp]),
+    'b2_thermo': (_int, [_vp, _c_dp]),
+    'b2_neighbors': (_int, [_vp, _c_ip, _c_ip, ctypes.c_int32, _c_ip]),
+    'b2_run_nve': (_int, [_vp, _i64, _dbl]),
+    'b2_minimize': (_int, [_vp, _int, _i64, _dbl, _dbl, _c_lp, ctypes.POINTER(_int)]),
+    'b2_stats': (_int, [_vp, _c_lp]),
+    'b2_last_timing': (_int, [_vp, _c_dp, _c_lp]),
+}
+
+
+class B2Error(RuntimeError):
+    """Failure reported by the engine (negative B2_E* code)."""
+
+    def __init__(self, code, message):
+        RuntimeError.__init__(self, '[b2 error %d] %s' % (code, message))
+        self.code = code
+
+
+def library_path():
+    """Where build() puts the product library (in-tree, so it travels to the GPU box)."""
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), 'lib', 'libatooms_b200.so')
+
+
+class Library(object):
+
+    """A shared object exporting the b2_* ABI."""
+
+    def __init__(self, path):
+        if not os.path.exists(path):
+            raise OSError('atooms_b200: shared library not found: %s '
+                          '(build it with `python -c "import __graft_entry__ as g; g.build()"`; '
+                          'there is no CPU fallback)' % path)
+        self.path = path
+        self.dll = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        for name, (restype, argtypes) in SYMBOLS.items():
+            fn = getattr(self.dll, name)   # AttributeError if the symbol is missing
+            fn.restype = restype
+            fn.argtypes = argtypes
+        version = self.dll.b2_abi_version()
+        if version != ABI_VERSION:
+            raise OSError('atooms_b200: %s has ABI version %d, expected %d' % (path, version, ABI_VERSION))
+        self.name = self.dll.b2_backend_name().decode()
+
+    def check(self, code, handle=None):
+        if code == 0:
+            return
+        msg = self.dll.b2_last_error(handle)
+        msg = msg.decode() if msg else ''
+        if code in _ERRORS:
+            raise _ERRORS[code]('[b2 error %d] %s' % (code, msg))
+        raise B2Error(code, msg)
+
+
+_product = None
+
+
+def load():
+    """The product library (CUDA).  Raises if it has not been built."""
+    global _product
+    if _product is None:
+        _product = Library(library_path())
+    return _product
+
+
+def _dp(a):
+    return None if a is None else a.ctypes.data_as(_c_dp)
+
+
+def _ip(a):
+    return None if a is None else a.ctypes.data_as(_c_ip)
+
+
+def _as_xyz(a, n=None, name='array'):
+    """Accept (N,3) C-order or (3,N) F-order float64; return an array whose
+    memory is N x 3 interleaved (no copy if it already is)."""
+    a = numpy.asarray(a)
+    if a.ndim != 2:
+        raise ValueError('%s must be 2-dimensional' % name)
+    if a.shape[0] == 3 and a.flags.f_contiguous and not (a.shape[1] == 3 and a.flags.c_contiguous):
+        a = a.T
+    if a.shape[1] != 3:
+        raise ValueError('%s must be (N, 3) or Fortran-ordered (3, N)' % name)
+    a = numpy.ascontiguousarray(a, dtype=numpy.float64)
+    if n is not None and a.shape[0] != n:
+        raise ValueError('%s has %d rows, expected %d' % (name, a.shape[0], n))
+    return a
+
+
+class Engine(object):
+
+    """One b2_ctx: a particle system resident on one GPU."""
+
+    def __init__(self, precision=FP64, device=0, library=None, stream=None):
+        self.lib = library if library is not None else load()
+        self.precision = int(precision)
+        self.device = int(device)
+        self.n = 0
+        handle = _vp()
+        self.lib.check(self.lib.dll.b2_create(self.device, self.precision, ctypes.byref(handle)))
+        self._h = handle
+        if stream is not None:
+            self.set_stream(stream)
+
+    # -- lifetime ---------------------------------------------------------
+    def close(self):
+        h, self._h = getattr(self, '_h', None), None
+        if h:
+            self.lib.dll.b2_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _call(self, name, *args):
+        if not self._h:
+            raise B2Error(-4, 'engine is closed')
+        self.lib.check(getattr(self.lib.dll, name)(self._h, *args), self._h)
+
+    # -- model ------------------------------------------------------------
+    def set_stream(self, stream):
+        self._call('b2_set_stream', _vp(int(stream) if stream else 0))
+
+    def set_box(self, side, center=None):
+        side = numpy.ascontiguousarray(side, dtype=numpy.float64)
+        center = numpy.zeros(3) if center is None else numpy.ascontiguousarray(center, dtype=numpy.float64)
+        if side.shape != (3,) or center.shape != (3,):
+            raise ValueError('only 3-dimensional orthorhombic cells are supported')
+        self._call('b2_set_box', _dp(side), _dp(center))
+
+    def set_pair_table(self, eps, sigma, rcut, shifted=True):
+        eps = numpy.atleast_2d(numpy.ascontiguousarray(eps, dtype=numpy.float64))
+        sigma = numpy.atleast_2d(numpy.ascontiguousarray(sigma, dtype=numpy.float64))
+        rcut = numpy.atleast_2d(numpy.ascontiguousarray(rcut, dtype=numpy.float64))
+        nsp = eps.shape[0]
+        if not (eps.shape == sigma.shape == rcut.shape == (nsp, nsp)):
+            raise ValueError('eps, sigma, rcut must be square matrices of the same size')
+        self._call('b2_set_pair_table', nsp, _dp(eps), _dp(sigma), _dp(rcut), int(bool(shifted)))
+
+    def set_skin(self, skin):
+        self._call('b2_set_skin', float(skin))
+
+    # -- state ------------------------------------------------------------
+    def upload(self, position, species, velocity=None, mass=None):
+        pos = _as_xyz(position, name='position')
+        n = pos.shape[0]
+        vel = None if velocity is None else _as_xyz(velocity, n, 'velocity')
+        spe = numpy.ascontiguousarray(species, dtype=numpy.int32)
+        if spe.shape != (n,):
+            raise ValueError('species must have one entry per particle')
+        m = None if mass is None else numpy.ascontiguousarray(mass, dtype=numpy.float64)
+        if m is not None and m.shape != (n,):
+            raise ValueError('mass must have one entry per particle')
+        self._call('b2_upload', n, _dp(pos), _dp(vel), _ip(spe), _dp(m))
+        self.n = n
+
+    def update(self, position=None, velocity=None):
+        pos = None if position is None else _as_xyz(position, self.n, 'position')
+        vel = None if velocity is None else _as_xyz(velocity, self.n, 'velocity')
+        self._call('b2_update', _dp(pos), _dp(vel))
+
+    def download(self, position=True, velocity=True, image=False):
+        pos = numpy.empty((self.n, 3)) if position else None
+        vel = numpy.empty((self.n, 3)) if velocity else None
+        img = numpy.empty((self.n, 3), dtype=numpy.int32) if image else None
+        self._call('b2_download', _dp(pos), _dp(vel), _ip(img))
+        return pos, vel, img
+
+    def scale_velocities(self, factor):
+        self._call('b2_scale_velocities', float(factor))
+
+    def mark_reference(self):
+        self._call('b2_mark_reference')
+
+    # -- single point -----------------------------------------------------
+    def compute(self, what=ENERGY | FORCES | VIRIAL, forces=True, per_particle=False, stress=False):
+        """Returns a dict with energy, virial and optionally forces (N,3),
+        stress (3,3), pe (N), vir (N)."""
+        e, w = _dbl(), _dbl()
+        f = numpy.empty((self.n, 3)) if forces else None
+        s = numpy.empty((3, 3)) if stress else None
+        pe = numpy.empty(self.n) if per_particle else None
+        vir = numpy.empty(self.n) if per_particle else None
+        if stress:
+            what |= STRESS
+        self._call('b2_compute', int(what), ctypes.byref(e), ctypes.byref(w), _dp(s), _dp(f), _dp(pe), _dp(vir))
+        out = {'energy': e.value, 'virial': w.value}
+        if forces:
+            out['forces'] = f
+        if stress:
+            out['stress'] = s
+        if per_particle:
+            out['pe'], out['vir'] = pe, vir
+        return out
+
+    def thermo(self):
+        out = numpy.zeros(T_LEN)
+        self._call('b2_thermo', _dp(out))
+        return {'kinetic': out[T_KINETIC], 'potential': out[T_POTENTIAL], 'virial': out[T_VIRIAL],
+                'fnorm2': out[T_FNORM2], 'momentum': out[T_PX:T_PZ + 1].copy(), 'mass': out[T_MASS],
+                'msd_sum': out[T_MSD]}
+
+    def neighbors(self):
+        """List of sorted int32 arrays (original numbering) for the current configuration."""
+        count = numpy.zeros(self.n, dtype=numpy.int32)
+        mx = ctypes.c_int32()
+        self._call('b2_neighbors', _ip(count), None, 0, ctypes.byref(mx))
+        stride = max(int(mx.value), 1)
+        nbr = numpy.empty((self.n, stride), dtype=numpy.int32)
+        self._call('b2_neighbors', _ip(count), _ip(nbr), stride, ctypes.byref(mx))
+        return [nbr[i, :count[i]].copy() for i in range(self.n)]
+
+    # -- dynamics ---------------------------------------------------------
+    def run_nve(self, steps, dt):
+        self._call('b2_run_nve', int(steps), float(dt))
+
+    def minimize(self, method, max_steps, dt, fn2_tol):
+        done, conv = _i64(), _int()
+        self._call('b2_minimize', int(method), int(max_steps), float(dt), float(fn2_tol),
+                   ctypes.byref(done), ctypes.byref(conv))
+        return done.value, bool(conv.value)
+
+    # -- introspection ----------------------------------------------------
+    def stats(self):
+        out = numpy.zeros(S_LEN, dtype=numpy.int64)
+        self._call('b2_stats', out.ctypes.data_as(_c_lp))
+        return {'steps': int(out[S_STEPS]), 'rebuilds': int(out[S_REBUILDS]),
+                'launches': int(out[S_LAUNCHES]), 'max_neighbors': int(out[S_MAX_NEIGH]),
+                'neighbor_capacity': int(out[S_NEIGH_CAP]), 'list_mode': int(out[S_LIST_MODE]),
+                'ncells': int(out[S_NCELLS])}
+
+    def last_timing(self):
+        ms, launches = _dbl(), _i64()
+        self._call('b2_last_timing', ctypes.byref(ms), ctypes.byref(launches))
+        return ms.value, launches.value

@@ -1,0 +1,212 @@
+/*
+ * atooms_b200.h — C ABI of the B200-native pair-interaction / MD engine.
+ *
+ * This is the drop-in boundary for the ONE hot path of atooms-mirror/atooms
+ * (SURVEY.md §8): pair force/energy/virial evaluation, neighbour search, the
+ * NVE velocity-Verlet loop and SD/FIRE minimisation.  The reference reaches
+ * that path through Python duck-typed plugins and external engines (LAMMPS
+ * subprocess, RUMD SWIG module); it has no FFI of its own, so every entry
+ * point below cites the reference *interface* it serves.  All citations are
+ * `path:line` into the reference tree (atooms 3.14.1).
+ *
+ * Conventions
+ *   - plain C: pointers + sizes, no C++/torch types.  All array arguments are
+ *     HOST pointers unless a name ends in `_dev`.
+ *   - positions / velocities / forces are N x 3, xyz interleaved
+ *     ([x0,y0,z0,x1,...]) float64 — byte-identical to the (3,N) Fortran-order
+ *     arrays `System.dump(..., order='F')` hands to `Interaction.compute`
+ *     (atooms/system/system.py:245-259, :486-487).
+ *   - every function returns 0 (B2_OK) or a negative B2_E* code, never throws
+ *     or aborts; `b2_last_error` gives the message (Python side raises, like
+ *     atooms/backends/lammps.py:68-73 re-raises engine failures).
+ *   - a context is re-entrant per handle, not thread-safe on one handle
+ *     (the reference host is single-threaded).
+ *
+ * Two libraries export this ABI: the product `libatooms_b200.so` (CUDA,
+ * sm_100a) and the CPU oracle `oracle/_build/liboracle_b2.so` (test
+ * infrastructure; never loaded by the product package).
+ */
+#ifndef ATOOMS_B200_H
+#define ATOOMS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_ABI_VERSION 1
+
+/* error codes */
+#define B2_OK            0
+#define B2_EINVAL       -1   /* bad argument (-> ValueError)                         */
+#define B2_ECUDA        -2   /* CUDA runtime failure                                 */
+#define B2_ENOMEM       -3   /* allocation failed                                    */
+#define B2_ESTATE       -4   /* call order: box / table / particles not set yet      */
+#define B2_EUNSUPPORTED -5   /* e.g. observable 'hessian'                             */
+#define B2_ENOCUDA      -6   /* no CUDA device / driver: the product has no CPU path */
+
+/* arithmetic the path computes in */
+#define B2_FP32 32
+#define B2_FP64 64
+
+/* `what` bit mask for b2_compute; mirrors the observable names asserted at
+ * atooms/system/interaction.py:65-66 ('energy','forces','virial','stress').
+ * 'hessian' is out of scope -> B2_EUNSUPPORTED.           */
+#define B2_ENERGY  1
+#define B2_FORCES  2
+#define B2_VIRIAL  4
+#define B2_STRESS  8
+
+/* minimiser methods: `method` of the EnergyMinimization surface
+ * (atooms/backends/dryrun.py:129-144, atooms/backends/lammps.py:291-311).   */
+#define B2_MIN_SD   0
+#define B2_MIN_FIRE 1
+
+/* b2_thermo slots */
+#define B2_T_KINETIC     0   /* sum 1/2 m v^2          (system.py:232-243)            */
+#define B2_T_POTENTIAL   1   /* U                      (system.py:261-274)            */
+#define B2_T_VIRIAL      2   /* W = sum_{i<j} r.F      (system.py:321-335, :348)      */
+#define B2_T_FNORM2      3   /* sum F^2                (system.py:305-319)            */
+#define B2_T_PX          4   /* total momentum x,y,z   (particle.py:156-165)          */
+#define B2_T_PY          5
+#define B2_T_PZ          6
+#define B2_T_MASS        7   /* total mass                                            */
+#define B2_T_MSD         8   /* sum |unfolded x - x at b2_mark_reference|^2 (rumd.py:163-177) */
+#define B2_T_LEN        16
+
+/* b2_stats slots (int64) */
+#define B2_S_STEPS       0   /* MD / minimiser steps since create                     */
+#define B2_S_REBUILDS    1   /* neighbour-list rebuilds since create                  */
+#define B2_S_LAUNCHES    2   /* kernels launched by this library since create         */
+#define B2_S_MAX_NEIGH   3   /* largest neighbour count in the current list           */
+#define B2_S_NEIGH_CAP   4   /* slots per particle in the current list                */
+#define B2_S_LIST_MODE   5   /* 0 = cell list, 1 = all-pairs (box < 3 cells wide)     */
+#define B2_S_NCELLS      6
+#define B2_S_LEN        16
+
+typedef struct b2_ctx b2_ctx;
+
+/* ---- library ---------------------------------------------------------- */
+
+/* ABI version of the loaded library (== B2_ABI_VERSION).
+ * Serves: `backend.version` read by atooms/simulation/core.py:443-444.      */
+int b2_abi_version(void);
+
+/* "cuda-sm_100a" for the product, "oracle-c" for the CPU oracle.            */
+const char *b2_backend_name(void);
+
+/* Message of the last failure on `ctx` (or of the last failed b2_create when
+ * ctx == NULL).  Replaces the engine-output echo of lammps.py:68-73.        */
+const char *b2_last_error(const b2_ctx *ctx);
+
+/* ---- context ----------------------------------------------------------- */
+
+/* Create an engine on CUDA device `device` computing in `precision`
+ * (B2_FP32 | B2_FP64).  Replaces engine construction in
+ * atooms/backends/rumd.py:52-121 / lammps.py:151-202.  Fails with
+ * B2_ENOCUDA when no GPU is usable — there is no CPU fallback.              */
+int b2_create(int device, int precision, b2_ctx **out);
+int b2_destroy(b2_ctx *ctx);
+
+/* Run all work of this context on `cuda_stream` (a cudaStream_t; NULL = the
+ * legacy default stream).  The caller keeps ownership of the stream.        */
+int b2_set_stream(b2_ctx *ctx, void *cuda_stream);
+
+/* ---- model -------------------------------------------------------------- */
+
+/* Orthorhombic periodic cell: atooms/system/cell.py:13-33 (side, center).   */
+int b2_set_box(b2_ctx *ctx, const double side[3], const double center[3]);
+
+/* 12-6 Lennard-Jones table for `nsp` species, row-major nsp x nsp:
+ * u = 4 eps [(sigma/r)^12 - (sigma/r)^6] (- u(rcut) if `shifted`), r < rcut.
+ * `rcut` is absolute.  Replaces the potential definitions the reference
+ * passes to its engines: tests/test_rumd.py:26-31 (Pot_LJ_12_6 SetParams),
+ * tests/test_lammps.py:24-27 (pair_style lj/cut, pair_modify shift).        */
+int b2_set_pair_table(b2_ctx *ctx, int nsp, const double *eps,
+                      const double *sigma, const double *rcut, int shifted);
+
+/* Verlet skin (LAMMPS `neighbor 0.3 bin`, tests/test_lammps.py:27).         */
+int b2_set_skin(b2_ctx *ctx, double skin);
+
+/* ---- state -------------------------------------------------------------- */
+
+/* Copy the particle state to the device (what LAMMPS.run does by writing a
+ * data file, lammps.py:243-246, and RUMD by ReadConf, rumd.py:69-75).
+ * vel == NULL -> zeros; mass == NULL -> 1.0; species are 0-based ids.
+ * Positions are folded into the cell (particle.py:90-99); image counters and
+ * the rmsd reference are reset.                                             */
+int b2_upload(b2_ctx *ctx, int64_t n, const double *pos, const double *vel,
+              const int32_t *species, const double *mass);
+
+/* Replace only positions and/or velocities (either may be NULL) of the
+ * resident particles; used when host views were modified between run()
+ * calls (docs/simulations.org:302-308).                                     */
+int b2_update(b2_ctx *ctx, const double *pos, const double *vel);
+
+/* Copy state back in ORIGINAL particle order; any pointer may be NULL.
+ * `image` is N x 3 int32 box-crossing counters (RUMD GetImages,
+ * rumd.py:172-176).  Replaces the dump read-back of lammps.py:277-285.      */
+int b2_download(b2_ctx *ctx, double *pos, double *vel, int32_t *image);
+
+/* v *= factor   (System.scale_velocities, system.py:227-230)                */
+int b2_scale_velocities(b2_ctx *ctx, double factor);
+
+/* Remember the current unfolded positions as the rmsd origin
+ * (rumd.py:117-121 snapshots `_initial_sample`).                            */
+int b2_mark_reference(b2_ctx *ctx);
+
+/* ---- single point ------------------------------------------------------- */
+
+/* Evaluate the interaction on the resident state.  Serves
+ * InteractionBase.compute (interaction.py:57-82) and the accessors of
+ * system.py:261-335.  Outputs (each may be NULL): energy, virial (scalars),
+ * stress9 (3x3 row-major, sum_{i<j} d_a F_b), forces (N x 3, original
+ * order), pe / vir (N; 1/2 sum_j u_ij and 1/2 sum_j r.F — the RUMD per-
+ * particle columns of data/ka_N256_rho1.185_rumd.xyz.gz).                   */
+int b2_compute(b2_ctx *ctx, int what, double *energy, double *virial,
+               double *stress9, double *forces, double *pe, double *vir);
+
+/* K, U, W, sum F^2, momentum, mass, msd — device reductions behind
+ * System.temperature / kinetic_energy / potential_energy / pressure
+ * (observers.py:247-256).  Recomputes forces if the state changed.          */
+int b2_thermo(b2_ctx *ctx, double out[B2_T_LEN]);
+
+/* Full Verlet list of the current configuration in ORIGINAL numbering, each
+ * row sorted ascending: count[i], nbr[i*stride + k].  Membership rule:
+ * r2 < (rcut_ab + skin)^2 with d - rint(d/L)*L minimum image
+ * (particle.py:129-130) and r2 = (dx*dx + dy*dy) + dz*dz, evaluated in the
+ * context's precision.  nbr may be NULL (counts only).  Returns B2_EINVAL if
+ * stride < max count (max count is written to *max_count first).            */
+int b2_neighbors(b2_ctx *ctx, int32_t *count, int32_t *nbr, int32_t stride,
+                 int32_t *max_count);
+
+/* ---- dynamics ----------------------------------------------------------- */
+
+/* `steps` velocity-Verlet NVE steps of size dt, entirely on the device.
+ * Replaces LAMMPS.run (lammps.py:217-288, `fix nve` :236-238) and RUMD.run
+ * (rumd.py:189-193) as called from Simulation.run_until
+ * (simulation/core.py:308-315).  steps == 0 is a no-op (round-off pin,
+ * tests/test_lammps.py:123-142).                                            */
+int b2_run_nve(b2_ctx *ctx, int64_t steps, double dt);
+
+/* Minimise the potential energy with `method` for at most `max_steps`
+ * iterations; stop early when sum F^2 / N < fn2_tol
+ * (optimization/core.py:34-36).  *converged = 1 if the tolerance was met
+ * (=> backend.reached_steps = False, lammps.py:350-354).  Velocities are
+ * zero on return.  `dt` is the initial FIRE time step / SD step length.     */
+int b2_minimize(b2_ctx *ctx, int method, int64_t max_steps, double dt,
+                double fn2_tol, int64_t *steps_done, int *converged);
+
+/* ---- introspection ------------------------------------------------------ */
+
+int b2_stats(b2_ctx *ctx, int64_t out[B2_S_LEN]);
+
+/* Device time (ms, CUDA events on the context's stream) and kernel-launch
+ * count of the last b2_run_nve / b2_minimize / b2_compute call.             */
+int b2_last_timing(b2_ctx *ctx, double *ms, int64_t *launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ATOOMS_B200_H */
