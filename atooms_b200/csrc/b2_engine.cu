@@ -1,0 +1,1001 @@
+// atooms_b200 engine: context, host orchestration and the C ABI
+// (include/atooms_b200.h).  Pure CUDA runtime; no torch, no CPU fallback.
+#include "../../include/atooms_b200.h"
+#include "b2_common.cuh"
+#include "b2_neigh.cuh"
+#include "b2_force.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#define MAX_RED_BLOCKS 1024
+
+struct b2_ctx {
+    int device = 0, precision = 64;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // model
+    bool have_box = false, have_table = false;
+    double side[3] = {0, 0, 0}, center[3] = {0, 0, 0};
+    int nsp = 0, shifted = 1;
+    double rcut[64], rcut_max = 0, skin = 0.3;
+    PairConst pc;
+    uint64_t const_serial = 0;
+    // particles (sorted order unless noted)
+    int64_t n = 0;
+    void *pos[2] = {nullptr, nullptr}, *vel = nullptr, *frc = nullptr, *vir = nullptr;
+    void *tpos = nullptr, *tvel = nullptr;
+    int *orig = nullptr, *torig = nullptr;
+    int *img = nullptr;        // [3n] by original id
+    double *ref = nullptr;     // [3n] by original id, unfolded, relative to centre
+    // neighbour search
+    Grid grid;
+    uint32_t *keys[2] = {nullptr, nullptr}, *vals[2] = {nullptr, nullptr};
+    int *hist = nullptr, *cell_start = nullptr, *cell_end = nullptr;
+    int ncelltab = 0, sort_blocks = 0, sort_passes = 0;
+    int *nbr = nullptr, *nnb = nullptr;
+    int cap = 0;
+    // control / reductions / staging
+    Ctl *ctl = nullptr, *hctl = nullptr;
+    double *partial = nullptr;
+    double *stage = nullptr;   // device staging, 6n doubles
+    int *stage_i = nullptr;    // 3n ints
+    // host-side knowledge
+    bool list_dirty = true, forces_valid = false, ev_valid = false;
+    int batch = 8;
+    int64_t launches = 0, last_launches = 0, steps_total = 0;
+    double last_ms = 0;
+    char err[512] = "";
+};
+
+static char g_err[512] = "";
+static uint64_t g_const_owner[64];      // per device: serial of the ctx whose table is resident
+static uint64_t g_serial = 0;
+
+static int fail(b2_ctx *c, int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(c ? c->err : g_err, 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(c, e_ == cudaErrorMemoryAllocation ? B2_ENOMEM : B2_ECUDA,        \
+                        "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+#define LAUNCH(kernel, grid, block, ...)                                                  \
+    do {                                                                                  \
+        kernel<<<(grid), (block), 0, c->stream>>>(__VA_ARGS__);                           \
+        c->launches++;                                                                    \
+    } while (0)
+
+static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+template <typename T> static int dev_alloc(b2_ctx *c, T **p, size_t count)
+{
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    CU(cudaMalloc((void **)p, std::max<size_t>(count, 1) * sizeof(T)));
+    return B2_OK;
+}
+
+template <typename R> static Box<R> make_box(const b2_ctx *c)
+{
+    Box<R> b;
+    for (int d = 0; d < 3; d++) {
+        b.L[d] = (R)c->side[d];
+        b.invL[d] = (R)1 / b.L[d];
+    }
+    return b;
+}
+
+static int bind_device(b2_ctx *c)
+{
+    CU(cudaSetDevice(c->device));
+    return B2_OK;
+}
+
+// the pair table lives in __constant__ memory: (re)load it when another
+// context used the device since our last launch
+static int bind_table(b2_ctx *c)
+{
+    if (g_const_owner[c->device] != c->const_serial) {
+        CU(cudaMemcpyToSymbolAsync(g_pair, &c->pc, sizeof(PairConst), 0, cudaMemcpyHostToDevice, c->stream));
+        g_const_owner[c->device] = c->const_serial;
+    }
+    return B2_OK;
+}
+
+static void rebuild_table(b2_ctx *c)
+{
+    for (int a = 0; a < c->nsp * c->nsp; a++) {
+        double rl = c->rcut[a] + c->skin;
+        c->pc.rl2_d[a] = rl * rl;
+        float rlf = (float)rl;
+        c->pc.rl2_f[a] = rlf * rlf;
+    }
+    c->const_serial = ++g_serial;
+}
+
+static int pull_ctl(b2_ctx *c)
+{
+    CU(cudaMemcpyAsync(c->hctl, c->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return B2_OK;
+}
+
+static int push_ctl(b2_ctx *c)
+{
+    CU(cudaMemcpyAsync(c->ctl, c->hctl, sizeof(Ctl), cudaMemcpyHostToDevice, c->stream));
+    return B2_OK;
+}
+
+// ---------------------------------------------------------------------------
+template <typename R> struct Impl {
+    typedef typename Vec4<R>::type V4;
+
+    static int alloc_particles(b2_ctx *c, int64_t n)
+    {
+        int rc;
+        for (int k = 0; k < 2; k++)
+            if ((rc = dev_alloc(c, (V4 **)&c->pos[k], n))) return rc;
+        if ((rc = dev_alloc(c, (V4 **)&c->vel, n))) return rc;
+        if ((rc = dev_alloc(c, (V4 **)&c->frc, n))) return rc;
+        if ((rc = dev_alloc(c, (R **)&c->vir, n))) return rc;
+        if ((rc = dev_alloc(c, (V4 **)&c->tpos, n))) return rc;
+        if ((rc = dev_alloc(c, (V4 **)&c->tvel, n))) return rc;
+        if ((rc = dev_alloc(c, &c->orig, n))) return rc;
+        if ((rc = dev_alloc(c, &c->torig, n))) return rc;
+        if ((rc = dev_alloc(c, &c->img, 3 * n))) return rc;
+        if ((rc = dev_alloc(c, &c->ref, 3 * n))) return rc;
+        for (int k = 0; k < 2; k++) {
+            if ((rc = dev_alloc(c, &c->keys[k], n))) return rc;
+            if ((rc = dev_alloc(c, &c->vals[k], n))) return rc;
+        }
+        if ((rc = dev_alloc(c, &c->nnb, n))) return rc;
+        if ((rc = dev_alloc(c, &c->stage, 6 * n))) return rc;
+        if ((rc = dev_alloc(c, &c->stage_i, 3 * n))) return rc;
+        c->sort_blocks = std::max(1, cdiv(n, SORT_TILE));
+        if ((rc = dev_alloc(c, &c->hist, (size_t)256 * c->sort_blocks))) return rc;
+        size_t np = std::max<size_t>((size_t)MAX_RED_BLOCKS * 9, (size_t)cdiv(n, FORCE_THREADS) * 6);
+        if ((rc = dev_alloc(c, &c->partial, np))) return rc;
+        return B2_OK;
+    }
+
+    static int setup_grid(b2_ctx *c)
+    {
+        // cell width >= (r_cut,max + skin)(1 + 1e-5): every listed pair sits in adjacent cells
+        double rl = (c->rcut_max + c->skin) * (1.0 + 1e-5);
+        Grid &g = c->grid;
+        g.allpairs = 0;
+        int mx = 1;
+        for (int d = 0; d < 3; d++) {
+            int nc = (int)std::floor(c->side[d] / rl);
+            if (nc < 3) g.allpairs = 1;
+            nc = std::min(std::max(nc, 1), 256);
+            g.nc[d] = nc;
+            mx = std::max(mx, nc);
+        }
+        g.cellbits = 1;
+        while ((1 << g.cellbits) < mx) g.cellbits++;
+        if (g.allpairs) { g.cellbits = 1; g.nc[0] = g.nc[1] = g.nc[2] = 1; }
+        int tab = 1 << (3 * g.cellbits);
+        c->sort_passes = (3 * g.cellbits + 7) / 8;
+        if (tab != c->ncelltab || !c->cell_start) {
+            int rc;
+            if ((rc = dev_alloc(c, &c->cell_start, tab))) return rc;
+            if ((rc = dev_alloc(c, &c->cell_end, tab))) return rc;
+            c->ncelltab = tab;
+        }
+        return B2_OK;
+    }
+
+    static int ensure_capacity(b2_ctx *c, int want)
+    {
+        int64_t n = c->n;
+        want = (int)std::min<int64_t>(want, std::max<int64_t>(n - 1, 1));
+        want = (want + 7) / 8 * 8;
+        if (want <= c->cap && c->nbr) return B2_OK;
+        int rc;
+        size_t tiles = (size_t)cdiv(n, 32);
+        if ((rc = dev_alloc(c, &c->nbr, tiles * (size_t)want * 32))) return rc;
+        c->cap = want;
+        return B2_OK;
+    }
+
+    static int upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
+                      const int32_t *species, const double *mass);
+    static int update(b2_ctx *c, const double *pos, const double *vel);
+    static int download(b2_ctx *c, double *pos, double *vel, int32_t *image);
+
+    // -- neighbour refresh (guarded pipeline, enqueue only) -------------------
+    static void enqueue_rebuild(b2_ctx *c)
+    {
+        int n = (int)c->n;
+        Box<R> box = make_box<R>(c);
+        const V4 *p0 = (const V4 *)c->pos[0], *p1 = (const V4 *)c->pos[1];
+        LAUNCH(k_rebuild_begin, 1, 1, c->ctl);
+        if (!c->grid.allpairs) {
+            LAUNCH(k_cell_keys<R>, cdiv(n, 256), 256, c->ctl, p0, p1, n, box, c->grid, c->keys[0], c->vals[0]);
+            int src = 0;
+            for (int pass = 0; pass < c->sort_passes; pass++) {
+                LAUNCH(k_sort_hist, c->sort_blocks, SORT_THREADS, c->ctl, c->keys[src], n, 8 * pass, c->sort_blocks, c->hist);
+                LAUNCH(k_sort_scan, 1, 1024, c->ctl, c->hist, 256 * c->sort_blocks);
+                LAUNCH(k_sort_scatter, c->sort_blocks, SORT_THREADS, c->ctl, c->keys[src], c->vals[src],
+                       c->keys[src ^ 1], c->vals[src ^ 1], n, 8 * pass, c->sort_blocks, c->hist);
+                src ^= 1;
+            }
+            LAUNCH(k_gather<R>, cdiv(n, 256), 256, c->ctl, c->vals[src], n, p0, p1, (const V4 *)c->vel, c->orig,
+                   (V4 *)c->tpos, (V4 *)c->tvel, c->torig);
+            LAUNCH(k_gather_commit<R>, cdiv(n, 256), 256, c->ctl, n, (const V4 *)c->tpos, (const V4 *)c->tvel,
+                   c->torig, (V4 *)c->pos[0], (V4 *)c->pos[1], (V4 *)c->vel, c->orig);
+            LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
+            LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
+        }
+        LAUNCH(k_build_list<R>, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
+               c->nbr, c->nnb, c->cap);
+        LAUNCH(k_rebuild_finish, 1, 1, c->ctl);
+    }
+
+    // make the list valid for the current configuration (synchronises)
+    static int ensure_list(b2_ctx *c)
+    {
+        int rc;
+        if ((rc = bind_table(c))) return rc;
+        if (!c->list_dirty) return B2_OK;
+        if (c->n == 0) { c->list_dirty = false; return B2_OK; }
+        if ((rc = setup_grid(c))) return rc;
+        if (c->cap == 0) {
+            double rl = c->rcut_max + c->skin;
+            double vol = c->side[0] * c->side[1] * c->side[2];
+            double nbar = (double)c->n / vol * 4.18879 * rl * rl * rl;
+            if ((rc = ensure_capacity(c, (int)(1.3 * nbar) + 24))) return rc;
+        }
+        for (int attempt = 0; attempt < 8; attempt++) {
+            if ((rc = pull_ctl(c))) return rc;
+            c->hctl->halt_rebuild = 1u;
+            c->hctl->overflow = 0u;
+            c->hctl->half_skin = 0.5 * c->skin;
+            if ((rc = push_ctl(c))) return rc;
+            enqueue_rebuild(c);
+            if ((rc = pull_ctl(c))) return rc;
+            CU(cudaGetLastError());
+            if (!c->hctl->overflow) {
+                c->list_dirty = false;
+                return B2_OK;
+            }
+            if ((rc = ensure_capacity(c, (int)(c->hctl->max_count * 1.15) + 8))) return rc;
+        }
+        return fail(c, B2_ECUDA, "neighbour list did not fit after 8 attempts (max count %u, capacity %d)",
+                    c->hctl->max_count, c->cap);
+    }
+
+    template <bool EV, bool STRESS>
+    static void enqueue_force(b2_ctx *c, bool guarded)
+    {
+        ForceArgs<R> a;
+        a.ctl = c->ctl;
+        a.pos[0] = (const V4 *)c->pos[0];
+        a.pos[1] = (const V4 *)c->pos[1];
+        a.frc = (V4 *)c->frc;
+        a.vir = (R *)c->vir;
+        a.nbr = c->nbr;
+        a.nnb = c->nnb;
+        a.partial = c->partial;
+        a.n = (int)c->n;
+        a.cap = c->cap;
+        a.guarded = guarded ? 1 : 0;
+        a.box = make_box<R>(c);
+        auto kern = k_force<R, EV, STRESS>;
+        LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
+    }
+
+    // forces + per-particle energy/virial of the current configuration
+    static int ensure_forces(b2_ctx *c)
+    {
+        int rc;
+        if ((rc = ensure_list(c))) return rc;
+        if (c->forces_valid && c->ev_valid) return B2_OK;
+        if (c->n > 0) enqueue_force<true, false>(c, false);
+        c->forces_valid = c->ev_valid = true;
+        return B2_OK;
+    }
+
+    static int thermo(b2_ctx *c, double *out, bool want_stress, double *stress9);
+    static int run_nve(b2_ctx *c, int64_t steps, double dt);
+    static int minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double tol,
+                        int64_t *steps_done, int *converged);
+    static int neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, int32_t *max_count);
+    static int mark_reference(b2_ctx *c);
+    static int compute(b2_ctx *c, int what, double *energy, double *virial, double *stress9,
+                       double *forces, double *pe, double *vir);
+};
+
+// ---- staging kernels ---------------------------------------------------------
+template <typename R>
+__global__ void k_ingest(const double *__restrict__ spos, const double *__restrict__ svel,
+                         const int *__restrict__ sspe, const double *__restrict__ smass, int n,
+                         double cx, double cy, double cz, double Lx, double Ly, double Lz,
+                         typename Vec4<R>::type *__restrict__ pos, typename Vec4<R>::type *__restrict__ vel,
+                         int *__restrict__ orig, int *__restrict__ img, double *__restrict__ ref)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // fold in double (particle.py:90-99), then narrow to the working precision
+    double px = spos[3 * i] - cx, py = spos[3 * i + 1] - cy, pz = spos[3 * i + 2] - cz;
+    px -= rint(px / Lx) * Lx; py -= rint(py / Ly) * Ly; pz -= rint(pz / Lz) * Lz;
+    R x = (R)px, y = (R)py, z = (R)pz;
+    pos[i] = make4(x, y, z, type_as((R)0, sspe[i]));
+    vel[i] = make4((R)(svel ? svel[3 * i] : 0.0), (R)(svel ? svel[3 * i + 1] : 0.0),
+                   (R)(svel ? svel[3 * i + 2] : 0.0), (R)(smass ? smass[i] : 1.0));
+    orig[i] = i;
+    img[3 * i] = img[3 * i + 1] = img[3 * i + 2] = 0;
+    ref[3 * i] = (double)x; ref[3 * i + 1] = (double)y; ref[3 * i + 2] = (double)z;
+}
+
+template <typename R>
+__global__ void k_update(const Ctl *__restrict__ ctl, const double *__restrict__ spos,
+                         const double *__restrict__ svel, int n, double cx, double cy, double cz,
+                         double Lx, double Ly, double Lz, typename Vec4<R>::type *pos0,
+                         typename Vec4<R>::type *pos1, typename Vec4<R>::type *__restrict__ vel,
+                         const int *__restrict__ orig, int *__restrict__ img)
+{
+    typedef typename Vec4<R>::type V4;
+    V4 *pos = ctl->cur ? pos1 : pos0;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    size_t o = 3 * (size_t)orig[s];
+    if (spos) {
+        double px = spos[o] - cx, py = spos[o + 1] - cy, pz = spos[o + 2] - cz;
+        double kx = rint(px / Lx), ky = rint(py / Ly), kz = rint(pz / Lz);
+        img[o] += (int)kx; img[o + 1] += (int)ky; img[o + 2] += (int)kz;
+        V4 p = pos[s];
+        pos[s] = make4((R)(px - kx * Lx), (R)(py - ky * Ly), (R)(pz - kz * Lz), p.w);
+    }
+    if (svel) {
+        V4 v = vel[s];
+        vel[s] = make4((R)svel[o], (R)svel[o + 1], (R)svel[o + 2], v.w);
+    }
+}
+
+template <typename R>
+__global__ void k_export(const Ctl *__restrict__ ctl, int n, double cx, double cy, double cz,
+                         const typename Vec4<R>::type *pos0, const typename Vec4<R>::type *pos1,
+                         const typename Vec4<R>::type *__restrict__ vel,
+                         const typename Vec4<R>::type *__restrict__ frc, const R *__restrict__ vir,
+                         const int *__restrict__ orig, double *__restrict__ opos,
+                         double *__restrict__ ovel, double *__restrict__ ofrc,
+                         double *__restrict__ ope, double *__restrict__ ovir)
+{
+    typedef typename Vec4<R>::type V4;
+    const V4 *pos = ctl->cur ? pos1 : pos0;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    size_t o = (size_t)orig[s];
+    if (opos) {
+        V4 p = pos[s];
+        opos[3 * o] = (double)p.x + cx; opos[3 * o + 1] = (double)p.y + cy; opos[3 * o + 2] = (double)p.z + cz;
+    }
+    if (ovel) {
+        V4 v = vel[s];
+        ovel[3 * o] = v.x; ovel[3 * o + 1] = v.y; ovel[3 * o + 2] = v.z;
+    }
+    if (ofrc || ope) {
+        V4 f = frc[s];
+        if (ofrc) { ofrc[3 * o] = f.x; ofrc[3 * o + 1] = f.y; ofrc[3 * o + 2] = f.z; }
+        if (ope) ope[o] = f.w;
+    }
+    if (ovir) ovir[o] = vir[s];
+}
+
+template <typename R>
+__global__ void k_mark_ref(const Ctl *__restrict__ ctl, int n, const typename Vec4<R>::type *pos0,
+                           const typename Vec4<R>::type *pos1, const int *__restrict__ orig,
+                           const int *__restrict__ img, Box<R> box, double *__restrict__ ref)
+{
+    typedef typename Vec4<R>::type V4;
+    const V4 *pos = ctl->cur ? pos1 : pos0;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    size_t o = 3 * (size_t)orig[s];
+    V4 p = pos[s];
+    ref[o] = (double)p.x + (double)img[o] * (double)box.L[0];
+    ref[o + 1] = (double)p.y + (double)img[o + 1] * (double)box.L[1];
+    ref[o + 2] = (double)p.z + (double)img[o + 2] * (double)box.L[2];
+}
+
+// export the list in original numbering: out[orig[s]*stride + k] = orig[nbr]
+__global__ void k_export_list(int n, const int *__restrict__ nbr, const int *__restrict__ nnb,
+                              const int *__restrict__ orig, int cap, int stride,
+                              int *__restrict__ ocount, int *__restrict__ onbr)
+{
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    int o = orig[s], cnt = nnb[s];
+    ocount[o] = cnt;
+    if (!onbr) return;
+    const int *row = nbr + ((size_t)(s >> 5) * cap) * 32 + (s & 31);
+    for (int k = 0; k < cnt; k++) onbr[(size_t)o * stride + k] = orig[row[(size_t)k * 32]];
+}
+
+__global__ void k_ctl_begin(Ctl *ctl, long long target, int min_mode, double dt, double dt_max, double tol)
+{
+    ctl->steps_done = 0;
+    ctl->steps_target = target;
+    ctl->done = target <= 0 ? 1u : 0u;
+    ctl->converged = 0u;
+    ctl->blocks_done = 0u;
+    ctl->vmax2_bits = 0u;
+    ctl->iter = 0;
+    ctl->min_mode = min_mode;
+    ctl->dt_now = dt;
+    ctl->dt_max = dt_max;
+    ctl->alpha = 0.1;
+    ctl->npos = 0;
+    ctl->fn2_tol = tol;
+    ctl->step_len = 0.0;
+}
+
+// ---------------------------------------------------------------------------
+template <typename R>
+int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
+                    const int32_t *species, const double *mass)
+{
+    int rc;
+    if (n != c->n || !c->pos[0]) {
+        if ((rc = alloc_particles(c, n))) return rc;
+        c->cap = 0;
+        if (c->nbr) { cudaFree(c->nbr); c->nbr = nullptr; }
+    }
+    c->n = n;
+    c->list_dirty = true;
+    c->forces_valid = c->ev_valid = false;
+    memset(c->hctl, 0, sizeof(Ctl));
+    c->hctl->halt_rebuild = 1u;
+    c->hctl->half_skin = 0.5 * c->skin;
+    if ((rc = push_ctl(c))) return rc;
+    if (n == 0) return B2_OK;
+    double *spos = c->stage, *svel = c->stage + 3 * n;
+    double *smass = (double *)c->tpos;     // scratch reuse: n doubles fit in n V4
+    CU(cudaMemcpyAsync(spos, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    if (vel) CU(cudaMemcpyAsync(svel, vel, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    if (mass) CU(cudaMemcpyAsync(smass, mass, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->stage_i, species, n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(k_ingest<R>, cdiv(n, 256), 256, spos, vel ? svel : nullptr, c->stage_i, mass ? smass : nullptr,
+           (int)n, c->center[0], c->center[1], c->center[2], c->side[0], c->side[1], c->side[2],
+           (V4 *)c->pos[0], (V4 *)c->vel, c->orig, c->img, c->ref);
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::update(b2_ctx *c, const double *pos, const double *vel)
+{
+    int64_t n = c->n;
+    if (n == 0 || (!pos && !vel)) return B2_OK;
+    double *spos = c->stage, *svel = c->stage + 3 * n;
+    if (pos) CU(cudaMemcpyAsync(spos, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    if (vel) CU(cudaMemcpyAsync(svel, vel, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(k_update<R>, cdiv(n, 256), 256, c->ctl, pos ? spos : nullptr, vel ? svel : nullptr, (int)n,
+           c->center[0], c->center[1], c->center[2], c->side[0], c->side[1], c->side[2],
+           (V4 *)c->pos[0], (V4 *)c->pos[1], (V4 *)c->vel, c->orig, c->img);
+    CU(cudaStreamSynchronize(c->stream));
+    if (pos) {
+        c->list_dirty = true;
+        c->forces_valid = c->ev_valid = false;
+    }
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::download(b2_ctx *c, double *pos, double *vel, int32_t *image)
+{
+    int64_t n = c->n;
+    if (n == 0) return B2_OK;
+    double *spos = c->stage, *svel = c->stage + 3 * n;
+    LAUNCH(k_export<R>, cdiv(n, 256), 256, c->ctl, (int)n, c->center[0], c->center[1], c->center[2],
+           (const V4 *)c->pos[0], (const V4 *)c->pos[1], (const V4 *)c->vel, (const V4 *)c->frc,
+           (const R *)c->vir, c->orig, pos ? spos : nullptr, vel ? svel : nullptr, nullptr, nullptr, nullptr);
+    if (pos) CU(cudaMemcpyAsync(pos, spos, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (vel) CU(cudaMemcpyAsync(vel, svel, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (image) CU(cudaMemcpyAsync(image, c->img, 3 * n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::mark_reference(b2_ctx *c)
+{
+    if (c->n == 0) return B2_OK;
+    LAUNCH(k_mark_ref<R>, cdiv(c->n, 256), 256, c->ctl, (int)c->n, (const V4 *)c->pos[0], (const V4 *)c->pos[1],
+           c->orig, c->img, make_box<R>(c), c->ref);
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::thermo(b2_ctx *c, double *out, bool want_stress, double *stress9)
+{
+    int rc;
+    for (int k = 0; k < B2_T_LEN; k++) out[k] = 0.0;
+    if (c->n == 0) return B2_OK;
+    if ((rc = ensure_forces(c))) return rc;
+    int n = (int)c->n;
+    int nblk = std::min(MAX_RED_BLOCKS, cdiv(n, RED_THREADS));
+    LAUNCH(k_thermo_partial<R>, nblk, RED_THREADS, c->ctl, (const V4 *)c->pos[0], (const V4 *)c->pos[1],
+           (const V4 *)c->vel, (const V4 *)c->frc, (const R *)c->vir, c->orig, c->img, c->ref, n,
+           make_box<R>(c), c->partial);
+    LAUNCH(k_sum_partials, 1, 32, c->partial, nblk, 9, c->ctl->red);
+    if (want_stress) {
+        enqueue_force<true, true>(c, false);
+        LAUNCH(k_sum_partials, 1, 32, c->partial, cdiv(n, FORCE_THREADS), 6, c->ctl->red + Q_S0);
+    }
+    if ((rc = pull_ctl(c))) return rc;
+    CU(cudaGetLastError());
+    const double *r = c->hctl->red;
+    out[B2_T_KINETIC] = r[Q_KIN]; out[B2_T_POTENTIAL] = r[Q_POT]; out[B2_T_VIRIAL] = r[Q_VIR];
+    out[B2_T_FNORM2] = r[Q_FF]; out[B2_T_PX] = r[Q_PX]; out[B2_T_PY] = r[Q_PY]; out[B2_T_PZ] = r[Q_PZ];
+    out[B2_T_MASS] = r[Q_MASS]; out[B2_T_MSD] = r[Q_MSD];
+    if (want_stress && stress9) {
+        const double *s = r + Q_S0;   // xx xy xz yy yz zz
+        stress9[0] = s[0]; stress9[1] = s[1]; stress9[2] = s[2];
+        stress9[3] = s[1]; stress9[4] = s[3]; stress9[5] = s[4];
+        stress9[6] = s[2]; stress9[7] = s[4]; stress9[8] = s[5];
+    }
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::compute(b2_ctx *c, int what, double *energy, double *virial, double *stress9,
+                     double *forces, double *pe, double *vir)
+{
+    int rc;
+    double t[B2_T_LEN];
+    bool want_stress = (what & B2_STRESS) && stress9;
+    if ((rc = thermo(c, t, want_stress, stress9))) return rc;
+    if (energy) *energy = t[B2_T_POTENTIAL];
+    if (virial) *virial = t[B2_T_VIRIAL];
+    if (c->n == 0) {
+        if (want_stress) memset(stress9, 0, 9 * sizeof(double));
+        return B2_OK;
+    }
+    if (forces || pe || vir) {
+        int64_t n = c->n;
+        double *sf = c->stage, *spe = c->stage + 3 * n, *sv = c->stage + 4 * n;
+        LAUNCH(k_export<R>, cdiv(n, 256), 256, c->ctl, (int)n, 0.0, 0.0, 0.0, (const V4 *)c->pos[0],
+               (const V4 *)c->pos[1], (const V4 *)c->vel, (const V4 *)c->frc, (const R *)c->vir, c->orig,
+               nullptr, nullptr, forces ? sf : nullptr, pe ? spe : nullptr, vir ? sv : nullptr);
+        if (forces) CU(cudaMemcpyAsync(forces, sf, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        if (pe) CU(cudaMemcpyAsync(pe, spe, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        if (vir) CU(cudaMemcpyAsync(vir, sv, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, int32_t *max_count)
+{
+    int rc;
+    int64_t n = c->n;
+    if (max_count) *max_count = 0;
+    if (n == 0) return B2_OK;
+    // always the list of the CURRENT configuration
+    c->list_dirty = true;
+    if ((rc = ensure_list(c))) return rc;
+    int mx = (int)c->hctl->max_count;
+    if (max_count) *max_count = mx;
+    if (nbr && stride < mx) return fail(c, B2_EINVAL, "b2_neighbors: stride %d smaller than max count %d", stride, mx);
+    int *ocount = c->stage_i, *onbr = nullptr;
+    if (nbr) CU(cudaMalloc((void **)&onbr, (size_t)n * stride * sizeof(int)));
+    LAUNCH(k_export_list, cdiv(n, 128), 128, (int)n, c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
+    std::vector<int32_t> hc((size_t)n);
+    CU(cudaMemcpyAsync(hc.data(), ocount, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (nbr) CU(cudaMemcpyAsync(nbr, onbr, (size_t)n * stride * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (onbr) cudaFree(onbr);
+    for (int64_t i = 0; i < n; i++) {
+        if (count) count[i] = hc[i];
+        if (nbr) std::sort(nbr + i * stride, nbr + i * stride + hc[i]);
+    }
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
+{
+    int rc;
+    if (steps == 0 || c->n == 0) return B2_OK;
+    int n = (int)c->n;
+    if ((rc = ensure_forces(c))) return rc;
+    // opening half kick (backwards): velocities move to t - dt/2
+    LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(-0.5 * dt));
+    LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0);
+    StepArgs<R> a;
+    a.ctl = c->ctl;
+    a.pos[0] = (V4 *)c->pos[0];
+    a.pos[1] = (V4 *)c->pos[1];
+    a.vel = (V4 *)c->vel;
+    a.nbr = c->nbr;
+    a.nnb = c->nnb;
+    a.orig = c->orig;
+    a.img = c->img;
+    a.n = n;
+    a.cap = c->cap;
+    a.kick = (R)dt;
+    a.drift = (R)dt;
+    a.box = make_box<R>(c);
+    int64_t done = 0;
+    while (done < steps) {
+        // speculative batches: [guarded refresh][batch x step]; steps after the
+        // displacement bound trips are no-ops until the next refresh
+        int64_t remaining = steps - done;
+        int64_t quota = std::min<int64_t>(remaining + c->batch, 4096);
+        for (int64_t launched = 0; launched < quota;) {
+            enqueue_rebuild(c);
+            int m = (int)std::min<int64_t>(c->batch, quota - launched);
+            for (int k = 0; k < m; k++) LAUNCH(k_step_nve<R>, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
+            launched += m;
+        }
+        long long rb0 = c->hctl->rebuilds;
+        if ((rc = pull_ctl(c))) return rc;
+        CU(cudaGetLastError());
+        int64_t progressed = c->hctl->steps_done - done;
+        done = c->hctl->steps_done;
+        if (c->hctl->overflow) {
+            if ((rc = ensure_capacity(c, (int)(c->hctl->max_count * 1.15) + 8))) return rc;
+            a.nbr = c->nbr;
+            a.cap = c->cap;
+            c->hctl->overflow = 0u;
+            if ((rc = push_ctl(c))) return rc;
+        } else {
+            long long nrb = c->hctl->rebuilds - rb0;
+            if (nrb > 0 && progressed > 0)   // refresh period seen in this round -> batch length
+                c->batch = (int)std::min<int64_t>(std::max<int64_t>(progressed / nrb, 1), 64);
+        }
+    }
+    // closing half kick at the final configuration
+    c->list_dirty = c->hctl->halt_rebuild != 0u;
+    c->forces_valid = c->ev_valid = false;
+    if ((rc = ensure_forces(c))) return rc;
+    LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(0.5 * dt));
+    c->steps_total += steps;
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double tol,
+                      int64_t *steps_done, int *converged)
+{
+    int rc;
+    *steps_done = 0;
+    *converged = 0;
+    if (c->n == 0) { *converged = 1; return B2_OK; }
+    int n = (int)c->n;
+    if ((rc = ensure_list(c))) return rc;
+    LAUNCH(k_scale_vel<R>, cdiv(n, 256), 256, (V4 *)c->vel, n, (R)0);
+    LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)max_steps, method == B2_MIN_FIRE ? MIN_MODE_FIRE : MIN_MODE_SD,
+           dt, 10.0 * dt, tol);
+    // k_ctl_begin marks a zero budget as done; the first iteration must still test convergence
+    MinArgs<R> a;
+    a.ctl = c->ctl;
+    a.pos[0] = (V4 *)c->pos[0];
+    a.pos[1] = (V4 *)c->pos[1];
+    a.vel = (V4 *)c->vel;
+    a.frc = (const V4 *)c->frc;
+    a.orig = c->orig;
+    a.img = c->img;
+    a.n = n;
+    a.box = make_box<R>(c);
+    int nblk = std::min(MAX_RED_BLOCKS, cdiv(n, RED_THREADS));
+    if (max_steps == 0) {
+        if ((rc = pull_ctl(c))) return rc;
+        c->hctl->done = 0u;
+        if ((rc = push_ctl(c))) return rc;
+    }
+    for (;;) {
+        int64_t budget = std::min<int64_t>(max_steps + 1, 2048);
+        for (int64_t launched = 0; launched < budget;) {
+            enqueue_rebuild(c);
+            int m = (int)std::min<int64_t>(c->batch, budget - launched);
+            for (int k = 0; k < m; k++) {
+                enqueue_force<true, false>(c, true);
+                LAUNCH(k_min_partial<R>, nblk, RED_THREADS, c->ctl, (const V4 *)c->vel, (const V4 *)c->frc, n, c->partial);
+                LAUNCH(k_min_logic, 1, 1, c->ctl, c->partial, nblk, n);
+                LAUNCH(k_min_step<R>, cdiv(n, RED_THREADS), RED_THREADS, a);
+            }
+            launched += m;
+        }
+        if ((rc = pull_ctl(c))) return rc;
+        CU(cudaGetLastError());
+        if (c->hctl->overflow) {
+            if ((rc = ensure_capacity(c, (int)(c->hctl->max_count * 1.15) + 8))) return rc;
+            c->hctl->overflow = 0u;
+            if ((rc = push_ctl(c))) return rc;
+            continue;
+        }
+        if (c->hctl->done) break;
+    }
+    *steps_done = c->hctl->iter;
+    *converged = (int)c->hctl->converged;
+    c->steps_total += c->hctl->iter;
+    // forces / energies of the final configuration are the ones just computed
+    LAUNCH(k_scale_vel<R>, cdiv(n, 256), 256, (V4 *)c->vel, n, (R)0);
+    c->list_dirty = c->hctl->halt_rebuild != 0u;
+    c->forces_valid = c->ev_valid = true;
+    return B2_OK;
+}
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+#define DISPATCH(fn, ...) (c->precision == B2_FP32 ? Impl<float>::fn(__VA_ARGS__) : Impl<double>::fn(__VA_ARGS__))
+
+struct Timed {
+    b2_ctx *c;
+    int64_t l0;
+    explicit Timed(b2_ctx *ctx) : c(ctx), l0(ctx->launches) { cudaEventRecord(c->ev0, c->stream); }
+    ~Timed()
+    {
+        cudaEventRecord(c->ev1, c->stream);
+        cudaEventSynchronize(c->ev1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        c->last_ms = ms;
+        c->last_launches = c->launches - l0;
+    }
+};
+
+extern "C" {
+
+int b2_abi_version(void) { return B2_ABI_VERSION; }
+const char *b2_backend_name(void) { return "cuda-sm_100a"; }
+const char *b2_last_error(const b2_ctx *c) { return c ? c->err : g_err; }
+
+int b2_create(int device, int precision, b2_ctx **out)
+{
+    if (!out) return fail(nullptr, B2_EINVAL, "b2_create: out is NULL");
+    *out = nullptr;
+    if (precision != B2_FP32 && precision != B2_FP64)
+        return fail(nullptr, B2_EINVAL, "b2_create: precision must be 32 or 64");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, B2_ENOCUDA, "b2_create: no usable CUDA device (%s); this library has no CPU path",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= ndev || device >= 64)
+        return fail(nullptr, B2_EINVAL, "b2_create: device %d out of range (0..%d)", device, ndev - 1);
+    b2_ctx *ctx = new b2_ctx();
+    ctx->device = device;
+    ctx->precision = precision;
+    memset(&ctx->pc, 0, sizeof(PairConst));
+    memset(&ctx->grid, 0, sizeof(Grid));
+    int rc = B2_OK;
+    do {
+        if ((e = cudaSetDevice(device)) != cudaSuccess) break;
+        if ((e = cudaMalloc((void **)&ctx->ctl, sizeof(Ctl))) != cudaSuccess) break;
+        if ((e = cudaMemset(ctx->ctl, 0, sizeof(Ctl))) != cudaSuccess) break;
+        if ((e = cudaMallocHost((void **)&ctx->hctl, sizeof(Ctl))) != cudaSuccess) break;
+        memset(ctx->hctl, 0, sizeof(Ctl));
+        if ((e = cudaEventCreate(&ctx->ev0)) != cudaSuccess) break;
+        if ((e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) break;
+    } while (0);
+    if (e != cudaSuccess) {
+        rc = fail(nullptr, B2_ECUDA, "b2_create: %s", cudaGetErrorString(e));
+        delete ctx;
+        return rc;
+    }
+    *out = ctx;
+    return B2_OK;
+}
+
+int b2_destroy(b2_ctx *c)
+{
+    if (!c) return B2_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig,
+                    c->img, c->ref, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
+                    c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    if (c->hctl) cudaFreeHost(c->hctl);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (g_const_owner[c->device] == c->const_serial) g_const_owner[c->device] = 0;
+    delete c;
+    return B2_OK;
+}
+
+int b2_set_stream(b2_ctx *c, void *cuda_stream)
+{
+    if (!c) return fail(nullptr, B2_EINVAL, "NULL context");
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->stream = (cudaStream_t)cuda_stream;
+    return B2_OK;
+}
+
+int b2_set_box(b2_ctx *c, const double side[3], const double center[3])
+{
+    if (!c || !side) return fail(c, B2_EINVAL, "b2_set_box: NULL argument");
+    for (int d = 0; d < 3; d++) {
+        if (!(side[d] > 0.0)) return fail(c, B2_EINVAL, "b2_set_box: side must be > 0");
+        c->side[d] = side[d];
+        c->center[d] = center ? center[d] : 0.0;
+    }
+    c->have_box = true;
+    c->list_dirty = true;
+    c->forces_valid = c->ev_valid = false;
+    return B2_OK;
+}
+
+int b2_set_pair_table(b2_ctx *c, int nsp, const double *eps, const double *sigma, const double *rcut, int shifted)
+{
+    if (!c || !eps || !sigma || !rcut) return fail(c, B2_EINVAL, "b2_set_pair_table: NULL argument");
+    if (nsp < 1 || nsp > B2_MAXSP) return fail(c, B2_EINVAL, "b2_set_pair_table: 1 <= nsp <= %d", B2_MAXSP);
+    for (int a = 0; a < nsp * nsp; a++)
+        if (!(sigma[a] > 0.0) || !(rcut[a] > 0.0))
+            return fail(c, B2_EINVAL, "b2_set_pair_table: sigma and rcut must be > 0");
+    memset(&c->pc, 0, sizeof(PairConst));
+    c->nsp = c->pc.nsp = nsp;
+    c->shifted = shifted;
+    c->rcut_max = 0;
+    for (int a = 0; a < nsp * nsp; a++) {
+        // same expression order as the oracles (oracle_np.PairTable, oracle_c.c)
+        double s2 = sigma[a] * sigma[a];
+        double s6 = s2 * s2 * s2;
+        c->pc.c6[a] = 4.0 * eps[a] * s6;
+        c->pc.c12[a] = 4.0 * eps[a] * s6 * s6;
+        c->rcut[a] = rcut[a];
+        c->pc.rc2[a] = rcut[a] * rcut[a];
+        double ir2 = 1.0 / c->pc.rc2[a];
+        double ir6 = ir2 * ir2 * ir2;
+        c->pc.ushift[a] = shifted ? ir6 * (c->pc.c12[a] * ir6 - c->pc.c6[a]) : 0.0;
+        c->rcut_max = std::max(c->rcut_max, rcut[a]);
+    }
+    rebuild_table(c);
+    c->have_table = true;
+    c->list_dirty = true;
+    c->forces_valid = c->ev_valid = false;
+    c->cap = 0;
+    return B2_OK;
+}
+
+int b2_set_skin(b2_ctx *c, double skin)
+{
+    if (!c || !(skin >= 0.0)) return fail(c, B2_EINVAL, "b2_set_skin: skin must be >= 0");
+    c->skin = skin;
+    if (c->have_table) rebuild_table(c);
+    c->list_dirty = true;
+    c->cap = 0;
+    return B2_OK;
+}
+
+#define NEED_PARTICLES(who)                                                                   \
+    if (!c) return fail(nullptr, B2_EINVAL, who ": NULL context");                            \
+    if (!c->pos[0]) return fail(c, B2_ESTATE, who ": no particles resident (call b2_upload)"); \
+    { int rc_ = bind_device(c); if (rc_) return rc_; }
+
+int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel, const int32_t *species,
+              const double *mass)
+{
+    if (!c || n < 0 || (n > 0 && (!pos || !species))) return fail(c, B2_EINVAL, "b2_upload: bad argument");
+    if (n > 0x7fffff00LL) return fail(c, B2_EINVAL, "b2_upload: at most 2^31 particles per context");
+    if (!c->have_box) return fail(c, B2_ESTATE, "b2_upload: call b2_set_box first");
+    if (!c->have_table) return fail(c, B2_ESTATE, "b2_upload: call b2_set_pair_table first");
+    for (int64_t i = 0; i < n; i++) {
+        if (species[i] < 0 || species[i] >= c->nsp)
+            return fail(c, B2_EINVAL, "b2_upload: species id %d of particle %lld outside the pair table",
+                        species[i], (long long)i);
+        if (mass && !(mass[i] > 0.0)) return fail(c, B2_EINVAL, "b2_upload: mass must be > 0");
+    }
+    int rc = bind_device(c);
+    if (rc) return rc;
+    return DISPATCH(upload, c, n, pos, vel, species, mass);
+}
+
+int b2_update(b2_ctx *c, const double *pos, const double *vel)
+{
+    NEED_PARTICLES("b2_update");
+    return DISPATCH(update, c, pos, vel);
+}
+
+int b2_download(b2_ctx *c, double *pos, double *vel, int32_t *image)
+{
+    NEED_PARTICLES("b2_download");
+    return DISPATCH(download, c, pos, vel, image);
+}
+
+int b2_scale_velocities(b2_ctx *c, double factor)
+{
+    NEED_PARTICLES("b2_scale_velocities");
+    if (c->n == 0) return B2_OK;
+    if (c->precision == B2_FP32)
+        LAUNCH(k_scale_vel<float>, cdiv(c->n, 256), 256, (float4 *)c->vel, (int)c->n, (float)factor);
+    else
+        LAUNCH(k_scale_vel<double>, cdiv(c->n, 256), 256, (double4 *)c->vel, (int)c->n, factor);
+    return B2_OK;
+}
+
+int b2_mark_reference(b2_ctx *c)
+{
+    NEED_PARTICLES("b2_mark_reference");
+    return DISPATCH(mark_reference, c);
+}
+
+int b2_compute(b2_ctx *c, int what, double *energy, double *virial, double *stress9, double *forces,
+               double *pe, double *vir)
+{
+    NEED_PARTICLES("b2_compute");
+    if (what & ~(B2_ENERGY | B2_FORCES | B2_VIRIAL | B2_STRESS))
+        return fail(c, B2_EUNSUPPORTED, "b2_compute: unsupported observable mask 0x%x", what);
+    Timed t(c);
+    return DISPATCH(compute, c, what, energy, virial, stress9, forces, pe, vir);
+}
+
+int b2_thermo(b2_ctx *c, double out[B2_T_LEN])
+{
+    NEED_PARTICLES("b2_thermo");
+    if (!out) return fail(c, B2_EINVAL, "b2_thermo: out is NULL");
+    return DISPATCH(thermo, c, out, false, nullptr);
+}
+
+int b2_neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, int32_t *max_count)
+{
+    NEED_PARTICLES("b2_neighbors");
+    return DISPATCH(neighbors, c, count, nbr, stride, max_count);
+}
+
+int b2_run_nve(b2_ctx *c, int64_t steps, double dt)
+{
+    NEED_PARTICLES("b2_run_nve");
+    if (steps < 0 || !(dt > 0.0)) return fail(c, B2_EINVAL, "b2_run_nve: steps >= 0 and dt > 0 required");
+    Timed t(c);
+    return DISPATCH(run_nve, c, steps, dt);
+}
+
+int b2_minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double fn2_tol, int64_t *steps_done,
+                int *converged)
+{
+    NEED_PARTICLES("b2_minimize");
+    if (max_steps < 0 || !(dt > 0.0) || !steps_done || !converged)
+        return fail(c, B2_EINVAL, "b2_minimize: bad argument");
+    if (method != B2_MIN_SD && method != B2_MIN_FIRE) return fail(c, B2_EINVAL, "b2_minimize: unknown method %d", method);
+    Timed t(c);
+    return DISPATCH(minimize, c, method, max_steps, dt, fn2_tol, steps_done, converged);
+}
+
+int b2_stats(b2_ctx *c, int64_t out[B2_S_LEN])
+{
+    if (!c || !out) return fail(c, B2_EINVAL, "b2_stats: NULL argument");
+    for (int k = 0; k < B2_S_LEN; k++) out[k] = 0;
+    out[B2_S_STEPS] = c->steps_total;
+    out[B2_S_REBUILDS] = c->hctl ? c->hctl->rebuilds : 0;
+    out[B2_S_LAUNCHES] = c->launches;
+    out[B2_S_MAX_NEIGH] = c->hctl ? c->hctl->max_count : 0;
+    out[B2_S_NEIGH_CAP] = c->cap;
+    out[B2_S_LIST_MODE] = c->grid.allpairs;
+    out[B2_S_NCELLS] = (int64_t)c->grid.nc[0] * c->grid.nc[1] * c->grid.nc[2];
+    return B2_OK;
+}
+
+int b2_last_timing(b2_ctx *c, double *ms, int64_t *launches)
+{
+    if (!c) return fail(nullptr, B2_EINVAL, "NULL context");
+    if (ms) *ms = c->last_ms;
+    if (launches) *launches = c->last_launches;
+    return B2_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,453 @@
+// Pair force / energy / virial evaluation over the Verlet list, the fused
+// velocity-Verlet step, minimiser updates and the device reductions.
+#pragma once
+#include "b2_common.cuh"
+
+#define FORCE_THREADS 128
+#define RED_THREADS 256
+
+
+template <typename R> struct PairTab {       // per-block copy of the pair table
+    R c12[B2_MAXSP * B2_MAXSP], c6[B2_MAXSP * B2_MAXSP], rc2[B2_MAXSP * B2_MAXSP],
+      ush[B2_MAXSP * B2_MAXSP];
+};
+
+template <typename R>
+__device__ __forceinline__ void load_pair_table(PairTab<R> &t)
+{
+    for (int a = threadIdx.x; a < B2_MAXSP * B2_MAXSP; a += blockDim.x) {
+        t.c12[a] = (R)g_pair.c12[a];
+        t.c6[a] = (R)g_pair.c6[a];
+        t.rc2[a] = (R)g_pair.rc2[a];
+        t.ush[a] = (R)g_pair.ushift[a];
+    }
+}
+
+// One particle against its Verlet row.  Pair expressions are the oracle's:
+//   r2inv = 1/r2 ; r6inv = r2inv^3
+//   u = r6inv (c12 r6inv - c6) - ushift ;  w = r6inv (12 c12 r6inv - 6 c6) = r.F
+//   F_i += (w r2inv) d ,  d = r_i - r_j  (minimum image, particle.py:129-130)
+template <typename R, bool EV, bool STRESS>
+__device__ __forceinline__ void pair_row(const typename Vec4<R>::type *__restrict__ pos,
+                                         const int *__restrict__ row, int cnt,
+                                         typename Vec4<R>::type pi, const Box<R> &box,
+                                         const PairTab<R> &tab, int nsp,
+                                         R &fx, R &fy, R &fz, R &pe, R &vir, R *st)
+{
+    typedef typename Vec4<R>::type V4;
+    const int ti = type_of(pi.w) * nsp;
+    const R Lx = box.L[0], Ly = box.L[1], Lz = box.L[2];
+    const R ix = box.invL[0], iy = box.invL[1], iz = box.invL[2];
+    int k = 0;
+#define B2_PAIR(PJ)                                                                   \
+    {                                                                                 \
+        R dx = pi.x - PJ.x, dy = pi.y - PJ.y, dz = pi.z - PJ.z;                       \
+        dx -= Lx * r_rint(dx * ix);                                                   \
+        dy -= Ly * r_rint(dy * iy);                                                   \
+        dz -= Lz * r_rint(dz * iz);                                                   \
+        R r2 = dx * dx + dy * dy + dz * dz;                                           \
+        int a = ti + type_of(PJ.w);                                                   \
+        if (r2 < tab.rc2[a]) {                                                        \
+            R r2inv = r_rcp(r2);                                                      \
+            R r6inv = r2inv * r2inv * r2inv;                                          \
+            R c12 = tab.c12[a], c6 = tab.c6[a];                                       \
+            R w = r6inv * ((R)12 * c12 * r6inv - (R)6 * c6);                          \
+            R fp = w * r2inv;                                                         \
+            fx += fp * dx; fy += fp * dy; fz += fp * dz;                              \
+            if (EV) { pe += r6inv * (c12 * r6inv - c6) - tab.ush[a]; vir += w; }      \
+            if (STRESS) {                                                             \
+                st[0] += dx * fp * dx; st[1] += dx * fp * dy; st[2] += dx * fp * dz;  \
+                st[3] += dy * fp * dy; st[4] += dy * fp * dz; st[5] += dz * fp * dz;  \
+            }                                                                         \
+        }                                                                             \
+    }
+    for (; k + 4 <= cnt; k += 4) {
+        int j0 = ld_stream(row + (size_t)(k + 0) * 32);
+        int j1 = ld_stream(row + (size_t)(k + 1) * 32);
+        int j2 = ld_stream(row + (size_t)(k + 2) * 32);
+        int j3 = ld_stream(row + (size_t)(k + 3) * 32);
+        V4 p0 = pos[j0], p1 = pos[j1], p2 = pos[j2], p3 = pos[j3];
+        B2_PAIR(p0) B2_PAIR(p1) B2_PAIR(p2) B2_PAIR(p3)
+    }
+    for (; k < cnt; k++) {
+        int j = ld_stream(row + (size_t)k * 32);
+        V4 p0 = pos[j];
+        B2_PAIR(p0)
+    }
+#undef B2_PAIR
+}
+
+template <typename R> struct ForceArgs {
+    Ctl *ctl;
+    const typename Vec4<R>::type *pos[2];
+    typename Vec4<R>::type *frc;    // (fx, fy, fz, pe_i)
+    R *vir;                          // vir_i
+    const int *nbr, *nnb;
+    double *partial;                 // [gridDim][9] stress partial sums (STRESS only)
+    int n, cap, guarded;
+    Box<R> box;
+};
+
+// Forces (+ per-particle energy / virial, + stress partials) of the current
+// configuration, stored.  `guarded` launches obey the speculative-batch flags.
+template <typename R, bool EV, bool STRESS>
+__global__ void __launch_bounds__(FORCE_THREADS)
+k_force(ForceArgs<R> a)
+{
+    typedef typename Vec4<R>::type V4;
+    const Ctl *ctl = a.ctl;
+    if (a.guarded && (ctl->halt_rebuild | ctl->overflow | ctl->done)) return;
+    __shared__ PairTab<R> tab;
+    load_pair_table(tab);
+    __syncthreads();
+    const V4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    R st[6] = {0, 0, 0, 0, 0, 0};
+    if (i < a.n) {
+        V4 pi = pos[i];
+        R fx = 0, fy = 0, fz = 0, pe = 0, vir = 0;
+        const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
+        pair_row<R, EV, STRESS>(pos, row, a.nnb[i], pi, a.box, tab, g_pair.nsp, fx, fy, fz, pe, vir, st);
+        a.frc[i] = make4(fx, fy, fz, (R)0.5 * pe);
+        if (EV) a.vir[i] = (R)0.5 * vir;
+    }
+    if (STRESS) {
+        __shared__ double s_st[FORCE_THREADS / 32][6];
+        int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+            double v = warp_sum((double)st[q]);
+            if (lane == 0) s_st[w][q] = v;
+        }
+        __syncthreads();
+        if (threadIdx.x < 6) {
+            double v = 0;
+            for (int ww = 0; ww < FORCE_THREADS / 32; ww++) v += s_st[ww][threadIdx.x];
+            a.partial[(size_t)blockIdx.x * 6 + threadIdx.x] = 0.5 * v;
+        }
+    }
+}
+
+template <typename R> struct StepArgs {
+    Ctl *ctl;
+    typename Vec4<R>::type *pos[2];
+    typename Vec4<R>::type *vel;     // (vx, vy, vz, mass)
+    const int *nbr, *nnb, *orig;
+    int *img;                        // [3 n] box crossings, by ORIGINAL id
+    int n, cap;
+    R kick, drift;                   // v += kick F/m ; x += drift v
+    Box<R> box;
+};
+
+// The fused velocity-Verlet step (kick-drift form): F(x) -> v += dt F/m ->
+// x += dt v -> fold into the cell (particle.py:90-99) -> max |v|^2 for the
+// displacement bound.  Reads the current position buffer, writes the other;
+// the last block to finish flips the buffers and settles the step's
+// bookkeeping on the device.
+template <typename R>
+__global__ void __launch_bounds__(FORCE_THREADS)
+k_step_nve(StepArgs<R> a)
+{
+    typedef typename Vec4<R>::type V4;
+    Ctl *ctl = a.ctl;
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
+    __shared__ PairTab<R> tab;
+    __shared__ float s_v2[FORCE_THREADS / 32];
+    __shared__ bool s_last;
+    load_pair_table(tab);
+    __syncthreads();
+    const unsigned cur = ctl->cur;
+    const V4 *__restrict__ pos = cur ? a.pos[1] : a.pos[0];
+    V4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float v2 = 0.f;
+    if (i < a.n) {
+        V4 pi = pos[i];
+        R fx = 0, fy = 0, fz = 0, pe = 0, vir = 0;
+        const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
+        pair_row<R, false, false>(pos, row, a.nnb[i], pi, a.box, tab, g_pair.nsp, fx, fy, fz, pe, vir, nullptr);
+        V4 v = a.vel[i];
+        R s = a.kick / v.w;
+        v.x += s * fx; v.y += s * fy; v.z += s * fz;
+        R x = pi.x + a.drift * v.x, y = pi.y + a.drift * v.y, z = pi.z + a.drift * v.z;
+        R kx = r_rint(x * a.box.invL[0]), ky = r_rint(y * a.box.invL[1]), kz = r_rint(z * a.box.invL[2]);
+        if (kx != (R)0 || ky != (R)0 || kz != (R)0) {
+            x -= kx * a.box.L[0]; y -= ky * a.box.L[1]; z -= kz * a.box.L[2];
+            int *im = a.img + 3 * (size_t)a.orig[i];
+            im[0] += (int)kx; im[1] += (int)ky; im[2] += (int)kz;
+        }
+        posn[i] = make4(x, y, z, pi.w);
+        a.vel[i] = v;
+        // rounded up: the bound must never be smaller than the true speed
+        v2 = __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+    }
+    v2 = warp_max(v2);
+    if ((threadIdx.x & 31) == 0) s_v2[threadIdx.x >> 5] = v2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = s_v2[0];
+        for (int w = 1; w < FORCE_THREADS / 32; w++) m = fmaxf(m, s_v2[w]);
+        atomicMax(&ctl->vmax2_bits, __float_as_uint(m));
+        __threadfence();
+        unsigned ticket = atomicAdd(&ctl->blocks_done, 1u);
+        s_last = (ticket == gridDim.x - 1);
+        if (s_last) {
+            __threadfence();
+            float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
+            double bound = ctl->disp_bound + fabs((double)a.drift) * sqrt((double)vm2) * (1.0 + 1e-6);
+            ctl->disp_bound = bound;
+            ctl->cur = cur ^ 1u;
+            long long s = ctl->steps_done + 1;
+            ctl->steps_done = s;
+            if (s >= ctl->steps_target) ctl->done = 1u;
+            if (bound > ctl->half_skin) ctl->halt_rebuild = 1u;
+            ctl->blocks_done = 0u;
+        }
+    }
+}
+
+// v += c F / m   (opening / closing half kick of a run)
+template <typename R>
+__global__ void k_kick(typename Vec4<R>::type *__restrict__ vel,
+                       const typename Vec4<R>::type *__restrict__ frc, int n, R c)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typename Vec4<R>::type v = vel[i], f = frc[i];
+    R s = c / v.w;
+    v.x += s * f.x; v.y += s * f.y; v.z += s * f.z;
+    vel[i] = v;
+}
+
+template <typename R>
+__global__ void k_scale_vel(typename Vec4<R>::type *__restrict__ vel, int n, R c)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typename Vec4<R>::type v = vel[i];
+    v.x *= c; v.y *= c; v.z *= c;
+    vel[i] = v;
+}
+
+// ---- reductions: per-block partials in scratch, one block sums them in a
+// fixed order (deterministic totals, SURVEY.md §7 "summation order") ----------
+template <int NQ>
+__device__ __forceinline__ void block_partials(double (&q)[NQ], double *__restrict__ partial)
+{
+    __shared__ double s_q[RED_THREADS / 32][NQ];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NQ; k++) {
+        double v = warp_sum(q[k]);
+        if (lane == 0) s_q[w][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < NQ) {
+        double v = 0;
+        for (int ww = 0; ww < RED_THREADS / 32; ww++) v += s_q[ww][threadIdx.x];
+        partial[(size_t)blockIdx.x * NQ + threadIdx.x] = v;
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(RED_THREADS)
+k_thermo_partial(const Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0,
+                 const typename Vec4<R>::type *pos1,
+                 const typename Vec4<R>::type *__restrict__ vel,
+                 const typename Vec4<R>::type *__restrict__ frc, const R *__restrict__ vir,
+                 const int *__restrict__ orig, const int *__restrict__ img,
+                 const double *__restrict__ ref, int n, Box<R> box, double *__restrict__ partial)
+{
+    typedef typename Vec4<R>::type V4;
+    const V4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
+    double q[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        V4 v = vel[i], f = frc[i], p = pos[i];
+        double m = (double)v.w;
+        double vx = v.x, vy = v.y, vz = v.z, fx = f.x, fy = f.y, fz = f.z;
+        q[Q_KIN] += 0.5 * m * ((vx * vx + vy * vy) + vz * vz);
+        q[Q_POT] += (double)f.w;
+        q[Q_VIR] += (double)vir[i];
+        q[Q_FF] += (fx * fx + fy * fy) + fz * fz;
+        q[Q_PX] += m * vx; q[Q_PY] += m * vy; q[Q_PZ] += m * vz;
+        q[Q_MASS] += m;
+        size_t o = 3 * (size_t)orig[i];
+        double ux = ((double)p.x + (double)img[o + 0] * (double)box.L[0]) - ref[o + 0];
+        double uy = ((double)p.y + (double)img[o + 1] * (double)box.L[1]) - ref[o + 1];
+        double uz = ((double)p.z + (double)img[o + 2] * (double)box.L[2]) - ref[o + 2];
+        q[Q_MSD] += (ux * ux + uy * uy) + uz * uz;
+    }
+    block_partials<9>(q, partial);
+}
+
+// sum `nblk` rows of `nq` partials into out[0..nq)
+__global__ void k_sum_partials(const double *__restrict__ partial, int nblk, int nq,
+                               double *__restrict__ out)
+{
+    int q = threadIdx.x;
+    if (q >= nq) return;
+    double v = 0;
+    for (int b = 0; b < nblk; b++) v += partial[(size_t)b * nq + q];
+    out[q] = v;
+}
+
+// ---- minimisers -------------------------------------------------------------
+// Shared by FIRE and steepest descent: P = F.v, |v|^2, |F|^2, max_i |F_i|^2.
+template <typename R>
+__global__ void __launch_bounds__(RED_THREADS)
+k_min_partial(const Ctl *__restrict__ ctl, const typename Vec4<R>::type *__restrict__ vel,
+              const typename Vec4<R>::type *__restrict__ frc, int n, double *__restrict__ partial)
+{
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
+    typedef typename Vec4<R>::type V4;
+    double q[4] = {0, 0, 0, 0};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        V4 v = vel[i], f = frc[i];
+        double vx = v.x, vy = v.y, vz = v.z, fx = f.x, fy = f.y, fz = f.z;
+        double f2 = (fx * fx + fy * fy) + fz * fz;
+        q[0] += (fx * vx + fy * vy) + fz * vz;
+        q[1] += (vx * vx + vy * vy) + vz * vz;
+        q[2] += f2;
+        q[3] = fmax(q[3], f2);
+    }
+    // sums for 0..2, max for 3
+    __shared__ double s_q[RED_THREADS / 32][4];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 3; k++) q[k] = warp_sum(q[k]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) q[3] = fmax(q[3], __shfl_xor_sync(0xffffffffu, q[3], o));
+    if (lane == 0)
+        for (int k = 0; k < 4; k++) s_q[w][k] = q[k];
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        double v = 0;
+        for (int ww = 0; ww < RED_THREADS / 32; ww++)
+            v = threadIdx.x < 3 ? v + s_q[ww][threadIdx.x] : fmax(v, s_q[ww][threadIdx.x]);
+        partial[(size_t)blockIdx.x * 4 + threadIdx.x] = v;
+    }
+}
+
+#define MIN_MODE_SD 0
+#define MIN_MODE_FIRE 1
+
+// One thread: finish the reduction and advance the minimiser's scalar state.
+// FIRE: Bitzek et al., PRL 97, 170201 (2006): n_min 5, f_inc 1.1, f_dec 0.5,
+// alpha0 0.1, f_alpha 0.99.  SD: step h = min(h_now, 0.1 / max|F_i|), h_now
+// grows 1.1x while successive gradients agree (F.F_prev > 0), halves otherwise.
+__global__ void k_min_logic(Ctl *ctl, const double *__restrict__ partial, int nblk, int n)
+{
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
+    double P = 0, vv = 0, ff = 0, fmax2 = 0;
+    for (int b = 0; b < nblk; b++) {
+        P += partial[4 * (size_t)b + 0];
+        vv += partial[4 * (size_t)b + 1];
+        ff += partial[4 * (size_t)b + 2];
+        fmax2 = fmax(fmax2, partial[4 * (size_t)b + 3]);
+    }
+    ctl->fn2 = ff / (double)n;
+    if (ctl->fn2 < ctl->fn2_tol) {
+        ctl->converged = 1u;
+        ctl->done = 1u;
+        return;
+    }
+    if (ctl->iter >= ctl->steps_target) {
+        ctl->done = 1u;
+        return;
+    }
+    if (ctl->min_mode == MIN_MODE_FIRE) {
+        if (P > 0.0) {
+            // mixing coefficients use alpha BEFORE this iteration's update
+            ctl->red[0] = 1.0 - ctl->alpha;
+            ctl->red[1] = ctl->alpha * sqrt(vv / ff);
+            ctl->npos += 1;
+            if (ctl->npos > 5) {
+                ctl->dt_now = fmin(ctl->dt_now * 1.1, ctl->dt_max);
+                ctl->alpha *= 0.99;
+            }
+        } else {
+            ctl->red[0] = 0.0;
+            ctl->red[1] = 0.0;
+            ctl->npos = 0;
+            ctl->dt_now *= 0.5;
+            ctl->alpha = 0.1;
+        }
+        ctl->step_len = ctl->dt_now;
+    } else {
+        if (ctl->iter > 0) ctl->dt_now *= (P > 0.0) ? 1.1 : 0.5;
+        ctl->step_len = fmin(ctl->dt_now, 0.1 / sqrt(fmax2));
+        ctl->red[2] = sqrt(fmax2);
+    }
+}
+
+template <typename R> struct MinArgs {
+    Ctl *ctl;
+    typename Vec4<R>::type *pos[2];
+    typename Vec4<R>::type *vel;
+    const typename Vec4<R>::type *frc;
+    const int *orig;
+    int *img;
+    int n;
+    Box<R> box;
+};
+
+// FIRE: v = a v + b F ; v += dt F/m ; x += dt v.   SD: x += h F ; v = F.
+// Positions are updated in place (forces come from the stored array).
+template <typename R>
+__global__ void __launch_bounds__(RED_THREADS)
+k_min_step(MinArgs<R> a)
+{
+    typedef typename Vec4<R>::type V4;
+    Ctl *ctl = a.ctl;
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
+    __shared__ float s_d2[RED_THREADS / 32];
+    V4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
+    const int mode = ctl->min_mode;
+    const R h = (R)ctl->step_len, ca = (R)ctl->red[0], cb = (R)ctl->red[1];
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float d2 = 0.f;
+    if (i < a.n) {
+        V4 p = pos[i], v = a.vel[i], f = a.frc[i];
+        R ux, uy, uz;
+        if (mode == MIN_MODE_FIRE) {
+            R s = h / v.w;
+            v.x = ca * v.x + cb * f.x + s * f.x;
+            v.y = ca * v.y + cb * f.y + s * f.y;
+            v.z = ca * v.z + cb * f.z + s * f.z;
+            ux = h * v.x; uy = h * v.y; uz = h * v.z;
+        } else {
+            ux = h * f.x; uy = h * f.y; uz = h * f.z;
+            v.x = f.x; v.y = f.y; v.z = f.z;
+        }
+        R x = p.x + ux, y = p.y + uy, z = p.z + uz;
+        R kx = r_rint(x * a.box.invL[0]), ky = r_rint(y * a.box.invL[1]), kz = r_rint(z * a.box.invL[2]);
+        if (kx != (R)0 || ky != (R)0 || kz != (R)0) {
+            x -= kx * a.box.L[0]; y -= ky * a.box.L[1]; z -= kz * a.box.L[2];
+            int *im = a.img + 3 * (size_t)a.orig[i];
+            im[0] += (int)kx; im[1] += (int)ky; im[2] += (int)kz;
+        }
+        pos[i] = make4(x, y, z, p.w);
+        a.vel[i] = v;
+        d2 = __double2float_ru((double)ux * ux + (double)uy * uy + (double)uz * uz);
+    }
+    d2 = warp_max(d2);
+    if ((threadIdx.x & 31) == 0) s_d2[threadIdx.x >> 5] = d2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = s_d2[0];
+        for (int w = 1; w < RED_THREADS / 32; w++) m = fmaxf(m, s_d2[w]);
+        atomicMax(&ctl->vmax2_bits, __float_as_uint(m));
+        __threadfence();
+        unsigned ticket = atomicAdd(&ctl->blocks_done, 1u);
+        if (ticket == gridDim.x - 1) {
+            __threadfence();
+            float dm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
+            double bound = ctl->disp_bound + sqrt((double)dm2) * (1.0 + 1e-6);
+            ctl->disp_bound = bound;
+            ctl->iter += 1;
+            ctl->steps_done += 1;
+            if (bound > ctl->half_skin) ctl->halt_rebuild = 1u;
+            ctl->blocks_done = 0u;
+        }
+    }
+}

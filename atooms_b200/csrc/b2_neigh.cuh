@@ -1,0 +1,318 @@
+// Neighbour search: Morton cell binning, LSD radix sort, cell table, Verlet list.
+//
+// All kernels of the refresh pipeline are guarded by Ctl::halt_rebuild: the
+// host enqueues them speculatively between batches of MD steps and they do
+// work only when the displacement bound has invalidated the list.
+#pragma once
+#include "b2_common.cuh"
+
+#define SORT_THREADS 256
+#define SORT_WARPS 8
+#define SORT_ITEMS 16                                  // keys per thread
+#define SORT_TILE (SORT_THREADS * SORT_ITEMS)          // keys per block
+#define SORT_SEG (SORT_TILE / SORT_WARPS)              // contiguous keys per warp
+
+// ---- keys -----------------------------------------------------------------
+template <typename R>
+__global__ void k_cell_keys(const Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0,
+                            const typename Vec4<R>::type *pos1, int n, Box<R> box, Grid g,
+                            uint32_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    if (!ctl->halt_rebuild) return;
+    const typename Vec4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    typename Vec4<R>::type p = pos[i];
+    int cx, cy, cz;
+    cell_of(box, g, p.x, p.y, p.z, cx, cy, cz);
+    keys[i] = morton3(cx, cy, cz);
+    vals[i] = (uint32_t)i;
+}
+
+// ---- radix sort, one 8-bit digit per pass -----------------------------------
+__global__ void __launch_bounds__(SORT_THREADS)
+k_sort_hist(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ keys, int n, int shift,
+            int nblk, int *__restrict__ hist)
+{
+    if (!ctl->halt_rebuild) return;
+    __shared__ int sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    int base = blockIdx.x * SORT_TILE;
+#pragma unroll 4
+    for (int it = 0; it < SORT_ITEMS; it++) {
+        int idx = base + it * SORT_THREADS + threadIdx.x;
+        if (idx < n) atomicAdd(&sh[(keys[idx] >> shift) & 255u], 1);
+    }
+    __syncthreads();
+    hist[threadIdx.x * nblk + blockIdx.x] = sh[threadIdx.x];   // digit-major
+}
+
+// exclusive scan of `total` ints in place, one block of 1024 threads
+__global__ void __launch_bounds__(1024)
+k_sort_scan(const Ctl *__restrict__ ctl, int *__restrict__ hist, int total)
+{
+    if (!ctl->halt_rebuild) return;
+    __shared__ int s_warp[32];
+    int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    int chunk = (total + 1023) / 1024;
+    int lo = min(tid * chunk, total), hi = min(lo + chunk, total);
+    int sum = 0;
+    for (int k = lo; k < hi; k++) sum += hist[k];
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        int v = s_warp[lane], inc2 = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, inc2, o);
+            if (lane >= o) inc2 += t;
+        }
+        s_warp[lane] = inc2 - v;
+    }
+    __syncthreads();
+    int run = s_warp[w] + incl - sum;
+    for (int k = lo; k < hi; k++) {
+        int t = hist[k];
+        hist[k] = run;
+        run += t;
+    }
+}
+
+// stable scatter: each warp owns a contiguous segment of the block's tile
+__global__ void __launch_bounds__(SORT_THREADS)
+k_sort_scatter(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ kin,
+               const uint32_t *__restrict__ vin, uint32_t *__restrict__ kout,
+               uint32_t *__restrict__ vout, int n, int shift, int nblk,
+               const int *__restrict__ hist)
+{
+    if (!ctl->halt_rebuild) return;
+    __shared__ int wh[SORT_WARPS][256];
+    int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int k = tid; k < SORT_WARPS * 256; k += SORT_THREADS) ((int *)wh)[k] = 0;
+    __syncthreads();
+    int seg = blockIdx.x * SORT_TILE + w * SORT_SEG;
+    uint32_t key[SORT_ITEMS];
+    // pass 1: per-warp digit histogram
+#pragma unroll
+    for (int it = 0; it < SORT_ITEMS; it++) {
+        int idx = seg + it * 32 + lane;
+        bool ok = idx < n;
+        key[it] = ok ? kin[idx] : 0u;
+        unsigned d = ok ? ((key[it] >> shift) & 255u) : 256u;
+        unsigned peers = __match_any_sync(0xffffffffu, d);
+        if (ok && lane == __ffs(peers) - 1) wh[w][d] += __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // exclusive prefix over the warps, on top of this block's global base
+        int d = tid;
+        int run = hist[d * nblk + blockIdx.x];
+#pragma unroll
+        for (int ww = 0; ww < SORT_WARPS; ww++) {
+            int t = wh[ww][d];
+            wh[ww][d] = run;
+            run += t;
+        }
+    }
+    __syncthreads();
+    // pass 2: ranks within the warp keep the order of equal digits
+#pragma unroll
+    for (int it = 0; it < SORT_ITEMS; it++) {
+        int idx = seg + it * 32 + lane;
+        bool ok = idx < n;
+        unsigned d = ok ? ((key[it] >> shift) & 255u) : 256u;
+        unsigned peers = __match_any_sync(0xffffffffu, d);
+        int leader = __ffs(peers) - 1;
+        int off = 0;
+        if (ok && lane == leader) {
+            off = wh[w][d];
+            wh[w][d] = off + __popc(peers);
+        }
+        off = __shfl_sync(0xffffffffu, off, leader);
+        int rank = __popc(peers & ((1u << lane) - 1u));
+        if (ok) {
+            kout[off + rank] = key[it];
+            vout[off + rank] = vin[idx];
+        }
+        __syncwarp();
+    }
+}
+
+// ---- permute the particle arrays into sorted order ---------------------------
+template <typename R>
+__global__ void k_gather(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ perm, int n,
+                         const typename Vec4<R>::type *pos0, const typename Vec4<R>::type *pos1,
+                         const typename Vec4<R>::type *__restrict__ vel,
+                         const int *__restrict__ orig,
+                         typename Vec4<R>::type *__restrict__ tpos,
+                         typename Vec4<R>::type *__restrict__ tvel, int *__restrict__ torig)
+{
+    if (!ctl->halt_rebuild) return;
+    const typename Vec4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    uint32_t src = perm[s];
+    tpos[s] = pos[src];
+    tvel[s] = vel[src];
+    torig[s] = orig[src];
+}
+
+template <typename R>
+__global__ void k_gather_commit(const Ctl *__restrict__ ctl, int n,
+                                const typename Vec4<R>::type *__restrict__ tpos,
+                                const typename Vec4<R>::type *__restrict__ tvel,
+                                const int *__restrict__ torig,
+                                typename Vec4<R>::type *pos0, typename Vec4<R>::type *pos1,
+                                typename Vec4<R>::type *__restrict__ vel, int *__restrict__ orig)
+{
+    if (!ctl->halt_rebuild) return;
+    typename Vec4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    pos[s] = tpos[s];
+    vel[s] = tvel[s];
+    orig[s] = torig[s];
+}
+
+// ---- cell table ------------------------------------------------------------
+__global__ void k_fill_int(const Ctl *__restrict__ ctl, int *__restrict__ a, int *__restrict__ b,
+                           int count, int value)
+{
+    if (!ctl->halt_rebuild) return;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) {
+        a[i] = value;
+        b[i] = value;
+    }
+}
+
+__global__ void k_cell_bounds(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ keys, int n,
+                              int *__restrict__ cell_start, int *__restrict__ cell_end)
+{
+    if (!ctl->halt_rebuild) return;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    uint32_t k = keys[s];
+    if (s == 0 || keys[s - 1] != k) cell_start[k] = s;
+    if (s == n - 1 || keys[s + 1] != k) cell_end[k] = s + 1;
+}
+
+// ---- Verlet list -----------------------------------------------------------
+// Membership: r2 < (rcut_ab + skin)^2, strict, with the reference's minimum
+// image d - rint(d/L)*L (atooms/system/particle.py:129-130) and
+// r2 = (dx*dx + dy*dy) + dz*dz, all correctly rounded and uncontracted.  The
+// division-free estimate decides every pair outside a thin band around the
+// threshold; the band is re-evaluated with the canonical expression, so the
+// result is bit-identical to evaluating the canonical one everywhere.
+template <typename R> struct PredEps;
+template <> struct PredEps<float>  { static constexpr float  v = 2e-5f; };
+template <> struct PredEps<double> { static constexpr double v = 1e-11; };
+
+template <typename R>
+__device__ __forceinline__ bool in_list(const Box<R> &box, R xi, R yi, R zi, R xj, R yj, R zj, R rl2)
+{
+    R dx = xi - xj, dy = yi - yj, dz = zi - zj;
+    R ex = dx - r_rint(dx * box.invL[0]) * box.L[0];
+    R ey = dy - r_rint(dy * box.invL[1]) * box.L[1];
+    R ez = dz - r_rint(dz * box.invL[2]) * box.L[2];
+    R r2 = ex * ex + ey * ey + ez * ez;
+    if (r2 > rl2 * ((R)1 + PredEps<R>::v)) return false;
+    if (r2 < rl2 * ((R)1 - PredEps<R>::v)) return true;
+    ex = nc_sub(dx, nc_mul(r_rint(nc_div(dx, box.L[0])), box.L[0]));
+    ey = nc_sub(dy, nc_mul(r_rint(nc_div(dy, box.L[1])), box.L[1]));
+    ez = nc_sub(dz, nc_mul(r_rint(nc_div(dz, box.L[2])), box.L[2]));
+    r2 = nc_add(nc_add(nc_mul(ex, ex), nc_mul(ey, ey)), nc_mul(ez, ez));
+    return r2 < rl2;
+}
+
+__device__ __forceinline__ float  rl2_of(const PairConst &pc, int a, float)  { return pc.rl2_f[a]; }
+__device__ __forceinline__ double rl2_of(const PairConst &pc, int a, double) { return pc.rl2_d[a]; }
+
+
+// List layout: warp tile t = slot / 32 owns `cap` rows of 32 lanes:
+//     nbr[(t * cap + k) * 32 + lane]   = k-th neighbour of slot t*32 + lane
+// so a warp of the force kernel reads one coalesced 128-byte row per k.
+template <typename R>
+__global__ void __launch_bounds__(128)
+k_build_list(Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0,
+             const typename Vec4<R>::type *pos1, int n, Box<R> box, Grid g,
+             const int *__restrict__ cell_start, const int *__restrict__ cell_end,
+             int *__restrict__ nbr, int *__restrict__ nnb, int cap)
+{
+    if (!ctl->halt_rebuild) return;
+    typedef typename Vec4<R>::type V4;
+    const V4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
+    __shared__ R s_rl2[B2_MAXSP * B2_MAXSP];
+    if (threadIdx.x < B2_MAXSP * B2_MAXSP) s_rl2[threadIdx.x] = rl2_of(g_pair, threadIdx.x, (R)0);
+    __syncthreads();
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int nsp = g_pair.nsp;
+    V4 pi = pos[i];
+    int ti = type_of(pi.w);
+    int *row = nbr + ((size_t)(i >> 5) * cap) * 32 + (i & 31);
+    int cnt = 0;
+    if (g.allpairs) {
+        for (int j = 0; j < n; j++) {
+            if (j == i) continue;
+            V4 pj = pos[j];
+            if (in_list(box, pi.x, pi.y, pi.z, pj.x, pj.y, pj.z, s_rl2[ti * nsp + type_of(pj.w)])) {
+                if (cnt < cap) row[(size_t)cnt * 32] = j;
+                cnt++;
+            }
+        }
+    } else {
+        int cx, cy, cz;
+        cell_of(box, g, pi.x, pi.y, pi.z, cx, cy, cz);
+        for (int dz = -1; dz <= 1; dz++) {
+            int z = cz + dz;
+            z = z < 0 ? z + g.nc[2] : (z >= g.nc[2] ? z - g.nc[2] : z);
+            for (int dy = -1; dy <= 1; dy++) {
+                int y = cy + dy;
+                y = y < 0 ? y + g.nc[1] : (y >= g.nc[1] ? y - g.nc[1] : y);
+                for (int dx = -1; dx <= 1; dx++) {
+                    int x = cx + dx;
+                    x = x < 0 ? x + g.nc[0] : (x >= g.nc[0] ? x - g.nc[0] : x);
+                    uint32_t key = morton3(x, y, z);
+                    int s = cell_start[key], e = cell_end[key];
+                    for (int j = s; j < e; j++) {
+                        if (j == i) continue;
+                        V4 pj = pos[j];
+                        if (in_list(box, pi.x, pi.y, pi.z, pj.x, pj.y, pj.z,
+                                    s_rl2[ti * nsp + type_of(pj.w)])) {
+                            if (cnt < cap) row[(size_t)cnt * 32] = j;
+                            cnt++;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    nnb[i] = min(cnt, cap);
+    if (cnt > cap) ctl->overflow = 1u;
+    atomicMax(&ctl->max_count, (unsigned)cnt);
+}
+
+__global__ void k_rebuild_begin(Ctl *ctl)
+{
+    if (!ctl->halt_rebuild) return;
+    ctl->max_count = 0u;
+    ctl->overflow = 0u;
+}
+
+__global__ void k_rebuild_finish(Ctl *ctl)
+{
+    if (!ctl->halt_rebuild) return;
+    if (!ctl->overflow) {
+        ctl->halt_rebuild = 0u;
+        ctl->disp_bound = 0.0;
+        ctl->rebuilds += 1;
+    }
+}

@@ -45,7 +45,7 @@ struct b2_ctx {
     double c6[MAXSP * MAXSP], c12[MAXSP * MAXSP], rc2[MAXSP * MAXSP], ushift[MAXSP * MAXSP];
     double rcut[MAXSP * MAXSP], rcut_max;
     double skin;
-    double *pos, *vel, *mass, *frc, *pe, *vir, *ref, *trial, *ftrial;
+    double *pos, *vel, *mass, *frc, *pe, *vir, *ref;
     int32_t *spe, *img, *img_ref;
     /* Verlet list (CSR, original numbering, rows ascending) */
     int64_t *row;
@@ -90,9 +90,9 @@ int b2_create(int device, int precision, b2_ctx **out)
 static void free_particles(b2_ctx *c)
 {
     free(c->pos); free(c->vel); free(c->mass); free(c->frc); free(c->pe); free(c->vir);
-    free(c->ref); free(c->trial); free(c->ftrial); free(c->spe); free(c->img); free(c->img_ref);
+    free(c->ref); free(c->spe); free(c->img); free(c->img_ref);
     free(c->row); free(c->nbr);
-    c->pos = c->vel = c->mass = c->frc = c->pe = c->vir = c->ref = c->trial = c->ftrial = NULL;
+    c->pos = c->vel = c->mass = c->frc = c->pe = c->vir = c->ref = NULL;
     c->spe = c->img = c->img_ref = NULL;
     c->row = NULL; c->nbr = NULL; c->nbr_cap = 0;
 }
@@ -173,6 +173,11 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     if (!c || n < 0 || (n > 0 && (!pos || !species))) return fail(c, B2_EINVAL, "b2_upload: bad argument");
     if (!c->have_box) return fail(c, B2_ESTATE, "b2_upload: call b2_set_box first");
     if (!c->have_table) return fail(c, B2_ESTATE, "b2_upload: call b2_set_pair_table first");
+    for (int64_t i = 0; i < n; i++) {
+        if (species[i] < 0 || species[i] >= c->nsp)
+            return fail(c, B2_EINVAL, "b2_upload: species id outside the pair table");
+        if (mass && !(mass[i] > 0.0)) return fail(c, B2_EINVAL, "b2_upload: mass must be > 0");
+    }
     free_particles(c);
     c->n = n;
     size_t n3 = (size_t)(n > 0 ? n : 1) * 3;
@@ -180,8 +185,6 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     c->vel = (double *)calloc(n3, sizeof(double));
     c->frc = (double *)calloc(n3, sizeof(double));
     c->ref = (double *)malloc(n3 * sizeof(double));
-    c->trial = (double *)malloc(n3 * sizeof(double));
-    c->ftrial = (double *)malloc(n3 * sizeof(double));
     c->mass = (double *)malloc(n3 / 3 * sizeof(double));
     c->pe = (double *)calloc(n3 / 3, sizeof(double));
     c->vir = (double *)calloc(n3 / 3, sizeof(double));
@@ -190,14 +193,11 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     c->img_ref = (int32_t *)calloc(n3, sizeof(int32_t));
     c->row = (int64_t *)calloc((size_t)n + 1, sizeof(int64_t));
     if (!c->pos || !c->vel || !c->frc || !c->ref || !c->mass || !c->pe || !c->vir || !c->spe ||
-        !c->img || !c->img_ref || !c->row || !c->trial || !c->ftrial)
+        !c->img || !c->img_ref || !c->row)
         return fail(c, B2_ENOMEM, "b2_upload: out of memory");
     for (int64_t i = 0; i < n; i++) {
-        if (species[i] < 0 || species[i] >= c->nsp)
-            return fail(c, B2_EINVAL, "b2_upload: species id outside the pair table");
         c->spe[i] = species[i];
         c->mass[i] = mass ? mass[i] : 1.0;
-        if (!(c->mass[i] > 0.0)) return fail(c, B2_EINVAL, "b2_upload: mass must be > 0");
         for (int d = 0; d < 3; d++) {
             c->pos[3 * i + d] = pos[3 * i + d];
             if (vel) c->vel[3 * i + d] = vel[3 * i + d];
@@ -287,7 +287,7 @@ static inline int in_list(const b2_ctx *c, int64_t i, int64_t j)
         double rl = c->rcut[a] + c->skin;
         return in_list64(c->pos + 3 * i, c->pos + 3 * j, c->side, rl * rl);
     } else {
-        float rl = (float)c->rcut[a] + (float)c->skin;
+        float rl = (float)(c->rcut[a] + c->skin);
         return in_list32(c->pos + 3 * i, c->pos + 3 * j, c->center, c->side, rl * rl);
     }
 }
@@ -636,56 +636,38 @@ static int minimize_fire(b2_ctx *c, int64_t max_steps, double dt, double tol,
 static int minimize_sd(b2_ctx *c, int64_t max_steps, double step, double tol,
                        int64_t *steps_done, int *converged)
 {
+    /* see oracle_np.steepest_descent: the previous force is kept in c->vel */
     const double max_disp = 0.1;
     int64_t n = c->n, it = 0;
     int rc;
     double h_now = step;
+    memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
     *converged = 0;
-    if ((rc = ensure_forces(c)) != B2_OK) return rc;
     for (;;) {
+        if ((rc = ensure_forces(c)) != B2_OK) return rc;
         double ff = sum_f2(c, c->frc);
         if (ff / (double)n < tol) { *converged = 1; break; }
         if (it >= max_steps) break;
-        double fmax2 = 0;
+        double dot = 0, fmax2 = 0;
+        for (int64_t k = 0; k < 3 * n; k++) dot += c->frc[k] * c->vel[k];
         for (int64_t i = 0; i < n; i++) {
             const double *f = c->frc + 3 * i;
             double f2 = (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
             if (f2 > fmax2) fmax2 = f2;
         }
+        if (it > 0) h_now *= (dot > 0.0) ? 1.1 : 0.5;
         double h = fmin(h_now, max_disp / sqrt(fmax2));
-        /* trial move; keep the old state to roll back */
-        memcpy(c->trial, c->pos, (size_t)n * 3 * sizeof(double));
-        memcpy(c->ftrial, c->frc, (size_t)n * 3 * sizeof(double));
-        int32_t *img_old = (int32_t *)malloc((size_t)n * 3 * sizeof(int32_t));
-        memcpy(img_old, c->img, (size_t)n * 3 * sizeof(int32_t));
-        double e_old = c->energy, w_old = c->virial, bound_old = c->disp_bound;
         for (int64_t i = 0; i < n; i++) {
-            for (int d = 0; d < 3; d++) c->pos[3 * i + d] += h * c->frc[3 * i + d];
+            for (int d = 0; d < 3; d++) {
+                c->pos[3 * i + d] += h * c->frc[3 * i + d];
+                c->vel[3 * i + d] = c->frc[3 * i + d];
+            }
             fold3(c, c->pos + 3 * i, c->img + 3 * i);
         }
         advance_bound(c, h * sqrt(fmax2));
         c->forces_valid = 0;
-        if ((rc = ensure_forces(c)) != B2_OK) { free(img_old); return rc; }
-        if (c->energy <= e_old) {
-            h_now *= 1.2;
-        } else {
-            /* reject: restore positions; the list built for either configuration
-             * stays valid for the restored one only if it was not rebuilt */
-            memcpy(c->pos, c->trial, (size_t)n * 3 * sizeof(double));
-            memcpy(c->frc, c->ftrial, (size_t)n * 3 * sizeof(double));
-            memcpy(c->img, img_old, (size_t)n * 3 * sizeof(int32_t));
-            c->energy = e_old; c->virial = w_old;
-            c->list_valid = 0;
-            c->disp_bound = bound_old;
-            c->forces_valid = 1;
-            h_now *= 0.5;
-        }
-        free(img_old);
         it++;
     }
-    /* pe/vir/stress of the accepted configuration */
-    c->forces_valid = 0;
-    if ((rc = ensure_forces(c)) != B2_OK) return rc;
     memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
     *steps_done = it;
     return B2_OK;
@@ -699,6 +681,7 @@ int b2_minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double fn2_
     if (max_steps < 0 || !(dt > 0.0) || !steps_done || !converged)
         return fail(c, B2_EINVAL, "b2_minimize: bad argument");
     double t0 = now_ms();
+    if (c->n == 0) { *steps_done = 0; *converged = 1; return B2_OK; }
     if (method == B2_MIN_FIRE) rc = minimize_fire(c, max_steps, dt, fn2_tol, steps_done, converged);
     else if (method == B2_MIN_SD) rc = minimize_sd(c, max_steps, dt, fn2_tol, steps_done, converged);
     else return fail(c, B2_EINVAL, "b2_minimize: unknown method");

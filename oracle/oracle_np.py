@@ -245,7 +245,7 @@ def fire(position, mass, species, side, table, dt, max_steps, fn2_tol, center=No
         fn2 = sum F^2 / N ; stop if fn2 < tol       (optimization/core.py:34-36)
         P = F.v
         if P > 0: npos += 1; if npos > n_min: dt = min(dt f_inc, dt_max), alpha *= f_alpha
-                  v = (1 - alpha) v + alpha |v|/|F| F      [alpha BEFORE the update above]
+                  v = (1 - alpha) v + alpha |v|/|F| F      [with alpha as it was BEFORE this update]
         else:     npos = 0; dt *= f_dec; alpha = alpha0; v = 0
         v += dt F / m ; x += dt v ; fold ; F = F(x)
     Returns (pos, steps_done, converged, energy, fn2).
@@ -291,21 +291,23 @@ def fire(position, mass, species, side, table, dt, max_steps, fn2_tol, center=No
 
 def steepest_descent(position, species, side, table, step, max_steps, fn2_tol,
                      max_disp=0.1, center=None):
-    """Steepest descent with a capped, adaptive step.
+    """Steepest descent with a capped step that adapts to gradient agreement.
 
-    Per iteration:  fn2 = sum F^2/N ; stop if fn2 < tol
-        h = min(step_now, max_disp / max_i |F_i|) ; x' = x + h F ; U' = U(x')
-        if U' <= U: accept, step_now *= 1.2   else: reject, step_now *= 0.5
-    Returns (pos, steps_done, converged, energy, fn2); rejected trials count
-    as iterations (each costs one force evaluation).
+    Per iteration, with F = F(x) and F_prev the force of the previous iterate:
+        fn2 = sum F^2 / N ; stop if fn2 < tol            (optimization/core.py:34-36)
+        if it > 0:  h_now *= 1.1 if F . F_prev > 0 else 0.5   (overshoot => halve)
+        h = min(h_now, max_disp / max_i |F_i|) ;  x += h F ; fold
+    No energy evaluations and no rejected moves, so one force evaluation per
+    iteration.  Returns (pos, steps_done, converged, energy, fn2).
     """
     pos = numpy.array(position, dtype=numpy.float64)
     n = pos.shape[0]
-    out = compute(pos, species, side, table)
+    prev = numpy.zeros_like(pos)
     h_now = step
     it = 0
     converged = False
     while True:
+        out = compute(pos, species, side, table)
         f = out['forces']
         ff = float(numpy.sum(f * f))
         if ff / n < fn2_tol:
@@ -313,14 +315,11 @@ def steepest_descent(position, species, side, table, step, max_steps, fn2_tol,
             break
         if it >= max_steps:
             break
+        if it > 0:
+            h_now *= 1.1 if float(numpy.sum(f * prev)) > 0.0 else 0.5
         fmax = float(numpy.sqrt(numpy.max(numpy.sum(f * f, axis=1))))
         h = min(h_now, max_disp / fmax)
-        trial, _ = fold(pos + h * f, side, center)
-        new = compute(trial, species, side, table)
-        if new['energy'] <= out['energy']:
-            pos, out = trial, new
-            h_now *= 1.2
-        else:
-            h_now *= 0.5
+        pos, _ = fold(pos + h * f, side, center)
+        prev = f
         it += 1
     return pos, it, converged, out['energy'], ff / n

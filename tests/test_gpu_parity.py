@@ -1,0 +1,307 @@
+"""
+Parity of the CUDA engine against the CPU oracle, through the C ABI.
+
+Tolerances (BASELINE.json north_star), stated here once:
+  fp64: per-particle forces 1e-10 (max |dF| / max |F|), energy / virial 1e-12 relative
+  fp32: forces 1e-5, energy / virial 1e-6 — against the oracle evaluated in fp64 on the
+        SAME fp32-rounded positions the fp32 engine holds
+  neighbour lists: bit-exact (sorted index sets in original numbering), both precisions
+"""
+import numpy
+import pytest
+
+from conftest import golden, make_engine
+from oracle import oracle_np as onp
+from atooms_b200 import capi
+
+pytestmark = pytest.mark.gpu
+
+TOL = {64: dict(f=1e-10, e=1e-12), 32: dict(f=1e-5, e=1e-6)}
+DTYPE = {64: numpy.float64, 32: numpy.float32}
+
+
+def tables():
+    return {
+        'lj_N256': onp.lennard_jones(2.5, True),         # 2 cells wide -> all-pairs list
+        'lj_N1000': onp.lennard_jones(2.5, False),       # 3 cells wide -> cell list
+        'lj_fcc_N108': onp.lennard_jones(2.5, False),    # L < 2 rc
+        'ka_N256_rumd': onp.kob_andersen(),
+        'ka_N1200': onp.kob_andersen(),
+        'ka_N1212_rumd': onp.kob_andersen(nsp=3),
+        'lj_N3_inline': onp.lennard_jones(2.5, True),
+    }
+
+
+def rounded(data, precision):
+    """Fixture with positions representable in the engine's precision."""
+    d = {k: data[k] for k in data.files} if hasattr(data, 'files') else dict(data)
+    if precision == 32:
+        d['position'] = d['position'].astype(numpy.float32).astype(numpy.float64)
+    return d
+
+
+def replicated(name, reps, jitter, seed):
+    """Tile a fixture reps^3 times (NumPy, not System.replicate) and jitter it."""
+    d = golden(name)
+    side = d['side']
+    shifts = numpy.array([[i, j, k] for i in range(reps) for j in range(reps) for k in range(reps)])
+    pos = (d['position'][None, :, :] + shifts[:, None, :] * side).reshape(-1, 3)
+    pos -= 0.5 * (reps - 1) * side
+    rng = numpy.random.default_rng(seed)
+    pos += rng.uniform(-jitter, jitter, size=pos.shape)
+    n = pos.shape[0]
+    return {'position': pos, 'species': numpy.tile(d['species'], reps ** 3), 'side': side * reps,
+            'center': numpy.zeros(3), 'mass': numpy.ones(n),
+            'velocity': onp.maxwell_boltzmann(n, 0.8, 1.0, seed + 1)}
+
+
+def assert_observables(got, ref, precision):
+    tol = TOL[precision]
+    assert abs(got['energy'] - ref['energy']) <= tol['e'] * abs(ref['energy'])
+    assert abs(got['virial'] - ref['virial']) <= tol['e'] * max(abs(ref['virial']), abs(ref['energy']))
+    fmax = numpy.abs(ref['forces']).max()
+    assert numpy.abs(got['forces'] - ref['forces']).max() <= tol['f'] * max(fmax, 1e-30)
+    if 'pe' in got:
+        assert numpy.abs(got['pe'] - ref['pe']).max() <= 10 * tol['f'] * numpy.abs(ref['pe']).max()
+        assert numpy.abs(got['vir'] - ref['vir']).max() <= 10 * tol['f'] * numpy.abs(ref['vir']).max()
+    if 'stress' in got:
+        assert numpy.abs(got['stress'] - ref['stress']).max() <= 10 * tol['e'] * numpy.abs(ref['stress']).max()
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+@pytest.mark.parametrize('name', sorted(tables()))
+def test_single_point_fixtures(cuda_lib, oracle_lib, name, precision):
+    table = tables()[name]
+    d = rounded(golden(name), precision)
+    got = make_engine(cuda_lib, d, table, precision).compute(per_particle=True, stress=True)
+    ref = make_engine(oracle_lib, d, table, 64).compute(per_particle=True, stress=True)
+    if name == 'lj_fcc_N108':
+        # forces vanish by symmetry (|F| ~ 1e-6): compare on the scale of the pair forces
+        assert numpy.abs(got['forces'] - ref['forces']).max() < TOL[precision]['f'] * 30
+        got['forces'] = ref['forces']
+    assert_observables(got, ref, precision)
+
+
+def test_golden_rumd_columns(cuda_lib):
+    """fp32 engine vs RUMD's own fp32 per-particle columns (the only golden vector)."""
+    d = golden('ka_N256_rumd')
+    got = make_engine(cuda_lib, d, onp.kob_andersen(), 32).compute(per_particle=True)
+    fref = numpy.c_[d['fx'], d['fy'], d['fz']]
+    assert numpy.abs(got['forces'] - fref).max() / numpy.abs(fref).max() < 1e-5
+    assert numpy.abs(got['pe'] - d['pe']).max() < 5e-5
+    assert numpy.abs(got['vir'] - d['vir']).max() / numpy.abs(d['vir']).max() < 1e-5
+    assert round(abs(got['energy'] / 256 - (-6.4014371344819665)), 3) == 0
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+def test_single_point_replicated(cuda_lib, oracle_lib, precision):
+    """N = 9600 (6 cells per side): exercises the Morton sort and the cell table."""
+    d = rounded(replicated('ka_N1200', 2, 0.01, 2), precision)
+    ka = onp.kob_andersen()
+    eng = make_engine(cuda_lib, d, ka, precision)
+    got = eng.compute(per_particle=True, stress=True)
+    ref = make_engine(oracle_lib, d, ka, 64).compute(per_particle=True, stress=True)
+    assert_observables(got, ref, precision)
+    st = eng.stats()
+    assert st['list_mode'] == 0 and st['ncells'] == 7 ** 3
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+@pytest.mark.parametrize('name', ['ka_N256_rumd', 'ka_N1200', 'lj_N1000'])
+def test_neighbor_list_bit_exact(cuda_lib, oracle_lib, name, precision):
+    table = tables()[name]
+    d = rounded(golden(name), precision)
+    got = make_engine(cuda_lib, d, table, precision).neighbors()
+    ref = make_engine(oracle_lib, d, table, precision).neighbors()
+    assert len(got) == len(ref)
+    for a, b in zip(got, ref):
+        assert numpy.array_equal(a, b)
+    brute = onp.neighbor_list(d['position'], d['species'], d['side'], table, 0.3, dtype=DTYPE[precision])
+    for a, b in zip(got, brute):
+        assert numpy.array_equal(a, b)
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+def test_neighbor_list_bit_exact_replicated(cuda_lib, oracle_lib, precision):
+    d = rounded(replicated('ka_N1200', 3, 0.02, 5), precision)   # N = 32400
+    ka = onp.kob_andersen()
+    got = make_engine(cuda_lib, d, ka, precision, skin=0.4).neighbors()
+    ref = make_engine(oracle_lib, d, ka, precision, skin=0.4).neighbors()
+    assert sum(len(a) for a in got) == sum(len(b) for b in ref)
+    for a, b in zip(got, ref):
+        assert numpy.array_equal(a, b)
+
+
+def test_nve_trajectory_pin(cuda_lib, oracle_lib, pins):
+    """tests/test_lammps.py:33-40 through the CUDA engine, and step-for-step vs the oracle."""
+    pin = pins['lj_N1000_nve_x0']
+    d = golden('lj_N1000')
+    lj = onp.lennard_jones(2.5, False)
+    eng = make_engine(cuda_lib, d, lj, 64)
+    ora = make_engine(oracle_lib, d, lj, 64)
+    for target in pin['value'][1:]:
+        eng.run_nve(10, pin['dt'])
+        ora.run_nve(10, pin['dt'])
+        pos, vel, _ = eng.download()
+        opos, ovel, _ = ora.download()
+        assert round(abs(pos[0, 0] - target), 5) == 0
+        assert numpy.abs(pos - opos).max() < 1e-10
+        assert numpy.abs(vel - ovel).max() < 1e-9
+    # run(0) is a no-op (tests/test_lammps.py:123-142)
+    eng.run_nve(0, pin['dt'])
+    pos2 = eng.download()[0]
+    assert numpy.abs(pos2 - pos).max() < 1e-12
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+def test_nve_list_stays_valid_and_energy_conserved(cuda_lib, oracle_lib, precision):
+    """After hundreds of steps and several refreshes the forces the engine holds
+    must equal a from-scratch evaluation of the configuration it holds."""
+    d = replicated('ka_N1200', 2, 0.0, 7)
+    ka = onp.kob_andersen()
+    eng = make_engine(cuda_lib, d, ka, precision)
+    t0 = eng.thermo()
+    e0 = (t0['kinetic'] + t0['potential']) / eng.n
+    eng.run_nve(600, 0.002)
+    t1 = eng.thermo()
+    e1 = (t1['kinetic'] + t1['potential']) / eng.n
+    st = eng.stats()
+    assert st['rebuilds'] >= 5 and st['steps'] == 600
+    assert abs(e1 - e0) < (2e-4 if precision == 64 else 1e-3)
+    pos, vel, img = eng.download(image=True)
+    got = eng.compute()
+    chk = dict(d, position=pos, velocity=vel)
+    ref = make_engine(oracle_lib, chk, ka, 64).compute()
+    assert_observables(got, ref, precision)
+    # momentum stays zero, kinetic energy matches the downloaded velocities
+    assert numpy.abs(t1['momentum']).max() < (1e-9 if precision == 64 else 1e-2)
+    assert abs(t1['kinetic'] - onp.kinetic_energy(vel, d['mass'])) < 1e-6 * t1['kinetic']
+    # msd from image counters == msd from unfolded positions
+    unf = pos + img * d['side']
+    start, _ = onp.fold(d['position'], d['side'])
+    msd = numpy.sum((unf - start) ** 2)
+    assert abs(t1['msd_sum'] - msd) < 1e-4 * msd
+
+
+def test_nve_energy_drift_matches_oracle(cuda_lib, oracle_lib):
+    """Same drift statistics as the CPU oracle over 2000 steps (trajectories
+    themselves diverge chaotically)."""
+    d = dict(golden('lj_N256').items())
+    d['velocity'] = onp.maxwell_boltzmann(256, 2.0, 1.0, seed=1)
+    lj = onp.lennard_jones(2.5, True)
+    series = {}
+    for key, lib in (('cuda', cuda_lib), ('oracle', oracle_lib)):
+        eng = make_engine(lib, d, lj, 64)
+        e = []
+        for _ in range(20):
+            eng.run_nve(100, 0.002)
+            t = eng.thermo()
+            e.append((t['kinetic'] + t['potential']) / 256)
+        series[key] = numpy.array(e)
+    for e in series.values():
+        assert numpy.abs(e - e[0]).max() < 5e-3
+    assert abs(series['cuda'].std() - series['oracle'].std()) < 2e-3
+    assert abs(series['cuda'].mean() - series['oracle'].mean()) < 2e-3
+    # the first 100 steps are still deterministic to round-off
+    assert abs(series['cuda'][0] - series['oracle'][0]) < 1e-8
+
+
+def test_determinism_and_state_reset(cuda_lib):
+    """deepcopy / reassign property of tests/test_rumd.py:178-194."""
+    d = golden('ka_N256_rumd')
+    ka = onp.kob_andersen()
+    a = make_engine(cuda_lib, d, ka, 64)
+    a.run_nve(100, 0.002)
+    p1 = a.download()[0]
+    b = make_engine(cuda_lib, d, ka, 64)
+    b.run_nve(100, 0.002)
+    p2 = b.download()[0]
+    assert abs(p1[0, 0] - d['position'][0, 0]) > 1e-3
+    assert numpy.abs(p1 - p2).max() == 0.0
+
+
+@pytest.mark.parametrize('method,dt', [(capi.MIN_FIRE, 0.002), (capi.MIN_SD, 0.001)])
+def test_minimisers_follow_the_oracle(cuda_lib, oracle_lib, method, dt):
+    d = golden('lj_N256')
+    lj = onp.lennard_jones(2.5, True)
+    eng = make_engine(cuda_lib, d, lj, 64, velocities=False)
+    ora = make_engine(oracle_lib, d, lj, 64, velocities=False)
+    got = eng.minimize(method, 200, dt, 1e-30)
+    ref = ora.minimize(method, 200, dt, 1e-30)
+    assert got == ref == (200, False)
+    tg, tr = eng.thermo(), ora.thermo()
+    assert abs(tg['potential'] - tr['potential']) < 1e-7 * abs(tr['potential'])
+    assert abs(tg['fnorm2'] - tr['fnorm2']) < 1e-4 * tr['fnorm2']
+    assert tg['kinetic'] == 0.0
+
+
+def test_fire_reaches_the_reference_inequalities(cuda_lib, pins):
+    """tests/test_optimization.py:20-35 (LAMMPS ftol 1e-4 on |F|_2)."""
+    pin = pins['lj_N256_minimised']
+    d = golden('lj_N256')
+    for precision, tol in ((64, 1e-8 / 256), (32, 1e-6)):
+        eng = make_engine(cuda_lib, d, onp.lennard_jones(2.5, True), precision, velocities=False)
+        steps, converged = eng.minimize(capi.MIN_FIRE, 100000, 0.002, tol)
+        assert converged and steps < 100000
+        t = eng.thermo()
+        assert t['potential'] / 256 < pin['U_per_particle_below']
+        assert t['fnorm2'] / 256 < pin['fn2_per_particle_below']
+
+
+def test_update_and_scale(cuda_lib, oracle_lib):
+    d = golden('ka_N1200')
+    ka = onp.kob_andersen()
+    vel = onp.maxwell_boltzmann(1200, 1.0, 1.0, seed=9)
+    eng = make_engine(cuda_lib, d, ka, 64)
+    eng.update(velocity=vel)
+    eng.scale_velocities(2.0)
+    assert abs(eng.thermo()['kinetic'] - 4 * onp.kinetic_energy(vel, d['mass'])) < 1e-9
+    rng = numpy.random.default_rng(4)
+    pos = d['position'] + rng.uniform(-0.05, 0.05, size=d['position'].shape) + d['side']  # outside the cell
+    eng.update(position=pos)
+    got = eng.compute()
+    ref = make_engine(oracle_lib, dict(d.items(), position=pos), ka, 64).compute()
+    assert_observables(got, ref, 64)
+    back, _, img = eng.download(image=True)
+    assert numpy.abs(back + img * d['side'] - pos).max() < 1e-12
+
+
+def test_edge_cases(cuda_lib):
+    lj = onp.lennard_jones(2.5, True)
+    base = {'side': numpy.array([10., 10., 10.]), 'center': numpy.zeros(3)}
+    # empty system
+    eng = make_engine(cuda_lib, dict(base, position=numpy.zeros((0, 3)), species=numpy.zeros(0, dtype=numpy.int32)), lj)
+    assert eng.compute()['energy'] == 0.0
+    eng.run_nve(5, 0.001)
+    assert eng.minimize(capi.MIN_FIRE, 10, 0.001, 1e-10) == (0, True)
+    # one particle: no forces, free flight with folding
+    one = dict(base, position=numpy.array([[4.999, 0., 0.]]), species=numpy.zeros(1, dtype=numpy.int32),
+               velocity=numpy.array([[1.0, 0., 0.]]))
+    eng = make_engine(cuda_lib, one, lj)
+    eng.run_nve(10, 0.01)
+    pos, vel, img = eng.download(image=True)
+    assert abs(pos[0, 0] - (4.999 + 0.1 - 10.0)) < 1e-12 and img[0, 0] == 1
+    # two particles at the docs distance (docs/basics.org:166-183)
+    two = dict(base, position=numpy.array([[0., 0., 0.], [1.122, 0., 0.]]), species=numpy.zeros(2, dtype=numpy.int32))
+    r = make_engine(cuda_lib, two, onp.lennard_jones(2.5, False)).compute()
+    assert round(abs(r['energy'] - (-0.99999388)), 7) == 0
+    assert numpy.abs(r['forces'].sum(axis=0)).max() < 1e-12
+    # a pair exactly at the cutoff is excluded (strict <)
+    cut = dict(base, position=numpy.array([[0., 0., 0.], [2.5, 0., 0.]]), species=numpy.zeros(2, dtype=numpy.int32))
+    assert make_engine(cuda_lib, cut, lj).compute()['energy'] == 0.0
+
+
+def test_error_conventions(cuda_lib):
+    eng = capi.Engine(capi.FP64, library=cuda_lib)
+    with pytest.raises(capi.B2Error):
+        eng.upload(numpy.zeros((2, 3)), numpy.zeros(2, dtype=numpy.int32))   # no box yet
+    eng.set_box([5., 5., 5.])
+    with pytest.raises(ValueError):
+        eng.set_pair_table([[1.0]], [[-1.0]], [[2.5]])
+    eng.set_pair_table([[1.0]], [[1.0]], [[2.5]])
+    with pytest.raises(ValueError):
+        eng.upload(numpy.zeros((2, 3)), numpy.array([0, 3], dtype=numpy.int32))   # species outside the table
+    with pytest.raises(capi.B2Error):
+        eng.compute()
+    with pytest.raises(ValueError):
+        capi.Engine(16, library=cuda_lib)
