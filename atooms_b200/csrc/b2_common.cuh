@@ -17,12 +17,6 @@ template <> struct Vec4<double> { typedef double4 type; };
 __device__ __forceinline__ float4  make4(float x, float y, float z, float w)     { return make_float4(x, y, z, w); }
 __device__ __forceinline__ double4 make4(double x, double y, double z, double w) { return make_double4(x, y, z, w); }
 
-// species id travels in the .w lane of a position, bit-cast
-__device__ __forceinline__ int   type_of(float w)  { return __float_as_int(w); }
-__device__ __forceinline__ int   type_of(double w) { return (int)__double_as_longlong(w); }
-__device__ __forceinline__ float  type_as(float,  int t) { return __int_as_float(t); }
-__device__ __forceinline__ double type_as(double, int t) { return __longlong_as_double((long long)t); }
-
 __device__ __forceinline__ float  r_rint(float x)  { return rintf(x); }
 __device__ __forceinline__ double r_rint(double x) { return rint(x); }
 __device__ __forceinline__ float  r_rcp(float x)   { return __frcp_rn(x); }
@@ -64,9 +58,133 @@ struct PairConst {
 // single translation unit: the table is defined here, once
 __constant__ PairConst g_pair;
 
+// ---------------------------------------------------------------------------
+// Position storage.
+//   fp64: double4 (x, y, z, species bits), coordinates relative to the cell
+//         centre in [-L/2, L/2]; minimum image d - rint(d/L) L.
+//   fp32: int4 (x, y, z, species): 32-bit FIXED-POINT fractions of the cell,
+//         x_int = round(x / L * 2^32).  Two's-complement wrap-around IS the
+//         periodic boundary: (x_i - x_j) mod 2^32 is the minimum-image
+//         separation exactly, with a uniform resolution of L / 2^32 — no
+//         loss of precision for pairs across the boundary or far from the
+//         origin (float coordinates at |x| ~ 50 resolve only 4e-6).
+// ---------------------------------------------------------------------------
+template <typename R> struct Pos4;
+template <> struct Pos4<float>  { typedef int4    type; };
+template <> struct Pos4<double> { typedef double4 type; };
+
 template <typename R> struct Box {
     R L[3], invL[3];
+    R s[3], is[3];        // fp32: grid spacing L / 2^32 and its inverse; fp64: 1
+    double Ld[3], sd[3];
 };
+
+__device__ __forceinline__ int ptype(const int4 &p)    { return p.w; }
+__device__ __forceinline__ int ptype(const double4 &p) { return (int)__double_as_longlong(p.w); }
+
+__device__ __forceinline__ int wrap_sub(int a, int b) { return (int)((unsigned)a - (unsigned)b); }
+
+// minimum-image separation a - b
+__device__ __forceinline__ void delta(const int4 &a, const int4 &b, const Box<float> &box,
+                                      float &dx, float &dy, float &dz)
+{
+    dx = (float)wrap_sub(a.x, b.x) * box.s[0];
+    dy = (float)wrap_sub(a.y, b.y) * box.s[1];
+    dz = (float)wrap_sub(a.z, b.z) * box.s[2];
+}
+__device__ __forceinline__ void delta(const double4 &a, const double4 &b, const Box<double> &box,
+                                      double &dx, double &dy, double &dz)
+{
+    dx = a.x - b.x; dy = a.y - b.y; dz = a.z - b.z;
+    dx -= box.L[0] * rint(dx * box.invL[0]);
+    dy -= box.L[1] * rint(dy * box.invL[1]);
+    dz -= box.L[2] * rint(dz * box.invL[2]);
+}
+
+// the same separation in double (observables are always summed in fp64)
+__device__ __forceinline__ void delta_d(const int4 &a, const int4 &b, const Box<float> &box,
+                                        double &dx, double &dy, double &dz)
+{
+    dx = (double)wrap_sub(a.x, b.x) * box.sd[0];
+    dy = (double)wrap_sub(a.y, b.y) * box.sd[1];
+    dz = (double)wrap_sub(a.z, b.z) * box.sd[2];
+}
+__device__ __forceinline__ void delta_d(const double4 &a, const double4 &b, const Box<double> &box,
+                                        double &dx, double &dy, double &dz)
+{
+    delta(a, b, box, dx, dy, dz);
+}
+
+// canonical squared distance of the neighbour predicate: correctly rounded,
+// never contracted, so that it can be compared bit-for-bit with the oracle
+__device__ __forceinline__ float r2_canon(const int4 &a, const int4 &b, const Box<float> &box)
+{
+    float dx = __fmul_rn(__int2float_rn(wrap_sub(a.x, b.x)), box.s[0]);
+    float dy = __fmul_rn(__int2float_rn(wrap_sub(a.y, b.y)), box.s[1]);
+    float dz = __fmul_rn(__int2float_rn(wrap_sub(a.z, b.z)), box.s[2]);
+    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+__device__ __forceinline__ double r2_canon(const double4 &a, const double4 &b, const Box<double> &box)
+{
+    // atooms/system/particle.py:129-130: d - rint(d / L) * L
+    double dx = __dsub_rn(a.x, b.x), dy = __dsub_rn(a.y, b.y), dz = __dsub_rn(a.z, b.z);
+    dx = __dsub_rn(dx, __dmul_rn(rint(__ddiv_rn(dx, box.L[0])), box.L[0]));
+    dy = __dsub_rn(dy, __dmul_rn(rint(__ddiv_rn(dy, box.L[1])), box.L[1]));
+    dz = __dsub_rn(dz, __dmul_rn(rint(__ddiv_rn(dz, box.L[2])), box.L[2]));
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+// displace by u, fold into the cell (particle.py:90-99), report box crossings
+__device__ __forceinline__ int4 advance(const int4 &p, float ux, float uy, float uz,
+                                        const Box<float> &box, int &kx, int &ky, int &kz)
+{
+    int ix = __float2int_rn(ux * box.is[0]);
+    int iy = __float2int_rn(uy * box.is[1]);
+    int iz = __float2int_rn(uz * box.is[2]);
+    int nx = (int)((unsigned)p.x + (unsigned)ix);
+    int ny = (int)((unsigned)p.y + (unsigned)iy);
+    int nz = (int)((unsigned)p.z + (unsigned)iz);
+    kx = (ix > 0 && nx < p.x) ? 1 : ((ix < 0 && nx > p.x) ? -1 : 0);
+    ky = (iy > 0 && ny < p.y) ? 1 : ((iy < 0 && ny > p.y) ? -1 : 0);
+    kz = (iz > 0 && nz < p.z) ? 1 : ((iz < 0 && nz > p.z) ? -1 : 0);
+    return make_int4(nx, ny, nz, p.w);
+}
+__device__ __forceinline__ double4 advance(const double4 &p, double ux, double uy, double uz,
+                                           const Box<double> &box, int &kx, int &ky, int &kz)
+{
+    double x = p.x + ux, y = p.y + uy, z = p.z + uz;
+    double fx = rint(x * box.invL[0]), fy = rint(y * box.invL[1]), fz = rint(z * box.invL[2]);
+    kx = (int)fx; ky = (int)fy; kz = (int)fz;
+    if (kx | ky | kz) { x -= fx * box.L[0]; y -= fy * box.L[1]; z -= fz * box.L[2]; }
+    return make_double4(x, y, z, p.w);
+}
+
+// coordinates relative to the cell centre, in double
+__device__ __forceinline__ void to_double(const int4 &p, const Box<float> &box, double &x, double &y, double &z)
+{
+    x = (double)p.x * box.sd[0]; y = (double)p.y * box.sd[1]; z = (double)p.z * box.sd[2];
+}
+__device__ __forceinline__ void to_double(const double4 &p, const Box<double> &, double &x, double &y, double &z)
+{
+    x = p.x; y = p.y; z = p.z;
+}
+
+// encode folded coordinates (relative to the centre, |x| <= L/2)
+__device__ __forceinline__ int enc32(double x, double L)
+{
+    double f = x / L;
+    f -= rint(f);
+    long long k = llrint(f * 4294967296.0);          // in [-2^31, 2^31]
+    return (int)(unsigned)(k & 0xffffffffLL);         // +2^31 wraps to -2^31: the same point
+}
+__device__ __forceinline__ int4 encode_pos(double x, double y, double z, int t, const Box<float> &box)
+{
+    return make_int4(enc32(x, box.Ld[0]), enc32(y, box.Ld[1]), enc32(z, box.Ld[2]), t);
+}
+__device__ __forceinline__ double4 encode_pos(double x, double y, double z, int t, const Box<double> &)
+{
+    return make_double4(x, y, z, __longlong_as_double((long long)t));
+}
 
 // Device-resident control block: every data-dependent decision of the inner
 // loop (list refresh, step budget, minimiser state) lives here so that the
@@ -112,13 +230,18 @@ struct Grid {
     int allpairs;      // fewer than 3 cells along some axis: O(N^2) list build
 };
 
-template <typename R>
-__device__ __forceinline__ void cell_of(const Box<R> &box, const Grid &g, R x, R y, R z, int &cx, int &cy, int &cz)
+__device__ __forceinline__ void cell_of(const Box<float> &, const Grid &g, const int4 &p, int &cx, int &cy, int &cz)
 {
-    // positions are stored relative to the cell centre, in [-L/2, L/2]
-    cx = (int)floor((x * box.invL[0] + (R)0.5) * (R)g.nc[0]);
-    cy = (int)floor((y * box.invL[1] + (R)0.5) * (R)g.nc[1]);
-    cz = (int)floor((z * box.invL[2] + (R)0.5) * (R)g.nc[2]);
+    // exact integer binning of the fixed-point coordinate
+    cx = (int)__umulhi((unsigned)p.x + 0x80000000u, (unsigned)g.nc[0]);
+    cy = (int)__umulhi((unsigned)p.y + 0x80000000u, (unsigned)g.nc[1]);
+    cz = (int)__umulhi((unsigned)p.z + 0x80000000u, (unsigned)g.nc[2]);
+}
+__device__ __forceinline__ void cell_of(const Box<double> &box, const Grid &g, const double4 &p, int &cx, int &cy, int &cz)
+{
+    cx = (int)floor((p.x * box.invL[0] + 0.5) * (double)g.nc[0]);
+    cy = (int)floor((p.y * box.invL[1] + 0.5) * (double)g.nc[1]);
+    cz = (int)floor((p.z * box.invL[2] + 0.5) * (double)g.nc[2]);
     cx = min(max(cx, 0), g.nc[0] - 1);
     cy = min(max(cy, 0), g.nc[1] - 1);
     cz = min(max(cz, 0), g.nc[2] - 1);

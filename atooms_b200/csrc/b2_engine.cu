@@ -92,9 +92,14 @@ template <typename T> static int dev_alloc(b2_ctx *c, T **p, size_t count)
 template <typename R> static Box<R> make_box(const b2_ctx *c)
 {
     Box<R> b;
+    const bool fixed = sizeof(R) == 4;     // fp32 positions are 32-bit fixed point
     for (int d = 0; d < 3; d++) {
         b.L[d] = (R)c->side[d];
         b.invL[d] = (R)1 / b.L[d];
+        b.Ld[d] = c->side[d];
+        b.sd[d] = fixed ? c->side[d] / 4294967296.0 : 1.0;
+        b.s[d] = (R)b.sd[d];
+        b.is[d] = fixed ? (R)(4294967296.0 / c->side[d]) : (R)1;
     }
     return b;
 }
@@ -143,16 +148,17 @@ static int push_ctl(b2_ctx *c)
 // ---------------------------------------------------------------------------
 template <typename R> struct Impl {
     typedef typename Vec4<R>::type V4;
+    typedef typename Pos4<R>::type P4;
 
     static int alloc_particles(b2_ctx *c, int64_t n)
     {
         int rc;
         for (int k = 0; k < 2; k++)
-            if ((rc = dev_alloc(c, (V4 **)&c->pos[k], n))) return rc;
+            if ((rc = dev_alloc(c, (P4 **)&c->pos[k], n))) return rc;
         if ((rc = dev_alloc(c, (V4 **)&c->vel, n))) return rc;
         if ((rc = dev_alloc(c, (V4 **)&c->frc, n))) return rc;
         if ((rc = dev_alloc(c, (R **)&c->vir, n))) return rc;
-        if ((rc = dev_alloc(c, (V4 **)&c->tpos, n))) return rc;
+        if ((rc = dev_alloc(c, (V4 **)&c->tpos, n))) return rc;   // >= n P4, also n doubles of scratch
         if ((rc = dev_alloc(c, (V4 **)&c->tvel, n))) return rc;
         if ((rc = dev_alloc(c, &c->orig, n))) return rc;
         if ((rc = dev_alloc(c, &c->torig, n))) return rc;
@@ -223,7 +229,7 @@ template <typename R> struct Impl {
     {
         int n = (int)c->n;
         Box<R> box = make_box<R>(c);
-        const V4 *p0 = (const V4 *)c->pos[0], *p1 = (const V4 *)c->pos[1];
+        const P4 *p0 = (const P4 *)c->pos[0], *p1 = (const P4 *)c->pos[1];
         LAUNCH(k_rebuild_begin, 1, 1, c->ctl);
         if (!c->grid.allpairs) {
             LAUNCH(k_cell_keys<R>, cdiv(n, 256), 256, c->ctl, p0, p1, n, box, c->grid, c->keys[0], c->vals[0]);
@@ -236,9 +242,9 @@ template <typename R> struct Impl {
                 src ^= 1;
             }
             LAUNCH(k_gather<R>, cdiv(n, 256), 256, c->ctl, c->vals[src], n, p0, p1, (const V4 *)c->vel, c->orig,
-                   (V4 *)c->tpos, (V4 *)c->tvel, c->torig);
-            LAUNCH(k_gather_commit<R>, cdiv(n, 256), 256, c->ctl, n, (const V4 *)c->tpos, (const V4 *)c->tvel,
-                   c->torig, (V4 *)c->pos[0], (V4 *)c->pos[1], (V4 *)c->vel, c->orig);
+                   (P4 *)c->tpos, (V4 *)c->tvel, c->torig);
+            LAUNCH(k_gather_commit<R>, cdiv(n, 256), 256, c->ctl, n, (const P4 *)c->tpos, (const V4 *)c->tvel,
+                   c->torig, (P4 *)c->pos[0], (P4 *)c->pos[1], (V4 *)c->vel, c->orig);
             LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
             LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
         }
@@ -285,8 +291,8 @@ template <typename R> struct Impl {
     {
         ForceArgs<R> a;
         a.ctl = c->ctl;
-        a.pos[0] = (const V4 *)c->pos[0];
-        a.pos[1] = (const V4 *)c->pos[1];
+        a.pos[0] = (const P4 *)c->pos[0];
+        a.pos[1] = (const P4 *)c->pos[1];
         a.frc = (V4 *)c->frc;
         a.vir = (R *)c->vir;
         a.nbr = c->nbr;
@@ -325,42 +331,44 @@ template <typename R> struct Impl {
 template <typename R>
 __global__ void k_ingest(const double *__restrict__ spos, const double *__restrict__ svel,
                          const int *__restrict__ sspe, const double *__restrict__ smass, int n,
-                         double cx, double cy, double cz, double Lx, double Ly, double Lz,
-                         typename Vec4<R>::type *__restrict__ pos, typename Vec4<R>::type *__restrict__ vel,
+                         double cx, double cy, double cz, Box<R> box,
+                         typename Pos4<R>::type *__restrict__ pos, typename Vec4<R>::type *__restrict__ vel,
                          int *__restrict__ orig, int *__restrict__ img, double *__restrict__ ref)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    // fold in double (particle.py:90-99), then narrow to the working precision
+    // fold in double (particle.py:90-99), then encode in the working precision
     double px = spos[3 * i] - cx, py = spos[3 * i + 1] - cy, pz = spos[3 * i + 2] - cz;
-    px -= rint(px / Lx) * Lx; py -= rint(py / Ly) * Ly; pz -= rint(pz / Lz) * Lz;
-    R x = (R)px, y = (R)py, z = (R)pz;
-    pos[i] = make4(x, y, z, type_as((R)0, sspe[i]));
+    px -= rint(px / box.Ld[0]) * box.Ld[0];
+    py -= rint(py / box.Ld[1]) * box.Ld[1];
+    pz -= rint(pz / box.Ld[2]) * box.Ld[2];
+    typename Pos4<R>::type p = encode_pos(px, py, pz, sspe[i], box);
+    pos[i] = p;
     vel[i] = make4((R)(svel ? svel[3 * i] : 0.0), (R)(svel ? svel[3 * i + 1] : 0.0),
                    (R)(svel ? svel[3 * i + 2] : 0.0), (R)(smass ? smass[i] : 1.0));
     orig[i] = i;
     img[3 * i] = img[3 * i + 1] = img[3 * i + 2] = 0;
-    ref[3 * i] = (double)x; ref[3 * i + 1] = (double)y; ref[3 * i + 2] = (double)z;
+    to_double(p, box, px, py, pz);
+    ref[3 * i] = px; ref[3 * i + 1] = py; ref[3 * i + 2] = pz;
 }
 
 template <typename R>
 __global__ void k_update(const Ctl *__restrict__ ctl, const double *__restrict__ spos,
                          const double *__restrict__ svel, int n, double cx, double cy, double cz,
-                         double Lx, double Ly, double Lz, typename Vec4<R>::type *pos0,
-                         typename Vec4<R>::type *pos1, typename Vec4<R>::type *__restrict__ vel,
-                         const int *__restrict__ orig, int *__restrict__ img)
+                         Box<R> box, typename Pos4<R>::type *pos0, typename Pos4<R>::type *pos1,
+                         typename Vec4<R>::type *__restrict__ vel, const int *__restrict__ orig,
+                         int *__restrict__ img)
 {
     typedef typename Vec4<R>::type V4;
-    V4 *pos = ctl->cur ? pos1 : pos0;
+    typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     size_t o = 3 * (size_t)orig[s];
     if (spos) {
         double px = spos[o] - cx, py = spos[o + 1] - cy, pz = spos[o + 2] - cz;
-        double kx = rint(px / Lx), ky = rint(py / Ly), kz = rint(pz / Lz);
+        double kx = rint(px / box.Ld[0]), ky = rint(py / box.Ld[1]), kz = rint(pz / box.Ld[2]);
         img[o] += (int)kx; img[o + 1] += (int)ky; img[o + 2] += (int)kz;
-        V4 p = pos[s];
-        pos[s] = make4((R)(px - kx * Lx), (R)(py - ky * Ly), (R)(pz - kz * Lz), p.w);
+        pos[s] = encode_pos(px - kx * box.Ld[0], py - ky * box.Ld[1], pz - kz * box.Ld[2], ptype(pos[s]), box);
     }
     if (svel) {
         V4 v = vel[s];
@@ -369,8 +377,8 @@ __global__ void k_update(const Ctl *__restrict__ ctl, const double *__restrict__
 }
 
 template <typename R>
-__global__ void k_export(const Ctl *__restrict__ ctl, int n, double cx, double cy, double cz,
-                         const typename Vec4<R>::type *pos0, const typename Vec4<R>::type *pos1,
+__global__ void k_export(const Ctl *__restrict__ ctl, int n, double cx, double cy, double cz, Box<R> box,
+                         const typename Pos4<R>::type *pos0, const typename Pos4<R>::type *pos1,
                          const typename Vec4<R>::type *__restrict__ vel,
                          const typename Vec4<R>::type *__restrict__ frc, const R *__restrict__ vir,
                          const int *__restrict__ orig, double *__restrict__ opos,
@@ -378,13 +386,14 @@ __global__ void k_export(const Ctl *__restrict__ ctl, int n, double cx, double c
                          double *__restrict__ ope, double *__restrict__ ovir)
 {
     typedef typename Vec4<R>::type V4;
-    const V4 *pos = ctl->cur ? pos1 : pos0;
+    const typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     size_t o = (size_t)orig[s];
     if (opos) {
-        V4 p = pos[s];
-        opos[3 * o] = (double)p.x + cx; opos[3 * o + 1] = (double)p.y + cy; opos[3 * o + 2] = (double)p.z + cz;
+        double x, y, z;
+        to_double(pos[s], box, x, y, z);
+        opos[3 * o] = x + cx; opos[3 * o + 1] = y + cy; opos[3 * o + 2] = z + cz;
     }
     if (ovel) {
         V4 v = vel[s];
@@ -399,19 +408,19 @@ __global__ void k_export(const Ctl *__restrict__ ctl, int n, double cx, double c
 }
 
 template <typename R>
-__global__ void k_mark_ref(const Ctl *__restrict__ ctl, int n, const typename Vec4<R>::type *pos0,
-                           const typename Vec4<R>::type *pos1, const int *__restrict__ orig,
+__global__ void k_mark_ref(const Ctl *__restrict__ ctl, int n, const typename Pos4<R>::type *pos0,
+                           const typename Pos4<R>::type *pos1, const int *__restrict__ orig,
                            const int *__restrict__ img, Box<R> box, double *__restrict__ ref)
 {
-    typedef typename Vec4<R>::type V4;
-    const V4 *pos = ctl->cur ? pos1 : pos0;
+    const typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     size_t o = 3 * (size_t)orig[s];
-    V4 p = pos[s];
-    ref[o] = (double)p.x + (double)img[o] * (double)box.L[0];
-    ref[o + 1] = (double)p.y + (double)img[o + 1] * (double)box.L[1];
-    ref[o + 2] = (double)p.z + (double)img[o + 2] * (double)box.L[2];
+    double x, y, z;
+    to_double(pos[s], box, x, y, z);
+    ref[o] = x + (double)img[o] * box.Ld[0];
+    ref[o + 1] = y + (double)img[o + 1] * box.Ld[1];
+    ref[o + 2] = z + (double)img[o + 2] * box.Ld[2];
 }
 
 // export the list in original numbering: out[orig[s]*stride + k] = orig[nbr]
@@ -472,8 +481,8 @@ int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     if (mass) CU(cudaMemcpyAsync(smass, mass, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(c->stage_i, species, n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_ingest<R>, cdiv(n, 256), 256, spos, vel ? svel : nullptr, c->stage_i, mass ? smass : nullptr,
-           (int)n, c->center[0], c->center[1], c->center[2], c->side[0], c->side[1], c->side[2],
-           (V4 *)c->pos[0], (V4 *)c->vel, c->orig, c->img, c->ref);
+           (int)n, c->center[0], c->center[1], c->center[2], make_box<R>(c),
+           (P4 *)c->pos[0], (V4 *)c->vel, c->orig, c->img, c->ref);
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     return B2_OK;
@@ -488,8 +497,8 @@ int Impl<R>::update(b2_ctx *c, const double *pos, const double *vel)
     if (pos) CU(cudaMemcpyAsync(spos, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     if (vel) CU(cudaMemcpyAsync(svel, vel, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_update<R>, cdiv(n, 256), 256, c->ctl, pos ? spos : nullptr, vel ? svel : nullptr, (int)n,
-           c->center[0], c->center[1], c->center[2], c->side[0], c->side[1], c->side[2],
-           (V4 *)c->pos[0], (V4 *)c->pos[1], (V4 *)c->vel, c->orig, c->img);
+           c->center[0], c->center[1], c->center[2], make_box<R>(c),
+           (P4 *)c->pos[0], (P4 *)c->pos[1], (V4 *)c->vel, c->orig, c->img);
     CU(cudaStreamSynchronize(c->stream));
     if (pos) {
         c->list_dirty = true;
@@ -504,8 +513,8 @@ int Impl<R>::download(b2_ctx *c, double *pos, double *vel, int32_t *image)
     int64_t n = c->n;
     if (n == 0) return B2_OK;
     double *spos = c->stage, *svel = c->stage + 3 * n;
-    LAUNCH(k_export<R>, cdiv(n, 256), 256, c->ctl, (int)n, c->center[0], c->center[1], c->center[2],
-           (const V4 *)c->pos[0], (const V4 *)c->pos[1], (const V4 *)c->vel, (const V4 *)c->frc,
+    LAUNCH(k_export<R>, cdiv(n, 256), 256, c->ctl, (int)n, c->center[0], c->center[1], c->center[2], make_box<R>(c),
+           (const P4 *)c->pos[0], (const P4 *)c->pos[1], (const V4 *)c->vel, (const V4 *)c->frc,
            (const R *)c->vir, c->orig, pos ? spos : nullptr, vel ? svel : nullptr, nullptr, nullptr, nullptr);
     if (pos) CU(cudaMemcpyAsync(pos, spos, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     if (vel) CU(cudaMemcpyAsync(vel, svel, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -518,7 +527,7 @@ template <typename R>
 int Impl<R>::mark_reference(b2_ctx *c)
 {
     if (c->n == 0) return B2_OK;
-    LAUNCH(k_mark_ref<R>, cdiv(c->n, 256), 256, c->ctl, (int)c->n, (const V4 *)c->pos[0], (const V4 *)c->pos[1],
+    LAUNCH(k_mark_ref<R>, cdiv(c->n, 256), 256, c->ctl, (int)c->n, (const P4 *)c->pos[0], (const P4 *)c->pos[1],
            c->orig, c->img, make_box<R>(c), c->ref);
     return B2_OK;
 }
@@ -532,7 +541,7 @@ int Impl<R>::thermo(b2_ctx *c, double *out, bool want_stress, double *stress9)
     if ((rc = ensure_forces(c))) return rc;
     int n = (int)c->n;
     int nblk = std::min(MAX_RED_BLOCKS, cdiv(n, RED_THREADS));
-    LAUNCH(k_thermo_partial<R>, nblk, RED_THREADS, c->ctl, (const V4 *)c->pos[0], (const V4 *)c->pos[1],
+    LAUNCH(k_thermo_partial<R>, nblk, RED_THREADS, c->ctl, (const P4 *)c->pos[0], (const P4 *)c->pos[1],
            (const V4 *)c->vel, (const V4 *)c->frc, (const R *)c->vir, c->orig, c->img, c->ref, n,
            make_box<R>(c), c->partial);
     LAUNCH(k_sum_partials, 1, 32, c->partial, nblk, 9, c->ctl->red);
@@ -572,8 +581,8 @@ int Impl<R>::compute(b2_ctx *c, int what, double *energy, double *virial, double
     if (forces || pe || vir) {
         int64_t n = c->n;
         double *sf = c->stage, *spe = c->stage + 3 * n, *sv = c->stage + 4 * n;
-        LAUNCH(k_export<R>, cdiv(n, 256), 256, c->ctl, (int)n, 0.0, 0.0, 0.0, (const V4 *)c->pos[0],
-               (const V4 *)c->pos[1], (const V4 *)c->vel, (const V4 *)c->frc, (const R *)c->vir, c->orig,
+        LAUNCH(k_export<R>, cdiv(n, 256), 256, c->ctl, (int)n, 0.0, 0.0, 0.0, make_box<R>(c), (const P4 *)c->pos[0],
+               (const P4 *)c->pos[1], (const V4 *)c->vel, (const V4 *)c->frc, (const R *)c->vir, c->orig,
                nullptr, nullptr, forces ? sf : nullptr, pe ? spe : nullptr, vir ? sv : nullptr);
         if (forces) CU(cudaMemcpyAsync(forces, sf, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
         if (pe) CU(cudaMemcpyAsync(pe, spe, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -623,8 +632,8 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
     LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0);
     StepArgs<R> a;
     a.ctl = c->ctl;
-    a.pos[0] = (V4 *)c->pos[0];
-    a.pos[1] = (V4 *)c->pos[1];
+    a.pos[0] = (P4 *)c->pos[0];
+    a.pos[1] = (P4 *)c->pos[1];
     a.vel = (V4 *)c->vel;
     a.nbr = c->nbr;
     a.nnb = c->nnb;
@@ -689,8 +698,8 @@ int Impl<R>::minimize(b2_ctx *c, int method, int64_t max_steps, double dt, doubl
     // k_ctl_begin marks a zero budget as done; the first iteration must still test convergence
     MinArgs<R> a;
     a.ctl = c->ctl;
-    a.pos[0] = (V4 *)c->pos[0];
-    a.pos[1] = (V4 *)c->pos[1];
+    a.pos[0] = (P4 *)c->pos[0];
+    a.pos[1] = (P4 *)c->pos[1];
     a.vel = (V4 *)c->vel;
     a.frc = (const V4 *)c->frc;
     a.orig = c->orig;

@@ -26,27 +26,23 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
 // One particle against its Verlet row.  Pair expressions are the oracle's:
 //   r2inv = 1/r2 ; r6inv = r2inv^3
 //   u = r6inv (c12 r6inv - c6) - ushift ;  w = r6inv (12 c12 r6inv - 6 c6) = r.F
-//   F_i += (w r2inv) d ,  d = r_i - r_j  (minimum image, particle.py:129-130)
+//   F_i += (w r2inv) d ,  d = r_i - r_j  (minimum image, particle.py:129-130; see delta())
 template <typename R, bool EV, bool STRESS>
-__device__ __forceinline__ void pair_row(const typename Vec4<R>::type *__restrict__ pos,
+__device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restrict__ pos,
                                          const int *__restrict__ row, int cnt,
-                                         typename Vec4<R>::type pi, const Box<R> &box,
+                                         typename Pos4<R>::type pi, const Box<R> &box,
                                          const PairTab<R> &tab, int nsp,
-                                         R &fx, R &fy, R &fz, R &pe, R &vir, R *st)
+                                         R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
 {
-    typedef typename Vec4<R>::type V4;
-    const int ti = type_of(pi.w) * nsp;
-    const R Lx = box.L[0], Ly = box.L[1], Lz = box.L[2];
-    const R ix = box.invL[0], iy = box.invL[1], iz = box.invL[2];
+    typedef typename Pos4<R>::type P4;
+    const int ti = ptype(pi) * nsp;
     int k = 0;
 #define B2_PAIR(PJ)                                                                   \
     {                                                                                 \
-        R dx = pi.x - PJ.x, dy = pi.y - PJ.y, dz = pi.z - PJ.z;                       \
-        dx -= Lx * r_rint(dx * ix);                                                   \
-        dy -= Ly * r_rint(dy * iy);                                                   \
-        dz -= Lz * r_rint(dz * iz);                                                   \
+        R dx, dy, dz;                                                                 \
+        delta(pi, PJ, box, dx, dy, dz);                                               \
         R r2 = dx * dx + dy * dy + dz * dz;                                           \
-        int a = ti + type_of(PJ.w);                                                   \
+        int a = ti + ptype(PJ);                                                       \
         if (r2 < tab.rc2[a]) {                                                        \
             R r2inv = r_rcp(r2);                                                      \
             R r6inv = r2inv * r2inv * r2inv;                                          \
@@ -54,10 +50,26 @@ __device__ __forceinline__ void pair_row(const typename Vec4<R>::type *__restric
             R w = r6inv * ((R)12 * c12 * r6inv - (R)6 * c6);                          \
             R fp = w * r2inv;                                                         \
             fx += fp * dx; fy += fp * dy; fz += fp * dz;                              \
-            if (EV) { pe += r6inv * (c12 * r6inv - c6) - tab.ush[a]; vir += w; }      \
-            if (STRESS) {                                                             \
-                st[0] += dx * fp * dx; st[1] += dx * fp * dy; st[2] += dx * fp * dz;  \
-                st[3] += dy * fp * dy; st[4] += dy * fp * dz; st[5] += dz * fp * dz;  \
+        }                                                                             \
+        if (EV || STRESS) {                                                           \
+            /* observables: fp64 pair arithmetic on the stored positions, in both */ \
+            /* precisions (totals cancel heavily; fp32 would leave systematic    */ \
+            /* errors that do not average out)                                   */ \
+            double ex, ey, ez;                                                        \
+            delta_d(pi, PJ, box, ex, ey, ez);                                         \
+            double q2 = ex * ex + ey * ey + ez * ez;                                  \
+            if (q2 < g_pair.rc2[a]) {                                                 \
+                double q2inv = 1.0 / q2;                                              \
+                double q6inv = q2inv * q2inv * q2inv;                                 \
+                double d12 = g_pair.c12[a], d6 = g_pair.c6[a];                        \
+                double wd = q6inv * (12.0 * d12 * q6inv - 6.0 * d6);                  \
+                if (EV) { pe += q6inv * (d12 * q6inv - d6) - g_pair.ushift[a]; vir += wd; } \
+                if (STRESS) {                                                         \
+                    double gp = wd * q2inv;                                           \
+                    double gx = gp * ex, gy = gp * ey, gz = gp * ez;                  \
+                    st[0] += ex * gx; st[1] += ex * gy; st[2] += ex * gz;             \
+                    st[3] += ey * gy; st[4] += ey * gz; st[5] += ez * gz;             \
+                }                                                                     \
             }                                                                         \
         }                                                                             \
     }
@@ -66,12 +78,12 @@ __device__ __forceinline__ void pair_row(const typename Vec4<R>::type *__restric
         int j1 = ld_stream(row + (size_t)(k + 1) * 32);
         int j2 = ld_stream(row + (size_t)(k + 2) * 32);
         int j3 = ld_stream(row + (size_t)(k + 3) * 32);
-        V4 p0 = pos[j0], p1 = pos[j1], p2 = pos[j2], p3 = pos[j3];
+        P4 p0 = pos[j0], p1 = pos[j1], p2 = pos[j2], p3 = pos[j3];
         B2_PAIR(p0) B2_PAIR(p1) B2_PAIR(p2) B2_PAIR(p3)
     }
     for (; k < cnt; k++) {
         int j = ld_stream(row + (size_t)k * 32);
-        V4 p0 = pos[j];
+        P4 p0 = pos[j];
         B2_PAIR(p0)
     }
 #undef B2_PAIR
@@ -79,7 +91,7 @@ __device__ __forceinline__ void pair_row(const typename Vec4<R>::type *__restric
 
 template <typename R> struct ForceArgs {
     Ctl *ctl;
-    const typename Vec4<R>::type *pos[2];
+    const typename Pos4<R>::type *pos[2];
     typename Vec4<R>::type *frc;    // (fx, fy, fz, pe_i)
     R *vir;                          // vir_i
     const int *nbr, *nnb;
@@ -94,29 +106,30 @@ template <typename R, bool EV, bool STRESS>
 __global__ void __launch_bounds__(FORCE_THREADS)
 k_force(ForceArgs<R> a)
 {
-    typedef typename Vec4<R>::type V4;
+    typedef typename Pos4<R>::type P4;
     const Ctl *ctl = a.ctl;
     if (a.guarded && (ctl->halt_rebuild | ctl->overflow | ctl->done)) return;
     __shared__ PairTab<R> tab;
     load_pair_table(tab);
     __syncthreads();
-    const V4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
+    const P4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    R st[6] = {0, 0, 0, 0, 0, 0};
+    double st[6] = {0, 0, 0, 0, 0, 0};
     if (i < a.n) {
-        V4 pi = pos[i];
-        R fx = 0, fy = 0, fz = 0, pe = 0, vir = 0;
+        P4 pi = pos[i];
+        R fx = 0, fy = 0, fz = 0;
+        double pe = 0, vir = 0;
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
         pair_row<R, EV, STRESS>(pos, row, a.nnb[i], pi, a.box, tab, g_pair.nsp, fx, fy, fz, pe, vir, st);
-        a.frc[i] = make4(fx, fy, fz, (R)0.5 * pe);
-        if (EV) a.vir[i] = (R)0.5 * vir;
+        a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
+        if (EV) a.vir[i] = (R)(0.5 * vir);
     }
     if (STRESS) {
         __shared__ double s_st[FORCE_THREADS / 32][6];
         int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 #pragma unroll
         for (int q = 0; q < 6; q++) {
-            double v = warp_sum((double)st[q]);
+            double v = warp_sum(st[q]);
             if (lane == 0) s_st[w][q] = v;
         }
         __syncthreads();
@@ -130,7 +143,7 @@ k_force(ForceArgs<R> a)
 
 template <typename R> struct StepArgs {
     Ctl *ctl;
-    typename Vec4<R>::type *pos[2];
+    typename Pos4<R>::type *pos[2];
     typename Vec4<R>::type *vel;     // (vx, vy, vz, mass)
     const int *nbr, *nnb, *orig;
     int *img;                        // [3 n] box crossings, by ORIGINAL id
@@ -149,6 +162,7 @@ __global__ void __launch_bounds__(FORCE_THREADS)
 k_step_nve(StepArgs<R> a)
 {
     typedef typename Vec4<R>::type V4;
+    typedef typename Pos4<R>::type P4;
     Ctl *ctl = a.ctl;
     if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
     __shared__ PairTab<R> tab;
@@ -157,26 +171,25 @@ k_step_nve(StepArgs<R> a)
     load_pair_table(tab);
     __syncthreads();
     const unsigned cur = ctl->cur;
-    const V4 *__restrict__ pos = cur ? a.pos[1] : a.pos[0];
-    V4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
+    const P4 *__restrict__ pos = cur ? a.pos[1] : a.pos[0];
+    P4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     float v2 = 0.f;
     if (i < a.n) {
-        V4 pi = pos[i];
-        R fx = 0, fy = 0, fz = 0, pe = 0, vir = 0;
+        P4 pi = pos[i];
+        R fx = 0, fy = 0, fz = 0;
+        double pe = 0, vir = 0;
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
         pair_row<R, false, false>(pos, row, a.nnb[i], pi, a.box, tab, g_pair.nsp, fx, fy, fz, pe, vir, nullptr);
         V4 v = a.vel[i];
         R s = a.kick / v.w;
         v.x += s * fx; v.y += s * fy; v.z += s * fz;
-        R x = pi.x + a.drift * v.x, y = pi.y + a.drift * v.y, z = pi.z + a.drift * v.z;
-        R kx = r_rint(x * a.box.invL[0]), ky = r_rint(y * a.box.invL[1]), kz = r_rint(z * a.box.invL[2]);
-        if (kx != (R)0 || ky != (R)0 || kz != (R)0) {
-            x -= kx * a.box.L[0]; y -= ky * a.box.L[1]; z -= kz * a.box.L[2];
+        int kx, ky, kz;
+        posn[i] = advance(pi, a.drift * v.x, a.drift * v.y, a.drift * v.z, a.box, kx, ky, kz);
+        if (kx | ky | kz) {
             int *im = a.img + 3 * (size_t)a.orig[i];
-            im[0] += (int)kx; im[1] += (int)ky; im[2] += (int)kz;
+            im[0] += kx; im[1] += ky; im[2] += kz;
         }
-        posn[i] = make4(x, y, z, pi.w);
         a.vel[i] = v;
         // rounded up: the bound must never be smaller than the true speed
         v2 = __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
@@ -251,18 +264,22 @@ __device__ __forceinline__ void block_partials(double (&q)[NQ], double *__restri
 
 template <typename R>
 __global__ void __launch_bounds__(RED_THREADS)
-k_thermo_partial(const Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0,
-                 const typename Vec4<R>::type *pos1,
+k_thermo_partial(const Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
+                 const typename Pos4<R>::type *pos1,
                  const typename Vec4<R>::type *__restrict__ vel,
                  const typename Vec4<R>::type *__restrict__ frc, const R *__restrict__ vir,
                  const int *__restrict__ orig, const int *__restrict__ img,
                  const double *__restrict__ ref, int n, Box<R> box, double *__restrict__ partial)
 {
     typedef typename Vec4<R>::type V4;
-    const V4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
+    typedef typename Pos4<R>::type P4;
+    const P4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
     double q[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        V4 v = vel[i], f = frc[i], p = pos[i];
+        V4 v = vel[i], f = frc[i];
+        P4 p = pos[i];
+        double rx, ry, rz;
+        to_double(p, box, rx, ry, rz);
         double m = (double)v.w;
         double vx = v.x, vy = v.y, vz = v.z, fx = f.x, fy = f.y, fz = f.z;
         q[Q_KIN] += 0.5 * m * ((vx * vx + vy * vy) + vz * vz);
@@ -272,9 +289,9 @@ k_thermo_partial(const Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0
         q[Q_PX] += m * vx; q[Q_PY] += m * vy; q[Q_PZ] += m * vz;
         q[Q_MASS] += m;
         size_t o = 3 * (size_t)orig[i];
-        double ux = ((double)p.x + (double)img[o + 0] * (double)box.L[0]) - ref[o + 0];
-        double uy = ((double)p.y + (double)img[o + 1] * (double)box.L[1]) - ref[o + 1];
-        double uz = ((double)p.z + (double)img[o + 2] * (double)box.L[2]) - ref[o + 2];
+        double ux = (rx + (double)img[o + 0] * box.Ld[0]) - ref[o + 0];
+        double uy = (ry + (double)img[o + 1] * box.Ld[1]) - ref[o + 1];
+        double uz = (rz + (double)img[o + 2] * box.Ld[2]) - ref[o + 2];
         q[Q_MSD] += (ux * ux + uy * uy) + uz * uz;
     }
     block_partials<9>(q, partial);
@@ -382,7 +399,7 @@ __global__ void k_min_logic(Ctl *ctl, const double *__restrict__ partial, int nb
 
 template <typename R> struct MinArgs {
     Ctl *ctl;
-    typename Vec4<R>::type *pos[2];
+    typename Pos4<R>::type *pos[2];
     typename Vec4<R>::type *vel;
     const typename Vec4<R>::type *frc;
     const int *orig;
@@ -401,13 +418,15 @@ k_min_step(MinArgs<R> a)
     Ctl *ctl = a.ctl;
     if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
     __shared__ float s_d2[RED_THREADS / 32];
-    V4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
+    typedef typename Pos4<R>::type P4;
+    P4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
     const int mode = ctl->min_mode;
     const R h = (R)ctl->step_len, ca = (R)ctl->red[0], cb = (R)ctl->red[1];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     float d2 = 0.f;
     if (i < a.n) {
-        V4 p = pos[i], v = a.vel[i], f = a.frc[i];
+        P4 p = pos[i];
+        V4 v = a.vel[i], f = a.frc[i];
         R ux, uy, uz;
         if (mode == MIN_MODE_FIRE) {
             R s = h / v.w;
@@ -419,14 +438,12 @@ k_min_step(MinArgs<R> a)
             ux = h * f.x; uy = h * f.y; uz = h * f.z;
             v.x = f.x; v.y = f.y; v.z = f.z;
         }
-        R x = p.x + ux, y = p.y + uy, z = p.z + uz;
-        R kx = r_rint(x * a.box.invL[0]), ky = r_rint(y * a.box.invL[1]), kz = r_rint(z * a.box.invL[2]);
-        if (kx != (R)0 || ky != (R)0 || kz != (R)0) {
-            x -= kx * a.box.L[0]; y -= ky * a.box.L[1]; z -= kz * a.box.L[2];
+        int kx, ky, kz;
+        pos[i] = advance(p, ux, uy, uz, a.box, kx, ky, kz);
+        if (kx | ky | kz) {
             int *im = a.img + 3 * (size_t)a.orig[i];
-            im[0] += (int)kx; im[1] += (int)ky; im[2] += (int)kz;
+            im[0] += kx; im[1] += ky; im[2] += kz;
         }
-        pos[i] = make4(x, y, z, p.w);
         a.vel[i] = v;
         d2 = __double2float_ru((double)ux * ux + (double)uy * uy + (double)uz * uz);
     }

@@ -14,17 +14,17 @@
 
 // ---- keys -----------------------------------------------------------------
 template <typename R>
-__global__ void k_cell_keys(const Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0,
-                            const typename Vec4<R>::type *pos1, int n, Box<R> box, Grid g,
+__global__ void k_cell_keys(const Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
+                            const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
                             uint32_t *__restrict__ keys, uint32_t *__restrict__ vals)
 {
     if (!ctl->halt_rebuild) return;
-    const typename Vec4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    const typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    typename Vec4<R>::type p = pos[i];
+    typename Pos4<R>::type p = pos[i];
     int cx, cy, cz;
-    cell_of(box, g, p.x, p.y, p.z, cx, cy, cz);
+    cell_of(box, g, p, cx, cy, cz);
     keys[i] = morton3(cx, cy, cz);
     vals[i] = (uint32_t)i;
 }
@@ -148,14 +148,14 @@ k_sort_scatter(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ kin,
 // ---- permute the particle arrays into sorted order ---------------------------
 template <typename R>
 __global__ void k_gather(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ perm, int n,
-                         const typename Vec4<R>::type *pos0, const typename Vec4<R>::type *pos1,
+                         const typename Pos4<R>::type *pos0, const typename Pos4<R>::type *pos1,
                          const typename Vec4<R>::type *__restrict__ vel,
                          const int *__restrict__ orig,
-                         typename Vec4<R>::type *__restrict__ tpos,
+                         typename Pos4<R>::type *__restrict__ tpos,
                          typename Vec4<R>::type *__restrict__ tvel, int *__restrict__ torig)
 {
     if (!ctl->halt_rebuild) return;
-    const typename Vec4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    const typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     uint32_t src = perm[s];
@@ -166,14 +166,14 @@ __global__ void k_gather(const Ctl *__restrict__ ctl, const uint32_t *__restrict
 
 template <typename R>
 __global__ void k_gather_commit(const Ctl *__restrict__ ctl, int n,
-                                const typename Vec4<R>::type *__restrict__ tpos,
+                                const typename Pos4<R>::type *__restrict__ tpos,
                                 const typename Vec4<R>::type *__restrict__ tvel,
                                 const int *__restrict__ torig,
-                                typename Vec4<R>::type *pos0, typename Vec4<R>::type *pos1,
+                                typename Pos4<R>::type *pos0, typename Pos4<R>::type *pos1,
                                 typename Vec4<R>::type *__restrict__ vel, int *__restrict__ orig)
 {
     if (!ctl->halt_rebuild) return;
-    typename Vec4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     pos[s] = tpos[s];
@@ -205,31 +205,27 @@ __global__ void k_cell_bounds(const Ctl *__restrict__ ctl, const uint32_t *__res
 }
 
 // ---- Verlet list -----------------------------------------------------------
-// Membership: r2 < (rcut_ab + skin)^2, strict, with the reference's minimum
-// image d - rint(d/L)*L (atooms/system/particle.py:129-130) and
-// r2 = (dx*dx + dy*dy) + dz*dz, all correctly rounded and uncontracted.  The
-// division-free estimate decides every pair outside a thin band around the
-// threshold; the band is re-evaluated with the canonical expression, so the
-// result is bit-identical to evaluating the canonical one everywhere.
+// Membership: r2 < (rcut_ab + skin)^2, strict.  r2 is the CANONICAL squared
+// minimum-image distance (r2_canon): correctly rounded and uncontracted —
+//   fp64: d - rint(d/L)*L (atooms/system/particle.py:129-130), (dx*dx + dy*dy) + dz*dz
+//   fp32: d = float(wrapped int difference) * float(L / 2^32), same sum
+// The cheap contracted estimate decides every pair outside a thin band around
+// the threshold; the band is re-evaluated canonically, so the result is
+// bit-identical to evaluating the canonical expression everywhere.
 template <typename R> struct PredEps;
 template <> struct PredEps<float>  { static constexpr float  v = 2e-5f; };
 template <> struct PredEps<double> { static constexpr double v = 1e-11; };
 
 template <typename R>
-__device__ __forceinline__ bool in_list(const Box<R> &box, R xi, R yi, R zi, R xj, R yj, R zj, R rl2)
+__device__ __forceinline__ bool in_list(const Box<R> &box, const typename Pos4<R>::type &pi,
+                                        const typename Pos4<R>::type &pj, R rl2)
 {
-    R dx = xi - xj, dy = yi - yj, dz = zi - zj;
-    R ex = dx - r_rint(dx * box.invL[0]) * box.L[0];
-    R ey = dy - r_rint(dy * box.invL[1]) * box.L[1];
-    R ez = dz - r_rint(dz * box.invL[2]) * box.L[2];
-    R r2 = ex * ex + ey * ey + ez * ez;
+    R dx, dy, dz;
+    delta(pi, pj, box, dx, dy, dz);
+    R r2 = dx * dx + dy * dy + dz * dz;
     if (r2 > rl2 * ((R)1 + PredEps<R>::v)) return false;
     if (r2 < rl2 * ((R)1 - PredEps<R>::v)) return true;
-    ex = nc_sub(dx, nc_mul(r_rint(nc_div(dx, box.L[0])), box.L[0]));
-    ey = nc_sub(dy, nc_mul(r_rint(nc_div(dy, box.L[1])), box.L[1]));
-    ez = nc_sub(dz, nc_mul(r_rint(nc_div(dz, box.L[2])), box.L[2]));
-    r2 = nc_add(nc_add(nc_mul(ex, ex), nc_mul(ey, ey)), nc_mul(ez, ez));
-    return r2 < rl2;
+    return r2_canon(pi, pj, box) < rl2;
 }
 
 __device__ __forceinline__ float  rl2_of(const PairConst &pc, int a, float)  { return pc.rl2_f[a]; }
@@ -241,36 +237,36 @@ __device__ __forceinline__ double rl2_of(const PairConst &pc, int a, double) { r
 // so a warp of the force kernel reads one coalesced 128-byte row per k.
 template <typename R>
 __global__ void __launch_bounds__(128)
-k_build_list(Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0,
-             const typename Vec4<R>::type *pos1, int n, Box<R> box, Grid g,
+k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
+             const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
              const int *__restrict__ cell_start, const int *__restrict__ cell_end,
              int *__restrict__ nbr, int *__restrict__ nnb, int cap)
 {
     if (!ctl->halt_rebuild) return;
-    typedef typename Vec4<R>::type V4;
-    const V4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
+    typedef typename Pos4<R>::type P4;
+    const P4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
     __shared__ R s_rl2[B2_MAXSP * B2_MAXSP];
     if (threadIdx.x < B2_MAXSP * B2_MAXSP) s_rl2[threadIdx.x] = rl2_of(g_pair, threadIdx.x, (R)0);
     __syncthreads();
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int nsp = g_pair.nsp;
-    V4 pi = pos[i];
-    int ti = type_of(pi.w);
+    P4 pi = pos[i];
+    int ti = ptype(pi);
     int *row = nbr + ((size_t)(i >> 5) * cap) * 32 + (i & 31);
     int cnt = 0;
     if (g.allpairs) {
         for (int j = 0; j < n; j++) {
             if (j == i) continue;
-            V4 pj = pos[j];
-            if (in_list(box, pi.x, pi.y, pi.z, pj.x, pj.y, pj.z, s_rl2[ti * nsp + type_of(pj.w)])) {
+            P4 pj = pos[j];
+            if (in_list<R>(box, pi, pj, s_rl2[ti * nsp + ptype(pj)])) {
                 if (cnt < cap) row[(size_t)cnt * 32] = j;
                 cnt++;
             }
         }
     } else {
         int cx, cy, cz;
-        cell_of(box, g, pi.x, pi.y, pi.z, cx, cy, cz);
+        cell_of(box, g, pi, cx, cy, cz);
         for (int dz = -1; dz <= 1; dz++) {
             int z = cz + dz;
             z = z < 0 ? z + g.nc[2] : (z >= g.nc[2] ? z - g.nc[2] : z);
@@ -284,9 +280,8 @@ k_build_list(Ctl *__restrict__ ctl, const typename Vec4<R>::type *pos0,
                     int s = cell_start[key], e = cell_end[key];
                     for (int j = s; j < e; j++) {
                         if (j == i) continue;
-                        V4 pj = pos[j];
-                        if (in_list(box, pi.x, pi.y, pi.z, pj.x, pj.y, pj.z,
-                                    s_rl2[ti * nsp + type_of(pj.w)])) {
+                        P4 pj = pos[j];
+                        if (in_list<R>(box, pi, pj, s_rl2[ti * nsp + ptype(pj)])) {
                             if (cnt < cap) row[(size_t)cnt * 32] = j;
                             cnt++;
                         }

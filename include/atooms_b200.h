@@ -174,8 +174,9 @@ int b2_thermo(b2_ctx *ctx, double out[B2_T_LEN]);
 
 /* Full Verlet list of the current configuration in ORIGINAL numbering, each
  * row sorted ascending: count[i], nbr[i*stride + k].  Membership rule:
- * r2 < (rcut_ab + skin)^2 with d - rint(d/L)*L minimum image
- * (particle.py:129-130) and r2 = (dx*dx + dy*dy) + dz*dz, evaluated in the
+ * r2 < (rcut_ab + skin)^2; fp64: d - rint(d/L)*L minimum image
+ * (particle.py:129-130); fp32: wrapped difference of the 32-bit fixed-point
+ * coordinates times float(L/2^32); r2 = (dx*dx + dy*dy) + dz*dz, evaluated in the
  * context's precision.  nbr may be NULL (counts only).  Returns B2_EINVAL if
  * stride < max count (max count is written to *max_count first).            */
 int b2_neighbors(b2_ctx *ctx, int32_t *count, int32_t *nbr, int32_t stride,

@@ -167,6 +167,17 @@ static inline void fold3(const b2_ctx *c, double *x, int32_t *img)
     }
 }
 
+/* fp32 engine: positions are 32-bit fixed-point fractions of the cell,
+ * x_int = round(x / L * 2^32); the wrapped integer difference is the minimum
+ * image, scaled by float(L / 2^32) (see b2_common.cuh, r2_canon). */
+static inline int32_t fixed32(double x_rel, double L)
+{
+    double f = x_rel / L;
+    f -= rint(f);
+    long long k = llrint(f * 4294967296.0);
+    return (int32_t)(uint32_t)(k & 0xffffffffLL);
+}
+
 int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
               const int32_t *species, const double *mass)
 {
@@ -203,9 +214,10 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
             if (vel) c->vel[3 * i + d] = vel[3 * i + d];
         }
         fold3(c, c->pos + 3 * i, NULL);
-        if (c->precision == B2_FP32)   /* the fp32 engine holds float positions */
+        if (c->precision == B2_FP32)   /* the fp32 engine holds fixed-point positions */
             for (int d = 0; d < 3; d++)
-                c->pos[3 * i + d] = (double)(float)(c->pos[3 * i + d] - c->center[d]) + c->center[d];
+                c->pos[3 * i + d] = (double)fixed32(c->pos[3 * i + d] - c->center[d], c->side[d]) *
+                                    (c->side[d] / 4294967296.0) + c->center[d];
     }
     memcpy(c->ref, c->pos, n3 * sizeof(double));
     c->list_valid = c->forces_valid = 0;
@@ -269,14 +281,13 @@ static inline int in_list64(const double *xi, const double *xj, const double *L,
 static inline int in_list32(const double *xi, const double *xj, const double *ctr,
                             const double *L, float rl2)
 {
-    float Lx = (float)L[0], Ly = (float)L[1], Lz = (float)L[2];
-    float dx = (float)(xi[0] - ctr[0]) - (float)(xj[0] - ctr[0]);
-    float dy = (float)(xi[1] - ctr[1]) - (float)(xj[1] - ctr[1]);
-    float dz = (float)(xi[2] - ctr[2]) - (float)(xj[2] - ctr[2]);
-    dx = dx - rintf(dx / Lx) * Lx;
-    dy = dy - rintf(dy / Ly) * Ly;
-    dz = dz - rintf(dz / Lz) * Lz;
-    float r2 = (dx * dx + dy * dy) + dz * dz;
+    float d[3];
+    for (int k = 0; k < 3; k++) {
+        int32_t a = fixed32(xi[k] - ctr[k], L[k]), b = fixed32(xj[k] - ctr[k], L[k]);
+        int32_t w = (int32_t)((uint32_t)a - (uint32_t)b);
+        d[k] = (float)w * (float)(L[k] / 4294967296.0);
+    }
+    float r2 = (d[0] * d[0] + d[1] * d[1]) + d[2] * d[2];
     return r2 < rl2;
 }
 

@@ -35,7 +35,7 @@ Conventions followed (citations are into /root/reference):
 """
 import numpy
 
-__all__ = ['PairTable', 'lennard_jones', 'kob_andersen', 'compute', 'neighbor_list',
+__all__ = ['PairTable', 'lennard_jones', 'kob_andersen', 'compute', 'neighbor_list', 'quantize32',
            'fold', 'kinetic_energy', 'temperature', 'nve', 'fire', 'steepest_descent',
            'maxwell_boltzmann']
 
@@ -149,26 +149,50 @@ def compute(position, species, side, table, chunk=512, per_particle=False):
     return out
 
 
-def neighbor_list(position, species, side, table, skin, dtype=numpy.float64, chunk=512):
+def quantize32(position, side, center=None):
+    """Positions as the fp32 engine holds them: 32-bit fixed-point fractions of
+    the cell, x_int = round(x / L * 2^32) (wrapping), returned as float64
+    coordinates together with the integers."""
+    c = numpy.zeros(3) if center is None else numpy.asarray(center, dtype=numpy.float64)
+    side = numpy.asarray(side, dtype=numpy.float64)
+    f = (numpy.asarray(position, dtype=numpy.float64) - c) / side
+    f -= numpy.rint(f)
+    k = numpy.rint(f * 4294967296.0).astype(numpy.int64)
+    k = ((k + 2 ** 31) % 2 ** 32 - 2 ** 31)
+    return k * (side / 4294967296.0) + c, k.astype(numpy.int32)
+
+
+def neighbor_list(position, species, side, table, skin, dtype=numpy.float64, chunk=512, center=None):
     """Brute-force full Verlet list: j in list(i) iff r2 < (rcut_ab + skin)^2, strict.
 
-    The predicate is evaluated in `dtype` arithmetic exactly as
-        d  = x_i - x_j ;  d = d - rint(d / L) * L      (particle.py:129-130)
-        r2 = (dx*dx + dy*dy) + dz*dz                    (no FMA contraction)
-    so that membership is bit-comparable with the CUDA list in the same
-    precision.  Returns a list of sorted int32 arrays (original numbering).
+    The predicate is evaluated exactly as the engine of that precision does,
+    so that membership is bit-comparable:
+      float64: d = x_i - x_j ; d = d - rint(d / L) * L   (particle.py:129-130)
+      float32: d = float32(wrapped int32 difference of the fixed-point
+               coordinates) * float32(L / 2^32)
+      r2 = (dx*dx + dy*dy) + dz*dz in `dtype`, no FMA contraction.
+    Returns a list of sorted int32 arrays (original numbering).
     """
-    pos = numpy.ascontiguousarray(position, dtype=dtype)
-    side = numpy.asarray(side, dtype=dtype)
     spe = numpy.asarray(species, dtype=numpy.int64)
     rl = (table.rcut + skin).astype(dtype)
     rl2 = rl * rl
-    n = pos.shape[0]
+    fixed = numpy.dtype(dtype) == numpy.float32
+    if fixed:
+        _, ipos = quantize32(position, side, center)
+        scale = (numpy.asarray(side, dtype=numpy.float64) / 4294967296.0).astype(numpy.float32)
+    else:
+        pos = numpy.ascontiguousarray(position, dtype=numpy.float64)
+        side = numpy.asarray(side, dtype=numpy.float64)
+    n = len(spe)
     out = []
     for start in range(0, n, chunk):
         stop = min(n, start + chunk)
-        d = pos[start:stop, None, :] - pos[None, :, :]
-        d = d - numpy.rint(d / side) * side
+        if fixed:
+            w = (ipos[start:stop, None, :].astype(numpy.uint32) - ipos[None, :, :].astype(numpy.uint32))
+            d = w.astype(numpy.int32).astype(numpy.float32) * scale
+        else:
+            d = pos[start:stop, None, :] - pos[None, :, :]
+            d = d - numpy.rint(d / side) * side
         r2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
         assert r2.dtype == dtype
         mask = r2 < rl2[spe[start:stop, None], spe[None, :]]

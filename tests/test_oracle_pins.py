@@ -146,8 +146,7 @@ def test_neighbor_lists_agree(oracle_lib, precision, dtype):
     for name in ['ka_N256_rumd', 'ka_N1200']:
         d = golden(name)
         eng = make_engine(oracle_lib, d, ka, precision=precision)
-        pos = d['position'].astype(dtype).astype(numpy.float64)
-        ref = onp.neighbor_list(pos, d['species'], d['side'], ka, 0.3, dtype=dtype)
+        ref = onp.neighbor_list(d['position'], d['species'], d['side'], ka, 0.3, dtype=dtype)
         got = eng.neighbors()
         assert all(numpy.array_equal(a, b) for a, b in zip(got, ref))
 
