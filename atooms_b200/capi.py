@@ -58,6 +58,8 @@ SYMBOLS = {
     'b2_minimize': (_int, [_vp, _int, _i64, _dbl, _dbl, _c_lp, ctypes.POINTER(_int)]),
     'b2_stats': (_int, [_vp, _c_lp]),
     'b2_last_timing': (_int, [_vp, _c_dp, _c_lp]),
+    'b2_set_profile': (_int, [_vp, _int]),
+    'b2_profile': (_int, [_vp, _c_dp]),
 }
 
 
@@ -220,6 +222,13 @@ class Engine(object):
         self._call('b2_download', _dp(pos), _dp(vel), _ip(img))
         return pos, vel, img
 
+    def download_into(self, position=None, velocity=None, image=None):
+        """Copy state into caller-owned (N,3) C-contiguous arrays (e.g. pinned host memory)."""
+        for a, dt in ((position, numpy.float64), (velocity, numpy.float64), (image, numpy.int32)):
+            if a is not None and (a.dtype != dt or a.shape != (self.n, 3) or not a.flags.c_contiguous):
+                raise ValueError('download_into: arrays must be C-contiguous (N, 3) float64 / int32')
+        self._call('b2_download', _dp(position), _dp(velocity), _ip(image))
+
     def scale_velocities(self, factor):
         self._call('b2_scale_velocities', float(factor))
 
@@ -287,3 +296,12 @@ class Engine(object):
         ms, launches = _dbl(), _i64()
         self._call('b2_last_timing', ctypes.byref(ms), ctypes.byref(launches))
         return ms.value, launches.value
+
+    def set_profile(self, on=True):
+        self._call('b2_set_profile', int(bool(on)))
+
+    def profile(self):
+        out = numpy.zeros(8)
+        self._call('b2_profile', _dp(out))
+        return {'ms_steps': out[0], 'ms_refresh': out[1], 'step_launches': int(out[2]),
+                'steps': int(out[3]), 'refreshes': int(out[4])}

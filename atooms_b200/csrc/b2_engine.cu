@@ -48,6 +48,10 @@ struct b2_ctx {
     // host-side knowledge
     bool list_dirty = true, forces_valid = false, ev_valid = false;
     int batch = 8;
+    // profiling (b2_set_profile): events around step batches / refresh chains
+    bool profile = false;
+    std::vector<cudaEvent_t> pev;
+    double prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0, last_launches = 0, steps_total = 0;
     double last_ms = 0;
     char err[512] = "";
@@ -630,6 +634,8 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
     // opening half kick (backwards): velocities move to t - dt/2
     LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(-0.5 * dt));
     LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0);
+    for (int k = 0; k < 8; k++) c->prof[k] = 0;
+    long long rebuilds0 = c->hctl->rebuilds;
     StepArgs<R> a;
     a.ctl = c->ctl;
     a.pos[0] = (P4 *)c->pos[0];
@@ -650,15 +656,32 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
         // displacement bound trips are no-ops until the next refresh
         int64_t remaining = steps - done;
         int64_t quota = std::min<int64_t>(remaining + c->batch, 4096);
+        size_t nev = 0;
+        auto mark = [&]() {
+            if (!c->profile) return;
+            if (nev == c->pev.size()) { cudaEvent_t e; cudaEventCreate(&e); c->pev.push_back(e); }
+            cudaEventRecord(c->pev[nev++], c->stream);
+        };
         for (int64_t launched = 0; launched < quota;) {
+            mark();
             enqueue_rebuild(c);
+            mark();
             int m = (int)std::min<int64_t>(c->batch, quota - launched);
             for (int k = 0; k < m; k++) LAUNCH(k_step_nve<R>, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
             launched += m;
+            c->prof[2] += m;
         }
+        mark();
         long long rb0 = c->hctl->rebuilds;
         if ((rc = pull_ctl(c))) return rc;
         CU(cudaGetLastError());
+        for (size_t k = 0; k + 2 < nev; k += 2) {   // [k] refresh [k+1] steps [k+2]
+            float t_r = 0, t_s = 0;
+            cudaEventElapsedTime(&t_r, c->pev[k], c->pev[k + 1]);
+            cudaEventElapsedTime(&t_s, c->pev[k + 1], c->pev[k + 2]);
+            c->prof[1] += t_r;
+            c->prof[0] += t_s;
+        }
         int64_t progressed = c->hctl->steps_done - done;
         done = c->hctl->steps_done;
         if (c->hctl->overflow) {
@@ -673,6 +696,8 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
                 c->batch = (int)std::min<int64_t>(std::max<int64_t>(progressed / nrb, 1), 64);
         }
     }
+    c->prof[3] = (double)steps;
+    c->prof[4] = (double)(c->hctl->rebuilds - rebuilds0);
     // closing half kick at the final configuration
     c->list_dirty = c->hctl->halt_rebuild != 0u;
     c->forces_valid = c->ev_valid = false;
@@ -821,6 +846,7 @@ int b2_destroy(b2_ctx *c)
     if (c->hctl) cudaFreeHost(c->hctl);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    for (cudaEvent_t e : c->pev) cudaEventDestroy(e);
     if (g_const_owner[c->device] == c->const_serial) g_const_owner[c->device] = 0;
     delete c;
     return B2_OK;
@@ -1004,6 +1030,20 @@ int b2_last_timing(b2_ctx *c, double *ms, int64_t *launches)
     if (!c) return fail(nullptr, B2_EINVAL, "NULL context");
     if (ms) *ms = c->last_ms;
     if (launches) *launches = c->last_launches;
+    return B2_OK;
+}
+
+int b2_set_profile(b2_ctx *c, int on)
+{
+    if (!c) return fail(nullptr, B2_EINVAL, "NULL context");
+    c->profile = on != 0;
+    return B2_OK;
+}
+
+int b2_profile(b2_ctx *c, double out[8])
+{
+    if (!c || !out) return fail(c, B2_EINVAL, "b2_profile: NULL argument");
+    for (int k = 0; k < 8; k++) out[k] = c->prof[k];
     return B2_OK;
 }
 

@@ -1,0 +1,368 @@
+#!/usr/bin/env python
+"""
+bench.py — particle-timesteps/s of the NVE hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One bench "step" = one `run(INNER)` chunk of the backend: INNER velocity-Verlet
+timesteps of the whole system, the unit atooms' Simulation hands to a backend
+between observer calls (atooms/simulation/core.py:308-315).
+
+Workload at N = 1 (BASELINE.json configs[2]): Kob-Andersen
+80:20, N = 1 200 000 — frame 0 of the reference's data/trajectory.xyz
+(tests/golden/ka_N1200.npz) rescaled to rho = 1.2, tiled 10^3, jitter +-0.01
+(seed 2), Maxwell-Boltzmann velocities T = 0.8 (seed 3); cut & shifted at
+2.5 sigma_ab, dt = 0.002, skin 0.3.  N > 1 ranks: one such system per GPU
+(independent, no collective: "weak").
+
+value : device-resident throughput (CUDA events on the launching stream).
+e2e   : the same chunk through the C ABI with HOST buffers: positions and
+        velocities are pushed from pinned host memory before, and pulled
+        back (plus the thermodynamic scalars) after every chunk.
+roofline : the fused step kernel k_step_nve against the measured HBM peak,
+        algorithmic bytes = 7 P + 4 nbar per particle-step.
+cpu_baseline : the C/OpenMP oracle (oracle/oracle_c.c) on this box's cores, on
+        a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+INNER = 100          # MD timesteps per bench step (one backend.run(INNER) chunk)
+DT = 0.002
+SKIN = 0.3
+RHO = 1.2
+TEMPERATURE = 0.8
+KA_EPS = numpy.array([[1.0, 1.5], [1.5, 0.5]])
+KA_SIG = numpy.array([[1.0, 0.8], [0.8, 0.88]])
+# algorithmic bytes per particle-step, SURVEY.md 8(d): 7 P + 4 nbar, nbar = 93.3 (KA, rho 1.2, skin 0.3)
+NBAR = 93.3
+B_ALG = {32: 7 * 16 + 4 * NBAR, 64: 7 * 32 + 4 * NBAR}
+
+
+def ka_workload(reps=10, seed=2):
+    """SURVEY.md 8d C3.  Returns position (N,3), species, side, velocity."""
+    d = numpy.load(os.path.join(ROOT, 'tests', 'golden', 'ka_N1200.npz'))
+    n0 = len(d['species'])
+    scale = (n0 / RHO / numpy.prod(d['side'])) ** (1.0 / 3.0)
+    pos0, side0 = d['position'] * scale, d['side'] * scale
+    shifts = numpy.stack(numpy.meshgrid(*[numpy.arange(reps)] * 3, indexing='ij'), -1).reshape(-1, 3)
+    pos = (pos0[None, :, :] + shifts[:, None, :] * side0).reshape(-1, 3) - 0.5 * (reps - 1) * side0
+    rng = numpy.random.default_rng(seed)
+    pos += rng.uniform(-0.01, 0.01, size=pos.shape)
+    n = pos.shape[0]
+    # Maxwell-Boltzmann, COM removed, rescaled to exactly T with (N-1)d dof (system.py:164-198)
+    rng = numpy.random.default_rng(seed + 1)
+    vel = rng.normal(0.0, numpy.sqrt(TEMPERATURE), size=(n, 3))
+    vel -= vel.mean(axis=0)
+    vel *= numpy.sqrt(TEMPERATURE / (numpy.sum(vel * vel) / (3 * (n - 1))))
+    return pos, numpy.tile(d['species'], reps ** 3).astype(numpy.int32), side0 * reps, vel
+
+
+def make_engine(lib, precision, pos, spe, side, vel, device=0):
+    from atooms_b200 import capi
+    eng = capi.Engine(precision, device=device, library=lib)
+    eng.set_box(side)
+    eng.set_pair_table(KA_EPS, KA_SIG, 2.5 * KA_SIG, True)
+    eng.set_skin(SKIN)
+    eng.upload(pos, spe, vel)
+    return eng
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks and throttle reasons DURING the timed region."""
+    QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, device):
+        self.device = device
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix='.csv')
+            os.close(fd)
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.device), '--query-gpu=' + self.QUERY,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': []}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, reasons = [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(',')]
+                if len(f) < 9:
+                    continue
+                sm.append(float(f[1]))
+                out['sm_max_mhz'] = float(f[2])
+                for name, val in zip(names, f[5:9]):
+                    if val.lower().startswith('active'):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out['sm_mhz'] = float(numpy.median(sm))
+        out['reasons'] = sorted(reasons)
+        return out
+
+
+def measured_peak():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+        except Exception:
+            pass
+    return 6650.0, 'fallback (B200_PROFILING.md: 6.65 TB/s)'
+
+
+def oracle_library():
+    """The CPU oracle: used by the cpu_baseline leg and by --impl reference only."""
+    from atooms_b200 import capi
+    path = os.path.join(ROOT, 'oracle', '_build', 'liboracle_b2.so')
+    if not os.path.exists(path):
+        subprocess.check_call(['make', '-s', '-C', os.path.join(ROOT, 'oracle')])
+    return capi.Library(path)
+
+
+def time_oracle(pos, spe, side, vel, md_steps, repeats=1):
+    """particle-timesteps/s of the C/OpenMP oracle for `md_steps` NVE steps
+    (list build included, as in the GPU number)."""
+    lib = oracle_library()
+    eng = make_engine(lib, 64, pos, spe, side, vel)
+    eng.compute(forces=False)                  # first list build + forces: not timed (as on the GPU)
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        eng.run_nve(md_steps, DT)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    eng.close()
+    return len(spe) * md_steps / best, best
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference has no CPU engine for this path;
+    the timed stand-in is the oracle port on all host cores, same workload, bounded sample."""
+    if rank != 0:
+        return
+    cores = os.cpu_count()
+    os.environ.setdefault('OMP_NUM_THREADS', str(cores))
+    pos, spe, side, vel = ka_workload()
+    n = len(spe)
+    inner = 5                                   # MD timesteps per bench step (bounded sample)
+    lib = oracle_library()
+    eng = make_engine(lib, 64, pos, spe, side, vel)
+    eng.compute(forces=False)
+    for _ in range(args.warmup):
+        eng.run_nve(inner, DT)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.run_nve(inner, DT)
+    elapsed = time.perf_counter() - t0
+    value = n * inner * args.steps / elapsed
+    line = {
+        'impl': 'reference', 'metric': 'particle-timesteps/s', 'value': value, 'unit': 'particle-timesteps/s',
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': 1e3 * elapsed / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': workload_config(n, inner),
+        'cpu_baseline': {'value': value, 'unit': 'particle-timesteps/s', 'cores': cores, 'kind': 'port',
+                         'sample': '%d bench steps x %d NVE timesteps of the full N=%d system, '
+                                   'oracle/oracle_c.c (C + OpenMP, fp64, Verlet list)' % (args.steps, inner, n)},
+        'e2e': {'value': value, 'unit': 'particle-timesteps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n, inner):
+    return {'workload': 'Kob-Andersen 80:20 N=%d rho=1.2 NVE velocity-Verlet dt=0.002, LJ cut&shifted 2.5 sigma_ab, '
+                        'Verlet skin 0.3 (BASELINE.json configs[2], SURVEY.md 8d C3)' % n,
+            'particles_per_gpu': n, 'md_timesteps_per_step': inner,
+            'cache': 'inputs larger than L2 (neighbour list ~0.8 GB per GPU vs 126 MB L2)'}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--precision', type=int, default=32, choices=[32, 64])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
+
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+
+    if args.impl == 'reference':
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from atooms_b200 import capi
+
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device; the product has no CPU path '
+                         '(use --impl reference for the CPU stand-in)')
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    lib = capi.load()
+    pos, spe, side, vel = ka_workload(seed=2 + 10 * rank)
+    n = len(spe)
+    stream = torch.cuda.Stream()
+    results = {}
+    clocks = None
+    for precision in ([args.precision] + [p for p in (32, 64) if p != args.precision]):
+        eng = make_engine(lib, precision, pos, spe, side, vel, device=local_rank)
+        eng.set_stream(stream.cuda_stream)
+        eng.compute(forces=False)
+        primary = precision == args.precision
+        eng.set_profile(True)
+        # ---- device-resident ------------------------------------------------
+        for _ in range(args.warmup):
+            eng.run_nve(INNER, DT)
+        l0 = eng.stats()['launches']
+        prof = {'ms_steps': 0.0, 'ms_refresh': 0.0, 'step_launches': 0, 'steps': 0, 'refreshes': 0}
+        sampler = ClockSampler(local_rank) if (primary and rank == 0) else None
+        barrier()
+        if sampler:
+            sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            ev0.record(stream)
+            for _ in range(args.steps):
+                eng.run_nve(INNER, DT)
+                p = eng.profile()
+                for k in prof:
+                    prof[k] += p[k]
+            ev1.record(stream)
+        barrier()
+        ms = max_over_ranks(ev0.elapsed_time(ev1))
+        if sampler:
+            clocks = sampler.stop()
+        launches = eng.stats()['launches'] - l0
+        value = world * n * INNER * args.steps / (ms * 1e-3)
+        # ---- end to end through the C ABI with host buffers --------------------
+        hpos = torch.empty((n, 3), dtype=torch.float64, pin_memory=True).numpy()
+        hvel = torch.empty((n, 3), dtype=torch.float64, pin_memory=True).numpy()
+        p0, v0, _ = eng.download()
+        hpos[:], hvel[:] = p0, v0
+        e2e_steps = max(2, args.steps // 2)
+        out_pos = torch.empty((n, 3), dtype=torch.float64, pin_memory=True).numpy()
+        out_vel = torch.empty((n, 3), dtype=torch.float64, pin_memory=True).numpy()
+
+        def e2e_step():
+            eng.update(hpos, hvel)                            # host -> device: 2 x 3N x 8 bytes
+            eng.run_nve(INNER, DT)
+            eng.download_into(out_pos, out_vel)               # device -> host
+            th = eng.thermo()                                 # + the scalars an observer reads
+            hpos[:], hvel[:] = out_pos, out_vel
+            return th
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            th = e2e_step()
+        barrier()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        e2e_value = world * n * INNER * e2e_steps / e2e_s
+        st = eng.stats()
+        results[precision] = dict(value=value, ms=ms, launches=launches, prof=prof, e2e=e2e_value,
+                                  e2e_steps=e2e_steps, stats=st,
+                                  energy=(th['kinetic'] + th['potential']) / n)
+        eng.close()
+
+    if rank == 0:
+        r = results[args.precision]
+        peak, peak_src = measured_peak()
+        step_launches = max(r['prof']['step_launches'], 1)
+        # average duration of one k_step_nve launch that did work (no-op launches of a
+        # speculative batch are inside the bracket, so this is an upper bound)
+        kernel_ms = r['prof']['ms_steps'] / max(r['prof']['steps'], 1)
+        achieved = B_ALG[args.precision] * n / (kernel_ms * 1e-3) / 1e9
+        line = {
+            'metric': 'particle-timesteps/s', 'value': r['value'], 'unit': 'particle-timesteps/s',
+            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+            'ms_per_step': r['ms'] / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32' if args.precision == 32 else 'f64', 'data': 'synthetic',
+            'config': workload_config(n, INNER),
+            'e2e': {'value': r['e2e'], 'unit': 'particle-timesteps/s',
+                    'h2d_bytes_per_step': 2 * 3 * n * 8, 'd2h_bytes_per_step': 2 * 3 * n * 8 + 16 * 8,
+                    'steps': r['e2e_steps']},
+            'gpu_launches': int(r['launches']),
+            'clocks': clocks,
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                         'frac': achieved / peak, 'traffic': None, 'kernel': 'k_step_nve',
+                         'kernel_ms': kernel_ms, 'bytes_per_particle_step': B_ALG[args.precision],
+                         'peak_source': peak_src,
+                         'step_kernel_share': r['prof']['ms_steps'] / r['ms'],
+                         'refresh_share': r['prof']['ms_refresh'] / r['ms']},
+            'detail': {('fp%d' % p): {'value': results[p]['value'], 'e2e': results[p]['e2e'],
+                                      'ms_per_md_step': results[p]['ms'] / (args.steps * INNER),
+                                      'step_kernel_ms': results[p]['prof']['ms_steps'] / max(results[p]['prof']['steps'], 1),
+                                      'refresh_ms_each': results[p]['prof']['ms_refresh'] / max(results[p]['prof']['refreshes'], 1),
+                                      'refreshes': results[p]['prof']['refreshes'],
+                                      'noop_step_launches': results[p]['prof']['step_launches'] - results[p]['prof']['steps'],
+                                      'max_neighbors': results[p]['stats']['max_neighbors'],
+                                      'total_energy_per_particle': results[p]['energy']}
+                       for p in results},
+        }
+        if not args.no_cpu_baseline:
+            cores = os.cpu_count()
+            os.environ.setdefault('OMP_NUM_THREADS', str(cores))
+            md = 10
+            cpu_value, cpu_s = time_oracle(pos, spe, side, vel, md)
+            line['cpu_baseline'] = {'value': cpu_value, 'unit': 'particle-timesteps/s', 'cores': cores, 'kind': 'port',
+                                    'sample': '%d NVE timesteps of the full N=%d system (%.1f s), oracle/oracle_c.c '
+                                              '(C + OpenMP, fp64, Verlet list)' % (md, n, cpu_s)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -207,6 +207,15 @@ int b2_stats(b2_ctx *ctx, int64_t out[B2_S_LEN]);
  * count of the last b2_run_nve / b2_minimize / b2_compute call.             */
 int b2_last_timing(b2_ctx *ctx, double *ms, int64_t *launches);
 
+/* Measurement aid (nothing like it in the reference, whose only timer is the
+ * wall-clock TSP of simulation/core.py:286-306): with profiling on,
+ * b2_run_nve brackets the step kernels and the list-refresh pipeline with
+ * CUDA events on the context's stream.  b2_profile returns, for the last
+ * b2_run_nve: out[0] ms in step kernels, out[1] ms in list refreshes,
+ * out[2] step-kernel launches, out[3] steps done, out[4] refreshes done.   */
+int b2_set_profile(b2_ctx *ctx, int on);
+int b2_profile(b2_ctx *ctx, double out[8]);
+
 #ifdef __cplusplus
 }
 #endif

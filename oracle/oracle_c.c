@@ -722,3 +722,13 @@ int b2_last_timing(b2_ctx *c, double *ms, int64_t *launches)
     if (launches) *launches = 0;
     return B2_OK;
 }
+
+int b2_set_profile(b2_ctx *c, int on) { (void)c; (void)on; return B2_OK; }
+
+int b2_profile(b2_ctx *c, double out[8])
+{
+    if (!c || !out) return fail(c, B2_EINVAL, "b2_profile: NULL argument");
+    for (int k = 0; k < 8; k++) out[k] = 0.0;
+    out[0] = c->last_ms;
+    return B2_OK;
+}
