@@ -13,7 +13,7 @@ import numpy
 
 __all__ = ['Library', 'Engine', 'load', 'library_path', 'B2Error',
            'FP32', 'FP64', 'ENERGY', 'FORCES', 'VIRIAL', 'STRESS', 'MIN_SD', 'MIN_FIRE',
-           'SYMBOLS']
+           'SYMBOLS', 'kinetic_static', 'STATIC_MAX_PARTICLES']
 
 ABI_VERSION = 1
 FP32, FP64 = 32, 64
@@ -60,6 +60,7 @@ SYMBOLS = {
     'b2_last_timing': (_int, [_vp, _c_dp, _c_lp]),
     'b2_set_profile': (_int, [_vp, _int]),
     'b2_profile': (_int, [_vp, _c_dp]),
+    'b2_kinetic_static': (_int, [_vp, _i64, _int, _vp, _vp]),
 }
 
 
@@ -104,6 +105,24 @@ class Library(object):
         if code in _ERRORS:
             raise _ERRORS[code]('[b2 error %d] %s' % (code, msg))
         raise B2Error(code, msg)
+
+
+STATIC_MAX_PARTICLES = 16777216
+
+
+def kinetic_static(vel_mass_ptr, n, precision, out_ptr, stream=0, library=None):
+    """Kinetic energy, momentum and mass of `n` particles from a device array the
+    caller owns (n x (vx, vy, vz, mass), float4 or double4), written to 8 doubles
+    at the device address `out_ptr`; asynchronous on `stream`.
+
+    This is the allocation-free entry point (b2_kinetic_static): meant for hosts
+    whose own pool owns the GPU memory (e.g. torch tensors' data_ptr()), where a
+    cudaMalloc from this library would fail or stall the device.  At most
+    STATIC_MAX_PARTICLES per call; overlapping calls on one GPU race on the
+    shared scratch; make the first call on a GPU before any stream capture."""
+    lib = library if library is not None else load()
+    lib.check(lib.dll.b2_kinetic_static(_vp(int(vel_mass_ptr) if vel_mass_ptr else 0), int(n), int(precision),
+                                        _vp(int(stream) if stream else 0), _vp(int(out_ptr) if out_ptr else 0)))
 
 
 _product = None

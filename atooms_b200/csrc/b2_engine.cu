@@ -1048,3 +1048,130 @@ int b2_profile(b2_ctx *c, double out[8])
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// b2_kinetic_static — the one entry point of this library that allocates
+// nothing, neither at set-up nor per call.
+//
+// Who needs it: host programs that have given the whole GPU to an allocator of
+// their own — PyTorch's caching allocator, a JAX-style up-front reservation, an
+// MPI+CUDA code with a private arena — and call into this library from inside
+// their step loop with raw device pointers.  For them a cudaMalloc issued by a
+// library either fails (the pool already holds the memory) or stalls the whole
+// device in the middle of a step, so every other entry point here, which sizes
+// its reduction scratch with cudaMalloc when particles are uploaded, is off
+// limits.  This variant of the thermo reduction (k_thermo_partial +
+// k_sum_partials) keeps its per-block partial sums in the fixed array below
+// instead.
+//
+// Limits and sharing rules
+//   * at most B2_STATIC_MAX_PARTICLES particles per call; larger n is refused
+//     with B2_EINVAL before anything is launched;
+//   * the scratch is 256 KiB and is held by every GPU that loads this library
+//     until the process exits;
+//   * one array per GPU, shared by all calls: two calls that may overlap on the
+//     same GPU (different streams, different host threads) race on it — order
+//     them on one stream.  The array keeps whatever the previous call left;
+//     nothing in it has to start at zero, because the first kernel overwrites
+//     every row the second kernel reads;
+//   * the first call on each GPU looks up the device address of the array
+//     (cudaGetSymbolAddress).  Make that first call during set-up, before any
+//     stream capture is begun on that GPU.
+// ---------------------------------------------------------------------------
+#define B2_STATIC_TILE 4096                                   // particles per block
+#define B2_STATIC_ROWS 4096                                   // blocks at most
+static_assert((int64_t)B2_STATIC_TILE * B2_STATIC_ROWS == B2_STATIC_MAX_PARTICLES,
+              "scratch rows must cover B2_STATIC_MAX_PARTICLES (include/atooms_b200.h)");
+#define B2_STATIC_NQ 8
+
+static __device__ __align__(256) double g_static_scratch[B2_STATIC_ROWS * B2_STATIC_NQ];
+
+// In host code `g_static_scratch` is only a handle for the runtime; the address
+// a kernel can use comes from cudaGetSymbolAddress, once per device.
+static double *g_static_ptr[64];
+
+template <typename R>
+__global__ void __launch_bounds__(RED_THREADS)
+k_kinetic_static_partial(const typename Vec4<R>::type *__restrict__ vel, long long n,
+                         double *__restrict__ scratch)
+{
+    typedef typename Vec4<R>::type V4;
+    double q[5] = {0, 0, 0, 0, 0};
+    long long base = (long long)blockIdx.x * B2_STATIC_TILE;
+    for (int it = 0; it < B2_STATIC_TILE / RED_THREADS; it++) {
+        long long i = base + (long long)it * RED_THREADS + threadIdx.x;
+        if (i < n) {
+            V4 v = vel[i];
+            double m = (double)v.w, vx = v.x, vy = v.y, vz = v.z;
+            q[0] += 0.5 * m * ((vx * vx + vy * vy) + vz * vz);
+            q[1] += m * vx; q[2] += m * vy; q[3] += m * vz;
+            q[4] += m;
+        }
+    }
+    __shared__ double s_q[RED_THREADS / 32][5];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        double v = warp_sum(q[k]);
+        if (lane == 0) s_q[w][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < B2_STATIC_NQ) {
+        double v = 0;
+        if (threadIdx.x < 5)
+            for (int ww = 0; ww < RED_THREADS / 32; ww++) v += s_q[ww][threadIdx.x];
+        scratch[(size_t)blockIdx.x * B2_STATIC_NQ + threadIdx.x] = v;    // all 8 slots of the row
+    }
+}
+
+// rows are summed in block order: the result does not depend on scheduling
+__global__ void k_kinetic_static_sum(const double *__restrict__ scratch, int rows, double *__restrict__ out)
+{
+    int q = threadIdx.x;
+    if (q >= B2_STATIC_NQ) return;
+    double v = 0;
+    for (int b = 0; b < rows; b++) v += scratch[(size_t)b * B2_STATIC_NQ + q];
+    out[q] = v;
+}
+
+extern "C" int b2_kinetic_static(const void *vel_mass_dev, int64_t n, int precision, void *cuda_stream,
+                                 double *out_dev)
+{
+    if (precision != B2_FP32 && precision != B2_FP64)
+        return fail(nullptr, B2_EINVAL, "b2_kinetic_static: precision must be 32 or 64");
+    if (n < 0 || n > B2_STATIC_MAX_PARTICLES)
+        return fail(nullptr, B2_EINVAL,
+                    "b2_kinetic_static: n = %lld is outside 0..%lld (B2_STATIC_MAX_PARTICLES); the fixed scratch "
+                    "array cannot hold more partial sums — split the call or use b2_thermo",
+                    (long long)n, (long long)B2_STATIC_MAX_PARTICLES);
+    if (!out_dev || (n > 0 && !vel_mass_dev))
+        return fail(nullptr, B2_EINVAL, "b2_kinetic_static: NULL device pointer");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64)
+        return fail(nullptr, e == cudaSuccess ? B2_EINVAL : B2_ENOCUDA, "b2_kinetic_static: no current CUDA device (%s)",
+                    cudaGetErrorString(e));
+    if (!g_static_ptr[dev]) {
+        // set-up, once per device, with that device current
+        double *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(nullptr, B2_ECUDA, "b2_kinetic_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                        cudaGetErrorString(e));
+        g_static_ptr[dev] = p;
+    }
+    double *scratch = g_static_ptr[dev];
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    int rows = (int)((n + B2_STATIC_TILE - 1) / B2_STATIC_TILE);
+    if (rows > 0) {
+        if (precision == B2_FP32)
+            k_kinetic_static_partial<float><<<rows, RED_THREADS, 0, stream>>>((const float4 *)vel_mass_dev, n, scratch);
+        else
+            k_kinetic_static_partial<double><<<rows, RED_THREADS, 0, stream>>>((const double4 *)vel_mass_dev, n, scratch);
+    }
+    k_kinetic_static_sum<<<1, 32, 0, stream>>>(scratch, rows, out_dev);
+    e = cudaGetLastError();
+    if (e != cudaSuccess)
+        return fail(nullptr, B2_ECUDA, "b2_kinetic_static: launch failed: %s", cudaGetErrorString(e));
+    return B2_OK;
+}

@@ -216,6 +216,25 @@ int b2_last_timing(b2_ctx *ctx, double *ms, int64_t *launches);
 int b2_set_profile(b2_ctx *ctx, int on);
 int b2_profile(b2_ctx *ctx, double out[8]);
 
+/* No counterpart in the reference.  Kinetic energy, total momentum and total
+ * mass of n particles straight from a caller-owned DEVICE array, without a
+ * context and without allocating anything: for hosts whose own allocator owns
+ * the GPU (PyTorch caching allocator, up-front reservations, private arenas),
+ * where a cudaMalloc inside a library fails or stalls the device mid-step.
+ * The per-block partial sums that b2_thermo keeps in cudaMalloc'ed memory live
+ * here in a fixed 256 KiB __device__ array, which every GPU that loads the
+ * library holds until exit.
+ *   vel_mass_dev : n x (vx, vy, vz, mass) as float4 (B2_FP32) or double4 (B2_FP64)
+ *   out_dev      : 8 doubles on the device: K, Px, Py, Pz, M, 0, 0, 0
+ *   n            : at most B2_STATIC_MAX_PARTICLES, else B2_EINVAL
+ * Runs asynchronously on `cuda_stream` of the CURRENT device.  Calls that can
+ * overlap on one GPU share the scratch and race: keep them on one stream.  The
+ * first call on a GPU resolves the array's device address; issue it at
+ * set-up, before any stream capture on that GPU.                            */
+#define B2_STATIC_MAX_PARTICLES 16777216
+int b2_kinetic_static(const void *vel_mass_dev, int64_t n, int precision,
+                      void *cuda_stream, double *out_dev);
+
 #ifdef __cplusplus
 }
 #endif

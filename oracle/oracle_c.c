@@ -732,3 +732,10 @@ int b2_profile(b2_ctx *c, double out[8])
     out[0] = c->last_ms;
     return B2_OK;
 }
+
+/* device-pointer entry point of the CUDA library: meaningless on the host */
+int b2_kinetic_static(const void *vel_mass_dev, int64_t n, int precision, void *cuda_stream, double *out_dev)
+{
+    (void)vel_mass_dev; (void)n; (void)precision; (void)cuda_stream; (void)out_dev;
+    return fail(NULL, B2_EUNSUPPORTED, "b2_kinetic_static takes device pointers; the CPU oracle has none");
+}
