@@ -1,0 +1,172 @@
+"""
+`B200` and `EnergyMinimization` — simulation backends in the sense of
+atooms/backends/__init__.py:7-11: duck-typed objects with `.system` and
+`.run(steps)`, consumed unchanged by `atooms.simulation.Simulation`
+(atooms/simulation/core.py:65-130, :308-315) and
+`atooms.optimization.Optimization` (atooms/optimization/core.py:39-74).
+
+The optional members `Simulation` probes with hasattr are all provided:
+`trajectory_class` (core.py:89-92), `write_checkpoint` / `read_checkpoint`
+(:225-227, :263-265), `rmsd` (:276-280), `version` (:443-444), `timestep`
+(observers.py:198-199), `__str__` (core.py:126).
+"""
+import os
+
+import numpy
+
+from . import __version__, capi, models
+from .interaction import Interaction
+from .system import Cell, System
+from .trajectory import Trajectory
+
+__all__ = ['B200', 'EnergyMinimization']
+
+_PRECISION = {'fp32': 32, 'f32': 32, 'float32': 32, 'single': 32, 32: 32,
+              'fp64': 64, 'f64': 64, 'float64': 64, 'double': 64, 64: 64}
+
+
+def _last_frame(inp):
+    """A System, a Trajectory (last frame) or a path, as LAMMPS.__init__ accepts
+    (atooms/backends/lammps.py:151-188)."""
+    if isinstance(inp, System) or (hasattr(inp, 'particle') and hasattr(inp, 'cell')):
+        return inp
+    if hasattr(inp, '__getitem__') and hasattr(inp, 'steps'):
+        return inp[-1]
+    if isinstance(inp, str) and os.path.exists(inp):
+        try:
+            from atooms import trajectory
+        except ImportError:
+            raise ValueError('reading %s needs the atooms trajectory readers' % inp)
+        if not hasattr(numpy, 'set_string_function'):      # numpy >= 2: close() of the xyz reader
+            numpy.set_string_function = lambda *a, **k: None   # (atooms/trajectory/xyz.py:472-474)
+        with trajectory.Trajectory(inp) as th:
+            return th[-1]
+    raise ValueError('could not initialize system from {}'.format(inp))
+
+
+class B200(object):
+
+    """NVE molecular dynamics (velocity-Verlet, the LAMMPS backend's default
+    `fix nve`, atooms/backends/lammps.py:236-238) on one B200."""
+
+    version = __version__
+
+    def __init__(self, inp, model='lennard_jones', dt=0.002, skin=0.3, precision='fp64', device=0,
+                 library=None):
+        self.model = models.get(model)
+        self.timestep = float(dt)
+        self.skin = float(skin)
+        self.precision = _PRECISION[precision]
+        self.device = device
+        self._library = library
+        self.trajectory_class = Trajectory
+        self.verbose = False
+        self.steps = 0
+        self._system = None
+        self.system = _last_frame(inp)
+
+    def __str__(self):
+        return 'B200 (atooms_b200 %s, fp%d, %s)' % (__version__, self.precision, self.model)
+
+    # `Simulation` reads and assigns backend.system (simulation/core.py:111-123,
+    # tests/test_simulation.py:179-187; tests/test_rumd.py:178-194 assigns a deepcopy)
+    @property
+    def system(self):
+        return self._system
+
+    @system.setter
+    def system(self, value):
+        if not isinstance(value, System):
+            value = System.from_atooms(value, model=self.model, precision=self.precision, skin=self.skin,
+                                       device=self.device, library=self._library)
+        if value.interaction is None:
+            value.interaction = Interaction(self.model, precision=self.precision, skin=self.skin,
+                                            device=self.device, library=self._library)
+        self._system = value
+        value._push()
+        value._engine.mark_reference()       # rmsd origin (rumd.py:117-121)
+
+    @property
+    def rmsd(self):
+        """Root mean square displacement since the system was attached, from the
+        unfolded coordinates (rumd.py:163-177)."""
+        s = self._system
+        return float((s._get_thermo()['msd_sum'] / max(len(s), 1)) ** 0.5)
+
+    def run(self, steps):
+        s = self._system
+        s._push()
+        s._engine.run_nve(int(steps), self.timestep)
+        if steps > 0:
+            s._advanced()
+        self.steps += int(steps)
+
+    # binary checkpoints: the reference's fallback goes through TrajectoryXYZ and
+    # breaks under numpy >= 2 (simulation/core.py:225-234)
+    def write_checkpoint(self, output_path):
+        s = self._system
+        s._pull()
+        numpy.savez(output_path + '.chk.npz', position=s._pos, velocity=s._vel, image=s._img, ids=s._ids,
+                    names=numpy.array(s._names), mass=s._mass, radius=s._radius, side=s.cell.side,
+                    center=s.cell.center, steps=self.steps)
+
+    def read_checkpoint(self, output_path):
+        path = output_path + '.chk.npz'
+        if not os.path.exists(path):
+            return
+        d = numpy.load(path)
+        s = self._system
+        if len(d['ids']) != len(s):
+            raise ValueError('checkpoint %s holds %d particles, the system %d' % (path, len(d['ids']), len(s)))
+        s._pull()
+        s._pos[:], s._vel[:] = d['position'], d['velocity']
+        s._host_pos_dirty = s._host_vel_dirty = True
+        s._thermo = None
+        self.steps = int(d['steps'])
+
+
+class EnergyMinimization(B200):
+
+    """Energy minimisation backend with the surface of the LAMMPS one
+    (atooms/backends/lammps.py:291-363): `method`, `ftol`, `steps`,
+    `reached_steps`; driven by `Optimization` (optimization/core.py:69-74).
+
+    `ftol` follows LAMMPS `minimize 0.0 ftol ...`: stop when the 2-norm of the
+    global force vector drops below it, i.e. sum F^2 / N < ftol^2 / N.
+    `tolerance`, if given, is instead the bound on sum F^2 / N used by
+    `Optimization._target_force_norm_square` (optimization/core.py:34-36).
+    """
+
+    def __init__(self, inp, model='lennard_jones', method='fire', ftol=1e-4, steps=100000, dt=None,
+                 tolerance=None, skin=0.3, precision='fp64', device=0, library=None):
+        method = method.lower()
+        if method not in ('fire', 'sd'):
+            raise ValueError("method must be 'fire' or 'sd', not %r" % method)
+        B200.__init__(self, inp, model=model, dt=dt if dt is not None else (0.002 if method == 'fire' else 0.001),
+                      skin=skin, precision=precision, device=device, library=library)
+        self.method = method
+        self.ftol = ftol
+        self.tolerance = tolerance
+        self.steps = steps
+        self.max_evaluations = 100000
+        # "Optimization backends must set a boolean reached_steps attribute. It is True at
+        # the beginning." (lammps.py:307-309); read at step 0 by optimization/core.py:30-32
+        self.reached_steps = True
+        self.iterations = 0
+
+    def __str__(self):
+        return 'B200 energy minimization (%s)' % self.method
+
+    def run(self, steps=None):
+        if steps is not None:
+            self.steps = steps
+        s = self._system
+        s._push()
+        n = max(len(s), 1)
+        fn2_tol = self.tolerance if self.tolerance is not None else self.ftol ** 2 / n
+        done, converged = s._engine.minimize(capi.MIN_FIRE if self.method == 'fire' else capi.MIN_SD,
+                                             int(min(100000000, self.steps)), self.timestep, fn2_tol)
+        self.iterations += done
+        # True when the iteration budget stopped us, False when the tolerance did (lammps.py:350-354)
+        self.reached_steps = not converged
+        s._advanced()

@@ -203,6 +203,7 @@ struct Ctl {
     // minimiser
     double dt_now, dt_max, alpha, fn2_tol, fn2, step_len;
     int npos, min_mode;
+    int has_prev, pad1_;         // SD: the previous gradient is available (survives a resumed call)
     long long iter;
     double red[32];              // reduction results
 };

@@ -30,6 +30,9 @@ struct b2_ctx {
     int64_t n = 0;
     void *pos[2] = {nullptr, nullptr}, *vel = nullptr, *frc = nullptr, *vir = nullptr;
     void *tpos = nullptr, *tvel = nullptr;
+    void *mvel = nullptr;      // parked minimiser velocities, by original id
+    bool min_resume = false;
+    int min_method = -1;
     int *orig = nullptr, *torig = nullptr;
     int *img = nullptr;        // [3n] by original id
     double *ref = nullptr;     // [3n] by original id, unfolded, relative to centre
@@ -441,7 +444,8 @@ __global__ void k_export_list(int n, const int *__restrict__ nbr, const int *__r
     for (int k = 0; k < cnt; k++) onbr[(size_t)o * stride + k] = orig[row[(size_t)k * 32]];
 }
 
-__global__ void k_ctl_begin(Ctl *ctl, long long target, int min_mode, double dt, double dt_max, double tol)
+__global__ void k_ctl_begin(Ctl *ctl, long long target, int min_mode, double dt, double dt_max, double tol,
+                            int resume)
 {
     ctl->steps_done = 0;
     ctl->steps_target = target;
@@ -451,12 +455,33 @@ __global__ void k_ctl_begin(Ctl *ctl, long long target, int min_mode, double dt,
     ctl->vmax2_bits = 0u;
     ctl->iter = 0;
     ctl->min_mode = min_mode;
-    ctl->dt_now = dt;
-    ctl->dt_max = dt_max;
-    ctl->alpha = 0.1;
-    ctl->npos = 0;
     ctl->fn2_tol = tol;
     ctl->step_len = 0.0;
+    if (!resume) {               // a resumed minimisation keeps dt, alpha, npos of the previous call
+        ctl->dt_now = dt;
+        ctl->dt_max = dt_max;
+        ctl->alpha = 0.1;
+        ctl->npos = 0;
+        ctl->has_prev = 0;
+    }
+}
+
+// minimiser velocities (FIRE) / previous gradient (SD) parked between two
+// consecutive b2_minimize calls, by ORIGINAL id so that a re-sort in between is harmless
+template <typename R>
+__global__ void k_park_minvel(int n, int save, typename Vec4<R>::type *__restrict__ vel,
+                              typename Vec4<R>::type *__restrict__ parked, const int *__restrict__ orig)
+{
+    typedef typename Vec4<R>::type V4;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    int o = orig[s];
+    if (save) {
+        parked[o] = vel[s];
+    } else {
+        V4 p = parked[o], v = vel[s];
+        vel[s] = make4(p.x, p.y, p.z, v.w);
+    }
 }
 
 // ---------------------------------------------------------------------------
@@ -473,6 +498,8 @@ int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     c->n = n;
     c->list_dirty = true;
     c->forces_valid = c->ev_valid = false;
+    c->min_resume = false;
+    if (c->mvel) { cudaFree(c->mvel); c->mvel = nullptr; }
     memset(c->hctl, 0, sizeof(Ctl));
     c->hctl->halt_rebuild = 1u;
     c->hctl->half_skin = 0.5 * c->skin;
@@ -497,6 +524,7 @@ int Impl<R>::update(b2_ctx *c, const double *pos, const double *vel)
 {
     int64_t n = c->n;
     if (n == 0 || (!pos && !vel)) return B2_OK;
+    c->min_resume = false;
     double *spos = c->stage, *svel = c->stage + 3 * n;
     if (pos) CU(cudaMemcpyAsync(spos, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     if (vel) CU(cudaMemcpyAsync(svel, vel, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
@@ -633,7 +661,8 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
     if ((rc = ensure_forces(c))) return rc;
     // opening half kick (backwards): velocities move to t - dt/2
     LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(-0.5 * dt));
-    LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0);
+    LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0, 0);
+    c->min_resume = false;
     for (int k = 0; k < 8; k++) c->prof[k] = 0;
     long long rebuilds0 = c->hctl->rebuilds;
     StepArgs<R> a;
@@ -717,9 +746,15 @@ int Impl<R>::minimize(b2_ctx *c, int method, int64_t max_steps, double dt, doubl
     if (c->n == 0) { *converged = 1; return B2_OK; }
     int n = (int)c->n;
     if ((rc = ensure_list(c))) return rc;
-    LAUNCH(k_scale_vel<R>, cdiv(n, 256), 256, (V4 *)c->vel, n, (R)0);
+    const bool resume = c->min_resume && c->min_method == method && c->mvel;
+    if (resume) {
+        auto park = k_park_minvel<R>;
+        LAUNCH(park, cdiv(n, 256), 256, n, 0, (V4 *)c->vel, (V4 *)c->mvel, c->orig);
+    } else {
+        LAUNCH(k_scale_vel<R>, cdiv(n, 256), 256, (V4 *)c->vel, n, (R)0);
+    }
     LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)max_steps, method == B2_MIN_FIRE ? MIN_MODE_FIRE : MIN_MODE_SD,
-           dt, 10.0 * dt, tol);
+           dt, 10.0 * dt, tol, resume ? 1 : 0);
     // k_ctl_begin marks a zero budget as done; the first iteration must still test convergence
     MinArgs<R> a;
     a.ctl = c->ctl;
@@ -763,6 +798,16 @@ int Impl<R>::minimize(b2_ctx *c, int method, int64_t max_steps, double dt, doubl
     *steps_done = c->hctl->iter;
     *converged = (int)c->hctl->converged;
     c->steps_total += c->hctl->iter;
+    // an unfinished minimisation can be continued by the next call (Optimization drives the
+    // backend in chunks, optimization/core.py:56): park the minimiser's velocities
+    c->min_resume = false;
+    if (!c->hctl->converged) {
+        if (!c->mvel && (rc = dev_alloc(c, (V4 **)&c->mvel, n))) return rc;
+        auto park = k_park_minvel<R>;
+        LAUNCH(park, cdiv(n, 256), 256, n, 1, (V4 *)c->vel, (V4 *)c->mvel, c->orig);
+        c->min_resume = true;
+        c->min_method = method;
+    }
     // forces / energies of the final configuration are the ones just computed
     LAUNCH(k_scale_vel<R>, cdiv(n, 256), 256, (V4 *)c->vel, n, (R)0);
     c->list_dirty = c->hctl->halt_rebuild != 0u;
@@ -839,7 +884,7 @@ int b2_destroy(b2_ctx *c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig,
-                    c->img, c->ref, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
+                    c->img, c->ref, c->mvel, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -956,6 +1001,7 @@ int b2_scale_velocities(b2_ctx *c, double factor)
 {
     NEED_PARTICLES("b2_scale_velocities");
     if (c->n == 0) return B2_OK;
+    c->min_resume = false;
     if (c->precision == B2_FP32)
         LAUNCH(k_scale_vel<float>, cdiv(c->n, 256), 256, (float4 *)c->vel, (int)c->n, (float)factor);
     else

@@ -391,7 +391,8 @@ __global__ void k_min_logic(Ctl *ctl, const double *__restrict__ partial, int nb
         }
         ctl->step_len = ctl->dt_now;
     } else {
-        if (ctl->iter > 0) ctl->dt_now *= (P > 0.0) ? 1.1 : 0.5;
+        if (ctl->has_prev) ctl->dt_now *= (P > 0.0) ? 1.1 : 0.5;
+        ctl->has_prev = 1;
         ctl->step_len = fmin(ctl->dt_now, 0.1 / sqrt(fmax2));
         ctl->red[2] = sqrt(fmax2);
     }

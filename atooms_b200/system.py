@@ -1,0 +1,477 @@
+"""
+Array-backed `System` for the B200 backend.
+
+atooms' `System` is a list of `Particle` objects, each owning 3-element numpy
+arrays (atooms/system/system.py:38-41, particle.py:15-30); at N >= 1e5 every
+accessor costs seconds and `System(N=10**6)` raises.  Like the
+RUMD backend's wrapper (atooms/backends/rumd.py:225-357) this class keeps the
+state in flat arrays — here mirrored on the GPU — and materialises
+`system.particle` lazily, only when somebody asks for the list.
+
+Synchronisation contract
+  * the device is authoritative after `backend.run()`; host arrays are
+    refreshed lazily, in place, on access (`b2_download`).
+  * observers' accessors (temperature, kinetic / potential energy, virial,
+    force norm, pressure, len(system.particle)) are device reductions
+    (`b2_thermo`) or O(1): no N-sized copy, no Python loop.
+  * once a MUTABLE handle on the host arrays has been handed out —
+    `view()` / `dump(view=True)`, `system.position`, an element of
+    `system.particle` — in-place edits cannot be detected
+    (docs/simulations.org:302-308 relies on them), so from then on the host
+    arrays are pushed (`b2_update`) before every device operation and pulled
+    right after every run; the handles stay valid because downloads write
+    into the same arrays.  `release_views()` ends that mode.
+"""
+import copy
+
+import numpy
+
+from . import capi, models
+
+__all__ = ['System', 'Cell', 'Particle', 'Thermostat']
+
+
+class Cell(object):
+
+    """Orthorhombic periodic cell (atooms/system/cell.py:11-39)."""
+
+    def __init__(self, side, center=None):
+        self.side = numpy.asarray(side, dtype=numpy.float64)
+        self.center = numpy.zeros_like(self.side) if center is None else numpy.asarray(center, dtype=numpy.float64)
+        self.shape = 'cubic'
+        self.periodic = numpy.ones(self.side.size, dtype=bool)
+
+    @property
+    def volume(self):
+        return float(numpy.prod(self.side))
+
+
+class Particle(object):
+
+    """Minimal stand-in for atooms.system.particle.Particle (particle.py:15-30),
+    used for the lazily materialised `system.particle` when atooms itself is not
+    importable.  Attributes are views on the system's host arrays."""
+
+    def __init__(self, position, velocity, species, mass=1.0, radius=0.5):
+        self.position = position
+        self.velocity = velocity
+        self.species = species
+        self.mass = mass
+        self.radius = radius
+
+    @property
+    def kinetic_energy(self):
+        return 0.5 * self.mass * numpy.dot(self.velocity, self.velocity)
+
+    def fold(self, cell):
+        # atooms/system/particle.py:90-99
+        p = self.position - cell.center
+        self.position[:] = p - numpy.rint(p / cell.side) * cell.side + cell.center
+        return self
+
+    def __repr__(self):
+        return 'Particle(species={0.species}, mass={0.mass}, position={0.position}, ' \
+               'velocity={0.velocity}, radius={0.radius})'.format(self)
+
+
+class Thermostat(object):
+    """Place-holder (atooms/backends/dryrun.py:99-104): NVE only, kept so that
+    `system.thermostat` exists; `pressure` uses the kinetic temperature."""
+
+    def __init__(self, temperature=None):
+        self.temperature = temperature
+
+
+class _ParticleList(object):
+
+    """`system.particle`: a sequence that builds Particle objects on demand.
+    `len()` is free (Simulation.wall_time calls it, simulation/core.py:296-297);
+    indexing or iterating creates Particle objects whose position / velocity are
+    views on the system's host arrays and switches the system to the
+    "views handed out" mode (see the module docstring)."""
+
+    def __init__(self, system):
+        self._system = system
+        self._cache = {}
+
+    def __len__(self):
+        return len(self._system)
+
+    def _make(self, i):
+        s = self._system
+        p = self._cache.get(i)
+        if p is None:
+            p = _particle_class()(position=s._pos[i], velocity=s._vel[i], species=s._names[s._ids[i]],
+                                  mass=s._mass[i], radius=s._radius[i])
+            # numpy.asarray keeps the row views (particle.py:24-30)
+            p.periodic_image = s._img[i]
+            self._cache[i] = p
+        return p
+
+    def __getitem__(self, i):
+        self._system._hand_out()
+        if isinstance(i, slice):
+            return [self._make(k) for k in range(*i.indices(len(self)))]
+        n = len(self)
+        if i < 0:
+            i += n
+        if not 0 <= i < n:
+            raise IndexError('particle index out of range')
+        return self._make(i)
+
+    def __iter__(self):
+        self._system._hand_out()
+        return (self._make(i) for i in range(len(self)))
+
+
+def _particle_class():
+    try:
+        from atooms.system.particle import Particle as P   # the real one when atooms is installed
+        return P
+    except Exception:
+        return Particle
+
+
+class System(object):
+
+    def __init__(self, position, species, cell, velocity=None, mass=None, radius=None,
+                 model='lennard_jones', precision=64, skin=0.3, device=0, library=None):
+        position = numpy.array(position, dtype=numpy.float64)
+        if position.ndim != 2 or position.shape[1] != 3:
+            raise ValueError('position must be (N, 3); only three dimensions are supported')
+        n = position.shape[0]
+        self._pos = numpy.ascontiguousarray(position)
+        self._vel = numpy.zeros((n, 3)) if velocity is None else numpy.array(velocity, dtype=numpy.float64)
+        self._mass = numpy.ones(n) if mass is None else numpy.array(mass, dtype=numpy.float64)
+        self._radius = numpy.full(n, 0.5) if radius is None else numpy.array(radius, dtype=numpy.float64)
+        self._img = numpy.zeros((n, 3), dtype=numpy.int32)
+        self.cell = cell if hasattr(cell, 'side') else Cell(cell)
+        self.model = models.get(model)
+        # species names -> 0-based ids in table order
+        names = [str(s) for s in species]
+        order = self.model.species if self.model.species is not None else sorted(set(names))
+        if len(order) > self.model.nsp:
+            raise ValueError('system has %d species but the model %s has %d'
+                             % (len(order), self.model, self.model.nsp))
+        lookup = {s: i for i, s in enumerate(order)}
+        try:
+            self._ids = numpy.array([lookup[s] for s in names], dtype=numpy.int32)
+        except KeyError as err:
+            raise ValueError('species %s not in the model species %s' % (err, order))
+        self._names = list(order)
+        self.thermostat = None
+        self.barostat = None
+        self.reservoir = None
+        self.interaction = None      # set by the backend (atooms_b200.interaction.Interaction)
+        self.precision = int(precision)
+        self._skin_value = float(skin)
+        self._engine = capi.Engine(self.precision, device=device, library=library)
+        self._engine.set_box(self.cell.side, self.cell.center)
+        self._engine.set_pair_table(self.model.eps, self.model.sigma, self.model.rcut, self.model.shifted)
+        self._engine.set_skin(skin)
+        self._engine.upload(self._pos, self._ids, self._vel, self._mass)
+        self._host_pos_dirty = False     # host positions changed since the last push
+        self._host_vel_dirty = False
+        self._device_newer = False       # device moved on since the last pull
+        self._views_out = False          # a mutable handle on the host arrays is in user hands
+        self._particle = _ParticleList(self)
+        self._thermo = None              # cached b2_thermo of the current state
+
+    # -- construction from / conversion to reference objects ------------------
+    @classmethod
+    def from_atooms(cls, system, **kwargs):
+        """Build from an `atooms.system.System` (or anything with .particle / .cell)."""
+        if isinstance(system, cls):
+            return system
+        particle = system.particle
+        if system.cell is None:
+            raise ValueError('the B200 backend needs a periodic cell')
+        return cls(position=[p.position for p in particle],
+                   species=[p.species for p in particle],
+                   cell=Cell(system.cell.side, getattr(system.cell, 'center', None)),
+                   velocity=[p.velocity for p in particle],
+                   mass=[p.mass for p in particle],
+                   radius=[getattr(p, 'radius', 0.5) for p in particle], **kwargs)
+
+    # -- synchronisation ---------------------------------------------------------
+    def _push(self):
+        """Host -> device, if the host side was (or may have been) touched."""
+        if self._views_out:
+            self._pull()
+            self._host_pos_dirty = self._host_vel_dirty = True
+        if self._host_pos_dirty or self._host_vel_dirty:
+            self._engine.update(self._pos if self._host_pos_dirty else None,
+                                self._vel if self._host_vel_dirty else None)
+            self._host_pos_dirty = self._host_vel_dirty = False
+            self._thermo = None
+            if self.interaction is not None:
+                self.interaction._invalidate()
+
+    def _pull(self):
+        """Device -> host (in place), if the device moved on."""
+        if self._device_newer:
+            self._engine.download_into(self._pos, self._vel, self._img)
+            self._device_newer = False
+
+    def _hand_out(self):
+        """A mutable handle on the host arrays is about to leave our hands."""
+        self._pull()
+        self._views_out = True
+
+    def release_views(self):
+        """Promise that host arrays handed out earlier are no longer edited:
+        back to lazy synchronisation."""
+        self._push()
+        self._views_out = False
+
+    def _advanced(self):
+        """Called by the backend after the device state changed."""
+        self._device_newer = True
+        self._thermo = None
+        if self.interaction is not None:
+            self.interaction._invalidate()
+        if self._views_out:
+            self._pull()
+
+    def _get_thermo(self):
+        self._push()
+        if self._thermo is None:
+            self._thermo = self._engine.thermo()
+        return self._thermo
+
+    # -- array accessors -----------------------------------------------------------
+    @property
+    def position(self):
+        """(N, 3) host array, mutable: editing it in place edits the system."""
+        self._hand_out()
+        return self._pos
+
+    @property
+    def velocity(self):
+        self._hand_out()
+        return self._vel
+
+    @property
+    def image(self):
+        self._pull()
+        return self._img
+
+    @property
+    def species(self):
+        return numpy.array(self._names)[self._ids]
+
+    @property
+    def mass(self):
+        return self._mass.copy()
+
+    def __len__(self):
+        return len(self._ids)
+
+    # -- the reference's System interface (atooms/system/system.py) ----------------
+    @property
+    def particle(self):
+        """Lazily materialised particle sequence (cf. rumd.py:326-352, which rebuilds
+        the whole list on each access)."""
+        return self._particle
+
+    @property
+    def number_of_dimensions(self):
+        return 3
+
+    @property
+    def distinct_species(self):
+        return sorted(set(self._names[i] for i in numpy.unique(self._ids)))
+
+    @property
+    def composition(self):
+        ids, counts = numpy.unique(self._ids, return_counts=True)
+        return {self._names[i]: int(c) for i, c in zip(ids, counts)}
+
+    @property
+    def concentration(self):
+        n = float(len(self))
+        return {k: v / n for k, v in self.composition.items()}
+
+    @property
+    def density(self):
+        return len(self) / self.cell.volume if len(self) else 0.0
+
+    def kinetic_energy(self, per_particle=False, normed=False):
+        # system.py:232-243
+        ekin = self._get_thermo()['kinetic'] if len(self) else 0.0
+        return ekin / len(self) if (per_particle or normed) else ekin
+
+    @property
+    def temperature(self):
+        # system.py:164-179: (N-1) d degrees of freedom
+        n = len(self)
+        if n > 1:
+            return 2.0 / ((n - 1) * 3) * self.kinetic_energy()
+        if n == 1:
+            return 2.0 / 3 * self.kinetic_energy()
+        return 0.0
+
+    @temperature.setter
+    def temperature(self, T):
+        self.set_temperature(T)
+
+    def set_temperature(self, temperature, seed=None):
+        """Maxwell-Boltzmann velocities, centre of mass removed, rescaled to exactly
+        `temperature` (system.py:185-198); numpy's generator replaces random.gauss."""
+        rng = numpy.random.default_rng(seed)
+        n = len(self)
+        self._push()
+        self._pull()
+        self._vel[:] = rng.normal(0.0, 1.0, size=(n, 3)) * numpy.sqrt(temperature / self._mass)[:, None]
+        self._vel -= (self._mass[:, None] * self._vel).sum(axis=0) / self._mass.sum()
+        self._host_vel_dirty = True
+        self._thermo = None
+        t_old = self.temperature
+        if t_old > 0.0:
+            self.scale_velocities((temperature / t_old) ** 0.5)
+
+    def scale_velocities(self, factor):
+        # system.py:227-230, on the device
+        self._push()
+        self._engine.scale_velocities(factor)
+        self._advanced()
+
+    def cm_velocity(self):
+        t = self._get_thermo()
+        return t['momentum'] / t['mass']
+
+    def fix_momentum(self):
+        vcm = self.cm_velocity()
+        self._pull()
+        self._vel -= vcm
+        self._host_vel_dirty = True
+        self._thermo = None
+
+    def fold(self):
+        """Positions on the device are always folded; expose them folded (system.py:376-379)."""
+        self._pull()
+        return self
+
+    def compute_interaction(self, what=None):
+        # system.py:245-259 — but the state is already resident: no marshalling
+        if self.interaction is not None:
+            self.interaction.compute_resident(what, self)
+
+    def potential_energy(self, per_particle=False, normed=False, cache=False):
+        if self.interaction is None:
+            return 0.0
+        if not cache or self.interaction.energy is None:
+            self.compute_interaction('energy')
+        e = self.interaction.energy
+        return e / len(self) if (per_particle or normed) else e
+
+    def total_energy(self, per_particle=False, normed=None, cache=False):
+        if normed is not None:
+            per_particle = normed
+        return self.potential_energy(per_particle, cache=cache) + self.kinetic_energy(per_particle)
+
+    def force_norm_square(self, per_particle=True, cache=False):
+        # system.py:305-319; the sum is reduced on the device
+        if self.interaction is None:
+            return 0.0
+        f2 = self._get_thermo()['fnorm2']
+        return f2 / len(self) if per_particle else f2
+
+    def force_norm(self, per_particle=True, cache=False):
+        if self.interaction is None:
+            return 0.0
+        f = self._get_thermo()['fnorm2'] ** 0.5
+        return f / len(self) if per_particle else f
+
+    def virial(self, per_particle=True, cache=False):
+        if self.interaction is None:
+            return 0.0
+        w = self._get_thermo()['virial']
+        return w / len(self) if per_particle else w
+
+    @property
+    def pressure(self):
+        # system.py:337-348
+        T = self.thermostat.temperature if (self.thermostat and self.thermostat.temperature is not None) \
+            else self.temperature
+        return (len(self) * T + self._get_thermo()['virial'] / 3) / self.cell.volume
+
+    def dump(self, what=None, order='C', dtype=None, view=False, clear=False, flat=False):
+        """Array marshalling compatible with system.py:398-530 for the attributes
+        the path uses.  `view=True` hands out the host array itself."""
+        if what is None:
+            return None
+        aliases = {'box': 'cell.side', 'pos': 'particle.position', 'vel': 'particle.velocity',
+                   'spe': 'particle.species', 'rad': 'particle.radius',
+                   'position': 'particle.position', 'velocity': 'particle.velocity',
+                   'species': 'particle.species', 'mass': 'particle.mass', 'radius': 'particle.radius'}
+        what = aliases.get(what, what)
+        if what == 'cell.side':
+            data = self.cell.side
+        elif what == 'cell.center':
+            data = self.cell.center
+        elif what == 'particle.position':
+            data = self.position if view else self._synced('_pos')
+        elif what == 'particle.velocity':
+            data = self.velocity if view else self._synced('_vel')
+        elif what == 'particle.species':
+            data = self.species
+        elif what == 'particle.mass':
+            data = self._mass
+        elif what == 'particle.radius':
+            data = self._radius
+        else:
+            raise ValueError('Unknown attribute %s' % what)
+        if not view:
+            data = numpy.array(data, dtype=dtype)
+        elif dtype is not None and numpy.dtype(dtype) != data.dtype:
+            data = data.astype(dtype)
+        if data.ndim == 2 and order == 'F':
+            data = data.T          # (3, N) Fortran-ordered view of the same memory
+        if flat:
+            data = data.flatten(order=order)
+        return data
+
+    def view(self, what=None, order='C', dtype=None, clear=False, flat=False):
+        return self.dump(what, order=order, dtype=dtype, view=True, clear=clear, flat=flat)
+
+    def _synced(self, name):
+        self._pull()
+        return getattr(self, name)
+
+    def update(self, other, full=False, exclude=None, only=None):
+        """Take the state of `other` (same particles), as `System.update` does (system.py:72-101)."""
+        other = System.from_atooms(other, model=self.model, precision=self.precision) \
+            if not isinstance(other, System) else other
+        other._pull()
+        self._pull()
+        self._pos[:], self._vel[:] = other._pos, other._vel
+        self._host_pos_dirty = self._host_vel_dirty = True
+        self._thermo = None
+
+    def __deepcopy__(self, memo):
+        """An independent system with its own device context (tests/test_rumd.py:178-194)."""
+        self._pull()
+        new = System(self._pos, [self._names[i] for i in self._ids], Cell(self.cell.side.copy(), self.cell.center.copy()),
+                     velocity=self._vel, mass=self._mass, radius=self._radius, model=self.model,
+                     precision=self.precision, skin=self._skin(), device=self._engine.device,
+                     library=self._engine.lib)
+        new.thermostat = copy.deepcopy(self.thermostat, memo)
+        if self.interaction is not None:
+            new.interaction = self.interaction.__class__(self.model)
+        return new
+
+    def _skin(self):
+        return getattr(self, '_skin_value', 0.3)
+
+    def __str__(self):
+        # array-based: Simulation._report prints str(system) at start (simulation/core.py:348-351)
+        txt = 'system composed by N={} particles\n'.format(len(self))
+        txt += 'with chemical composition C={}\n'.format(self.composition)
+        txt += 'with chemical concentration x={}\n'.format(self.concentration)
+        txt += 'enclosed in a cubic box at number density rho={:.6f}\n'.format(self.density)
+        txt += 'interacting via {} on the B200 engine (fp{})'.format(self.model, self.precision)
+        return txt
+
+    def close(self):
+        self._engine.close()

@@ -195,7 +195,12 @@ int b2_run_nve(b2_ctx *ctx, int64_t steps, double dt);
  * iterations; stop early when sum F^2 / N < fn2_tol
  * (optimization/core.py:34-36).  *converged = 1 if the tolerance was met
  * (=> backend.reached_steps = False, lammps.py:350-354).  Velocities are
- * zero on return.  `dt` is the initial FIRE time step / SD step length.     */
+ * zero on return.  `dt` is the initial FIRE time step / SD step length.
+ * A call that stopped on its budget can be continued: if nothing touched the
+ * state in between, the next b2_minimize with the same method resumes with the
+ * minimiser's internal velocities, step and mixing state (the reference's
+ * Optimization drives backends in chunks, optimization/core.py:56, :69-74), so
+ * the result does not depend on the chunking.                                */
 int b2_minimize(b2_ctx *ctx, int method, int64_t max_steps, double dt,
                 double fn2_tol, int64_t *steps_done, int *converged);
 

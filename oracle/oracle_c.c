@@ -58,6 +58,10 @@ struct b2_ctx {
     double energy, virial, stress[9];
     int64_t steps_total, rebuilds;
     double last_ms;
+    /* resumable minimiser state (see b2_minimize in the header) */
+    double *mvel;
+    int min_resume, min_method, m_npos, m_has_prev;
+    double m_dt, m_alpha, m_dt0;
     char err[512];
 };
 
@@ -91,7 +95,8 @@ static void free_particles(b2_ctx *c)
 {
     free(c->pos); free(c->vel); free(c->mass); free(c->frc); free(c->pe); free(c->vir);
     free(c->ref); free(c->spe); free(c->img); free(c->img_ref);
-    free(c->row); free(c->nbr);
+    free(c->row); free(c->nbr); free(c->mvel);
+    c->mvel = NULL; c->min_resume = 0;
     c->pos = c->vel = c->mass = c->frc = c->pe = c->vir = c->ref = NULL;
     c->spe = c->img = c->img_ref = NULL;
     c->row = NULL; c->nbr = NULL; c->nbr_cap = 0;
@@ -228,6 +233,7 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
 int b2_update(b2_ctx *c, const double *pos, const double *vel)
 {
     if (!c || !c->pos) return fail(c, B2_ESTATE, "b2_update: no particles resident");
+    c->min_resume = 0;
     if (pos) {
         for (int64_t i = 0; i < c->n; i++) {
             for (int d = 0; d < 3; d++) c->pos[3 * i + d] = pos[3 * i + d];
@@ -252,6 +258,7 @@ int b2_download(b2_ctx *c, double *pos, double *vel, int32_t *image)
 int b2_scale_velocities(b2_ctx *c, double factor)
 {
     if (!c || !c->pos) return fail(c, B2_ESTATE, "b2_scale_velocities: no particles resident");
+    c->min_resume = 0;
     for (int64_t i = 0; i < 3 * c->n; i++) c->vel[i] *= factor;
     return B2_OK;
 }
@@ -557,6 +564,7 @@ int b2_run_nve(b2_ctx *c, int64_t steps, double dt)
     if (rc) return rc;
     if (steps < 0 || !(dt > 0.0)) return fail(c, B2_EINVAL, "b2_run_nve: steps >= 0 and dt > 0 required");
     if (steps == 0) return B2_OK;
+    c->min_resume = 0;
     double t0 = now_ms();
     int64_t n = c->n;
     if ((rc = ensure_forces(c)) != B2_OK) return rc;
@@ -597,16 +605,36 @@ static double sum_f2(const b2_ctx *c, const double *f)
     return s;
 }
 
+static void park(b2_ctx *c, int method, int converged)
+{
+    size_t n3 = (size_t)c->n * 3;
+    c->min_resume = 0;
+    if (!converged) {
+        if (!c->mvel) c->mvel = (double *)malloc((n3 ? n3 : 1) * sizeof(double));
+        memcpy(c->mvel, c->vel, n3 * sizeof(double));
+        c->min_resume = 1;
+        c->min_method = method;
+    }
+    memset(c->vel, 0, n3 * sizeof(double));
+}
+
 static int minimize_fire(b2_ctx *c, int64_t max_steps, double dt, double tol,
                          int64_t *steps_done, int *converged)
 {
     /* Bitzek et al. 2006 defaults; see oracle_np.fire for the iteration */
     const int n_min = 5;
-    const double f_inc = 1.1, f_dec = 0.5, alpha0 = 0.1, f_alpha = 0.99, dt_max = 10.0 * dt;
+    const double f_inc = 1.1, f_dec = 0.5, alpha0 = 0.1, f_alpha = 0.99;
     int64_t n = c->n, it = 0;
     int rc, npos = 0;
-    double dt_now = dt, alpha = alpha0;
-    memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
+    double dt_now = dt, alpha = alpha0, dt_max = 10.0 * dt;
+    if (c->min_resume && c->min_method == B2_MIN_FIRE) {
+        memcpy(c->vel, c->mvel, (size_t)n * 3 * sizeof(double));
+        dt_now = c->m_dt; alpha = c->m_alpha; npos = c->m_npos;
+    } else {
+        memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
+        c->m_dt = dt;   /* dt_max refers to the dt of the fresh start */
+    }
+    dt_max = 10.0 * (c->min_resume && c->min_method == B2_MIN_FIRE ? c->m_dt0 : dt);
     *converged = 0;
     for (;;) {
         if ((rc = ensure_forces(c)) != B2_OK) return rc;
@@ -639,7 +667,9 @@ static int minimize_fire(b2_ctx *c, int64_t max_steps, double dt, double tol,
         c->forces_valid = 0;
         it++;
     }
-    memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
+    if (!(c->min_resume && c->min_method == B2_MIN_FIRE)) c->m_dt0 = dt;
+    c->m_dt = dt_now; c->m_alpha = alpha; c->m_npos = npos;
+    park(c, B2_MIN_FIRE, *converged);
     *steps_done = it;
     return B2_OK;
 }
@@ -650,9 +680,14 @@ static int minimize_sd(b2_ctx *c, int64_t max_steps, double step, double tol,
     /* see oracle_np.steepest_descent: the previous force is kept in c->vel */
     const double max_disp = 0.1;
     int64_t n = c->n, it = 0;
-    int rc;
+    int rc, has_prev = 0;
     double h_now = step;
-    memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
+    if (c->min_resume && c->min_method == B2_MIN_SD) {
+        memcpy(c->vel, c->mvel, (size_t)n * 3 * sizeof(double));
+        h_now = c->m_dt; has_prev = c->m_has_prev;
+    } else {
+        memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
+    }
     *converged = 0;
     for (;;) {
         if ((rc = ensure_forces(c)) != B2_OK) return rc;
@@ -666,7 +701,8 @@ static int minimize_sd(b2_ctx *c, int64_t max_steps, double step, double tol,
             double f2 = (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
             if (f2 > fmax2) fmax2 = f2;
         }
-        if (it > 0) h_now *= (dot > 0.0) ? 1.1 : 0.5;
+        if (has_prev) h_now *= (dot > 0.0) ? 1.1 : 0.5;
+        has_prev = 1;
         double h = fmin(h_now, max_disp / sqrt(fmax2));
         for (int64_t i = 0; i < n; i++) {
             for (int d = 0; d < 3; d++) {
@@ -679,7 +715,8 @@ static int minimize_sd(b2_ctx *c, int64_t max_steps, double step, double tol,
         c->forces_valid = 0;
         it++;
     }
-    memset(c->vel, 0, (size_t)n * 3 * sizeof(double));
+    c->m_dt = h_now; c->m_has_prev = has_prev;
+    park(c, B2_MIN_SD, *converged);
     *steps_done = it;
     return B2_OK;
 }

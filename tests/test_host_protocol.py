@@ -1,0 +1,269 @@
+"""
+Host-side logic of the drop-in (Interaction / System / B200 / EnergyMinimization /
+Trajectory) on CPU.  The numerical engine behind the C ABI is the CPU oracle here
+(injected with `library=`; the product default is the CUDA library), so what is
+tested is the Python layer: protocol, synchronisation contract, checkpointing and,
+when /root/reference is present, the reference's OWN drivers
+(atooms.simulation.Simulation, atooms.optimization.Optimization) running our
+backend unchanged.  GPU runs of the same classes are in test_gpu_backend.py.
+"""
+import copy
+import os
+import sys
+
+import numpy
+import pytest
+
+from conftest import golden
+import atooms_b200
+from atooms_b200 import B200, EnergyMinimization, Interaction, System, Cell, Trajectory
+
+REF = '/root/reference'
+HAVE_REF = os.path.isdir(os.path.join(REF, 'atooms'))
+if HAVE_REF:
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+    if not hasattr(numpy, 'set_string_function'):     # numpy >= 2 shim for the reference's xyz reader
+        numpy.set_string_function = lambda *a, **k: None
+needs_ref = pytest.mark.skipif(not HAVE_REF, reason='reference tree not present (GPU box)')
+
+
+def make_system(name, lib, model, precision=64, velocities=True):
+    d = golden(name)
+    names = d['species_names'][d['species']]
+    return System(d['position'], names, Cell(d['side'], d['center']),
+                  velocity=d['velocity'] if velocities else None, mass=d['mass'],
+                  model=model, precision=precision, library=lib)
+
+
+def test_backend_surface(oracle_lib):
+    """Members Simulation probes (atooms/backends/dryrun.py:13-40; simulation/core.py:89,225,263,277,443)."""
+    bck = B200(make_system('lj_N1000', oracle_lib, 'lennard_jones'), 'lennard_jones', dt=0.005, library=oracle_lib)
+    for name in ('system', 'run', 'rmsd', 'timestep', 'version', 'trajectory_class',
+                 'write_checkpoint', 'read_checkpoint'):
+        assert hasattr(bck, name)
+    assert 'B200' in str(bck)
+    assert bck.rmsd == 0.0
+    s = bck.system
+    assert len(s.particle) == 1000 and s.number_of_dimensions == 3
+    assert s.distinct_species == ['A'] and s.composition == {'A': 1000}
+    assert abs(s.density - 1.0) < 1e-12
+    assert 'N=1000' in str(s)
+
+
+def test_nve_pin_through_the_backend(oracle_lib, pins):
+    """tests/test_lammps.py:20-40 with B200 in place of LAMMPS (unshifted LJ 2.5, dt 0.005)."""
+    pin = pins['lj_N1000_nve_x0']
+    model = atooms_b200.lennard_jones(2.5, shifted=False)
+    bck = B200(make_system('lj_N1000', oracle_lib, model), model, dt=pin['dt'], library=oracle_lib)
+    assert round(abs(bck.system.particle[0].position[0] - pin['value'][0]), 5) == 0
+    for target in pin['value'][1:]:
+        bck.run(10)
+        assert round(abs(bck.system.particle[0].position[0] - target), 5) == 0
+    x1 = bck.system.particle[3].position[0]
+    bck.run(0)                                   # tests/test_lammps.py:123-142
+    assert abs(bck.system.particle[3].position[0] - x1) < 1e-12
+    assert bck.rmsd > 0.0
+
+
+def test_observers_accessors(oracle_lib, pins):
+    """What write_thermo reads (simulation/observers.py:247-256) + the energy pins."""
+    model = atooms_b200.lennard_jones(2.5, shifted=False)
+    s = B200(make_system('lj_fcc_N108', oracle_lib, model, velocities=False), model, library=oracle_lib).system
+    assert round(abs(s.potential_energy(per_particle=True) - pins['lj_fcc_N108_unshifted_U_per_particle']['value']), 7) == 0
+    assert round(abs(s.pressure - pins['lj_fcc_N108_unshifted_pressure']['value']), 7) == 0   # T = 0
+    assert round(abs(s.force_norm(per_particle=True) - 4.2e-11), 2) == 0
+    assert s.temperature == 0.0 and s.kinetic_energy() == 0.0
+    assert s.total_energy(per_particle=True, cache=True) == s.potential_energy(per_particle=True)
+    s = B200(make_system('lj_N3_inline', oracle_lib, 'lennard_jones'), 'lennard_jones', library=oracle_lib).system
+    assert round(abs(s.potential_energy() - pins['lj_N3_shifted_U']['value']), 4) == 0
+    assert round(abs(s.temperature - 1.0), 7) == 0        # tests/test_backends.py:91-99
+    ka3 = atooms_b200.PairModel(numpy.ones((2, 2)), numpy.ones((2, 2)), 2.5 * numpy.ones((2, 2)))
+    s = B200(make_system('lj_N4_inline', oracle_lib, ka3), ka3, library=oracle_lib).system
+    assert round(abs(s.temperature - 10.0 / 9.0), 7) == 0  # mass-aware, tests/test_backends.py:101-105
+
+
+def test_sync_contract(oracle_lib):
+    """Host views handed out are pushed before the next run; the device is pulled lazily."""
+    bck = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib)
+    s = bck.system
+    e0 = s.potential_energy()
+    pos = s.view('position')                      # docs/simulations.org:302-308: modify views in place
+    assert pos.shape == (256, 3) and s.dump('position', order='F', view=True).shape == (3, 256)
+    pos[0, 0] += 0.05
+    assert abs(s.potential_energy() - e0) > 1e-6
+    pos[0, 0] -= 0.05
+    assert abs(s.potential_energy() - e0) < 1e-9
+    s.particle[1].position[1] += 0.05             # through the materialised Particle list
+    assert abs(s.potential_energy() - e0) > 1e-6
+    s.particle[1].position[1] -= 0.05
+    bck.run(5)
+    assert not numpy.allclose(s.dump('position'), golden('ka_N256_rumd')['position'])
+    # velocities: set_temperature hits the target exactly, scale_velocities runs on the device
+    s.set_temperature(1.5, seed=1)
+    assert abs(s.temperature - 1.5) < 1e-10
+    assert numpy.abs(s.cm_velocity()).max() < 1e-12
+    s.scale_velocities(2.0)
+    assert abs(s.temperature - 6.0) < 1e-9
+    assert abs(numpy.sum(s.dump('velocity') ** 2) / (3 * 255) - 6.0) < 1e-9
+
+
+def test_deepcopy_and_reassign(oracle_lib):
+    """tests/test_rumd.py:178-194."""
+    bck = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib)
+    pos0 = bck.system.particle[0].position[0]
+    s = copy.deepcopy(bck.system)
+    assert round(abs(bck.system.potential_energy(per_particle=True) - (-6.4014371344819665)), 3) == 0
+    bck.run(100)
+    pos1 = bck.system.particle[0].position[0]
+    bck.system = s
+    assert bck.system is s
+    bck.run(100)
+    pos2 = bck.system.particle[0].position[0]
+    assert abs(pos1 - pos0) > 1e-2
+    assert abs(pos1 - pos2) < 1e-4
+
+
+def test_checkpoint_roundtrip(oracle_lib, tmp_path):
+    bck = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib)
+    bck.run(10)
+    path = str(tmp_path / 'run')
+    bck.write_checkpoint(path)
+    ref = bck.system.dump('position').copy()
+    bck.run(10)
+    after = bck.system.dump('position').copy()
+    bck.read_checkpoint(path)
+    assert numpy.array_equal(bck.system.dump('position'), ref)
+    assert bck.steps == 10
+    bck.run(10)
+    assert numpy.abs(bck.system.dump('position') - after).max() < 1e-9
+
+
+def test_minimisation_backend(oracle_lib, pins):
+    """tests/test_optimization.py:20-35 without the driver: reached_steps semantics."""
+    pin = pins['lj_N256_minimised']
+    bck = EnergyMinimization(make_system('lj_N256', oracle_lib, 'lennard_jones', velocities=False),
+                             'lennard_jones', method='fire', ftol=1e-4, library=oracle_lib)
+    assert bck.reached_steps is True              # lammps.py:307-309
+    bck.run(50)
+    assert bck.reached_steps is True and bck.iterations == 50     # stopped by the budget
+    bck.run(100000)
+    assert bck.reached_steps is False             # stopped by the tolerance
+    assert bck.system.potential_energy(per_particle=True) < pin['U_per_particle_below']
+    assert bck.system.force_norm_square(per_particle=True) < pin['fn2_per_particle_below']
+    with pytest.raises(ValueError):
+        EnergyMinimization(bck.system, 'lennard_jones', method='cg', library=oracle_lib)
+
+
+def test_generic_interaction_protocol(oracle_lib):
+    """Interaction.compute(observable, **variables) with host arrays (interaction.py:57-82)."""
+    d = golden('ka_N256_rumd')
+
+    class P(object):
+        def __init__(self, species, mass):
+            self.species, self.mass = species, mass
+    particle = [P(str(s), m) for s, m in zip(d['species'], d['mass'])]
+    position = numpy.asfortranarray(d['position'].T)          # (3, N) F order, as system.dump(order='F')
+    inter = Interaction('kob_andersen', library=oracle_lib)
+    assert inter.variables == {'position': 'particle.position', 'particle': 'particle', 'cell': 'cell'}
+    assert inter.order == 'F' and inter.energy is None and inter.forces is None
+    inter.compute('energy', position, particle, Cell(d['side']))
+    assert round(abs(inter.energy / 256 - (-6.4014371344819665)), 3) == 0 and inter.forces is None
+    inter.compute('forces', position, particle, Cell(d['side']))
+    assert inter.forces.shape == (3, 256) and inter.forces.flags.f_contiguous
+    fref = numpy.c_[d['fx'], d['fy'], d['fz']]
+    assert numpy.abs(inter.forces.T - fref).max() / numpy.abs(fref).max() < 1e-5
+    inter.compute('stress', position, particle, Cell(d['side']))
+    assert inter.stress.shape == (3, 3) and abs(numpy.trace(inter.stress) - inter.virial) < 1e-8
+    with pytest.raises(AssertionError):
+        inter.compute('bogus', position, particle, Cell(d['side']))
+    with pytest.raises(NotImplementedError):
+        inter.compute('hessian', position, particle, Cell(d['side']))
+    total = inter + inter                                      # interaction.py:37-55
+    assert abs(total.energy - 2 * inter.energy) < 1e-9
+
+
+def test_trajectory_writer(oracle_lib, tmp_path):
+    s = make_system('ka_N256_rumd', oracle_lib, 'kob_andersen')
+    path = str(tmp_path / 'out.xyz')
+    with Trajectory(path, 'w') as th:
+        th.timestep = 0.002
+        th.precision = 9
+        th.variables = ['species', 'position', 'velocity']
+        th.write(s, 0)
+        th.write(s, 10)
+    lines = open(path).read().splitlines()
+    assert lines[0] == '256' and lines[1].startswith('step:0 columns:species,position,velocity dt:0.002 cell:6.0,6.0,6.0')
+    assert len(lines) == 2 * 258
+    if HAVE_REF:
+        from atooms.trajectory import TrajectoryXYZ
+        th = TrajectoryXYZ(path)
+        assert th.steps == [0, 10]
+        back = th[1]
+        th.close()
+        assert numpy.abs(numpy.array([p.position for p in back.particle]) - s.dump('position')).max() < 1e-8
+        assert [p.species for p in back.particle] == list(s.species)
+
+
+# ---- the reference's own drivers on top of our backend -------------------------------
+@needs_ref
+def test_reference_simulation_driver(oracle_lib, pins, tmp_path):
+    from atooms.simulation import Simulation, write_thermo, Scheduler
+    pin = pins['lj_N1000_nve_x0']
+    model = atooms_b200.lennard_jones(2.5, shifted=False)
+    bck = B200(os.path.join(REF, 'data', 'lj_N1000_rho1.0.xyz'), model, dt=pin['dt'], library=oracle_lib)
+    out = str(tmp_path / 'sim')
+    sim = Simulation(bck, output_path=out, checkpoint_interval=10, enable_speedometer=False)
+    sim.add(write_thermo, Scheduler(5))
+    assert sim.system is bck.system
+    sim.run(10)
+    assert round(abs(sim.system.particle[0].position[0] - pin['value'][1]), 5) == 0
+    sim.run(10)
+    assert round(abs(sim.system.particle[0].position[0] - pin['value'][2]), 5) == 0
+    assert sim.current_step == 20
+    thermo = numpy.loadtxt(out + '.thermo')
+    assert thermo.shape[0] == 5 and list(thermo[:, 0]) == [0, 5, 10, 15, 20]
+    assert numpy.abs(thermo[:, 4] - thermo[0, 4]).max() < 2e-2          # total energy (unshifted cutoff, dt 0.005)
+    assert os.path.exists(out + '.chk.npz') and os.path.exists(out + '.chk.step')
+    # restart from the checkpoint (simulation/core.py:240-273)
+    bck2 = B200(os.path.join(REF, 'data', 'lj_N1000_rho1.0.xyz'), model, dt=pin['dt'], library=oracle_lib)
+    sim2 = Simulation(bck2, output_path=out, restart=True, enable_speedometer=False)
+    sim2.run(30)
+    assert sim2.current_step == 30
+    bck.run(10)
+    assert numpy.abs(bck2.system.dump('position') - bck.system.dump('position')).max() < 1e-9
+
+
+@needs_ref
+def test_reference_optimization_driver(oracle_lib, pins):
+    """tests/test_optimization.py:20-35 with our backend in place of LAMMPS."""
+    from atooms.optimization import Optimization
+    pin = pins['lj_N256_minimised']
+    bck = EnergyMinimization(os.path.join(REF, 'data', 'lj_N256_rho1.0.xyz'), 'lennard_jones', library=oracle_lib)
+    opt = Optimization(bck)
+    opt.tolerance = 1e-4
+    opt.run()
+    assert bck.system.potential_energy(per_particle=True) < pin['U_per_particle_below']
+    assert bck.system.force_norm_square(per_particle=True) < pin['fn2_per_particle_below']
+    assert bck.reached_steps is False
+
+
+@needs_ref
+def test_interaction_with_reference_system(oracle_lib, pins):
+    """system.interaction = Interaction(...) on a plain atooms System (system.py:245-335)."""
+    from atooms.trajectory import TrajectoryXYZ
+    th = TrajectoryXYZ(os.path.join(REF, 'data', 'lj_N1000_rho1.0.xyz'))
+    system = th[0]
+    th.close()
+    system.interaction = Interaction(atooms_b200.lennard_jones(2.5, shifted=False), library=oracle_lib)
+    assert float('%.7f' % system.potential_energy(per_particle=True)) == pins['lj_N1000_unshifted_U_per_particle']['value']
+    assert system.interaction.forces.shape == (3, 1000)
+    assert system.force_norm_square(per_particle=True) > 0
+    assert abs(system.virial(per_particle=False) - system.interaction.virial) < 1e-9
+    # the reference's composite Interaction fans out to terms and sums them (interaction.py:85-115)
+    from atooms.system.interaction import Interaction as Composite
+    both = Composite(Interaction(atooms_b200.lennard_jones(2.5, False), library=oracle_lib),
+                     Interaction(atooms_b200.lennard_jones(2.5, False), library=oracle_lib))
+    e1 = system.interaction.energy
+    system.interaction = both
+    assert abs(system.potential_energy() - 2 * e1) < 1e-8
