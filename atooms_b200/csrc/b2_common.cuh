@@ -19,8 +19,23 @@ __device__ __forceinline__ double4 make4(double x, double y, double z, double w)
 
 __device__ __forceinline__ float  r_rint(float x)  { return rintf(x); }
 __device__ __forceinline__ double r_rint(double x) { return rint(x); }
-__device__ __forceinline__ float  r_rcp(float x)   { return __frcp_rn(x); }
-__device__ __forceinline__ double r_rcp(double x)  { return 1.0 / x; }
+// reciprocal without the range-check / slow-path branch of the IEEE sequences:
+// hardware approximation refined by Newton steps (x is a squared distance:
+// finite, positive, far from the denormal range)
+__device__ __forceinline__ float r_rcp(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return fmaf(r, fmaf(-x, r, 1.0f), r);                       // < 1 ulp
+}
+__device__ __forceinline__ double r_rcp(double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));     // ~20 bits
+    r = fma(r, fma(-x, r, 1.0), r);                             // ~40 bits
+    r = fma(r, fma(-x, r, 1.0), r);                             // ~80 bits -> rounding limited
+    return fma(r, fma(-x, r, 1.0), r);
+}
 
 // round-to-nearest, never contracted into FMA: the neighbour predicate is
 // compared bit-for-bit with the CPU oracle (particle.py:129-130 arithmetic)

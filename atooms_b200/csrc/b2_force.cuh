@@ -8,18 +8,16 @@
 
 
 template <typename R> struct PairTab {       // per-block copy of the pair table
-    R c12[B2_MAXSP * B2_MAXSP], c6[B2_MAXSP * B2_MAXSP], rc2[B2_MAXSP * B2_MAXSP],
-      ush[B2_MAXSP * B2_MAXSP];
+    R c12x12[B2_MAXSP * B2_MAXSP], c6x6[B2_MAXSP * B2_MAXSP], rc2[B2_MAXSP * B2_MAXSP];
 };
 
 template <typename R>
 __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
 {
     for (int a = threadIdx.x; a < B2_MAXSP * B2_MAXSP; a += blockDim.x) {
-        t.c12[a] = (R)g_pair.c12[a];
-        t.c6[a] = (R)g_pair.c6[a];
+        t.c12x12[a] = (R)(12.0 * g_pair.c12[a]);
+        t.c6x6[a] = (R)(6.0 * g_pair.c6[a]);
         t.rc2[a] = (R)g_pair.rc2[a];
-        t.ush[a] = (R)g_pair.ushift[a];
     }
 }
 
@@ -27,7 +25,10 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
 //   r2inv = 1/r2 ; r6inv = r2inv^3
 //   u = r6inv (c12 r6inv - c6) - ushift ;  w = r6inv (12 c12 r6inv - 6 c6) = r.F
 //   F_i += (w r2inv) d ,  d = r_i - r_j  (minimum image, particle.py:129-130; see delta())
-template <typename R, bool EV, bool STRESS>
+// The force part is branch-free (pairs beyond the cut-off contribute a zero
+// through a select).  FAST2: at most two species — the particle's row of the
+// table sits in registers and is picked with selects instead of shared loads.
+template <typename R, bool EV, bool STRESS, bool FAST2>
 __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restrict__ pos,
                                          const int *__restrict__ row, int cnt,
                                          typename Pos4<R>::type pi, const Box<R> &box,
@@ -36,25 +37,34 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
 {
     typedef typename Pos4<R>::type P4;
     const int ti = ptype(pi) * nsp;
+    R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
+    if (FAST2) {
+        a12_0 = tab.c12x12[ti]; a6_0 = tab.c6x6[ti]; rc_0 = tab.rc2[ti];
+        a12_1 = tab.c12x12[ti + nsp - 1]; a6_1 = tab.c6x6[ti + nsp - 1]; rc_1 = tab.rc2[ti + nsp - 1];
+    }
     int k = 0;
 #define B2_PAIR(PJ)                                                                   \
     {                                                                                 \
         R dx, dy, dz;                                                                 \
         delta(pi, PJ, box, dx, dy, dz);                                               \
         R r2 = dx * dx + dy * dy + dz * dz;                                           \
-        int a = ti + ptype(PJ);                                                       \
-        if (r2 < tab.rc2[a]) {                                                        \
-            R r2inv = r_rcp(r2);                                                      \
-            R r6inv = r2inv * r2inv * r2inv;                                          \
-            R c12 = tab.c12[a], c6 = tab.c6[a];                                       \
-            R w = r6inv * ((R)12 * c12 * r6inv - (R)6 * c6);                          \
-            R fp = w * r2inv;                                                         \
-            fx += fp * dx; fy += fp * dy; fz += fp * dz;                              \
+        const int tj = ptype(PJ);                                                     \
+        R a12, a6, rc2;                                                               \
+        if (FAST2) {                                                                  \
+            a12 = tj ? a12_1 : a12_0; a6 = tj ? a6_1 : a6_0; rc2 = tj ? rc_1 : rc_0;  \
+        } else {                                                                      \
+            a12 = tab.c12x12[ti + tj]; a6 = tab.c6x6[ti + tj]; rc2 = tab.rc2[ti + tj]; \
         }                                                                             \
+        R r2inv = r_rcp(r2);                                                          \
+        R r6inv = r2inv * r2inv * r2inv;                                              \
+        R fp = r6inv * (a12 * r6inv - a6) * r2inv;                                    \
+        fp = r2 < rc2 ? fp : (R)0;                                                    \
+        fx += fp * dx; fy += fp * dy; fz += fp * dz;                                  \
         if (EV || STRESS) {                                                           \
             /* observables: fp64 pair arithmetic on the stored positions, in both */ \
             /* precisions (totals cancel heavily; fp32 would leave systematic    */ \
             /* errors that do not average out)                                   */ \
+            const int a = ti + tj;                                                    \
             double ex, ey, ez;                                                        \
             delta_d(pi, PJ, box, ex, ey, ez);                                         \
             double q2 = ex * ex + ey * ey + ez * ez;                                  \
@@ -120,7 +130,9 @@ k_force(ForceArgs<R> a)
         R fx = 0, fy = 0, fz = 0;
         double pe = 0, vir = 0;
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
-        pair_row<R, EV, STRESS>(pos, row, a.nnb[i], pi, a.box, tab, g_pair.nsp, fx, fy, fz, pe, vir, st);
+        const int nsp = g_pair.nsp;
+        if (nsp <= 2) pair_row<R, EV, STRESS, true>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        else pair_row<R, EV, STRESS, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
         a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
         if (EV) a.vir[i] = (R)(0.5 * vir);
     }
@@ -180,7 +192,9 @@ k_step_nve(StepArgs<R> a)
         R fx = 0, fy = 0, fz = 0;
         double pe = 0, vir = 0;
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
-        pair_row<R, false, false>(pos, row, a.nnb[i], pi, a.box, tab, g_pair.nsp, fx, fy, fz, pe, vir, nullptr);
+        const int nsp = g_pair.nsp;
+        if (nsp <= 2) pair_row<R, false, false, true>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        else pair_row<R, false, false, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
         V4 v = a.vel[i];
         R s = a.kick / v.w;
         v.x += s * fx; v.y += s * fy; v.z += s * fz;
