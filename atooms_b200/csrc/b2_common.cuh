@@ -243,7 +243,10 @@ __device__ __forceinline__ uint32_t morton3(int cx, int cy, int cz)
 struct Grid {
     int nc[3];
     int cellbits;      // Morton bits per dimension; table has 1 << (3 cellbits) entries
-    int allpairs;      // fewer than 3 cells along some axis: O(N^2) list build
+    int allpairs;      // too few cells along some axis: O(N^2) list build
+    int m;             // cells are (r_list,max / m) wide; the stencil reaches m cells (1 or 2)
+    float w[3];        // cell widths
+    float reach2;      // (r_list,max)^2, padded: cells farther than this cannot hold a neighbour
 };
 
 __device__ __forceinline__ void cell_of(const Box<float> &, const Grid &g, const int4 &p, int &cx, int &cy, int &cz)
@@ -261,6 +264,35 @@ __device__ __forceinline__ void cell_of(const Box<double> &box, const Grid &g, c
     cx = min(max(cx, 0), g.nc[0] - 1);
     cy = min(max(cy, 0), g.nc[1] - 1);
     cz = min(max(cz, 0), g.nc[2] - 1);
+}
+
+// cell coordinates plus the position inside the cell as a fraction in [0, 1]
+__device__ __forceinline__ void cell_frac(const Box<float> &box, const Grid &g, const int4 &p,
+                                          int &cx, int &cy, int &cz, float &fx, float &fy, float &fz)
+{
+    cell_of(box, g, p, cx, cy, cz);
+    const float k = 1.0f / 4294967296.0f;
+    fx = __uint2float_rn((unsigned)p.x + 0x80000000u) * k * (float)g.nc[0] - (float)cx;
+    fy = __uint2float_rn((unsigned)p.y + 0x80000000u) * k * (float)g.nc[1] - (float)cy;
+    fz = __uint2float_rn((unsigned)p.z + 0x80000000u) * k * (float)g.nc[2] - (float)cz;
+    fx = fminf(fmaxf(fx, 0.f), 1.f); fy = fminf(fmaxf(fy, 0.f), 1.f); fz = fminf(fmaxf(fz, 0.f), 1.f);
+}
+__device__ __forceinline__ void cell_frac(const Box<double> &box, const Grid &g, const double4 &p,
+                                          int &cx, int &cy, int &cz, float &fx, float &fy, float &fz)
+{
+    cell_of(box, g, p, cx, cy, cz);
+    fx = (float)((p.x * box.invL[0] + 0.5) * (double)g.nc[0] - (double)cx);
+    fy = (float)((p.y * box.invL[1] + 0.5) * (double)g.nc[1] - (double)cy);
+    fz = (float)((p.z * box.invL[2] + 0.5) * (double)g.nc[2] - (double)cz);
+    fx = fminf(fmaxf(fx, 0.f), 1.f); fy = fminf(fmaxf(fy, 0.f), 1.f); fz = fminf(fmaxf(fz, 0.f), 1.f);
+}
+
+// distance (in cell widths, never over-estimated) from a point at fraction f of
+// its cell to the cell d steps away along one axis
+__device__ __forceinline__ float cell_gap(int d, float f)
+{
+    float g = d == 0 ? 0.f : (d > 0 ? (float)(d - 1) + (1.f - f) : (float)(-d - 1) + f);
+    return fmaxf(g - 1e-3f, 0.f);
 }
 
 __device__ __forceinline__ double warp_sum(double v)

@@ -187,21 +187,31 @@ template <typename R> struct Impl {
 
     static int setup_grid(b2_ctx *c)
     {
-        // cell width >= (r_cut,max + skin)(1 + 1e-5): every listed pair sits in adjacent cells
-        double rl = (c->rcut_max + c->skin) * (1.0 + 1e-5);
+        // cells of width >= r_list,max (1 + 1e-5) / m with a stencil of m cells: every listed
+        // pair sits within the stencil.  m = 2 needs >= 5 cells per axis, m = 1 needs >= 3
+        // (distinct periodic images in the stencil); below that, all pairs.
+        const double rl = (c->rcut_max + c->skin) * (1.0 + 1e-5);
         Grid &g = c->grid;
-        g.allpairs = 0;
-        int mx = 1;
-        for (int d = 0; d < 3; d++) {
-            int nc = (int)std::floor(c->side[d] / rl);
-            if (nc < 3) g.allpairs = 1;
-            nc = std::min(std::max(nc, 1), 256);
-            g.nc[d] = nc;
-            mx = std::max(mx, nc);
+        g.allpairs = 1;
+        g.m = 0;
+        for (int m = 2; m >= 1 && g.allpairs; m--) {
+            bool ok = true;
+            for (int d = 0; d < 3; d++) {
+                int nc = std::min((int)std::floor(c->side[d] / (rl / m)), 256);
+                if (nc < 2 * m + 1) ok = false;
+                g.nc[d] = nc;
+            }
+            if (ok) { g.allpairs = 0; g.m = m; }
         }
+        int mx = 1;
+        if (g.allpairs) g.nc[0] = g.nc[1] = g.nc[2] = 1;
+        for (int d = 0; d < 3; d++) {
+            mx = std::max(mx, g.nc[d]);
+            g.w[d] = (float)(c->side[d] / g.nc[d]);
+        }
+        g.reach2 = (float)(rl * rl * (1.0 + 1e-3));
         g.cellbits = 1;
         while ((1 << g.cellbits) < mx) g.cellbits++;
-        if (g.allpairs) { g.cellbits = 1; g.nc[0] = g.nc[1] = g.nc[2] = 1; }
         int tab = 1 << (3 * g.cellbits);
         c->sort_passes = (3 * g.cellbits + 7) / 8;
         if (tab != c->ncelltab || !c->cell_start) {
@@ -243,7 +253,7 @@ template <typename R> struct Impl {
             int src = 0;
             for (int pass = 0; pass < c->sort_passes; pass++) {
                 LAUNCH(k_sort_hist, c->sort_blocks, SORT_THREADS, c->ctl, c->keys[src], n, 8 * pass, c->sort_blocks, c->hist);
-                LAUNCH(k_sort_scan, 1, 1024, c->ctl, c->hist, 256 * c->sort_blocks);
+                LAUNCH(k_sort_scan, 1, 256, c->ctl, c->hist, c->sort_blocks);
                 LAUNCH(k_sort_scatter, c->sort_blocks, SORT_THREADS, c->ctl, c->keys[src], c->vals[src],
                        c->keys[src ^ 1], c->vals[src ^ 1], n, 8 * pass, c->sort_blocks, c->hist);
                 src ^= 1;
@@ -255,7 +265,8 @@ template <typename R> struct Impl {
             LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
             LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
         }
-        LAUNCH(k_build_list<R>, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
+        auto build = c->grid.m == 2 ? k_build_list<R, 2> : (c->grid.m == 1 ? k_build_list<R, 1> : k_build_list<R, 0>);
+        LAUNCH(build, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
                c->nbr, c->nnb, c->cap);
         LAUNCH(k_rebuild_finish, 1, 1, c->ctl);
     }
