@@ -18,6 +18,7 @@ __all__ = ['Library', 'Engine', 'load', 'library_path', 'B2Error',
 ABI_VERSION = 1
 FP32, FP64 = 32, 64
 ENERGY, FORCES, VIRIAL, STRESS = 1, 2, 4, 8
+GHOST = 256
 MIN_SD, MIN_FIRE = 0, 1
 T_KINETIC, T_POTENTIAL, T_VIRIAL, T_FNORM2, T_PX, T_PY, T_PZ, T_MASS, T_MSD, T_LEN = \
     0, 1, 2, 3, 4, 5, 6, 7, 8, 16
@@ -61,6 +62,15 @@ SYMBOLS = {
     'b2_set_profile': (_int, [_vp, _int]),
     'b2_profile': (_int, [_vp, _c_dp]),
     'b2_kinetic_static': (_int, [_vp, _i64, _int, _vp, _vp]),
+    'b2_upload_device': (_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
+    'b2_download_device': (_int, [_vp, _vp, _vp, _vp]),
+    'b2_dd_begin': (_int, [_vp, _i64, _dbl, _int]),
+    'b2_dd_step': (_int, [_vp, _vp]),
+    'b2_dd_commit': (_int, [_vp, _vp]),
+    'b2_dd_poll': (_int, [_vp, _c_lp, ctypes.POINTER(_int)]),
+    'b2_dd_end': (_int, [_vp]),
+    'b2_dd_pack': (_int, [_vp, _vp, _i64, _vp]),
+    'b2_dd_unpack': (_int, [_vp, _i64, _i64, _vp]),
 }
 
 
@@ -324,3 +334,36 @@ class Engine(object):
         self._call('b2_profile', _dp(out))
         return {'ms_steps': out[0], 'ms_refresh': out[1], 'step_launches': int(out[2]),
                 'steps': int(out[3]), 'refreshes': int(out[4])}
+
+    # -- domain decomposition primitives: raw addresses in the engine's memory space ----
+    # (device pointers for the CUDA library, host pointers for the CPU oracle)
+    def upload_device(self, n, pos_ptr, species_ptr, vel_ptr=0, mass_ptr=0):
+        self._call('b2_upload_device', int(n), _vp(pos_ptr or 0), _vp(vel_ptr or 0), _vp(species_ptr or 0),
+                   _vp(mass_ptr or 0))
+        self.n = int(n)
+
+    def download_device(self, pos_ptr=0, vel_ptr=0, image_ptr=0):
+        self._call('b2_download_device', _vp(pos_ptr or 0), _vp(vel_ptr or 0), _vp(image_ptr or 0))
+
+    def dd_begin(self, steps, dt, opening_kick=True):
+        self._call('b2_dd_begin', int(steps), float(dt), int(bool(opening_kick)))
+
+    def dd_step(self, vmax_ptr):
+        self._call('b2_dd_step', _vp(vmax_ptr))
+
+    def dd_commit(self, gvmax_ptr):
+        self._call('b2_dd_commit', _vp(gvmax_ptr))
+
+    def dd_poll(self):
+        done, need = _i64(), _int()
+        self._call('b2_dd_poll', ctypes.byref(done), ctypes.byref(need))
+        return done.value, bool(need.value)
+
+    def dd_end(self):
+        self._call('b2_dd_end')
+
+    def dd_pack(self, ids_ptr, n, out_ptr):
+        self._call('b2_dd_pack', _vp(ids_ptr or 0), int(n), _vp(out_ptr or 0))
+
+    def dd_unpack(self, first_id, n, in_ptr):
+        self._call('b2_dd_unpack', int(first_id), int(n), _vp(in_ptr or 0))

@@ -94,8 +94,16 @@ template <typename R> struct Box {
     double Ld[3], sd[3];
 };
 
-__device__ __forceinline__ int ptype(const int4 &p)    { return p.w; }
-__device__ __forceinline__ int ptype(const double4 &p) { return (int)__double_as_longlong(p.w); }
+// The species lane also carries the ghost flag (B2_GHOST in the C ABI): a ghost
+// is a read-only copy of a particle owned by a neighbouring spatial domain — it
+// acts on its neighbours but is neither integrated nor counted in any total.
+#define B2_GHOST_BIT 256
+__device__ __forceinline__ int praw(const int4 &p)     { return p.w; }
+__device__ __forceinline__ int praw(const double4 &p)  { return (int)__double_as_longlong(p.w); }
+__device__ __forceinline__ int ptype(const int4 &p)    { return p.w & 0xff; }
+__device__ __forceinline__ int ptype(const double4 &p) { return (int)__double_as_longlong(p.w) & 0xff; }
+__device__ __forceinline__ bool is_ghost(const int4 &p)    { return (p.w & B2_GHOST_BIT) != 0; }
+__device__ __forceinline__ bool is_ghost(const double4 &p) { return ((int)__double_as_longlong(p.w) & B2_GHOST_BIT) != 0; }
 
 __device__ __forceinline__ int wrap_sub(int a, int b) { return (int)((unsigned)a - (unsigned)b); }
 

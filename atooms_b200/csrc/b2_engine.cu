@@ -27,13 +27,16 @@ struct b2_ctx {
     PairConst pc;
     uint64_t const_serial = 0;
     // particles (sorted order unless noted)
-    int64_t n = 0;
+    int64_t n = 0, ncap = 0;   // particles resident / allocated
+    size_t nbr_alloc = 0;
     void *pos[2] = {nullptr, nullptr}, *vel = nullptr, *frc = nullptr, *vir = nullptr;
     void *tpos = nullptr, *tvel = nullptr;
     void *mvel = nullptr;      // parked minimiser velocities, by original id
     bool min_resume = false;
     int min_method = -1;
     int *orig = nullptr, *torig = nullptr;
+    int *inv = nullptr;        // slot of each local id (inverse of orig); used by the halo pack / unpack
+    double dd_dt = 0;
     int *img = nullptr;        // [3n] by original id
     double *ref = nullptr;     // [3n] by original id, unfolded, relative to centre
     // neighbour search
@@ -160,6 +163,7 @@ template <typename R> struct Impl {
     static int alloc_particles(b2_ctx *c, int64_t n)
     {
         int rc;
+        c->ncap = n;
         for (int k = 0; k < 2; k++)
             if ((rc = dev_alloc(c, (P4 **)&c->pos[k], n))) return rc;
         if ((rc = dev_alloc(c, (V4 **)&c->vel, n))) return rc;
@@ -169,6 +173,7 @@ template <typename R> struct Impl {
         if ((rc = dev_alloc(c, (V4 **)&c->tvel, n))) return rc;
         if ((rc = dev_alloc(c, &c->orig, n))) return rc;
         if ((rc = dev_alloc(c, &c->torig, n))) return rc;
+        if ((rc = dev_alloc(c, &c->inv, n))) return rc;
         if ((rc = dev_alloc(c, &c->img, 3 * n))) return rc;
         if ((rc = dev_alloc(c, &c->ref, 3 * n))) return rc;
         for (int k = 0; k < 2; k++) {
@@ -228,10 +233,14 @@ template <typename R> struct Impl {
         int64_t n = c->n;
         want = (int)std::min<int64_t>(want, std::max<int64_t>(n - 1, 1));
         want = (want + 7) / 8 * 8;
-        if (want <= c->cap && c->nbr) return B2_OK;
+        if (want <= c->cap && c->nbr && (size_t)cdiv(c->ncap, 32) * (size_t)c->cap * 32 <= c->nbr_alloc) return B2_OK;
+        want = std::max(want, c->cap);
         int rc;
-        size_t tiles = (size_t)cdiv(n, 32);
-        if ((rc = dev_alloc(c, &c->nbr, tiles * (size_t)want * 32))) return rc;
+        size_t need = (size_t)cdiv(c->ncap, 32) * (size_t)want * 32;
+        if (need > c->nbr_alloc || !c->nbr) {
+            if ((rc = dev_alloc(c, &c->nbr, need))) return rc;
+            c->nbr_alloc = need;
+        }
         c->cap = want;
         return B2_OK;
     }
@@ -262,6 +271,7 @@ template <typename R> struct Impl {
                    (P4 *)c->tpos, (V4 *)c->tvel, c->torig);
             LAUNCH(k_gather_commit<R>, cdiv(n, 256), 256, c->ctl, n, (const P4 *)c->tpos, (const V4 *)c->tvel,
                    c->torig, (P4 *)c->pos[0], (P4 *)c->pos[1], (V4 *)c->vel, c->orig);
+            LAUNCH(k_inverse, cdiv(n, 256), 256, c->ctl, 1, c->orig, n, c->inv);
             LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
             LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
         }
@@ -341,6 +351,11 @@ template <typename R> struct Impl {
                         int64_t *steps_done, int *converged);
     static int neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, int32_t *max_count);
     static int mark_reference(b2_ctx *c);
+    static int dd_begin(b2_ctx *c, int64_t steps, double dt, int opening_kick);
+    static int dd_step(b2_ctx *c, float *vmax_out);
+    static int dd_end(b2_ctx *c);
+    static int dd_pack(b2_ctx *c, const int32_t *ids_dev, int64_t n, double *out_dev);
+    static int dd_unpack(b2_ctx *c, int64_t first, int64_t n, const double *in_dev);
     static int compute(b2_ctx *c, int what, double *energy, double *virial, double *stress9,
                        double *forces, double *pe, double *vir);
 };
@@ -386,7 +401,7 @@ __global__ void k_update(const Ctl *__restrict__ ctl, const double *__restrict__
         double px = spos[o] - cx, py = spos[o + 1] - cy, pz = spos[o + 2] - cz;
         double kx = rint(px / box.Ld[0]), ky = rint(py / box.Ld[1]), kz = rint(pz / box.Ld[2]);
         img[o] += (int)kx; img[o + 1] += (int)ky; img[o + 2] += (int)kz;
-        pos[s] = encode_pos(px - kx * box.Ld[0], py - ky * box.Ld[1], pz - kz * box.Ld[2], ptype(pos[s]), box);
+        pos[s] = encode_pos(px - kx * box.Ld[0], py - ky * box.Ld[1], pz - kz * box.Ld[2], praw(pos[s]), box);
     }
     if (svel) {
         V4 v = vel[s];
@@ -501,10 +516,9 @@ int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
                     const int32_t *species, const double *mass)
 {
     int rc;
-    if (n != c->n || !c->pos[0]) {
-        if ((rc = alloc_particles(c, n))) return rc;
-        c->cap = 0;
-        if (c->nbr) { cudaFree(c->nbr); c->nbr = nullptr; }
+    if (n > c->ncap || !c->pos[0]) {
+        // grow with headroom: a decomposed domain re-uploads a slightly different n at every refresh
+        if ((rc = alloc_particles(c, c->pos[0] ? n + n / 8 + 1024 : n))) return rc;
     }
     c->n = n;
     c->list_dirty = true;
@@ -518,13 +532,15 @@ int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     if (n == 0) return B2_OK;
     double *spos = c->stage, *svel = c->stage + 3 * n;
     double *smass = (double *)c->tpos;     // scratch reuse: n doubles fit in n V4
-    CU(cudaMemcpyAsync(spos, pos, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-    if (vel) CU(cudaMemcpyAsync(svel, vel, 3 * n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-    if (mass) CU(cudaMemcpyAsync(smass, mass, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-    CU(cudaMemcpyAsync(c->stage_i, species, n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    // cudaMemcpyDefault: the sources may be host (b2_upload) or device (b2_upload_device) memory
+    CU(cudaMemcpyAsync(spos, pos, 3 * n * sizeof(double), cudaMemcpyDefault, c->stream));
+    if (vel) CU(cudaMemcpyAsync(svel, vel, 3 * n * sizeof(double), cudaMemcpyDefault, c->stream));
+    if (mass) CU(cudaMemcpyAsync(smass, mass, n * sizeof(double), cudaMemcpyDefault, c->stream));
+    CU(cudaMemcpyAsync(c->stage_i, species, n * sizeof(int32_t), cudaMemcpyDefault, c->stream));
     LAUNCH(k_ingest<R>, cdiv(n, 256), 256, spos, vel ? svel : nullptr, c->stage_i, mass ? smass : nullptr,
            (int)n, c->center[0], c->center[1], c->center[2], make_box<R>(c),
            (P4 *)c->pos[0], (V4 *)c->vel, c->orig, c->img, c->ref);
+    LAUNCH(k_inverse, cdiv(n, 256), 256, c->ctl, 0, c->orig, (int)n, c->inv);
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     return B2_OK;
@@ -559,9 +575,9 @@ int Impl<R>::download(b2_ctx *c, double *pos, double *vel, int32_t *image)
     LAUNCH(k_export<R>, cdiv(n, 256), 256, c->ctl, (int)n, c->center[0], c->center[1], c->center[2], make_box<R>(c),
            (const P4 *)c->pos[0], (const P4 *)c->pos[1], (const V4 *)c->vel, (const V4 *)c->frc,
            (const R *)c->vir, c->orig, pos ? spos : nullptr, vel ? svel : nullptr, nullptr, nullptr, nullptr);
-    if (pos) CU(cudaMemcpyAsync(pos, spos, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    if (vel) CU(cudaMemcpyAsync(vel, svel, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    if (image) CU(cudaMemcpyAsync(image, c->img, 3 * n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    if (pos) CU(cudaMemcpyAsync(pos, spos, 3 * n * sizeof(double), cudaMemcpyDefault, c->stream));
+    if (vel) CU(cudaMemcpyAsync(vel, svel, 3 * n * sizeof(double), cudaMemcpyDefault, c->stream));
+    if (image) CU(cudaMemcpyAsync(image, c->img, 3 * n * sizeof(int32_t), cudaMemcpyDefault, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     return B2_OK;
 }
@@ -690,6 +706,8 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
     a.kick = (R)dt;
     a.drift = (R)dt;
     a.box = make_box<R>(c);
+    a.dd = 0;
+    a.vmax_out = nullptr;
     int64_t done = 0;
     while (done < steps) {
         // speculative batches: [guarded refresh][batch x step]; steps after the
@@ -826,6 +844,75 @@ int Impl<R>::minimize(b2_ctx *c, int method, int64_t max_steps, double dt, doubl
     return B2_OK;
 }
 
+// ---- domain decomposition primitives (no communication in here) ---------------
+template <typename R>
+int Impl<R>::dd_begin(b2_ctx *c, int64_t steps, double dt, int opening_kick)
+{
+    int rc;
+    int n = (int)c->n;
+    // after a mid-run refresh the velocities already live at half steps: only the list is needed
+    if ((rc = opening_kick ? ensure_forces(c) : ensure_list(c))) return rc;
+    c->dd_dt = dt;
+    c->min_resume = false;
+    if (n > 0 && opening_kick)
+        LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(-0.5 * dt));
+    LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0, 0);
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::dd_step(b2_ctx *c, float *vmax_out)
+{
+    int n = (int)c->n;
+    StepArgs<R> a;
+    a.ctl = c->ctl;
+    a.pos[0] = (P4 *)c->pos[0];
+    a.pos[1] = (P4 *)c->pos[1];
+    a.vel = (V4 *)c->vel;
+    a.nbr = c->nbr;
+    a.nnb = c->nnb;
+    a.orig = c->orig;
+    a.img = c->img;
+    a.n = n;
+    a.cap = c->cap;
+    a.kick = (R)c->dd_dt;
+    a.drift = (R)c->dd_dt;
+    a.box = make_box<R>(c);
+    a.dd = 1;
+    a.vmax_out = vmax_out;
+    if (n > 0) LAUNCH(k_step_nve<R>, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::dd_end(b2_ctx *c)
+{
+    int rc;
+    int n = (int)c->n;
+    c->forces_valid = c->ev_valid = false;
+    if ((rc = ensure_forces(c))) return rc;
+    if (n > 0) LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(0.5 * c->dd_dt));
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::dd_pack(b2_ctx *c, const int32_t *ids_dev, int64_t n, double *out_dev)
+{
+    if (n > 0)
+        LAUNCH(k_dd_pack<R>, cdiv(n, 256), 256, c->ctl, (const P4 *)c->pos[0], (const P4 *)c->pos[1], c->inv,
+               ids_dev, (int)n, make_box<R>(c), out_dev);
+    return B2_OK;
+}
+
+template <typename R>
+int Impl<R>::dd_unpack(b2_ctx *c, int64_t first, int64_t n, const double *in_dev)
+{
+    if (n > 0)
+        LAUNCH(k_dd_unpack<R>, cdiv(n, 256), 256, c->ctl, (P4 *)c->pos[0], (P4 *)c->pos[1], c->inv, (int)first,
+               (int)n, make_box<R>(c), in_dev);
+    return B2_OK;
+}
+
 // ---------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------
@@ -894,7 +981,7 @@ int b2_destroy(b2_ctx *c)
     if (!c) return B2_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig,
+    void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv,
                     c->img, c->ref, c->mvel, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i};
     for (void *p : ptrs)
@@ -986,7 +1073,7 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel, const 
     if (!c->have_box) return fail(c, B2_ESTATE, "b2_upload: call b2_set_box first");
     if (!c->have_table) return fail(c, B2_ESTATE, "b2_upload: call b2_set_pair_table first");
     for (int64_t i = 0; i < n; i++) {
-        if (species[i] < 0 || species[i] >= c->nsp)
+        if (species[i] < 0 || (species[i] & ~B2_GHOST) >= c->nsp)
             return fail(c, B2_EINVAL, "b2_upload: species id %d of particle %lld outside the pair table",
                         species[i], (long long)i);
         if (mass && !(mass[i] > 0.0)) return fail(c, B2_EINVAL, "b2_upload: mass must be > 0");
@@ -1088,6 +1175,80 @@ int b2_last_timing(b2_ctx *c, double *ms, int64_t *launches)
     if (ms) *ms = c->last_ms;
     if (launches) *launches = c->last_launches;
     return B2_OK;
+}
+
+int b2_upload_device(b2_ctx *c, int64_t n, const double *pos_dev, const double *vel_dev,
+                     const int32_t *species_dev, const double *mass_dev)
+{
+    if (!c || n < 0 || (n > 0 && (!pos_dev || !species_dev))) return fail(c, B2_EINVAL, "b2_upload_device: bad argument");
+    if (n > 0x7fffff00LL) return fail(c, B2_EINVAL, "b2_upload_device: at most 2^31 particles per context");
+    if (!c->have_box || !c->have_table) return fail(c, B2_ESTATE, "b2_upload_device: set the box and the pair table first");
+    int rc = bind_device(c);
+    if (rc) return rc;
+    return DISPATCH(upload, c, n, pos_dev, vel_dev, species_dev, mass_dev);
+}
+
+int b2_download_device(b2_ctx *c, double *pos_dev, double *vel_dev, int32_t *image_dev)
+{
+    NEED_PARTICLES("b2_download_device");
+    return DISPATCH(download, c, pos_dev, vel_dev, image_dev);
+}
+
+int b2_dd_begin(b2_ctx *c, int64_t steps, double dt, int opening_kick)
+{
+    NEED_PARTICLES("b2_dd_begin");
+    if (steps < 0 || !(dt > 0.0)) return fail(c, B2_EINVAL, "b2_dd_begin: steps >= 0 and dt > 0 required");
+    return DISPATCH(dd_begin, c, steps, dt, opening_kick);
+}
+
+int b2_dd_step(b2_ctx *c, float *vmax2_out_dev)
+{
+    NEED_PARTICLES("b2_dd_step");
+    if (!vmax2_out_dev) return fail(c, B2_EINVAL, "b2_dd_step: NULL argument");
+    if (!(c->dd_dt > 0.0)) return fail(c, B2_ESTATE, "b2_dd_step: call b2_dd_begin first");
+    if (c->n == 0) CU(cudaMemsetAsync(vmax2_out_dev, 0, sizeof(float), c->stream));
+    return DISPATCH(dd_step, c, vmax2_out_dev);
+}
+
+int b2_dd_commit(b2_ctx *c, const float *gvmax2_dev)
+{
+    NEED_PARTICLES("b2_dd_commit");
+    if (!gvmax2_dev) return fail(c, B2_EINVAL, "b2_dd_commit: NULL argument");
+    LAUNCH(k_dd_commit, 1, 1, c->ctl, gvmax2_dev, c->dd_dt);
+    return B2_OK;
+}
+
+int b2_dd_poll(b2_ctx *c, int64_t *steps_done, int *need_refresh)
+{
+    NEED_PARTICLES("b2_dd_poll");
+    int rc = pull_ctl(c);
+    if (rc) return rc;
+    CU(cudaGetLastError());
+    if (steps_done) *steps_done = c->hctl->steps_done;
+    if (need_refresh) *need_refresh = (c->hctl->halt_rebuild || c->hctl->overflow) ? 1 : 0;
+    if (c->hctl->halt_rebuild) c->list_dirty = true;
+    return B2_OK;
+}
+
+int b2_dd_end(b2_ctx *c)
+{
+    NEED_PARTICLES("b2_dd_end");
+    return DISPATCH(dd_end, c);
+}
+
+int b2_dd_pack(b2_ctx *c, const int32_t *ids_dev, int64_t n, double *out_dev)
+{
+    NEED_PARTICLES("b2_dd_pack");
+    if (n < 0 || (n > 0 && (!ids_dev || !out_dev))) return fail(c, B2_EINVAL, "b2_dd_pack: bad argument");
+    return DISPATCH(dd_pack, c, ids_dev, n, out_dev);
+}
+
+int b2_dd_unpack(b2_ctx *c, int64_t first_id, int64_t n, const double *in_dev)
+{
+    NEED_PARTICLES("b2_dd_unpack");
+    if (n < 0 || first_id < 0 || first_id + n > c->n || (n > 0 && !in_dev))
+        return fail(c, B2_EINVAL, "b2_dd_unpack: id range outside the resident particles");
+    return DISPATCH(dd_unpack, c, first_id, n, in_dev);
 }
 
 int b2_set_profile(b2_ctx *c, int on)

@@ -131,6 +131,7 @@ k_force(ForceArgs<R> a)
         double pe = 0, vir = 0;
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
         const int nsp = g_pair.nsp;
+        // (a ghost has an empty row: nnb == 0)
         if (nsp <= 2) pair_row<R, EV, STRESS, true>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
         else pair_row<R, EV, STRESS, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
         a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
@@ -162,6 +163,10 @@ template <typename R> struct StepArgs {
     int n, cap;
     R kick, drift;                   // v += kick F/m ; x += drift v
     Box<R> box;
+    // domain decomposition: the step's bookkeeping waits for the GLOBAL max |v|^2
+    // (k_dd_commit); this kernel only publishes the local one
+    int dd;
+    float *vmax_out;
 };
 
 // The fused velocity-Verlet step (kick-drift form): F(x) -> v += dt F/m ->
@@ -176,7 +181,10 @@ k_step_nve(StepArgs<R> a)
     typedef typename Vec4<R>::type V4;
     typedef typename Pos4<R>::type P4;
     Ctl *ctl = a.ctl;
-    if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) {
+        if (a.dd && blockIdx.x == 0 && threadIdx.x == 0) *a.vmax_out = 0.f;    // a no-op step moves nothing
+        return;
+    }
     __shared__ PairTab<R> tab;
     __shared__ float s_v2[FORCE_THREADS / 32];
     __shared__ bool s_last;
@@ -189,6 +197,9 @@ k_step_nve(StepArgs<R> a)
     float v2 = 0.f;
     if (i < a.n) {
         P4 pi = pos[i];
+        if (is_ghost(pi)) {
+            posn[i] = pi;            // overwritten by the halo exchange before the next step
+        } else {
         R fx = 0, fy = 0, fz = 0;
         double pe = 0, vir = 0;
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
@@ -207,6 +218,7 @@ k_step_nve(StepArgs<R> a)
         a.vel[i] = v;
         // rounded up: the bound must never be smaller than the true speed
         v2 = __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+        }
     }
     v2 = warp_max(v2);
     if ((threadIdx.x & 31) == 0) s_v2[threadIdx.x >> 5] = v2;
@@ -218,7 +230,11 @@ k_step_nve(StepArgs<R> a)
         __threadfence();
         unsigned ticket = atomicAdd(&ctl->blocks_done, 1u);
         s_last = (ticket == gridDim.x - 1);
-        if (s_last) {
+        if (s_last && a.dd) {
+            __threadfence();
+            *a.vmax_out = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
+            ctl->blocks_done = 0u;
+        } else if (s_last) {
             __threadfence();
             float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
             double bound = ctl->disp_bound + fabs((double)a.drift) * sqrt((double)vm2) * (1.0 + 1e-6);
@@ -292,6 +308,7 @@ k_thermo_partial(const Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         V4 v = vel[i], f = frc[i];
         P4 p = pos[i];
+        if (is_ghost(p)) continue;
         double rx, ry, rz;
         to_double(p, box, rx, ry, rz);
         double m = (double)v.w;
@@ -482,4 +499,52 @@ k_min_step(MinArgs<R> a)
             ctl->blocks_done = 0u;
         }
     }
+}
+
+// Domain decomposition: settle a step once the global max |v|^2 is known (the
+// same number on every rank, so every rank takes the same decisions).
+__global__ void k_dd_commit(Ctl *ctl, const float *__restrict__ gvmax2, double drift)
+{
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) return;
+    double bound = ctl->disp_bound + fabs(drift) * sqrt((double)*gvmax2) * (1.0 + 1e-6);
+    ctl->disp_bound = bound;
+    ctl->cur ^= 1u;
+    long long s = ctl->steps_done + 1;
+    ctl->steps_done = s;
+    if (s >= ctl->steps_target) ctl->done = 1u;
+    if (bound > ctl->half_skin) ctl->halt_rebuild = 1u;
+}
+
+// halo exchange: positions by LOCAL id (upload order), as 3 doubles relative to the cell centre
+template <typename R>
+__global__ void k_dd_pack(const Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
+                          const typename Pos4<R>::type *pos1, const int *__restrict__ inv,
+                          const int *__restrict__ ids, int n, Box<R> box, double *__restrict__ out)
+{
+    const typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    double x, y, z;
+    to_double(pos[inv[ids[k]]], box, x, y, z);
+    out[3 * k] = x; out[3 * k + 1] = y; out[3 * k + 2] = z;
+}
+
+template <typename R>
+__global__ void k_dd_unpack(const Ctl *__restrict__ ctl, typename Pos4<R>::type *pos0,
+                            typename Pos4<R>::type *pos1, const int *__restrict__ inv, int first, int n,
+                            Box<R> box, const double *__restrict__ in)
+{
+    typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int s = inv[first + k];
+    pos[s] = encode_pos(in[3 * k], in[3 * k + 1], in[3 * k + 2], praw(pos[s]), box);
+}
+
+__global__ void k_inverse(const Ctl *__restrict__ ctl, int guarded, const int *__restrict__ orig, int n,
+                          int *__restrict__ inv)
+{
+    if (guarded && !ctl->halt_rebuild) return;
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n) inv[orig[s]] = s;
 }

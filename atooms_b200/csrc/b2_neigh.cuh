@@ -252,10 +252,10 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     if (threadIdx.x < B2_MAXSP * B2_MAXSP) s_rl2[threadIdx.x] = rl2_of(g_pair, threadIdx.x, (R)0);
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool active = i < n;
     if (((blockIdx.x * blockDim.x + threadIdx.x) & ~31) >= n) return;     // whole warp out of range
     const int nsp = g_pair.nsp;
-    const P4 pi = pos[active ? i : n - 1];
+    const P4 pi = pos[i < n ? i : n - 1];
+    const bool active = i < n && !is_ghost(pi);      // ghosts act as neighbours but own no row
     const int ti = ptype(pi);
     const R *rl2_row = s_rl2 + ti * nsp;
     int *row = nbr + ((size_t)(i >> 5) * cap) * 32 + (i & 31);
@@ -297,7 +297,7 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
         }
     }
 #undef B2_TEST
-    if (active) {
+    if (i < n) {
         nnb[i] = min(cnt, cap);
         if (cnt > cap) ctl->overflow = 1u;
         atomicMax(&ctl->max_count, (unsigned)cnt);

@@ -1,0 +1,291 @@
+"""
+Spatial slab decomposition of one large periodic system over several GPUs.
+
+The reference has no domain decomposition: its only
+multi-process route is `mpirun -n lammps_mpi_tasks` inside the LAMMPS
+subprocess (atooms/backends/lammps.py:61-62).  Here each rank (one process per
+GPU) owns the particles of one slab along x and keeps read-only copies
+("ghosts") of the neighbours' particles within r_list of its two faces.
+
+  every step     fused step kernel on the owned particles (b2_dd_step)
+                 -> all_reduce(MAX) of ONE float, the max |v|^2, so that every
+                    rank takes the same list-refresh decision (b2_dd_commit)
+                 -> halo: pack boundary positions, send/recv with the two ring
+                    neighbours (NCCL over NVLink through torch.distributed),
+                    unpack into the ghosts
+  every refresh  (displacement bound > skin/2, ~ every 15-20 steps; host-
+                 synchronous) migrate particles that left the slab, re-select
+                 the ghosts, re-upload the domain, rebuild the Verlet list
+
+Coordinates stay global on every rank (same box), so packed positions need no
+translation.  The engine primitives do no communication; everything that
+moves between ranks is a torch tensor, so the same code runs on CUDA tensors
+with the NCCL backend (product) and on CPU tensors with gloo (tests, with the
+CPU oracle standing in as the engine).
+"""
+import numpy
+import torch
+import torch.distributed as dist
+
+from . import capi, models
+
+__all__ = ['SlabDomain']
+
+
+class SlabDomain(object):
+
+    def __init__(self, position, velocity, species, side, model='lennard_jones', dt=0.002, skin=0.3,
+                 precision=64, mass=None, gid=None, center=None, device=None, library=None, group=None):
+        """`position` ... are the particles this rank holds initially (global
+        coordinates, any x: the first refresh sends strays to the ring neighbour
+        that owns them; they must not be more than one slab away)."""
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.model = models.get(model)
+        self.dt, self.skin, self.precision = float(dt), float(skin), int(precision)
+        self.side = numpy.asarray(side, dtype=numpy.float64)
+        self.center = numpy.zeros(3) if center is None else numpy.asarray(center, dtype=numpy.float64)
+        self.rlist = float(self.model.rcut.max()) + self.skin
+        self.width = self.side[0] / self.world
+        if self.world > 1 and self.width < 2.0 * self.rlist * (1 + 1e-9):
+            raise ValueError('slab width %g is below 2 r_list = %g: use fewer ranks' % (self.width, 2 * self.rlist))
+        lib = library if library is not None else capi.load()
+        on_gpu = lib.name.startswith('cuda')
+        if device is None:
+            device = torch.device('cuda', torch.cuda.current_device()) if on_gpu else torch.device('cpu')
+        self.dev = torch.device(device)
+        self.engine = capi.Engine(self.precision, device=self.dev.index or 0, library=lib)
+        if on_gpu:
+            self.engine.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
+        self.engine.set_box(self.side, self.center)
+        self.engine.set_pair_table(self.model.eps, self.model.sigma, self.model.rcut, self.model.shifted)
+        self.engine.set_skin(self.skin)
+        f64 = dict(dtype=torch.float64, device=self.dev)
+        n = len(species)
+        self.pos = torch.as_tensor(numpy.ascontiguousarray(position, dtype=numpy.float64).reshape(n, 3)).to(**f64)
+        self.vel = torch.zeros((n, 3), **f64) if velocity is None else \
+            torch.as_tensor(numpy.ascontiguousarray(velocity, dtype=numpy.float64).reshape(n, 3)).to(**f64)
+        self.mass = torch.ones(n, **f64) if mass is None else torch.as_tensor(numpy.asarray(mass, dtype=numpy.float64)).to(**f64)
+        self.spe = torch.as_tensor(numpy.asarray(species, dtype=numpy.int32)).to(self.dev)
+        self.gid = torch.arange(n, dtype=torch.int64, device=self.dev) if gid is None else \
+            torch.as_tensor(numpy.asarray(gid, dtype=numpy.int64)).to(self.dev)
+        self.img = torch.zeros((n, 3), dtype=torch.int64, device=self.dev)
+        self._vmax = torch.zeros(2, dtype=torch.float32, device=self.dev)
+        self._resident = False
+        self._batch = 8
+        self.refreshes = 0
+        self.steps = 0
+        self.halo_bytes_per_step = 0
+
+    # -- helpers ---------------------------------------------------------------------
+    @property
+    def n_own(self):
+        return self.pos.shape[0]
+
+    def _left(self):
+        return (self.rank - 1) % self.world
+
+    def _right(self):
+        return (self.rank + 1) % self.world
+
+    def _exchange(self, to_left, to_right, like_cols):
+        """Send two (rows, cols) float64 tensors to the ring neighbours and return what
+        arrives (from_left, from_right).  Posting order [to-left, to-right] /
+        [from-right, from-left] keeps the pairing unambiguous when both neighbours
+        are the same rank (world size 2)."""
+        counts = torch.tensor([to_left.shape[0], to_right.shape[0]], dtype=torch.int64, device=self.dev)
+        all_counts = [torch.empty_like(counts) for _ in range(self.world)]
+        dist.all_gather(all_counts, counts, group=self.group)
+        n_from_right = int(all_counts[self._right()][0])      # the right neighbour's to-left message
+        n_from_left = int(all_counts[self._left()][1])
+        pad = lambda t: t if t.shape[0] > 0 else torch.zeros((1, like_cols), dtype=torch.float64, device=self.dev)
+        from_right = torch.empty((max(n_from_right, 1), like_cols), dtype=torch.float64, device=self.dev)
+        from_left = torch.empty((max(n_from_left, 1), like_cols), dtype=torch.float64, device=self.dev)
+        ops = [dist.P2POp(dist.isend, pad(to_left).contiguous(), self._left(), self.group),
+               dist.P2POp(dist.isend, pad(to_right).contiguous(), self._right(), self.group),
+               dist.P2POp(dist.irecv, from_right, self._right(), self.group),
+               dist.P2POp(dist.irecv, from_left, self._left(), self.group)]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        return from_left[:n_from_left], from_right[:n_from_right]
+
+    # -- refresh: migration + ghost selection + re-upload ---------------------------------
+    def refresh(self):
+        if self._resident:
+            n = self.n_own
+            img = torch.empty((self.engine.n, 3), dtype=torch.int32, device=self.dev)
+            pos = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
+            vel = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
+            self.engine.download_device(pos.data_ptr(), vel.data_ptr(), img.data_ptr())
+            self.pos, self.vel = pos[:n].clone(), vel[:n].clone()
+            self.img += img[:n].to(torch.int64)
+        side = torch.as_tensor(self.side, dtype=torch.float64, device=self.dev)
+        ctr = torch.as_tensor(self.center, dtype=torch.float64, device=self.dev)
+        # fold into the global cell (atooms/system/particle.py:90-99)
+        rel = self.pos - ctr
+        k = torch.round(rel / side)
+        rel = rel - k * side
+        if self._resident:          # like b2_upload, the fold of the INITIAL coordinates is not a crossing
+            self.img += k.to(torch.int64)
+        self.pos = rel + ctr
+        # which slab owns each particle now
+        u = rel[:, 0] / side[0] + 0.5
+        slab = torch.clamp(torch.floor(u * self.world).to(torch.int64), 0, self.world - 1)
+        hop = (slab - self.rank + self.world // 2) % self.world - self.world // 2 if self.world > 1 else slab * 0
+        if self.world == 2:
+            hop = torch.where(slab != self.rank, torch.ones_like(hop), hop)    # either way round the ring
+        if self.world > 1 and int(hop.abs().max()) > 1:
+            raise RuntimeError('a particle moved more than one slab between two refreshes')
+        stay, go_l, go_r = hop == 0, hop == -1, hop == 1
+
+        def payload(mask):
+            return torch.cat([self.pos[mask], self.vel[mask], self.mass[mask, None],
+                              self.gid[mask, None].to(torch.float64), self.spe[mask, None].to(torch.float64),
+                              self.img[mask].to(torch.float64)], dim=1)
+        from_l, from_r = self._exchange(payload(go_l), payload(go_r), 12) if self.world > 1 else \
+            (self.pos.new_zeros((0, 12)), self.pos.new_zeros((0, 12)))
+        keep = payload(stay)
+        own = torch.cat([keep, from_l, from_r], dim=0)
+        self.pos, self.vel, self.mass = own[:, 0:3].contiguous(), own[:, 3:6].contiguous(), own[:, 6].contiguous()
+        self.gid = own[:, 7].round().to(torch.int64)
+        self.spe = own[:, 8].round().to(torch.int32)
+        self.img = own[:, 9:12].round().to(torch.int64)
+        n = self.n_own
+        # ghosts: owned particles within r_list of a face are copied to the neighbour beyond it
+        if self.world > 1:
+            x_in = (self.pos[:, 0] - ctr[0]) / side[0] + 0.5          # in [0, 1)
+            lo, hi = self.rank / self.world, (self.rank + 1) / self.world
+            margin = self.rlist / self.side[0] * (1 + 1e-6) + 1e-12
+            near_l = torch.nonzero(x_in < lo + margin).flatten()
+            near_r = torch.nonzero(x_in >= hi - margin).flatten()
+            ghost = lambda idx: torch.cat([self.pos[idx], self.spe[idx, None].to(torch.float64)], dim=1)
+            g_from_l, g_from_r = self._exchange(ghost(near_l), ghost(near_r), 4)
+            self._send_l, self._send_r = near_l.to(torch.int32).contiguous(), near_r.to(torch.int32).contiguous()
+        else:
+            g_from_l = g_from_r = self.pos.new_zeros((0, 4))
+            self._send_l = self._send_r = torch.zeros(0, dtype=torch.int32, device=self.dev)
+        self._n_gl, self._n_gr = g_from_l.shape[0], g_from_r.shape[0]
+        ghosts = torch.cat([g_from_l, g_from_r], dim=0)
+        ng = ghosts.shape[0]
+        pos = torch.cat([self.pos, ghosts[:, 0:3]], dim=0).contiguous()
+        vel = torch.cat([self.vel, self.vel.new_zeros((ng, 3))], dim=0).contiguous()
+        mass = torch.cat([self.mass, self.mass.new_ones(ng)], dim=0).contiguous()
+        spe = torch.cat([self.spe, ghosts[:, 3].round().to(torch.int32) | capi.GHOST], dim=0).contiguous()
+        self.engine.upload_device(n + ng, pos.data_ptr(), spe.data_ptr(), vel.data_ptr(), mass.data_ptr())
+        # halo buffers of the new shape
+        f64 = dict(dtype=torch.float64, device=self.dev)
+        self._out_l = torch.zeros((max(len(self._send_l), 1), 3), **f64)
+        self._out_r = torch.zeros((max(len(self._send_r), 1), 3), **f64)
+        self._in_l = torch.zeros((max(self._n_gl, 1), 3), **f64)
+        self._in_r = torch.zeros((max(self._n_gr, 1), 3), **f64)
+        self.halo_bytes_per_step = 24 * (len(self._send_l) + len(self._send_r))
+        self._resident = True
+        self.refreshes += 1
+
+    def _halo(self):
+        """Ghost positions of the new time level: pack -> ring exchange -> unpack."""
+        if self.world == 1:
+            return
+        eng, n = self.engine, self.n_own
+        eng.dd_pack(self._send_l.data_ptr(), len(self._send_l), self._out_l.data_ptr())
+        eng.dd_pack(self._send_r.data_ptr(), len(self._send_r), self._out_r.data_ptr())
+        ops = [dist.P2POp(dist.isend, self._out_l, self._left(), self.group),
+               dist.P2POp(dist.isend, self._out_r, self._right(), self.group),
+               dist.P2POp(dist.irecv, self._in_r, self._right(), self.group),
+               dist.P2POp(dist.irecv, self._in_l, self._left(), self.group)]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        eng.dd_unpack(n, self._n_gl, self._in_l.data_ptr())
+        eng.dd_unpack(n + self._n_gl, self._n_gr, self._in_r.data_ptr())
+
+    # -- dynamics -------------------------------------------------------------------------
+    def run(self, steps):
+        """`steps` velocity-Verlet NVE steps of the whole decomposed system."""
+        steps = int(steps)
+        if steps <= 0:
+            return
+        if not self._resident:
+            self.refresh()
+        eng = self.engine
+        eng.dd_begin(steps, self.dt, True)
+        base, since_refresh = 0, 0
+        while base < steps:
+            m = min(self._batch, steps - base)
+            for _ in range(m):
+                eng.dd_step(self._vmax.data_ptr())
+                if self.world > 1:
+                    dist.all_reduce(self._vmax[:1], op=dist.ReduceOp.MAX, group=self.group)
+                eng.dd_commit(self._vmax.data_ptr())
+                self._halo()
+            done, need = eng.dd_poll()
+            since_refresh += done
+            base += done
+            if need:
+                # every rank sees the same flag (the bound comes from the global max)
+                self._batch = max(1, min(since_refresh, 64))
+                self.refresh()
+                eng.dd_begin(steps - base, self.dt, False)
+                since_refresh = 0
+            elif done == m and base < steps:
+                self._batch = min(self._batch + 2, 64)
+            if base < steps and not need:
+                eng.dd_begin(steps - base, self.dt, False)     # new budget for the next round
+        eng.dd_end()
+        self.steps += steps
+
+    # -- observables -----------------------------------------------------------------------
+    def thermo(self):
+        """Totals over the whole system (owned particles of every rank, all_reduce SUM)."""
+        if not self._resident:
+            self.refresh()
+        t = self.engine.thermo()
+        vec = torch.tensor([t['kinetic'], t['potential'], t['virial'], t['fnorm2'], *t['momentum'], t['mass'],
+                            float(self.n_own)], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(vec, op=dist.ReduceOp.SUM, group=self.group)
+        v = vec.cpu().numpy()
+        return {'kinetic': v[0], 'potential': v[1], 'virial': v[2], 'fnorm2': v[3], 'momentum': v[4:7],
+                'mass': v[7], 'n': int(round(v[8]))}
+
+    def gather(self):
+        """(gid-ordered) global position, velocity, image on every rank — for tests."""
+        if self._resident:
+            n = self.n_own
+            pos = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
+            vel = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
+            img = torch.empty((self.engine.n, 3), dtype=torch.int32, device=self.dev)
+            self.engine.download_device(pos.data_ptr(), vel.data_ptr(), img.data_ptr())
+            pos, vel, img = pos[:n], vel[:n], self.img + img[:n].to(torch.int64)
+        else:
+            pos, vel, img = self.pos, self.vel, self.img
+        mine = torch.cat([self.gid[:, None].to(torch.float64), pos, vel, img.to(torch.float64)], dim=1).cpu()
+        if self.world > 1:
+            parts = [None] * self.world
+            dist.all_gather_object(parts, mine.numpy(), group=self.group)
+            allp = numpy.concatenate(parts, axis=0)
+        else:
+            allp = mine.numpy()
+        order = numpy.argsort(allp[:, 0])
+        allp = allp[order]
+        return allp[:, 1:4], allp[:, 4:7], numpy.round(allp[:, 7:10]).astype(numpy.int64)
+
+    def load_host(self, position, velocity):
+        """Replace the owned particles' coordinates and velocities from host arrays
+        (pinned memory makes the copies asynchronous); same particles, same order."""
+        self.pos = torch.as_tensor(position).to(self.dev, non_blocking=True)
+        self.vel = torch.as_tensor(velocity).to(self.dev, non_blocking=True)
+        self._resident = False
+
+    def store_host(self, position, velocity):
+        """Copy the owned particles' state into host arrays of shape (n_own, 3)."""
+        n = self.n_own
+        pos = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
+        vel = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
+        self.engine.download_device(pos.data_ptr(), vel.data_ptr(), 0)
+        torch.as_tensor(position)[:n].copy_(pos[:n])
+        torch.as_tensor(velocity)[:n].copy_(vel[:n])
+        return n
+
+    def close(self):
+        self.engine.close()

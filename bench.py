@@ -199,11 +199,22 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(n, inner):
-    return {'workload': 'Kob-Andersen 80:20 N=%d rho=1.2 NVE velocity-Verlet dt=0.002, LJ cut&shifted 2.5 sigma_ab, '
-                        'Verlet skin 0.3 (BASELINE.json configs[2], SURVEY.md 8d C3)' % n,
-            'particles_per_gpu': n, 'md_timesteps_per_step': inner,
-            'cache': 'inputs larger than L2 (neighbour list ~0.8 GB per GPU vs 126 MB L2)'}
+def workload_config(n, inner, world=1, halo_bytes=0):
+    cfg = {'workload': 'Kob-Andersen 80:20 N=%d rho=1.2 NVE velocity-Verlet dt=0.002, LJ cut&shifted 2.5 sigma_ab, '
+                       'Verlet skin 0.3 (BASELINE.json configs[2], SURVEY.md 8d C3)' % (n * world),
+           'particles_per_gpu': n, 'md_timesteps_per_step': inner,
+           'cache': 'inputs larger than L2 (neighbour list ~0.8 GB per GPU vs 126 MB L2)'}
+    if world > 1:
+        cfg['decomposition'] = ('one periodic box of %d x 1.2M particles, %d slabs along x, ring halo exchange '
+                                '(NCCL send/recv) + 4-byte all_reduce per step, migration at list refresh'
+                                % (world, world))
+        cfg['halo_bytes_per_step_per_gpu'] = int(halo_bytes)
+    return cfg
+
+
+def atooms_model():
+    from atooms_b200 import models
+    return models.PairModel(KA_EPS, KA_SIG, 2.5 * KA_SIG, True, name='kob_andersen')
 
 
 def main():
@@ -255,11 +266,76 @@ def main():
     stream = torch.cuda.Stream()
     results = {}
     clocks = None
+    if world > 1:
+        # ONE periodic system of world x 1.2M particles, slab-decomposed along x: rank r owns
+        # tile r of the (world L) x L x L box; per step one ring halo exchange (NCCL send/recv)
+        # and one 4-byte all_reduce; particles migrate at every list refresh (atooms_b200/dd.py)
+        from atooms_b200.dd import SlabDomain
+        gside = side * numpy.array([world, 1, 1])
+        gpos = pos + numpy.array([(rank - 0.5 * (world - 1)) * side[0], 0.0, 0.0])
     for precision in ([args.precision] + [p for p in (32, 64) if p != args.precision]):
+        primary = precision == args.precision
+        if world > 1:
+            if not primary:
+                continue
+            dom = SlabDomain(gpos, vel, spe, gside, model=atooms_model(), dt=DT, skin=SKIN, precision=precision,
+                             gid=numpy.arange(n, dtype=numpy.int64) + rank * n, library=lib)
+            dom.thermo()
+            for _ in range(args.warmup):
+                dom.run(INNER)
+            l0 = dom.engine.stats()['launches']
+            r0 = dom.refreshes
+            sampler = ClockSampler(local_rank) if rank == 0 else None
+            barrier()
+            if sampler:
+                sampler.start()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            for _ in range(args.steps):
+                dom.run(INNER)
+            ev1.record()
+            barrier()
+            ms = max_over_ranks(ev0.elapsed_time(ev1))
+            if sampler:
+                clocks = sampler.stop()
+            launches = dom.engine.stats()['launches'] - l0
+            th = dom.thermo()
+            ntot = th['n']
+            value = ntot * INNER * args.steps / (ms * 1e-3)
+            # end to end: host buffers in and out around every chunk
+            cap = int(n * 1.2)
+            hpos = torch.empty((cap, 3), dtype=torch.float64, pin_memory=True)
+            hvel = torch.empty((cap, 3), dtype=torch.float64, pin_memory=True)
+            e2e_steps = max(2, args.steps // 2)
+            m = dom.store_host(hpos, hvel)
+
+            def e2e_step(m):
+                dom.load_host(hpos[:m], hvel[:m])
+                dom.run(INNER)
+                th = dom.thermo()
+                return dom.store_host(hpos, hvel), th
+            m, th = e2e_step(m)
+            barrier()
+            t0 = time.perf_counter()
+            h2d = d2h = 0
+            for _ in range(e2e_steps):
+                h2d += 2 * 3 * m * 8
+                m, th = e2e_step(m)
+                d2h += 2 * 3 * m * 8 + 9 * 8
+            barrier()
+            e2e_s = max_over_ranks(time.perf_counter() - t0)
+            results[precision] = dict(value=value, ms=ms, launches=launches,
+                                      prof={'ms_steps': 0.0, 'ms_refresh': 0.0, 'step_launches': 0,
+                                            'steps': INNER * args.steps, 'refreshes': dom.refreshes - r0},
+                                      e2e=ntot * INNER * e2e_steps / e2e_s, e2e_steps=e2e_steps,
+                                      stats=dom.engine.stats(), energy=(th['kinetic'] + th['potential']) / ntot,
+                                      h2d=h2d // e2e_steps, d2h=d2h // e2e_steps, ntot=ntot,
+                                      halo_bytes=dom.halo_bytes_per_step)
+            dom.close()
+            continue
         eng = make_engine(lib, precision, pos, spe, side, vel, device=local_rank)
         eng.set_stream(stream.cuda_stream)
         eng.compute(forces=False)
-        primary = precision == args.precision
         eng.set_profile(True)
         # ---- device-resident ------------------------------------------------
         for _ in range(args.warmup):
@@ -311,26 +387,30 @@ def main():
         e2e_value = world * n * INNER * e2e_steps / e2e_s
         st = eng.stats()
         results[precision] = dict(value=value, ms=ms, launches=launches, prof=prof, e2e=e2e_value,
-                                  e2e_steps=e2e_steps, stats=st,
-                                  energy=(th['kinetic'] + th['potential']) / n)
+                                  e2e_steps=e2e_steps, stats=st, h2d=2 * 3 * n * 8, d2h=2 * 3 * n * 8 + 16 * 8,
+                                  energy=(th['kinetic'] + th['potential']) / n, ntot=n, halo_bytes=0)
         eng.close()
 
     if rank == 0:
         r = results[args.precision]
         peak, peak_src = measured_peak()
-        step_launches = max(r['prof']['step_launches'], 1)
         # average duration of one k_step_nve launch that did work (no-op launches of a
-        # speculative batch are inside the bracket, so this is an upper bound)
-        kernel_ms = r['prof']['ms_steps'] / max(r['prof']['steps'], 1)
-        achieved = B_ALG[args.precision] * n / (kernel_ms * 1e-3) / 1e9
+        # speculative batch are inside the bracket, so this is an upper bound).  With
+        # several GPUs the step kernel is not bracketed separately: the whole step
+        # (kernel + halo exchange + refreshes) is charged to it, per GPU.
+        if world == 1:
+            kernel_ms = r['prof']['ms_steps'] / max(r['prof']['steps'], 1)
+        else:
+            kernel_ms = r['ms'] / (args.steps * INNER)
+        achieved = B_ALG[args.precision] * (r['ntot'] / world) / (kernel_ms * 1e-3) / 1e9
         line = {
             'metric': 'particle-timesteps/s', 'value': r['value'], 'unit': 'particle-timesteps/s',
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': r['ms'] / args.steps, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32' if args.precision == 32 else 'f64', 'data': 'synthetic',
-            'config': workload_config(n, INNER),
+            'config': workload_config(n, INNER, world, r['halo_bytes']),
             'e2e': {'value': r['e2e'], 'unit': 'particle-timesteps/s',
-                    'h2d_bytes_per_step': 2 * 3 * n * 8, 'd2h_bytes_per_step': 2 * 3 * n * 8 + 16 * 8,
+                    'h2d_bytes_per_step': int(r['h2d']), 'd2h_bytes_per_step': int(r['d2h']),
                     'steps': r['e2e_steps']},
             'gpu_launches': int(r['launches']),
             'clocks': clocks,
@@ -338,8 +418,8 @@ def main():
                          'frac': achieved / peak, 'traffic': None, 'kernel': 'k_step_nve',
                          'kernel_ms': kernel_ms, 'bytes_per_particle_step': B_ALG[args.precision],
                          'peak_source': peak_src,
-                         'step_kernel_share': r['prof']['ms_steps'] / r['ms'],
-                         'refresh_share': r['prof']['ms_refresh'] / r['ms']},
+                         'step_kernel_share': (r['prof']['ms_steps'] / r['ms']) if world == 1 else None,
+                         'refresh_share': (r['prof']['ms_refresh'] / r['ms']) if world == 1 else None},
             'detail': {('fp%d' % p): {'value': results[p]['value'], 'e2e': results[p]['e2e'],
                                       'ms_per_md_step': results[p]['ms'] / (args.steps * INNER),
                                       'step_kernel_ms': results[p]['prof']['ms_steps'] / max(results[p]['prof']['steps'], 1),

@@ -212,6 +212,49 @@ int b2_stats(b2_ctx *ctx, int64_t out[B2_S_LEN]);
  * count of the last b2_run_nve / b2_minimize / b2_compute call.             */
 int b2_last_timing(b2_ctx *ctx, double *ms, int64_t *launches);
 
+/* ---- spatial domain decomposition (one context = one slab of a larger system) --
+ *
+ * Nothing like it in the reference, whose only multi-process route is
+ * `mpirun -n lammps_mpi_tasks` inside the LAMMPS subprocess
+ * (atooms/backends/lammps.py:61-62).  These entry points do NO communication:
+ * the caller moves the packed buffers between ranks (NCCL send/recv through
+ * torch.distributed in atooms_b200/dd.py) and reduces the one float per step.
+ * All `_dev` pointers are device pointers of the context's GPU.
+ *
+ * A species id with B2_GHOST set marks a ghost: a read-only copy of a particle
+ * owned by a neighbouring domain.  Ghosts act on their neighbours but are not
+ * integrated and are excluded from every total of b2_thermo / b2_compute.
+ * Coordinates stay GLOBAL (same box on every rank), so packed positions are
+ * meaningful on the receiving side as they are.                             */
+#define B2_GHOST 256
+
+/* b2_upload / b2_download with device-resident buffers (same layouts).      */
+int b2_upload_device(b2_ctx *ctx, int64_t n, const double *pos_dev, const double *vel_dev,
+                     const int32_t *species_dev, const double *mass_dev);
+int b2_download_device(b2_ctx *ctx, double *pos_dev, double *vel_dev, int32_t *image_dev);
+
+/* Open (opening_kick = 1: forces + opening half kick) or, after a mid-run
+ * refresh re-uploaded the domain, continue (opening_kick = 0: list only) a run
+ * of at most `steps` NVE steps.                                             */
+int b2_dd_begin(b2_ctx *ctx, int64_t steps, double dt, int opening_kick);
+/* Enqueue one fused step for the owned particles.  The device float
+ * *vmax2_out_dev receives this rank's max |v|^2 of the step (0 if the step
+ * was a no-op because the list is stale or the budget is spent).            */
+int b2_dd_step(b2_ctx *ctx, float *vmax2_out_dev);
+/* Settle the step with the GLOBAL max |v|^2 (device float): advances the
+ * step count and the displacement bound, flips the position buffers, raises
+ * the refresh flag — identically on every rank.                             */
+int b2_dd_commit(b2_ctx *ctx, const float *gvmax2_dev);
+/* Synchronise and report progress.                                          */
+int b2_dd_poll(b2_ctx *ctx, int64_t *steps_done, int *need_refresh);
+/* Close the run: forces of the final configuration, closing half kick.      */
+int b2_dd_end(b2_ctx *ctx);
+/* Halo: gather current positions of the particles with the given LOCAL ids
+ * (upload order) as 3 doubles each / scatter received ones into the ghosts
+ * with local ids first_id .. first_id + n - 1.                              */
+int b2_dd_pack(b2_ctx *ctx, const int32_t *ids_dev, int64_t n, double *out_dev);
+int b2_dd_unpack(b2_ctx *ctx, int64_t first_id, int64_t n, const double *in_dev);
+
 /* Measurement aid (nothing like it in the reference, whose only timer is the
  * wall-clock TSP of simulation/core.py:286-306): with profiling on,
  * b2_run_nve brackets the step kernels and the list-refresh pipeline with

@@ -35,6 +35,8 @@
 #endif
 
 #define MAXSP 8
+#define TYPE(c, i) ((c)->spe[i] & 0xff)
+#define GHOST(c, i) (((c)->spe[i] & B2_GHOST) != 0)
 
 struct b2_ctx {
     int precision;
@@ -62,6 +64,10 @@ struct b2_ctx {
     double *mvel;
     int min_resume, min_method, m_npos, m_has_prev;
     double m_dt, m_alpha, m_dt0;
+    /* domain decomposition */
+    double dd_dt;
+    int64_t dd_steps, dd_target;
+    int dd_halt;
     char err[512];
 };
 
@@ -190,7 +196,7 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     if (!c->have_box) return fail(c, B2_ESTATE, "b2_upload: call b2_set_box first");
     if (!c->have_table) return fail(c, B2_ESTATE, "b2_upload: call b2_set_pair_table first");
     for (int64_t i = 0; i < n; i++) {
-        if (species[i] < 0 || species[i] >= c->nsp)
+        if (species[i] < 0 || (species[i] & ~B2_GHOST) >= c->nsp)
             return fail(c, B2_EINVAL, "b2_upload: species id outside the pair table");
         if (mass && !(mass[i] > 0.0)) return fail(c, B2_EINVAL, "b2_upload: mass must be > 0");
     }
@@ -300,7 +306,7 @@ static inline int in_list32(const double *xi, const double *xj, const double *ct
 
 static inline int in_list(const b2_ctx *c, int64_t i, int64_t j)
 {
-    int a = c->spe[i] * c->nsp + c->spe[j];
+    int a = TYPE(c, i) * c->nsp + TYPE(c, j);
     if (c->precision == B2_FP64) {
         double rl = c->rcut[a] + c->skin;
         return in_list64(c->pos + 3 * i, c->pos + 3 * j, c->side, rl * rl);
@@ -377,7 +383,9 @@ static int build_list(b2_ctx *c)
         for (int64_t i = 0; i < n; i++) {
             int64_t cnt = 0;
             int32_t *out = pass ? c->nbr + c->row[i] : NULL;
-            if (cells_ok) {
+            if (GHOST(c, i)) {
+                /* a ghost acts as a neighbour but owns no row */
+            } else if (cells_ok) {
                 for (int dz = -1; dz <= 1; dz++)
                     for (int dy = -1; dy <= 1; dy++)
                         for (int dx = -1; dx <= 1; dx++) {
@@ -419,12 +427,12 @@ static int compute_forces(b2_ctx *c, const double *pos, double *frc, double *pe,
 #pragma omp parallel for schedule(static) reduction(+ : e_tot, w_tot, s[:9])
     for (int64_t i = 0; i < n; i++) {
         const double *xi = pos + 3 * i;
-        int ti = c->spe[i];
+        int ti = TYPE(c, i);
         double fx = 0, fy = 0, fz = 0, ei = 0, wi = 0;
         double si[9] = {0};
         for (int64_t k = c->row[i]; k < c->row[i + 1]; k++) {
             int64_t j = c->nbr[k];
-            int a = ti * c->nsp + c->spe[j];
+            int a = ti * c->nsp + TYPE(c, j);
             double dx = xi[0] - pos[3 * j], dy = xi[1] - pos[3 * j + 1], dz = xi[2] - pos[3 * j + 2];
             dx = dx - rint(dx / c->side[0]) * c->side[0];
             dy = dy - rint(dy / c->side[1]) * c->side[1];
@@ -515,6 +523,7 @@ int b2_thermo(b2_ctx *c, double out[B2_T_LEN])
     for (int k = 0; k < B2_T_LEN; k++) out[k] = 0.0;
     double kin = 0, f2 = 0, px = 0, py = 0, pz = 0, mt = 0, msd = 0;
     for (int64_t i = 0; i < c->n; i++) {
+        if (GHOST(c, i)) continue;
         const double *v = c->vel + 3 * i, *f = c->frc + 3 * i;
         double m = c->mass[i];
         kin += 0.5 * m * ((v[0] * v[0] + v[1] * v[1]) + v[2] * v[2]);
@@ -579,6 +588,7 @@ int b2_run_nve(b2_ctx *c, int64_t steps, double dt)
 #pragma omp parallel for schedule(static) reduction(max : vmax2)
         for (int64_t i = 0; i < n; i++) {
             double *v = c->vel + 3 * i, *x = c->pos + 3 * i;
+            if (GHOST(c, i)) continue;
             for (int d = 0; d < 3; d++) {
                 v[d] += dt * c->frc[3 * i + d] / c->mass[i];
                 x[d] += dt * v[d];
@@ -775,4 +785,112 @@ int b2_kinetic_static(const void *vel_mass_dev, int64_t n, int precision, void *
 {
     (void)vel_mass_dev; (void)n; (void)precision; (void)cuda_stream; (void)out_dev;
     return fail(NULL, B2_EUNSUPPORTED, "b2_kinetic_static takes device pointers; the CPU oracle has none");
+}
+
+/* ---- domain decomposition primitives: the "device" of the oracle is the host ---- */
+int b2_upload_device(b2_ctx *c, int64_t n, const double *pos, const double *vel, const int32_t *species,
+                     const double *mass)
+{
+    return b2_upload(c, n, pos, vel, species, mass);
+}
+
+int b2_download_device(b2_ctx *c, double *pos, double *vel, int32_t *image)
+{
+    return b2_download(c, pos, vel, image);
+}
+
+int b2_dd_begin(b2_ctx *c, int64_t steps, double dt, int opening_kick)
+{
+    int rc = ensure_ready(c, "b2_dd_begin");
+    if (rc) return rc;
+    c->dd_dt = dt;
+    c->dd_steps = 0;
+    c->dd_target = steps;
+    c->min_resume = 0;
+    if (opening_kick) {
+        if ((rc = ensure_forces(c)) != B2_OK) return rc;
+        for (int64_t i = 0; i < c->n; i++)
+            for (int d = 0; d < 3; d++) c->vel[3 * i + d] -= (0.5 * dt) * c->frc[3 * i + d] / c->mass[i];
+    } else if (!c->list_valid && (rc = build_list(c)) != B2_OK) {
+        return rc;
+    }
+    c->dd_halt = 0;
+    return B2_OK;
+}
+
+int b2_dd_step(b2_ctx *c, float *vmax2)
+{
+    int rc = ensure_ready(c, "b2_dd_step");
+    if (rc) return rc;
+    if (!vmax2) return fail(c, B2_EINVAL, "b2_dd_step: NULL argument");
+    *vmax2 = 0.f;
+    if (c->dd_halt || c->dd_steps >= c->dd_target) return B2_OK;
+    double dt = c->dd_dt, vmax2v = 0.0;
+    compute_forces(c, c->pos, c->frc, NULL, NULL, NULL, NULL, NULL);
+    for (int64_t i = 0; i < c->n; i++) {
+        double *v = c->vel + 3 * i, *x = c->pos + 3 * i;
+        if (GHOST(c, i)) continue;
+        for (int d = 0; d < 3; d++) {
+            v[d] += dt * c->frc[3 * i + d] / c->mass[i];
+            x[d] += dt * v[d];
+        }
+        fold3(c, x, c->img + 3 * i);
+        double v2 = (v[0] * v[0] + v[1] * v[1]) + v[2] * v[2];
+        if (v2 > vmax2v) vmax2v = v2;
+    }
+    *vmax2 = (float)vmax2v;
+    if ((double)*vmax2 < vmax2v) *vmax2 = nextafterf(*vmax2, INFINITY);   /* round up */
+    c->forces_valid = 0;
+    return B2_OK;
+}
+
+int b2_dd_commit(b2_ctx *c, const float *gvmax2)
+{
+    int rc = ensure_ready(c, "b2_dd_commit");
+    if (rc) return rc;
+    if (c->dd_halt || c->dd_steps >= c->dd_target) return B2_OK;
+    c->disp_bound += c->dd_dt * sqrt((double)*gvmax2) * (1.0 + 1e-6);
+    c->dd_steps++;
+    c->steps_total++;
+    if (c->disp_bound > 0.5 * c->skin) { c->dd_halt = 1; c->list_valid = 0; }
+    return B2_OK;
+}
+
+int b2_dd_poll(b2_ctx *c, int64_t *steps_done, int *need_refresh)
+{
+    int rc = ensure_ready(c, "b2_dd_poll");
+    if (rc) return rc;
+    if (steps_done) *steps_done = c->dd_steps;
+    if (need_refresh) *need_refresh = c->dd_halt;
+    return B2_OK;
+}
+
+int b2_dd_end(b2_ctx *c)
+{
+    int rc = ensure_ready(c, "b2_dd_end");
+    if (rc) return rc;
+    c->forces_valid = 0;
+    if ((rc = ensure_forces(c)) != B2_OK) return rc;
+    for (int64_t i = 0; i < c->n; i++)
+        for (int d = 0; d < 3; d++) c->vel[3 * i + d] += (0.5 * c->dd_dt) * c->frc[3 * i + d] / c->mass[i];
+    return B2_OK;
+}
+
+int b2_dd_pack(b2_ctx *c, const int32_t *ids, int64_t n, double *out)
+{
+    int rc = ensure_ready(c, "b2_dd_pack");
+    if (rc) return rc;
+    for (int64_t k = 0; k < n; k++)
+        for (int d = 0; d < 3; d++) out[3 * k + d] = c->pos[3 * (int64_t)ids[k] + d] - c->center[d];
+    return B2_OK;
+}
+
+int b2_dd_unpack(b2_ctx *c, int64_t first_id, int64_t n, const double *in)
+{
+    int rc = ensure_ready(c, "b2_dd_unpack");
+    if (rc) return rc;
+    if (first_id < 0 || first_id + n > c->n) return fail(c, B2_EINVAL, "b2_dd_unpack: id range outside the resident particles");
+    for (int64_t k = 0; k < n; k++)
+        for (int d = 0; d < 3; d++) c->pos[3 * (first_id + k) + d] = in[3 * k + d] + c->center[d];
+    return B2_OK;
 }

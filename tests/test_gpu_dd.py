@@ -1,0 +1,70 @@
+"""
+Slab decomposition on the real engine: two ranks, CUDA tensors, one process per
+rank.  With two GPUs the ranks talk NCCL (the product path); on a single-GPU box
+both ranks share GPU 0 and the same code runs over gloo — the engine-side
+primitives (ghost flag, pack / unpack, global-max commit, device upload) are the
+CUDA ones either way.  The decomposed run must match one engine holding the
+whole system.
+"""
+import os
+import sys
+
+import numpy
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from test_dd_gloo import global_system, ROOT
+
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, port, steps, precision, backend, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    ngpu = torch.cuda.device_count()
+    torch.cuda.set_device(rank % ngpu)
+    dist.init_process_group(backend, rank=rank, world_size=world)
+    from atooms_b200.dd import SlabDomain
+    pos, vel, spe, side = global_system()
+    slab = numpy.clip(numpy.floor((pos[:, 0] / side[0] + 0.5) * world).astype(int), 0, world - 1)
+    mine = numpy.nonzero(slab == rank)[0]
+    dom = SlabDomain(pos[mine], vel[mine], spe[mine], side, model='kob_andersen', dt=0.002, skin=0.3,
+                     precision=precision, gid=mine)
+    assert dom.engine.lib.name == 'cuda-sm_100a'
+    t0 = dom.thermo()
+    dom.run(steps)
+    t1 = dom.thermo()
+    gpos, gvel, gimg = dom.gather()
+    if rank == 0:
+        numpy.savez(out, pos=gpos, vel=gvel, img=gimg, e0=t0['kinetic'] + t0['potential'],
+                    e1=t1['kinetic'] + t1['potential'], n=t1['n'], refreshes=dom.refreshes, virial=t1['virial'])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+def test_two_rank_slab_run_on_cuda(precision, tmp_path, cuda_lib):
+    from conftest import make_engine
+    from oracle import oracle_np as onp
+    steps, world = 120, 2
+    backend = 'nccl' if torch.cuda.device_count() >= 2 else 'gloo'
+    out = str(tmp_path / 'dd.npz')
+    port = 29500 + (os.getpid() + precision) % 2000
+    mp.spawn(_worker, args=(world, port, steps, precision, backend, out), nprocs=world, join=True)
+    got = numpy.load(out)
+    pos, vel, spe, side = global_system()
+    ref = make_engine(cuda_lib, {'position': pos, 'velocity': vel, 'species': spe, 'side': side,
+                                 'center': numpy.zeros(3)}, onp.kob_andersen(), precision)
+    e0 = ref.thermo()
+    ref.run_nve(steps, 0.002)
+    rpos, rvel, rimg = ref.download(image=True)
+    e1 = ref.thermo()
+    tol = 1e-8 if precision == 64 else 2e-4
+    assert int(got['n']) == len(spe) and int(got['refreshes']) >= 3
+    assert abs(got['e0'] - (e0['kinetic'] + e0['potential'])) < 1e-9 * abs(got['e0'])
+    assert abs(got['e1'] - (e1['kinetic'] + e1['potential'])) < (1e-8 if precision == 64 else 1e-5) * abs(got['e1'])
+    unf_got, unf_ref = got['pos'] + got['img'] * side, rpos + rimg * side
+    assert numpy.abs(unf_got - unf_ref).max() < tol
+    assert numpy.abs(got['vel'] - rvel).max() < 10 * tol
