@@ -102,6 +102,15 @@ class Library(object):
             fn = getattr(self.dll, name)   # AttributeError if the symbol is missing
             fn.restype = restype
             fn.argtypes = argtypes
+        # optional NCCL fast path (include/atooms_b200_nccl.h): CUDA library only
+        self.has_nccl = hasattr(self.dll, 'b2_nccl_run')
+        if self.has_nccl:
+            self.dll.b2_nccl_unique_id.argtypes = [ctypes.c_char_p]
+            self.dll.b2_nccl_init.argtypes = [_vp, ctypes.c_char_p, _int, _int]
+            self.dll.b2_nccl_set_halo.argtypes = [_vp, _vp, _i64, _vp, _i64, _i64, _i64]
+            self.dll.b2_nccl_run.argtypes = [_vp, _i64]
+            for name in ('b2_nccl_unique_id', 'b2_nccl_init', 'b2_nccl_set_halo', 'b2_nccl_run'):
+                getattr(self.dll, name).restype = _int
         version = self.dll.b2_abi_version()
         if version != ABI_VERSION:
             raise OSError('atooms_b200: %s has ABI version %d, expected %d' % (path, version, ABI_VERSION))
@@ -367,3 +376,19 @@ class Engine(object):
 
     def dd_unpack(self, first_id, n, in_ptr):
         self._call('b2_dd_unpack', int(first_id), int(n), _vp(in_ptr or 0))
+
+    # -- NCCL fast path (CUDA library only) ----------------------------------------------------
+    def nccl_unique_id(self):
+        buf = ctypes.create_string_buffer(128)
+        self.lib.check(self.lib.dll.b2_nccl_unique_id(buf))
+        return buf.raw
+
+    def nccl_init(self, unique_id, rank, nranks):
+        self._call('b2_nccl_init', ctypes.c_char_p(bytes(unique_id)), int(rank), int(nranks))
+
+    def nccl_set_halo(self, send_l_ptr, n_send_l, send_r_ptr, n_send_r, n_ghost_l, n_ghost_r):
+        self._call('b2_nccl_set_halo', _vp(send_l_ptr or 0), int(n_send_l), _vp(send_r_ptr or 0), int(n_send_r),
+                   int(n_ghost_l), int(n_ghost_r))
+
+    def nccl_run(self, count):
+        self._call('b2_nccl_run', int(count))

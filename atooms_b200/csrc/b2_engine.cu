@@ -5,6 +5,9 @@
 #include "b2_neigh.cuh"
 #include "b2_force.cuh"
 
+#include <dlfcn.h>
+#include <nccl.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
@@ -37,6 +40,14 @@ struct b2_ctx {
     int *orig = nullptr, *torig = nullptr;
     int *inv = nullptr;        // slot of each local id (inverse of orig); used by the halo pack / unpack
     double dd_dt = 0;
+    // NCCL fast path of the domain decomposition (b2_nccl_*)
+    ncclComm_t comm = nullptr;
+    int nranks = 1, myrank = 0, left = 0, right = 0;
+    const int *send_l = nullptr, *send_r = nullptr;   // caller-owned device arrays of local ids
+    int n_send_l = 0, n_send_r = 0, n_ghost_l = 0, n_ghost_r = 0;
+    double *halo_buf = nullptr;                       // out_l | out_r | in_l | in_r
+    size_t halo_cap = 0;
+    float *dd_vmax = nullptr;
     int *img = nullptr;        // [3n] by original id
     double *ref = nullptr;     // [3n] by original id, unfolded, relative to centre
     // neighbour search
@@ -66,6 +77,21 @@ struct b2_ctx {
 static char g_err[512] = "";
 static uint64_t g_const_owner[64];      // per device: serial of the ctx whose table is resident
 static uint64_t g_serial = 0;
+
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+
 
 static int fail(b2_ctx *c, int code, const char *fmt, ...)
 {
@@ -981,11 +1007,12 @@ int b2_destroy(b2_ctx *c)
     if (!c) return B2_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv,
+    void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv, c->halo_buf, c->dd_vmax,
                     c->img, c->ref, c->mvel, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i};
     for (void *p : ptrs)
         if (p) cudaFree(p);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     if (c->hctl) cudaFreeHost(c->hctl);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -1393,3 +1420,133 @@ extern "C" int b2_kinetic_static(const void *vel_mass_dev, int64_t n, int precis
         return fail(nullptr, B2_ECUDA, "b2_kinetic_static: launch failed: %s", cudaGetErrorString(e));
     return B2_OK;
 }
+
+// ---------------------------------------------------------------------------
+// NCCL fast path of the slab decomposition: the whole per-step sequence
+//   step kernel -> all-reduce(max) of one float -> commit -> pack -> ring
+//   send/recv -> unpack
+// is enqueued from C on the context's stream, `count` steps per call, so the
+// host pays microseconds per step instead of a Python round trip per collective.
+// NCCL is resolved at run time (dlopen): the library has no link-time
+// dependency on it, and inside a torch process it picks up the NCCL torch loaded.
+// ---------------------------------------------------------------------------
+static int load_nccl(b2_ctx *c)
+{
+    if (g_nccl.handle) return B2_OK;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(c, B2_EUNSUPPORTED, "NCCL not available: %s", dlerror());
+#define B2_SYM(name)                                                                   \
+    *(void **)(&g_nccl.name) = dlsym(h, "nccl" #name);                                 \
+    if (!g_nccl.name) return fail(c, B2_EUNSUPPORTED, "NCCL symbol nccl" #name " not found");
+    B2_SYM(GetUniqueId) B2_SYM(CommInitRank) B2_SYM(CommDestroy) B2_SYM(AllReduce) B2_SYM(Send) B2_SYM(Recv)
+    B2_SYM(GroupStart) B2_SYM(GroupEnd) B2_SYM(GetErrorString)
+#undef B2_SYM
+    g_nccl.handle = h;
+    return B2_OK;
+}
+
+#define NC(call)                                                                          \
+    do {                                                                                  \
+        ncclResult_t r_ = (call);                                                         \
+        if (r_ != ncclSuccess)                                                            \
+            return fail(c, B2_ECUDA, "%s failed: %s", #call, g_nccl.GetErrorString(r_));  \
+    } while (0)
+
+template <typename R> struct ImplDD {
+    typedef typename Vec4<R>::type V4;
+    typedef typename Pos4<R>::type P4;
+    static int run(b2_ctx *c, int64_t count)
+    {
+        const int n = (int)c->n;
+        // halo buffers: [out_l | out_r | in_l | in_r], each at least one record so that no message is empty
+        const size_t sl = std::max(c->n_send_l, 1), sr = std::max(c->n_send_r, 1);
+        const size_t gl = std::max(c->n_ghost_l, 1), gr = std::max(c->n_ghost_r, 1);
+        const size_t need = 3 * (sl + sr + gl + gr);
+        if (need > c->halo_cap) {
+            if (c->halo_buf) cudaFree(c->halo_buf);
+            c->halo_buf = nullptr;
+            CU(cudaMalloc((void **)&c->halo_buf, (need + need / 4) * sizeof(double)));
+            CU(cudaMemsetAsync(c->halo_buf, 0, (need + need / 4) * sizeof(double), c->stream));
+            c->halo_cap = need + need / 4;
+        }
+        if (!c->dd_vmax) {
+            CU(cudaMalloc((void **)&c->dd_vmax, 2 * sizeof(float)));
+            CU(cudaMemsetAsync(c->dd_vmax, 0, 2 * sizeof(float), c->stream));
+        }
+        double *out_l = c->halo_buf, *out_r = out_l + 3 * sl, *in_l = out_r + 3 * sr, *in_r = in_l + 3 * gl;
+        const int n_own = n - c->n_ghost_l - c->n_ghost_r;
+        for (int64_t k = 0; k < count; k++) {
+            int rc = Impl<R>::dd_step(c, c->dd_vmax);
+            if (rc) return rc;
+            NC(g_nccl.AllReduce(c->dd_vmax, c->dd_vmax, 1, ncclFloat32, ncclMax, c->comm, c->stream));
+            LAUNCH(k_dd_commit, 1, 1, c->ctl, c->dd_vmax, c->dd_dt);
+            if ((rc = Impl<R>::dd_pack(c, c->send_l, c->n_send_l, out_l))) return rc;
+            if ((rc = Impl<R>::dd_pack(c, c->send_r, c->n_send_r, out_r))) return rc;
+            // posting order [to-left, to-right] / [from-right, from-left]: unambiguous on a 2-rank ring
+            NC(g_nccl.GroupStart());
+            NC(g_nccl.Send(out_l, 3 * sl, ncclFloat64, c->left, c->comm, c->stream));
+            NC(g_nccl.Send(out_r, 3 * sr, ncclFloat64, c->right, c->comm, c->stream));
+            NC(g_nccl.Recv(in_r, 3 * gr, ncclFloat64, c->right, c->comm, c->stream));
+            NC(g_nccl.Recv(in_l, 3 * gl, ncclFloat64, c->left, c->comm, c->stream));
+            NC(g_nccl.GroupEnd());
+            if ((rc = Impl<R>::dd_unpack(c, n_own, c->n_ghost_l, in_l))) return rc;
+            if ((rc = Impl<R>::dd_unpack(c, n_own + c->n_ghost_l, c->n_ghost_r, in_r))) return rc;
+        }
+        return B2_OK;
+    }
+};
+
+extern "C" {
+
+int b2_nccl_unique_id(char out[128])
+{
+    b2_ctx *c = nullptr;
+    int rc = load_nccl(nullptr);
+    if (rc) return rc;
+    ncclUniqueId id;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    NC(g_nccl.GetUniqueId(&id));
+    memcpy(out, &id, 128);
+    return B2_OK;
+}
+
+int b2_nccl_init(b2_ctx *c, const char id[128], int rank, int nranks)
+{
+    if (!c || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(c, B2_EINVAL, "b2_nccl_init: bad argument");
+    int rc = load_nccl(c);
+    if (rc) return rc;
+    if ((rc = bind_device(c))) return rc;
+    if (c->comm) { g_nccl.CommDestroy(c->comm); c->comm = nullptr; }
+    ncclUniqueId uid;
+    memcpy(&uid, id, 128);
+    NC(g_nccl.CommInitRank(&c->comm, nranks, uid, rank));
+    c->nranks = nranks;
+    c->myrank = rank;
+    c->left = (rank + nranks - 1) % nranks;
+    c->right = (rank + 1) % nranks;
+    return B2_OK;
+}
+
+int b2_nccl_set_halo(b2_ctx *c, const int32_t *send_l_dev, int64_t n_send_l, const int32_t *send_r_dev,
+                     int64_t n_send_r, int64_t n_ghost_l, int64_t n_ghost_r)
+{
+    NEED_PARTICLES("b2_nccl_set_halo");
+    if (n_send_l < 0 || n_send_r < 0 || n_ghost_l < 0 || n_ghost_r < 0 || n_ghost_l + n_ghost_r > c->n)
+        return fail(c, B2_EINVAL, "b2_nccl_set_halo: bad counts");
+    c->send_l = send_l_dev; c->send_r = send_r_dev;
+    c->n_send_l = (int)n_send_l; c->n_send_r = (int)n_send_r;
+    c->n_ghost_l = (int)n_ghost_l; c->n_ghost_r = (int)n_ghost_r;
+    return B2_OK;
+}
+
+int b2_nccl_run(b2_ctx *c, int64_t count)
+{
+    NEED_PARTICLES("b2_nccl_run");
+    if (!c->comm) return fail(c, B2_ESTATE, "b2_nccl_run: call b2_nccl_init first");
+    if (!(c->dd_dt > 0.0)) return fail(c, B2_ESTATE, "b2_nccl_run: call b2_dd_begin first");
+    if (count < 0) return fail(c, B2_EINVAL, "b2_nccl_run: count >= 0 required");
+    return c->precision == B2_FP32 ? ImplDD<float>::run(c, count) : ImplDD<double>::run(c, count);
+}
+
+}  // extern "C"

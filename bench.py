@@ -209,6 +209,7 @@ def workload_config(n, inner, world=1, halo_bytes=0):
                                 '(NCCL send/recv) + 4-byte all_reduce per step, migration at list refresh'
                                 % (world, world))
         cfg['halo_bytes_per_step_per_gpu'] = int(halo_bytes)
+        cfg['comm'] = 'NCCL send/recv + all-reduce enqueued from C (b2_nccl_run)'
     return cfg
 
 
@@ -299,6 +300,7 @@ def main():
             if sampler:
                 clocks = sampler.stop()
             launches = dom.engine.stats()['launches'] - l0
+            refreshes_timed = dom.refreshes - r0
             th = dom.thermo()
             ntot = th['n']
             value = ntot * INNER * args.steps / (ms * 1e-3)
@@ -326,11 +328,11 @@ def main():
             e2e_s = max_over_ranks(time.perf_counter() - t0)
             results[precision] = dict(value=value, ms=ms, launches=launches,
                                       prof={'ms_steps': 0.0, 'ms_refresh': 0.0, 'step_launches': 0,
-                                            'steps': INNER * args.steps, 'refreshes': dom.refreshes - r0},
+                                            'steps': INNER * args.steps, 'refreshes': refreshes_timed},
                                       e2e=ntot * INNER * e2e_steps / e2e_s, e2e_steps=e2e_steps,
                                       stats=dom.engine.stats(), energy=(th['kinetic'] + th['potential']) / ntot,
                                       h2d=h2d // e2e_steps, d2h=d2h // e2e_steps, ntot=ntot,
-                                      halo_bytes=dom.halo_bytes_per_step)
+                                      halo_bytes=dom.halo_bytes_per_step, fast_comm=dom._fast)
             dom.close()
             continue
         eng = make_engine(lib, precision, pos, spe, side, vel, device=local_rank)

@@ -1,0 +1,39 @@
+/*
+ * atooms_b200_nccl.h — NCCL fast path of the slab decomposition (CUDA library only).
+ *
+ * No counterpart in the reference (it has no domain decomposition and no data
+ * collectives).  The generic path in atooms_b200/dd.py moves
+ * the halo with torch.distributed from Python, one round trip per collective;
+ * these entry points enqueue the same per-step sequence
+ *     fused step kernel -> ncclAllReduce(max, 1 float) -> commit
+ *     -> pack -> ncclSend/ncclRecv with the two ring neighbours -> unpack
+ * from C on the context's stream.  NCCL is resolved with dlopen at run time.
+ */
+#ifndef ATOOMS_B200_NCCL_H
+#define ATOOMS_B200_NCCL_H
+
+#include "atooms_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* 128-byte ncclUniqueId, to be created on one rank and broadcast by the caller. */
+int b2_nccl_unique_id(char out[128]);
+/* Create this context's communicator (collective over all ranks).               */
+int b2_nccl_init(b2_ctx *ctx, const char id[128], int rank, int nranks);
+/* Describe the halo of the resident domain: device arrays (caller-owned, kept
+ * alive until the next call) of the LOCAL ids sent to the left / right ring
+ * neighbour each step, and how many ghosts arrive from the left / right; ghosts
+ * are the last n_ghost_l + n_ghost_r local ids, left block first.               */
+int b2_nccl_set_halo(b2_ctx *ctx, const int32_t *send_l_dev, int64_t n_send_l,
+                     const int32_t *send_r_dev, int64_t n_send_r,
+                     int64_t n_ghost_l, int64_t n_ghost_r);
+/* Enqueue `count` guarded steps with their communication (after b2_dd_begin);
+ * returns without waiting.  Every rank must call it with the same count.       */
+int b2_nccl_run(b2_ctx *ctx, int64_t count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -20,7 +20,7 @@ from test_dd_gloo import global_system, ROOT
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, port, steps, precision, backend, out):
+def _worker(rank, world, port, steps, precision, backend, fast, out):
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
     ngpu = torch.cuda.device_count()
@@ -31,8 +31,8 @@ def _worker(rank, world, port, steps, precision, backend, out):
     slab = numpy.clip(numpy.floor((pos[:, 0] / side[0] + 0.5) * world).astype(int), 0, world - 1)
     mine = numpy.nonzero(slab == rank)[0]
     dom = SlabDomain(pos[mine], vel[mine], spe[mine], side, model='kob_andersen', dt=0.002, skin=0.3,
-                     precision=precision, gid=mine)
-    assert dom.engine.lib.name == 'cuda-sm_100a'
+                     precision=precision, gid=mine, fast_comm=fast)
+    assert dom.engine.lib.name == 'cuda-sm_100a' and dom._fast == fast
     t0 = dom.thermo()
     dom.run(steps)
     t1 = dom.thermo()
@@ -44,15 +44,18 @@ def _worker(rank, world, port, steps, precision, backend, out):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize('fast', [False, True], ids=['torch.distributed', 'nccl-in-C'])
 @pytest.mark.parametrize('precision', [64, 32])
-def test_two_rank_slab_run_on_cuda(precision, tmp_path, cuda_lib):
+def test_two_rank_slab_run_on_cuda(precision, fast, tmp_path, cuda_lib):
     from conftest import make_engine
     from oracle import oracle_np as onp
     steps, world = 120, 2
     backend = 'nccl' if torch.cuda.device_count() >= 2 else 'gloo'
+    if fast and backend != 'nccl':
+        pytest.skip('the NCCL fast path needs two GPUs')
     out = str(tmp_path / 'dd.npz')
-    port = 29500 + (os.getpid() + precision) % 2000
-    mp.spawn(_worker, args=(world, port, steps, precision, backend, out), nprocs=world, join=True)
+    port = 29500 + (os.getpid() + precision + 7 * int(fast)) % 2000
+    mp.spawn(_worker, args=(world, port, steps, precision, backend, fast, out), nprocs=world, join=True)
     got = numpy.load(out)
     pos, vel, spe, side = global_system()
     ref = make_engine(cuda_lib, {'position': pos, 'velocity': vel, 'species': spe, 'side': side,
