@@ -11,7 +11,7 @@ import os
 
 import numpy
 
-__all__ = ['Library', 'Engine', 'load', 'library_path', 'B2Error',
+__all__ = ['Library', 'Engine', 'Batch', 'load', 'library_path', 'B2Error',
            'FP32', 'FP64', 'ENERGY', 'FORCES', 'VIRIAL', 'STRESS', 'MIN_SD', 'MIN_FIRE',
            'SYMBOLS', 'kinetic_static', 'STATIC_MAX_PARTICLES']
 
@@ -71,6 +71,12 @@ SYMBOLS = {
     'b2_dd_end': (_int, [_vp]),
     'b2_dd_pack': (_int, [_vp, _vp, _i64, _vp]),
     'b2_dd_unpack': (_int, [_vp, _i64, _i64, _vp]),
+    'b2_batch_create': (_int, [_int, _int, ctypes.POINTER(_vp)]),
+    'b2_batch_destroy': (_int, [_vp]),
+    'b2_batch_set_model': (_int, [_vp, _c_dp, _int, _c_dp, _c_dp, _c_dp, _int]),
+    'b2_batch_upload': (_int, [_vp, _i64, _int, _c_dp, _c_ip, _c_dp]),
+    'b2_batch_minimize': (_int, [_vp, _int, _i64, _dbl, _dbl, _c_lp, ctypes.POINTER(_int), _c_dp, _c_dp, _c_dp]),
+    'b2_batch_download': (_int, [_vp, _c_dp, _c_dp]),
 }
 
 
@@ -392,3 +398,65 @@ class Engine(object):
 
     def nccl_run(self, count):
         self._call('b2_nccl_run', int(count))
+
+
+class Batch(object):
+
+    """An ensemble of small independent replicas sharing cell and pair table
+    (b2_batch_*): one thread block per replica, all pairs, whole minimisation
+    in one launch."""
+
+    def __init__(self, side, eps, sigma, rcut, shifted=True, precision=FP64, device=0, library=None):
+        self.lib = library if library is not None else load()
+        self.precision = int(precision)
+        handle = _vp()
+        self.lib.check(self.lib.dll.b2_batch_create(int(device), self.precision, ctypes.byref(handle)))
+        self._h = handle
+        side = numpy.ascontiguousarray(side, dtype=numpy.float64)
+        eps = numpy.atleast_2d(numpy.ascontiguousarray(eps, dtype=numpy.float64))
+        sigma = numpy.atleast_2d(numpy.ascontiguousarray(sigma, dtype=numpy.float64))
+        rcut = numpy.atleast_2d(numpy.ascontiguousarray(rcut, dtype=numpy.float64))
+        self._call('b2_batch_set_model', _dp(side), eps.shape[0], _dp(eps), _dp(sigma), _dp(rcut), int(bool(shifted)))
+        self.nrep = self.n = 0
+
+    def _call(self, name, *args):
+        if not self._h:
+            raise B2Error(-4, 'batch is closed')
+        self.lib.check(getattr(self.lib.dll, name)(self._h, *args))
+
+    def close(self):
+        h, self._h = getattr(self, '_h', None), None
+        if h:
+            self.lib.dll.b2_batch_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, position, species, mass=None):
+        """position (nrep, n, 3); species (n,) shared by all replicas or (nrep, n)."""
+        pos = numpy.ascontiguousarray(position, dtype=numpy.float64)
+        if pos.ndim != 3 or pos.shape[2] != 3:
+            raise ValueError('position must be (nrep, n, 3)')
+        nrep, n = pos.shape[:2]
+        spe = numpy.asarray(species, dtype=numpy.int32)
+        spe = numpy.ascontiguousarray(numpy.broadcast_to(spe, (nrep, n)))
+        m = None if mass is None else numpy.ascontiguousarray(numpy.broadcast_to(numpy.asarray(mass, dtype=numpy.float64), (nrep, n)))
+        self._call('b2_batch_upload', nrep, n, _dp(pos), _ip(spe), _dp(m))
+        self.nrep, self.n = nrep, n
+
+    def minimize(self, method, max_steps, dt, fn2_tol):
+        steps = numpy.zeros(self.nrep, dtype=numpy.int64)
+        conv = numpy.zeros(self.nrep, dtype=numpy.int32)
+        energy, fn2, virial = numpy.zeros(self.nrep), numpy.zeros(self.nrep), numpy.zeros(self.nrep)
+        self._call('b2_batch_minimize', int(method), int(max_steps), float(dt), float(fn2_tol),
+                   steps.ctypes.data_as(_c_lp), conv.ctypes.data_as(ctypes.POINTER(_int)), _dp(energy), _dp(fn2), _dp(virial))
+        return {'steps': steps, 'converged': conv.astype(bool), 'energy': energy, 'fn2': fn2, 'virial': virial}
+
+    def download(self, forces=False):
+        pos = numpy.empty((self.nrep, self.n, 3))
+        frc = numpy.empty((self.nrep, self.n, 3)) if forces else None
+        self._call('b2_batch_download', _dp(pos), _dp(frc))
+        return (pos, frc) if forces else pos

@@ -4,6 +4,7 @@
 #include "b2_common.cuh"
 #include "b2_neigh.cuh"
 #include "b2_force.cuh"
+#include "b2_batch.cuh"
 
 #include <dlfcn.h>
 #include <nccl.h>
@@ -1547,6 +1548,216 @@ int b2_nccl_run(b2_ctx *c, int64_t count)
     if (!(c->dd_dt > 0.0)) return fail(c, B2_ESTATE, "b2_nccl_run: call b2_dd_begin first");
     if (count < 0) return fail(c, B2_EINVAL, "b2_nccl_run: count >= 0 required");
     return c->precision == B2_FP32 ? ImplDD<float>::run(c, count) : ImplDD<double>::run(c, count);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Replica ensembles (b2_batch_*): one block per replica, see b2_batch.cuh
+// ---------------------------------------------------------------------------
+struct b2_batch {
+    int device = 0, precision = 64;
+    bool have_model = false;
+    double side[3] = {0, 0, 0};
+    PairConst pc;
+    uint64_t const_serial = 0;
+    int64_t nrep = 0;
+    int n = 0;
+    void *pos = nullptr, *frc = nullptr, *mass = nullptr;
+    double *stage = nullptr;
+    int *stage_i = nullptr;
+    long long *d_steps = nullptr;
+    int *d_conv = nullptr;
+    double *d_out = nullptr;     // energy | fn2 | virial
+    int64_t launches = 0;
+};
+
+template <typename R> struct BatchImpl {
+    typedef typename Vec4<R>::type V4;
+    typedef typename Pos4<R>::type P4;
+
+    static Box<R> box_of(const b2_batch *b)
+    {
+        b2_ctx tmp;
+        for (int d = 0; d < 3; d++) tmp.side[d] = b->side[d];
+        return make_box<R>(&tmp);
+    }
+
+    static int upload(b2_batch *b, int64_t nrep, int n, const double *pos, const int32_t *species, const double *mass)
+    {
+        b2_ctx *c = nullptr;
+        const size_t tot = (size_t)nrep * n;
+        void *old[] = {b->pos, b->frc, b->mass, b->stage, b->stage_i, b->d_steps, b->d_conv, b->d_out};
+        for (void *p : old) if (p) cudaFree(p);
+        b->pos = b->frc = b->mass = nullptr; b->stage = nullptr; b->stage_i = nullptr;
+        b->d_steps = nullptr; b->d_conv = nullptr; b->d_out = nullptr;
+        CU(cudaMalloc(&b->pos, std::max<size_t>(tot, 1) * sizeof(P4)));
+        CU(cudaMalloc(&b->frc, std::max<size_t>(tot, 1) * sizeof(V4)));
+        CU(cudaMalloc(&b->mass, std::max<size_t>(tot, 1) * sizeof(R)));
+        CU(cudaMalloc((void **)&b->stage, std::max<size_t>(tot, 1) * 4 * sizeof(double)));
+        CU(cudaMalloc((void **)&b->stage_i, std::max<size_t>(tot, 1) * sizeof(int)));
+        CU(cudaMalloc((void **)&b->d_steps, std::max<int64_t>(nrep, 1) * sizeof(long long)));
+        CU(cudaMalloc((void **)&b->d_conv, std::max<int64_t>(nrep, 1) * sizeof(int)));
+        CU(cudaMalloc((void **)&b->d_out, std::max<int64_t>(nrep, 1) * 3 * sizeof(double)));
+        b->nrep = nrep;
+        b->n = n;
+        if (tot == 0) return B2_OK;
+        CU(cudaMemcpy(b->stage, pos, tot * 3 * sizeof(double), cudaMemcpyHostToDevice));
+        if (mass) CU(cudaMemcpy(b->stage + 3 * tot, mass, tot * sizeof(double), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(b->stage_i, species, tot * sizeof(int), cudaMemcpyHostToDevice));
+        k_batch_ingest<R><<<cdiv(tot, 256), 256>>>(b->stage, mass ? b->stage + 3 * tot : nullptr, b->stage_i, (long long)tot,
+                                                  box_of(b), (P4 *)b->pos, (R *)b->mass);
+        b->launches++;
+        CU(cudaDeviceSynchronize());
+        return B2_OK;
+    }
+
+    static int minimize(b2_batch *b, int method, int64_t max_steps, double dt, double tol, int64_t *steps_done,
+                        int *converged, double *energy, double *fn2, double *virial)
+    {
+        b2_ctx *c = nullptr;
+        if (b->nrep == 0) return B2_OK;
+        if (g_const_owner[b->device] != b->const_serial) {
+            CU(cudaMemcpyToSymbol(g_pair, &b->pc, sizeof(PairConst)));
+            g_const_owner[b->device] = b->const_serial;
+        }
+        BatchArgs<R> a;
+        a.pos = (P4 *)b->pos;
+        a.vel0 = nullptr;
+        a.mass = (const R *)b->mass;
+        a.n = b->n;
+        a.nrep = (int)b->nrep;
+        a.box = box_of(b);
+        a.method = method == B2_MIN_FIRE ? MIN_MODE_FIRE : MIN_MODE_SD;
+        a.max_steps = max_steps;
+        a.dt = dt;
+        a.fn2_tol = tol;
+        a.steps_done = b->d_steps;
+        a.converged = b->d_conv;
+        a.energy = b->d_out;
+        a.fn2 = b->d_out + b->nrep;
+        a.virial = b->d_out + 2 * b->nrep;
+        a.frc = (V4 *)b->frc;
+        const int threads = (b->n + 31) / 32 * 32;
+        k_batch_minimize<R><<<(unsigned)b->nrep, threads, (size_t)b->n * sizeof(P4)>>>(a);
+        b->launches++;
+        CU(cudaGetLastError());
+        std::vector<long long> hs((size_t)b->nrep);
+        CU(cudaMemcpy(hs.data(), b->d_steps, b->nrep * sizeof(long long), cudaMemcpyDeviceToHost));
+        for (int64_t r = 0; r < b->nrep; r++) if (steps_done) steps_done[r] = hs[r];
+        if (converged) CU(cudaMemcpy(converged, b->d_conv, b->nrep * sizeof(int), cudaMemcpyDeviceToHost));
+        if (energy) CU(cudaMemcpy(energy, b->d_out, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
+        if (fn2) CU(cudaMemcpy(fn2, b->d_out + b->nrep, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
+        if (virial) CU(cudaMemcpy(virial, b->d_out + 2 * b->nrep, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
+        return B2_OK;
+    }
+
+    static int download(b2_batch *b, double *pos, double *forces)
+    {
+        b2_ctx *c = nullptr;
+        const size_t tot = (size_t)b->nrep * b->n;
+        if (tot == 0) return B2_OK;
+        k_batch_export<R><<<cdiv(tot, 256), 256>>>((const P4 *)b->pos, (const V4 *)b->frc, (long long)tot, box_of(b),
+                                                  pos ? b->stage : nullptr, nullptr);
+        b->launches++;
+        // the staging buffer is reused: positions first, forces in a second trip
+        if (pos) CU(cudaMemcpy(pos, b->stage, tot * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+        if (forces) {
+            k_batch_export<R><<<cdiv(tot, 256), 256>>>((const P4 *)b->pos, (const V4 *)b->frc, (long long)tot, box_of(b),
+                                                      nullptr, b->stage);
+            b->launches++;
+            CU(cudaMemcpy(forces, b->stage, tot * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+        }
+        return B2_OK;
+    }
+};
+
+extern "C" {
+
+int b2_batch_create(int device, int precision, b2_batch **out)
+{
+    if (!out) return fail(nullptr, B2_EINVAL, "b2_batch_create: out is NULL");
+    *out = nullptr;
+    if (precision != B2_FP32 && precision != B2_FP64)
+        return fail(nullptr, B2_EINVAL, "b2_batch_create: precision must be 32 or 64");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, B2_ENOCUDA, "b2_batch_create: no usable CUDA device (%s); this library has no CPU path",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= ndev || device >= 64) return fail(nullptr, B2_EINVAL, "b2_batch_create: bad device");
+    b2_batch *b = new b2_batch();
+    b->device = device;
+    b->precision = precision;
+    memset(&b->pc, 0, sizeof(PairConst));
+    *out = b;
+    return B2_OK;
+}
+
+int b2_batch_destroy(b2_batch *b)
+{
+    if (!b) return B2_OK;
+    cudaSetDevice(b->device);
+    void *ptrs[] = {b->pos, b->frc, b->mass, b->stage, b->stage_i, b->d_steps, b->d_conv, b->d_out};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    if (g_const_owner[b->device] == b->const_serial) g_const_owner[b->device] = 0;
+    delete b;
+    return B2_OK;
+}
+
+int b2_batch_set_model(b2_batch *b, const double side[3], int nsp, const double *eps, const double *sigma,
+                       const double *rcut, int shifted)
+{
+    if (!b || !side || !eps || !sigma || !rcut) return fail(nullptr, B2_EINVAL, "b2_batch_set_model: NULL argument");
+    if (nsp < 1 || nsp > B2_MAXSP) return fail(nullptr, B2_EINVAL, "b2_batch_set_model: 1 <= nsp <= %d", B2_MAXSP);
+    for (int d = 0; d < 3; d++) {
+        if (!(side[d] > 0.0)) return fail(nullptr, B2_EINVAL, "b2_batch_set_model: side must be > 0");
+        b->side[d] = side[d];
+    }
+    memset(&b->pc, 0, sizeof(PairConst));
+    b->pc.nsp = nsp;
+    for (int a = 0; a < nsp * nsp; a++) {
+        if (!(sigma[a] > 0.0) || !(rcut[a] > 0.0)) return fail(nullptr, B2_EINVAL, "b2_batch_set_model: sigma, rcut > 0");
+        double s2 = sigma[a] * sigma[a], s6 = s2 * s2 * s2;
+        b->pc.c6[a] = 4.0 * eps[a] * s6;
+        b->pc.c12[a] = 4.0 * eps[a] * s6 * s6;
+        b->pc.rc2[a] = rcut[a] * rcut[a];
+        double ir2 = 1.0 / b->pc.rc2[a], ir6 = ir2 * ir2 * ir2;
+        b->pc.ushift[a] = shifted ? ir6 * (b->pc.c12[a] * ir6 - b->pc.c6[a]) : 0.0;
+    }
+    b->const_serial = ++g_serial;
+    b->have_model = true;
+    return B2_OK;
+}
+
+#define BDISPATCH(fn, ...) (b->precision == B2_FP32 ? BatchImpl<float>::fn(__VA_ARGS__) : BatchImpl<double>::fn(__VA_ARGS__))
+
+int b2_batch_upload(b2_batch *b, int64_t nrep, int n, const double *pos, const int32_t *species, const double *mass)
+{
+    if (!b || nrep < 0 || n < 0 || (nrep * n > 0 && (!pos || !species))) return fail(nullptr, B2_EINVAL, "b2_batch_upload: bad argument");
+    if (!b->have_model) return fail(nullptr, B2_ESTATE, "b2_batch_upload: call b2_batch_set_model first");
+    if (n > BATCH_MAX_THREADS) return fail(nullptr, B2_EINVAL, "b2_batch_upload: at most %d particles per replica", BATCH_MAX_THREADS);
+    for (int64_t k = 0; k < nrep * n; k++)
+        if (species[k] < 0 || species[k] >= b->pc.nsp) return fail(nullptr, B2_EINVAL, "b2_batch_upload: species id outside the pair table");
+    cudaSetDevice(b->device);
+    return BDISPATCH(upload, b, nrep, n, pos, species, mass);
+}
+
+int b2_batch_minimize(b2_batch *b, int method, int64_t max_steps, double dt, double fn2_tol, int64_t *steps_done,
+                      int *converged, double *energy, double *fn2, double *virial)
+{
+    if (!b || !b->pos) return fail(nullptr, B2_ESTATE, "b2_batch_minimize: no replicas resident");
+    if (max_steps < 0 || !(dt > 0.0)) return fail(nullptr, B2_EINVAL, "b2_batch_minimize: bad argument");
+    if (method != B2_MIN_SD && method != B2_MIN_FIRE) return fail(nullptr, B2_EINVAL, "b2_batch_minimize: unknown method");
+    cudaSetDevice(b->device);
+    return BDISPATCH(minimize, b, method, max_steps, dt, fn2_tol, steps_done, converged, energy, fn2, virial);
+}
+
+int b2_batch_download(b2_batch *b, double *pos, double *forces)
+{
+    if (!b || !b->pos) return fail(nullptr, B2_ESTATE, "b2_batch_download: no replicas resident");
+    cudaSetDevice(b->device);
+    return BDISPATCH(download, b, pos, forces);
 }
 
 }  // extern "C"

@@ -147,20 +147,30 @@ class SlabDomain(object):
             hop = torch.where(slab != self.rank, torch.ones_like(hop), hop)    # either way round the ring
         if self.world > 1 and int(hop.abs().max()) > 1:
             raise RuntimeError('a particle moved more than one slab between two refreshes')
-        stay, go_l, go_r = hop == 0, hop == -1, hop == 1
+        # migrants are a tiny fraction: move only their rows, keep the rest in place
+        idx_l = torch.nonzero(hop == -1).flatten()
+        idx_r = torch.nonzero(hop == 1).flatten()
 
-        def payload(mask):
-            return torch.cat([self.pos[mask], self.vel[mask], self.mass[mask, None],
-                              self.gid[mask, None].to(torch.float64), self.spe[mask, None].to(torch.float64),
-                              self.img[mask].to(torch.float64)], dim=1)
-        from_l, from_r = self._exchange(payload(go_l), payload(go_r), 12) if self.world > 1 else \
-            (self.pos.new_zeros((0, 12)), self.pos.new_zeros((0, 12)))
-        keep = payload(stay)
-        own = torch.cat([keep, from_l, from_r], dim=0)
-        self.pos, self.vel, self.mass = own[:, 0:3].contiguous(), own[:, 3:6].contiguous(), own[:, 6].contiguous()
-        self.gid = own[:, 7].round().to(torch.int64)
-        self.spe = own[:, 8].round().to(torch.int32)
-        self.img = own[:, 9:12].round().to(torch.int64)
+        def payload(idx):
+            return torch.cat([self.pos[idx], self.vel[idx], self.mass[idx, None],
+                              self.gid[idx, None].to(torch.float64), self.spe[idx, None].to(torch.float64),
+                              self.img[idx].to(torch.float64)], dim=1)
+        if self.world > 1:
+            from_l, from_r = self._exchange(payload(idx_l), payload(idx_r), 12)
+            gone = idx_l.numel() + idx_r.numel()
+            if gone or from_l.shape[0] or from_r.shape[0]:
+                new = torch.cat([from_l, from_r], dim=0)
+                if gone:
+                    keep = torch.nonzero(hop == 0).flatten()
+                    sel = lambda t: t[keep]
+                else:
+                    sel = lambda t: t
+                self.pos = torch.cat([sel(self.pos), new[:, 0:3]], dim=0)
+                self.vel = torch.cat([sel(self.vel), new[:, 3:6]], dim=0)
+                self.mass = torch.cat([sel(self.mass), new[:, 6]], dim=0)
+                self.gid = torch.cat([sel(self.gid), new[:, 7].round().to(torch.int64)], dim=0)
+                self.spe = torch.cat([sel(self.spe), new[:, 8].round().to(torch.int32)], dim=0)
+                self.img = torch.cat([sel(self.img), new[:, 9:12].round().to(torch.int64)], dim=0)
         n = self.n_own
         # ghosts: owned particles within r_list of a face are copied to the neighbour beyond it
         if self.world > 1:

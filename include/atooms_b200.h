@@ -255,6 +255,33 @@ int b2_dd_end(b2_ctx *ctx);
 int b2_dd_pack(b2_ctx *ctx, const int32_t *ids_dev, int64_t n, double *out_dev);
 int b2_dd_unpack(b2_ctx *ctx, int64_t first_id, int64_t n, const double *in_dev);
 
+/* ---- ensembles of small independent systems ("replicas") --------------------------
+ *
+ * BASELINE.json configs[3]: thousands of small configurations minimised at once
+ * (the reference drives ONE system per Optimization, optimization/core.py:39-74,
+ * one LAMMPS subprocess per chunk, backends/lammps.py:314-363).  All replicas
+ * share the cell and the pair table; each is handled by one thread block with
+ * all pairs under the minimum image, the whole minimisation inside one launch.
+ * At most 1024 particles per replica.  Errors are reported through
+ * b2_last_error(NULL).                                                        */
+typedef struct b2_batch b2_batch;
+int b2_batch_create(int device, int precision, b2_batch **out);
+int b2_batch_destroy(b2_batch *batch);
+/* cell sides (centre at the origin) and the pair table of b2_set_pair_table     */
+int b2_batch_set_model(b2_batch *batch, const double side[3], int nsp, const double *eps,
+                       const double *sigma, const double *rcut, int shifted);
+/* pos: nrep x n x 3, species: nrep x n (0-based), mass: nrep x n or NULL (1.0)  */
+int b2_batch_upload(b2_batch *batch, int64_t nrep, int n, const double *pos,
+                    const int32_t *species, const double *mass);
+/* Minimise every replica (method, max_steps, dt, fn2_tol as in b2_minimize).
+ * Per-replica outputs, each nrep long or NULL: iterations, converged flag,
+ * potential energy, sum F^2 / n, virial of the final configuration.           */
+int b2_batch_minimize(b2_batch *batch, int method, int64_t max_steps, double dt, double fn2_tol,
+                      int64_t *steps_done, int *converged, double *energy, double *fn2,
+                      double *virial);
+/* final positions (folded) and forces, nrep x n x 3 each, either may be NULL    */
+int b2_batch_download(b2_batch *batch, double *pos, double *forces);
+
 /* Measurement aid (nothing like it in the reference, whose only timer is the
  * wall-clock TSP of simulation/core.py:286-306): with profiling on,
  * b2_run_nve brackets the step kernels and the list-refresh pipeline with

@@ -894,3 +894,105 @@ int b2_dd_unpack(b2_ctx *c, int64_t first_id, int64_t n, const double *in)
         for (int d = 0; d < 3; d++) c->pos[3 * (first_id + k) + d] = in[3 * k + d] + c->center[d];
     return B2_OK;
 }
+
+/* ---- replica ensembles: every replica is an ordinary context, minimised in turn ---- */
+struct b2_batch {
+    int precision, nsp, shifted, n, have_model;
+    int64_t nrep;
+    double side[3];
+    double eps[MAXSP * MAXSP], sigma[MAXSP * MAXSP], rcut[MAXSP * MAXSP];
+    b2_ctx **rep;
+};
+
+int b2_batch_create(int device, int precision, b2_batch **out)
+{
+    (void)device;
+    if (!out || (precision != B2_FP32 && precision != B2_FP64)) return fail(NULL, B2_EINVAL, "b2_batch_create: bad argument");
+    b2_batch *b = (b2_batch *)calloc(1, sizeof(b2_batch));
+    if (!b) return fail(NULL, B2_ENOMEM, "b2_batch_create: out of memory");
+    b->precision = precision;
+    *out = b;
+    return B2_OK;
+}
+
+static void batch_free(b2_batch *b)
+{
+    for (int64_t r = 0; r < b->nrep; r++) b2_destroy(b->rep[r]);
+    free(b->rep);
+    b->rep = NULL;
+    b->nrep = 0;
+}
+
+int b2_batch_destroy(b2_batch *b)
+{
+    if (!b) return B2_OK;
+    batch_free(b);
+    free(b);
+    return B2_OK;
+}
+
+int b2_batch_set_model(b2_batch *b, const double side[3], int nsp, const double *eps, const double *sigma,
+                       const double *rcut, int shifted)
+{
+    if (!b || !side || !eps || !sigma || !rcut || nsp < 1 || nsp > MAXSP) return fail(NULL, B2_EINVAL, "b2_batch_set_model: bad argument");
+    memcpy(b->side, side, 3 * sizeof(double));
+    b->nsp = nsp; b->shifted = shifted;
+    memcpy(b->eps, eps, (size_t)nsp * nsp * sizeof(double));
+    memcpy(b->sigma, sigma, (size_t)nsp * nsp * sizeof(double));
+    memcpy(b->rcut, rcut, (size_t)nsp * nsp * sizeof(double));
+    b->have_model = 1;
+    return B2_OK;
+}
+
+int b2_batch_upload(b2_batch *b, int64_t nrep, int n, const double *pos, const int32_t *species, const double *mass)
+{
+    if (!b || nrep < 0 || n < 0 || !b->have_model) return fail(NULL, B2_EINVAL, "b2_batch_upload: bad argument or no model");
+    batch_free(b);
+    b->rep = (b2_ctx **)calloc((size_t)(nrep > 0 ? nrep : 1), sizeof(b2_ctx *));
+    b->n = n;
+    for (int64_t r = 0; r < nrep; r++) {
+        int rc = b2_create(0, b->precision, &b->rep[r]);
+        if (rc) return rc;
+        b->nrep = r + 1;
+        b2_set_box(b->rep[r], b->side, NULL);
+        b2_set_pair_table(b->rep[r], b->nsp, b->eps, b->sigma, b->rcut, b->shifted);
+        rc = b2_upload(b->rep[r], n, pos + 3 * r * (int64_t)n, NULL, species + r * (int64_t)n, mass ? mass + r * (int64_t)n : NULL);
+        if (rc) return fail(NULL, rc, b2_last_error(b->rep[r]));
+    }
+    return B2_OK;
+}
+
+int b2_batch_minimize(b2_batch *b, int method, int64_t max_steps, double dt, double fn2_tol, int64_t *steps_done,
+                      int *converged, double *energy, double *fn2, double *virial)
+{
+    if (!b) return fail(NULL, B2_EINVAL, "b2_batch_minimize: NULL batch");
+    int err = B2_OK;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t r = 0; r < b->nrep; r++) {
+        int64_t it = 0;
+        int conv = 0;
+        double th[B2_T_LEN];
+        int rc = b2_minimize(b->rep[r], method, max_steps, dt, fn2_tol, &it, &conv);
+        if (rc == B2_OK) rc = b2_thermo(b->rep[r], th);
+        if (rc != B2_OK) { err = rc; continue; }
+        if (steps_done) steps_done[r] = it;
+        if (converged) converged[r] = conv;
+        if (energy) energy[r] = th[B2_T_POTENTIAL];
+        if (fn2) fn2[r] = th[B2_T_FNORM2] / (double)(b->n > 0 ? b->n : 1);
+        if (virial) virial[r] = th[B2_T_VIRIAL];
+    }
+    return err == B2_OK ? B2_OK : fail(NULL, err, "b2_batch_minimize: a replica failed");
+}
+
+int b2_batch_download(b2_batch *b, double *pos, double *forces)
+{
+    if (!b) return fail(NULL, B2_EINVAL, "b2_batch_download: NULL batch");
+    for (int64_t r = 0; r < b->nrep; r++) {
+        int rc = B2_OK;
+        if (pos) rc = b2_download(b->rep[r], pos + 3 * r * (int64_t)b->n, NULL, NULL);
+        if (rc == B2_OK && forces)
+            rc = b2_compute(b->rep[r], B2_FORCES, NULL, NULL, NULL, forces + 3 * r * (int64_t)b->n, NULL, NULL);
+        if (rc) return rc;
+    }
+    return B2_OK;
+}
