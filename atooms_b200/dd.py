@@ -78,6 +78,9 @@ class SlabDomain(object):
         if fast_comm is None:
             fast_comm = on_gpu and lib.has_nccl and self.world > 1 and dist.get_backend(group) == 'nccl'
         self._fast = bool(fast_comm)
+        # a backend that cannot move device memory (gloo) gets host-staged messages
+        self._stage = on_gpu and self.world > 1 and dist.get_backend(group) != 'nccl'
+        self._cdev = torch.device('cpu') if self._stage else self.dev
         if self._fast:
             box = [self.engine.nccl_unique_id() if self.rank == 0 else None]
             dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
@@ -104,21 +107,22 @@ class SlabDomain(object):
         arrives (from_left, from_right).  Posting order [to-left, to-right] /
         [from-right, from-left] keeps the pairing unambiguous when both neighbours
         are the same rank (world size 2)."""
-        counts = torch.tensor([to_left.shape[0], to_right.shape[0]], dtype=torch.int64, device=self.dev)
+        counts = torch.tensor([to_left.shape[0], to_right.shape[0]], dtype=torch.int64, device=self._cdev)
         all_counts = [torch.empty_like(counts) for _ in range(self.world)]
         dist.all_gather(all_counts, counts, group=self.group)
         n_from_right = int(all_counts[self._right()][0])      # the right neighbour's to-left message
         n_from_left = int(all_counts[self._left()][1])
-        pad = lambda t: t if t.shape[0] > 0 else torch.zeros((1, like_cols), dtype=torch.float64, device=self.dev)
-        from_right = torch.empty((max(n_from_right, 1), like_cols), dtype=torch.float64, device=self.dev)
-        from_left = torch.empty((max(n_from_left, 1), like_cols), dtype=torch.float64, device=self.dev)
-        ops = [dist.P2POp(dist.isend, pad(to_left).contiguous(), self._left(), self.group),
-               dist.P2POp(dist.isend, pad(to_right).contiguous(), self._right(), self.group),
+        pad = lambda t: (t if t.shape[0] > 0 else torch.zeros((1, like_cols), dtype=torch.float64,
+                                                               device=self.dev)).to(self._cdev).contiguous()
+        from_right = torch.empty((max(n_from_right, 1), like_cols), dtype=torch.float64, device=self._cdev)
+        from_left = torch.empty((max(n_from_left, 1), like_cols), dtype=torch.float64, device=self._cdev)
+        ops = [dist.P2POp(dist.isend, pad(to_left), self._left(), self.group),
+               dist.P2POp(dist.isend, pad(to_right), self._right(), self.group),
                dist.P2POp(dist.irecv, from_right, self._right(), self.group),
                dist.P2POp(dist.irecv, from_left, self._left(), self.group)]
         for req in dist.batch_isend_irecv(ops):
             req.wait()
-        return from_left[:n_from_left], from_right[:n_from_right]
+        return from_left[:n_from_left].to(self.dev), from_right[:n_from_right].to(self.dev)
 
     # -- refresh: migration + ghost selection + re-upload ---------------------------------
     def refresh(self):
@@ -213,12 +217,18 @@ class SlabDomain(object):
         eng, n = self.engine, self.n_own
         eng.dd_pack(self._send_l.data_ptr(), len(self._send_l), self._out_l.data_ptr())
         eng.dd_pack(self._send_r.data_ptr(), len(self._send_r), self._out_r.data_ptr())
-        ops = [dist.P2POp(dist.isend, self._out_l, self._left(), self.group),
-               dist.P2POp(dist.isend, self._out_r, self._right(), self.group),
-               dist.P2POp(dist.irecv, self._in_r, self._right(), self.group),
-               dist.P2POp(dist.irecv, self._in_l, self._left(), self.group)]
+        out_l, out_r = self._out_l.to(self._cdev), self._out_r.to(self._cdev)
+        in_l = self._in_l if not self._stage else torch.empty_like(self._in_l, device=self._cdev)
+        in_r = self._in_r if not self._stage else torch.empty_like(self._in_r, device=self._cdev)
+        ops = [dist.P2POp(dist.isend, out_l, self._left(), self.group),
+               dist.P2POp(dist.isend, out_r, self._right(), self.group),
+               dist.P2POp(dist.irecv, in_r, self._right(), self.group),
+               dist.P2POp(dist.irecv, in_l, self._left(), self.group)]
         for req in dist.batch_isend_irecv(ops):
             req.wait()
+        if self._stage:
+            self._in_l.copy_(in_l)
+            self._in_r.copy_(in_r)
         eng.dd_unpack(n, self._n_gl, self._in_l.data_ptr())
         eng.dd_unpack(n + self._n_gl, self._n_gr, self._in_r.data_ptr())
 
@@ -237,8 +247,12 @@ class SlabDomain(object):
             m = min(self._batch, steps - base)
             for _ in range(0 if self._fast else m):
                 eng.dd_step(self._vmax.data_ptr())
-                if self.world > 1:
+                if self.world > 1 and not self._stage:
                     dist.all_reduce(self._vmax[:1], op=dist.ReduceOp.MAX, group=self.group)
+                elif self.world > 1:
+                    v = self._vmax[:1].to(self._cdev)
+                    dist.all_reduce(v, op=dist.ReduceOp.MAX, group=self.group)
+                    self._vmax[:1].copy_(v)
                 eng.dd_commit(self._vmax.data_ptr())
                 self._halo()
             if self._fast:
@@ -268,6 +282,7 @@ class SlabDomain(object):
         vec = torch.tensor([t['kinetic'], t['potential'], t['virial'], t['fnorm2'], *t['momentum'], t['mass'],
                             float(self.n_own)], dtype=torch.float64, device=self.dev)
         if self.world > 1:
+            vec = vec.to(self._cdev)
             dist.all_reduce(vec, op=dist.ReduceOp.SUM, group=self.group)
         v = vec.cpu().numpy()
         return {'kinetic': v[0], 'potential': v[1], 'virial': v[2], 'fnorm2': v[3], 'momentum': v[4:7],
