@@ -36,7 +36,7 @@ def build(force=False, verbose=False, extra=()):
         return OUT
     nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
-    cmd = [nvcc] + NVCC_FLAGS + list(extra) + ['-o', OUT] + sources() + ['-ldl']
+    cmd = [nvcc] + NVCC_FLAGS + list(extra) + ['-o', OUT] + sources() + ['-ldl', '-Xlinker', '-Bsymbolic']
     if verbose:
         cmd.insert(1, '-Xptxas=-v')
         print(' '.join(cmd))

@@ -103,7 +103,9 @@ class Library(object):
                           '(build it with `python -c "import __graft_entry__ as g; g.build()"`; '
                           'there is no CPU fallback)' % path)
         self.path = path
-        self.dll = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        # RTLD_LOCAL: two libraries exporting the same b2_* names (product + oracle in the
+        # tests) must never see each other's symbols; both are also linked -Bsymbolic
+        self.dll = ctypes.CDLL(path, mode=ctypes.RTLD_LOCAL)
         for name, (restype, argtypes) in SYMBOLS.items():
             fn = getattr(self.dll, name)   # AttributeError if the symbol is missing
             fn.restype = restype

@@ -3,7 +3,12 @@
 #pragma once
 #include "b2_common.cuh"
 
-#define FORCE_THREADS 128
+#ifndef FORCE_THREADS
+#define FORCE_THREADS 256
+#endif
+#ifndef B2_UNROLL
+#define B2_UNROLL 4
+#endif
 #define RED_THREADS 256
 
 
@@ -83,13 +88,15 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
             }                                                                         \
         }                                                                             \
     }
-    for (; k + 4 <= cnt; k += 4) {
-        int j0 = ld_stream(row + (size_t)(k + 0) * 32);
-        int j1 = ld_stream(row + (size_t)(k + 1) * 32);
-        int j2 = ld_stream(row + (size_t)(k + 2) * 32);
-        int j3 = ld_stream(row + (size_t)(k + 3) * 32);
-        P4 p0 = pos[j0], p1 = pos[j1], p2 = pos[j2], p3 = pos[j3];
-        B2_PAIR(p0) B2_PAIR(p1) B2_PAIR(p2) B2_PAIR(p3)
+    for (; k + B2_UNROLL <= cnt; k += B2_UNROLL) {
+        int jj[B2_UNROLL];
+        P4 pp[B2_UNROLL];
+#pragma unroll
+        for (int u = 0; u < B2_UNROLL; u++) jj[u] = ld_stream(row + (size_t)(k + u) * 32);
+#pragma unroll
+        for (int u = 0; u < B2_UNROLL; u++) pp[u] = pos[jj[u]];
+#pragma unroll
+        for (int u = 0; u < B2_UNROLL; u++) B2_PAIR(pp[u])
     }
     for (; k < cnt; k++) {
         int j = ld_stream(row + (size_t)k * 32);
