@@ -140,6 +140,15 @@ def measured_peak():
     return 6650.0, 'fallback (B200_PROFILING.md: 6.65 TB/s)'
 
 
+def ncu_traffic(precision, n):
+    """DRAM bytes per k_step_nve launch from the committed ncu capture (same workload), else None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))['k_step_nve_fp%d' % precision]
+        return float(t['bytes_per_launch']) if int(t['particles']) == int(n) else None
+    except Exception:
+        return None
+
+
 def oracle_library():
     """The CPU oracle: used by the cpu_baseline leg and by --impl reference only."""
     from atooms_b200 import capi
@@ -417,7 +426,8 @@ def main():
             'gpu_launches': int(r['launches']),
             'clocks': clocks,
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                         'frac': achieved / peak, 'traffic': None, 'kernel': 'k_step_nve',
+                         'frac': achieved / peak, 'traffic': ncu_traffic(args.precision, n) if world == 1 else None,
+                         'kernel': 'k_step_nve',
                          'kernel_ms': kernel_ms, 'bytes_per_particle_step': B_ALG[args.precision],
                          'peak_source': peak_src,
                          'step_kernel_share': (r['prof']['ms_steps'] / r['ms']) if world == 1 else None,
