@@ -9,6 +9,17 @@
 #ifndef B2_UNROLL
 #define B2_UNROLL 4
 #endif
+#ifndef B2_PIPE
+#define B2_PIPE 1
+#endif
+// resident blocks per SM asked of ptxas for the step kernel: fp32 fits 6 x 256 threads in 40
+// registers without spilling (measured 0.243 -> 0.224 ms at N = 1.2M); fp64 runs best at 4 x 256 in 64 (0.568 -> 0.486 ms)
+#ifndef B2_MINBLK32
+#define B2_MINBLK32 6
+#endif
+#ifndef B2_MINBLK64
+#define B2_MINBLK64 4
+#endif
 #define RED_THREADS 256
 
 
@@ -88,6 +99,22 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
             }                                                                         \
         }                                                                             \
     }
+#if B2_PIPE
+    // software pipeline: the index loads of group g+1 are in flight while the positions of
+    // group g arrive and its pairs are evaluated (index -> position is a dependent chain)
+    int jj[B2_UNROLL];
+#pragma unroll
+    for (int u = 0; u < B2_UNROLL; u++) jj[u] = ld_stream(row + (size_t)min(u, max(cnt - 1, 0)) * 32);
+    for (; k + B2_UNROLL <= cnt; k += B2_UNROLL) {
+        P4 pp[B2_UNROLL];
+#pragma unroll
+        for (int u = 0; u < B2_UNROLL; u++) pp[u] = pos[jj[u]];
+#pragma unroll
+        for (int u = 0; u < B2_UNROLL; u++) jj[u] = ld_stream(row + (size_t)min(k + B2_UNROLL + u, cnt - 1) * 32);
+#pragma unroll
+        for (int u = 0; u < B2_UNROLL; u++) B2_PAIR(pp[u])
+    }
+#else
     for (; k + B2_UNROLL <= cnt; k += B2_UNROLL) {
         int jj[B2_UNROLL];
         P4 pp[B2_UNROLL];
@@ -98,6 +125,7 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
 #pragma unroll
         for (int u = 0; u < B2_UNROLL; u++) B2_PAIR(pp[u])
     }
+#endif
     for (; k < cnt; k++) {
         int j = ld_stream(row + (size_t)k * 32);
         P4 p0 = pos[j];
@@ -182,7 +210,7 @@ template <typename R> struct StepArgs {
 // the last block to finish flips the buffers and settles the step's
 // bookkeeping on the device.
 template <typename R>
-__global__ void __launch_bounds__(FORCE_THREADS)
+__global__ void __launch_bounds__(FORCE_THREADS, (sizeof(R) == 4 ? B2_MINBLK32 : B2_MINBLK64))
 k_step_nve(StepArgs<R> a)
 {
     typedef typename Vec4<R>::type V4;

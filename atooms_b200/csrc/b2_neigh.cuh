@@ -260,10 +260,18 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     const R *rl2_row = s_rl2 + ti * nsp;
     int *row = nbr + ((size_t)(i >> 5) * cap) * 32 + (i & 31);
     int cnt = 0;
+    // the thin band around the threshold that must be decided canonically (see in_list)
+    const R band_lo = (R)1 - PredEps<R>::v, band_hi = (R)1 + PredEps<R>::v;
 #define B2_TEST(J)                                                        \
     {                                                                     \
         const P4 pj = pos[J];                                             \
-        if (active && (J) != i && in_list<R>(box, pi, pj, rl2_row[ptype(pj)])) { \
+        const R rl2 = rl2_row[ptype(pj)];                                 \
+        R dx_, dy_, dz_;                                                  \
+        delta(pi, pj, box, dx_, dy_, dz_);                                \
+        const R r2_ = dx_ * dx_ + dy_ * dy_ + dz_ * dz_;                  \
+        bool in_ = r2_ < rl2 * band_lo;                                   \
+        if (!in_ && r2_ <= rl2 * band_hi) in_ = r2_canon(pi, pj, box) < rl2; \
+        if (in_ && active && (J) != i) {                                  \
             if (cnt < cap) row[(size_t)cnt * 32] = (J);                   \
             cnt++;                                                        \
         }                                                                 \
@@ -274,24 +282,31 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
         int cx, cy, cz;
         float fx, fy, fz;
         cell_frac(box, g, pi, cx, cy, cz, fx, fy, fz);
-        {
-            for (int dz = -M; dz <= M; dz++) {
-                float gz = cell_gap(dz, fz) * g.w[2];
-                float gz2 = gz * gz;
-                if (gz2 > g.reach2) continue;
-                const int z = wrap_cell(cz + dz, g.nc[2]);
-                for (int dy = -M; dy <= M; dy++) {
-                    float gy = cell_gap(dy, fy) * g.w[1];
-                    float gyz2 = gz2 + gy * gy;
-                    if (gyz2 > g.reach2) continue;
-                    const int y = wrap_cell(cy + dy, g.nc[1]);
-                    for (int dx = -M; dx <= M; dx++) {
-                        float gx = cell_gap(dx, fx) * g.w[0];
-                        if (gyz2 + gx * gx > g.reach2) continue;
-                        const uint32_t key = morton3(wrap_cell(cx + dx, g.nc[0]), y, z);
-                        const int s = cell_start[key], e = cell_end[key];
-                        for (int j = s; j < e; j++) B2_TEST(j)
-                    }
+        // Morton bits of the 2M+1 x-columns of the stencil, once per particle
+        uint32_t sx[2 * M + 1];
+        float gx2[2 * M + 1];
+#pragma unroll
+        for (int dx = -M; dx <= M; dx++) {
+            sx[dx + M] = spread3((uint32_t)wrap_cell(cx + dx, g.nc[0]));
+            const float gx = cell_gap(dx, fx) * g.w[0];
+            gx2[dx + M] = gx * gx;
+        }
+        for (int dz = -M; dz <= M; dz++) {
+            const float gz = cell_gap(dz, fz) * g.w[2];
+            const float gz2 = gz * gz;
+            if (gz2 > g.reach2) continue;
+            const uint32_t sz = spread3((uint32_t)wrap_cell(cz + dz, g.nc[2])) << 2;
+            for (int dy = -M; dy <= M; dy++) {
+                const float gy = cell_gap(dy, fy) * g.w[1];
+                const float gyz2 = gz2 + gy * gy;
+                if (gyz2 > g.reach2) continue;
+                const uint32_t syz = sz | (spread3((uint32_t)wrap_cell(cy + dy, g.nc[1])) << 1);
+#pragma unroll
+                for (int dx = 0; dx <= 2 * M; dx++) {
+                    if (gyz2 + gx2[dx] > g.reach2) continue;
+                    const uint32_t key = syz | sx[dx];
+                    const int s = cell_start[key], e = cell_end[key];
+                    for (int j = s; j < e; j++) B2_TEST(j)
                 }
             }
         }
