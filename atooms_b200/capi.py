@@ -117,7 +117,11 @@ class Library(object):
             self.dll.b2_nccl_init.argtypes = [_vp, ctypes.c_char_p, _int, _int]
             self.dll.b2_nccl_set_halo.argtypes = [_vp, _vp, _i64, _vp, _i64, _i64, _i64]
             self.dll.b2_nccl_run.argtypes = [_vp, _i64]
-            for name in ('b2_nccl_unique_id', 'b2_nccl_init', 'b2_nccl_set_halo', 'b2_nccl_run'):
+            self.dll.b2_peer_export.argtypes = [_vp, _i64, _int, _int, ctypes.c_char_p]
+            self.dll.b2_peer_connect.argtypes = [_vp, ctypes.c_char_p]
+            self.dll.b2_peer_run.argtypes = [_vp, _i64]
+            for name in ('b2_nccl_unique_id', 'b2_nccl_init', 'b2_nccl_set_halo', 'b2_nccl_run',
+                         'b2_peer_export', 'b2_peer_connect', 'b2_peer_run'):
                 getattr(self.dll, name).restype = _int
         version = self.dll.b2_abi_version()
         if version != ABI_VERSION:
@@ -462,3 +466,15 @@ class Batch(object):
         frc = numpy.empty((self.nrep, self.n, 3)) if forces else None
         self._call('b2_batch_download', _dp(pos), _dp(frc))
         return (pos, frc) if forces else pos
+
+    # -- peer-memory halo (CUDA library only, one rank per GPU) ---------------------------------
+    def peer_export(self, halo_capacity, rank, nranks):
+        buf = ctypes.create_string_buffer(64)
+        self._call('b2_peer_export', int(halo_capacity), int(rank), int(nranks), buf)
+        return buf.raw
+
+    def peer_connect(self, handles):
+        self._call('b2_peer_connect', ctypes.c_char_p(b''.join(handles)))
+
+    def peer_run(self, count):
+        self._call('b2_peer_run', int(count))

@@ -221,6 +221,7 @@ struct Ctl {
     unsigned int blocks_done;    // ticket for "last block finishes the step"
     unsigned int max_count;      // largest neighbour count seen by the last build
     unsigned int converged;
+    unsigned int peer_error, pad0_;   // a peer-memory wait timed out (1) or lost step (2)
     long long steps_done, steps_target, rebuilds;
     double disp_bound, half_skin;
     // minimiser

@@ -49,6 +49,14 @@ struct b2_ctx {
     double *halo_buf = nullptr;                       // out_l | out_r | in_l | in_r
     size_t halo_cap = 0;
     float *dd_vmax = nullptr;
+    // peer-memory halo (b2_peer_*)
+    char *peer_buf = nullptr;                         // our mailbox block (IPC-exported)
+    char *peer_map[64] = {nullptr};                   // the other ranks' blocks, mapped
+    unsigned long long **peer_mail = nullptr;         // device array [nranks]: our slot in every rank's block
+    unsigned *peer_ticket = nullptr;
+    int64_t peer_cap = 0;                             // records per inbox
+    bool peer_on = false;
+    unsigned dd_seq = 0;
     int *img = nullptr;        // [3n] by original id
     double *ref = nullptr;     // [3n] by original id, unfolded, relative to centre
     // neighbour search
@@ -735,6 +743,9 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
     a.box = make_box<R>(c);
     a.dd = 0;
     a.vmax_out = nullptr;
+    a.vmax_mail = nullptr;
+    a.nranks = 1;
+    a.seq = 0;
     int64_t done = 0;
     while (done < steps) {
         // speculative batches: [guarded refresh][batch x step]; steps after the
@@ -907,6 +918,9 @@ int Impl<R>::dd_step(b2_ctx *c, float *vmax_out)
     a.box = make_box<R>(c);
     a.dd = 1;
     a.vmax_out = vmax_out;
+    a.vmax_mail = c->peer_on ? c->peer_mail : nullptr;
+    a.nranks = c->nranks;
+    a.seq = c->dd_seq;
     if (n > 0) LAUNCH(k_step_nve<R>, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
     return B2_OK;
 }
@@ -1014,6 +1028,11 @@ int b2_destroy(b2_ctx *c)
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    for (int r = 0; r < 64; r++)
+        if (c->peer_map[r] && c->peer_map[r] != c->peer_buf) cudaIpcCloseMemHandle(c->peer_map[r]);
+    if (c->peer_buf) cudaFree(c->peer_buf);
+    if (c->peer_mail) cudaFree(c->peer_mail);
+    if (c->peer_ticket) cudaFree(c->peer_ticket);
     if (c->hctl) cudaFreeHost(c->hctl);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -1255,6 +1274,9 @@ int b2_dd_poll(b2_ctx *c, int64_t *steps_done, int *need_refresh)
     if (steps_done) *steps_done = c->hctl->steps_done;
     if (need_refresh) *need_refresh = (c->hctl->halt_rebuild || c->hctl->overflow) ? 1 : 0;
     if (c->hctl->halt_rebuild) c->list_dirty = true;
+    if (c->hctl->peer_error)
+        return fail(c, B2_ECUDA, "peer-memory halo: %s", c->hctl->peer_error == 1u
+                    ? "timed out waiting for a neighbouring rank" : "a rank ran ahead of the step protocol");
     return B2_OK;
 }
 
@@ -1758,6 +1780,135 @@ int b2_batch_download(b2_batch *b, double *pos, double *forces)
     if (!b || !b->pos) return fail(nullptr, B2_ESTATE, "b2_batch_download: no replicas resident");
     cudaSetDevice(b->device);
     return BDISPATCH(download, b, pos, forces);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Peer-memory halo: host side.  Mailbox block layout (identical on every rank):
+//   [0, 2*64*W)            max|v|^2 slots: [parity][source rank], 64 bytes each
+//   [.., +2*64)            arrival flags: from the left, from the right neighbour
+//   [.., +4*cap*24)        inboxes: [from-left | from-right][parity][cap records of 3 doubles]
+// ---------------------------------------------------------------------------
+static size_t peer_off_flags(int W) { return (size_t)2 * 64 * W; }
+static size_t peer_off_inbox(int W) { return peer_off_flags(W) + 2 * 64; }
+static size_t peer_inbox(int W, int64_t cap, int side, int parity)
+{
+    return peer_off_inbox(W) + ((size_t)side * 2 + parity) * (size_t)cap * 24;
+}
+static size_t peer_bytes(int W, int64_t cap) { return peer_inbox(W, cap, 2, 0); }
+
+template <typename R> struct ImplPeer {
+    typedef typename Pos4<R>::type P4;
+    static int run(b2_ctx *c, int64_t count)
+    {
+        const int n = (int)c->n, W = c->nranks;
+        const int n_own = n - c->n_ghost_l - c->n_ghost_r;
+        if (std::max(c->n_send_l, c->n_send_r) > c->peer_cap || std::max(c->n_ghost_l, c->n_ghost_r) > c->peer_cap)
+            return fail(c, B2_EINVAL, "b2_peer_run: halo of %d / %d records exceeds the mailbox capacity %lld",
+                        std::max(c->n_send_l, c->n_send_r), std::max(c->n_ghost_l, c->n_ghost_r), (long long)c->peer_cap);
+        if (!c->dd_vmax) {
+            CU(cudaMalloc((void **)&c->dd_vmax, 2 * sizeof(float)));
+            CU(cudaMemsetAsync(c->dd_vmax, 0, 2 * sizeof(float), c->stream));
+        }
+        char *L = c->peer_map[c->left], *Rt = c->peer_map[c->right];
+        for (int64_t k = 0; k < count; k++) {
+            const unsigned seq = ++c->dd_seq;
+            const int par = (int)(seq & 1u);
+            int rc = Impl<R>::dd_step(c, c->dd_vmax);
+            if (rc) return rc;
+            LAUNCH(k_peer_commit, 1, 32, c->ctl, (const unsigned long long *)c->peer_buf, W, seq, c->dd_dt, c->dd_vmax + 1);
+            PeerArgs<R> a;
+            a.ctl = c->ctl;
+            a.pos[0] = (P4 *)c->pos[0];
+            a.pos[1] = (P4 *)c->pos[1];
+            a.inv = c->inv;
+            a.send_l = c->send_l; a.send_r = c->send_r;
+            a.n_send_l = c->n_send_l; a.n_send_r = c->n_send_r;
+            a.first_l = n_own; a.n_ghost_l = c->n_ghost_l;
+            a.first_r = n_own + c->n_ghost_l; a.n_ghost_r = c->n_ghost_r;
+            a.box = make_box<R>(c);
+            // what we send to the LEFT neighbour arrives there "from the right" (side 1), and vice versa
+            a.out_l = (double *)(L + peer_inbox(W, c->peer_cap, 1, par));
+            a.out_r = (double *)(Rt + peer_inbox(W, c->peer_cap, 0, par));
+            a.flag_l = (unsigned long long *)(L + peer_off_flags(W) + 64);
+            a.flag_r = (unsigned long long *)(Rt + peer_off_flags(W));
+            a.in_l = (const double *)(c->peer_buf + peer_inbox(W, c->peer_cap, 0, par));
+            a.in_r = (const double *)(c->peer_buf + peer_inbox(W, c->peer_cap, 1, par));
+            a.my_flag_l = (const unsigned long long *)(c->peer_buf + peer_off_flags(W));
+            a.my_flag_r = (const unsigned long long *)(c->peer_buf + peer_off_flags(W) + 64);
+            a.ticket = c->peer_ticket;
+            a.seq = seq;
+            LAUNCH(k_peer_push<R>, std::max(1, cdiv(c->n_send_l + c->n_send_r, 256)), 256, a);
+            LAUNCH(k_peer_pull<R>, std::max(1, cdiv(c->n_ghost_l + c->n_ghost_r, 256)), 256, a);
+        }
+        return B2_OK;
+    }
+};
+
+extern "C" {
+
+int b2_peer_export(b2_ctx *c, int64_t halo_capacity, int rank, int nranks, char handle_out[64])
+{
+    if (!c || !handle_out || nranks < 2 || nranks > 64 || rank < 0 || rank >= nranks || halo_capacity < 1)
+        return fail(c, B2_EINVAL, "b2_peer_export: bad argument (2 <= nranks <= 64)");
+    int rc = bind_device(c);
+    if (rc) return rc;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    if (c->peer_buf) return fail(c, B2_ESTATE, "b2_peer_export: already exported");
+    const size_t bytes = peer_bytes(nranks, halo_capacity);
+    CU(cudaMalloc((void **)&c->peer_buf, bytes));
+    CU(cudaMemset(c->peer_buf, 0, bytes));
+    CU(cudaMalloc((void **)&c->peer_ticket, sizeof(unsigned)));
+    CU(cudaMemset(c->peer_ticket, 0, sizeof(unsigned)));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, c->peer_buf));
+    memcpy(handle_out, &h, 64);
+    c->peer_cap = halo_capacity;
+    c->nranks = nranks;
+    c->myrank = rank;
+    c->left = (rank + nranks - 1) % nranks;
+    c->right = (rank + 1) % nranks;
+    return B2_OK;
+}
+
+int b2_peer_connect(b2_ctx *c, const char *handles)
+{
+    if (!c || !handles || !c->peer_buf) return fail(c, B2_ESTATE, "b2_peer_connect: call b2_peer_export first");
+    int rc = bind_device(c);
+    if (rc) return rc;
+    const int W = c->nranks;
+    std::vector<unsigned long long *> mail((size_t)W);
+    for (int r = 0; r < W; r++) {
+        if (r == c->myrank) {
+            c->peer_map[r] = c->peer_buf;
+        } else {
+            cudaIpcMemHandle_t h;
+            memcpy(&h, handles + 64 * (size_t)r, 64);
+            void *p = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess)
+                return fail(c, B2_ECUDA, "b2_peer_connect: cannot map rank %d's mailbox (%s): peer access over "
+                            "NVLink/PCIe is required, and two ranks must not share a GPU", r, cudaGetErrorString(e));
+            c->peer_map[r] = (char *)p;
+        }
+        // our value lands in rank r's block, slot [parity 0][our rank]
+        mail[r] = (unsigned long long *)(c->peer_map[r] + (size_t)64 * c->myrank);
+    }
+    CU(cudaMalloc((void **)&c->peer_mail, W * sizeof(unsigned long long *)));
+    CU(cudaMemcpy(c->peer_mail, mail.data(), W * sizeof(unsigned long long *), cudaMemcpyHostToDevice));
+    c->peer_on = true;
+    c->dd_seq = 0;
+    return B2_OK;
+}
+
+int b2_peer_run(b2_ctx *c, int64_t count)
+{
+    NEED_PARTICLES("b2_peer_run");
+    if (!c->peer_on) return fail(c, B2_ESTATE, "b2_peer_run: call b2_peer_export / b2_peer_connect first");
+    if (!(c->dd_dt > 0.0)) return fail(c, B2_ESTATE, "b2_peer_run: call b2_dd_begin first");
+    if (count < 0) return fail(c, B2_EINVAL, "b2_peer_run: count >= 0 required");
+    return c->precision == B2_FP32 ? ImplPeer<float>::run(c, count) : ImplPeer<double>::run(c, count);
 }
 
 }  // extern "C"

@@ -202,7 +202,23 @@ template <typename R> struct StepArgs {
     // (k_dd_commit); this kernel only publishes the local one
     int dd;
     float *vmax_out;
+    // peer-memory mode (b2_peer_*): the local max is also stored, tagged with the step's
+    // sequence number, straight into every rank's mailbox over NVLink
+    unsigned long long *const *vmax_mail;   // [nranks] device pointers: rank r's slot for OUR value
+    int nranks;
+    unsigned seq;
 };
+
+// mail[r] points at OUR slot in rank r's mailbox (parity 0); the parity-1 slot sits 8 * nranks
+// words further (64-byte slots).  A rank that is not our neighbour may run one step ahead of
+// us, hence the two parities.
+__device__ __forceinline__ void peer_publish(unsigned long long *const *mail, int nranks, unsigned seq, float v)
+{
+    const unsigned long long packed = ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(v);
+    const size_t off = (size_t)(seq & 1u) * 8u * (size_t)nranks;
+    __threadfence_system();
+    for (int r = 0; r < nranks; r++) *(volatile unsigned long long *)(mail[r] + off) = packed;
+}
 
 // The fused velocity-Verlet step (kick-drift form): F(x) -> v += dt F/m ->
 // x += dt v -> fold into the cell (particle.py:90-99) -> max |v|^2 for the
@@ -217,7 +233,10 @@ k_step_nve(StepArgs<R> a)
     typedef typename Pos4<R>::type P4;
     Ctl *ctl = a.ctl;
     if (ctl->halt_rebuild | ctl->overflow | ctl->done) {
-        if (a.dd && blockIdx.x == 0 && threadIdx.x == 0) *a.vmax_out = 0.f;    // a no-op step moves nothing
+        if (a.dd && blockIdx.x == 0 && threadIdx.x == 0) {      // a no-op step moves nothing
+            *a.vmax_out = 0.f;
+            if (a.vmax_mail) peer_publish(a.vmax_mail, a.nranks, a.seq, 0.f);
+        }
         return;
     }
     __shared__ PairTab<R> tab;
@@ -267,8 +286,10 @@ k_step_nve(StepArgs<R> a)
         s_last = (ticket == gridDim.x - 1);
         if (s_last && a.dd) {
             __threadfence();
-            *a.vmax_out = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
+            const float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
+            *a.vmax_out = vm2;
             ctl->blocks_done = 0u;
+            if (a.vmax_mail) peer_publish(a.vmax_mail, a.nranks, a.seq, vm2);
         } else if (s_last) {
             __threadfence();
             float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
@@ -582,4 +603,131 @@ __global__ void k_inverse(const Ctl *__restrict__ ctl, int guarded, const int *_
     if (guarded && !ctl->halt_rebuild) return;
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s < n) inv[orig[s]] = s;
+}
+
+// ---------------------------------------------------------------------------
+// Peer-memory halo (b2_peer_*): the per-step exchange without a communication
+// library.  Every rank owns a mailbox block in its own HBM, mapped into its
+// peers with CUDA IPC; senders store into it over NVLink, receivers spin on a
+// sequence number.  Per step:   step kernel (publishes max|v|^2 to all ranks)
+//   -> k_peer_commit  (waits for all ranks' values: the 4-byte all-reduce)
+//   -> k_peer_push    (gathers boundary positions INTO the neighbours' inboxes)
+//   -> k_peer_pull    (waits for both neighbours, scatters the inbox into the ghosts)
+// Inboxes are double-buffered on the step parity: a neighbour can run at most
+// one step ahead.  Every wait has a time-out that raises Ctl::peer_error.
+// ---------------------------------------------------------------------------
+#define PEER_TIMEOUT_CYCLES 20000000000LL      // ~10 s
+
+__device__ __forceinline__ bool peer_wait_ge(const volatile unsigned long long *flag, unsigned long long want, Ctl *ctl)
+{
+    const long long t0 = clock64();
+    while (*flag < want) {
+        if (clock64() - t0 > PEER_TIMEOUT_CYCLES) { ctl->peer_error = 1u; return false; }
+        __nanosleep(100);
+    }
+    __threadfence_system();
+    return true;
+}
+
+__global__ void k_peer_commit(Ctl *ctl, const unsigned long long *mail, int nranks, unsigned seq, double drift,
+                              float *gv_out)
+{
+    // one warp; lane r waits for rank r's value of this step
+    const int lane = threadIdx.x;
+    unsigned bits = 0u;
+    bool ok = true;
+    if (ctl->peer_error) ok = false;
+    for (int r = lane; r < nranks && ok; r += 32) {
+        const volatile unsigned long long *slot = mail + (size_t)(seq & 1u) * 8u * nranks + 8 * r;   // 64-byte slots
+        const long long t0 = clock64();
+        unsigned long long v;
+        while (((v = *slot) >> 32) < (unsigned long long)seq) {
+            if (clock64() - t0 > PEER_TIMEOUT_CYCLES) { ctl->peer_error = 1u; ok = false; break; }
+            __nanosleep(100);
+        }
+        if ((v >> 32) == (unsigned long long)seq) bits = max(bits, (unsigned)(v & 0xffffffffu));
+        else if (ok) { ctl->peer_error = 2u; ok = false; }            // a neighbour ran ahead of the protocol
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) bits = max(bits, __shfl_xor_sync(0xffffffffu, bits, o));
+    if (lane == 0) {
+        const float gv = __uint_as_float(bits);                       // non-negative floats order like their bits
+        *gv_out = gv;
+        if (!(ctl->halt_rebuild | ctl->overflow | ctl->done | ctl->peer_error)) {
+            double bound = ctl->disp_bound + fabs(drift) * sqrt((double)gv) * (1.0 + 1e-6);
+            ctl->disp_bound = bound;
+            ctl->cur ^= 1u;
+            long long s = ctl->steps_done + 1;
+            ctl->steps_done = s;
+            if (s >= ctl->steps_target) ctl->done = 1u;
+            if (bound > ctl->half_skin) ctl->halt_rebuild = 1u;
+        }
+    }
+}
+
+template <typename R> struct PeerArgs {
+    Ctl *ctl;
+    typename Pos4<R>::type *pos[2];
+    const int *inv;
+    const int *send_l, *send_r;
+    int n_send_l, n_send_r;
+    int first_l, n_ghost_l, first_r, n_ghost_r;      // local ids of the ghosts
+    Box<R> box;
+    double *out_l, *out_r;                           // REMOTE: the neighbours' inboxes of this parity
+    unsigned long long *flag_l, *flag_r;             // REMOTE: the neighbours' arrival flags
+    const double *in_l, *in_r;                       // LOCAL inboxes of this parity
+    const unsigned long long *my_flag_l, *my_flag_r; // LOCAL arrival flags (from the left / right neighbour)
+    unsigned *ticket;                                // LOCAL counter
+    unsigned seq;
+};
+
+template <typename R>
+__global__ void __launch_bounds__(256)
+k_peer_push(PeerArgs<R> a)
+{
+    const typename Pos4<R>::type *pos = a.ctl->cur ? a.pos[1] : a.pos[0];
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    const int total = a.n_send_l + a.n_send_r;
+    if (k < total) {
+        const bool left = k < a.n_send_l;
+        const int q = left ? k : k - a.n_send_l;
+        const int id = left ? a.send_l[q] : a.send_r[q];
+        double x, y, z;
+        to_double(pos[a.inv[id]], a.box, x, y, z);
+        double *dst = (left ? a.out_l : a.out_r) + 3 * (size_t)q;
+        dst[0] = x; dst[1] = y; dst[2] = z;                          // stores into the neighbour's HBM
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(a.ticket, 1u);
+        if (t == gridDim.x - 1) {                                     // everything of this rank is on its way
+            *a.ticket = 0u;
+            __threadfence_system();
+            *(volatile unsigned long long *)a.flag_l = (unsigned long long)a.seq;
+            *(volatile unsigned long long *)a.flag_r = (unsigned long long)a.seq;
+        }
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256)
+k_peer_pull(PeerArgs<R> a)
+{
+    __shared__ bool s_ok;
+    if (threadIdx.x == 0)
+        s_ok = !a.ctl->peer_error &&
+               peer_wait_ge((const volatile unsigned long long *)a.my_flag_l, a.seq, a.ctl) &&
+               peer_wait_ge((const volatile unsigned long long *)a.my_flag_r, a.seq, a.ctl);
+    __syncthreads();
+    if (!s_ok) return;
+    typename Pos4<R>::type *pos = a.ctl->cur ? a.pos[1] : a.pos[0];
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= a.n_ghost_l + a.n_ghost_r) return;
+    const bool left = k < a.n_ghost_l;
+    const int q = left ? k : k - a.n_ghost_l;
+    const double *src = (left ? a.in_l : a.in_r) + 3 * (size_t)q;
+    const int s = a.inv[(left ? a.first_l : a.first_r) + q];
+    // written by another GPU: read around L1
+    pos[s] = encode_pos(__ldcg(src), __ldcg(src + 1), __ldcg(src + 2), praw(pos[s]), a.box);
 }

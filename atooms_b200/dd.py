@@ -36,7 +36,7 @@ class SlabDomain(object):
 
     def __init__(self, position, velocity, species, side, model='lennard_jones', dt=0.002, skin=0.3,
                  precision=64, mass=None, gid=None, center=None, device=None, library=None, group=None,
-                 fast_comm=None):
+                 fast_comm=None, peer=None):
         """`position` ... are the particles this rank holds initially (global
         coordinates, any x: the first refresh sends strays to the ring neighbour
         that owns them; they must not be more than one slab away)."""
@@ -85,6 +85,13 @@ class SlabDomain(object):
             box = [self.engine.nccl_unique_id() if self.rank == 0 else None]
             dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
             self.engine.nccl_init(box[0], self.rank, self.world)
+        # peer-memory halo (b2_peer_*): boundary positions are stored straight into the neighbours'
+        # HBM over NVLink and the all-reduce is a mailbox wait: no library call per step.
+        # Needs the C path's set-up (NCCL backend, one rank per GPU); connected at the first refresh.
+        if peer is None:
+            peer = self._fast
+        self._peer = bool(peer) and self._fast
+        self._peer_cap = 0
         self._resident = False
         self._batch = 8
         self.refreshes = 0
@@ -207,6 +214,28 @@ class SlabDomain(object):
         if self._fast:
             self.engine.nccl_set_halo(self._send_l.data_ptr(), len(self._send_l), self._send_r.data_ptr(),
                                       len(self._send_r), self._n_gl, self._n_gr)
+        if self._peer:
+            need = torch.tensor([max(len(self._send_l), len(self._send_r), self._n_gl, self._n_gr)],
+                                dtype=torch.int64, device=self.dev)
+            dist.all_reduce(need, op=dist.ReduceOp.MAX, group=self.group)
+            need = int(need)
+            if self._peer_cap == 0:
+                # mailboxes sized once, with headroom for density fluctuations; handles travel by all_gather
+                self._peer_cap = need + need // 2 + 4096
+                try:
+                    mine = self.engine.peer_export(self._peer_cap, self.rank, self.world)
+                    handles = [None] * self.world
+                    dist.all_gather_object(handles, mine, group=self.group)
+                    self.engine.peer_connect(handles)
+                    ok = 1
+                except capi.B2Error:
+                    ok = 0
+                flag = torch.tensor([ok], dtype=torch.int64, device=self.dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+                if int(flag) == 0:
+                    self._peer = False              # no peer access on this box: stay on NCCL
+            elif need > self._peer_cap:
+                self._peer = False                  # (same decision on every rank)
         self._resident = True
         self.refreshes += 1
 
@@ -255,7 +284,9 @@ class SlabDomain(object):
                     self._vmax[:1].copy_(v)
                 eng.dd_commit(self._vmax.data_ptr())
                 self._halo()
-            if self._fast:
+            if self._peer:
+                eng.peer_run(m)
+            elif self._fast:
                 eng.nccl_run(m)
             done, need = eng.dd_poll()
             since_refresh += done

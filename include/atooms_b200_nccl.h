@@ -33,6 +33,25 @@ int b2_nccl_set_halo(b2_ctx *ctx, const int32_t *send_l_dev, int64_t n_send_l,
  * returns without waiting.  Every rank must call it with the same count.       */
 int b2_nccl_run(b2_ctx *ctx, int64_t count);
 
+/* ---- peer-memory halo: the same per-step sequence without a communication library ----
+ *
+ * Each rank owns a mailbox block in its own HBM (b2_peer_export returns its 64-byte CUDA
+ * IPC handle); after the caller has gathered every rank's handle, b2_peer_connect maps
+ * the others' blocks.  b2_peer_run then enqueues, per step,
+ *     fused step kernel, which stores this rank's max |v|^2 into every rank's mailbox
+ *     -> a one-warp kernel that waits for all ranks' values (the all-reduce) and commits
+ *     -> a kernel that gathers the boundary positions straight INTO the two neighbours'
+ *        inboxes over NVLink and raises their arrival flags
+ *     -> a kernel that waits for both neighbours' flags and scatters its inbox into the ghosts
+ * i.e. 4 launches and no library call per step (NCCL path: 8 launches, two of them
+ * collectives).  One rank per GPU is required (kernels of different ranks wait on each
+ * other).  `halo_capacity` (records per inbox, the same on every rank) must cover
+ * b2_nccl_set_halo's counts, which describes the halo for this path too.  Waits time out
+ * after ~10 s and surface through b2_dd_poll.                                            */
+int b2_peer_export(b2_ctx *ctx, int64_t halo_capacity, int rank, int nranks, char handle_out[64]);
+int b2_peer_connect(b2_ctx *ctx, const char *handles /* nranks x 64 bytes, by rank */);
+int b2_peer_run(b2_ctx *ctx, int64_t count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,8 @@ from test_dd_gloo import global_system, ROOT
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, port, steps, precision, backend, fast, out):
+def _worker(rank, world, port, steps, precision, backend, mode, out):
+    fast, peer = mode != 'torch', mode == 'peer'
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
     ngpu = torch.cuda.device_count()
@@ -31,11 +32,12 @@ def _worker(rank, world, port, steps, precision, backend, fast, out):
     slab = numpy.clip(numpy.floor((pos[:, 0] / side[0] + 0.5) * world).astype(int), 0, world - 1)
     mine = numpy.nonzero(slab == rank)[0]
     dom = SlabDomain(pos[mine], vel[mine], spe[mine], side, model='kob_andersen', dt=0.002, skin=0.3,
-                     precision=precision, gid=mine, fast_comm=fast)
+                     precision=precision, gid=mine, fast_comm=fast, peer=peer)
     assert dom.engine.lib.name == 'cuda-sm_100a' and dom._fast == fast
     t0 = dom.thermo()
     dom.run(steps)
     t1 = dom.thermo()
+    assert dom._peer == peer, 'the peer-memory halo fell back to NCCL'
     gpos, gvel, gimg = dom.gather()
     if rank == 0:
         numpy.savez(out, pos=gpos, vel=gvel, img=gimg, e0=t0['kinetic'] + t0['potential'],
@@ -44,18 +46,19 @@ def _worker(rank, world, port, steps, precision, backend, fast, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('fast', [False, True], ids=['torch.distributed', 'nccl-in-C'])
+@pytest.mark.parametrize('mode', ['torch', 'nccl', 'peer'])
 @pytest.mark.parametrize('precision', [64, 32])
-def test_two_rank_slab_run_on_cuda(precision, fast, tmp_path, cuda_lib):
+def test_two_rank_slab_run_on_cuda(precision, mode, tmp_path, cuda_lib):
+    fast = mode != 'torch' 
     from conftest import make_engine
     from oracle import oracle_np as onp
     steps, world = 120, 2
     backend = 'nccl' if torch.cuda.device_count() >= 2 else 'gloo'
     if fast and backend != 'nccl':
-        pytest.skip('the NCCL fast path needs two GPUs')
+        pytest.skip('the C-side communication paths need two GPUs')
     out = str(tmp_path / 'dd.npz')
-    port = 29500 + (os.getpid() + precision + 7 * int(fast)) % 2000
-    mp.spawn(_worker, args=(world, port, steps, precision, backend, fast, out), nprocs=world, join=True)
+    port = 29500 + (os.getpid() + precision + 7 * len(mode)) % 2000
+    mp.spawn(_worker, args=(world, port, steps, precision, backend, mode, out), nprocs=world, join=True)
     got = numpy.load(out)
     pos, vel, spe, side = global_system()
     ref = make_engine(cuda_lib, {'position': pos, 'velocity': vel, 'species': spe, 'side': side,
