@@ -406,6 +406,19 @@ class Engine(object):
         self._call('b2_nccl_run', int(count))
 
 
+    # -- peer-memory halo (CUDA library only, one rank per GPU) ---------------------------------
+    def peer_export(self, halo_capacity, rank, nranks):
+        buf = ctypes.create_string_buffer(64)
+        self._call('b2_peer_export', int(halo_capacity), int(rank), int(nranks), buf)
+        return buf.raw
+
+    def peer_connect(self, handles):
+        self._call('b2_peer_connect', ctypes.c_char_p(b''.join(handles)))
+
+    def peer_run(self, count):
+        self._call('b2_peer_run', int(count))
+
+
 class Batch(object):
 
     """An ensemble of small independent replicas sharing cell and pair table
@@ -466,15 +479,3 @@ class Batch(object):
         frc = numpy.empty((self.nrep, self.n, 3)) if forces else None
         self._call('b2_batch_download', _dp(pos), _dp(frc))
         return (pos, frc) if forces else pos
-
-    # -- peer-memory halo (CUDA library only, one rank per GPU) ---------------------------------
-    def peer_export(self, halo_capacity, rank, nranks):
-        buf = ctypes.create_string_buffer(64)
-        self._call('b2_peer_export', int(halo_capacity), int(rank), int(nranks), buf)
-        return buf.raw
-
-    def peer_connect(self, handles):
-        self._call('b2_peer_connect', ctypes.c_char_p(b''.join(handles)))
-
-    def peer_run(self, count):
-        self._call('b2_peer_run', int(count))

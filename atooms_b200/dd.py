@@ -71,7 +71,7 @@ class SlabDomain(object):
         self.spe = torch.as_tensor(numpy.asarray(species, dtype=numpy.int32)).to(self.dev)
         self.gid = torch.arange(n, dtype=torch.int64, device=self.dev) if gid is None else \
             torch.as_tensor(numpy.asarray(gid, dtype=numpy.int64)).to(self.dev)
-        self.img = torch.zeros((n, 3), dtype=torch.int64, device=self.dev)
+        self.img = torch.zeros((n, 3), dtype=torch.int32, device=self.dev)
         self._vmax = torch.zeros(2, dtype=torch.float32, device=self.dev)
         # NCCL fast path: the per-step sequence (step, all-reduce, commit, pack, send/recv,
         # unpack) enqueued from C (b2_nccl_run) instead of one Python round trip per collective
@@ -92,6 +92,7 @@ class SlabDomain(object):
             peer = self._fast
         self._peer = bool(peer) and self._fast
         self._peer_cap = 0
+        self.profile = None
         self._resident = False
         self._batch = 8
         self.refreshes = 0
@@ -131,36 +132,50 @@ class SlabDomain(object):
             req.wait()
         return from_left[:n_from_left].to(self.dev), from_right[:n_from_right].to(self.dev)
 
+    def _tick(self, name):
+        """Phase timer of refresh() (only when self.profile is a dict; synchronises)."""
+        if self.profile is None:
+            return
+        import time
+        if self.dev.type == 'cuda':
+            torch.cuda.synchronize(self.dev)
+        now = time.perf_counter()
+        if name is not None:
+            self.profile[name] = self.profile.get(name, 0.0) + (now - self._t_last) * 1e3
+        self._t_last = now
+
     # -- refresh: migration + ghost selection + re-upload ---------------------------------
     def refresh(self):
+        self._tick(None)
+        side = torch.as_tensor(self.side, dtype=torch.float64, device=self.dev)
+        ctr = torch.as_tensor(self.center, dtype=torch.float64, device=self.dev)
         if self._resident:
             n = self.n_own
             img = torch.empty((self.engine.n, 3), dtype=torch.int32, device=self.dev)
             pos = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
             vel = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
             self.engine.download_device(pos.data_ptr(), vel.data_ptr(), img.data_ptr())
-            self.pos, self.vel = pos[:n].clone(), vel[:n].clone()
-            self.img += img[:n].to(torch.int64)
-        side = torch.as_tensor(self.side, dtype=torch.float64, device=self.dev)
-        ctr = torch.as_tensor(self.center, dtype=torch.float64, device=self.dev)
-        # fold into the global cell (atooms/system/particle.py:90-99)
-        rel = self.pos - ctr
-        k = torch.round(rel / side)
-        rel = rel - k * side
-        if self._resident:          # like b2_upload, the fold of the INITIAL coordinates is not a crossing
-            self.img += k.to(torch.int64)
-        self.pos = rel + ctr
-        # which slab owns each particle now
-        u = rel[:, 0] / side[0] + 0.5
+            self.pos, self.vel = pos[:n], vel[:n]          # already folded into the global cell
+            self.img += img[:n]
+        else:
+            # fold the initial coordinates (atooms/system/particle.py:90-99); like b2_upload,
+            # this fold is not counted as a box crossing
+            rel = self.pos - ctr
+            self.pos = rel - torch.round(rel / side) * side + ctr
+        self._tick('download')
+        # which slab owns each particle now; only the few that changed slab are looked at further
+        u = (self.pos[:, 0] - ctr[0]) / side[0] + 0.5
         slab = torch.clamp(torch.floor(u * self.world).to(torch.int64), 0, self.world - 1)
-        hop = (slab - self.rank + self.world // 2) % self.world - self.world // 2 if self.world > 1 else slab * 0
-        if self.world == 2:
-            hop = torch.where(slab != self.rank, torch.ones_like(hop), hop)    # either way round the ring
-        if self.world > 1 and int(hop.abs().max()) > 1:
-            raise RuntimeError('a particle moved more than one slab between two refreshes')
-        # migrants are a tiny fraction: move only their rows, keep the rest in place
-        idx_l = torch.nonzero(hop == -1).flatten()
-        idx_r = torch.nonzero(hop == 1).flatten()
+        moved = torch.nonzero(slab != self.rank).flatten()
+        hop = slab[moved] - self.rank
+        if self.world > 2:
+            hop = (hop + self.world // 2) % self.world - self.world // 2
+            if moved.numel() and int(hop.abs().max()) > 1:
+                raise RuntimeError('a particle moved more than one slab between two refreshes')
+        else:
+            hop = torch.ones_like(hop)                    # two ranks: either way round the ring
+        idx_l, idx_r = moved[hop == -1], moved[hop == 1]
+        self._tick('classify')
 
         def payload(idx):
             return torch.cat([self.pos[idx], self.vel[idx], self.mass[idx, None],
@@ -172,7 +187,7 @@ class SlabDomain(object):
             if gone or from_l.shape[0] or from_r.shape[0]:
                 new = torch.cat([from_l, from_r], dim=0)
                 if gone:
-                    keep = torch.nonzero(hop == 0).flatten()
+                    keep = torch.nonzero(slab == self.rank).flatten()
                     sel = lambda t: t[keep]
                 else:
                     sel = lambda t: t
@@ -181,7 +196,8 @@ class SlabDomain(object):
                 self.mass = torch.cat([sel(self.mass), new[:, 6]], dim=0)
                 self.gid = torch.cat([sel(self.gid), new[:, 7].round().to(torch.int64)], dim=0)
                 self.spe = torch.cat([sel(self.spe), new[:, 8].round().to(torch.int32)], dim=0)
-                self.img = torch.cat([sel(self.img), new[:, 9:12].round().to(torch.int64)], dim=0)
+                self.img = torch.cat([sel(self.img), new[:, 9:12].round().to(torch.int32)], dim=0)
+        self._tick('migrate')
         n = self.n_own
         # ghosts: owned particles within r_list of a face are copied to the neighbour beyond it
         if self.world > 1:
@@ -196,6 +212,7 @@ class SlabDomain(object):
         else:
             g_from_l = g_from_r = self.pos.new_zeros((0, 4))
             self._send_l = self._send_r = torch.zeros(0, dtype=torch.int32, device=self.dev)
+        self._tick('ghosts')
         self._n_gl, self._n_gr = g_from_l.shape[0], g_from_r.shape[0]
         ghosts = torch.cat([g_from_l, g_from_r], dim=0)
         ng = ghosts.shape[0]
@@ -204,38 +221,38 @@ class SlabDomain(object):
         mass = torch.cat([self.mass, self.mass.new_ones(ng)], dim=0).contiguous()
         spe = torch.cat([self.spe, ghosts[:, 3].round().to(torch.int32) | capi.GHOST], dim=0).contiguous()
         self.engine.upload_device(n + ng, pos.data_ptr(), spe.data_ptr(), vel.data_ptr(), mass.data_ptr())
-        # halo buffers of the new shape
-        f64 = dict(dtype=torch.float64, device=self.dev)
-        self._out_l = torch.zeros((max(len(self._send_l), 1), 3), **f64)
-        self._out_r = torch.zeros((max(len(self._send_r), 1), 3), **f64)
-        self._in_l = torch.zeros((max(self._n_gl, 1), 3), **f64)
-        self._in_r = torch.zeros((max(self._n_gr, 1), 3), **f64)
+        self._tick('upload')
+        if not self._fast:          # halo buffers of the generic (torch.distributed) path
+            f64 = dict(dtype=torch.float64, device=self.dev)
+            self._out_l = torch.zeros((max(len(self._send_l), 1), 3), **f64)
+            self._out_r = torch.zeros((max(len(self._send_r), 1), 3), **f64)
+            self._in_l = torch.zeros((max(self._n_gl, 1), 3), **f64)
+            self._in_r = torch.zeros((max(self._n_gr, 1), 3), **f64)
         self.halo_bytes_per_step = 24 * (len(self._send_l) + len(self._send_r))
         if self._fast:
             self.engine.nccl_set_halo(self._send_l.data_ptr(), len(self._send_l), self._send_r.data_ptr(),
                                       len(self._send_r), self._n_gl, self._n_gr)
-        if self._peer:
+        if self._peer and self._peer_cap == 0:
+            # mailboxes are sized once, from the largest halo of any rank plus 50 % headroom for
+            # density fluctuations (b2_peer_run refuses a halo that outgrows them); the IPC
+            # handles travel by all_gather
             need = torch.tensor([max(len(self._send_l), len(self._send_r), self._n_gl, self._n_gr)],
                                 dtype=torch.int64, device=self.dev)
             dist.all_reduce(need, op=dist.ReduceOp.MAX, group=self.group)
-            need = int(need)
-            if self._peer_cap == 0:
-                # mailboxes sized once, with headroom for density fluctuations; handles travel by all_gather
-                self._peer_cap = need + need // 2 + 4096
-                try:
-                    mine = self.engine.peer_export(self._peer_cap, self.rank, self.world)
-                    handles = [None] * self.world
-                    dist.all_gather_object(handles, mine, group=self.group)
-                    self.engine.peer_connect(handles)
-                    ok = 1
-                except capi.B2Error:
-                    ok = 0
-                flag = torch.tensor([ok], dtype=torch.int64, device=self.dev)
-                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
-                if int(flag) == 0:
-                    self._peer = False              # no peer access on this box: stay on NCCL
-            elif need > self._peer_cap:
-                self._peer = False                  # (same decision on every rank)
+            self._peer_cap = int(need) + int(need) // 2 + 4096
+            try:
+                mine = self.engine.peer_export(self._peer_cap, self.rank, self.world)
+                handles = [None] * self.world
+                dist.all_gather_object(handles, mine, group=self.group)
+                self.engine.peer_connect(handles)
+                ok = 1
+            except capi.B2Error:
+                ok = 0
+            flag = torch.tensor([ok], dtype=torch.int64, device=self.dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+            if int(flag) == 0:
+                self._peer = False              # no peer access on this box: stay on NCCL
+        self._tick('halo setup')
         self._resident = True
         self.refreshes += 1
 
@@ -327,7 +344,7 @@ class SlabDomain(object):
             vel = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
             img = torch.empty((self.engine.n, 3), dtype=torch.int32, device=self.dev)
             self.engine.download_device(pos.data_ptr(), vel.data_ptr(), img.data_ptr())
-            pos, vel, img = pos[:n], vel[:n], self.img + img[:n].to(torch.int64)
+            pos, vel, img = pos[:n], vel[:n], self.img + img[:n]
         else:
             pos, vel, img = self.pos, self.vel, self.img
         mine = torch.cat([self.gid[:, None].to(torch.float64), pos, vel, img.to(torch.float64)], dim=1).cpu()

@@ -208,17 +208,17 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(n, inner, world=1, halo_bytes=0):
+def workload_config(n, inner, world=1, halo_bytes=0, comm=None):
     cfg = {'workload': 'Kob-Andersen 80:20 N=%d rho=1.2 NVE velocity-Verlet dt=0.002, LJ cut&shifted 2.5 sigma_ab, '
                        'Verlet skin 0.3 (BASELINE.json configs[2], SURVEY.md 8d C3)' % (n * world),
            'particles_per_gpu': n, 'md_timesteps_per_step': inner,
            'cache': 'inputs larger than L2 (neighbour list ~0.8 GB per GPU vs 126 MB L2)'}
     if world > 1:
         cfg['decomposition'] = ('one periodic box of %d x 1.2M particles, %d slabs along x, ring halo exchange '
-                                '(NCCL send/recv) + 4-byte all_reduce per step, migration at list refresh'
+                                '+ 4-byte max-reduction per step, migration at list refresh'
                                 % (world, world))
         cfg['halo_bytes_per_step_per_gpu'] = int(halo_bytes)
-        cfg['comm'] = 'NCCL send/recv + all-reduce enqueued from C (b2_nccl_run)'
+        cfg['comm'] = comm
     return cfg
 
 
@@ -341,7 +341,9 @@ def main():
                                       e2e=ntot * INNER * e2e_steps / e2e_s, e2e_steps=e2e_steps,
                                       stats=dom.engine.stats(), energy=(th['kinetic'] + th['potential']) / ntot,
                                       h2d=h2d // e2e_steps, d2h=d2h // e2e_steps, ntot=ntot,
-                                      halo_bytes=dom.halo_bytes_per_step, fast_comm=dom._fast)
+                                      halo_bytes=dom.halo_bytes_per_step,
+                                      comm='peer-memory mailboxes over NVLink (b2_peer_run)' if dom._peer else
+                                      ('NCCL enqueued from C (b2_nccl_run)' if dom._fast else 'torch.distributed'))
             dom.close()
             continue
         eng = make_engine(lib, precision, pos, spe, side, vel, device=local_rank)
@@ -419,7 +421,7 @@ def main():
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': r['ms'] / args.steps, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32' if args.precision == 32 else 'f64', 'data': 'synthetic',
-            'config': workload_config(n, INNER, world, r['halo_bytes']),
+            'config': workload_config(n, INNER, world, r['halo_bytes'], r.get('comm')),
             'e2e': {'value': r['e2e'], 'unit': 'particle-timesteps/s',
                     'h2d_bytes_per_step': int(r['h2d']), 'd2h_bytes_per_step': int(r['d2h']),
                     'steps': r['e2e_steps']},

@@ -23,7 +23,7 @@ def timed(f, reps=5):
 t_ref = timed(dom.refresh)
 eng = dom.engine
 eng.dd_begin(10**9, dom.dt, False)
-t_step = timed(lambda: eng.nccl_run(10), 10) / 10
+t_step = timed(lambda: (eng.peer_run(10) if dom._peer else eng.nccl_run(10)), 10) / 10
 def only_kernels():
     for _ in range(10):
         eng.dd_step(dom._vmax.data_ptr()); eng.dd_commit(dom._vmax.data_ptr())
@@ -32,17 +32,15 @@ t_poll = timed(lambda: eng.dd_poll(), 20)
 if rank == 0:
     print('refresh %.2f ms | dd step with comm %.3f ms | step+commit only %.3f ms | poll %.3f ms | batch %d' % (t_ref, t_step, t_kern, t_poll, dom._batch))
 # refresh breakdown
-import types
+dom.profile = {}
+for _ in range(5): dom.refresh()
+if rank == 0:
+    print('peer %s fast %s' % (dom._peer, dom._fast))
+    for k, v in dom.profile.items(): print('   %-12s %.3f ms' % (k, v / 5))
+dom.profile = None
 def phase(name, f):
     torch.cuda.synchronize(); t = time.perf_counter(); r = f(); torch.cuda.synchronize()
     if rank == 0: print('   %-28s %.2f ms' % (name, (time.perf_counter() - t) * 1e3))
     return r
-N = eng.n
-pos_t = torch.empty((N, 3), dtype=torch.float64, device=dom.dev); vel_t = torch.empty_like(pos_t); img_t = torch.empty((N, 3), dtype=torch.int32, device=dom.dev)
-phase('download_device', lambda: eng.download_device(pos_t.data_ptr(), vel_t.data_ptr(), img_t.data_ptr()))
-spe_t = torch.cat([dom.spe, torch.zeros(N - dom.n_own, dtype=torch.int32, device=dom.dev) | 256])
-mass_t = torch.ones(N, dtype=torch.float64, device=dom.dev)
-phase('upload_device', lambda: eng.upload_device(N, pos_t.data_ptr(), spe_t.data_ptr(), vel_t.data_ptr(), mass_t.data_ptr()))
 phase('dd_begin (list build)', lambda: eng.dd_begin(100, dom.dt, False))
-phase('payload cat', lambda: torch.cat([dom.pos, dom.vel, dom.mass[:, None], dom.gid[:, None].to(torch.float64), dom.spe[:, None].to(torch.float64), dom.img.to(torch.float64)], dim=1))
 dist.barrier(); dist.destroy_process_group()
