@@ -52,8 +52,21 @@ class ReplicaEnsemble(object):
         self.result = self.batch.minimize(capi.MIN_FIRE if method == 'fire' else capi.MIN_SD, steps, dt, tolerance)
         return self.result
 
+    def set_velocities(self, velocity):
+        """velocity (nrep, n, 3) of ALL replicas (this rank keeps its share)."""
+        self.batch.set_velocities(numpy.asarray(velocity, dtype=numpy.float64)[self.index])
+
+    def run_nve(self, steps, dt=0.002):
+        """`steps` velocity-Verlet steps of every replica in one kernel launch; returns
+        per-replica kinetic / potential energy and virial of the final configuration."""
+        self.result = self.batch.run_nve(steps, dt)
+        return self.result
+
     def positions(self):
         return self.batch.download()
+
+    def velocities(self):
+        return self.batch.state()[0]
 
     def close(self):
         self.batch.close()

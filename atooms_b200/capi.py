@@ -77,6 +77,9 @@ SYMBOLS = {
     'b2_batch_upload': (_int, [_vp, _i64, _int, _c_dp, _c_ip, _c_dp]),
     'b2_batch_minimize': (_int, [_vp, _int, _i64, _dbl, _dbl, _c_lp, ctypes.POINTER(_int), _c_dp, _c_dp, _c_dp]),
     'b2_batch_download': (_int, [_vp, _c_dp, _c_dp]),
+    'b2_batch_set_velocities': (_int, [_vp, _c_dp]),
+    'b2_batch_run_nve': (_int, [_vp, _i64, _dbl, _c_dp, _c_dp, _c_dp]),
+    'b2_batch_get_state': (_int, [_vp, _c_dp, _c_ip]),
 }
 
 
@@ -473,6 +476,23 @@ class Batch(object):
         self._call('b2_batch_minimize', int(method), int(max_steps), float(dt), float(fn2_tol),
                    steps.ctypes.data_as(_c_lp), conv.ctypes.data_as(ctypes.POINTER(_int)), _dp(energy), _dp(fn2), _dp(virial))
         return {'steps': steps, 'converged': conv.astype(bool), 'energy': energy, 'fn2': fn2, 'virial': virial}
+
+    def set_velocities(self, velocity):
+        vel = numpy.ascontiguousarray(velocity, dtype=numpy.float64)
+        if vel.shape != (self.nrep, self.n, 3):
+            raise ValueError('velocity must be (nrep, n, 3)')
+        self._call('b2_batch_set_velocities', _dp(vel))
+
+    def run_nve(self, steps, dt):
+        kin, energy, virial = numpy.zeros(self.nrep), numpy.zeros(self.nrep), numpy.zeros(self.nrep)
+        self._call('b2_batch_run_nve', int(steps), float(dt), _dp(kin), _dp(energy), _dp(virial))
+        return {'kinetic': kin, 'energy': energy, 'virial': virial}
+
+    def state(self):
+        vel = numpy.empty((self.nrep, self.n, 3))
+        img = numpy.empty((self.nrep, self.n, 3), dtype=numpy.int32)
+        self._call('b2_batch_get_state', _dp(vel), _ip(img))
+        return vel, img
 
     def download(self, forces=False):
         pos = numpy.empty((self.nrep, self.n, 3))

@@ -15,8 +15,7 @@
 
 template <typename R> struct BatchArgs {
     typename Pos4<R>::type *pos;        // [nrep][n]
-    const typename Vec4<R>::type *vel0; // unused (minimisers start at rest)
-    const R *mass;                      // [nrep][n]
+    const typename Vec4<R>::type *vel;  // [nrep][n]: .w is the mass
     int n, nrep;
     Box<R> box;
     int method;                         // MIN_MODE_FIRE / MIN_MODE_SD
@@ -71,7 +70,7 @@ __global__ void k_batch_minimize(BatchArgs<R> a)
     const bool own = i < n;
     P4 *gpos = a.pos + (size_t)rep * n;
     P4 p = own ? gpos[i] : P4();
-    const R m = own ? a.mass[(size_t)rep * n + i] : (R)1;
+    const R m = own ? a.vel[(size_t)rep * n + i].w : (R)1;
     const int ti = own ? ptype(p) * nsp : 0;
     R vx = 0, vy = 0, vz = 0;             // FIRE velocity, or the previous gradient for SD
     R fx = 0, fy = 0, fz = 0;
@@ -170,10 +169,127 @@ __global__ void k_batch_minimize(BatchArgs<R> a)
     }
 }
 
+// all-pairs force on particle i of a replica whose positions sit in shared memory
+template <typename R>
+__device__ __forceinline__ void batch_force(const typename Pos4<R>::type *s_pos, int n, int i,
+                                            const typename Pos4<R>::type &p, int ti, const Box<R> &box,
+                                            const R *s_c12x12, const R *s_c6x6, const R *s_rc2,
+                                            R &fx, R &fy, R &fz)
+{
+    fx = fy = fz = 0;
+    for (int j = 0; j < n; j++) {
+        if (j == i) continue;
+        const typename Pos4<R>::type q = s_pos[j];
+        R dx, dy, dz;
+        delta(p, q, box, dx, dy, dz);
+        const R r2 = dx * dx + dy * dy + dz * dz;
+        const int t = ti + ptype(q);
+        const R r2inv = r_rcp(r2);
+        const R r6inv = r2inv * r2inv * r2inv;
+        R fp = r6inv * (s_c12x12[t] * r6inv - s_c6x6[t]) * r2inv;
+        fp = r2 < s_rc2[t] ? fp : (R)0;
+        fx += fp * dx; fy += fp * dy; fz += fp * dz;
+    }
+}
+
+template <typename R> struct BatchNveArgs {
+    typename Pos4<R>::type *pos;        // [nrep][n]
+    typename Vec4<R>::type *vel;        // [nrep][n] (vx, vy, vz, mass)
+    typename Vec4<R>::type *frc;        // [nrep][n] forces of the final configuration (+ pe_i)
+    int *img;                           // [nrep][n][3] box crossings, accumulated
+    int n, nrep;
+    Box<R> box;
+    long long steps;
+    double dt;
+    double *kinetic, *energy, *virial;  // [nrep] of the final configuration
+};
+
+// `steps` velocity-Verlet steps of every replica in ONE launch: kick-drift form
+// exactly as in k_step_nve (opening half kick, identical steps, closing half kick),
+// two block barriers per step, nothing leaves the SM until the end.
+template <typename R>
+__global__ void k_batch_nve(BatchNveArgs<R> a)
+{
+    typedef typename Pos4<R>::type P4;
+    typedef typename Vec4<R>::type V4;
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    P4 *s_pos = reinterpret_cast<P4 *>(s_raw);
+    __shared__ double s_red[32];
+    __shared__ R s_c12x12[B2_MAXSP * B2_MAXSP], s_c6x6[B2_MAXSP * B2_MAXSP], s_rc2[B2_MAXSP * B2_MAXSP];
+    for (int k = threadIdx.x; k < B2_MAXSP * B2_MAXSP; k += blockDim.x) {
+        s_c12x12[k] = (R)(12.0 * g_pair.c12[k]);
+        s_c6x6[k] = (R)(6.0 * g_pair.c6[k]);
+        s_rc2[k] = (R)g_pair.rc2[k];
+    }
+    const int rep = blockIdx.x, i = threadIdx.x, n = a.n, nsp = g_pair.nsp;
+    const bool own = i < n;
+    const size_t g = (size_t)rep * n + i;
+    P4 p = own ? a.pos[g] : P4();
+    V4 v = own ? a.vel[g] : make4((R)0, (R)0, (R)0, (R)1);
+    const int ti = own ? ptype(p) * nsp : 0;
+    const R dt = (R)a.dt, hdt = (R)(0.5 * a.dt);
+    int ix = 0, iy = 0, iz = 0;
+    R fx = 0, fy = 0, fz = 0;
+    if (own) s_pos[i] = p;
+    __syncthreads();
+    if (own) batch_force<R>(s_pos, n, i, p, ti, a.box, s_c12x12, s_c6x6, s_rc2, fx, fy, fz);
+    if (a.steps > 0) {
+        R s = hdt / v.w;
+        v.x -= s * fx; v.y -= s * fy; v.z -= s * fz;            // velocities to t - dt/2
+        for (long long step = 0; step < a.steps; step++) {
+            s = dt / v.w;
+            v.x += s * fx; v.y += s * fy; v.z += s * fz;
+            if (own) {
+                int kx, ky, kz;
+                p = advance(p, dt * v.x, dt * v.y, dt * v.z, a.box, kx, ky, kz);
+                ix += kx; iy += ky; iz += kz;
+            }
+            __syncthreads();                                    // everybody has read the old positions
+            if (own) s_pos[i] = p;
+            __syncthreads();
+            if (own) batch_force<R>(s_pos, n, i, p, ti, a.box, s_c12x12, s_c6x6, s_rc2, fx, fy, fz);
+        }
+        s = hdt / v.w;
+        v.x += s * fx; v.y += s * fy; v.z += s * fz;            // closing half kick
+    }
+    // final configuration: fp64 energy, virial, kinetic energy
+    double pe = 0, vir = 0, kin = 0;
+    if (own) {
+        for (int j = 0; j < n; j++) {
+            if (j == i) continue;
+            double ex, ey, ez;
+            delta_d(p, s_pos[j], a.box, ex, ey, ez);
+            const double q2 = ex * ex + ey * ey + ez * ez;
+            const int t = ti + ptype(s_pos[j]);
+            if (q2 < g_pair.rc2[t]) {
+                const double q2inv = 1.0 / q2, q6inv = q2inv * q2inv * q2inv;
+                pe += q6inv * (g_pair.c12[t] * q6inv - g_pair.c6[t]) - g_pair.ushift[t];
+                vir += q6inv * (12.0 * g_pair.c12[t] * q6inv - 6.0 * g_pair.c6[t]);
+            }
+        }
+        const double vx = v.x, vy = v.y, vz = v.z;
+        kin = 0.5 * (double)v.w * ((vx * vx + vy * vy) + vz * vz);
+        a.pos[g] = p;
+        a.vel[g] = v;
+        a.frc[g] = make4(fx, fy, fz, (R)(0.5 * pe));
+        int *im = a.img + 3 * g;
+        im[0] += ix; im[1] += iy; im[2] += iz;
+    }
+    const double e_tot = block_sum(0.5 * pe, s_red);
+    const double w_tot = block_sum(0.5 * vir, s_red);
+    const double k_tot = block_sum(kin, s_red);
+    if (threadIdx.x == 0) {
+        a.energy[rep] = e_tot;
+        a.virial[rep] = w_tot;
+        a.kinetic[rep] = k_tot;
+    }
+}
+
 template <typename R>
 __global__ void k_batch_ingest(const double *__restrict__ spos, const double *__restrict__ smass,
                                const int *__restrict__ sspe, long long tot, Box<R> box,
-                               typename Pos4<R>::type *__restrict__ pos, R *__restrict__ mass)
+                               typename Pos4<R>::type *__restrict__ pos,
+                               typename Vec4<R>::type *__restrict__ vel, int *__restrict__ img)
 {
     long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= tot) return;
@@ -182,7 +298,8 @@ __global__ void k_batch_ingest(const double *__restrict__ spos, const double *__
     y -= rint(y / box.Ld[1]) * box.Ld[1];
     z -= rint(z / box.Ld[2]) * box.Ld[2];
     pos[k] = encode_pos(x, y, z, sspe[k], box);
-    mass[k] = (R)(smass ? smass[k] : 1.0);
+    vel[k] = make4((R)0, (R)0, (R)0, (R)(smass ? smass[k] : 1.0));
+    img[3 * k] = img[3 * k + 1] = img[3 * k + 2] = 0;
 }
 
 template <typename R>
@@ -201,4 +318,24 @@ __global__ void k_batch_export(const typename Pos4<R>::type *__restrict__ pos,
         typename Vec4<R>::type f = frc[k];
         ofrc[3 * k] = f.x; ofrc[3 * k + 1] = f.y; ofrc[3 * k + 2] = f.z;
     }
+}
+
+template <typename R>
+__global__ void k_batch_set_vel(const double *__restrict__ svel, long long tot,
+                                typename Vec4<R>::type *__restrict__ vel)
+{
+    long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= tot) return;
+    typename Vec4<R>::type v = vel[k];
+    vel[k] = make4((R)svel[3 * k], (R)svel[3 * k + 1], (R)svel[3 * k + 2], v.w);
+}
+
+template <typename R>
+__global__ void k_batch_get_vel(const typename Vec4<R>::type *__restrict__ vel, long long tot,
+                                double *__restrict__ ovel)
+{
+    long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= tot) return;
+    typename Vec4<R>::type v = vel[k];
+    ovel[3 * k] = v.x; ovel[3 * k + 1] = v.y; ovel[3 * k + 2] = v.z;
 }

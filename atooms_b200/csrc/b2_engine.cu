@@ -1585,7 +1585,8 @@ struct b2_batch {
     uint64_t const_serial = 0;
     int64_t nrep = 0;
     int n = 0;
-    void *pos = nullptr, *frc = nullptr, *mass = nullptr;
+    void *pos = nullptr, *frc = nullptr, *vel = nullptr;   // vel: (vx, vy, vz, mass)
+    int *img = nullptr;
     double *stage = nullptr;
     int *stage_i = nullptr;
     long long *d_steps = nullptr;
@@ -1609,13 +1610,14 @@ template <typename R> struct BatchImpl {
     {
         b2_ctx *c = nullptr;
         const size_t tot = (size_t)nrep * n;
-        void *old[] = {b->pos, b->frc, b->mass, b->stage, b->stage_i, b->d_steps, b->d_conv, b->d_out};
+        void *old[] = {b->pos, b->frc, b->vel, b->img, b->stage, b->stage_i, b->d_steps, b->d_conv, b->d_out};
         for (void *p : old) if (p) cudaFree(p);
-        b->pos = b->frc = b->mass = nullptr; b->stage = nullptr; b->stage_i = nullptr;
+        b->pos = b->frc = b->vel = nullptr; b->img = nullptr; b->stage = nullptr; b->stage_i = nullptr;
         b->d_steps = nullptr; b->d_conv = nullptr; b->d_out = nullptr;
         CU(cudaMalloc(&b->pos, std::max<size_t>(tot, 1) * sizeof(P4)));
         CU(cudaMalloc(&b->frc, std::max<size_t>(tot, 1) * sizeof(V4)));
-        CU(cudaMalloc(&b->mass, std::max<size_t>(tot, 1) * sizeof(R)));
+        CU(cudaMalloc(&b->vel, std::max<size_t>(tot, 1) * sizeof(V4)));
+        CU(cudaMalloc((void **)&b->img, std::max<size_t>(tot, 1) * 3 * sizeof(int)));
         CU(cudaMalloc((void **)&b->stage, std::max<size_t>(tot, 1) * 4 * sizeof(double)));
         CU(cudaMalloc((void **)&b->stage_i, std::max<size_t>(tot, 1) * sizeof(int)));
         CU(cudaMalloc((void **)&b->d_steps, std::max<int64_t>(nrep, 1) * sizeof(long long)));
@@ -1628,7 +1630,7 @@ template <typename R> struct BatchImpl {
         if (mass) CU(cudaMemcpy(b->stage + 3 * tot, mass, tot * sizeof(double), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(b->stage_i, species, tot * sizeof(int), cudaMemcpyHostToDevice));
         k_batch_ingest<R><<<cdiv(tot, 256), 256>>>(b->stage, mass ? b->stage + 3 * tot : nullptr, b->stage_i, (long long)tot,
-                                                  box_of(b), (P4 *)b->pos, (R *)b->mass);
+                                                  box_of(b), (P4 *)b->pos, (V4 *)b->vel, b->img);
         b->launches++;
         CU(cudaDeviceSynchronize());
         return B2_OK;
@@ -1645,8 +1647,7 @@ template <typename R> struct BatchImpl {
         }
         BatchArgs<R> a;
         a.pos = (P4 *)b->pos;
-        a.vel0 = nullptr;
-        a.mass = (const R *)b->mass;
+        a.vel = (const V4 *)b->vel;
         a.n = b->n;
         a.nrep = (int)b->nrep;
         a.box = box_of(b);
@@ -1671,6 +1672,64 @@ template <typename R> struct BatchImpl {
         if (energy) CU(cudaMemcpy(energy, b->d_out, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
         if (fn2) CU(cudaMemcpy(fn2, b->d_out + b->nrep, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
         if (virial) CU(cudaMemcpy(virial, b->d_out + 2 * b->nrep, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
+        return B2_OK;
+    }
+
+    static int set_velocities(b2_batch *b, const double *vel)
+    {
+        b2_ctx *c = nullptr;
+        const size_t tot = (size_t)b->nrep * b->n;
+        if (tot == 0) return B2_OK;
+        CU(cudaMemcpy(b->stage, vel, tot * 3 * sizeof(double), cudaMemcpyHostToDevice));
+        k_batch_set_vel<R><<<cdiv(tot, 256), 256>>>(b->stage, (long long)tot, (V4 *)b->vel);
+        b->launches++;
+        CU(cudaDeviceSynchronize());
+        return B2_OK;
+    }
+
+    static int run_nve(b2_batch *b, int64_t steps, double dt, double *kinetic, double *energy, double *virial)
+    {
+        b2_ctx *c = nullptr;
+        if (b->nrep == 0) return B2_OK;
+        if (g_const_owner[b->device] != b->const_serial) {
+            CU(cudaMemcpyToSymbol(g_pair, &b->pc, sizeof(PairConst)));
+            g_const_owner[b->device] = b->const_serial;
+        }
+        BatchNveArgs<R> a;
+        a.pos = (P4 *)b->pos;
+        a.vel = (V4 *)b->vel;
+        a.frc = (V4 *)b->frc;
+        a.img = b->img;
+        a.n = b->n;
+        a.nrep = (int)b->nrep;
+        a.box = box_of(b);
+        a.steps = steps;
+        a.dt = dt;
+        a.kinetic = b->d_out;
+        a.energy = b->d_out + b->nrep;
+        a.virial = b->d_out + 2 * b->nrep;
+        const int threads = (b->n + 31) / 32 * 32;
+        k_batch_nve<R><<<(unsigned)b->nrep, threads, (size_t)b->n * sizeof(P4)>>>(a);
+        b->launches++;
+        CU(cudaGetLastError());
+        if (kinetic) CU(cudaMemcpy(kinetic, b->d_out, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
+        if (energy) CU(cudaMemcpy(energy, b->d_out + b->nrep, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
+        if (virial) CU(cudaMemcpy(virial, b->d_out + 2 * b->nrep, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
+        CU(cudaDeviceSynchronize());
+        return B2_OK;
+    }
+
+    static int get_state(b2_batch *b, double *vel, int32_t *image)
+    {
+        b2_ctx *c = nullptr;
+        const size_t tot = (size_t)b->nrep * b->n;
+        if (tot == 0) return B2_OK;
+        if (vel) {
+            k_batch_get_vel<R><<<cdiv(tot, 256), 256>>>((const V4 *)b->vel, (long long)tot, b->stage);
+            b->launches++;
+            CU(cudaMemcpy(vel, b->stage, tot * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+        }
+        if (image) CU(cudaMemcpy(image, b->img, tot * 3 * sizeof(int), cudaMemcpyDeviceToHost));
         return B2_OK;
     }
 
@@ -1720,7 +1779,7 @@ int b2_batch_destroy(b2_batch *b)
 {
     if (!b) return B2_OK;
     cudaSetDevice(b->device);
-    void *ptrs[] = {b->pos, b->frc, b->mass, b->stage, b->stage_i, b->d_steps, b->d_conv, b->d_out};
+    void *ptrs[] = {b->pos, b->frc, b->vel, b->img, b->stage, b->stage_i, b->d_steps, b->d_conv, b->d_out};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (g_const_owner[b->device] == b->const_serial) g_const_owner[b->device] = 0;
     delete b;
@@ -1780,6 +1839,28 @@ int b2_batch_download(b2_batch *b, double *pos, double *forces)
     if (!b || !b->pos) return fail(nullptr, B2_ESTATE, "b2_batch_download: no replicas resident");
     cudaSetDevice(b->device);
     return BDISPATCH(download, b, pos, forces);
+}
+
+int b2_batch_set_velocities(b2_batch *b, const double *vel)
+{
+    if (!b || !b->pos || !vel) return fail(nullptr, B2_ESTATE, "b2_batch_set_velocities: no replicas resident / NULL");
+    cudaSetDevice(b->device);
+    return BDISPATCH(set_velocities, b, vel);
+}
+
+int b2_batch_run_nve(b2_batch *b, int64_t steps, double dt, double *kinetic, double *energy, double *virial)
+{
+    if (!b || !b->pos) return fail(nullptr, B2_ESTATE, "b2_batch_run_nve: no replicas resident");
+    if (steps < 0 || !(dt > 0.0)) return fail(nullptr, B2_EINVAL, "b2_batch_run_nve: steps >= 0 and dt > 0 required");
+    cudaSetDevice(b->device);
+    return BDISPATCH(run_nve, b, steps, dt, kinetic, energy, virial);
+}
+
+int b2_batch_get_state(b2_batch *b, double *vel, int32_t *image)
+{
+    if (!b || !b->pos) return fail(nullptr, B2_ESTATE, "b2_batch_get_state: no replicas resident");
+    cudaSetDevice(b->device);
+    return BDISPATCH(get_state, b, vel, image);
 }
 
 }  // extern "C"

@@ -281,6 +281,16 @@ int b2_batch_minimize(b2_batch *batch, int method, int64_t max_steps, double dt,
                       double *virial);
 /* final positions (folded) and forces, nrep x n x 3 each, either may be NULL    */
 int b2_batch_download(b2_batch *batch, double *pos, double *forces);
+/* NVE for the whole ensemble: velocities (nrep x n x 3), then `steps` velocity-
+ * Verlet steps of every replica inside ONE kernel launch (configs[0], LJ N=256
+ * 1e4 steps, is launch-latency-bound on the list-based path: ~25 us per step;
+ * here a step costs two block barriers).  Per-replica kinetic / potential energy
+ * and virial of the final configuration, each nrep long or NULL.                */
+int b2_batch_set_velocities(b2_batch *batch, const double *vel);
+int b2_batch_run_nve(b2_batch *batch, int64_t steps, double dt, double *kinetic, double *energy,
+                     double *virial);
+/* velocities (nrep x n x 3) and accumulated box crossings (nrep x n x 3 int32)  */
+int b2_batch_get_state(b2_batch *batch, double *vel, int32_t *image);
 
 /* Measurement aid (nothing like it in the reference, whose only timer is the
  * wall-clock TSP of simulation/core.py:286-306): with profiling on,

@@ -996,3 +996,41 @@ int b2_batch_download(b2_batch *b, double *pos, double *forces)
     }
     return B2_OK;
 }
+
+int b2_batch_set_velocities(b2_batch *b, const double *vel)
+{
+    if (!b || !vel) return fail(NULL, B2_EINVAL, "b2_batch_set_velocities: NULL argument");
+    for (int64_t r = 0; r < b->nrep; r++) {
+        int rc = b2_update(b->rep[r], NULL, vel + 3 * r * (int64_t)b->n);
+        if (rc) return rc;
+    }
+    return B2_OK;
+}
+
+int b2_batch_run_nve(b2_batch *b, int64_t steps, double dt, double *kinetic, double *energy, double *virial)
+{
+    if (!b) return fail(NULL, B2_EINVAL, "b2_batch_run_nve: NULL batch");
+    int err = B2_OK;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t r = 0; r < b->nrep; r++) {
+        double th[B2_T_LEN];
+        int rc = b2_run_nve(b->rep[r], steps, dt);
+        if (rc == B2_OK) rc = b2_thermo(b->rep[r], th);
+        if (rc != B2_OK) { err = rc; continue; }
+        if (kinetic) kinetic[r] = th[B2_T_KINETIC];
+        if (energy) energy[r] = th[B2_T_POTENTIAL];
+        if (virial) virial[r] = th[B2_T_VIRIAL];
+    }
+    return err == B2_OK ? B2_OK : fail(NULL, err, "b2_batch_run_nve: a replica failed");
+}
+
+int b2_batch_get_state(b2_batch *b, double *vel, int32_t *image)
+{
+    if (!b) return fail(NULL, B2_EINVAL, "b2_batch_get_state: NULL batch");
+    for (int64_t r = 0; r < b->nrep; r++) {
+        int rc = b2_download(b->rep[r], NULL, vel ? vel + 3 * r * (int64_t)b->n : NULL,
+                             image ? image + 3 * r * (int64_t)b->n : NULL);
+        if (rc) return rc;
+    }
+    return B2_OK;
+}

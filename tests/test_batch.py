@@ -85,3 +85,63 @@ def test_replica_edge_cases(cuda_lib):
         ens.minimize('cg')
     with pytest.raises(ValueError):
         ReplicaEnsemble(numpy.zeros((1, 2000, 3)), numpy.zeros(2000, dtype=int), side, 'kob_andersen')
+
+
+# ---- NVE of small systems inside one launch (BASELINE.json configs[0]) ----
+def lj256():
+    d = golden('lj_N256')
+    vel = onp.maxwell_boltzmann(256, 2.0, 1.0, seed=1)
+    return d['position'][None], d['species'], d['side'], vel[None]
+
+
+def test_oracle_batch_nve_matches_engine(oracle_lib):
+    from conftest import make_engine
+    pos, spe, side, vel = lj256()
+    ens = ReplicaEnsemble(pos, spe, side, 'lennard_jones', library=oracle_lib)
+    ens.set_velocities(vel)
+    r = ens.run_nve(50, 0.002)
+    eng = make_engine(oracle_lib, {'position': pos[0], 'velocity': vel[0], 'species': spe, 'side': side,
+                                   'center': numpy.zeros(3)}, onp.lennard_jones(2.5, True))
+    eng.run_nve(50, 0.002)
+    t = eng.thermo()
+    assert abs(r['energy'][0] - t['potential']) < 1e-9 * abs(t['potential'])
+    assert abs(r['kinetic'][0] - t['kinetic']) < 1e-9 * t['kinetic']
+    assert numpy.abs(ens.positions()[0] - eng.download()[0]).max() < 1e-10
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('precision', [64, 32])
+def test_batch_nve_follows_the_oracle_and_conserves_energy(cuda_lib, oracle_lib, precision):
+    """C1: LJ N=256 rho=1.0 (data/lj_N256_rho1.0.xyz), T=2.0 velocities seed 1, cut & shifted 2.5,
+    dt=0.002: 50 steps step-for-step against the oracle, then 1e4 steps for the drift."""
+    pos, spe, side, vel = lj256()
+    got = ReplicaEnsemble(pos, spe, side, 'lennard_jones', precision=precision)
+    ref = ReplicaEnsemble(pos, spe, side, 'lennard_jones', library=oracle_lib)
+    for e in (got, ref):
+        e.set_velocities(vel)
+    a, b = got.run_nve(50, 0.002), ref.run_nve(50, 0.002)
+    tol = 1e-9 if precision == 64 else 2e-4
+    assert numpy.abs(got.positions() - ref.positions()).max() < tol
+    assert numpy.abs(got.velocities() - ref.velocities()).max() < 10 * tol
+    assert abs(a['energy'][0] - b['energy'][0]) < (1e-9 if precision == 64 else 1e-4) * abs(b['energy'][0])
+    e0 = (a['energy'][0] + a['kinetic'][0]) / 256
+    long = got.run_nve(10000, 0.002)
+    e1 = (long['energy'][0] + long['kinetic'][0]) / 256
+    assert abs(e1 - e0) < (5e-4 if precision == 64 else 2e-3)
+    # momentum stays zero, images are tracked
+    v = got.velocities()[0]
+    assert numpy.abs(v.sum(axis=0)).max() < (1e-9 if precision == 64 else 1e-2)
+    assert numpy.abs(got.batch.state()[1]).max() >= 1
+
+
+@pytest.mark.gpu
+def test_batch_nve_many_replicas_are_independent(cuda_lib):
+    pos, spe, side = replicas(8)
+    vel = numpy.stack([onp.maxwell_boltzmann(150, 0.5, 1.0, seed=50 + k) for k in range(8)])
+    ens = ReplicaEnsemble(pos, spe, side, 'kob_andersen')
+    ens.set_velocities(vel)
+    r8 = ens.run_nve(200, 0.002)
+    one = ReplicaEnsemble(pos[5:6], spe, side, 'kob_andersen')
+    one.set_velocities(vel[5:6])
+    r1 = one.run_nve(200, 0.002)
+    assert r8['energy'][5] == r1['energy'][0] and r8['kinetic'][5] == r1['kinetic'][0]

@@ -25,6 +25,23 @@ for prec in (64, 32):
                              'particle_steps_per_s': 256 * 10000 / (ms * 1e-3), 'launches': launches,
                              'dE_per_particle': (t1['kinetic'] + t1['potential'] - t0['kinetic'] - t0['potential']) / 256}
     e.close()
+# ---- C1 through the one-block-per-system kernel (whole run in one launch) ----
+for prec in (64, 32):
+    ens = ReplicaEnsemble(d['position'][None], d['species'], d['side'], 'lennard_jones', precision=prec)
+    ens.set_velocities(vel[None])
+    r0 = ens.run_nve(1000, 0.002)
+    t = time.perf_counter(); r1 = ens.run_nve(10000, 0.002); wall = time.perf_counter() - t
+    out['C1_single_block_fp%d' % prec] = {'steps': 10000, 'wall_s': wall, 'us_per_step': wall * 100,
+                                          'particle_steps_per_s': 256 * 10000 / wall,
+                                          'dE_per_particle': float(r1['energy'][0] + r1['kinetic'][0] - r0['energy'][0] - r0['kinetic'][0]) / 256}
+    ens.close()
+    many = ReplicaEnsemble(numpy.repeat(d['position'][None], 1184, axis=0), d['species'], d['side'], 'lennard_jones', precision=prec)
+    many.set_velocities(numpy.repeat(vel[None], 1184, axis=0))
+    many.run_nve(100, 0.002)
+    t = time.perf_counter(); many.run_nve(2000, 0.002); wall = time.perf_counter() - t
+    out['C1_x1184_replicas_fp%d' % prec] = {'replicas': 1184, 'steps': 2000, 'wall_s': wall,
+                                            'particle_steps_per_s': 1184 * 256 * 2000 / wall}
+    many.close()
 # ---- C4 ----
 fr = g('ka_N150_frames')
 nrep = 4096
