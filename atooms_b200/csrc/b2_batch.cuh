@@ -174,10 +174,10 @@ template <typename R>
 __device__ __forceinline__ void batch_force(const typename Pos4<R>::type *s_pos, int n, int i,
                                             const typename Pos4<R>::type &p, int ti, const Box<R> &box,
                                             const R *s_c12x12, const R *s_c6x6, const R *s_rc2,
-                                            R &fx, R &fy, R &fz)
+                                            R &fx, R &fy, R &fz, int first = 0, int stride = 1)
 {
     fx = fy = fz = 0;
-    for (int j = 0; j < n; j++) {
+    for (int j = first; j < n; j += stride) {
         if (j == i) continue;
         const typename Pos4<R>::type q = s_pos[j];
         R dx, dy, dz;
@@ -207,7 +207,10 @@ template <typename R> struct BatchNveArgs {
 // `steps` velocity-Verlet steps of every replica in ONE launch: kick-drift form
 // exactly as in k_step_nve (opening half kick, identical steps, closing half kick),
 // two block barriers per step, nothing leaves the SM until the end.
-template <typename R>
+// T threads share one particle (its neighbours dealt out round-robin, partial forces combined by
+// a butterfly so that all T lanes hold the identical sum): a lone small system is bound by the
+// latency of one thread's serial pair loop, which T divides.
+template <typename R, int T>
 __global__ void k_batch_nve(BatchNveArgs<R> a)
 {
     typedef typename Pos4<R>::type P4;
@@ -221,18 +224,28 @@ __global__ void k_batch_nve(BatchNveArgs<R> a)
         s_c6x6[k] = (R)(6.0 * g_pair.c6[k]);
         s_rc2[k] = (R)g_pair.rc2[k];
     }
-    const int rep = blockIdx.x, i = threadIdx.x, n = a.n, nsp = g_pair.nsp;
+    const int rep = blockIdx.x, i = threadIdx.x / T, sub = threadIdx.x % T, n = a.n, nsp = g_pair.nsp;
     const bool own = i < n;
-    const size_t g = (size_t)rep * n + i;
+    const bool lead = own && sub == 0;
+    const size_t g = (size_t)rep * n + (own ? i : 0);
     P4 p = own ? a.pos[g] : P4();
     V4 v = own ? a.vel[g] : make4((R)0, (R)0, (R)0, (R)1);
     const int ti = own ? ptype(p) * nsp : 0;
     const R dt = (R)a.dt, hdt = (R)(0.5 * a.dt);
     int ix = 0, iy = 0, iz = 0;
     R fx = 0, fy = 0, fz = 0;
-    if (own) s_pos[i] = p;
+#define B2_BATCH_FORCE()                                                                           \
+    {                                                                                              \
+        if (own) batch_force<R>(s_pos, n, i, p, ti, a.box, s_c12x12, s_c6x6, s_rc2, fx, fy, fz, sub, T); \
+        _Pragma("unroll") for (int o = 1; o < T; o <<= 1) {                                        \
+            fx += __shfl_xor_sync(0xffffffffu, fx, o);                                             \
+            fy += __shfl_xor_sync(0xffffffffu, fy, o);                                             \
+            fz += __shfl_xor_sync(0xffffffffu, fz, o);                                             \
+        }                                                                                          \
+    }
+    if (lead) s_pos[i] = p;
     __syncthreads();
-    if (own) batch_force<R>(s_pos, n, i, p, ti, a.box, s_c12x12, s_c6x6, s_rc2, fx, fy, fz);
+    B2_BATCH_FORCE()
     if (a.steps > 0) {
         R s = hdt / v.w;
         v.x -= s * fx; v.y -= s * fy; v.z -= s * fz;            // velocities to t - dt/2
@@ -245,16 +258,17 @@ __global__ void k_batch_nve(BatchNveArgs<R> a)
                 ix += kx; iy += ky; iz += kz;
             }
             __syncthreads();                                    // everybody has read the old positions
-            if (own) s_pos[i] = p;
+            if (lead) s_pos[i] = p;
             __syncthreads();
-            if (own) batch_force<R>(s_pos, n, i, p, ti, a.box, s_c12x12, s_c6x6, s_rc2, fx, fy, fz);
+            B2_BATCH_FORCE()
         }
         s = hdt / v.w;
         v.x += s * fx; v.y += s * fy; v.z += s * fz;            // closing half kick
     }
     // final configuration: fp64 energy, virial, kinetic energy
+#undef B2_BATCH_FORCE
     double pe = 0, vir = 0, kin = 0;
-    if (own) {
+    if (lead) {
         for (int j = 0; j < n; j++) {
             if (j == i) continue;
             double ex, ey, ez;

@@ -1708,8 +1708,15 @@ template <typename R> struct BatchImpl {
         a.kinetic = b->d_out;
         a.energy = b->d_out + b->nrep;
         a.virial = b->d_out + 2 * b->nrep;
-        const int threads = (b->n + 31) / 32 * 32;
-        k_batch_nve<R><<<(unsigned)b->nrep, threads, (size_t)b->n * sizeof(P4)>>>(a);
+        // few replicas: several threads per particle shorten each thread's serial pair loop
+        int T = 1;
+        while (T < 8 && b->n * 2 * T <= BATCH_MAX_THREADS && b->nrep * (int64_t)((b->n * T + 31) / 32) < 148 * 16) T *= 2;
+        const int threads = (b->n * T + 31) / 32 * 32;
+        const size_t smem = (size_t)b->n * sizeof(P4);
+        if (T == 8) k_batch_nve<R, 8><<<(unsigned)b->nrep, threads, smem>>>(a);
+        else if (T == 4) k_batch_nve<R, 4><<<(unsigned)b->nrep, threads, smem>>>(a);
+        else if (T == 2) k_batch_nve<R, 2><<<(unsigned)b->nrep, threads, smem>>>(a);
+        else k_batch_nve<R, 1><<<(unsigned)b->nrep, threads, smem>>>(a);
         b->launches++;
         CU(cudaGetLastError());
         if (kinetic) CU(cudaMemcpy(kinetic, b->d_out, b->nrep * sizeof(double), cudaMemcpyDeviceToHost));
