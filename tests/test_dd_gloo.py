@@ -34,14 +34,14 @@ def global_system(reps_x=2, seed=5):
     return pos, vel, numpy.tile(d['species'], reps_x).astype(numpy.int32), side
 
 
-def _worker(rank, world, port, steps, out):
+def _worker(rank, world, port, steps, out, reps_x=2):
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
     dist.init_process_group('gloo', rank=rank, world_size=world)
     from atooms_b200 import capi
     from atooms_b200.dd import SlabDomain
     lib = capi.Library(os.path.join(ROOT, 'oracle', '_build', 'liboracle_b2.so'))
-    pos, vel, spe, side = global_system()
+    pos, vel, spe, side = global_system(reps_x)
     n = len(spe)
     # deliberately NOT pre-sorted into slabs: rank r starts with every world-th particle that
     # lies in its own or an adjacent slab; the first refresh migrates the strays
@@ -61,17 +61,20 @@ def _worker(rank, world, port, steps, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('world', [2])
-def test_two_rank_slab_run_matches_single_domain(world, tmp_path, oracle_lib):
+@pytest.mark.parametrize('world', [2, 3])
+def test_slab_run_matches_single_domain(world, tmp_path, oracle_lib):
+    """world = 2: both ring neighbours are the same rank; world = 3: a genuine ring (the hop
+    arithmetic, distinct left / right peers), on a box three fixtures long."""
     steps = 120
+    reps_x = 2 if world == 2 else 3
     out = str(tmp_path / 'dd.npz')
-    port = 29500 + os.getpid() % 2000
-    mp.spawn(_worker, args=(world, port, steps, out), nprocs=world, join=True)
+    port = 29500 + (os.getpid() + 17 * world) % 2000
+    mp.spawn(_worker, args=(world, port, steps, out, reps_x), nprocs=world, join=True)
     got = numpy.load(out)
     # the same global system on ONE engine
     from conftest import make_engine
     from oracle import oracle_np as onp
-    pos, vel, spe, side = global_system()
+    pos, vel, spe, side = global_system(reps_x)
     ref = make_engine(oracle_lib, {'position': pos, 'velocity': vel, 'species': spe, 'side': side,
                                    'center': numpy.zeros(3)}, onp.kob_andersen(), 64)
     e0 = ref.thermo()
