@@ -206,6 +206,33 @@ def test_nve_energy_drift_matches_oracle(cuda_lib, oracle_lib):
     assert abs(series['cuda'][0] - series['oracle'][0]) < 1e-8
 
 
+def test_nve_energy_drift_parity_1e5_steps(cuda_lib, oracle_lib):
+    """BASELINE.json: "NVE energy-drift parity over 1e5 steps" on configs[0] (LJ N=256 rho=1.0,
+    T=2.0 velocities seed 1, cut & shifted 2.5, dt=0.002).  Trajectories diverge chaotically after
+    ~1e3 steps, so the comparison is statistical: drift slope and fluctuation of E/N sampled every
+    2000 steps, fp64 engine vs fp64 oracle (and the fp32 engine within a looser band)."""
+    d = dict(golden('lj_N256').items())
+    d['velocity'] = onp.maxwell_boltzmann(256, 2.0, 1.0, seed=1)
+    lj = onp.lennard_jones(2.5, True)
+    series = {}
+    for key, lib, prec in (('cuda64', cuda_lib, 64), ('cuda32', cuda_lib, 32), ('oracle', oracle_lib, 64)):
+        eng = make_engine(lib, d, lj, prec)
+        e = []
+        for _ in range(50):
+            eng.run_nve(2000, 0.002)
+            t = eng.thermo()
+            e.append((t['kinetic'] + t['potential']) / 256)
+        series[key] = numpy.array(e)
+    steps = numpy.arange(1, 51) * 2000.0
+    slope = {k: numpy.polyfit(steps, v, 1)[0] for k, v in series.items()}
+    for k in ('cuda64', 'oracle'):
+        assert abs(slope[k]) * 1e5 < 2e-3, (k, slope[k])            # drift per 1e5 steps
+        assert series[k].std() < 2e-3
+    assert abs(slope['cuda64'] - slope['oracle']) * 1e5 < 2e-3
+    assert abs(series['cuda64'].mean() - series['oracle'].mean()) < 2e-3
+    assert abs(slope['cuda32']) * 1e5 < 2e-2 and abs(series['cuda32'].mean() - series['oracle'].mean()) < 1e-2
+
+
 def test_determinism_and_state_reset(cuda_lib):
     """deepcopy / reassign property of tests/test_rumd.py:178-194."""
     d = golden('ka_N256_rumd')
