@@ -52,7 +52,13 @@ class B200(object):
     version = __version__
 
     def __init__(self, inp, model='lennard_jones', dt=0.002, skin=0.3, precision='fp64', device=0,
-                 library=None):
+                 library=None, thermostat='nose-hoover'):
+        """`thermostat` names the scheme used WHEN `system.thermostat` is set (the reference's
+        backends switch to NVT on that attribute, atooms/backends/lammps.py:229-241):
+        'nose-hoover' (LAMMPS `fix nvt`, RUMD IntegratorNVT) or 'berendsen'."""
+        if thermostat not in ('nose-hoover', 'berendsen'):
+            raise ValueError("thermostat must be 'nose-hoover' or 'berendsen'")
+        self.thermostat_kind = capi.NVT_NOSE_HOOVER if thermostat == 'nose-hoover' else capi.NVT_BERENDSEN
         self.model = models.get(model)
         self.timestep = float(dt)
         self.skin = float(skin)
@@ -96,7 +102,13 @@ class B200(object):
     def run(self, steps):
         s = self._system
         s._push()
-        s._engine.run_nve(int(steps), self.timestep)
+        th = s.thermostat
+        if th is not None and getattr(th, 'temperature', None) is not None:
+            # NVT: `fix 1 all nvt temp T T relaxation_time` (lammps.py:233-235)
+            s._engine.run_nvt(int(steps), self.timestep, th.temperature,
+                              getattr(th, 'relaxation_time', None) or 100 * self.timestep, self.thermostat_kind)
+        else:
+            s._engine.run_nve(int(steps), self.timestep)
         if steps > 0:
             s._advanced()
         self.steps += int(steps)

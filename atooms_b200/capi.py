@@ -20,6 +20,7 @@ FP32, FP64 = 32, 64
 ENERGY, FORCES, VIRIAL, STRESS = 1, 2, 4, 8
 GHOST = 256
 MIN_SD, MIN_FIRE = 0, 1
+NVT_BERENDSEN, NVT_NOSE_HOOVER = 0, 1
 T_KINETIC, T_POTENTIAL, T_VIRIAL, T_FNORM2, T_PX, T_PY, T_PZ, T_MASS, T_MSD, T_LEN = \
     0, 1, 2, 3, 4, 5, 6, 7, 8, 16
 S_STEPS, S_REBUILDS, S_LAUNCHES, S_MAX_NEIGH, S_NEIGH_CAP, S_LIST_MODE, S_NCELLS, S_LEN = \
@@ -57,6 +58,7 @@ SYMBOLS = {
     'b2_neighbors': (_int, [_vp, _c_ip, _c_ip, ctypes.c_int32, _c_ip]),
     'b2_run_nve': (_int, [_vp, _i64, _dbl]),
     'b2_minimize': (_int, [_vp, _int, _i64, _dbl, _dbl, _c_lp, ctypes.POINTER(_int)]),
+    'b2_run_nvt': (_int, [_vp, _i64, _dbl, _dbl, _dbl, _int]),
     'b2_stats': (_int, [_vp, _c_lp]),
     'b2_last_timing': (_int, [_vp, _c_dp, _c_lp]),
     'b2_set_profile': (_int, [_vp, _int]),
@@ -329,6 +331,9 @@ class Engine(object):
     # -- dynamics ---------------------------------------------------------
     def run_nve(self, steps, dt):
         self._call('b2_run_nve', int(steps), float(dt))
+
+    def run_nvt(self, steps, dt, temperature, relaxation_time, kind=NVT_NOSE_HOOVER):
+        self._call('b2_run_nvt', int(steps), float(dt), float(temperature), float(relaxation_time), int(kind))
 
     def minimize(self, method, max_steps, dt, fn2_tol):
         done, conv = _i64(), _int()

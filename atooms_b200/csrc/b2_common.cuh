@@ -229,6 +229,10 @@ struct Ctl {
     int npos, min_mode;
     int has_prev, pad1_;         // SD: the previous gradient is available (survives a resumed call)
     long long iter;
+    // thermostat (b2_run_nvt): v' = th_a v + th_b dt F/m, coefficients renewed every step by the
+    // last block from the kinetic energy of the half-step velocities just written
+    int th_kind, th_pad_;        // 0 Berendsen, 1 Nose-Hoover (leap-frog form)
+    double th_T0, th_tau, th_dt, th_xi, th_a, th_b, th_ndof, th_T;
     double red[32];              // reduction results
 };
 

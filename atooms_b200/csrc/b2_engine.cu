@@ -35,6 +35,7 @@ struct b2_ctx {
     size_t nbr_alloc = 0;
     void *pos[2] = {nullptr, nullptr}, *vel = nullptr, *frc = nullptr, *vir = nullptr;
     void *tpos = nullptr, *tvel = nullptr;
+    double *ke_partial = nullptr;   // per-block sum m v^2 of thermostatted steps
     void *mvel = nullptr;      // parked minimiser velocities, by original id
     bool min_resume = false;
     int min_method = -1;
@@ -199,6 +200,7 @@ template <typename R> struct Impl {
     {
         int rc;
         c->ncap = n;
+        if (c->ke_partial) { cudaFree(c->ke_partial); c->ke_partial = nullptr; }
         for (int k = 0; k < 2; k++)
             if ((rc = dev_alloc(c, (P4 **)&c->pos[k], n))) return rc;
         if ((rc = dev_alloc(c, (V4 **)&c->vel, n))) return rc;
@@ -381,7 +383,7 @@ template <typename R> struct Impl {
     }
 
     static int thermo(b2_ctx *c, double *out, bool want_stress, double *stress9);
-    static int run_nve(b2_ctx *c, int64_t steps, double dt);
+    static int run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind = -1, double T0 = 0, double tau = 0);
     static int minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double tol,
                         int64_t *steps_done, int *converged);
     static int neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, int32_t *max_count);
@@ -715,7 +717,7 @@ int Impl<R>::neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, 
 }
 
 template <typename R>
-int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
+int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0, double tau)
 {
     int rc;
     if (steps == 0 || c->n == 0) return B2_OK;
@@ -724,6 +726,12 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
     // opening half kick (backwards): velocities move to t - dt/2
     LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(-0.5 * dt));
     LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0, 0);
+    const bool nvt = th_kind >= 0;
+    if (nvt) {
+        if (!c->ke_partial && (rc = dev_alloc(c, &c->ke_partial, (size_t)cdiv(c->ncap, FORCE_THREADS) + 1))) return rc;
+        LAUNCH(k_thermostat_begin, 1, 1, c->ctl, th_kind, T0, tau, dt, 3.0 * (double)std::max<int64_t>(c->n - 1, 1));
+    }
+    auto step_kernel = nvt ? k_step_nve<R, true> : k_step_nve<R, false>;
     c->min_resume = false;
     for (int k = 0; k < 8; k++) c->prof[k] = 0;
     long long rebuilds0 = c->hctl->rebuilds;
@@ -746,6 +754,7 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
     a.vmax_mail = nullptr;
     a.nranks = 1;
     a.seq = 0;
+    a.ke_partial = c->ke_partial;
     int64_t done = 0;
     while (done < steps) {
         // speculative batches: [guarded refresh][batch x step]; steps after the
@@ -763,7 +772,7 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt)
             enqueue_rebuild(c);
             mark();
             int m = (int)std::min<int64_t>(c->batch, quota - launched);
-            for (int k = 0; k < m; k++) LAUNCH(k_step_nve<R>, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
+            for (int k = 0; k < m; k++) LAUNCH(step_kernel, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
             launched += m;
             c->prof[2] += m;
         }
@@ -921,7 +930,9 @@ int Impl<R>::dd_step(b2_ctx *c, float *vmax_out)
     a.vmax_mail = c->peer_on ? c->peer_mail : nullptr;
     a.nranks = c->nranks;
     a.seq = c->dd_seq;
-    if (n > 0) LAUNCH(k_step_nve<R>, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
+    a.ke_partial = nullptr;
+    auto step_kernel = k_step_nve<R, false>;
+    if (n > 0) LAUNCH(step_kernel, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
     return B2_OK;
 }
 
@@ -1023,7 +1034,7 @@ int b2_destroy(b2_ctx *c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv, c->halo_buf, c->dd_vmax,
-                    c->img, c->ref, c->mvel, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
+                    c->img, c->ref, c->mvel, c->ke_partial, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -1189,6 +1200,15 @@ int b2_run_nve(b2_ctx *c, int64_t steps, double dt)
     if (steps < 0 || !(dt > 0.0)) return fail(c, B2_EINVAL, "b2_run_nve: steps >= 0 and dt > 0 required");
     Timed t(c);
     return DISPATCH(run_nve, c, steps, dt);
+}
+
+int b2_run_nvt(b2_ctx *c, int64_t steps, double dt, double temperature, double relaxation_time, int kind)
+{
+    NEED_PARTICLES("b2_run_nvt");
+    if (steps < 0 || !(dt > 0.0) || !(temperature > 0.0) || !(relaxation_time > 0.0) || (kind != 0 && kind != 1))
+        return fail(c, B2_EINVAL, "b2_run_nvt: steps >= 0, dt, temperature, relaxation_time > 0, kind 0 | 1 required");
+    Timed t(c);
+    return DISPATCH(run_nve, c, steps, dt, kind, temperature, relaxation_time);
 }
 
 int b2_minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double fn2_tol, int64_t *steps_done,

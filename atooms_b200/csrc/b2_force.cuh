@@ -207,6 +207,7 @@ template <typename R> struct StepArgs {
     unsigned long long *const *vmax_mail;   // [nranks] device pointers: rank r's slot for OUR value
     int nranks;
     unsigned seq;
+    double *ke_partial;              // [gridDim] sum m v^2 per block (thermostatted runs)
 };
 
 // mail[r] points at OUR slot in rank r's mailbox (parity 0); the parity-1 slot sits 8 * nranks
@@ -225,7 +226,16 @@ __device__ __forceinline__ void peer_publish(unsigned long long *const *mail, in
 // displacement bound.  Reads the current position buffer, writes the other;
 // the last block to finish flips the buffers and settles the step's
 // bookkeeping on the device.
-template <typename R>
+//
+// NVT = true adds a thermostat at no extra pass over the data (the reference's
+// backends honour system.thermostat, atooms/backends/lammps.py:229-241): the kick becomes
+// v' = a v + b dt F/m with (a, b) read from the control block, each block leaves its sum of
+// m v'^2, and the last block turns the total into the next step's (a, b):
+//   Berendsen      lambda^2 = 1 + dt/tau (T0/T - 1),               a = b = lambda
+//   Nose-Hoover    xi += dt/tau^2 (T/T0 - 1), h = xi dt/2,           a = (1-h)/(1+h), b = 1/(1+h)
+// (the leap-frog form used by RUMD's IntegratorNVT); T is the kinetic temperature of the
+// half-step velocities, (N-1) d degrees of freedom (atooms/system/system.py:164-179).
+template <typename R, bool NVT>
 __global__ void __launch_bounds__(FORCE_THREADS, (sizeof(R) == 4 ? B2_MINBLK32 : B2_MINBLK64))
 k_step_nve(StepArgs<R> a)
 {
@@ -249,6 +259,8 @@ k_step_nve(StepArgs<R> a)
     P4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     float v2 = 0.f;
+    double mv2 = 0.0;
+    const R th_a = NVT ? (R)ctl->th_a : (R)1, th_b = NVT ? (R)ctl->th_b : (R)1;
     if (i < a.n) {
         P4 pi = pos[i];
         if (is_ghost(pi)) {
@@ -262,7 +274,13 @@ k_step_nve(StepArgs<R> a)
         else pair_row<R, false, false, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
         V4 v = a.vel[i];
         R s = a.kick / v.w;
-        v.x += s * fx; v.y += s * fy; v.z += s * fz;
+        if (NVT) {
+            s *= th_b;
+            v.x = th_a * v.x + s * fx; v.y = th_a * v.y + s * fy; v.z = th_a * v.z + s * fz;
+            mv2 = (double)v.w * ((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+        } else {
+            v.x += s * fx; v.y += s * fy; v.z += s * fz;
+        }
         int kx, ky, kz;
         posn[i] = advance(pi, a.drift * v.x, a.drift * v.y, a.drift * v.z, a.box, kx, ky, kz);
         if (kx | ky | kz) {
@@ -274,12 +292,22 @@ k_step_nve(StepArgs<R> a)
         v2 = __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
         }
     }
+    __shared__ double s_ke[FORCE_THREADS / 32];
+    if (NVT) {
+        mv2 = warp_sum(mv2);
+        if ((threadIdx.x & 31) == 0) s_ke[threadIdx.x >> 5] = mv2;
+    }
     v2 = warp_max(v2);
     if ((threadIdx.x & 31) == 0) s_v2[threadIdx.x >> 5] = v2;
     __syncthreads();
     if (threadIdx.x == 0) {
         float m = s_v2[0];
         for (int w = 1; w < FORCE_THREADS / 32; w++) m = fmaxf(m, s_v2[w]);
+        if (NVT) {
+            double k = 0;
+            for (int w = 0; w < FORCE_THREADS / 32; w++) k += s_ke[w];
+            a.ke_partial[blockIdx.x] = k;
+        }
         atomicMax(&ctl->vmax2_bits, __float_as_uint(m));
         __threadfence();
         unsigned ticket = atomicAdd(&ctl->blocks_done, 1u);
@@ -303,6 +331,47 @@ k_step_nve(StepArgs<R> a)
             ctl->blocks_done = 0u;
         }
     }
+    if (NVT) {
+        // the last block (every partial is visible to it after the ticket) renews the thermostat
+        __syncthreads();
+        if (s_last) {
+            double k = 0;
+            for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) k += __ldcg(a.ke_partial + b);
+            k = warp_sum(k);
+            __syncthreads();
+            if ((threadIdx.x & 31) == 0) s_ke[threadIdx.x >> 5] = k;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double tot = 0;
+                for (int w = 0; w < FORCE_THREADS / 32; w++) tot += s_ke[w];
+                const double T = tot / ctl->th_ndof, dt = ctl->th_dt;
+                ctl->th_T = T;
+                if (ctl->th_kind == 0) {
+                    const double l2 = 1.0 + dt / ctl->th_tau * (ctl->th_T0 / fmax(T, 1e-300) - 1.0);
+                    ctl->th_a = ctl->th_b = sqrt(fmax(l2, 0.25));
+                } else {
+                    const double xi = ctl->th_xi + dt / (ctl->th_tau * ctl->th_tau) * (T / ctl->th_T0 - 1.0);
+                    const double h = 0.5 * xi * dt;
+                    ctl->th_xi = xi;
+                    ctl->th_a = (1.0 - h) / (1.0 + h);
+                    ctl->th_b = 1.0 / (1.0 + h);
+                }
+            }
+        }
+    }
+}
+
+__global__ void k_thermostat_begin(Ctl *ctl, int kind, double T0, double tau, double dt, double ndof)
+{
+    ctl->th_kind = kind;
+    ctl->th_T0 = T0;
+    ctl->th_tau = tau;
+    ctl->th_dt = dt;
+    ctl->th_ndof = ndof;
+    // xi carries over between calls (reset by b2_upload); the first step uses the coefficients it implies
+    const double h = kind == 1 ? 0.5 * ctl->th_xi * dt : 0.0;
+    ctl->th_a = (1.0 - h) / (1.0 + h);
+    ctl->th_b = 1.0 / (1.0 + h);
 }
 
 // v += c F / m   (opening / closing half kick of a run)

@@ -75,11 +75,14 @@ class Particle(object):
 
 
 class Thermostat(object):
-    """Place-holder (atooms/backends/dryrun.py:99-104): NVE only, kept so that
-    `system.thermostat` exists; `pressure` uses the kinetic temperature."""
+    """Target temperature and coupling time, the two attributes of
+    atooms.system.reservoir.Thermostat (reservoir.py:22-40) that backends read
+    (lammps.py:233-235).  Assigning one to `system.thermostat` turns `B200.run`
+    into NVT dynamics; `pressure` then uses this temperature (system.py:343-346)."""
 
-    def __init__(self, temperature=None):
+    def __init__(self, temperature=None, relaxation_time=1.0):
         self.temperature = temperature
+        self.relaxation_time = relaxation_time
 
 
 class _ParticleList(object):

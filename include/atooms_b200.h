@@ -191,6 +191,19 @@ int b2_neighbors(b2_ctx *ctx, int32_t *count, int32_t *nbr, int32_t stride,
  * tests/test_lammps.py:123-142).                                            */
 int b2_run_nve(b2_ctx *ctx, int64_t steps, double dt);
 
+/* Thermostatted dynamics: what the reference's backends do when
+ * `system.thermostat` is set (`fix nvt temp T T relaxation_time`,
+ * atooms/backends/lammps.py:229-241; IntegratorNVT, backends/rumd.py:105-118).
+ * kind B2_NVT_BERENDSEN: velocities scaled by lambda, lambda^2 = 1 + dt/tau (T0/T - 1);
+ * kind B2_NVT_NOSE_HOOVER: leap-frog Nose-Hoover, d xi/dt = (T/T0 - 1)/tau^2,
+ * v' = [(1 - xi dt/2) v + dt F/m] / (1 + xi dt/2).  T is the kinetic temperature of the
+ * half-step velocities with (N-1) d degrees of freedom (system.py:164-179), taken one
+ * step late so that it costs no extra pass.  xi persists between calls; b2_upload resets it. */
+#define B2_NVT_BERENDSEN   0
+#define B2_NVT_NOSE_HOOVER 1
+int b2_run_nvt(b2_ctx *ctx, int64_t steps, double dt, double temperature,
+               double relaxation_time, int kind);
+
 /* Minimise the potential energy with `method` for at most `max_steps`
  * iterations; stop early when sum F^2 / N < fn2_tol
  * (optimization/core.py:34-36).  *converged = 1 if the tolerance was met

@@ -64,6 +64,7 @@ struct b2_ctx {
     double *mvel;
     int min_resume, min_method, m_npos, m_has_prev;
     double m_dt, m_alpha, m_dt0;
+    double th_xi;   /* Nose-Hoover friction, persists between b2_run_nvt calls */
     /* domain decomposition */
     double dd_dt;
     int64_t dd_steps, dd_target;
@@ -233,6 +234,7 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     memcpy(c->ref, c->pos, n3 * sizeof(double));
     c->list_valid = c->forces_valid = 0;
     c->disp_bound = 0.0;
+    c->th_xi = 0.0;
     return B2_OK;
 }
 
@@ -1032,5 +1034,61 @@ int b2_batch_get_state(b2_batch *b, double *vel, int32_t *image)
                              image ? image + 3 * r * (int64_t)b->n : NULL);
         if (rc) return rc;
     }
+    return B2_OK;
+}
+
+/* Thermostatted dynamics: same kick-drift loop as b2_run_nve with v' = a v + b dt F/m, the
+ * coefficients renewed after every step from the kinetic temperature of the half-step
+ * velocities just produced (one step late), exactly as the fused CUDA kernel does. */
+int b2_run_nvt(b2_ctx *c, int64_t steps, double dt, double T0, double tau, int kind)
+{
+    int rc = ensure_ready(c, "b2_run_nvt");
+    if (rc) return rc;
+    if (steps < 0 || !(dt > 0.0) || !(T0 > 0.0) || !(tau > 0.0) || (kind != 0 && kind != 1))
+        return fail(c, B2_EINVAL, "b2_run_nvt: bad argument");
+    if (steps == 0) return B2_OK;
+    c->min_resume = 0;
+    int64_t n = c->n;
+    const double ndof = 3.0 * (double)(n > 1 ? n - 1 : 1);
+    if ((rc = ensure_forces(c)) != B2_OK) return rc;
+    for (int64_t i = 0; i < n; i++)
+        for (int d = 0; d < 3; d++) c->vel[3 * i + d] -= (0.5 * dt) * c->frc[3 * i + d] / c->mass[i];
+    double h = kind == 1 ? 0.5 * c->th_xi * dt : 0.0;
+    double a = (1.0 - h) / (1.0 + h), b = 1.0 / (1.0 + h);
+    for (int64_t s = 0; s < steps; s++) {
+        if (s > 0) {
+            if (!c->list_valid && (rc = build_list(c)) != B2_OK) return rc;
+            compute_forces(c, c->pos, c->frc, NULL, NULL, NULL, NULL, NULL);
+        }
+        double vmax2 = 0.0, mv2 = 0.0;
+        for (int64_t i = 0; i < n; i++) {
+            double *v = c->vel + 3 * i, *x = c->pos + 3 * i;
+            if (GHOST(c, i)) continue;
+            for (int d = 0; d < 3; d++) {
+                v[d] = a * v[d] + b * (dt / c->mass[i]) * c->frc[3 * i + d];
+                x[d] += dt * v[d];
+            }
+            fold3(c, x, c->img + 3 * i);
+            double v2 = (v[0] * v[0] + v[1] * v[1]) + v[2] * v[2];
+            mv2 += c->mass[i] * v2;
+            if (v2 > vmax2) vmax2 = v2;
+        }
+        advance_bound(c, dt * sqrt(vmax2));
+        const double T = mv2 / ndof;
+        if (kind == 0) {
+            double l2 = 1.0 + dt / tau * (T0 / (T > 1e-300 ? T : 1e-300) - 1.0);
+            a = b = sqrt(l2 > 0.25 ? l2 : 0.25);
+        } else {
+            c->th_xi += dt / (tau * tau) * (T / T0 - 1.0);
+            h = 0.5 * c->th_xi * dt;
+            a = (1.0 - h) / (1.0 + h);
+            b = 1.0 / (1.0 + h);
+        }
+    }
+    c->forces_valid = 0;
+    if ((rc = ensure_forces(c)) != B2_OK) return rc;
+    for (int64_t i = 0; i < n; i++)
+        for (int d = 0; d < 3; d++) c->vel[3 * i + d] += (0.5 * dt) * c->frc[3 * i + d] / c->mass[i];
+    c->steps_total += steps;
     return B2_OK;
 }

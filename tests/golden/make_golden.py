@@ -151,6 +151,10 @@ def main():
         'lj_N256_minimised': {
             'U_per_particle_below': -6.8, 'fn2_per_particle_below': 1e-4,
             'source': 'tests/test_optimization.py:20-35'},
+        'lj_N1000_nvt_temperature': {
+            'value': 2.0, 'places': 1, 'source': 'tests/test_lammps.py:42-98',
+            'setup': 'lj_N1000, unshifted LJ 2.5, start at T=1.5 (or 1.4), fix nvt temp 2.0 2.0 0.2, dt=0.002, '
+                     'mean of T sampled every 500 steps after 1500 steps'},
         'ka_table': {
             'eps': [[1.0, 1.5], [1.5, 0.5]], 'sigma': [[1.0, 0.8], [0.8, 0.88]],
             'rcut_over_sigma': 2.5, 'source': 'tests/test_rumd.py:26-31; data/ka_rumd.ff:4-7'},

@@ -233,6 +233,28 @@ def test_nve_energy_drift_parity_1e5_steps(cuda_lib, oracle_lib):
     assert abs(slope['cuda32']) * 1e5 < 2e-2 and abs(series['cuda32'].mean() - series['oracle'].mean()) < 1e-2
 
 
+@pytest.mark.parametrize('kind', [capi.NVT_NOSE_HOOVER, capi.NVT_BERENDSEN], ids=['nose-hoover', 'berendsen'])
+def test_nvt_step_for_step_and_target_temperature(cuda_lib, oracle_lib, kind):
+    """Thermostatted fused step against the oracle's twin, then the reference's
+    NVT expectation (tests/test_lammps.py:42-98: <T> = 2.0 to one place)."""
+    d = dict(golden('lj_N1000').items())
+    d['velocity'] = onp.maxwell_boltzmann(1000, 1.5, 1.0, seed=1)
+    lj = onp.lennard_jones(2.5, False)
+    eng, ora = make_engine(cuda_lib, d, lj, 64), make_engine(oracle_lib, d, lj, 64)
+    for _ in range(2):                       # the second call continues with the stored friction
+        eng.run_nvt(30, 0.002, 2.0, 0.2, kind)
+        ora.run_nvt(30, 0.002, 2.0, 0.2, kind)
+        (p, v, _), (po, vo, _) = eng.download(), ora.download()
+        assert numpy.abs(p - po).max() < 1e-10 and numpy.abs(v - vo).max() < 1e-9
+    for precision in (64, 32):
+        eng = make_engine(cuda_lib, d, lj, precision)
+        T = []
+        for _ in range(40):
+            eng.run_nvt(100, 0.002, 2.0, 0.2, kind)
+            T.append(2 * eng.thermo()['kinetic'] / (3 * 999))
+        assert abs(numpy.mean(T[15:]) - 2.0) < 0.05
+
+
 def test_determinism_and_state_reset(cuda_lib):
     """deepcopy / reassign property of tests/test_rumd.py:178-194."""
     d = golden('ka_N256_rumd')

@@ -108,6 +108,23 @@ def test_sync_contract(oracle_lib):
     assert abs(numpy.sum(s.dump('velocity') ** 2) / (3 * 255) - 6.0) < 1e-9
 
 
+def test_thermostat_switches_the_backend_to_nvt(oracle_lib, pins):
+    """tests/test_lammps.py:80-98: `sim.system.thermostat = Thermostat(2.0)` turns the run into NVT."""
+    from atooms_b200 import Thermostat
+    model = atooms_b200.lennard_jones(2.5, shifted=False)
+    bck = B200(make_system('lj_N1000', oracle_lib, model), model, dt=0.002, library=oracle_lib)
+    bck.system.set_temperature(1.4, seed=1)
+    bck.system.thermostat = Thermostat(2.0, relaxation_time=0.2)
+    T = []
+    for _ in range(8):
+        bck.run(500)
+        T.append(bck.system.temperature)
+    assert round(abs(sum(T[3:]) / len(T[3:]) - pins['lj_N1000_nvt_temperature']['value']), 1) == 0
+    assert abs(bck.system.pressure - (1000 * 2.0 + bck.system.virial(per_particle=False) / 3) / 1000.0) < 1e-9
+    with pytest.raises(ValueError):
+        B200(bck.system, model, thermostat='langevin', library=oracle_lib)
+
+
 def test_deepcopy_and_reassign(oracle_lib):
     """tests/test_rumd.py:178-194."""
     bck = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib)

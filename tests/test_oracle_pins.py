@@ -160,3 +160,22 @@ def test_minimisers_agree(oracle_lib, lj_shifted):
                                            lj_shifted, 0.002, 300, 1e-4)
     assert steps == it and conv == conv_np
     assert abs(eng.thermo()['potential'] - e_np) < 1e-9 * abs(e_np)
+
+
+@pytest.mark.parametrize('kind', [1, 0], ids=['nose-hoover', 'berendsen'])
+def test_nvt_reaches_the_target_temperature(oracle_lib, pins, lj_unshifted, kind):
+    """tests/test_lammps.py:42-98: start at T = 1.5, thermostat at 2.0 with coupling time 0.2,
+    dt = 0.002; the reference averages T sampled every 500 steps after 1500 steps (1 place)."""
+    pin = pins['lj_N1000_nvt_temperature']
+    d = dict(golden('lj_N1000').items())
+    d['velocity'] = onp.maxwell_boltzmann(1000, 1.5, 1.0, seed=1)
+    eng = make_engine(oracle_lib, d, lj_unshifted)
+    T = []
+    for _ in range(40):
+        eng.run_nvt(100, 0.002, 2.0, 0.2, kind)
+        T.append(2 * eng.thermo()['kinetic'] / (3 * 999))
+    assert abs(numpy.mean(T[15:]) - pin['value']) < 0.05
+    # the thermostat really acts: NVE from the same start stays near its own temperature
+    nve = make_engine(oracle_lib, d, lj_unshifted)
+    nve.run_nve(1000, 0.002)
+    assert abs(2 * nve.thermo()['kinetic'] / (3 * 999) - 2.0) > 0.1
