@@ -39,8 +39,15 @@ def _last_frame(inp):
             raise ValueError('reading %s needs the atooms trajectory readers' % inp)
         if not hasattr(numpy, 'set_string_function'):      # numpy >= 2: close() of the xyz reader
             numpy.set_string_function = lambda *a, **k: None   # (atooms/trajectory/xyz.py:472-474)
-        with trajectory.Trajectory(inp) as th:
-            return th[-1]
+        try:
+            th = trajectory.Trajectory(inp)
+        except ValueError:
+            # the factory goes by suffix (trajectory/factory.py:93-114): RUMD's .xyz.gz
+            # configurations need their own reader
+            th = trajectory.TrajectoryRUMD(inp) if inp.endswith('.xyz.gz') else trajectory.TrajectoryXYZ(inp)
+        system = th[-1]
+        th.close()
+        return system
     raise ValueError('could not initialize system from {}'.format(inp))
 
 

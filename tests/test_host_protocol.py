@@ -284,3 +284,30 @@ def test_interaction_with_reference_system(oracle_lib, pins):
     e1 = system.interaction.energy
     system.interaction = both
     assert abs(system.potential_energy() - 2 * e1) < 1e-8
+
+
+@needs_ref
+def test_command_line_driver(oracle_lib, tmp_path, monkeypatch):
+    """bin/md_b200.py, the bin/md.py look-alike (bin/md.py:12-81).  The engine is swapped for
+    the oracle by patching the loader IN THIS TEST ONLY; the script itself has no such switch."""
+    import argparse
+    import importlib.util
+    from atooms_b200 import capi
+    monkeypatch.setattr(capi, 'load', lambda: oracle_lib)
+    spec = importlib.util.spec_from_file_location('md_b200', os.path.join(hp_root(), 'bin', 'md_b200.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = str(tmp_path / 'run')
+    params = argparse.Namespace(T=0.8, dt=0.002, input_file=os.path.join(REF, 'data', 'ka_N256_rho1.185_rumd.xyz.gz'),
+                                integrator='nve', model='kob_andersen', tau=0.2, skin=0.3, precision='fp64',
+                                device=0, steps=60, thermo_interval=20, config_interval=30, checkpoint_interval=0,
+                                restart=False, verbose=False, debug=False, output_dir=out)
+    mod.main(params)
+    thermo = numpy.loadtxt(os.path.join(out, 'trajectory.thermo'))
+    assert list(thermo[:, 0]) == [0, 20, 40, 60]
+    lines = open(os.path.join(out, 'trajectory')).read().splitlines()
+    assert lines[0] == '256' and lines[1].startswith('step:0 ') and len(lines) == 3 * 258
+
+
+def hp_root():
+    return os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
