@@ -326,11 +326,17 @@ template <typename R> struct Impl {
         if (!c->list_dirty) return B2_OK;
         if (c->n == 0) { c->list_dirty = false; return B2_OK; }
         if ((rc = setup_grid(c))) return rc;
-        if (c->cap == 0) {
-            double rl = c->rcut_max + c->skin;
-            double vol = c->side[0] * c->side[1] * c->side[2];
-            double nbar = (double)c->n / vol * 4.18879 * rl * rl * rl;
-            if ((rc = ensure_capacity(c, (int)(1.3 * nbar) + 24))) return rc;
+        {
+            // first build: slots from the mean density; afterwards keep the slot count, but ALWAYS
+            // re-check the allocation — a re-upload (domain decomposition) may have grown the arrays
+            int want = c->cap;
+            if (want == 0) {
+                double rl = c->rcut_max + c->skin;
+                double vol = c->side[0] * c->side[1] * c->side[2];
+                double nbar = (double)c->n / vol * 4.18879 * rl * rl * rl;
+                want = (int)(1.3 * nbar) + 24;
+            }
+            if ((rc = ensure_capacity(c, want))) return rc;
         }
         for (int attempt = 0; attempt < 8; attempt++) {
             if ((rc = pull_ctl(c))) return rc;
