@@ -317,6 +317,25 @@ def test_update_and_scale(cuda_lib, oracle_lib):
     assert numpy.abs(back + img * d['side'] - pos).max() < 1e-12
 
 
+def test_reupload_with_more_particles(cuda_lib, oracle_lib):
+    """A context re-used for a larger system (what the slab decomposition does at every refresh):
+    every per-particle allocation, the neighbour list included, must follow.  (An 8-rank run
+    once wrote past a list sized for the previous upload.)"""
+    ka = onp.kob_andersen()
+    small, big = golden('ka_N1200'), replicated('ka_N1200', 2, 0.01, 11)
+    eng = make_engine(cuda_lib, small, ka, 64)
+    eng.compute()
+    eng.set_box(big['side'], big['center'])
+    eng.upload(big['position'], big['species'], big['velocity'])
+    got = eng.compute()
+    ref = make_engine(oracle_lib, big, ka, 64).compute()
+    assert_observables(got, ref, 64)
+    eng.run_nve(40, 0.002)
+    eng.set_box(small['side'], small['center'])
+    eng.upload(small['position'], small['species'])               # and back to fewer
+    assert_observables(eng.compute(), make_engine(oracle_lib, small, ka, 64, velocities=False).compute(), 64)
+
+
 def test_edge_cases(cuda_lib):
     lj = onp.lennard_jones(2.5, True)
     base = {'side': numpy.array([10., 10., 10.]), 'center': numpy.zeros(3)}
