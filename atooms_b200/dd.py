@@ -110,27 +110,31 @@ class SlabDomain(object):
     def _right(self):
         return (self.rank + 1) % self.world
 
-    def _exchange(self, to_left, to_right, like_cols):
-        """Send two (rows, cols) float64 tensors to the ring neighbours and return what
-        arrives (from_left, from_right).  Posting order [to-left, to-right] /
-        [from-right, from-left] keeps the pairing unambiguous when both neighbours
-        are the same rank (world size 2)."""
-        counts = torch.tensor([to_left.shape[0], to_right.shape[0]], dtype=torch.int64, device=self._cdev)
+    def _exchange(self, to_left, to_right):
+        """The refresh exchange: each argument is (migrants (m, 12), ghosts (g, 4)); both go to
+        that neighbour as one flat message.  Returns ((migrants, ghosts) from the left,
+        (migrants, ghosts) from the right).  Posting order [to-left, to-right] / [from-right,
+        from-left] keeps the pairing unambiguous when both neighbours are the same rank
+        (world size 2)."""
+        counts = torch.tensor([to_left[0].shape[0], to_left[1].shape[0],
+                               to_right[0].shape[0], to_right[1].shape[0]], dtype=torch.int64, device=self._cdev)
         all_counts = [torch.empty_like(counts) for _ in range(self.world)]
         dist.all_gather(all_counts, counts, group=self.group)
-        n_from_right = int(all_counts[self._right()][0])      # the right neighbour's to-left message
-        n_from_left = int(all_counts[self._left()][1])
-        pad = lambda t: (t if t.shape[0] > 0 else torch.zeros((1, like_cols), dtype=torch.float64,
-                                                               device=self.dev)).to(self._cdev).contiguous()
-        from_right = torch.empty((max(n_from_right, 1), like_cols), dtype=torch.float64, device=self._cdev)
-        from_left = torch.empty((max(n_from_left, 1), like_cols), dtype=torch.float64, device=self._cdev)
-        ops = [dist.P2POp(dist.isend, pad(to_left), self._left(), self.group),
-               dist.P2POp(dist.isend, pad(to_right), self._right(), self.group),
+        mr, gr = (int(v) for v in all_counts[self._right()][0:2])     # the right neighbour's to-left message
+        ml, gl = (int(v) for v in all_counts[self._left()][2:4])
+        flat = lambda pair: torch.cat([pair[0].reshape(-1), pair[1].reshape(-1),
+                                       pair[0].new_zeros(1)]).to(self._cdev).contiguous()
+        from_right = torch.empty(12 * mr + 4 * gr + 1, dtype=torch.float64, device=self._cdev)
+        from_left = torch.empty(12 * ml + 4 * gl + 1, dtype=torch.float64, device=self._cdev)
+        ops = [dist.P2POp(dist.isend, flat(to_left), self._left(), self.group),
+               dist.P2POp(dist.isend, flat(to_right), self._right(), self.group),
                dist.P2POp(dist.irecv, from_right, self._right(), self.group),
                dist.P2POp(dist.irecv, from_left, self._left(), self.group)]
         for req in dist.batch_isend_irecv(ops):
             req.wait()
-        return from_left[:n_from_left].to(self.dev), from_right[:n_from_right].to(self.dev)
+        from_left, from_right = from_left.to(self.dev), from_right.to(self.dev)
+        split = lambda t, m, g: (t[:12 * m].reshape(m, 12), t[12 * m:12 * m + 4 * g].reshape(g, 4))
+        return split(from_left, ml, gl), split(from_right, mr, gr)
 
     def _tick(self, name):
         """Phase timer of refresh() (only when self.profile is a dict; synchronises)."""
@@ -181,38 +185,52 @@ class SlabDomain(object):
             return torch.cat([self.pos[idx], self.vel[idx], self.mass[idx, None],
                               self.gid[idx, None].to(torch.float64), self.spe[idx, None].to(torch.float64),
                               self.img[idx].to(torch.float64)], dim=1)
+
+        def ghost(idx):
+            return torch.cat([self.pos[idx], self.spe[idx, None].to(torch.float64)], dim=1)
         if self.world > 1:
-            from_l, from_r = self._exchange(payload(idx_l), payload(idx_r), 12)
+            # One exchange carries both the migrants and the ghost layer.  The ghost message
+            # holds the particles that STAY here and lie within r_list of the face; the ones
+            # that just crossed that face are ghosts of the rank they left as well, but that
+            # rank already has their coordinates, so it appends them itself (same order on
+            # both sides: [staying near-face particles, then the migrants in sending order]).
             gone = idx_l.numel() + idx_r.numel()
-            if gone or from_l.shape[0] or from_r.shape[0]:
+            keep = torch.nonzero(slab == self.rank).flatten() if gone else None
+            x_in = u if keep is None else u[keep]
+            lo, hi = self.rank / self.world, (self.rank + 1) / self.world
+            margin = self.rlist / self.side[0] * (1 + 1e-6) + 1e-12
+            near_l = torch.nonzero(x_in < lo + margin).flatten()          # numbering after the removal
+            near_r = torch.nonzero(x_in >= hi - margin).flatten()
+            src_l = near_l if keep is None else keep[near_l]
+            src_r = near_r if keep is None else keep[near_r]
+            mig_l, mig_r = payload(idx_l), payload(idx_r)
+            (from_l, g_from_l), (from_r, g_from_r) = self._exchange(
+                (mig_l, ghost(src_l)), (mig_r, ghost(src_r)))
+            n_keep = self.n_own - gone
+            n_fl, n_fr = from_l.shape[0], from_r.shape[0]
+            if gone or n_fl or n_fr:
                 new = torch.cat([from_l, from_r], dim=0)
-                if gone:
-                    keep = torch.nonzero(slab == self.rank).flatten()
-                    sel = lambda t: t[keep]
-                else:
-                    sel = lambda t: t
+                sel = (lambda t: t[keep]) if gone else (lambda t: t)
                 self.pos = torch.cat([sel(self.pos), new[:, 0:3]], dim=0)
                 self.vel = torch.cat([sel(self.vel), new[:, 3:6]], dim=0)
                 self.mass = torch.cat([sel(self.mass), new[:, 6]], dim=0)
                 self.gid = torch.cat([sel(self.gid), new[:, 7].round().to(torch.int64)], dim=0)
                 self.spe = torch.cat([sel(self.spe), new[:, 8].round().to(torch.int32)], dim=0)
                 self.img = torch.cat([sel(self.img), new[:, 9:12].round().to(torch.int32)], dim=0)
-        self._tick('migrate')
-        n = self.n_own
-        # ghosts: owned particles within r_list of a face are copied to the neighbour beyond it
-        if self.world > 1:
-            x_in = (self.pos[:, 0] - ctr[0]) / side[0] + 0.5          # in [0, 1)
-            lo, hi = self.rank / self.world, (self.rank + 1) / self.world
-            margin = self.rlist / self.side[0] * (1 + 1e-6) + 1e-12
-            near_l = torch.nonzero(x_in < lo + margin).flatten()
-            near_r = torch.nonzero(x_in >= hi - margin).flatten()
-            ghost = lambda idx: torch.cat([self.pos[idx], self.spe[idx, None].to(torch.float64)], dim=1)
-            g_from_l, g_from_r = self._exchange(ghost(near_l), ghost(near_r), 4)
+            if n_fl:
+                near_l = torch.cat([near_l, torch.arange(n_keep, n_keep + n_fl, device=self.dev)])
+            if n_fr:
+                near_r = torch.cat([near_r, torch.arange(n_keep + n_fl, n_keep + n_fl + n_fr, device=self.dev)])
+            if idx_l.numel():
+                g_from_l = torch.cat([g_from_l, mig_l[:, [0, 1, 2, 8]]], dim=0)
+            if idx_r.numel():
+                g_from_r = torch.cat([g_from_r, mig_r[:, [0, 1, 2, 8]]], dim=0)
             self._send_l, self._send_r = near_l.to(torch.int32).contiguous(), near_r.to(torch.int32).contiguous()
         else:
             g_from_l = g_from_r = self.pos.new_zeros((0, 4))
             self._send_l = self._send_r = torch.zeros(0, dtype=torch.int32, device=self.dev)
-        self._tick('ghosts')
+        n = self.n_own
+        self._tick('exchange')
         self._n_gl, self._n_gr = g_from_l.shape[0], g_from_r.shape[0]
         ghosts = torch.cat([g_from_l, g_from_r], dim=0)
         ng = ghosts.shape[0]
