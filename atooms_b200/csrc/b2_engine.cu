@@ -312,9 +312,20 @@ template <typename R> struct Impl {
             LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
             LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
         }
-        auto build = c->grid.m == 2 ? k_build_list<R, 2> : (c->grid.m == 1 ? k_build_list<R, 1> : k_build_list<R, 0>);
-        LAUNCH(build, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
-               c->nbr, c->nnb, c->cap);
+        // one warp per 2x2x2 block of cells when the grid allows it (at least 7 cells per axis: the
+        // 6x6x6 candidate region then holds distinct cells within half a box of the block's centre); B2_LIST_WALK=1 forces the per-particle walk (A/B timing)
+        static const bool force_walk = getenv("B2_LIST_WALK") && atoi(getenv("B2_LIST_WALK")) != 0;
+        const Grid &g = c->grid;
+        if (g.m == 2 && !g.allpairs && g.nc[0] >= 7 && g.nc[1] >= 7 && g.nc[2] >= 7 && n < (1 << 28) && !force_walk) {
+            int codes = 1 << (3 * g.cellbits - 3);
+            auto build = c->nsp <= 2 ? k_build_list_sc<R, true> : k_build_list_sc<R, false>;
+            LAUNCH(build, cdiv(codes, SC_WARPS), SC_WARPS * 32, c->ctl, p0, p1, n, box, c->grid,
+                   c->cell_start, c->cell_end, c->nbr, c->nnb, c->cap);
+        } else {
+            auto build = g.m == 2 ? k_build_list<R, 2> : (g.m == 1 ? k_build_list<R, 1> : k_build_list<R, 0>);
+            LAUNCH(build, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
+                   c->nbr, c->nnb, c->cap);
+        }
         LAUNCH(k_rebuild_finish, 1, 1, c->ctl);
     }
 
