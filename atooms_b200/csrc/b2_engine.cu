@@ -20,7 +20,7 @@
 #define MAX_RED_BLOCKS 1024
 
 struct b2_ctx {
-    int device = 0, precision = 64;
+    int device = 0, precision = 64, sms = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // model
@@ -299,7 +299,7 @@ template <typename R> struct Impl {
             int src = 0;
             for (int pass = 0; pass < c->sort_passes; pass++) {
                 LAUNCH(k_sort_hist, c->sort_blocks, SORT_THREADS, c->ctl, c->keys[src], n, 8 * pass, c->sort_blocks, c->hist);
-                LAUNCH(k_sort_scan, 1, 256, c->ctl, c->hist, c->sort_blocks);
+                LAUNCH(k_sort_scan, 1, 256 * SCAN_GROUPS, c->ctl, c->hist, c->sort_blocks);
                 LAUNCH(k_sort_scatter, c->sort_blocks, SORT_THREADS, c->ctl, c->keys[src], c->vals[src],
                        c->keys[src ^ 1], c->vals[src ^ 1], n, 8 * pass, c->sort_blocks, c->hist);
                 src ^= 1;
@@ -319,6 +319,8 @@ template <typename R> struct Impl {
         if (g.m == 2 && !g.allpairs && g.nc[0] >= 7 && g.nc[1] >= 7 && g.nc[2] >= 7 && n < (1 << 28) && !force_walk) {
             int codes = 1 << (3 * g.cellbits - 3);
             auto build = c->nsp <= 2 ? k_build_list_sc<R, true> : k_build_list_sc<R, false>;
+            // one warp per code (a strided grid of a few blocks per SM was measured 10 % slower:
+            // the valid codes are unevenly spread over the Morton range)
             LAUNCH(build, cdiv(codes, SC_WARPS), SC_WARPS * 32, c->ctl, p0, p1, n, box, c->grid,
                    c->cell_start, c->cell_end, c->nbr, c->nnb, c->cap);
         } else {
@@ -1029,6 +1031,7 @@ int b2_create(int device, int precision, b2_ctx **out)
     int rc = B2_OK;
     do {
         if ((e = cudaSetDevice(device)) != cudaSuccess) break;
+        if ((e = cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) break;
         if ((e = cudaMalloc((void **)&ctx->ctl, sizeof(Ctl))) != cudaSuccess) break;
         if ((e = cudaMemset(ctx->ctl, 0, sizeof(Ctl))) != cudaSuccess) break;
         if ((e = cudaMallocHost((void **)&ctx->hctl, sizeof(Ctl))) != cudaSuccess) break;

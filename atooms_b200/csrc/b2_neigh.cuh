@@ -50,33 +50,57 @@ k_sort_hist(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ keys, int 
 
 // hist[b][d] -> start offset of digit d of block b in the sorted output
 // (digit-major order: all blocks of digit 0, then digit 1, ...).  One block of
-// 256 threads, one digit per thread, coalesced sweeps over the blocks.
-__global__ void __launch_bounds__(256)
-k_sort_scan(const Ctl *__restrict__ ctl, int *__restrict__ hist, int nblk)
+// 1024 threads: four groups of 256 digits, each group sweeps a quarter of the
+// blocks with coalesced rows, eight independent loads in flight per thread.
+#define SCAN_GROUPS 4
+__global__ void __launch_bounds__(256 * SCAN_GROUPS)
+k_sort_scan(const Ctl *__restrict__ ctl, int *hist, int nblk)
 {
     if (!ctl->halt_rebuild) return;
+    __shared__ int s_tot[SCAN_GROUPS][256];
     __shared__ int s_warp[8];
-    int d = threadIdx.x, lane = d & 31, w = d >> 5;
+    const int d = threadIdx.x & 255, grp = threadIdx.x >> 8, lane = d & 31, w = d >> 5;
+    const int per = (nblk + SCAN_GROUPS - 1) / SCAN_GROUPS;
+    const int b0 = grp * per, b1 = min(nblk, b0 + per);
     int run = 0;
-#pragma unroll 8
-    for (int b = 0; b < nblk; b++) {
-        int t = hist[b * 256 + d];
-        hist[b * 256 + d] = run;
-        run += t;
+    for (int b = b0; b < b1; b += 8) {
+        int t[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) t[k] = b + k < b1 ? hist[(b + k) * 256 + d] : 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (b + k < b1) hist[(b + k) * 256 + d] = run;
+            run += t[k];
+        }
     }
-    // exclusive scan of the per-digit totals
-    int incl = run;
+    s_tot[grp][d] = run;
+    __syncthreads();
+    // exclusive scan of the per-digit totals (first group), then each group's base
+    int total = 0, before = 0;
+#pragma unroll
+    for (int g = 0; g < SCAN_GROUPS; g++) {
+        const int t = s_tot[g][d];
+        if (g < grp) before += t;
+        total += t;
+    }
+    int incl = total;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        int t = __shfl_up_sync(0xffffffffu, incl, o);
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += t;
     }
-    if (lane == 31) s_warp[w] = incl;
+    if (grp == 0 && lane == 31) s_warp[w] = incl;
     __syncthreads();
-    int base = incl - run;
+    int base = incl - total + before;
     for (int ww = 0; ww < w; ww++) base += s_warp[ww];
-#pragma unroll 8
-    for (int b = 0; b < nblk; b++) hist[b * 256 + d] += base;
+    for (int b = b0; b < b1; b += 8) {
+        int t[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) t[k] = b + k < b1 ? hist[(b + k) * 256 + d] : 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (b + k < b1) hist[(b + k) * 256 + d] = t[k] + base;
+    }
 }
 
 // stable scatter: each warp owns a contiguous segment of the block's tile
@@ -330,10 +354,13 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
 // every pair outside a thin band around the threshold; the band is settled with the
 // canonical predicate on the stored coordinates, exactly as in k_build_list.
 #define SC_WARPS 4
+#ifndef SC_MINBLK
+#define SC_MINBLK 7
+#endif
 #define SC_CHUNK 256
 #define SC_CELLS 216
-#define SC_EPS 2e-5f
-#define SC_TAG 0x40000000
+#define SC_EPS 4e-6f
+#define SC_TAKE 248            // candidates staged per round: 31 lanes x 8, leaves a gap of 8 in the chunk
 
 __device__ __forceinline__ uint32_t compact3(uint32_t x)
 {
@@ -363,29 +390,31 @@ __device__ __forceinline__ void rel_to(const double4 &p, const Box<double> &box,
     z = (float)(dz - box.L[2] * rint(dz * box.invL[2]));
 }
 
-template <typename R, bool FAST2>
-__global__ void __launch_bounds__(SC_WARPS * 32)
-k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
-                const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
-                const int *__restrict__ cell_start, const int *__restrict__ cell_end,
-                int *__restrict__ nbr, int *__restrict__ nnb, int cap)
+// append j to the row when `hit`, as predicated instructions: the compiler's branch plus its
+// reconvergence barrier cost more than the store they skip
+__device__ __forceinline__ void sc_append(bool hit, int *row, int &cnt, int cap, int j)
 {
-    if (!ctl->halt_rebuild) return;
+    int *dst = row + (size_t)cnt * 32;
+    asm volatile("{\n\t.reg .pred q, s;\n\tsetp.ne.s32 q, %1, 0;\n\tsetp.lt.and.s32 s, %0, %2, q;\n\t"
+                 "@s st.global.b32 [%3], %4;\n\t@q add.s32 %0, %0, 1;\n\t}"
+                 : "+r"(cnt) : "r"((int)hit), "r"(cap), "l"(dst), "r"(j) : "memory");
+}
+
+struct ScShared {
+    int prefix[SC_CELLS + 8];
+    int first[SC_CELLS + 8];
+    float4 cand[SC_CHUNK];
+};
+
+// one block of cells (Morton code ms), one warp
+template <typename R, bool FAST2>
+__device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, const R *s_rl2, const float *s_hi, const float *s_lo,
+                                         Ctl *__restrict__ ctl, const typename Pos4<R>::type *__restrict__ pos,
+                                         const Box<R> &box, const Grid &g, const int *__restrict__ cell_start,
+                                         const int *__restrict__ cell_end, int *__restrict__ nbr,
+                                         int *__restrict__ nnb, int cap)
+{
     typedef typename Pos4<R>::type P4;
-    const P4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
-    __shared__ R s_rl2[B2_MAXSP * B2_MAXSP];
-    __shared__ float s_hi[B2_MAXSP * B2_MAXSP];
-    __shared__ int s_prefix[SC_WARPS][SC_CELLS + 8];
-    __shared__ int s_first[SC_WARPS][SC_CELLS + 8];
-    __shared__ float4 s_cand[SC_WARPS][SC_CHUNK];
-    if (threadIdx.x < B2_MAXSP * B2_MAXSP) {
-        const R rl2 = rl2_of(g_pair, threadIdx.x, (R)0);
-        s_rl2[threadIdx.x] = rl2;
-        s_hi[threadIdx.x] = (float)rl2 * (1.f + SC_EPS);
-    }
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t ms = blockIdx.x * SC_WARPS + warp;            // Morton code of the block of cells
     const int bx = 2 * (int)compact3(ms), by = 2 * (int)compact3(ms >> 1), bz = 2 * (int)compact3(ms >> 2);
     if (bx >= g.nc[0] || by >= g.nc[1] || bz >= g.nc[2]) return;
     // the block's own particles: one contiguous run of slots
@@ -425,8 +454,8 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
             const int v = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += v;
         }
-        s_prefix[warp][q] = total + incl - l;
-        s_first[warp][q] = s0;
+        sh.prefix[q] = total + incl - l;
+        sh.first[q] = s0;
         total += __shfl_sync(0xffffffffu, incl, 31);
     }
     __syncwarp();
@@ -440,8 +469,9 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     org.d[1] = ((double)(by + 1) / g.nc[1] - 0.5) * box.Ld[1];
     org.d[2] = ((double)(bz + 1) / g.nc[2] - 0.5) * box.Ld[2];
     const int nsp = g_pair.nsp;
-    float4 *cand = s_cand[warp];
-    const int *prefix = s_prefix[warp], *firsts = s_first[warp];
+    float4 *cand = sh.cand;
+    const int *prefix = sh.prefix, *firsts = sh.first;
+    const float4 nobody = make_float4(1e18f, 0.f, 0.f, 0.f);      // never within reach of anyone
 
     for (int b0 = 0; b0 < n_own; b0 += 32) {          // more than 32 particles in the block: again
         const bool valid = b0 + lane < n_own;
@@ -454,70 +484,125 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
         // thresholds of this particle's row of the pair table; a lane without a row never matches
         const float *hi_row = s_hi + ti * nsp;
         const float hi0 = active ? hi_row[0] : -1.f, hi1 = active ? hi_row[nsp > 1 ? 1 : 0] : -1.f;
-        const float lo_over_hi = (1.f - SC_EPS) / (1.f + SC_EPS);
+        const float *lo_row = s_lo + ti * nsp;
+        const float lo0 = lo_row[0], lo1 = lo_row[nsp > 1 ? 1 : 0];
         int *row = nbr + ((size_t)(slot >> 5) * cap) * 32 + (slot & 31);
-        int cnt = 0, seen = 0;
-        for (int c0 = 0; c0 < total; c0 += SC_CHUNK) {
-            const int m = min(SC_CHUNK, total - c0);
-            {   // stage: lane takes 8 consecutive candidates, stored rotated (conflict-free)
+        int cnt = 0;
+        float near = -1.f;        // > 0 once a listed pair sits inside the band around its threshold
+        for (int c0 = 0; c0 < total; c0 += SC_TAKE) {
+            const int m = min(SC_TAKE, total - c0);
+            // ---- stage: lane takes 8 consecutive candidates; those farther than r_list,max from
+            // the block itself (a quarter of the 6x6x6 cells' content) are dropped here
+            float4 rec[8];
+            unsigned ok = 0u, tyb = 0u;
+            {
                 const int f0 = c0 + lane * 8;
                 int c = 0;
                 if (f0 < c0 + m) {
-                    int a = 0, b = SC_CELLS - 1;
-                    while (a < b) {                   // largest cell with prefix <= f0
-                        const int mid = (a + b + 1) >> 1;
-                        if (prefix[mid] <= f0) a = mid; else b = mid - 1;
+                    int lo_c = 0, hi_c = SC_CELLS - 1;
+                    while (lo_c < hi_c) {             // largest cell with prefix <= f0
+                        const int mid = (lo_c + hi_c + 1) >> 1;
+                        if (prefix[mid] <= f0) lo_c = mid; else hi_c = mid - 1;
                     }
-                    c = a;
+                    c = lo_c;
                 }
 #pragma unroll
                 for (int t = 0; t < 8; t++) {
                     const int f = f0 + t;
-                    float4 rec = make_float4(1e18f, 0.f, 0.f, 0.f);
                     if (f < c0 + m) {
                         while (f >= prefix[c + 1]) c++;
                         const int j = firsts[c] + (f - prefix[c]);
                         const P4 pj = pos[j];
-                        rel_to(pj, box, org, rec.x, rec.y, rec.z);
-                        rec.w = __int_as_float(j | (ptype(pj) << 28));
+                        rel_to(pj, box, org, rec[t].x, rec[t].y, rec[t].z);
+                        const int tj = ptype(pj);
+                        rec[t].w = __int_as_float(FAST2 ? j : (j | (tj << 28)));
+                        const float ex = fmaxf(fabsf(rec[t].x) - g.w[0], 0.f);
+                        const float ey = fmaxf(fabsf(rec[t].y) - g.w[1], 0.f);
+                        const float ez = fmaxf(fabsf(rec[t].z) - g.w[2], 0.f);
+                        if (ex * ex + ey * ey + ez * ez <= g.reach2) {
+                            ok |= 1u << t;
+                            if (FAST2 && tj) tyb |= 1u << t;
+                        }
                     }
-                    cand[lane * 8 + ((t + lane) & 7)] = rec;
                 }
             }
+            // species 0 packed from the front and (two species) species 1 from the back: each
+            // stretch is then tested against ONE threshold held in a register
+            const int mine = __popc(ok & ~tyb) | (__popc(ok & tyb) << 16);
+            int incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int tot = __shfl_sync(0xffffffffu, incl, 31);
+            int ia = (incl - mine) & 0xffff, ib = SC_CHUNK - 1 - ((incl - mine) >> 16);
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                if (ok & (1u << t)) {
+                    if (tyb & (1u << t)) cand[ib--] = rec[t];
+                    else cand[ia++] = rec[t];
+                }
+            const int n0 = tot & 0xffff, n1 = tot >> 16;
+            if (lane < 4) {                           // pad both stretches to a multiple of 4 (the gap is >= 8)
+                cand[n0 + lane] = nobody;
+                cand[SC_CHUNK - 1 - n1 - lane] = nobody;
+            }
             __syncwarp();
-            const int mr = (m + 7) & ~7;
+            const int e0 = (n0 + 3) & ~3;
+            if (FAST2) {
+                float far0 = 0.f, far1 = 0.f;         // largest listed r^2 of either stretch
+#define SC_TEST(R_, HI, FAR)                                                       \
+                {                                                                  \
+                    const float4 q = cand[R_];                                     \
+                    const float dx = q.x - px, dy = q.y - py, dz = q.z - pz;       \
+                    const float r2 = dx * dx + dy * dy + dz * dz;                  \
+                    const int j = __float_as_int(q.w);                             \
+                    const bool hit = r2 < HI && j != slot;                         \
+                    sc_append(hit, row, cnt, cap, j);                              \
+                    FAR = fmaxf(FAR, hit ? r2 : 0.f);                              \
+                }
+#pragma unroll 1
+                for (int r = 0; r < e0; r += 4) {
+                    SC_TEST(r, hi0, far0) SC_TEST(r + 1, hi0, far0) SC_TEST(r + 2, hi0, far0) SC_TEST(r + 3, hi0, far0)
+                }
+#pragma unroll 1
+                for (int r = SC_CHUNK - ((n1 + 3) & ~3); r < SC_CHUNK; r += 4) {
+                    SC_TEST(r, hi1, far1) SC_TEST(r + 1, hi1, far1) SC_TEST(r + 2, hi1, far1) SC_TEST(r + 3, hi1, far1)
+                }
+#undef SC_TEST
+                near = fmaxf(near, fmaxf(far0 - lo0, far1 - lo1));
+            } else {
 #pragma unroll 4
-            for (int r = 0; r < mr; r++) {
-                const float4 q = cand[r];
-                const float dx = q.x - px, dy = q.y - py, dz = q.z - pz;
-                const float r2 = dx * dx + dy * dy + dz * dz;
-                const int w = __float_as_int(q.w);
-                const int tj = (int)((unsigned)w >> 28);
-                const float hi = FAST2 ? (tj ? hi1 : hi0) : (active ? hi_row[tj] : -1.f);
-                const int j = w & 0x0fffffff;
-                // inside the band the pair is listed provisionally, tagged for the pass below
-                const int tagged = r2 > hi * lo_over_hi ? (j | SC_TAG) : j;
-                if (r2 < hi && j != slot) {
-                    if (cnt < cap) row[(size_t)cnt * 32] = tagged;
-                    cnt++;
-                    seen |= tagged;
+                for (int r = 0; r < e0; r++) {
+                    const float4 q = cand[r];
+                    const float dx = q.x - px, dy = q.y - py, dz = q.z - pz;
+                    const float r2 = dx * dx + dy * dy + dz * dz;
+                    const int w = __float_as_int(q.w);
+                    const float hi = active ? hi_row[(unsigned)w >> 28] : -1.f;
+                    const int j = w & 0x0fffffff;
+                    const bool hit = r2 < hi && j != slot;
+                    sc_append(hit, row, cnt, cap, j);
+                    near = fmaxf(near, hit ? r2 - lo_row[(unsigned)w >> 28] : -1.f);
                 }
             }
             __syncwarp();
         }
-        if (seen & SC_TAG) {
-            // settle the tagged pairs with the canonical predicate and close the gaps (rare: the
-            // band is 4e-5 wide in r^2, about one particle in a hundred has a pair in it)
+        if (near > 0.f) {
+            // Some listed pair is inside the band around its threshold: settle those with the
+            // canonical predicate and close the gaps (about one particle in a thousand).  Pairs
+            // beyond the band were rejected by the float test.
             const int lim = min(cnt, cap);
             int kept = 0;
             for (int k = 0; k < lim; k++) {
-                int e = row[(size_t)k * 32];
+                const int e = row[(size_t)k * 32];
+                const P4 pj = pos[e];
+                const int tj = ptype(pj);
+                float qx, qy, qz;
+                rel_to(pj, box, org, qx, qy, qz);
+                const float dx = qx - px, dy = qy - py, dz = qz - pz;
                 bool keep = true;
-                if (e & SC_TAG) {
-                    e &= ~SC_TAG;
-                    const P4 pj = pos[e];
-                    keep = r2_canon(pi, pj, box) < s_rl2[ti * nsp + ptype(pj)];
-                }
+                if (dx * dx + dy * dy + dz * dz > lo_row[tj]) keep = r2_canon(pi, pj, box) < s_rl2[ti * nsp + tj];
                 if (keep) row[(size_t)kept++ * 32] = e;
             }
             if (cnt <= cap) cnt = kept;
@@ -530,6 +615,39 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
         if (lane == 0) atomicMax(&ctl->max_count, (unsigned)mx);
+    }
+}
+
+// one warp per Morton code of a block of cells (the stride loop only matters for a smaller grid)
+template <typename R, bool FAST2>
+__global__ void __launch_bounds__(SC_WARPS * 32, SC_MINBLK)
+k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
+                const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
+                const int *__restrict__ cell_start, const int *__restrict__ cell_end,
+                int *__restrict__ nbr, int *__restrict__ nnb, int cap)
+{
+    if (!ctl->halt_rebuild) return;
+    typedef typename Pos4<R>::type P4;
+    const P4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
+    __shared__ R s_rl2[B2_MAXSP * B2_MAXSP];
+    __shared__ float s_hi[B2_MAXSP * B2_MAXSP], s_lo[B2_MAXSP * B2_MAXSP];
+    __shared__ ScShared s_warp[SC_WARPS];
+    if (threadIdx.x < B2_MAXSP * B2_MAXSP) {
+        const R rl2 = rl2_of(g_pair, threadIdx.x, (R)0);
+        s_rl2[threadIdx.x] = rl2;
+        // half-width of the band, relative to the pair's threshold: the float coordinates are good
+        // to ~2.5e-7 of the cell width each, i.e. r^2 to ~1e-6 r_list,max^2 in the worst case
+        const float eps = SC_EPS * fmaxf(1.f, sqrtf(g.reach2 / fmaxf((float)rl2, 1e-30f)));
+        s_hi[threadIdx.x] = (float)rl2 * (1.f + eps);
+        s_lo[threadIdx.x] = (float)rl2 * (1.f - eps);
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t codes = 1u << (3 * g.cellbits - 3);
+    for (uint32_t ms = blockIdx.x * SC_WARPS + warp; ms < codes; ms += gridDim.x * SC_WARPS) {
+        sc_block<R, FAST2>(ms, lane, s_warp[warp], s_rl2, s_hi, s_lo, ctl, pos, box, g, cell_start, cell_end,
+                           nbr, nnb, cap);
+        __syncwarp();
     }
 }
 

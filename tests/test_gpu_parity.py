@@ -132,6 +132,29 @@ def test_neighbor_list_bit_exact_replicated(cuda_lib, oracle_lib, precision):
         assert numpy.array_equal(a, b)
 
 
+@pytest.mark.parametrize('precision', [64, 32])
+def test_neighbor_list_bit_exact_slab_three_species(cuda_lib, oracle_lib, precision):
+    """A non-cubic box (14 x 7 x 7 cells: even and odd counts, periodic wrap of a half block of
+    cells) with three species; at this density about one 2x2x2 block of cells in ten holds more
+    than 32 particles: the block-of-cells list build in its general form."""
+    g = golden('ka_N1212_rumd')
+    side = numpy.array(g['side']) * numpy.array([2.0, 1.0, 1.0])
+    pos = numpy.concatenate([g['position'], g['position'] + numpy.array([g['side'][0], 0.0, 0.0])])
+    pos[:, 0] -= 0.5 * g['side'][0]
+    rng = numpy.random.default_rng(11)
+    pos += rng.uniform(-0.03, 0.03, size=pos.shape)
+    n = len(pos)
+    d = rounded({'position': pos, 'species': numpy.tile(g['species'], 2), 'side': side, 'center': numpy.zeros(3),
+                 'mass': numpy.ones(n), 'velocity': numpy.zeros((n, 3))}, precision)
+    ka3 = onp.kob_andersen(nsp=3)
+    eng = make_engine(cuda_lib, d, ka3, precision)
+    got = eng.neighbors()
+    assert eng.stats()['ncells'] == 14 * 7 * 7
+    ref = make_engine(oracle_lib, d, ka3, precision).neighbors()
+    for a, b in zip(got, ref):
+        assert numpy.array_equal(a, b)
+
+
 def test_nve_trajectory_pin(cuda_lib, oracle_lib, pins):
     """tests/test_lammps.py:33-40 through the CUDA engine, and step-for-step vs the oracle."""
     pin = pins['lj_N1000_nve_x0']
