@@ -57,7 +57,6 @@ struct b2_ctx {
     unsigned *peer_ticket = nullptr;
     int64_t peer_cap = 0;                             // records per inbox
     bool peer_on = false;
-    unsigned dd_seq = 0;
     int *img = nullptr;        // [3n] by original id
     double *ref = nullptr;     // [3n] by original id, unfolded, relative to centre
     // neighbour search
@@ -771,8 +770,8 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
     a.dd = 0;
     a.vmax_out = nullptr;
     a.vmax_mail = nullptr;
+    a.peer_state = nullptr;
     a.nranks = 1;
-    a.seq = 0;
     a.ke_partial = c->ke_partial;
     int64_t done = 0;
     while (done < steps) {
@@ -947,8 +946,8 @@ int Impl<R>::dd_step(b2_ctx *c, float *vmax_out)
     a.dd = 1;
     a.vmax_out = vmax_out;
     a.vmax_mail = c->peer_on ? c->peer_mail : nullptr;
+    a.peer_state = c->peer_on ? c->peer_ticket + 2 : nullptr;
     a.nranks = c->nranks;
-    a.seq = c->dd_seq;
     a.ke_partial = nullptr;
     auto step_kernel = k_step_nve<R, false>;
     if (n > 0) LAUNCH(step_kernel, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
@@ -1941,11 +1940,10 @@ template <typename R> struct ImplPeer {
         }
         char *L = c->peer_map[c->left], *Rt = c->peer_map[c->right];
         for (int64_t k = 0; k < count; k++) {
-            const unsigned seq = ++c->dd_seq;
-            const int par = (int)(seq & 1u);
             int rc = Impl<R>::dd_step(c, c->dd_vmax);
             if (rc) return rc;
-            LAUNCH(k_peer_commit, 1, 32, c->ctl, (const unsigned long long *)c->peer_buf, W, seq, c->dd_dt, c->dd_vmax + 1);
+            LAUNCH(k_peer_commit, 1, 32, c->ctl, c->peer_ticket + 2, (const unsigned long long *)c->peer_buf, W, c->dd_dt,
+                   c->dd_vmax + 1);
             PeerArgs<R> a;
             a.ctl = c->ctl;
             a.pos[0] = (P4 *)c->pos[0];
@@ -1957,16 +1955,18 @@ template <typename R> struct ImplPeer {
             a.first_r = n_own + c->n_ghost_l; a.n_ghost_r = c->n_ghost_r;
             a.box = make_box<R>(c);
             // what we send to the LEFT neighbour arrives there "from the right" (side 1), and vice versa
-            a.out_l = (double *)(L + peer_inbox(W, c->peer_cap, 1, par));
-            a.out_r = (double *)(Rt + peer_inbox(W, c->peer_cap, 0, par));
+            for (int par = 0; par < 2; par++) {
+                a.out_l[par] = (double *)(L + peer_inbox(W, c->peer_cap, 1, par));
+                a.out_r[par] = (double *)(Rt + peer_inbox(W, c->peer_cap, 0, par));
+                a.in_l[par] = (const double *)(c->peer_buf + peer_inbox(W, c->peer_cap, 0, par));
+                a.in_r[par] = (const double *)(c->peer_buf + peer_inbox(W, c->peer_cap, 1, par));
+            }
             a.flag_l = (unsigned long long *)(L + peer_off_flags(W) + 64);
             a.flag_r = (unsigned long long *)(Rt + peer_off_flags(W));
-            a.in_l = (const double *)(c->peer_buf + peer_inbox(W, c->peer_cap, 0, par));
-            a.in_r = (const double *)(c->peer_buf + peer_inbox(W, c->peer_cap, 1, par));
             a.my_flag_l = (const unsigned long long *)(c->peer_buf + peer_off_flags(W));
             a.my_flag_r = (const unsigned long long *)(c->peer_buf + peer_off_flags(W) + 64);
             a.ticket = c->peer_ticket;
-            a.seq = seq;
+            a.state = c->peer_ticket + 2;
             LAUNCH(k_peer_push<R>, std::max(1, cdiv(c->n_send_l + c->n_send_r, 256)), 256, a);
             LAUNCH(k_peer_pull<R>, std::max(1, cdiv(c->n_ghost_l + c->n_ghost_r, 256)), 256, a);
         }
@@ -1987,8 +1987,9 @@ int b2_peer_export(b2_ctx *c, int64_t halo_capacity, int rank, int nranks, char 
     const size_t bytes = peer_bytes(nranks, halo_capacity);
     CU(cudaMalloc((void **)&c->peer_buf, bytes));
     CU(cudaMemset(c->peer_buf, 0, bytes));
-    CU(cudaMalloc((void **)&c->peer_ticket, sizeof(unsigned)));
-    CU(cudaMemset(c->peer_ticket, 0, sizeof(unsigned)));
+    // [0] ticket of k_peer_push, [2] steps taken (the mail sequence), [3] halo wanted
+    CU(cudaMalloc((void **)&c->peer_ticket, 4 * sizeof(unsigned)));
+    CU(cudaMemset(c->peer_ticket, 0, 4 * sizeof(unsigned)));
     cudaIpcMemHandle_t h;
     CU(cudaIpcGetMemHandle(&h, c->peer_buf));
     memcpy(handle_out, &h, 64);
@@ -2026,7 +2027,6 @@ int b2_peer_connect(b2_ctx *c, const char *handles)
     CU(cudaMalloc((void **)&c->peer_mail, W * sizeof(unsigned long long *)));
     CU(cudaMemcpy(c->peer_mail, mail.data(), W * sizeof(unsigned long long *), cudaMemcpyHostToDevice));
     c->peer_on = true;
-    c->dd_seq = 0;
     return B2_OK;
 }
 

@@ -202,11 +202,11 @@ template <typename R> struct StepArgs {
     // (k_dd_commit); this kernel only publishes the local one
     int dd;
     float *vmax_out;
-    // peer-memory mode (b2_peer_*): the local max is also stored, tagged with the step's
-    // sequence number, straight into every rank's mailbox over NVLink
+    // peer-memory mode (b2_peer_*): the local max is also stored, tagged with the number of the
+    // step (peer_state[0] + 1), straight into every rank's mailbox over NVLink
     unsigned long long *const *vmax_mail;   // [nranks] device pointers: rank r's slot for OUR value
+    const unsigned *peer_state;             // see k_peer_commit
     int nranks;
-    unsigned seq;
     double *ke_partial;              // [gridDim] sum m v^2 per block (thermostatted runs)
 };
 
@@ -243,10 +243,9 @@ k_step_nve(StepArgs<R> a)
     typedef typename Pos4<R>::type P4;
     Ctl *ctl = a.ctl;
     if (ctl->halt_rebuild | ctl->overflow | ctl->done) {
-        if (a.dd && blockIdx.x == 0 && threadIdx.x == 0) {      // a no-op step moves nothing
-            *a.vmax_out = 0.f;
-            if (a.vmax_mail) peer_publish(a.vmax_mail, a.nranks, a.seq, 0.f);
-        }
+        // a no-op step moves nothing; with the peer-memory halo it also sends nothing: every rank
+        // takes the same decision, and the mail sequence counts the steps actually taken
+        if (a.dd && blockIdx.x == 0 && threadIdx.x == 0) *a.vmax_out = 0.f;
         return;
     }
     __shared__ PairTab<R> tab;
@@ -317,7 +316,7 @@ k_step_nve(StepArgs<R> a)
             const float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
             *a.vmax_out = vm2;
             ctl->blocks_done = 0u;
-            if (a.vmax_mail) peer_publish(a.vmax_mail, a.nranks, a.seq, vm2);
+            if (a.vmax_mail) peer_publish(a.vmax_mail, a.nranks, a.peer_state[0] + 1u, vm2);
         } else if (s_last) {
             __threadfence();
             float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
@@ -684,6 +683,11 @@ __global__ void k_inverse(const Ctl *__restrict__ ctl, int guarded, const int *_
 //   -> k_peer_pull    (waits for both neighbours, scatters the inbox into the ghosts)
 // Inboxes are double-buffered on the step parity: a neighbour can run at most
 // one step ahead.  Every wait has a time-out that raises Ctl::peer_error.
+// The sequence number is the count of steps TAKEN, kept on the device (state[0], which
+// outlives re-uploads; state[1] tells push/pull whether the last commit wants a halo):
+// a launch that finds the list invalid or the budget spent sends and awaits nothing
+// (all ranks decide alike, from the same global max), and the step that asks for a
+// refresh skips its halo, which the refresh replaces anyway.
 // ---------------------------------------------------------------------------
 #define PEER_TIMEOUT_CYCLES 20000000000LL      // ~10 s
 
@@ -698,11 +702,16 @@ __device__ __forceinline__ bool peer_wait_ge(const volatile unsigned long long *
     return true;
 }
 
-__global__ void k_peer_commit(Ctl *ctl, const unsigned long long *mail, int nranks, unsigned seq, double drift,
+__global__ void k_peer_commit(Ctl *ctl, unsigned *state, const unsigned long long *mail, int nranks, double drift,
                               float *gv_out)
 {
     // one warp; lane r waits for rank r's value of this step
     const int lane = threadIdx.x;
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) {              // the step kernel did nothing either
+        if (lane == 0) { state[1] = 0u; *gv_out = 0.f; }
+        return;
+    }
+    const unsigned seq = state[0] + 1u;
     unsigned bits = 0u;
     bool ok = true;
     if (ctl->peer_error) ok = false;
@@ -722,15 +731,19 @@ __global__ void k_peer_commit(Ctl *ctl, const unsigned long long *mail, int nran
     if (lane == 0) {
         const float gv = __uint_as_float(bits);                       // non-negative floats order like their bits
         *gv_out = gv;
-        if (!(ctl->halt_rebuild | ctl->overflow | ctl->done | ctl->peer_error)) {
+        unsigned go = 0u;
+        if (!ctl->peer_error) {
             double bound = ctl->disp_bound + fabs(drift) * sqrt((double)gv) * (1.0 + 1e-6);
             ctl->disp_bound = bound;
             ctl->cur ^= 1u;
             long long s = ctl->steps_done + 1;
             ctl->steps_done = s;
+            state[0] = seq;
             if (s >= ctl->steps_target) ctl->done = 1u;
-            if (bound > ctl->half_skin) ctl->halt_rebuild = 1u;
+            // a refresh re-selects and re-sends the ghosts anyway: no halo after the step that asks for one
+            if (bound > ctl->half_skin) ctl->halt_rebuild = 1u; else go = 1u;
         }
+        state[1] = go;
     }
 }
 
@@ -742,18 +755,20 @@ template <typename R> struct PeerArgs {
     int n_send_l, n_send_r;
     int first_l, n_ghost_l, first_r, n_ghost_r;      // local ids of the ghosts
     Box<R> box;
-    double *out_l, *out_r;                           // REMOTE: the neighbours' inboxes of this parity
+    double *out_l[2], *out_r[2];                     // REMOTE: the neighbours' inboxes, by step parity
     unsigned long long *flag_l, *flag_r;             // REMOTE: the neighbours' arrival flags
-    const double *in_l, *in_r;                       // LOCAL inboxes of this parity
+    const double *in_l[2], *in_r[2];                 // LOCAL inboxes, by step parity
     const unsigned long long *my_flag_l, *my_flag_r; // LOCAL arrival flags (from the left / right neighbour)
     unsigned *ticket;                                // LOCAL counter
-    unsigned seq;
+    const unsigned *state;                           // LOCAL [steps taken, halo wanted] (k_peer_commit)
 };
 
 template <typename R>
 __global__ void __launch_bounds__(256)
 k_peer_push(PeerArgs<R> a)
 {
+    if (!a.state[1]) return;
+    const unsigned seq = a.state[0];
     const typename Pos4<R>::type *pos = a.ctl->cur ? a.pos[1] : a.pos[0];
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = a.n_send_l + a.n_send_r;
@@ -763,7 +778,7 @@ k_peer_push(PeerArgs<R> a)
         const int id = left ? a.send_l[q] : a.send_r[q];
         double x, y, z;
         to_double(pos[a.inv[id]], a.box, x, y, z);
-        double *dst = (left ? a.out_l : a.out_r) + 3 * (size_t)q;
+        double *dst = (left ? (seq & 1u ? a.out_l[1] : a.out_l[0]) : (seq & 1u ? a.out_r[1] : a.out_r[0])) + 3 * (size_t)q;
         dst[0] = x; dst[1] = y; dst[2] = z;                          // stores into the neighbour's HBM
     }
     __threadfence_system();
@@ -773,8 +788,8 @@ k_peer_push(PeerArgs<R> a)
         if (t == gridDim.x - 1) {                                     // everything of this rank is on its way
             *a.ticket = 0u;
             __threadfence_system();
-            *(volatile unsigned long long *)a.flag_l = (unsigned long long)a.seq;
-            *(volatile unsigned long long *)a.flag_r = (unsigned long long)a.seq;
+            *(volatile unsigned long long *)a.flag_l = (unsigned long long)seq;
+            *(volatile unsigned long long *)a.flag_r = (unsigned long long)seq;
         }
     }
 }
@@ -784,10 +799,12 @@ __global__ void __launch_bounds__(256)
 k_peer_pull(PeerArgs<R> a)
 {
     __shared__ bool s_ok;
+    if (!a.state[1]) return;
+    const unsigned seq = a.state[0];
     if (threadIdx.x == 0)
         s_ok = !a.ctl->peer_error &&
-               peer_wait_ge((const volatile unsigned long long *)a.my_flag_l, a.seq, a.ctl) &&
-               peer_wait_ge((const volatile unsigned long long *)a.my_flag_r, a.seq, a.ctl);
+               peer_wait_ge((const volatile unsigned long long *)a.my_flag_l, seq, a.ctl) &&
+               peer_wait_ge((const volatile unsigned long long *)a.my_flag_r, seq, a.ctl);
     __syncthreads();
     if (!s_ok) return;
     typename Pos4<R>::type *pos = a.ctl->cur ? a.pos[1] : a.pos[0];
@@ -795,7 +812,7 @@ k_peer_pull(PeerArgs<R> a)
     if (k >= a.n_ghost_l + a.n_ghost_r) return;
     const bool left = k < a.n_ghost_l;
     const int q = left ? k : k - a.n_ghost_l;
-    const double *src = (left ? a.in_l : a.in_r) + 3 * (size_t)q;
+    const double *src = (left ? (seq & 1u ? a.in_l[1] : a.in_l[0]) : (seq & 1u ? a.in_r[1] : a.in_r[0])) + 3 * (size_t)q;
     const int s = a.inv[(left ? a.first_l : a.first_r) + q];
     // written by another GPU: read around L1
     pos[s] = encode_pos(__ldcg(src), __ldcg(src + 1), __ldcg(src + 2), praw(pos[s]), a.box);

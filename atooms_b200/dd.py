@@ -23,6 +23,8 @@ moves between ranks is a torch tensor, so the same code runs on CUDA tensors
 with the NCCL backend (product) and on CPU tensors with gloo (tests, with the
 CPU oracle standing in as the engine).
 """
+import time
+
 import numpy
 import torch
 import torch.distributed as dist
@@ -98,6 +100,7 @@ class SlabDomain(object):
         self.refreshes = 0
         self.steps = 0
         self.halo_bytes_per_step = 0
+        self.counters = {'rounds': 0, 'enqueued': 0, 'refreshes': 0, 'refresh_ms': 0.0}
 
     # -- helpers ---------------------------------------------------------------------
     @property
@@ -326,12 +329,18 @@ class SlabDomain(object):
             done, need = eng.dd_poll()
             since_refresh += done
             base += done
+            c = self.counters
+            c['rounds'] += 1
+            c['enqueued'] += m
             if need:
                 # every rank sees the same flag (the bound comes from the global max)
+                t0 = time.perf_counter()
                 self._batch = max(1, min(since_refresh, 64))
                 self.refresh()
                 eng.dd_begin(steps - base, self.dt, False)
                 since_refresh = 0
+                c['refreshes'] += 1
+                c['refresh_ms'] += (time.perf_counter() - t0) * 1e3     # both ends are synchronous
             elif done == m and base < steps:
                 self._batch = min(self._batch + 2, 64)
             if base < steps and not need:

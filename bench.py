@@ -295,6 +295,7 @@ def main():
                 dom.run(INNER)
             l0 = dom.engine.stats()['launches']
             r0 = dom.refreshes
+            c0 = dict(dom.counters)
             sampler = ClockSampler(local_rank) if rank == 0 else None
             barrier()
             if sampler:
@@ -310,6 +311,7 @@ def main():
                 clocks = sampler.stop()
             launches = dom.engine.stats()['launches'] - l0
             refreshes_timed = dom.refreshes - r0
+            cnt = {k: dom.counters[k] - c0[k] for k in c0}
             th = dom.thermo()
             ntot = th['n']
             value = ntot * INNER * args.steps / (ms * 1e-3)
@@ -336,7 +338,8 @@ def main():
             barrier()
             e2e_s = max_over_ranks(time.perf_counter() - t0)
             results[precision] = dict(value=value, ms=ms, launches=launches,
-                                      prof={'ms_steps': 0.0, 'ms_refresh': 0.0, 'step_launches': 0,
+                                      prof={'ms_steps': ms - cnt['refresh_ms'], 'ms_refresh': cnt['refresh_ms'],
+                                            'step_launches': cnt['enqueued'], 'rounds': cnt['rounds'],
                                             'steps': INNER * args.steps, 'refreshes': refreshes_timed},
                                       e2e=ntot * INNER * e2e_steps / e2e_s, e2e_steps=e2e_steps,
                                       stats=dom.engine.stats(), energy=(th['kinetic'] + th['potential']) / ntot,
