@@ -125,8 +125,12 @@ class Library(object):
             self.dll.b2_peer_export.argtypes = [_vp, _i64, _int, _int, ctypes.c_char_p]
             self.dll.b2_peer_connect.argtypes = [_vp, ctypes.c_char_p]
             self.dll.b2_peer_run.argtypes = [_vp, _i64]
+            self.dll.b2_peer_set_ids.argtypes = [_vp, _vp, _vp]
+            self.dll.b2_peer_refresh.argtypes = [_vp, _dbl, _dbl, _dbl, ctypes.POINTER(ctypes.c_int64)]
+            self.dll.b2_peer_state.argtypes = [_vp, _vp, _vp, _vp, _vp]
             for name in ('b2_nccl_unique_id', 'b2_nccl_init', 'b2_nccl_set_halo', 'b2_nccl_run',
-                         'b2_peer_export', 'b2_peer_connect', 'b2_peer_run'):
+                         'b2_peer_export', 'b2_peer_connect', 'b2_peer_run', 'b2_peer_set_ids',
+                         'b2_peer_refresh', 'b2_peer_state'):
                 getattr(self.dll, name).restype = _int
         version = self.dll.b2_abi_version()
         if version != ABI_VERSION:
@@ -425,6 +429,19 @@ class Engine(object):
 
     def peer_run(self, count):
         self._call('b2_peer_run', int(count))
+
+    def peer_set_ids(self, gid_ptr, image_ptr=None):
+        self._call('b2_peer_set_ids', gid_ptr, image_ptr)
+
+    def peer_refresh(self, x_lo, x_hi, margin):
+        """Device-side slab refresh; returns (owned, ghosts_l, ghosts_r, send_l, send_r, out, in)."""
+        out = (ctypes.c_int64 * 7)()
+        self._call('b2_peer_refresh', float(x_lo), float(x_hi), float(margin), out)
+        self.n = int(out[0] + out[1] + out[2])
+        return tuple(int(v) for v in out)
+
+    def peer_state(self, gid_ptr=None, image_ptr=None, species_ptr=None, mass_ptr=None):
+        self._call('b2_peer_state', gid_ptr, image_ptr, species_ptr, mass_ptr)
 
 
 class Batch(object):

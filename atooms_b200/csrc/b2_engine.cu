@@ -5,6 +5,7 @@
 #include "b2_neigh.cuh"
 #include "b2_force.cuh"
 #include "b2_batch.cuh"
+#include "b2_ddr.cuh"
 
 #include <dlfcn.h>
 #include <nccl.h>
@@ -57,6 +58,17 @@ struct b2_ctx {
     unsigned *peer_ticket = nullptr;
     int64_t peer_cap = 0;                             // records per inbox
     bool peer_on = false;
+    // slab refresh on the device (b2_peer_refresh, b2_ddr.cuh)
+    unsigned char *ddr_cls = nullptr;
+    int *ddr_blk = nullptr, *ddr_keep = nullptr, *ddr_go[2] = {nullptr, nullptr};
+    int *ddr_near[4] = {nullptr, nullptr, nullptr, nullptr};      // near_l slot / new id, near_r slot / new id
+    int *ddr_send[2] = {nullptr, nullptr};
+    unsigned *ddr_cnt = nullptr, *ddr_hcnt = nullptr;             // device counters and their pinned copy
+    long long *ddr_gid[2] = {nullptr, nullptr};                   // global ids by local id (current, next)
+    int *ddr_cimg[2] = {nullptr, nullptr};                        // box crossings before the last ingestion
+    int64_t ddr_ncap = 0;
+    int ddr_mig_cap = 0;
+    bool ddr_ids = false;                                         // gid / cimg describe the resident particles
     int *img = nullptr;        // [3n] by original id
     double *ref = nullptr;     // [3n] by original id, unfolded, relative to centre
     // neighbour search
@@ -575,6 +587,7 @@ int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
         // grow with headroom: a decomposed domain re-uploads a slightly different n at every refresh
         if ((rc = alloc_particles(c, c->pos[0] ? n + n / 8 + 1024 : n))) return rc;
     }
+    c->ddr_ids = false;
     c->n = n;
     c->list_dirty = true;
     c->forces_valid = c->ev_valid = false;
@@ -1063,6 +1076,15 @@ int b2_destroy(b2_ctx *c)
     if (c->peer_buf) cudaFree(c->peer_buf);
     if (c->peer_mail) cudaFree(c->peer_mail);
     if (c->peer_ticket) cudaFree(c->peer_ticket);
+    {
+        void *ddr[] = {c->ddr_cls, c->ddr_blk, c->ddr_keep, c->ddr_go[0], c->ddr_go[1], c->ddr_near[0], c->ddr_near[1],
+                       c->ddr_near[2], c->ddr_near[3], c->ddr_send[0], c->ddr_send[1], c->ddr_cnt, c->ddr_gid[0],
+                       c->ddr_gid[1], c->ddr_cimg[0], c->ddr_cimg[1]};
+        // the send lists may be the ones a context still points at; they die with it
+        for (void *q : ddr)
+            if (q) cudaFree(q);
+        if (c->ddr_hcnt) cudaFreeHost(c->ddr_hcnt);
+    }
     if (c->hctl) cudaFreeHost(c->hctl);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -1923,7 +1945,20 @@ static size_t peer_inbox(int W, int64_t cap, int side, int parity)
 {
     return peer_off_inbox(W) + ((size_t)side * 2 + parity) * (size_t)cap * 24;
 }
-static size_t peer_bytes(int W, int64_t cap) { return peer_inbox(W, cap, 2, 0); }
+static size_t peer_step_bytes(int W, int64_t cap) { return (peer_inbox(W, cap, 2, 0) + 255) & ~(size_t)255; }
+// the refresh mailboxes (b2_peer_refresh) follow the per-step ones: two arrival flags, then one
+// inbox per (side, parity) = [64-byte header][migrants][ghost layer]
+static int64_t ddr_mig_cap_of(int64_t cap) { return cap / 4 + 1024; }
+static size_t ddr_inbox_bytes(int64_t cap)
+{
+    return (64 + (size_t)ddr_mig_cap_of(cap) * DDR_MIG_BYTES + (size_t)cap * DDR_GHOST_BYTES + 255) & ~(size_t)255;
+}
+static size_t ddr_off_flags(int W, int64_t cap) { return peer_step_bytes(W, cap); }
+static size_t ddr_inbox(int W, int64_t cap, int side, int parity)
+{
+    return ddr_off_flags(W, cap) + 256 + ((size_t)side * 2 + parity) * ddr_inbox_bytes(cap);
+}
+static size_t peer_bytes(int W, int64_t cap) { return ddr_inbox(W, cap, 2, 0); }
 
 template <typename R> struct ImplPeer {
     typedef typename Pos4<R>::type P4;
@@ -2028,6 +2063,206 @@ int b2_peer_connect(b2_ctx *c, const char *handles)
     CU(cudaMemcpy(c->peer_mail, mail.data(), W * sizeof(unsigned long long *), cudaMemcpyHostToDevice));
     c->peer_on = true;
     return B2_OK;
+}
+
+}  // extern "C"
+
+// ---- slab refresh on the device (kernels in b2_ddr.cuh) ---------------------------------
+template <typename R>
+__global__ void k_ddr_state(const Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
+                            const typename Pos4<R>::type *pos1, const typename Vec4<R>::type *__restrict__ vel,
+                            const int *__restrict__ orig, const int *__restrict__ img, const int *__restrict__ cimg,
+                            int n, int *__restrict__ img_out, int *__restrict__ spe_out, double *__restrict__ mass_out)
+{
+    const typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const int o = orig[s];
+    if (spe_out) spe_out[o] = praw(pos[s]);
+    if (mass_out) mass_out[o] = (double)vel[s].w;
+    if (img_out)
+        for (int d = 0; d < 3; d++) img_out[3 * o + d] = cimg[3 * o + d] + img[3 * o + d];
+}
+
+static int ddr_alloc(b2_ctx *c)
+{
+    int rc;
+    if (c->ddr_ncap == c->ncap && c->ddr_cls) return B2_OK;
+    const int64_t n = c->ncap;
+    const int64_t gc = c->peer_cap, mc = ddr_mig_cap_of(c->peer_cap);
+    if ((rc = dev_alloc(c, &c->ddr_cls, n))) return rc;
+    if ((rc = dev_alloc(c, &c->ddr_blk, 5 * (size_t)cdiv(n, DDR_THREADS)))) return rc;
+    if ((rc = dev_alloc(c, &c->ddr_keep, n))) return rc;
+    for (int k = 0; k < 2; k++) {
+        if ((rc = dev_alloc(c, &c->ddr_go[k], mc))) return rc;
+        if ((rc = dev_alloc(c, &c->ddr_send[k], gc + mc))) return rc;
+        if ((rc = dev_alloc(c, &c->ddr_gid[k], n))) return rc;
+        if ((rc = dev_alloc(c, &c->ddr_cimg[k], 3 * n))) return rc;
+    }
+    for (int k = 0; k < 4; k++)
+        if ((rc = dev_alloc(c, &c->ddr_near[k], gc))) return rc;
+    if (!c->ddr_cnt) {
+        CU(cudaMalloc((void **)&c->ddr_cnt, 32 * sizeof(unsigned)));
+        CU(cudaMemset(c->ddr_cnt, 0, 32 * sizeof(unsigned)));
+        CU(cudaMallocHost((void **)&c->ddr_hcnt, 32 * sizeof(unsigned)));
+    }
+    c->ddr_ncap = n;
+    c->ddr_mig_cap = (int)mc;
+    c->ddr_ids = false;
+    return B2_OK;
+}
+
+template <typename R> struct ImplDdr {
+    typedef typename Pos4<R>::type P4;
+    typedef typename Vec4<R>::type V4;
+    static_assert(sizeof(DdrMig<R>) <= DDR_MIG_BYTES && sizeof(DdrMig<R>) % 16 == 0, "migrant record layout");
+    static_assert(sizeof(P4) <= DDR_GHOST_BYTES, "ghost record layout");
+
+    static int refresh(b2_ctx *c, double lo, double hi, double margin, int64_t *counts)
+    {
+        int rc;
+        const int n = (int)c->n, W = c->nranks;
+        DdrArgs<R> a;
+        a.ctl = c->ctl;
+        a.pos[0] = (const P4 *)c->pos[0];
+        a.pos[1] = (const P4 *)c->pos[1];
+        a.vel = (const V4 *)c->vel;
+        a.orig = c->orig;
+        a.img = c->img;
+        a.cimg = c->ddr_cimg[0];
+        a.gid = c->ddr_gid[0];
+        a.n = n;
+        a.ncap = (int)c->ncap;
+        a.rank = c->myrank;
+        a.nranks = W;
+        a.lo = lo; a.hi = hi; a.margin = margin;
+        a.box = make_box<R>(c);
+        a.cls = c->ddr_cls;
+        a.blk = c->ddr_blk;
+        a.nblk = cdiv(n, DDR_THREADS);
+        a.keep = c->ddr_keep;
+        a.go_l = c->ddr_go[0]; a.go_r = c->ddr_go[1];
+        a.near_l_slot = c->ddr_near[0]; a.near_l_new = c->ddr_near[1];
+        a.near_r_slot = c->ddr_near[2]; a.near_r_new = c->ddr_near[3];
+        a.mig_cap = c->ddr_mig_cap;
+        a.ghost_cap = (int)c->peer_cap;
+        a.cnt = c->ddr_cnt;
+        char *L = c->peer_map[c->left], *Rt = c->peer_map[c->right];
+        // what we send to the LEFT neighbour arrives there "from the right" (side 1), and vice versa
+        a.out_l = L + ddr_inbox(W, c->peer_cap, 1, 0);
+        a.out_r = Rt + ddr_inbox(W, c->peer_cap, 0, 0);
+        a.inbox_bytes = ddr_inbox_bytes(c->peer_cap);
+        a.flag_l = (unsigned long long *)(L + ddr_off_flags(W, c->peer_cap) + 64);
+        a.flag_r = (unsigned long long *)(Rt + ddr_off_flags(W, c->peer_cap));
+        a.in_l = c->peer_buf + ddr_inbox(W, c->peer_cap, 0, 0);
+        a.in_r = c->peer_buf + ddr_inbox(W, c->peer_cap, 1, 0);
+        a.my_flag_l = (const unsigned long long *)(c->peer_buf + ddr_off_flags(W, c->peer_cap));
+        a.my_flag_r = (const unsigned long long *)(c->peer_buf + ddr_off_flags(W, c->peer_cap) + 64);
+        a.npos = (P4 *)c->tpos;
+        a.nvel = (V4 *)c->tvel;
+        a.ngid = c->ddr_gid[1];
+        a.ncimg = c->ddr_cimg[1];
+        a.nsend_l = c->ddr_send[0];
+        a.nsend_r = c->ddr_send[1];
+
+        CU(cudaMemsetAsync(c->ddr_cnt, 0, 6 * sizeof(unsigned), c->stream));        // counts and error bits
+        LAUNCH(k_ddr_classify<R>, a.nblk, DDR_THREADS, a);
+        LAUNCH(k_ddr_scan, 1, 1024, a.blk, a.nblk, a.cnt);
+        LAUNCH(k_ddr_scatter<R>, a.nblk, DDR_THREADS, a);
+        LAUNCH(k_ddr_pack<R>, cdiv(2 * a.mig_cap + 2 * a.ghost_cap, DDR_THREADS), DDR_THREADS, a);
+        LAUNCH(k_ddr_assemble<R>, cdiv((int)c->ncap, DDR_THREADS), DDR_THREADS, a);
+        CU(cudaMemcpyAsync(c->ddr_hcnt, c->ddr_cnt, 32 * sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaGetLastError());
+        const unsigned *h = c->ddr_hcnt;
+        if (h[DC_ERR]) {
+            const unsigned e = h[DC_ERR];
+            return fail(c, e & DE_TIMEOUT ? B2_ECUDA : B2_ESTATE,
+                        "b2_peer_refresh failed:%s%s%s%s%s (stay %u, leave %u/%u, near-face %u/%u of capacity %d/%lld, "
+                        "room for %lld particles)",
+                        e & DE_HOP ? " a particle moved more than one slab;" : "",
+                        e & DE_MIG_CAP ? " more migrants than the mailbox holds;" : "",
+                        e & DE_GHOST_CAP ? " ghost layer larger than the mailbox;" : "",
+                        e & DE_TIMEOUT ? " a neighbour did not answer within 10 s;" : "",
+                        e & DE_NCAP ? " the new domain does not fit the particle arrays;" : "",
+                        h[DC_KEEP], h[DC_GO_L], h[DC_GO_R], h[DC_NEAR_L], h[DC_NEAR_R], c->ddr_mig_cap,
+                        (long long)c->peer_cap, (long long)c->ncap);
+        }
+        // adopt the new arrays: what b2_upload does, without the staging copies
+        const int64_t nn = (int64_t)h[DC_N_OWN] + h[DC_G_L] + h[DC_G_R];
+        std::swap(c->pos[0], c->tpos);
+        std::swap(c->vel, c->tvel);
+        std::swap(c->ddr_gid[0], c->ddr_gid[1]);
+        std::swap(c->ddr_cimg[0], c->ddr_cimg[1]);
+        c->n = nn;
+        c->list_dirty = true;
+        c->forces_valid = c->ev_valid = false;
+        c->min_resume = false;
+        if (c->mvel) { cudaFree(c->mvel); c->mvel = nullptr; }
+        memset(c->hctl, 0, sizeof(Ctl));
+        c->hctl->halt_rebuild = 1u;
+        c->hctl->half_skin = 0.5 * c->skin;
+        if ((rc = push_ctl(c))) return rc;
+        if (nn > 0)
+            LAUNCH(k_ddr_finish<R>, cdiv((int)nn, 256), 256, (const P4 *)c->pos[0], (int)nn, make_box<R>(c),
+                   c->orig, c->inv, c->img, c->ref);
+        c->send_l = c->ddr_send[0]; c->send_r = c->ddr_send[1];
+        c->n_send_l = (int)h[DC_SEND_L]; c->n_send_r = (int)h[DC_SEND_R];
+        c->n_ghost_l = (int)h[DC_G_L]; c->n_ghost_r = (int)h[DC_G_R];
+        counts[0] = h[DC_N_OWN]; counts[1] = h[DC_G_L]; counts[2] = h[DC_G_R];
+        counts[3] = h[DC_SEND_L]; counts[4] = h[DC_SEND_R];
+        counts[5] = h[DC_GO_L] + h[DC_GO_R]; counts[6] = h[DC_FROM_L] + h[DC_FROM_R];
+        return B2_OK;
+    }
+
+    static int state(b2_ctx *c, int32_t *img, int32_t *spe, double *mass)
+    {
+        const int n = (int)c->n;
+        LAUNCH(k_ddr_state<R>, cdiv(n, 256), 256, c->ctl, (const P4 *)c->pos[0], (const P4 *)c->pos[1],
+               (const V4 *)c->vel, c->orig, c->img, c->ddr_cimg[0], n, img, spe, mass);
+        return B2_OK;
+    }
+};
+
+extern "C" {
+
+int b2_peer_set_ids(b2_ctx *c, const int64_t *gid_dev, const int32_t *image_dev)
+{
+    NEED_PARTICLES("b2_peer_set_ids");
+    if (!c->peer_on) return fail(c, B2_ESTATE, "b2_peer_set_ids: call b2_peer_export / b2_peer_connect first");
+    if (!gid_dev) return fail(c, B2_EINVAL, "b2_peer_set_ids: gid_dev is NULL");
+    int rc = ddr_alloc(c);
+    if (rc) return rc;
+    static_assert(sizeof(long long) == sizeof(int64_t), "64-bit ids");
+    CU(cudaMemcpyAsync(c->ddr_gid[0], gid_dev, c->n * sizeof(int64_t), cudaMemcpyDefault, c->stream));
+    if (image_dev) CU(cudaMemcpyAsync(c->ddr_cimg[0], image_dev, 3 * c->n * sizeof(int32_t), cudaMemcpyDefault, c->stream));
+    else CU(cudaMemsetAsync(c->ddr_cimg[0], 0, 3 * c->n * sizeof(int32_t), c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->ddr_ids = true;
+    return B2_OK;
+}
+
+int b2_peer_state(b2_ctx *c, int64_t *gid_dev, int32_t *image_dev, int32_t *species_dev, double *mass_dev)
+{
+    NEED_PARTICLES("b2_peer_state");
+    if (!c->ddr_ids) return fail(c, B2_ESTATE, "b2_peer_state: no ids resident (b2_peer_set_ids, or a b2_upload since)");
+    int rc = c->precision == B2_FP32 ? ImplDdr<float>::state(c, image_dev, species_dev, mass_dev)
+                                     : ImplDdr<double>::state(c, image_dev, species_dev, mass_dev);
+    if (rc) return rc;
+    if (gid_dev) CU(cudaMemcpyAsync(gid_dev, c->ddr_gid[0], c->n * sizeof(int64_t), cudaMemcpyDefault, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return B2_OK;
+}
+
+int b2_peer_refresh(b2_ctx *c, double x_lo, double x_hi, double margin, int64_t counts_out[7])
+{
+    NEED_PARTICLES("b2_peer_refresh");
+    if (!c->peer_on) return fail(c, B2_ESTATE, "b2_peer_refresh: call b2_peer_export / b2_peer_connect first");
+    if (!c->ddr_ids) return fail(c, B2_ESTATE, "b2_peer_refresh: call b2_peer_set_ids after the last b2_upload");
+    if (!counts_out || !(x_hi > x_lo) || !(margin > 0.0)) return fail(c, B2_EINVAL, "b2_peer_refresh: bad argument");
+    if (c->ddr_ncap != c->ncap) return fail(c, B2_ESTATE, "b2_peer_refresh: the particle arrays were re-allocated");
+    return c->precision == B2_FP32 ? ImplDdr<float>::refresh(c, x_lo, x_hi, margin, counts_out)
+                                   : ImplDdr<double>::refresh(c, x_lo, x_hi, margin, counts_out);
 }
 
 int b2_peer_run(b2_ctx *c, int64_t count)

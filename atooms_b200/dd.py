@@ -38,7 +38,7 @@ class SlabDomain(object):
 
     def __init__(self, position, velocity, species, side, model='lennard_jones', dt=0.002, skin=0.3,
                  precision=64, mass=None, gid=None, center=None, device=None, library=None, group=None,
-                 fast_comm=None, peer=None):
+                 fast_comm=None, peer=None, device_refresh=None):
         """`position` ... are the particles this rank holds initially (global
         coordinates, any x: the first refresh sends strays to the ring neighbour
         that owns them; they must not be more than one slab away)."""
@@ -94,6 +94,13 @@ class SlabDomain(object):
             peer = self._fast
         self._peer = bool(peer) and self._fast
         self._peer_cap = 0
+        # refresh on the device (b2_peer_refresh): migration, ghost selection and re-ingestion in
+        # five kernels, exchanged through the same mailboxes; the engine then owns the global ids
+        # and image counters too, and the tensors below are fetched back only on demand
+        self._dev_refresh = self._peer if device_refresh is None else (bool(device_refresh) and self._peer)
+        self._ids_resident = False
+        self._n_own_res = 0
+        self._uploads = 0
         self.profile = None
         self._resident = False
         self._batch = 8
@@ -105,7 +112,7 @@ class SlabDomain(object):
     # -- helpers ---------------------------------------------------------------------
     @property
     def n_own(self):
-        return self.pos.shape[0]
+        return self._n_own_res if self._ids_resident else self.pos.shape[0]
 
     def _left(self):
         return (self.rank - 1) % self.world
@@ -152,7 +159,32 @@ class SlabDomain(object):
         self._t_last = now
 
     # -- refresh: migration + ghost selection + re-upload ---------------------------------
+    def _refresh_on_device(self):
+        lo, hi = self.rank / self.world, (self.rank + 1) / self.world
+        margin = self.rlist / self.side[0] * (1 + 1e-6) + 1e-12
+        c = self.engine.peer_refresh(lo, hi, margin)
+        self._n_own_res, self._n_gl, self._n_gr = c[0], c[1], c[2]
+        self.halo_bytes_per_step = 24 * (c[3] + c[4])
+        self.pos = self.vel = self.mass = self.spe = self.gid = self.img = None     # stale: see _pull_state
+        self.refreshes += 1
+
+    def _pull_state(self):
+        """Fetch the owned particles' state back from the engine (device-refresh mode)."""
+        n, m = self._n_own_res, self.engine.n
+        i32 = dict(dtype=torch.int32, device=self.dev)
+        pos = torch.empty((m, 3), dtype=torch.float64, device=self.dev)
+        vel = torch.empty((m, 3), dtype=torch.float64, device=self.dev)
+        gid = torch.empty(m, dtype=torch.int64, device=self.dev)
+        img, spe = torch.empty((m, 3), **i32), torch.empty(m, **i32)
+        mass = torch.empty(m, dtype=torch.float64, device=self.dev)
+        self.engine.download_device(pos.data_ptr(), vel.data_ptr(), 0)
+        self.engine.peer_state(gid.data_ptr(), img.data_ptr(), spe.data_ptr(), mass.data_ptr())
+        self.pos, self.vel, self.gid, self.img = pos[:n], vel[:n], gid[:n], img[:n]       # img: total crossings
+        self.spe, self.mass = spe[:n], mass[:n]
+
     def refresh(self):
+        if self._ids_resident and self._resident:
+            return self._refresh_on_device()
         self._tick(None)
         side = torch.as_tensor(self.side, dtype=torch.float64, device=self.dev)
         ctr = torch.as_tensor(self.center, dtype=torch.float64, device=self.dev)
@@ -242,6 +274,7 @@ class SlabDomain(object):
         mass = torch.cat([self.mass, self.mass.new_ones(ng)], dim=0).contiguous()
         spe = torch.cat([self.spe, ghosts[:, 3].round().to(torch.int32) | capi.GHOST], dim=0).contiguous()
         self.engine.upload_device(n + ng, pos.data_ptr(), spe.data_ptr(), vel.data_ptr(), mass.data_ptr())
+        self._uploads += 1
         self._tick('upload')
         if not self._fast:          # halo buffers of the generic (torch.distributed) path
             f64 = dict(dtype=torch.float64, device=self.dev)
@@ -273,6 +306,17 @@ class SlabDomain(object):
             dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
             if int(flag) == 0:
                 self._peer = False              # no peer access on this box: stay on NCCL
+        if self._peer and self._dev_refresh:
+            # hand the ids over; the engine's first upload has no headroom for a domain that grows,
+            # a repeated one has (12 %)
+            if self._uploads == 1:
+                self._uploads += 1
+                self.engine.upload_device(n + ng, pos.data_ptr(), spe.data_ptr(), vel.data_ptr(), mass.data_ptr())
+            none = torch.full((ng,), -1, dtype=torch.int64, device=self.dev)
+            gid_all = torch.cat([self.gid, none]).contiguous()
+            img_all = torch.cat([self.img, torch.zeros((ng, 3), dtype=torch.int32, device=self.dev)]).contiguous()
+            self.engine.peer_set_ids(gid_all.data_ptr(), img_all.data_ptr())
+            self._ids_resident, self._n_own_res = True, n
         self._tick('halo setup')
         self._resident = True
         self.refreshes += 1
@@ -365,7 +409,10 @@ class SlabDomain(object):
 
     def gather(self):
         """(gid-ordered) global position, velocity, image on every rank — for tests."""
-        if self._resident:
+        if self._ids_resident and self._resident:
+            self._pull_state()
+            pos, vel, img = self.pos, self.vel, self.img
+        elif self._resident:
             n = self.n_own
             pos = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
             vel = torch.empty((self.engine.n, 3), dtype=torch.float64, device=self.dev)
@@ -388,6 +435,9 @@ class SlabDomain(object):
     def load_host(self, position, velocity):
         """Replace the owned particles' coordinates and velocities from host arrays
         (pinned memory makes the copies asynchronous); same particles, same order."""
+        if self._ids_resident:
+            self._pull_state()              # ids, species, masses in the engine's current order
+            self._ids_resident = False
         self.pos = torch.as_tensor(position).to(self.dev, non_blocking=True)
         self.vel = torch.as_tensor(velocity).to(self.dev, non_blocking=True)
         self._resident = False

@@ -52,6 +52,34 @@ int b2_peer_export(b2_ctx *ctx, int64_t halo_capacity, int rank, int nranks, cha
 int b2_peer_connect(b2_ctx *ctx, const char *handles /* nranks x 64 bytes, by rank */);
 int b2_peer_run(b2_ctx *ctx, int64_t count);
 
+/* ---- slab refresh on the device (peer-memory path only) --------------------------------
+ *
+ * The reference has no counterpart (its engines are single-domain); this replaces the
+ * host-driven refresh of atooms_b200/dd.py — download, classify, exchange through
+ * torch.distributed, re-upload: 1.7 ms for 1.2M particles per GPU — by five kernels and one
+ * host synchronisation.  The context then also owns what travels with a particle besides
+ * position, velocity, mass and species: its global id and its count of box crossings.
+ *
+ * b2_peer_set_ids     hands over the global ids (and the crossings so far) of the resident
+ *                     particles, by local id; needed again after every b2_upload.
+ * b2_peer_refresh     owned particles whose x / L_x + 1/2 left [x_lo, x_hi) move to the ring
+ *                     neighbour they now belong to, those within `margin` (same units) of a
+ *                     face are sent as ghosts, and the context re-ingests
+ *                     [staying | from left | from right | ghosts left | ghosts right]
+ *                     with the per-step halo (b2_nccl_set_halo) set up to match; the list is
+ *                     rebuilt by the next b2_dd_begin.  Every rank must call it at the same
+ *                     point.  counts_out = {owned, ghosts left, ghosts right, sent left per
+ *                     step, sent right per step, migrants out, migrants in}.
+ *                     Limits: migrants per face <= halo_capacity / 4 + 1024, ghosts per face
+ *                     <= halo_capacity, and the new domain must fit the arrays allocated by
+ *                     the last b2_upload (which leaves 12 % headroom on a re-upload); beyond
+ *                     them the call fails with B2_ESTATE and the domain must be re-uploaded.
+ * b2_peer_state       global id, total crossings, species (with B2_GHOST) and mass of the
+ *                     resident particles, by local id, into device arrays (any may be NULL). */
+int b2_peer_set_ids(b2_ctx *ctx, const int64_t *gid_dev, const int32_t *image_dev /* or NULL */);
+int b2_peer_refresh(b2_ctx *ctx, double x_lo, double x_hi, double margin, int64_t counts_out[7]);
+int b2_peer_state(b2_ctx *ctx, int64_t *gid_dev, int32_t *image_dev, int32_t *species_dev, double *mass_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,7 +21,7 @@ pytestmark = pytest.mark.gpu
 
 
 def _worker(rank, world, port, steps, precision, backend, mode, out):
-    fast, peer = mode != 'torch', mode == 'peer'
+    fast, peer = mode != 'torch', mode.startswith('peer')
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
     ngpu = torch.cuda.device_count()
@@ -32,13 +32,26 @@ def _worker(rank, world, port, steps, precision, backend, mode, out):
     slab = numpy.clip(numpy.floor((pos[:, 0] / side[0] + 0.5) * world).astype(int), 0, world - 1)
     mine = numpy.nonzero(slab == rank)[0]
     dom = SlabDomain(pos[mine], vel[mine], spe[mine], side, model='kob_andersen', dt=0.002, skin=0.3,
-                     precision=precision, gid=mine, fast_comm=fast, peer=peer)
+                     precision=precision, gid=mine, fast_comm=fast, peer=peer, device_refresh=(mode == 'peer'))
     assert dom.engine.lib.name == 'cuda-sm_100a' and dom._fast == fast
     t0 = dom.thermo()
     dom.run(steps)
     t1 = dom.thermo()
     assert dom._peer == peer, 'the peer-memory halo fell back to NCCL'
+    assert dom._ids_resident == (mode == 'peer'), 'the refresh did not run on the device'
     gpos, gvel, gimg = dom.gather()
+    # host round trip (what bench.py's end-to-end leg does), then on with the device-side refresh
+    cap = int(1.2 * dom.n_own) + 64
+    hp = torch.empty((cap, 3), dtype=torch.float64, pin_memory=True)
+    hv = torch.empty((cap, 3), dtype=torch.float64, pin_memory=True)
+    m = dom.store_host(hp, hv)
+    dom.load_host(hp[:m], hv[:m])
+    t2 = dom.thermo()
+    assert abs((t2['kinetic'] + t2['potential']) - (t1['kinetic'] + t1['potential'])) < 1e-9 * abs(t1['potential'])
+    dom.run(40)
+    t3 = dom.thermo()
+    assert t3['n'] == t1['n']
+    assert abs((t3['kinetic'] + t3['potential']) - (t1['kinetic'] + t1['potential'])) < 2e-4 * abs(t1['potential'])
     if rank == 0:
         numpy.savez(out, pos=gpos, vel=gvel, img=gimg, e0=t0['kinetic'] + t0['potential'],
                     e1=t1['kinetic'] + t1['potential'], n=t1['n'], refreshes=dom.refreshes, virial=t1['virial'])
@@ -46,10 +59,10 @@ def _worker(rank, world, port, steps, precision, backend, mode, out):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('mode', ['torch', 'nccl', 'peer'])
+@pytest.mark.parametrize('mode', ['torch', 'nccl', 'peer-host', 'peer'])
 @pytest.mark.parametrize('precision', [64, 32])
 def test_two_rank_slab_run_on_cuda(precision, mode, tmp_path, cuda_lib):
-    fast = mode != 'torch' 
+    fast = mode != 'torch'
     from conftest import make_engine
     from oracle import oracle_np as onp
     steps, world = 120, 2
