@@ -2091,7 +2091,7 @@ static int ddr_alloc(b2_ctx *c)
     const int64_t n = c->ncap;
     const int64_t gc = c->peer_cap, mc = ddr_mig_cap_of(c->peer_cap);
     if ((rc = dev_alloc(c, &c->ddr_cls, n))) return rc;
-    if ((rc = dev_alloc(c, &c->ddr_blk, 5 * (size_t)cdiv(n, DDR_THREADS)))) return rc;
+    if ((rc = dev_alloc(c, &c->ddr_blk, 5 * (size_t)std::max<int64_t>(1, cdiv(n, DDR_THREADS))))) return rc;
     if ((rc = dev_alloc(c, &c->ddr_keep, n))) return rc;
     for (int k = 0; k < 2; k++) {
         if ((rc = dev_alloc(c, &c->ddr_go[k], mc))) return rc;
@@ -2139,7 +2139,7 @@ template <typename R> struct ImplDdr {
         a.box = make_box<R>(c);
         a.cls = c->ddr_cls;
         a.blk = c->ddr_blk;
-        a.nblk = cdiv(n, DDR_THREADS);
+        a.nblk = std::max(1, cdiv(n, DDR_THREADS));      // a rank may own nothing and must still take part
         a.keep = c->ddr_keep;
         a.go_l = c->ddr_go[0]; a.go_r = c->ddr_go[1];
         a.near_l_slot = c->ddr_near[0]; a.near_l_new = c->ddr_near[1];

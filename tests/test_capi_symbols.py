@@ -9,8 +9,8 @@ from atooms_b200 import capi
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _declared():
-    text = open(os.path.join(ROOT, 'include', 'atooms_b200.h')).read()
+def _declared(header='atooms_b200.h'):
+    text = open(os.path.join(ROOT, 'include', header)).read()
     text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
     return set(re.findall(r'\b(b2_\w+)\s*\(', text))
 
@@ -26,6 +26,20 @@ def test_product_library_builds_and_exports_every_symbol():
     assert lib.name == 'cuda-sm_100a'
     for name in _declared():
         assert hasattr(lib.dll, name), name
+
+
+def test_product_library_exports_the_multi_gpu_entry_points():
+    """include/atooms_b200_nccl.h: CUDA library only (NCCL and peer-memory transports, device-side
+    slab refresh); every declared symbol must be exported and bound."""
+    import __graft_entry__
+    __graft_entry__.build()
+    lib = capi.load()
+    names = _declared('atooms_b200_nccl.h')
+    assert {'b2_nccl_run', 'b2_peer_run', 'b2_peer_refresh', 'b2_peer_set_ids', 'b2_peer_state'} <= names
+    assert lib.has_nccl
+    for name in names:
+        fn = getattr(lib.dll, name)
+        assert fn.argtypes is not None, name + ' is exported but not bound in capi.Library'
 
 
 def test_oracle_library_exports_every_symbol(oracle_lib):
