@@ -583,7 +583,9 @@ int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
                     const int32_t *species, const double *mass)
 {
     int rc;
-    if (n > c->ncap || !c->pos[0]) {
+    // a domain that refreshes itself on the device (b2_peer_refresh) needs room to grow in place
+    const bool tight = c->peer_on && c->ncap < n + n / 16;
+    if (n > c->ncap || !c->pos[0] || tight) {
         // grow with headroom: a decomposed domain re-uploads a slightly different n at every refresh
         if ((rc = alloc_particles(c, c->pos[0] ? n + n / 8 + 1024 : n))) return rc;
     }

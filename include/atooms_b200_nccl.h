@@ -72,8 +72,9 @@ int b2_peer_run(b2_ctx *ctx, int64_t count);
  *                     step, sent right per step, migrants out, migrants in}.
  *                     Limits: migrants per face <= halo_capacity / 4 + 1024, ghosts per face
  *                     <= halo_capacity, and the new domain must fit the arrays allocated by
- *                     the last b2_upload (which leaves 12 % headroom on a re-upload); beyond
- *                     them the call fails with B2_ESTATE and the domain must be re-uploaded.
+ *                     the last b2_upload (on a connected context it leaves 12 % headroom);
+ *                     beyond them the call fails with B2_ESTATE and the domain must be
+ *                     re-uploaded.
  * b2_peer_state       global id, total crossings, species (with B2_GHOST) and mass of the
  *                     resident particles, by local id, into device arrays (any may be NULL). */
 int b2_peer_set_ids(b2_ctx *ctx, const int64_t *gid_dev, const int32_t *image_dev /* or NULL */);
