@@ -158,20 +158,25 @@ def oracle_library():
     return capi.Library(path)
 
 
-def time_oracle(pos, spe, side, vel, md_steps, repeats=1):
-    """particle-timesteps/s of the C/OpenMP oracle for `md_steps` NVE steps
-    (list build included, as in the GPU number)."""
+def time_oracle(pos, spe, side, vel, md_steps, target_s=None):
+    """particle-timesteps/s of the C/OpenMP oracle over NVE steps (list builds included, as in
+    the GPU number).  With `target_s` the sample grows from `md_steps` until about that many
+    seconds of CPU work are timed (at most 300 steps): hosts differ by more than 10x.
+    Returns (rate, seconds, steps)."""
     lib = oracle_library()
     eng = make_engine(lib, 64, pos, spe, side, vel)
     eng.compute(forces=False)                  # first list build + forces: not timed (as on the GPU)
-    best = None
-    for _ in range(repeats):
-        t0 = time.perf_counter()
-        eng.run_nve(md_steps, DT)
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
+    t0 = time.perf_counter()
+    eng.run_nve(md_steps, DT)
+    spent, done = time.perf_counter() - t0, md_steps
+    if target_s is not None and spent < target_s:
+        more = min(int(md_steps * (target_s - spent) / max(spent, 1e-3)), 300 - md_steps)
+        if more > 0:
+            t0 = time.perf_counter()
+            eng.run_nve(more, DT)
+            spent, done = spent + time.perf_counter() - t0, done + more
     eng.close()
-    return len(spe) * md_steps / best, best
+    return len(spe) * done / spent, spent, done
 
 
 def run_reference(args, rank, world):
@@ -450,8 +455,7 @@ def main():
         if not args.no_cpu_baseline:
             cores = os.cpu_count()
             os.environ.setdefault('OMP_NUM_THREADS', str(cores))
-            md = 10
-            cpu_value, cpu_s = time_oracle(pos, spe, side, vel, md)
+            cpu_value, cpu_s, md = time_oracle(pos, spe, side, vel, 10, target_s=15.0)
             line['cpu_baseline'] = {'value': cpu_value, 'unit': 'particle-timesteps/s', 'cores': cores, 'kind': 'port',
                                     'sample': '%d NVE timesteps of the full N=%d system (%.1f s), oracle/oracle_c.c '
                                               '(C + OpenMP, fp64, Verlet list)' % (md, n, cpu_s)}
