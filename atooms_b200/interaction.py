@@ -115,6 +115,19 @@ class Interaction(_Base):
         if observable == 'stress':
             self.stress = out['stress']
 
+    def neighbors(self, system=None):
+        """The engine's Verlet list (pairs within r_cut + skin) of the configuration last
+        computed — or of `system`, an array-backed System bound to a backend — as one sorted
+        int32 array per particle, 0-based, in the caller's numbering.  This is what the
+        reference stores in `particle.neighbors` / `system.neighbors` and writes with
+        TrajectoryNeighbors (atooms/trajectory/xyz.py:476-506)."""
+        engine = system._engine if system is not None and getattr(system, '_engine', None) is not None else self._engine
+        if engine is None:
+            raise ValueError('no configuration resident: call compute() first')
+        if system is not None and hasattr(system, '_push'):
+            system._push()
+        return engine.neighbors()
+
     # -- resident state -------------------------------------------------------------
     def compute_resident(self, observable, system):
         if observable is None:

@@ -14,7 +14,7 @@ import os
 
 import numpy
 
-__all__ = ['Trajectory']
+__all__ = ['Trajectory', 'TrajectoryNeighbors']
 
 
 class Trajectory(object):
@@ -68,3 +68,31 @@ class Trajectory(object):
         if self._fh is not None:
             self._fh.close()
             self._fh = None
+
+
+class TrajectoryNeighbors(Trajectory):
+
+    """Writer of the reference's neighbours format (atooms/trajectory/xyz.py:484-506): an xyz
+    layout whose single column holds each particle's neighbours, comma-separated, numbered from
+    `offset` (1 by default, as there).  `write` takes anything with a `neighbors` attribute (a
+    list of integer arrays, 0-based — what `Interaction.neighbors()` returns) or the list itself."""
+
+    def __init__(self, filename, mode='w', offset=1):
+        Trajectory.__init__(self, filename, mode)
+        self.variables = ['neighbors']
+        self.offset = int(offset)
+
+    def write(self, system, step):
+        if self._fh is None:
+            raise IOError('trajectory %s is not open for writing' % self.filename)
+        rows = getattr(system, 'neighbors', system)
+        line = 'step:{} columns:neighbors '.format(step)
+        if self.timestep is not None:
+            line += 'dt:{:g} '.format(self.timestep)
+        cell = getattr(system, 'cell', None)
+        if cell is not None:
+            line += 'cell:{} '.format(','.join(repr(float(x)) for x in cell.side))
+        self._fh.write('%d\n%s\n' % (len(rows), line))
+        off = self.offset
+        self._fh.write('\n'.join(','.join(map(str, (numpy.asarray(r, dtype=numpy.int64) + off).tolist())) for r in rows))
+        self._fh.write('\n')

@@ -287,6 +287,36 @@ def test_interaction_with_reference_system(oracle_lib, pins):
 
 
 @needs_ref
+def test_neighbors_export_round_trips_through_the_reference_reader(oracle_lib, tmp_path):
+    """the engine's Verlet list, written in the reference's neighbours format
+    (atooms/trajectory/xyz.py:484-506), comes back through the reference's own TrajectoryNeighbors."""
+    from atooms.trajectory import TrajectoryXYZ
+    from atooms.trajectory.xyz import TrajectoryNeighbors as RefNeighbors
+    from oracle import oracle_np as onp
+    th = TrajectoryXYZ(os.path.join(REF, 'data', 'lj_N256_rho1.0.xyz'))
+    system = th[0]
+    th.close()
+    inter = Interaction(atooms_b200.lennard_jones(2.5, True), skin=0.3, library=oracle_lib)
+    system.interaction = inter
+    system.potential_energy()
+    rows = inter.neighbors()
+    pos = numpy.array([p.position for p in system.particle])
+    brute = onp.neighbor_list(pos, numpy.zeros(len(pos), dtype=numpy.int32), numpy.array(system.cell.side),
+                              onp.lennard_jones(2.5, True), 0.3)
+    assert len(rows) == 256 and all(numpy.array_equal(a, b) for a, b in zip(rows, brute))
+    path = str(tmp_path / 'neighbors.xyz')
+    with atooms_b200.TrajectoryNeighbors(path, 'w') as out:
+        out.timestep = 0.002
+        system.neighbors = rows
+        out.write(system, 7)
+    with RefNeighbors(path) as back:                  # offset 1 on both sides
+        assert back.steps == [7] and back.timestep == 0.002
+        got = back[0]
+    for a, p in zip(rows, got.particle):
+        assert list(a) == [int(j) for j in p.neighbors]
+
+
+@needs_ref
 def test_command_line_driver(oracle_lib, tmp_path, monkeypatch):
     """bin/md_b200.py, the bin/md.py look-alike (bin/md.py:12-81).  The engine is swapped for
     the oracle by patching the loader IN THIS TEST ONLY; the script itself has no such switch."""
