@@ -20,7 +20,7 @@ from test_dd_gloo import global_system, ROOT
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, port, steps, precision, backend, mode, out):
+def _worker(rank, world, port, steps, precision, backend, mode, out, reps_x=2):
     fast, peer = mode != 'torch', mode.startswith('peer')
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
@@ -28,7 +28,7 @@ def _worker(rank, world, port, steps, precision, backend, mode, out):
     torch.cuda.set_device(rank % ngpu)
     dist.init_process_group(backend, rank=rank, world_size=world)
     from atooms_b200.dd import SlabDomain
-    pos, vel, spe, side = global_system()
+    pos, vel, spe, side = global_system(reps_x)
     slab = numpy.clip(numpy.floor((pos[:, 0] / side[0] + 0.5) * world).astype(int), 0, world - 1)
     mine = numpy.nonzero(slab == rank)[0]
     dom = SlabDomain(pos[mine], vel[mine], spe[mine], side, model='kob_andersen', dt=0.002, skin=0.3,
@@ -59,21 +59,33 @@ def _worker(rank, world, port, steps, precision, backend, mode, out):
     dist.destroy_process_group()
 
 
+def test_four_rank_ring_on_cuda(tmp_path, cuda_lib):
+    """Four slabs: left and right neighbours are different ranks and particles leave through
+    both faces (peer-memory halo, refresh on the device).  Needs four GPUs."""
+    if torch.cuda.device_count() < 4:
+        pytest.skip('needs four GPUs')
+    _compare(64, 'peer', tmp_path, cuda_lib, world=4, reps_x=3)
+
+
 @pytest.mark.parametrize('mode', ['torch', 'nccl', 'peer-host', 'peer'])
 @pytest.mark.parametrize('precision', [64, 32])
 def test_two_rank_slab_run_on_cuda(precision, mode, tmp_path, cuda_lib):
+    _compare(precision, mode, tmp_path, cuda_lib)
+
+
+def _compare(precision, mode, tmp_path, cuda_lib, world=2, reps_x=2):
     fast = mode != 'torch'
     from conftest import make_engine
     from oracle import oracle_np as onp
-    steps, world = 120, 2
+    steps = 120
     backend = 'nccl' if torch.cuda.device_count() >= 2 else 'gloo'
     if fast and backend != 'nccl':
         pytest.skip('the C-side communication paths need two GPUs')
     out = str(tmp_path / 'dd.npz')
     port = 29500 + (os.getpid() + precision + 7 * len(mode)) % 2000
-    mp.spawn(_worker, args=(world, port, steps, precision, backend, mode, out), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, steps, precision, backend, mode, out, reps_x), nprocs=world, join=True)
     got = numpy.load(out)
-    pos, vel, spe, side = global_system()
+    pos, vel, spe, side = global_system(reps_x)
     ref = make_engine(cuda_lib, {'position': pos, 'velocity': vel, 'species': spe, 'side': side,
                                  'center': numpy.zeros(3)}, onp.kob_andersen(), precision)
     e0 = ref.thermo()
