@@ -353,9 +353,11 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
 // per-particle walk above keeps 14 of 32 lanes busy).  The float distance decides
 // every pair outside a thin band around the threshold; the band is settled with the
 // canonical predicate on the stored coordinates, exactly as in k_build_list.
+#ifndef SC_WARPS
 #define SC_WARPS 4
+#endif
 #ifndef SC_MINBLK
-#define SC_MINBLK 7
+#define SC_MINBLK 5             // up to 102 registers: no spills (7 blocks of 72 registers timed the same)
 #endif
 #define SC_CHUNK 256
 #define SC_CELLS 216
