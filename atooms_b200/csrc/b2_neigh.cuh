@@ -357,7 +357,7 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
 #define SC_WARPS 4
 #endif
 #ifndef SC_MINBLK
-#define SC_MINBLK 5             // up to 102 registers: no spills (7 blocks of 72 registers timed the same)
+#define SC_MINBLK 5             // up to 102 registers per thread (7 blocks of 72 registers, with spills, timed the same)
 #endif
 #define SC_CHUNK 256
 #define SC_CELLS 216
