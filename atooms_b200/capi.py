@@ -128,9 +128,10 @@ class Library(object):
             self.dll.b2_peer_set_ids.argtypes = [_vp, _vp, _vp]
             self.dll.b2_peer_refresh.argtypes = [_vp, _dbl, _dbl, _dbl, ctypes.POINTER(ctypes.c_int64)]
             self.dll.b2_peer_state.argtypes = [_vp, _vp, _vp, _vp, _vp]
+            self.dll.b2_peer_update.argtypes = [_vp, _i64, _vp, _vp]
             for name in ('b2_nccl_unique_id', 'b2_nccl_init', 'b2_nccl_set_halo', 'b2_nccl_run',
                          'b2_peer_export', 'b2_peer_connect', 'b2_peer_run', 'b2_peer_set_ids',
-                         'b2_peer_refresh', 'b2_peer_state'):
+                         'b2_peer_refresh', 'b2_peer_state', 'b2_peer_update'):
                 getattr(self.dll, name).restype = _int
         version = self.dll.b2_abi_version()
         if version != ABI_VERSION:
@@ -439,6 +440,9 @@ class Engine(object):
         self._call('b2_peer_refresh', float(x_lo), float(x_hi), float(margin), out)
         self.n = int(out[0] + out[1] + out[2])
         return tuple(int(v) for v in out)
+
+    def peer_update(self, n_first, pos_ptr, vel_ptr):
+        self._call('b2_peer_update', int(n_first), pos_ptr, vel_ptr)
 
     def peer_state(self, gid_ptr=None, image_ptr=None, species_ptr=None, mass_ptr=None):
         self._call('b2_peer_state', gid_ptr, image_ptr, species_ptr, mass_ptr)

@@ -2086,6 +2086,31 @@ __global__ void k_ddr_state(const Ctl *__restrict__ ctl, const typename Pos4<R>:
         for (int d = 0; d < 3; d++) img_out[3 * o + d] = cimg[3 * o + d] + img[3 * o + d];
 }
 
+// k_update restricted to the local ids below n_first (the owned particles of a slab)
+template <typename R>
+__global__ void k_update_first(const Ctl *__restrict__ ctl, const double *__restrict__ spos,
+                               const double *__restrict__ svel, int n, int n_first, double cx, double cy, double cz,
+                               Box<R> box, typename Pos4<R>::type *pos0, typename Pos4<R>::type *pos1,
+                               typename Vec4<R>::type *__restrict__ vel, const int *__restrict__ orig,
+                               int *__restrict__ img)
+{
+    typedef typename Vec4<R>::type V4;
+    typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n || orig[s] >= n_first) return;
+    const size_t o = 3 * (size_t)orig[s];
+    if (spos) {
+        const double px = spos[o] - cx, py = spos[o + 1] - cy, pz = spos[o + 2] - cz;
+        const double kx = rint(px / box.Ld[0]), ky = rint(py / box.Ld[1]), kz = rint(pz / box.Ld[2]);
+        img[o] += (int)kx; img[o + 1] += (int)ky; img[o + 2] += (int)kz;
+        pos[s] = encode_pos(px - kx * box.Ld[0], py - ky * box.Ld[1], pz - kz * box.Ld[2], praw(pos[s]), box);
+    }
+    if (svel) {
+        const V4 v = vel[s];
+        vel[s] = make4((R)svel[o], (R)svel[o + 1], (R)svel[o + 2], v.w);
+    }
+}
+
 static int ddr_alloc(b2_ctx *c)
 {
     int rc;
@@ -2217,6 +2242,25 @@ template <typename R> struct ImplDdr {
         return B2_OK;
     }
 
+    static int update_first(b2_ctx *c, int64_t n_first, const double *pos, const double *vel)
+    {
+        const int n = (int)c->n;
+        double *spos = c->stage, *svel = c->stage + 3 * (size_t)n;
+        // cudaMemcpyDefault: pinned host memory or device memory
+        if (pos) CU(cudaMemcpyAsync(spos, pos, 3 * n_first * sizeof(double), cudaMemcpyDefault, c->stream));
+        if (vel) CU(cudaMemcpyAsync(svel, vel, 3 * n_first * sizeof(double), cudaMemcpyDefault, c->stream));
+        LAUNCH(k_update_first<R>, cdiv(n, 256), 256, c->ctl, pos ? spos : nullptr, vel ? svel : nullptr, n,
+               (int)n_first, c->center[0], c->center[1], c->center[2], make_box<R>(c), (P4 *)c->pos[0],
+               (P4 *)c->pos[1], (V4 *)c->vel, c->orig, c->img);
+        CU(cudaStreamSynchronize(c->stream));
+        c->min_resume = false;
+        if (pos) {
+            c->list_dirty = true;
+            c->forces_valid = c->ev_valid = false;
+        }
+        return B2_OK;
+    }
+
     static int state(b2_ctx *c, int32_t *img, int32_t *spe, double *mass)
     {
         const int n = (int)c->n;
@@ -2254,6 +2298,15 @@ int b2_peer_state(b2_ctx *c, int64_t *gid_dev, int32_t *image_dev, int32_t *spec
     if (gid_dev) CU(cudaMemcpyAsync(gid_dev, c->ddr_gid[0], c->n * sizeof(int64_t), cudaMemcpyDefault, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     return B2_OK;
+}
+
+int b2_peer_update(b2_ctx *c, int64_t n_first, const double *pos, const double *vel)
+{
+    NEED_PARTICLES("b2_peer_update");
+    if (n_first < 0 || n_first > c->n) return fail(c, B2_EINVAL, "b2_peer_update: n_first out of range");
+    if (n_first == 0 || (!pos && !vel)) return B2_OK;
+    return c->precision == B2_FP32 ? ImplDdr<float>::update_first(c, n_first, pos, vel)
+                                   : ImplDdr<double>::update_first(c, n_first, pos, vel);
 }
 
 int b2_peer_refresh(b2_ctx *c, double x_lo, double x_hi, double margin, int64_t counts_out[7])

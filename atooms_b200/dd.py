@@ -101,6 +101,7 @@ class SlabDomain(object):
         self._ids_resident = False
         self._n_own_res = 0
         self._uploads = 0
+        self._stale = False              # owned particles were overwritten: ghosts and list are out of date
         self.profile = None
         self._resident = False
         self._batch = 8
@@ -163,6 +164,7 @@ class SlabDomain(object):
         lo, hi = self.rank / self.world, (self.rank + 1) / self.world
         margin = self.rlist / self.side[0] * (1 + 1e-6) + 1e-12
         c = self.engine.peer_refresh(lo, hi, margin)
+        self._stale = False
         self._n_own_res, self._n_gl, self._n_gr = c[0], c[1], c[2]
         self.halo_bytes_per_step = 24 * (c[3] + c[4])
         self.pos = self.vel = self.mass = self.spe = self.gid = self.img = None     # stale: see _pull_state
@@ -319,6 +321,7 @@ class SlabDomain(object):
             self._ids_resident, self._n_own_res = True, n
         self._tick('halo setup')
         self._resident = True
+        self._stale = False
         self.refreshes += 1
 
     def _halo(self):
@@ -349,7 +352,7 @@ class SlabDomain(object):
         steps = int(steps)
         if steps <= 0:
             return
-        if not self._resident:
+        if not self._resident or self._stale:
             self.refresh()
         eng = self.engine
         eng.dd_begin(steps, self.dt, True)
@@ -395,7 +398,7 @@ class SlabDomain(object):
     # -- observables -----------------------------------------------------------------------
     def thermo(self):
         """Totals over the whole system (owned particles of every rank, all_reduce SUM)."""
-        if not self._resident:
+        if not self._resident or self._stale:
             self.refresh()
         t = self.engine.thermo()
         vec = torch.tensor([t['kinetic'], t['potential'], t['virial'], t['fnorm2'], *t['momentum'], t['mass'],
@@ -435,6 +438,16 @@ class SlabDomain(object):
     def load_host(self, position, velocity):
         """Replace the owned particles' coordinates and velocities from host arrays
         (pinned memory makes the copies asynchronous); same particles, same order."""
+        if self._ids_resident and self._resident:
+            # the engine owns the particles: overwrite the owned ones in place (pinned host or device
+            # memory, read by the engine directly); the next refresh re-sends the ghost layer
+            p, v = torch.as_tensor(position), torch.as_tensor(velocity)
+            ok = all(t.dtype == torch.float64 and t.is_contiguous() and tuple(t.shape) == (self._n_own_res, 3)
+                     and (t.is_cuda or t.is_pinned()) for t in (p, v))
+            if ok:
+                self.engine.peer_update(self._n_own_res, p.data_ptr(), v.data_ptr())
+                self._stale = True
+                return
         if self._ids_resident:
             self._pull_state()              # ids, species, masses in the engine's current order
             self._ids_resident = False

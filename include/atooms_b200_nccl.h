@@ -75,10 +75,15 @@ int b2_peer_run(b2_ctx *ctx, int64_t count);
  *                     the last b2_upload (on a connected context it leaves 12 % headroom);
  *                     beyond them the call fails with B2_ESTATE and the domain must be
  *                     re-uploaded.
+ * b2_peer_update      b2_update for the first n_first local ids only (the owned particles of a slab;
+ *                     the ghosts keep their coordinates until the next b2_peer_refresh, which the
+ *                     caller must run before stepping on).  pos / vel: n_first x 3 doubles in
+ *                     pinned host or device memory; either may be NULL.
  * b2_peer_state       global id, total crossings, species (with B2_GHOST) and mass of the
  *                     resident particles, by local id, into device arrays (any may be NULL). */
 int b2_peer_set_ids(b2_ctx *ctx, const int64_t *gid_dev, const int32_t *image_dev /* or NULL */);
 int b2_peer_refresh(b2_ctx *ctx, double x_lo, double x_hi, double margin, int64_t counts_out[7]);
+int b2_peer_update(b2_ctx *ctx, int64_t n_first, const double *pos, const double *vel);
 int b2_peer_state(b2_ctx *ctx, int64_t *gid_dev, int32_t *image_dev, int32_t *species_dev, double *mass_dev);
 
 #ifdef __cplusplus
