@@ -53,6 +53,16 @@ def _worker(rank, world, port, steps, out, reps_x=2):
     dom.run(steps)
     t1 = dom.thermo()
     gpos, gvel, gimg = dom.gather()
+    # host round trip (bench.py's end-to-end leg): same particles back in, same state, and on it goes
+    hp, hv = torch.empty((dom.n_own + 8, 3), dtype=torch.float64), torch.empty((dom.n_own + 8, 3), dtype=torch.float64)
+    m = dom.store_host(hp, hv)
+    dom.load_host(hp[:m], hv[:m])
+    t2 = dom.thermo()
+    assert abs((t2['kinetic'] + t2['potential']) - (t1['kinetic'] + t1['potential'])) < 1e-9 * abs(t1['potential'])
+    dom.run(20)
+    t3 = dom.thermo()
+    assert t3['n'] == t1['n']
+    assert abs((t3['kinetic'] + t3['potential']) - (t1['kinetic'] + t1['potential'])) < 1e-4 * abs(t1['potential'])
     if rank == 0:
         numpy.savez(out, pos=gpos, vel=gvel, img=gimg, e0=t0['kinetic'] + t0['potential'],
                     e1=t1['kinetic'] + t1['potential'], n=t1['n'], refreshes=dom.refreshes,
