@@ -405,7 +405,7 @@ __device__ __forceinline__ void sc_append(bool hit, int *row, int &cnt, int cap,
 struct ScShared {
     int prefix[SC_CELLS + 8];
     int first[SC_CELLS + 8];
-    float4 cand[SC_CHUNK];
+    float4 cand[SC_CHUNK + 4];       // + 4: the test loop reads one round ahead
 };
 
 // one block of cells (Morton code ms), one warp
@@ -554,24 +554,30 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
             const int e0 = (n0 + 3) & ~3;
             if (FAST2) {
                 float far0 = 0.f, far1 = 0.f;         // largest listed r^2 of either stretch
-#define SC_TEST(R_, HI, FAR)                                                       \
+#define SC_TEST(Q, HI, FAR)                                                        \
                 {                                                                  \
-                    const float4 q = cand[R_];                                     \
-                    const float dx = q.x - px, dy = q.y - py, dz = q.z - pz;       \
+                    const float dx = Q.x - px, dy = Q.y - py, dz = Q.z - pz;       \
                     const float r2 = dx * dx + dy * dy + dz * dz;                  \
-                    const int j = __float_as_int(q.w);                             \
+                    const int j = __float_as_int(Q.w);                             \
                     const bool hit = r2 < HI && j != slot;                         \
                     sc_append(hit, row, cnt, cap, j);                              \
                     FAR = fmaxf(FAR, hit ? r2 : 0.f);                              \
                 }
-#pragma unroll 1
-                for (int r = 0; r < e0; r += 4) {
-                    SC_TEST(r, hi0, far0) SC_TEST(r + 1, hi0, far0) SC_TEST(r + 2, hi0, far0) SC_TEST(r + 3, hi0, far0)
+                // four candidates per round, the next four already on their way from shared memory
+                // (the reads run up to 4 records past a stretch: the chunk is padded for that)
+#define SC_STRETCH(FIRST, LAST, HI, FAR)                                           \
+                if ((FIRST) < (LAST)) {                                            \
+                    float4 q0 = cand[FIRST], q1 = cand[(FIRST) + 1], q2 = cand[(FIRST) + 2], q3 = cand[(FIRST) + 3]; \
+                    _Pragma("unroll 1")                                            \
+                    for (int r = (FIRST); r < (LAST); r += 4) {                    \
+                        const float4 n0_ = cand[r + 4], n1_ = cand[r + 5], n2_ = cand[r + 6], n3_ = cand[r + 7]; \
+                        SC_TEST(q0, HI, FAR) SC_TEST(q1, HI, FAR) SC_TEST(q2, HI, FAR) SC_TEST(q3, HI, FAR) \
+                        q0 = n0_; q1 = n1_; q2 = n2_; q3 = n3_;                    \
+                    }                                                              \
                 }
-#pragma unroll 1
-                for (int r = SC_CHUNK - ((n1 + 3) & ~3); r < SC_CHUNK; r += 4) {
-                    SC_TEST(r, hi1, far1) SC_TEST(r + 1, hi1, far1) SC_TEST(r + 2, hi1, far1) SC_TEST(r + 3, hi1, far1)
-                }
+                SC_STRETCH(0, e0, hi0, far0)
+                SC_STRETCH(SC_CHUNK - ((n1 + 3) & ~3), SC_CHUNK, hi1, far1)
+#undef SC_STRETCH
 #undef SC_TEST
                 near = fmaxf(near, fmaxf(far0 - lo0, far1 - lo1));
             } else {
