@@ -3,8 +3,12 @@
 #pragma once
 #include "b2_common.cuh"
 
+// Block of the step / force kernels.  The blocks resident on an SM share its L1, where the
+// neighbours' coordinates live; fewer, larger blocks cover a more compact piece of the (Morton-
+// sorted) system and so need less of it: 0.241 / 0.224 / 0.216 / 0.213 ms per step (fp32, N = 1.2M)
+// with 128 / 256 / 512 / 1024 threads at the same 48 warps per SM (1024: 32 warps).
 #ifndef FORCE_THREADS
-#define FORCE_THREADS 256
+#define FORCE_THREADS 512
 #endif
 #ifndef B2_UNROLL
 #define B2_UNROLL 4
@@ -12,13 +16,13 @@
 #ifndef B2_PIPE
 #define B2_PIPE 1
 #endif
-// resident blocks per SM asked of ptxas for the step kernel: fp32 fits 6 x 256 threads in 40
-// registers without spilling (measured 0.243 -> 0.224 ms at N = 1.2M); fp64 runs best at 4 x 256 in 64 (0.568 -> 0.486 ms)
+// resident blocks per SM asked of ptxas for the step kernel: fp32 fits 3 x 512 threads in 40
+// registers without spilling (48 warps against 32: 0.243 -> 0.224 ms); fp64 runs best at 2 x 512 in 64
 #ifndef B2_MINBLK32
-#define B2_MINBLK32 6
+#define B2_MINBLK32 3
 #endif
 #ifndef B2_MINBLK64
-#define B2_MINBLK64 4
+#define B2_MINBLK64 2
 #endif
 #define RED_THREADS 256
 
