@@ -71,6 +71,13 @@ class Interaction(_Base):
     def __str__(self):
         return 'b200 %s' % self.model
 
+    # what the reference's HDF5 trajectory stores about an interaction (trajectory/hdf5.py:208-237)
+    name = 'atomic'
+
+    @property
+    def potential(self):
+        return self.model.potentials()
+
     def _invalidate(self):
         self.energy = self.virial = self.forces = self.stress = None
 

@@ -9,7 +9,7 @@ table of 12-6 Lennard-Jones parameters per species pair.
 """
 import numpy
 
-__all__ = ['PairModel', 'lennard_jones', 'kob_andersen', 'get']
+__all__ = ['PairModel', 'lennard_jones', 'kob_andersen', 'wca', 'from_potentials', 'get']
 
 
 class PairModel(object):
@@ -36,9 +36,75 @@ class PairModel(object):
         self.species = None if species is None else [str(s) for s in species]
         self.name = name
 
+    def potentials(self):
+        """The table in the reference's own description of a pair interaction: one record per
+        species pair with `func`, `params`, `species` (1-based), `cutoff.scheme` ('cs' cut and
+        shifted, 'c' cut) and `cutoff.radius` — the fields of `_PairPotential` / `_CutOff` that the
+        reference's HDF5 trajectories store (atooms/trajectory/hdf5.py:21-43, 208-237)."""
+        out = []
+        for a in range(self.nsp):
+            for b in range(a, self.nsp):
+                out.append(_Potential('lennard_jones', {'epsilon': float(self.eps[a, b]), 'sigma': float(self.sigma[a, b])},
+                                      [a + 1, b + 1], _CutOff('cs' if self.shifted else 'c', float(self.rcut[a, b]))))
+        return out
+
     def __str__(self):
         return '%s(nsp=%d, rcut_max=%g, %s)' % (self.name, self.nsp, self.rcut.max(),
                                                 'cut&shifted' if self.shifted else 'cut')
+
+
+class _CutOff(object):
+    def __init__(self, scheme, radius):
+        self.scheme, self.radius = scheme, radius
+
+
+class _Potential(object):
+    interacting_bodies = 2
+
+    def __init__(self, func, params, species, cutoff, npoints=20000):
+        self.func, self.params, self.species, self.cutoff, self.npoints = func, params, species, cutoff, npoints
+
+    def __str__(self):
+        return self.func
+
+
+def from_potentials(potentials, species=None):
+    """Build the table from records in the reference's schema (see PairModel.potentials): objects
+    or dicts with func / params / species / cutoff.  Only 12-6 Lennard-Jones with one cut-off
+    scheme for all pairs is representable; anything else raises ValueError."""
+    get_ = lambda o, k: o[k] if isinstance(o, dict) else getattr(o, k)
+    pairs, schemes = {}, set()
+    for phi in potentials:
+        func = str(get_(phi, 'func'))
+        if func not in ('lennard_jones', 'lj'):
+            raise ValueError('only lennard_jones pair potentials are supported, not %r' % func)
+        a, b = (int(x) - 1 for x in get_(phi, 'species'))
+        cut = get_(phi, 'cutoff')
+        scheme = str(get_(cut, 'scheme')).lower()
+        if scheme not in ('c', 'cs'):
+            raise ValueError('cut-off scheme %r is not supported (c: cut, cs: cut and shifted)' % scheme)
+        schemes.add(scheme)
+        par = get_(phi, 'params')
+        pairs[(min(a, b), max(a, b))] = (float(par['epsilon']), float(par['sigma']), float(get_(cut, 'radius')))
+    if len(schemes) != 1:
+        raise ValueError('one cut-off scheme for all pairs is required')
+    nsp = 1 + max(b for _, b in pairs)
+    eps, sig, rc = numpy.zeros((nsp, nsp)), numpy.ones((nsp, nsp)), numpy.zeros((nsp, nsp))
+    for a in range(nsp):
+        for b in range(a, nsp):
+            if (a, b) not in pairs:
+                raise ValueError('no potential for the species pair (%d, %d)' % (a + 1, b + 1))
+            e, s_, r = pairs[(a, b)]
+            eps[a, b] = eps[b, a] = e
+            sig[a, b] = sig[b, a] = s_
+            rc[a, b] = rc[b, a] = r
+    return PairModel(eps, sig, rc, schemes.pop() == 'cs', species=species, name='lennard_jones')
+
+
+def wca(epsilon=1.0, sigma=1.0):
+    """Weeks-Chandler-Andersen: the repulsive part of LJ, cut at its minimum 2^(1/6) sigma and
+    shifted up by epsilon."""
+    return PairModel([[epsilon]], [[sigma]], [[2.0 ** (1.0 / 6.0) * sigma]], True, name='wca')
 
 
 def lennard_jones(rcut=2.5, shifted=True, epsilon=1.0, sigma=1.0):
@@ -64,7 +130,7 @@ def kob_andersen(shifted=True, rcut=2.5, nsp=2):
 
 
 _REGISTRY = {'lennard_jones': lennard_jones, 'lj': lennard_jones,
-             'kob_andersen': kob_andersen, 'ka': kob_andersen}
+             'kob_andersen': kob_andersen, 'ka': kob_andersen, 'wca': wca}
 
 
 def get(model):

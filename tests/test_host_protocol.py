@@ -66,6 +66,36 @@ def test_nve_pin_through_the_backend(oracle_lib, pins):
     assert bck.rmsd > 0.0
 
 
+def test_model_registry_and_reference_schema(oracle_lib):
+    """named models, and the reference's own description of a pair interaction
+    (func / params / species / cutoff.scheme / cutoff.radius, trajectory/hdf5.py:21-43) in and out."""
+    from atooms_b200 import models
+    ka = models.get('kob_andersen')
+    phis = ka.potentials()
+    assert [p.species for p in phis] == [[1, 1], [1, 2], [2, 2]]
+    assert phis[1].func == 'lennard_jones' and phis[1].params == {'epsilon': 1.5, 'sigma': 0.8}
+    assert phis[1].cutoff.scheme == 'cs' and abs(phis[1].cutoff.radius - 2.0) < 1e-12
+    back = models.from_potentials(phis)
+    assert numpy.array_equal(back.eps, ka.eps) and numpy.array_equal(back.rcut, ka.rcut) and back.shifted
+    as_dicts = [{'func': 'lennard_jones', 'params': {'epsilon': 1.0, 'sigma': 1.0}, 'species': [1, 1],
+                 'cutoff': {'scheme': 'c', 'radius': 2.5}}]
+    lj = models.from_potentials(as_dicts)
+    assert lj.nsp == 1 and not lj.shifted and lj.rcut[0, 0] == 2.5
+    with pytest.raises(ValueError):
+        models.from_potentials([dict(as_dicts[0], func='gaussian')])
+    with pytest.raises(ValueError):
+        models.get('no_such_model')
+    inter = Interaction('kob_andersen', library=oracle_lib)
+    assert inter.name == 'atomic' and len(inter.potential) == 3
+    # WCA: the repulsive LJ core, u(sigma) = epsilon, nothing beyond 2^(1/6) sigma
+    def pair_energy(r):
+        s = System(numpy.array([[0.0, 0.0, 0.0], [r, 0.0, 0.0]]), ['A', 'A'], Cell([10.0] * 3, [0.0] * 3),
+                   model='wca', library=oracle_lib)
+        return B200(s, 'wca', library=oracle_lib).system.potential_energy()
+    assert abs(pair_energy(1.0) - 1.0) < 1e-12
+    assert pair_energy(1.13) == 0.0
+
+
 def test_observers_accessors(oracle_lib, pins):
     """What write_thermo reads (simulation/observers.py:247-256) + the energy pins."""
     model = atooms_b200.lennard_jones(2.5, shifted=False)
