@@ -10,16 +10,23 @@
 #ifndef FORCE_THREADS
 #define FORCE_THREADS 512
 #endif
-#ifndef B2_UNROLL
-#define B2_UNROLL 4
+// neighbours in flight per lane (index -> position -> pair arithmetic, software-pipelined); fp32
+// at 2 resident blocks of 512 threads has the registers for 6 (0.216 -> 0.205 ms per step against
+// 4 at 3 blocks: fewer warps, but more loads in flight each and a smaller working set in L1)
+#ifndef B2_UNROLL32
+#define B2_UNROLL32 6
+#endif
+#ifndef B2_UNROLL64
+#define B2_UNROLL64 4
 #endif
 #ifndef B2_PIPE
 #define B2_PIPE 1
 #endif
 // resident blocks per SM asked of ptxas for the step kernel: fp32 fits 3 x 512 threads in 40
-// registers without spilling (48 warps against 32: 0.243 -> 0.224 ms); fp64 runs best at 2 x 512 in 64
+// registers; 2 x 512 with 64 registers and a deeper pipeline (B2_UNROLL32) is faster still; fp64 runs
+// best at 2 x 512 in 64
 #ifndef B2_MINBLK32
-#define B2_MINBLK32 3
+#define B2_MINBLK32 2
 #endif
 #ifndef B2_MINBLK64
 #define B2_MINBLK64 2
@@ -103,6 +110,7 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
             }                                                                         \
         }                                                                             \
     }
+    constexpr int B2_UNROLL = sizeof(R) == 4 ? B2_UNROLL32 : B2_UNROLL64;
 #if B2_PIPE
     // software pipeline: the index loads of group g+1 are in flight while the positions of
     // group g arrive and its pairs are evaluated (index -> position is a dependent chain)
