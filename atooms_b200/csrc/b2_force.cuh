@@ -110,7 +110,8 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
             }                                                                         \
         }                                                                             \
     }
-    constexpr int B2_UNROLL = sizeof(R) == 4 ? B2_UNROLL32 : B2_UNROLL64;
+    // the deeper pipeline only where the registers are there for it: the step kernel (no energies)
+    constexpr int B2_UNROLL = (sizeof(R) == 4 && !EV) ? B2_UNROLL32 : B2_UNROLL64;
 #if B2_PIPE
     // software pipeline: the index loads of group g+1 are in flight while the positions of
     // group g arrive and its pairs are evaluated (index -> position is a dependent chain)
