@@ -16,7 +16,7 @@ import numpy
 
 from . import __version__, capi, models
 from .interaction import Interaction
-from .system import Cell, System
+from .system import System
 from .trajectory import Trajectory
 
 __all__ = ['B200', 'EnergyMinimization']

@@ -16,7 +16,6 @@ numpy >= 2 removed numpy.set_string_function, which the reference's
 TrajectoryXYZ.close() still calls (atooms/trajectory/xyz.py:472-474).  We
 install a no-op shim in THIS process only; the reference is not touched.
 """
-import io
 import json
 import os
 import sys

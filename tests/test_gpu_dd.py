@@ -7,7 +7,6 @@ CUDA ones either way.  The decomposed run must match one engine holding the
 whole system.
 """
 import os
-import sys
 
 import numpy
 import pytest
@@ -15,7 +14,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from test_dd_gloo import global_system, ROOT
+from test_dd_gloo import global_system
 
 pytestmark = pytest.mark.gpu
 

@@ -3,7 +3,7 @@ r_c = 2.5, NVE dt = 0.005, skin 0.3, jitter +-0.05 a (seed 5), T = 1.0 (seed 6);
 decomposition along x over the ranks of torchrun (strong scaling: the total is fixed).
     torchrun --nproc-per-node N tools/bench_c5.py [--steps 300] [--precision 32]
 With one rank it runs the plain single-GPU engine on all 8M particles."""
-import argparse, json, os, sys, time
+import argparse, json, os, sys
 import numpy, torch, torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
