@@ -333,6 +333,18 @@ class Engine(object):
         self._call('b2_neighbors', _ip(count), _ip(nbr), stride, ctypes.byref(mx))
         return [nbr[i, :count[i]].copy() for i in range(self.n)]
 
+    def neighbors_matrix(self):
+        """The same list as (count[n], nbr[n, max_count]) arrays, rows sorted and padded with -1:
+        no per-particle Python objects, for systems of millions of particles."""
+        count = numpy.zeros(self.n, dtype=numpy.int32)
+        mx = ctypes.c_int32()
+        self._call('b2_neighbors', _ip(count), None, 0, ctypes.byref(mx))
+        stride = max(int(mx.value), 1)
+        nbr = numpy.empty((self.n, stride), dtype=numpy.int32)
+        self._call('b2_neighbors', _ip(count), _ip(nbr), stride, ctypes.byref(mx))
+        nbr[numpy.arange(stride)[None, :] >= count[:, None]] = -1
+        return count, nbr
+
     # -- dynamics ---------------------------------------------------------
     def run_nve(self, steps, dt):
         self._call('b2_run_nve', int(steps), float(dt))

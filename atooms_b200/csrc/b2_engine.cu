@@ -1477,6 +1477,11 @@ extern "C" int b2_kinetic_static(const void *vel_mass_dev, int64_t n, int precis
                     (long long)n, (long long)B2_STATIC_MAX_PARTICLES);
     if (!out_dev || (n > 0 && !vel_mass_dev))
         return fail(nullptr, B2_EINVAL, "b2_kinetic_static: NULL device pointer");
+    // the records are read as float4 / double4: a pointer that is not 16-byte aligned (a tensor view at
+    // an odd offset) would fault inside the kernel, and such a fault poisons the CALLER's CUDA context
+    if (((uintptr_t)vel_mass_dev & 15u) != 0 || ((uintptr_t)out_dev & 7u) != 0)
+        return fail(nullptr, B2_EINVAL, "b2_kinetic_static: vel_mass_dev must be 16-byte aligned and out_dev "
+                                        "8-byte aligned");
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess || dev < 0 || dev >= 64)

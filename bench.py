@@ -12,8 +12,11 @@ Workload at N = 1 (BASELINE.json configs[2]): Kob-Andersen
 80:20, N = 1 200 000 — frame 0 of the reference's data/trajectory.xyz
 (tests/golden/ka_N1200.npz) rescaled to rho = 1.2, tiled 10^3, jitter +-0.01
 (seed 2), Maxwell-Boltzmann velocities T = 0.8 (seed 3); cut & shifted at
-2.5 sigma_ab, dt = 0.002, skin 0.3.  N > 1 ranks: one such system per GPU
-(independent, no collective: "weak").
+2.5 sigma_ab, dt = 0.002, skin 0.3.  N > 1 ranks: ONE periodic box of N x 1.2M
+particles, slab-decomposed along x, one slab per GPU, with a halo exchange every
+step and particle migration at every list refresh ("weak": fixed work per GPU).
+After the timed region the N-rank run is checked against a single-domain run of
+the same engine (`parity` block of the JSON line); out of tolerance => rc != 0.
 
 value : device-resident throughput (CUDA events on the launching stream).
 e2e   : the same chunk through the C ABI with HOST buffers: positions and
@@ -149,21 +152,37 @@ def ncu_traffic(precision, n):
         return None
 
 
-def oracle_library():
-    """The CPU oracle: used by the cpu_baseline leg and by --impl reference only."""
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count()
+
+
+def oracle_library(threads=None):
+    """The CPU oracle: used by the cpu_baseline leg and by --impl reference only.
+    `threads` sets the OpenMP team through the oracle's own entry point: OMP_NUM_THREADS is read
+    once per process and torch.distributed.run pre-sets it to 1.  Returns (library, threads in use)."""
+    import ctypes
     from atooms_b200 import capi
     path = os.path.join(ROOT, 'oracle', '_build', 'liboracle_b2.so')
     if not os.path.exists(path):
         subprocess.check_call(['make', '-s', '-C', os.path.join(ROOT, 'oracle')])
-    return capi.Library(path)
+    lib = capi.Library(path)
+    lib.dll.b2_oracle_set_threads.argtypes = [ctypes.c_int]
+    lib.dll.b2_oracle_set_threads.restype = ctypes.c_int
+    lib.dll.b2_oracle_threads.restype = ctypes.c_int
+    if threads:
+        lib.dll.b2_oracle_set_threads(int(threads))
+    return lib, int(lib.dll.b2_oracle_threads())
 
 
 def time_oracle(pos, spe, side, vel, md_steps, target_s=None):
     """particle-timesteps/s of the C/OpenMP oracle over NVE steps (list builds included, as in
     the GPU number).  With `target_s` the sample grows from `md_steps` until about that many
     seconds of CPU work are timed (at most 300 steps): hosts differ by more than 10x.
-    Returns (rate, seconds, steps)."""
-    lib = oracle_library()
+    Returns (rate, seconds, steps, threads)."""
+    lib, threads = oracle_library(host_cores())
     eng = make_engine(lib, 64, pos, spe, side, vel)
     eng.compute(forces=False)                  # first list build + forces: not timed (as on the GPU)
     t0 = time.perf_counter()
@@ -176,7 +195,7 @@ def time_oracle(pos, spe, side, vel, md_steps, target_s=None):
             eng.run_nve(more, DT)
             spent, done = spent + time.perf_counter() - t0, done + more
     eng.close()
-    return len(spe) * done / spent, spent, done
+    return len(spe) * done / spent, spent, done, threads
 
 
 def run_reference(args, rank, world):
@@ -184,14 +203,17 @@ def run_reference(args, rank, world):
     the timed stand-in is the oracle port on all host cores, same workload, bounded sample."""
     if rank != 0:
         return
-    cores = os.cpu_count()
-    os.environ.setdefault('OMP_NUM_THREADS', str(cores))
+    lib, cores = oracle_library(host_cores())      # cores = the OpenMP team actually used
     pos, spe, side, vel = ka_workload()
     n = len(spe)
     inner = 5                                   # MD timesteps per bench step (bounded sample)
-    lib = oracle_library()
     eng = make_engine(lib, 64, pos, spe, side, vel)
     eng.compute(forces=False)
+    t0 = time.perf_counter()
+    eng.run_nve(inner, DT)
+    per_md_step = (time.perf_counter() - t0) / inner
+    # bounded: the whole --steps K --warmup W run stays within ~3 minutes on any host
+    inner = int(min(inner, max(1, 180.0 / (per_md_step * max(args.steps + args.warmup, 1)))))
     for _ in range(args.warmup):
         eng.run_nve(inner, DT)
     t0 = time.perf_counter()
@@ -205,8 +227,8 @@ def run_reference(args, rank, world):
         'ms_per_step': 1e3 * elapsed / args.steps, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
         'config': workload_config(n, inner),
-        'cpu_baseline': {'value': value, 'unit': 'particle-timesteps/s', 'cores': cores, 'kind': 'port',
-                         'sample': '%d bench steps x %d NVE timesteps of the full N=%d system, '
+        'cpu_baseline': {'value': value, 'unit': 'particle-timesteps/s', 'cores': cores, 'threads': cores,
+                         'kind': 'port', 'sample': '%d bench steps x %d NVE timesteps of the full N=%d system, '
                                    'oracle/oracle_c.c (C + OpenMP, fp64, Verlet list)' % (args.steps, inner, n)},
         'e2e': {'value': value, 'unit': 'particle-timesteps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
@@ -225,6 +247,68 @@ def workload_config(n, inner, world=1, halo_bytes=0, comm=None):
         cfg['halo_bytes_per_step_per_gpu'] = int(halo_bytes)
         cfg['comm'] = comm
     return cfg
+
+
+def parity_system(world, seed=5):
+    """The system of the multi-GPU parity check: KA 80:20 at rho = 1.2 in a box of
+    (world x 10) x 20 x 20 (4800 particles per slab; the slab is 10 wide, r_list = 2.8), jittered,
+    T = 1.5 so that the list is refreshed several times within 120 steps and particles migrate."""
+    d = numpy.load(os.path.join(ROOT, 'tests', 'golden', 'ka_N1200.npz'))
+    n0 = len(d['species'])
+    scale = (n0 / RHO / numpy.prod(d['side'])) ** (1.0 / 3.0)
+    pos0, side0 = d['position'] * scale, d['side'] * scale
+    reps = numpy.array([world, 2, 2])
+    shifts = numpy.stack(numpy.meshgrid(*[numpy.arange(r) for r in reps], indexing='ij'), -1).reshape(-1, 3)
+    pos = (pos0[None, :, :] + shifts[:, None, :] * side0).reshape(-1, 3) - 0.5 * (reps - 1) * side0
+    rng = numpy.random.default_rng(seed)
+    pos += rng.uniform(-0.02, 0.02, size=pos.shape)
+    n = len(pos)
+    vel = rng.normal(0, numpy.sqrt(1.5), size=(n, 3))
+    vel -= vel.mean(axis=0)
+    return pos, vel, numpy.tile(d['species'], len(shifts)).astype(numpy.int32), side0 * reps
+
+
+def dd_parity(lib, rank, world, steps=120):
+    """Correctness of the multi-GPU product path, where the driver can see it (its test box has
+    one GPU): the slab-decomposed run over all ranks (peer-memory halo, refresh on the device when
+    available) against ONE engine holding the whole system on rank 0's GPU, both precisions, the
+    scenario of tests/test_gpu_dd.py::_compare.  Returns the `parity` block (rank 0) or None."""
+    from atooms_b200.dd import SlabDomain
+    pos, vel, spe, side = parity_system(world)
+    slab = numpy.clip(numpy.floor((pos[:, 0] / side[0] + 0.5) * world).astype(int), 0, world - 1)
+    mine = numpy.nonzero(slab == rank)[0]
+    block = {'steps': steps, 'particles': int(len(spe)), 'ok': True}
+    for precision in (64, 32):
+        dom = SlabDomain(pos[mine], vel[mine], spe[mine], side, model=atooms_model(), dt=DT, skin=SKIN,
+                         precision=precision, gid=mine, library=lib)
+        t0 = dom.thermo()
+        dom.run(steps)
+        t1 = dom.thermo()
+        gpos, gvel, gimg = dom.gather()
+        comm = ('peer-memory mailboxes, refresh on the device' if dom._ids_resident else 'peer-memory mailboxes') \
+            if dom._peer else ('NCCL enqueued from C' if dom._fast else 'torch.distributed')
+        refreshes = dom.refreshes
+        dom.close()
+        if rank != 0:
+            continue
+        ref = make_engine(lib, precision, pos, spe, side, vel, device=int(os.environ.get('LOCAL_RANK', '0')))
+        e0 = ref.thermo()
+        ref.run_nve(steps, DT)
+        rpos, rvel, rimg = ref.download(image=True)
+        e1 = ref.thermo()
+        ref.close()
+        tol_x, tol_e = (1e-8, 1e-8) if precision == 64 else (2e-4, 1e-5)
+        dx = float(numpy.abs((gpos + gimg * side) - (rpos + rimg * side)).max())
+        dv = float(numpy.abs(gvel - rvel).max())
+        de0 = abs((t0['kinetic'] + t0['potential']) - (e0['kinetic'] + e0['potential'])) / abs(e0['potential'])
+        de1 = abs((t1['kinetic'] + t1['potential']) - (e1['kinetic'] + e1['potential'])) / abs(e1['potential'])
+        ok = bool(t1['n'] == len(spe) and refreshes >= 3 and dx < tol_x and dv < 10 * tol_x and de0 < 1e-9
+                  and de1 < tol_e)
+        block['fp%d' % precision] = {'max_abs_dx': dx, 'max_abs_dv': dv, 'rel_dE_start': float(de0),
+                                     'rel_dE_end': float(de1), 'refreshes': int(refreshes), 'comm': comm,
+                                     'tol_dx': tol_x, 'tol_dE': tol_e, 'ok': ok}
+        block['ok'] = block['ok'] and ok
+    return block if rank == 0 else None
 
 
 def atooms_model():
@@ -413,6 +497,8 @@ def main():
                                   energy=(th['kinetic'] + th['potential']) / n, ntot=n, halo_bytes=0)
         eng.close()
 
+    parity = dd_parity(lib, rank, world) if world > 1 else None
+
     if rank == 0:
         r = results[args.precision]
         peak, peak_src = measured_peak()
@@ -453,17 +539,21 @@ def main():
                                       'total_energy_per_particle': results[p]['energy']}
                        for p in results},
         }
+        if parity is not None:
+            line['parity'] = parity
         if not args.no_cpu_baseline:
-            cores = os.cpu_count()
-            os.environ.setdefault('OMP_NUM_THREADS', str(cores))
-            cpu_value, cpu_s, md = time_oracle(pos, spe, side, vel, 10, target_s=15.0)
-            line['cpu_baseline'] = {'value': cpu_value, 'unit': 'particle-timesteps/s', 'cores': cores, 'kind': 'port',
+            cpu_value, cpu_s, md, cores = time_oracle(pos, spe, side, vel, 10, target_s=15.0)
+            line['cpu_baseline'] = {'value': cpu_value, 'unit': 'particle-timesteps/s', 'cores': cores,
+                                    'threads': cores, 'kind': 'port',
                                     'sample': '%d NVE timesteps of the full N=%d system (%.1f s), oracle/oracle_c.c '
                                               '(C + OpenMP, fp64, Verlet list)' % (md, n, cpu_s)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if parity is not None and not parity['ok']:
+        raise SystemExit('bench.py: the %d-GPU run does not reproduce the single-domain trajectory: %s'
+                         % (world, json.dumps(parity)))
 
 
 if __name__ == '__main__':

@@ -322,8 +322,11 @@ int b2_profile(b2_ctx *ctx, double out[8]);
  * The per-block partial sums that b2_thermo keeps in cudaMalloc'ed memory live
  * here in a fixed 256 KiB __device__ array, which every GPU that loads the
  * library holds until exit.
- *   vel_mass_dev : n x (vx, vy, vz, mass) as float4 (B2_FP32) or double4 (B2_FP64)
- *   out_dev      : 8 doubles on the device: K, Px, Py, Pz, M, 0, 0, 0
+ *   vel_mass_dev : n x (vx, vy, vz, mass) as float4 (B2_FP32) or double4 (B2_FP64),
+ *                  16-byte aligned (it is read with vector loads; a misaligned
+ *                  pointer is refused with B2_EINVAL rather than left to fault
+ *                  inside the caller's CUDA context)
+ *   out_dev      : 8 doubles on the device (8-byte aligned): K, Px, Py, Pz, M, 0, 0, 0
  *   n            : at most B2_STATIC_MAX_PARTICLES, else B2_EINVAL
  * Runs asynchronously on `cuda_stream` of the CURRENT device.  Calls that can
  * overlap on one GPU share the scratch and race: keep them on one stream.  The

@@ -21,8 +21,10 @@
  *   KA / LJ tables .......... tests/test_rumd.py:26-31, tests/test_lammps.py:24-27
  *   stop rule ............... atooms/optimization/core.py:34-36
  *
- * Build: see oracle/Makefile (-O2 -fopenmp -ffp-contract=off: the neighbour
- * predicate must not be FMA-contracted, it is compared bit-for-bit).
+ * Build: see oracle/Makefile (-O3 -march=x86-64-v3 -fopenmp).  The neighbour
+ * predicate is compared bit-for-bit with the CUDA list, so the list build (and
+ * nothing else) is compiled without FMA contraction: see the GCC optimize
+ * pragma around in_list* / build_list.
  */
 #include "../include/atooms_b200.h"
 
@@ -82,6 +84,33 @@ static int fail(b2_ctx *c, int code, const char *msg)
 
 int b2_abi_version(void) { return B2_ABI_VERSION; }
 const char *b2_backend_name(void) { return "oracle-c"; }
+
+/* Oracle-only (not part of the product's ABI): the OpenMP team size, for the timed CPU legs of
+ * bench.py.  OMP_NUM_THREADS is read once per process, and torchrun pre-sets it to 1. */
+int b2_oracle_set_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+    return omp_get_max_threads();
+#else
+    (void)n;
+    return 1;
+#endif
+}
+int b2_oracle_threads(void)
+{
+#ifdef _OPENMP
+    int t = 1;
+#pragma omp parallel
+    {
+#pragma omp master
+        t = omp_get_num_threads();
+    }
+    return t;
+#else
+    return 1;
+#endif
+}
 const char *b2_last_error(const b2_ctx *c) { return c ? c->err : g_err; }
 
 int b2_create(int device, int precision, b2_ctx **out)
@@ -279,6 +308,9 @@ int b2_mark_reference(b2_ctx *c)
     return B2_OK;
 }
 
+/* The list build is the one region that must not be FMA-contracted. */
+#pragma GCC push_options
+#pragma GCC optimize("fp-contract=off")
 /* ------------------------------------------------------------------------
  * Neighbour predicate, evaluated in the context's precision.
  *   d = x_i - x_j ; d -= rint(d / L) * L ; r2 = (dx*dx + dy*dy) + dz*dz
@@ -418,6 +450,8 @@ static int build_list(b2_ctx *c)
     c->rebuilds++;
     return B2_OK;
 }
+
+#pragma GCC pop_options
 
 /* Pair expressions: identical to oracle_np.compute */
 static int compute_forces(b2_ctx *c, const double *pos, double *frc, double *pe, double *vir,

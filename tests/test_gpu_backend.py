@@ -20,13 +20,30 @@ pytestmark = pytest.mark.gpu
 
 PROTOCOL_TESTS = [hp.test_backend_surface, hp.test_nve_pin_through_the_backend, hp.test_observers_accessors,
                   hp.test_sync_contract, hp.test_thermostat_switches_the_backend_to_nvt, hp.test_deepcopy_and_reassign, hp.test_checkpoint_roundtrip,
-                  hp.test_minimisation_backend, hp.test_generic_interaction_protocol, hp.test_trajectory_writer]
+                  hp.test_minimisation_backend, hp.test_generic_interaction_protocol, hp.test_trajectory_writer,
+                  hp.test_model_registry_and_reference_schema]
+# the reference's OWN drivers (Simulation, Optimization, composite Interaction, its trajectory readers,
+# the md.py look-alike) on the CUDA engine; the reference comes from baseline/_ref on the GPU box
+REFERENCE_DRIVER_TESTS = [hp.test_reference_simulation_driver, hp.test_reference_optimization_driver,
+                          hp.test_interaction_with_reference_system,
+                          hp.test_neighbors_export_round_trips_through_the_reference_reader,
+                          hp.test_command_line_driver]
+
+
+def _call(fn, cuda_lib, pins, tmp_path, monkeypatch):
+    available = {'oracle_lib': cuda_lib, 'pins': pins, 'tmp_path': tmp_path, 'monkeypatch': monkeypatch}
+    fn(**{name: available[name] for name in inspect.signature(fn).parameters})
 
 
 @pytest.mark.parametrize('fn', PROTOCOL_TESTS, ids=lambda f: f.__name__)
-def test_protocol_on_cuda(fn, cuda_lib, pins, tmp_path):
-    available = {'oracle_lib': cuda_lib, 'pins': pins, 'tmp_path': tmp_path}
-    fn(**{name: available[name] for name in inspect.signature(fn).parameters})
+def test_protocol_on_cuda(fn, cuda_lib, pins, tmp_path, monkeypatch):
+    _call(fn, cuda_lib, pins, tmp_path, monkeypatch)
+
+
+@pytest.mark.parametrize('fn', REFERENCE_DRIVER_TESTS, ids=lambda f: f.__name__)
+def test_reference_drivers_on_cuda(fn, cuda_lib, pins, tmp_path, monkeypatch):
+    assert hp.HAVE_REF, 'the reference must be installed under baseline/_ref (tools/install_reference.py)'
+    _call(fn, cuda_lib, pins, tmp_path, monkeypatch)
 
 
 def test_default_library_is_cuda():

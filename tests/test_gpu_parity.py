@@ -308,18 +308,40 @@ def test_minimisers_follow_the_oracle(cuda_lib, oracle_lib, method, dt):
 
 
 def test_fire_reaches_the_reference_inequalities(cuda_lib, pins):
-    """tests/test_optimization.py:20-35 (LAMMPS ftol 1e-4 on |F|_2)."""
+    """tests/test_optimization.py:20-35 (LAMMPS ftol 1e-4 on |F|_2): U/N < -6.8, sum F^2/N < 1e-4.
+
+    The start (LJ N=256 at rho=1, a liquid configuration) sits above many local minima and the
+    descent is chaotic: WHICH minimum is reached depends on round-off.  Shown here rather than
+    asserted away: from ten starts jittered by 1e-4 the fp64 engine itself lands anywhere in
+    U/N = -6.84 ... -6.78 (the oracle does the same on the CPU), i.e. the reference's -6.8 is a
+    property of the start it was written for, not of every neighbouring one.  So: (i) the
+    reference's own inequality is asserted for the UNJITTERED start in fp64, the precision of the
+    engine it was written for; (ii) every run, both precisions, must converge to the force
+    tolerance; (iii) the fp32 minima must be statistically indistinguishable from the fp64 ones
+    (same range, same median within the spread), and most of them must meet -6.8 too."""
     pin = pins['lj_N256_minimised']
-    d = golden('lj_N256')
-    for precision, tol in ((64, 1e-8 / 256), (32, 1e-7)):
-        eng = make_engine(cuda_lib, d, onp.lennard_jones(2.5, True), precision, velocities=False)
-        steps, converged = eng.minimize(capi.MIN_FIRE, 100000, 0.002, tol)
-        assert converged and steps < 100000
-        t = eng.thermo()
-        # fp32 round-off sends the (chaotic) descent into a neighbouring basin:
-        # the energy bound is the reference's only in fp64
-        assert t['potential'] / 256 < (pin['U_per_particle_below'] if precision == 64 else -6.7)
-        assert t['fnorm2'] / 256 < pin['fn2_per_particle_below']
+    d = dict(golden('lj_N256').items())
+    lj = onp.lennard_jones(2.5, True)
+    energy = {64: [], 32: []}
+    for seed in range(10):
+        start = dict(d)
+        if seed:
+            start['position'] = d['position'] + numpy.random.default_rng(seed).uniform(-1e-4, 1e-4, size=d['position'].shape)
+        for precision, tol in ((64, 1e-8 / 256), (32, 1e-7)):
+            eng = make_engine(cuda_lib, start, lj, precision, velocities=False)
+            steps, converged = eng.minimize(capi.MIN_FIRE, 100000, 0.002, tol)
+            assert converged and steps < 100000
+            t = eng.thermo()
+            assert t['fnorm2'] / 256 < pin['fn2_per_particle_below']
+            energy[precision].append(t['potential'] / 256)
+            eng.close()
+    e64, e32 = numpy.array(energy[64]), numpy.array(energy[32])
+    assert e64[0] < pin['U_per_particle_below']                     # the reference's test, as written
+    assert e64.max() - e64.min() > 0.01                             # the roulette is real, in fp64 already
+    assert e64.min() - 0.03 < e32.min() and e32.max() < e64.max() + 0.03
+    assert abs(numpy.median(e32) - numpy.median(e64)) < 0.03
+    assert numpy.sum(e32 < pin['U_per_particle_below']) >= 6 and numpy.sum(e64 < pin['U_per_particle_below']) >= 6
+    assert e32.max() < -6.75 and e64.max() < -6.75
 
 
 def test_update_and_scale(cuda_lib, oracle_lib):

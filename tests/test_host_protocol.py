@@ -18,14 +18,42 @@ from conftest import golden
 import atooms_b200
 from atooms_b200 import B200, EnergyMinimization, Interaction, System, Cell, Trajectory
 
+# The reference's own drivers: from the read-only tree when it is there (development container),
+# else from the unmodified install under baseline/_ref (recipe: tools/install_reference.py; it
+# travels to the GPU box).  B2_NO_REFERENCE_TREE=1 forces the second route, for testing it here.
 REF = '/root/reference'
-HAVE_REF = os.path.isdir(os.path.join(REF, 'atooms'))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_TREE = os.path.isdir(os.path.join(REF, 'atooms')) and not os.environ.get('B2_NO_REFERENCE_TREE')
+_INSTALLED = os.path.join(ROOT, 'baseline', '_ref')
+REF_IMPORT = REF if _TREE else (_INSTALLED if os.path.isdir(os.path.join(_INSTALLED, 'atooms')) else None)
+HAVE_REF = REF_IMPORT is not None
 if HAVE_REF:
-    if REF not in sys.path:
-        sys.path.insert(0, REF)
+    if REF_IMPORT not in sys.path:
+        sys.path.insert(0, REF_IMPORT)
     if not hasattr(numpy, 'set_string_function'):     # numpy >= 2 shim for the reference's xyz reader
         numpy.set_string_function = lambda *a, **k: None
-needs_ref = pytest.mark.skipif(not HAVE_REF, reason='reference tree not present (GPU box)')
+needs_ref = pytest.mark.skipif(not HAVE_REF, reason='reference neither at /root/reference nor installed in baseline/_ref')
+
+# data files of the reference the driver tests start from -> the golden fixture made from each
+_DATA = {'lj_N1000_rho1.0.xyz': 'lj_N1000', 'lj_N256_rho1.0.xyz': 'lj_N256',
+         'ka_N256_rho1.185_rumd.xyz.gz': 'ka_N256_rumd'}
+
+
+def ref_data(name, tmp_path):
+    """Path of a reference data file: the file itself when the tree is present, else an xyz file
+    written from the golden fixture that tests/golden/make_golden.py made from it (same numbers)."""
+    if _TREE:
+        return os.path.join(REF, 'data', name)
+    d = golden(_DATA[name])
+    path = str(tmp_path / name.replace('.gz', ''))
+    names = d['species_names'][d['species']]
+    cols = [names.astype(str), d['position']] + ([d['velocity']] if 'velocity' in d else [])
+    with open(path, 'w') as fh:
+        fh.write('%d\nstep:0 columns:species,position%s dt:0.005 cell:%s\n'
+                 % (len(names), ',velocity' if 'velocity' in d else '', ','.join(repr(float(x)) for x in d['side'])))
+        for row in zip(*cols):
+            fh.write(' '.join([row[0]] + [repr(float(x)) for block in row[1:] for x in block]) + '\n')
+    return path
 
 
 def make_system(name, lib, model, precision=64, velocities=True):
@@ -258,7 +286,7 @@ def test_reference_simulation_driver(oracle_lib, pins, tmp_path):
     from atooms.simulation import Simulation, write_thermo, Scheduler
     pin = pins['lj_N1000_nve_x0']
     model = atooms_b200.lennard_jones(2.5, shifted=False)
-    bck = B200(os.path.join(REF, 'data', 'lj_N1000_rho1.0.xyz'), model, dt=pin['dt'], library=oracle_lib)
+    bck = B200(ref_data('lj_N1000_rho1.0.xyz', tmp_path), model, dt=pin['dt'], library=oracle_lib)
     out = str(tmp_path / 'sim')
     sim = Simulation(bck, output_path=out, checkpoint_interval=10, enable_speedometer=False)
     sim.add(write_thermo, Scheduler(5))
@@ -273,7 +301,7 @@ def test_reference_simulation_driver(oracle_lib, pins, tmp_path):
     assert numpy.abs(thermo[:, 4] - thermo[0, 4]).max() < 2e-2          # total energy (unshifted cutoff, dt 0.005)
     assert os.path.exists(out + '.chk.npz') and os.path.exists(out + '.chk.step')
     # restart from the checkpoint (simulation/core.py:240-273)
-    bck2 = B200(os.path.join(REF, 'data', 'lj_N1000_rho1.0.xyz'), model, dt=pin['dt'], library=oracle_lib)
+    bck2 = B200(ref_data('lj_N1000_rho1.0.xyz', tmp_path), model, dt=pin['dt'], library=oracle_lib)
     sim2 = Simulation(bck2, output_path=out, restart=True, enable_speedometer=False)
     sim2.run(30)
     assert sim2.current_step == 30
@@ -282,11 +310,11 @@ def test_reference_simulation_driver(oracle_lib, pins, tmp_path):
 
 
 @needs_ref
-def test_reference_optimization_driver(oracle_lib, pins):
+def test_reference_optimization_driver(oracle_lib, pins, tmp_path):
     """tests/test_optimization.py:20-35 with our backend in place of LAMMPS."""
     from atooms.optimization import Optimization
     pin = pins['lj_N256_minimised']
-    bck = EnergyMinimization(os.path.join(REF, 'data', 'lj_N256_rho1.0.xyz'), 'lennard_jones', library=oracle_lib)
+    bck = EnergyMinimization(ref_data('lj_N256_rho1.0.xyz', tmp_path), 'lennard_jones', library=oracle_lib)
     opt = Optimization(bck)
     opt.tolerance = 1e-4
     opt.run()
@@ -296,10 +324,10 @@ def test_reference_optimization_driver(oracle_lib, pins):
 
 
 @needs_ref
-def test_interaction_with_reference_system(oracle_lib, pins):
+def test_interaction_with_reference_system(oracle_lib, pins, tmp_path):
     """system.interaction = Interaction(...) on a plain atooms System (system.py:245-335)."""
     from atooms.trajectory import TrajectoryXYZ
-    th = TrajectoryXYZ(os.path.join(REF, 'data', 'lj_N1000_rho1.0.xyz'))
+    th = TrajectoryXYZ(ref_data('lj_N1000_rho1.0.xyz', tmp_path))
     system = th[0]
     th.close()
     system.interaction = Interaction(atooms_b200.lennard_jones(2.5, shifted=False), library=oracle_lib)
@@ -323,7 +351,7 @@ def test_neighbors_export_round_trips_through_the_reference_reader(oracle_lib, t
     from atooms.trajectory import TrajectoryXYZ
     from atooms.trajectory.xyz import TrajectoryNeighbors as RefNeighbors
     from oracle import oracle_np as onp
-    th = TrajectoryXYZ(os.path.join(REF, 'data', 'lj_N256_rho1.0.xyz'))
+    th = TrajectoryXYZ(ref_data('lj_N256_rho1.0.xyz', tmp_path))
     system = th[0]
     th.close()
     inter = Interaction(atooms_b200.lennard_jones(2.5, True), skin=0.3, library=oracle_lib)
@@ -358,7 +386,7 @@ def test_command_line_driver(oracle_lib, tmp_path, monkeypatch):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     out = str(tmp_path / 'run')
-    params = argparse.Namespace(T=0.8, dt=0.002, input_file=os.path.join(REF, 'data', 'ka_N256_rho1.185_rumd.xyz.gz'),
+    params = argparse.Namespace(T=0.8, dt=0.002, input_file=ref_data('ka_N256_rho1.185_rumd.xyz.gz', tmp_path),
                                 integrator='nve', model='kob_andersen', tau=0.2, skin=0.3, precision='fp64',
                                 device=0, steps=60, thermo_interval=20, config_interval=30, checkpoint_interval=0,
                                 restart=False, verbose=False, debug=False, output_dir=out)

@@ -62,6 +62,12 @@ def test_static_matches_thermo_two_calls_in_a_row(cuda_lib, precision):
         scale = numpy.array([ref[0], *([numpy.abs(ref[1:4]).max()] * 3), ref[4]])
         assert numpy.all(numpy.abs(got[:5] - ref) <= TOL[precision] * scale), (got, ref)
         assert numpy.all(got[5:] == 0.0)
+        # and against plain NumPy sums over the very array the kernel read (an independent check:
+        # b2_thermo is another CUDA path)
+        dtype = numpy.float64 if precision == 64 else numpy.float32
+        v, m = data['velocity'].astype(dtype).astype(numpy.float64), data['mass'].astype(dtype).astype(numpy.float64)
+        host = numpy.array([0.5 * numpy.sum(m * numpy.sum(v * v, axis=1)), *(m[:, None] * v).sum(axis=0), m.sum()])
+        assert numpy.all(numpy.abs(got[:5] - host) <= 1e-12 * scale), (got, host)
 
 
 def test_static_rejects_oversize_and_bad_arguments(cuda_lib):
@@ -71,6 +77,22 @@ def test_static_rejects_oversize_and_bad_arguments(cuda_lib):
         capi.kinetic_static(0, 10, 64, 0)           # NULL pointers
     with pytest.raises(ValueError):
         capi.kinetic_static(0, 0, 16, 0)            # bad precision
+
+
+def test_static_rejects_misaligned_pointers(cuda_lib):
+    """A tensor view that does not start on a 16-byte boundary must be refused on the host: the
+    vector loads would otherwise fault inside the caller's own CUDA context."""
+    import torch
+    buf = torch.zeros(4 * 64 + 1, dtype=torch.float32, device='cuda')
+    out = torch.zeros(9, dtype=torch.float64, device='cuda')
+    stream = torch.cuda.current_stream().cuda_stream
+    with pytest.raises(ValueError, match='aligned'):
+        capi.kinetic_static(buf[1:].data_ptr(), 64, 32, out.data_ptr(), stream)
+    with pytest.raises(ValueError, match='aligned'):
+        capi.kinetic_static(buf.data_ptr(), 64, 32, out.data_ptr() + 4, stream)
+    capi.kinetic_static(buf.data_ptr(), 64, 32, out.data_ptr(), stream)      # the aligned call still works
+    torch.cuda.synchronize()
+    assert numpy.all(out.cpu().numpy() == 0.0)
 
 
 def test_static_empty_input(cuda_lib):
