@@ -85,17 +85,20 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
         R r2inv = r_rcp(r2);                                                          \
         R r6inv = r2inv * r2inv * r2inv;                                              \
         R fp = r6inv * (a12 * r6inv - a6) * r2inv;                                    \
-        fp = r2 < rc2 ? fp : (R)0;                                                    \
-        fx += fp * dx; fy += fp * dy; fz += fp * dz;                                  \
         if (EV || STRESS) {                                                           \
             /* observables: fp64 pair arithmetic on the stored positions, in both */ \
             /* precisions (totals cancel heavily; fp32 would leave systematic    */ \
-            /* errors that do not average out)                                   */ \
+            /* errors that do not average out).  The cut-off decision of the     */ \
+            /* REPORTED forces is taken on the same fp64 distance: the force is  */ \
+            /* discontinuous at r_c (|F(r_c)| ~ 0.04), and among ~4e7 pairs a    */ \
+            /* few sit within float round-off of it                              */ \
             const int a = ti + tj;                                                    \
             double ex, ey, ez;                                                        \
             delta_d(pi, PJ, box, ex, ey, ez);                                         \
             double q2 = ex * ex + ey * ey + ez * ez;                                  \
-            if (q2 < g_pair.rc2[a]) {                                                 \
+            const bool inside = q2 < g_pair.rc2[a];                                   \
+            fp = inside ? fp : (R)0;                                                  \
+            if (inside) {                                                             \
                 double q2inv = 1.0 / q2;                                              \
                 double q6inv = q2inv * q2inv * q2inv;                                 \
                 double d12 = g_pair.c12[a], d6 = g_pair.c6[a];                        \
@@ -108,7 +111,10 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
                     st[3] += ey * gy; st[4] += ey * gz; st[5] += ez * gz;             \
                 }                                                                     \
             }                                                                         \
+        } else {                                                                      \
+            fp = r2 < rc2 ? fp : (R)0;                                                \
         }                                                                             \
+        fx += fp * dx; fy += fp * dy; fz += fp * dz;                                  \
     }
     // the deeper pipeline only where the registers are there for it: the step kernel (no energies)
     constexpr int B2_UNROLL = (sizeof(R) == 4 && !EV) ? B2_UNROLL32 : B2_UNROLL64;

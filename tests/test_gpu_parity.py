@@ -337,6 +337,7 @@ def test_fire_reaches_the_reference_inequalities(cuda_lib, pins):
             eng.close()
     e64, e32 = numpy.array(energy[64]), numpy.array(energy[32])
     assert e64[0] < pin['U_per_particle_below']                     # the reference's test, as written
+    assert e32[0] < pin['U_per_particle_below']                     # ... and in fp32 (measured: -6.8115 in both)
     assert e64.max() - e64.min() > 0.01                             # the roulette is real, in fp64 already
     assert e64.min() - 0.03 < e32.min() and e32.max() < e64.max() + 0.03
     assert abs(numpy.median(e32) - numpy.median(e64)) < 0.03
