@@ -221,7 +221,8 @@ struct Ctl {
     unsigned int blocks_done;    // ticket for "last block finishes the step"
     unsigned int max_count;      // largest neighbour count seen by the last build
     unsigned int converged;
-    unsigned int peer_error, pad0_;   // a peer-memory wait timed out (1) or lost step (2)
+    unsigned int peer_error;     // a peer-memory wait timed out (1) or lost step (2)
+    unsigned int win_max;        // windowed list: records of the largest candidate window seen by the last build (+1 dummy)
     long long steps_done, steps_target, rebuilds;
     double disp_bound, half_skin;
     // minimiser
@@ -260,6 +261,10 @@ struct Grid {
     int m;             // cells are (r_list,max / m) wide; the stencil reaches m cells (1 or 2)
     float w[3];        // cell widths
     float reach2;      // (r_list,max)^2, padded: cells farther than this cannot hold a neighbour
+    // windowed list (b2_win.cuh): the grid is a whole number of 4x4x4-cell super-blocks per axis
+    int win;           // 1: list entries are 16-bit offsets into the super-block's candidate window
+    int nsb[3];        // super-blocks per axis (nc / 4)
+    int wcap;          // records a window may hold, the dummy included (shared memory of the step kernel)
 };
 
 __device__ __forceinline__ void cell_of(const Box<float> &, const Grid &g, const int4 &p, int &cx, int &cy, int &cz)

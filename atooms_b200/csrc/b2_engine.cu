@@ -4,6 +4,7 @@
 #include "b2_common.cuh"
 #include "b2_neigh.cuh"
 #include "b2_force.cuh"
+#include "b2_win.cuh"
 #include "b2_batch.cuh"
 #include "b2_ddr.cuh"
 
@@ -78,6 +79,11 @@ struct b2_ctx {
     int ncelltab = 0, sort_blocks = 0, sort_passes = 0;
     int *nbr = nullptr, *nnb = nullptr;
     int cap = 0;
+    // windowed list (b2_win.cuh)
+    int *b8start = nullptr, *tile_base = nullptr;
+    int nb8codes = 0, nsb_total = 0, win_tab_alloc = 0, win_sb_alloc = 0;
+    bool win_off = false;            // windows do not fit: this context keeps the global-index list
+    size_t smem_optin = 0;
     // control / reductions / staging
     Ctl *ctl = nullptr, *hctl = nullptr;
     double *partial = nullptr;
@@ -129,6 +135,12 @@ static int fail(b2_ctx *c, int code, const char *fmt, ...)
         if (e_ != cudaSuccess)                                                            \
             return fail(c, e_ == cudaErrorMemoryAllocation ? B2_ENOMEM : B2_ECUDA,        \
                         "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+#define LAUNCH_SMEM(kernel, grid, block, smem, ...)                                       \
+    do {                                                                                  \
+        kernel<<<(grid), (block), (smem), c->stream>>>(__VA_ARGS__);                      \
+        c->launches++;                                                                    \
     } while (0)
 
 #define LAUNCH(kernel, grid, block, ...)                                                  \
@@ -233,7 +245,9 @@ template <typename R> struct Impl {
         if ((rc = dev_alloc(c, &c->stage_i, 3 * n))) return rc;
         c->sort_blocks = std::max(1, cdiv(n, SORT_TILE));
         if ((rc = dev_alloc(c, &c->hist, (size_t)256 * c->sort_blocks))) return rc;
-        size_t np = std::max<size_t>((size_t)MAX_RED_BLOCKS * 9, (size_t)cdiv(n, FORCE_THREADS) * 6);
+        // stress partials: one row per block of k_force (n / FORCE_THREADS) or of k_force_win (a super-block of
+        // 4^3 half-width cells each; never more than one per 8 particles in any sensible system, checked at launch)
+        size_t np = std::max<size_t>((size_t)MAX_RED_BLOCKS * 9, (size_t)(cdiv(n, FORCE_THREADS) + n / 8 + 64) * 6);
         if ((rc = dev_alloc(c, &c->partial, np))) return rc;
         return B2_OK;
     }
@@ -262,6 +276,35 @@ template <typename R> struct Impl {
             mx = std::max(mx, g.nc[d]);
             g.w[d] = (float)(c->side[d] / g.nc[d]);
         }
+        // windowed list (b2_win.cuh): a whole number (>= 2) of 4x4x4-cell super-blocks per axis; the cells
+        // grow by at most 3 / nc to make it so.  B2_LIST_GLOBAL=1 keeps the global-index list (A/B timing).
+        static const bool force_global = getenv("B2_LIST_GLOBAL") && atoi(getenv("B2_LIST_GLOBAL")) != 0;
+        g.win = 0;
+        g.nsb[0] = g.nsb[1] = g.nsb[2] = 0;
+        if (!g.allpairs && g.m == 2 && !c->win_off && !force_global && g.nc[0] >= 8 && g.nc[1] >= 8 && g.nc[2] >= 8) {
+            double cellvol = 1.0;
+            for (int d = 0; d < 3; d++) cellvol *= c->side[d] / (g.nc[d] / 4 * 4);
+            // records of a window (8^3 cells) at the mean density, with room for fluctuations; a slab of a
+            // decomposed system is denser than its global mean: the first build reports what it needs
+            const double expect = (double)c->n / (c->side[0] * c->side[1] * c->side[2]) * 512.0 * cellvol;
+            int wcap = std::max(g.wcap, ((int)(1.25 * expect) + 128 + 7) / 8 * 8);
+            const size_t rec = c->precision == B2_FP32 ? 16 : 32;
+            const size_t lim = std::min<size_t>((c->smem_optin > 4096 ? c->smem_optin - 4096 : 0) / rec, 65528);
+            const size_t nsbt = (size_t)(g.nc[0] / 4) * (g.nc[1] / 4) * (g.nc[2] / 4);
+            if ((size_t)wcap <= lim && nsbt <= (size_t)c->ncap / 8 + 64) {
+                g.win = 1;
+                g.wcap = wcap;
+                for (int d = 0; d < 3; d++) {
+                    g.nc[d] = g.nc[d] / 4 * 4;
+                    g.nsb[d] = g.nc[d] / 4;
+                }
+                mx = 1;
+                for (int d = 0; d < 3; d++) {
+                    mx = std::max(mx, g.nc[d]);
+                    g.w[d] = (float)(c->side[d] / g.nc[d]);
+                }
+            }
+        }
         g.reach2 = (float)(rl * rl * (1.0 + 1e-3));
         g.cellbits = 1;
         while ((1 << g.cellbits) < mx) g.cellbits++;
@@ -273,7 +316,63 @@ template <typename R> struct Impl {
             if ((rc = dev_alloc(c, &c->cell_end, tab))) return rc;
             c->ncelltab = tab;
         }
+        if (g.win) {
+            int rc;
+            c->nb8codes = tab >> 3;
+            c->nsb_total = g.nsb[0] * g.nsb[1] * g.nsb[2];
+            if (c->nb8codes + 2 > c->win_tab_alloc) {
+                if ((rc = dev_alloc(c, &c->b8start, (size_t)c->nb8codes + 2))) return rc;
+                c->win_tab_alloc = c->nb8codes + 2;
+            }
+            if (c->nsb_total + 1 > c->win_sb_alloc) {
+                if ((rc = dev_alloc(c, &c->tile_base, (size_t)c->nsb_total + 1))) return rc;
+                c->win_sb_alloc = c->nsb_total + 1;
+            }
+            if ((rc = win_attributes(c))) return rc;
+        }
         return B2_OK;
+    }
+
+    // dynamic shared memory of the windowed kernels (above the 48 KB default)
+    static int win_attributes(b2_ctx *c)
+    {
+        const int bytes = (int)((size_t)c->grid.wcap * sizeof(P4));
+        CU(cudaFuncSetAttribute(k_step_win<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        CU(cudaFuncSetAttribute(k_step_win<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        CU(cudaFuncSetAttribute(k_force_win<R, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        CU(cudaFuncSetAttribute(k_force_win<R, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        return B2_OK;
+    }
+
+    // ints the list needs for `cap` slots per particle
+    static size_t list_ints(const b2_ctx *c, int cap)
+    {
+        if (c->grid.win)      // 16-bit entries in tiles local to the super-blocks: at most one partial tile each
+            return ((size_t)cdiv(c->ncap, 32) + (size_t)c->nsb_total + 1) * (size_t)cap * 16;
+        return (size_t)cdiv(c->ncap, 32) * (size_t)cap * 32;
+    }
+
+    // the last build did not fit: more slots per row, a larger window, or no windows at all
+    static int grow_after_overflow(b2_ctx *c)
+    {
+        int rc;
+        Grid &g = c->grid;
+        if (g.win && ((int)c->hctl->win_max > g.wcap || c->hctl->win_max >= 65535u)) {
+            const size_t rec = sizeof(P4);
+            const size_t lim = std::min<size_t>((c->smem_optin > 4096 ? c->smem_optin - 4096 : 0) / rec, 65528);
+            const size_t want = ((size_t)(c->hctl->win_max * 1.1) + 64 + 7) / 8 * 8;
+            if (want > lim) {
+                c->win_off = true;
+                c->cap = 0;
+                if ((rc = setup_grid(c))) return rc;
+                double rl = c->rcut_max + c->skin;
+                double nbar = (double)c->n / (c->side[0] * c->side[1] * c->side[2]) * 4.18879 * rl * rl * rl;
+                return ensure_capacity(c, std::max((int)(1.3 * nbar) + 24, (int)(c->hctl->max_count * 1.15) + 8));
+            }
+            g.wcap = (int)want;
+            if ((rc = win_attributes(c))) return rc;
+        }
+        return ensure_capacity(c, (int)(c->hctl->max_count * 1.15) + 8);
     }
 
     static int ensure_capacity(b2_ctx *c, int want)
@@ -281,10 +380,10 @@ template <typename R> struct Impl {
         int64_t n = c->n;
         want = (int)std::min<int64_t>(want, std::max<int64_t>(n - 1, 1));
         want = (want + 7) / 8 * 8;
-        if (want <= c->cap && c->nbr && (size_t)cdiv(c->ncap, 32) * (size_t)c->cap * 32 <= c->nbr_alloc) return B2_OK;
+        if (want <= c->cap && c->nbr && list_ints(c, c->cap) <= c->nbr_alloc) return B2_OK;
         want = std::max(want, c->cap);
         int rc;
-        size_t need = (size_t)cdiv(c->ncap, 32) * (size_t)want * 32;
+        size_t need = list_ints(c, want);
         if (need > c->nbr_alloc || !c->nbr) {
             if ((rc = dev_alloc(c, &c->nbr, need))) return rc;
             c->nbr_alloc = need;
@@ -322,18 +421,23 @@ template <typename R> struct Impl {
             LAUNCH(k_inverse, cdiv(n, 256), 256, c->ctl, 1, c->orig, n, c->inv);
             LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
             LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
+            if (c->grid.win) {
+                LAUNCH(k_b8_bounds, cdiv(c->nb8codes + 1, 256), 256, c->ctl, c->keys[src], n, c->nb8codes, c->b8start);
+                LAUNCH(k_sb_tiles, 1, 1024, c->ctl, c->grid, c->b8start, c->tile_base);
+            }
         }
         // one warp per 2x2x2 block of cells when the grid allows it (at least 7 cells per axis: the
         // 6x6x6 candidate region then holds distinct cells within half a box of the block's centre); B2_LIST_WALK=1 forces the per-particle walk (A/B timing)
         static const bool force_walk = getenv("B2_LIST_WALK") && atoi(getenv("B2_LIST_WALK")) != 0;
         const Grid &g = c->grid;
-        if (g.m == 2 && !g.allpairs && g.nc[0] >= 7 && g.nc[1] >= 7 && g.nc[2] >= 7 && n < (1 << 28) && !force_walk) {
+        if (g.m == 2 && !g.allpairs && g.nc[0] >= 7 && g.nc[1] >= 7 && g.nc[2] >= 7 && n < (1 << 28) && (!force_walk || g.win)) {
             int codes = 1 << (3 * g.cellbits - 3);
-            auto build = c->nsp <= 2 ? k_build_list_sc<R, true> : k_build_list_sc<R, false>;
+            auto build = g.win ? (c->nsp <= 2 ? k_build_list_sc<R, true, true> : k_build_list_sc<R, false, true>)
+                               : (c->nsp <= 2 ? k_build_list_sc<R, true, false> : k_build_list_sc<R, false, false>);
             // one warp per code (a strided grid of a few blocks per SM was measured 10 % slower:
             // the valid codes are unevenly spread over the Morton range)
             LAUNCH(build, cdiv(codes, SC_WARPS), SC_WARPS * 32, c->ctl, p0, p1, n, box, c->grid,
-                   c->cell_start, c->cell_end, c->nbr, c->nnb, c->cap);
+                   c->cell_start, c->cell_end, c->nbr, c->nnb, c->cap, c->b8start, c->tile_base);
         } else {
             auto build = g.m == 2 ? k_build_list<R, 2> : (g.m == 1 ? k_build_list<R, 1> : k_build_list<R, 0>);
             LAUNCH(build, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
@@ -375,7 +479,7 @@ template <typename R> struct Impl {
                 c->list_dirty = false;
                 return B2_OK;
             }
-            if ((rc = ensure_capacity(c, (int)(c->hctl->max_count * 1.15) + 8))) return rc;
+            if ((rc = grow_after_overflow(c))) return rc;
         }
         return fail(c, B2_ECUDA, "neighbour list did not fit after 8 attempts (max count %u, capacity %d)",
                     c->hctl->max_count, c->cap);
@@ -397,8 +501,38 @@ template <typename R> struct Impl {
         a.cap = c->cap;
         a.guarded = guarded ? 1 : 0;
         a.box = make_box<R>(c);
+        if (c->grid.win) {
+            auto kern = k_force_win<R, EV, STRESS>;
+            LAUNCH_SMEM(kern, c->nsb_total, WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
+            return;
+        }
         auto kern = k_force<R, EV, STRESS>;
         LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
+    }
+
+    static WinArgs<R> win_args(const b2_ctx *c)
+    {
+        WinArgs<R> w;
+        w.g = c->grid;
+        w.b8start = c->b8start;
+        w.tile_base = c->tile_base;
+        w.nbr32 = (const unsigned *)c->nbr;
+        return w;
+    }
+
+    // blocks of the force kernels (rows of stress partials)
+    static int force_blocks(const b2_ctx *c) { return c->grid.win ? c->nsb_total : cdiv(c->n, FORCE_THREADS); }
+
+    template <bool NVT>
+    static void enqueue_step(b2_ctx *c, const StepArgs<R> &a)
+    {
+        if (c->grid.win) {
+            auto kern = k_step_win<R, NVT>;
+            LAUNCH_SMEM(kern, c->nsb_total, WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
+        } else {
+            auto kern = k_step_nve<R, NVT>;
+            LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
+        }
     }
 
     // forces + per-particle energy/virial of the current configuration
@@ -676,7 +810,7 @@ int Impl<R>::thermo(b2_ctx *c, double *out, bool want_stress, double *stress9)
     LAUNCH(k_sum_partials, 1, 32, c->partial, nblk, 9, c->ctl->red);
     if (want_stress) {
         enqueue_force<true, true>(c, false);
-        LAUNCH(k_sum_partials, 1, 32, c->partial, cdiv(n, FORCE_THREADS), 6, c->ctl->red + Q_S0);
+        LAUNCH(k_sum_partials, 1, 32, c->partial, force_blocks(c), 6, c->ctl->red + Q_S0);
     }
     if ((rc = pull_ctl(c))) return rc;
     CU(cudaGetLastError());
@@ -736,7 +870,11 @@ int Impl<R>::neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, 
     if (nbr && stride < mx) return fail(c, B2_EINVAL, "b2_neighbors: stride %d smaller than max count %d", stride, mx);
     int *ocount = c->stage_i, *onbr = nullptr;
     if (nbr) CU(cudaMalloc((void **)&onbr, (size_t)n * stride * sizeof(int)));
-    LAUNCH(k_export_list, cdiv(n, 128), 128, (int)n, c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
+    if (c->grid.win)
+        LAUNCH(k_export_list_win, c->nsb_total, WIN_THREADS, c->grid, c->b8start, c->tile_base,
+               (const unsigned short *)c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
+    else
+        LAUNCH(k_export_list, cdiv(n, 128), 128, (int)n, c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
     std::vector<int32_t> hc((size_t)n);
     CU(cudaMemcpyAsync(hc.data(), ocount, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     if (nbr) CU(cudaMemcpyAsync(nbr, onbr, (size_t)n * stride * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -761,10 +899,9 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
     LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0, 0);
     const bool nvt = th_kind >= 0;
     if (nvt) {
-        if (!c->ke_partial && (rc = dev_alloc(c, &c->ke_partial, (size_t)cdiv(c->ncap, FORCE_THREADS) + 1))) return rc;
+        if (!c->ke_partial && (rc = dev_alloc(c, &c->ke_partial, (size_t)cdiv(c->ncap, FORCE_THREADS) + c->ncap / 8 + 65))) return rc;
         LAUNCH(k_thermostat_begin, 1, 1, c->ctl, th_kind, T0, tau, dt, 3.0 * (double)std::max<int64_t>(c->n - 1, 1));
     }
-    auto step_kernel = nvt ? k_step_nve<R, true> : k_step_nve<R, false>;
     c->min_resume = false;
     for (int k = 0; k < 8; k++) c->prof[k] = 0;
     long long rebuilds0 = c->hctl->rebuilds;
@@ -805,7 +942,9 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
             enqueue_rebuild(c);
             mark();
             int m = (int)std::min<int64_t>(c->batch, quota - launched);
-            for (int k = 0; k < m; k++) LAUNCH(step_kernel, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
+            for (int k = 0; k < m; k++) {
+                if (nvt) enqueue_step<true>(c, a); else enqueue_step<false>(c, a);
+            }
             launched += m;
             c->prof[2] += m;
         }
@@ -823,7 +962,7 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
         int64_t progressed = c->hctl->steps_done - done;
         done = c->hctl->steps_done;
         if (c->hctl->overflow) {
-            if ((rc = ensure_capacity(c, (int)(c->hctl->max_count * 1.15) + 8))) return rc;
+            if ((rc = grow_after_overflow(c))) return rc;
             a.nbr = c->nbr;
             a.cap = c->cap;
             c->hctl->overflow = 0u;
@@ -897,7 +1036,7 @@ int Impl<R>::minimize(b2_ctx *c, int method, int64_t max_steps, double dt, doubl
         if ((rc = pull_ctl(c))) return rc;
         CU(cudaGetLastError());
         if (c->hctl->overflow) {
-            if ((rc = ensure_capacity(c, (int)(c->hctl->max_count * 1.15) + 8))) return rc;
+            if ((rc = grow_after_overflow(c))) return rc;
             c->hctl->overflow = 0u;
             if ((rc = push_ctl(c))) return rc;
             continue;
@@ -964,8 +1103,7 @@ int Impl<R>::dd_step(b2_ctx *c, float *vmax_out)
     a.peer_state = c->peer_on ? c->peer_ticket + 2 : nullptr;
     a.nranks = c->nranks;
     a.ke_partial = nullptr;
-    auto step_kernel = k_step_nve<R, false>;
-    if (n > 0) LAUNCH(step_kernel, cdiv(n, FORCE_THREADS), FORCE_THREADS, a);
+    if (n > 0) enqueue_step<false>(c, a);
     return B2_OK;
 }
 
@@ -1046,6 +1184,11 @@ int b2_create(int device, int precision, b2_ctx **out)
     do {
         if ((e = cudaSetDevice(device)) != cudaSuccess) break;
         if ((e = cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) break;
+        {
+            int optin = 0;
+            if ((e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)) != cudaSuccess) break;
+            ctx->smem_optin = (size_t)std::max(optin, 0);
+        }
         if ((e = cudaMalloc((void **)&ctx->ctl, sizeof(Ctl))) != cudaSuccess) break;
         if ((e = cudaMemset(ctx->ctl, 0, sizeof(Ctl))) != cudaSuccess) break;
         if ((e = cudaMallocHost((void **)&ctx->hctl, sizeof(Ctl))) != cudaSuccess) break;
@@ -1069,7 +1212,8 @@ int b2_destroy(b2_ctx *c)
     cudaStreamSynchronize(c->stream);
     void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv, c->halo_buf, c->dd_vmax,
                     c->img, c->ref, c->mvel, c->ke_partial, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
-                    c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i};
+                    c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i, c->b8start,
+                    c->tile_base};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
@@ -1274,7 +1418,7 @@ int b2_stats(b2_ctx *c, int64_t out[B2_S_LEN])
     out[B2_S_LAUNCHES] = c->launches;
     out[B2_S_MAX_NEIGH] = c->hctl ? c->hctl->max_count : 0;
     out[B2_S_NEIGH_CAP] = c->cap;
-    out[B2_S_LIST_MODE] = c->grid.allpairs;
+    out[B2_S_LIST_MODE] = c->grid.allpairs ? 1 : (c->grid.win ? 2 : 0);
     out[B2_S_NCELLS] = (int64_t)c->grid.nc[0] * c->grid.nc[1] * c->grid.nc[2];
     return B2_OK;
 }

@@ -48,28 +48,9 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
     }
 }
 
-// One particle against its Verlet row.  Pair expressions are the oracle's:
-//   r2inv = 1/r2 ; r6inv = r2inv^3
-//   u = r6inv (c12 r6inv - c6) - ushift ;  w = r6inv (12 c12 r6inv - 6 c6) = r.F
-//   F_i += (w r2inv) d ,  d = r_i - r_j  (minimum image, particle.py:129-130; see delta())
-// The force part is branch-free (pairs beyond the cut-off contribute a zero
-// through a select).  FAST2: at most two species — the particle's row of the
-// table sits in registers and is picked with selects instead of shared loads.
-template <typename R, bool EV, bool STRESS, bool FAST2>
-__device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restrict__ pos,
-                                         const int *__restrict__ row, int cnt,
-                                         typename Pos4<R>::type pi, const Box<R> &box,
-                                         const PairTab<R> &tab, int nsp,
-                                         R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
-{
-    typedef typename Pos4<R>::type P4;
-    const int ti = ptype(pi) * nsp;
-    R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
-    if (FAST2) {
-        a12_0 = tab.c12x12[ti]; a6_0 = tab.c6x6[ti]; rc_0 = tab.rc2[ti];
-        a12_1 = tab.c12x12[ti + nsp - 1]; a6_1 = tab.c6x6[ti + nsp - 1]; rc_1 = tab.rc2[ti + nsp - 1];
-    }
-    int k = 0;
+// Body of one pair evaluation, shared by the row walkers (pair_row here, pair_row_win in
+// b2_win.cuh).  Uses the caller's pi, box, tab, ti, the register-held table row (a12_0 ...),
+// the accumulators fx fy fz pe vir st.  #undef'd at the end of b2_win.cuh.
 #define B2_PAIR(PJ)                                                                   \
     {                                                                                 \
         R dx, dy, dz;                                                                 \
@@ -116,6 +97,29 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
         }                                                                             \
         fx += fp * dx; fy += fp * dy; fz += fp * dz;                                  \
     }
+
+// One particle against its Verlet row.  Pair expressions are the oracle's:
+//   r2inv = 1/r2 ; r6inv = r2inv^3
+//   u = r6inv (c12 r6inv - c6) - ushift ;  w = r6inv (12 c12 r6inv - 6 c6) = r.F
+//   F_i += (w r2inv) d ,  d = r_i - r_j  (minimum image, particle.py:129-130; see delta())
+// The force part is branch-free (pairs beyond the cut-off contribute a zero
+// through a select).  FAST2: at most two species — the particle's row of the
+// table sits in registers and is picked with selects instead of shared loads.
+template <typename R, bool EV, bool STRESS, bool FAST2>
+__device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restrict__ pos,
+                                         const int *__restrict__ row, int cnt,
+                                         typename Pos4<R>::type pi, const Box<R> &box,
+                                         const PairTab<R> &tab, int nsp,
+                                         R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
+{
+    typedef typename Pos4<R>::type P4;
+    const int ti = ptype(pi) * nsp;
+    R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
+    if (FAST2) {
+        a12_0 = tab.c12x12[ti]; a6_0 = tab.c6x6[ti]; rc_0 = tab.rc2[ti];
+        a12_1 = tab.c12x12[ti + nsp - 1]; a6_1 = tab.c6x6[ti + nsp - 1]; rc_1 = tab.rc2[ti + nsp - 1];
+    }
+    int k = 0;
     // the deeper pipeline only where the registers are there for it: the step kernel (no energies)
     constexpr int B2_UNROLL = (sizeof(R) == 4 && !EV) ? B2_UNROLL32 : B2_UNROLL64;
 #if B2_PIPE
@@ -150,7 +154,6 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
         P4 p0 = pos[j];
         B2_PAIR(p0)
     }
-#undef B2_PAIR
 }
 
 template <typename R> struct ForceArgs {
@@ -240,6 +243,82 @@ __device__ __forceinline__ void peer_publish(unsigned long long *const *mail, in
     for (int r = 0; r < nranks; r++) *(volatile unsigned long long *)(mail[r] + off) = packed;
 }
 
+// What every block of a step kernel does after its particles moved: block maxima / sums, the
+// ticket, and - in the last block to finish - the step's bookkeeping (see k_step_nve).
+template <typename R, bool NVT, int THREADS>
+__device__ __forceinline__ void step_epilogue(const StepArgs<R> &a, Ctl *ctl, unsigned cur, float v2, double mv2)
+{
+    __shared__ float s_v2[THREADS / 32];
+    __shared__ bool s_last;
+    __shared__ double s_ke[THREADS / 32];
+    if (NVT) {
+        mv2 = warp_sum(mv2);
+        if ((threadIdx.x & 31) == 0) s_ke[threadIdx.x >> 5] = mv2;
+    }
+    v2 = warp_max(v2);
+    if ((threadIdx.x & 31) == 0) s_v2[threadIdx.x >> 5] = v2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = s_v2[0];
+        for (int w = 1; w < THREADS / 32; w++) m = fmaxf(m, s_v2[w]);
+        if (NVT) {
+            double k = 0;
+            for (int w = 0; w < THREADS / 32; w++) k += s_ke[w];
+            a.ke_partial[blockIdx.x] = k;
+        }
+        atomicMax(&ctl->vmax2_bits, __float_as_uint(m));
+        __threadfence();
+        unsigned ticket = atomicAdd(&ctl->blocks_done, 1u);
+        s_last = (ticket == gridDim.x - 1);
+        if (s_last && a.dd) {
+            __threadfence();
+            const float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
+            *a.vmax_out = vm2;
+            ctl->blocks_done = 0u;
+            if (a.vmax_mail) peer_publish(a.vmax_mail, a.nranks, a.peer_state[0] + 1u, vm2);
+        } else if (s_last) {
+            __threadfence();
+            float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
+            double bound = ctl->disp_bound + fabs((double)a.drift) * sqrt((double)vm2) * (1.0 + 1e-6);
+            ctl->disp_bound = bound;
+            ctl->cur = cur ^ 1u;
+            long long s = ctl->steps_done + 1;
+            ctl->steps_done = s;
+            if (s >= ctl->steps_target) ctl->done = 1u;
+            if (bound > ctl->half_skin) ctl->halt_rebuild = 1u;
+            ctl->blocks_done = 0u;
+        }
+    }
+    if (NVT) {
+        // the last block (every partial is visible to it after the ticket) renews the thermostat
+        __syncthreads();
+        if (s_last) {
+            double k = 0;
+            for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) k += __ldcg(a.ke_partial + b);
+            k = warp_sum(k);
+            __syncthreads();
+            if ((threadIdx.x & 31) == 0) s_ke[threadIdx.x >> 5] = k;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double tot = 0;
+                for (int w = 0; w < THREADS / 32; w++) tot += s_ke[w];
+                const double T = tot / ctl->th_ndof, dt = ctl->th_dt;
+                ctl->th_T = T;
+                if (ctl->th_kind == 0) {
+                    const double l2 = 1.0 + dt / ctl->th_tau * (ctl->th_T0 / fmax(T, 1e-300) - 1.0);
+                    ctl->th_a = ctl->th_b = sqrt(fmax(l2, 0.25));
+                } else {
+                    const double xi = ctl->th_xi + dt / (ctl->th_tau * ctl->th_tau) * (T / ctl->th_T0 - 1.0);
+                    const double h = 0.5 * xi * dt;
+                    ctl->th_xi = xi;
+                    ctl->th_a = (1.0 - h) / (1.0 + h);
+                    ctl->th_b = 1.0 / (1.0 + h);
+                }
+            }
+        }
+    }
+}
+
 // The fused velocity-Verlet step (kick-drift form): F(x) -> v += dt F/m ->
 // x += dt v -> fold into the cell (particle.py:90-99) -> max |v|^2 for the
 // displacement bound.  Reads the current position buffer, writes the other;
@@ -268,8 +347,6 @@ k_step_nve(StepArgs<R> a)
         return;
     }
     __shared__ PairTab<R> tab;
-    __shared__ float s_v2[FORCE_THREADS / 32];
-    __shared__ bool s_last;
     load_pair_table(tab);
     __syncthreads();
     const unsigned cur = ctl->cur;
@@ -310,73 +387,7 @@ k_step_nve(StepArgs<R> a)
         v2 = __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
         }
     }
-    __shared__ double s_ke[FORCE_THREADS / 32];
-    if (NVT) {
-        mv2 = warp_sum(mv2);
-        if ((threadIdx.x & 31) == 0) s_ke[threadIdx.x >> 5] = mv2;
-    }
-    v2 = warp_max(v2);
-    if ((threadIdx.x & 31) == 0) s_v2[threadIdx.x >> 5] = v2;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float m = s_v2[0];
-        for (int w = 1; w < FORCE_THREADS / 32; w++) m = fmaxf(m, s_v2[w]);
-        if (NVT) {
-            double k = 0;
-            for (int w = 0; w < FORCE_THREADS / 32; w++) k += s_ke[w];
-            a.ke_partial[blockIdx.x] = k;
-        }
-        atomicMax(&ctl->vmax2_bits, __float_as_uint(m));
-        __threadfence();
-        unsigned ticket = atomicAdd(&ctl->blocks_done, 1u);
-        s_last = (ticket == gridDim.x - 1);
-        if (s_last && a.dd) {
-            __threadfence();
-            const float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
-            *a.vmax_out = vm2;
-            ctl->blocks_done = 0u;
-            if (a.vmax_mail) peer_publish(a.vmax_mail, a.nranks, a.peer_state[0] + 1u, vm2);
-        } else if (s_last) {
-            __threadfence();
-            float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
-            double bound = ctl->disp_bound + fabs((double)a.drift) * sqrt((double)vm2) * (1.0 + 1e-6);
-            ctl->disp_bound = bound;
-            ctl->cur = cur ^ 1u;
-            long long s = ctl->steps_done + 1;
-            ctl->steps_done = s;
-            if (s >= ctl->steps_target) ctl->done = 1u;
-            if (bound > ctl->half_skin) ctl->halt_rebuild = 1u;
-            ctl->blocks_done = 0u;
-        }
-    }
-    if (NVT) {
-        // the last block (every partial is visible to it after the ticket) renews the thermostat
-        __syncthreads();
-        if (s_last) {
-            double k = 0;
-            for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) k += __ldcg(a.ke_partial + b);
-            k = warp_sum(k);
-            __syncthreads();
-            if ((threadIdx.x & 31) == 0) s_ke[threadIdx.x >> 5] = k;
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                double tot = 0;
-                for (int w = 0; w < FORCE_THREADS / 32; w++) tot += s_ke[w];
-                const double T = tot / ctl->th_ndof, dt = ctl->th_dt;
-                ctl->th_T = T;
-                if (ctl->th_kind == 0) {
-                    const double l2 = 1.0 + dt / ctl->th_tau * (ctl->th_T0 / fmax(T, 1e-300) - 1.0);
-                    ctl->th_a = ctl->th_b = sqrt(fmax(l2, 0.25));
-                } else {
-                    const double xi = ctl->th_xi + dt / (ctl->th_tau * ctl->th_tau) * (T / ctl->th_T0 - 1.0);
-                    const double h = 0.5 * xi * dt;
-                    ctl->th_xi = xi;
-                    ctl->th_a = (1.0 - h) / (1.0 + h);
-                    ctl->th_b = 1.0 / (1.0 + h);
-                }
-            }
-        }
-    }
+    step_epilogue<R, NVT, FORCE_THREADS>(a, ctl, cur, v2, mv2);
 }
 
 __global__ void k_thermostat_begin(Ctl *ctl, int kind, double T0, double tau, double dt, double ndof)

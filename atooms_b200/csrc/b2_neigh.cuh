@@ -407,14 +407,34 @@ struct ScShared {
     int first[SC_CELLS + 8];
     float4 cand[SC_CHUNK + 4];       // + 4: the test loop reads one round ahead
 };
+// windowed list (b2_win.cuh): the window layout of the block's super-block, and where each candidate
+// cell starts in it
+struct ScWindow {
+    int wP[64 + 1], wS[64];
+    int woff[SC_CELLS + 8];
+};
+
+__device__ __forceinline__ void sc_append16(bool hit, unsigned short *row, int &cnt, int cap, int off)
+{
+    unsigned short *dst = row + ((cnt >> 1) << 6) + (cnt & 1);
+    asm volatile("{\n\t.reg .pred q, s;\n\tsetp.ne.s32 q, %1, 0;\n\tsetp.lt.and.s32 s, %0, %2, q;\n\t"
+                 "@s st.global.b16 [%3], %4;\n\t@q add.s32 %0, %0, 1;\n\t}"
+                 : "+r"(cnt) : "r"((int)hit), "r"(cap), "l"(dst), "h"((unsigned short)off) : "memory");
+}
+
+// forward declarations (b2_win.cuh)
+__device__ __forceinline__ int win_layout(const Grid &g, int sx, int sy, int sz, int lane,
+                                          const int *__restrict__ b8start, int *sP, int *sS);
+__device__ __forceinline__ int win_slot_of(const int *sP, const int *sS, int off);
 
 // one block of cells (Morton code ms), one warp
-template <typename R, bool FAST2>
-__device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, const R *s_rl2, const float *s_hi, const float *s_lo,
+template <typename R, bool FAST2, bool WIN>
+__device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, ScWindow &sw, const R *s_rl2, const float *s_hi, const float *s_lo,
                                          Ctl *__restrict__ ctl, const typename Pos4<R>::type *__restrict__ pos,
                                          const Box<R> &box, const Grid &g, const int *__restrict__ cell_start,
                                          const int *__restrict__ cell_end, int *__restrict__ nbr,
-                                         int *__restrict__ nnb, int cap)
+                                         int *__restrict__ nnb, int cap,
+                                         const int *__restrict__ b8start, const int *__restrict__ tile_base)
 {
     typedef typename Pos4<R>::type P4;
     const int bx = 2 * (int)compact3(ms), by = 2 * (int)compact3(ms >> 1), bz = 2 * (int)compact3(ms >> 2);
@@ -436,6 +456,22 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
     first = __shfl_sync(0xffffffffu, first, 0);
     n_own = __shfl_sync(0xffffffffu, n_own, 0);
     if (n_own == 0) return;
+    // windowed list: entries are offsets into the window of this block's super-block
+    int W = 0, sb_first = 0, tbase = 0, self_base = 0;
+    if (WIN) {
+        const int sx = bx >> 2, sy = by >> 2, sz = bz >> 2;
+        W = win_layout(g, sx, sy, sz, lane, b8start, sw.wP, sw.wS);
+        __syncwarp();
+        sb_first = b8start[(ms >> 3) << 3];
+        tbase = tile_base[(sz * g.nsb[1] + sy) * g.nsb[0] + sx];
+        // the block's own run: B8 block ((bx & 2) + 2) / 2 ... of the window
+        const int r_own = (((((bz & 2) + 2) >> 1) * 4) + (((by & 2) + 2) >> 1)) * 4 + (((bx & 2) + 2) >> 1);
+        self_base = sw.wP[r_own] - sw.wS[r_own];      // offset of slot s = self_base + s
+        if (lane == 0) {
+            atomicMax(&ctl->win_max, (unsigned)(W + 1));
+            if (W + 1 > g.wcap || W >= 65535) ctl->overflow = 1u;
+        }
+    }
     // candidate cells: where each starts, and the running count of candidates before it
     int total = 0;
 #pragma unroll
@@ -458,6 +494,12 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
         }
         sh.prefix[q] = total + incl - l;
         sh.first[q] = s0;
+        if (WIN && q < SC_CELLS) {
+            // cells counted from the window's origin (4 sx - 2): the block starts (bx & 2) + 2 cells in
+            const int ox = (bx & 2) + q % 6, oy = (by & 2) + (q / 6) % 6, oz = (bz & 2) + q / 36;
+            const int r = ((oz >> 1) * 4 + (oy >> 1)) * 4 + (ox >> 1);
+            sw.woff[q] = sw.wP[r] + (s0 - sw.wS[r]);          // used only when the cell holds particles
+        }
         total += __shfl_sync(0xffffffffu, incl, 31);
     }
     __syncwarp();
@@ -472,7 +514,7 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
     org.d[2] = ((double)(bz + 1) / g.nc[2] - 0.5) * box.Ld[2];
     const int nsp = g_pair.nsp;
     float4 *cand = sh.cand;
-    const int *prefix = sh.prefix, *firsts = sh.first;
+    const int *prefix = sh.prefix, *firsts = sh.first, *woffs = sw.woff;
     const float4 nobody = make_float4(1e18f, 0.f, 0.f, 0.f);      // never within reach of anyone
 
     for (int b0 = 0; b0 < n_own; b0 += 32) {          // more than 32 particles in the block: again
@@ -489,6 +531,10 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
         const float *lo_row = s_lo + ti * nsp;
         const float lo0 = lo_row[0], lo1 = lo_row[nsp > 1 ? 1 : 0];
         int *row = nbr + ((size_t)(slot >> 5) * cap) * 32 + (slot & 31);
+        const int li = slot - sb_first;                   // windowed: rows live in tiles local to the super-block
+        unsigned short *row16 = reinterpret_cast<unsigned short *>(nbr) +
+                                (((size_t)(tbase + (li >> 5)) * (size_t)(cap >> 1)) * 32 + (li & 31)) * 2;
+        const int self = WIN ? self_base + slot : slot;   // the name candidates carry: window offset or slot
         int cnt = 0;
         float near = -1.f;        // > 0 once a listed pair sits inside the band around its threshold
         for (int c0 = 0; c0 < total; c0 += SC_TAKE) {
@@ -517,7 +563,8 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
                         const P4 pj = pos[j];
                         rel_to(pj, box, org, rec[t].x, rec[t].y, rec[t].z);
                         const int tj = ptype(pj);
-                        rec[t].w = __int_as_float(FAST2 ? j : (j | (tj << 28)));
+                        const int name = WIN ? woffs[c] + (f - prefix[c]) : j;
+                        rec[t].w = __int_as_float(FAST2 ? name : (name | (tj << 28)));
                         const float ex = fmaxf(fabsf(rec[t].x) - g.w[0], 0.f);
                         const float ey = fmaxf(fabsf(rec[t].y) - g.w[1], 0.f);
                         const float ez = fmaxf(fabsf(rec[t].z) - g.w[2], 0.f);
@@ -559,8 +606,9 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
                     const float dx = Q.x - px, dy = Q.y - py, dz = Q.z - pz;       \
                     const float r2 = dx * dx + dy * dy + dz * dz;                  \
                     const int j = __float_as_int(Q.w);                             \
-                    const bool hit = r2 < HI && j != slot;                         \
-                    sc_append(hit, row, cnt, cap, j);                              \
+                    const bool hit = r2 < HI && j != self;                         \
+                    if (WIN) sc_append16(hit, row16, cnt, cap, j);                 \
+                    else sc_append(hit, row, cnt, cap, j);                         \
                     FAR = fmaxf(FAR, hit ? r2 : 0.f);                              \
                 }
                 // four candidates per round, the next four already on their way from shared memory
@@ -589,8 +637,9 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
                     const int w = __float_as_int(q.w);
                     const float hi = active ? hi_row[(unsigned)w >> 28] : -1.f;
                     const int j = w & 0x0fffffff;
-                    const bool hit = r2 < hi && j != slot;
-                    sc_append(hit, row, cnt, cap, j);
+                    const bool hit = r2 < hi && j != self;
+                    if (WIN) sc_append16(hit, row16, cnt, cap, j);
+                    else sc_append(hit, row, cnt, cap, j);
                     near = fmaxf(near, hit ? r2 - lo_row[(unsigned)w >> 28] : -1.f);
                 }
             }
@@ -603,7 +652,8 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
             const int lim = min(cnt, cap);
             int kept = 0;
             for (int k = 0; k < lim; k++) {
-                const int e = row[(size_t)k * 32];
+                const int name = WIN ? (int)row16[(size_t)(k >> 1) * 64 + (k & 1)] : row[(size_t)k * 32];
+                const int e = WIN ? win_slot_of(sw.wP, sw.wS, name) : name;
                 const P4 pj = pos[e];
                 const int tj = ptype(pj);
                 float qx, qy, qz;
@@ -611,13 +661,19 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
                 const float dx = qx - px, dy = qy - py, dz = qz - pz;
                 bool keep = true;
                 if (dx * dx + dy * dy + dz * dz > lo_row[tj]) keep = r2_canon(pi, pj, box) < s_rl2[ti * nsp + tj];
-                if (keep) row[(size_t)kept++ * 32] = e;
+                if (keep) {
+                    if (WIN) row16[(size_t)(kept >> 1) * 64 + (kept & 1)] = (unsigned short)name;
+                    else row[(size_t)kept * 32] = e;
+                    kept++;
+                }
             }
             if (cnt <= cap) cnt = kept;
         }
         if (valid) {
             nnb[slot] = min(cnt, cap);
             if (cnt > cap) ctl->overflow = 1u;
+            // an odd row ends with the dummy record behind the window (cap is even)
+            if (WIN && (cnt & 1) && cnt < cap) row16[(size_t)(cnt >> 1) * 64 + 1] = (unsigned short)W;
         }
         int mx = valid ? cnt : 0;
 #pragma unroll
@@ -627,12 +683,13 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, co
 }
 
 // one warp per Morton code of a block of cells (the stride loop only matters for a smaller grid)
-template <typename R, bool FAST2>
+template <typename R, bool FAST2, bool WIN>
 __global__ void __launch_bounds__(SC_WARPS * 32, SC_MINBLK)
 k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
                 const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
                 const int *__restrict__ cell_start, const int *__restrict__ cell_end,
-                int *__restrict__ nbr, int *__restrict__ nnb, int cap)
+                int *__restrict__ nbr, int *__restrict__ nnb, int cap,
+                const int *__restrict__ b8start, const int *__restrict__ tile_base)
 {
     if (!ctl->halt_rebuild) return;
     typedef typename Pos4<R>::type P4;
@@ -640,6 +697,7 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     __shared__ R s_rl2[B2_MAXSP * B2_MAXSP];
     __shared__ float s_hi[B2_MAXSP * B2_MAXSP], s_lo[B2_MAXSP * B2_MAXSP];
     __shared__ ScShared s_warp[SC_WARPS];
+    __shared__ ScWindow s_win[WIN ? SC_WARPS : 1];
     if (threadIdx.x < B2_MAXSP * B2_MAXSP) {
         const R rl2 = rl2_of(g_pair, threadIdx.x, (R)0);
         s_rl2[threadIdx.x] = rl2;
@@ -653,8 +711,8 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t codes = 1u << (3 * g.cellbits - 3);
     for (uint32_t ms = blockIdx.x * SC_WARPS + warp; ms < codes; ms += gridDim.x * SC_WARPS) {
-        sc_block<R, FAST2>(ms, lane, s_warp[warp], s_rl2, s_hi, s_lo, ctl, pos, box, g, cell_start, cell_end,
-                           nbr, nnb, cap);
+        sc_block<R, FAST2, WIN>(ms, lane, s_warp[warp], s_win[WIN ? warp : 0], s_rl2, s_hi, s_lo, ctl, pos, box, g,
+                                cell_start, cell_end, nbr, nnb, cap, b8start, tile_base);
         __syncwarp();
     }
 }
@@ -663,6 +721,7 @@ __global__ void k_rebuild_begin(Ctl *ctl)
 {
     if (!ctl->halt_rebuild) return;
     ctl->max_count = 0u;
+    ctl->win_max = 0u;
     ctl->overflow = 0u;
 }
 

@@ -1,0 +1,444 @@
+// Windowed Verlet list: neighbour positions come from shared memory, not from L1 gathers.
+//
+// The per-lane gathers of pair_row (b2_force.cuh) touch ~26 sectors in a dozen 128-byte lines per
+// warp request and keep the L1 at 80 % of its throughput (profiles/r01_ncu_k_step_nve_fp32.txt).
+// Here the grid is cut into SUPER-BLOCKS of 4x4x4 cells (cells are r_list,max / 2 wide, so a
+// super-block is a cube of 2 r_list; its ~210 particles are 64 consecutive Morton codes, i.e. one
+// run of slots).  Every neighbour of every particle of a super-block lies in the WINDOW of 8x8x8
+// cells around it: 4x4x4 aligned 2x2x2 blocks of cells ("B8"), each of which is again one run of
+// slots.  A thread block takes one super-block, copies the 64 runs of its window into shared
+// memory with bulk asynchronous copies (cp.async.bulk, completion on an mbarrier) and walks
+// neighbour rows whose entries are 16-BIT OFFSETS INTO THE WINDOW, two per 32-bit word: the index
+// stream is half as long, and the position reads are LDS.128 instead of global gathers.
+//
+//   window order   run r = (rz * 4 + ry) * 4 + rx, B8 block (2 sx - 1 + rx, ...) wrapped
+//                  periodically; offset of slot j of run r = P[r] + (j - start[r]), P = exclusive
+//                  prefix of the run lengths.  The list build computes the same numbers.
+//   rows           tiles of 32 lanes are LOCAL to a super-block (tile_base[] = prefix over the
+//                  super-blocks of ceil(count / 32)); word k of a lane sits at
+//                  nbr32[((tile_base + t) * cap / 2 + k) * 32 + lane] = off[2k] | off[2k + 1] << 16
+//   odd counts     are padded by the build with the offset W of a DUMMY record that the kernels
+//                  place behind the window, half a box away from the super-block in every
+//                  direction: it contributes nothing, and the row walk needs no tail predicate.
+//
+// Requirements (else the context keeps the global-index list): half-width cells (m = 2), a whole
+// number of super-blocks per axis and at least two of them (setup_grid shrinks the cell count to a
+// multiple of 4), windows of fewer than 65535 particles that fit the shared memory of an SM.
+#pragma once
+#include "b2_common.cuh"
+#include "b2_force.cuh"
+
+#define WIN_RUNS 64
+#ifndef WIN_THREADS
+#define WIN_THREADS 256
+#endif
+#ifndef WIN_UNROLL32
+#define WIN_UNROLL32 3          // index WORDS in flight per lane (two neighbours each)
+#endif
+#ifndef WIN_UNROLL64
+#define WIN_UNROLL64 2
+#endif
+#ifndef WIN_MINBLK32
+#define WIN_MINBLK32 4
+#endif
+#ifndef WIN_MINBLK64
+#define WIN_MINBLK64 3
+#endif
+
+__device__ __forceinline__ int wrap_b8(int b, int nb) { return b < 0 ? b + nb : (b >= nb ? b - nb : b); }
+
+// run r of the window of super-block (sx, sy, sz): where it starts and how many slots it has
+__device__ __forceinline__ void win_run(const Grid &g, int sx, int sy, int sz, int r,
+                                        const int *__restrict__ b8start, int &start, int &len)
+{
+    const int bx = wrap_b8(2 * sx - 1 + (r & 3), 2 * g.nsb[0]);
+    const int by = wrap_b8(2 * sy - 1 + ((r >> 2) & 3), 2 * g.nsb[1]);
+    const int bz = wrap_b8(2 * sz - 1 + (r >> 4), 2 * g.nsb[2]);
+    const uint32_t code = morton3(bx, by, bz);
+    start = b8start[code];
+    len = b8start[code + 1] - start;
+}
+
+// warp-level: the 64 runs (two per lane), their exclusive prefix; returns the window size W
+__device__ __forceinline__ int win_layout(const Grid &g, int sx, int sy, int sz, int lane,
+                                          const int *__restrict__ b8start, int *sP, int *sS)
+{
+    int st0, ln0, st1, ln1;
+    win_run(g, sx, sy, sz, lane, b8start, st0, ln0);
+    win_run(g, sx, sy, sz, lane + 32, b8start, st1, ln1);
+    int i0 = ln0, i1 = ln1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v0 = __shfl_up_sync(0xffffffffu, i0, o), v1 = __shfl_up_sync(0xffffffffu, i1, o);
+        if (lane >= o) { i0 += v0; i1 += v1; }
+    }
+    const int tot0 = __shfl_sync(0xffffffffu, i0, 31);
+    sP[lane] = i0 - ln0;
+    sP[lane + 32] = tot0 + i1 - ln1;
+    sS[lane] = st0;
+    sS[lane + 32] = st1;
+    const int W = tot0 + __shfl_sync(0xffffffffu, i1, 31);
+    if (lane == 0) sP[WIN_RUNS] = W;
+    return W;
+}
+
+// slot of the window record at offset `off` (rare paths: band fix-up of the build, list export)
+__device__ __forceinline__ int win_slot_of(const int *sP, const int *sS, int off)
+{
+    int r = 0;
+#pragma unroll
+    for (int step = 32; step; step >>= 1)
+        if (r + step < WIN_RUNS && sP[r + step] <= off) r += step;
+    return sS[r] + off - sP[r];
+}
+
+// first slot of each B8 block: lower bound of its first cell key in the sorted keys
+__global__ void k_b8_bounds(const Ctl *__restrict__ ctl, const uint32_t *__restrict__ keys, int n, int ncodes,
+                            int *__restrict__ b8start)
+{
+    if (!ctl->halt_rebuild) return;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > ncodes) return;
+    const uint32_t target = (uint32_t)b << 3;
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (keys[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    b8start[b] = lo;
+}
+
+__device__ __forceinline__ void sb_coords(const Grid &g, int gi, int &sx, int &sy, int &sz)
+{
+    sx = gi % g.nsb[0];
+    sy = (gi / g.nsb[0]) % g.nsb[1];
+    sz = gi / (g.nsb[0] * g.nsb[1]);
+}
+
+// tile_base[gi] = tiles of 32 lanes before super-block gi (geometric index, x fastest)
+__global__ void __launch_bounds__(1024)
+k_sb_tiles(const Ctl *__restrict__ ctl, Grid g, const int *__restrict__ b8start, int *__restrict__ tile_base)
+{
+    if (!ctl->halt_rebuild) return;
+    __shared__ int s_w[32];
+    __shared__ int s_run;
+    const int nsb = g.nsb[0] * g.nsb[1] * g.nsb[2];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_run = 0;
+    __syncthreads();
+    for (int base = 0; base < nsb; base += 1024) {
+        const int gi = base + threadIdx.x;
+        int t = 0;
+        if (gi < nsb) {
+            int sx, sy, sz;
+            sb_coords(g, gi, sx, sy, sz);
+            const uint32_t code = morton3(sx, sy, sz);
+            t = (b8start[(code + 1) << 3] - b8start[code << 3] + 31) >> 5;
+        }
+        int incl = t;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_w[w] = incl;
+        __syncthreads();
+        if (w == 0) {
+            int v = s_w[lane], i = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, i, o);
+                if (lane >= o) i += u;
+            }
+            s_w[lane] = i - v;
+        }
+        __syncthreads();
+        const int excl = s_run + s_w[w] + incl - t;
+        if (gi < nsb) tile_base[gi] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_run = excl + t;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) tile_base[nsb] = s_run;
+}
+
+// ---- bulk asynchronous copies -----------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@!p bra WAIT_%=;\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> this block's shared memory; bytes is a multiple of 16, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// a record half a box away (in every direction) from the centre of super-block (sx, sy, sz)
+__device__ __forceinline__ int4 win_dummy(const Grid &g, const Box<float> &, int sx, int sy, int sz)
+{
+    // fixed point: u = x + 2^31 is the fraction of the box from its lower face; the centre's u IS the
+    // coordinate of the point half a box further
+    const unsigned ux = (unsigned)((((unsigned long long)(4 * sx + 2)) << 32) / (unsigned)(4 * g.nsb[0]));
+    const unsigned uy = (unsigned)((((unsigned long long)(4 * sy + 2)) << 32) / (unsigned)(4 * g.nsb[1]));
+    const unsigned uz = (unsigned)((((unsigned long long)(4 * sz + 2)) << 32) / (unsigned)(4 * g.nsb[2]));
+    return make_int4((int)ux, (int)uy, (int)uz, 0);
+}
+__device__ __forceinline__ double4 win_dummy(const Grid &g, const Box<double> &box, int sx, int sy, int sz)
+{
+    double x = (double)(4 * sx + 2) / (double)(4 * g.nsb[0]) * box.Ld[0];      // centre + L/2, from the lower face - L/2
+    double y = (double)(4 * sy + 2) / (double)(4 * g.nsb[1]) * box.Ld[1];
+    double z = (double)(4 * sz + 2) / (double)(4 * g.nsb[2]) * box.Ld[2];
+    if (x > 0.5 * box.Ld[0]) x -= box.Ld[0];
+    if (y > 0.5 * box.Ld[1]) y -= box.Ld[1];
+    if (z > 0.5 * box.Ld[2]) z -= box.Ld[2];
+    return make_double4(x, y, z, __longlong_as_double(0LL));
+}
+
+struct WinInfo { int first, cnt, tbase, W; };
+
+// Block prologue: warp 0 lays the window out and starts the copies; everybody waits for them.
+// On return the window (and the dummy behind it) is readable by every thread of the block.
+template <typename R>
+__device__ __forceinline__ WinInfo win_stage(const Grid &g, const Box<R> &box, const int *__restrict__ b8start,
+                                             const int *__restrict__ tile_base,
+                                             const typename Pos4<R>::type *__restrict__ pos,
+                                             typename Pos4<R>::type *win, int *sP, int *sS)
+{
+    typedef typename Pos4<R>::type P4;
+    __shared__ __align__(8) unsigned long long s_bar;
+    __shared__ WinInfo s_info;
+    int sx, sy, sz;
+    sb_coords(g, blockIdx.x, sx, sy, sz);
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        if (lane == 0) mbar_init(&s_bar, 1);
+        __syncwarp();
+        const int W = win_layout(g, sx, sy, sz, lane, b8start, sP, sS);
+        __syncwarp();
+        const uint32_t code = morton3(sx, sy, sz);
+        if (lane == 0) {
+            WinInfo wi;
+            wi.first = b8start[code << 3];
+            wi.cnt = b8start[(code + 1) << 3] - wi.first;
+            wi.tbase = tile_base[blockIdx.x];
+            wi.W = W;
+            s_info = wi;
+            mbar_expect_tx(&s_bar, (unsigned)W * (unsigned)sizeof(P4));
+            win[W] = win_dummy(g, box, sx, sy, sz);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int r = lane + 32 * h;
+            const int len = sP[r + 1] - sP[r];
+            if (len > 0) bulk_g2s(win + sP[r], pos + sS[r], (unsigned)len * (unsigned)sizeof(P4), &s_bar);
+        }
+    }
+    __syncthreads();
+    mbar_wait(&s_bar, 0u);
+    return s_info;
+}
+
+__device__ __forceinline__ unsigned ld_stream_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+// One particle against its row of window offsets (nw words, two neighbours each; odd counts are
+// padded with the dummy).  Pair arithmetic: B2_PAIR of b2_force.cuh, unchanged.
+template <typename R, bool EV, bool STRESS, bool FAST2>
+__device__ __forceinline__ void pair_row_win(const typename Pos4<R>::type *win, const unsigned *__restrict__ row, int nw,
+                                             typename Pos4<R>::type pi, const Box<R> &box,
+                                             const PairTab<R> &tab, int nsp,
+                                             R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
+{
+    typedef typename Pos4<R>::type P4;
+    const int ti = ptype(pi) * nsp;
+    R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
+    if (FAST2) {
+        a12_0 = tab.c12x12[ti]; a6_0 = tab.c6x6[ti]; rc_0 = tab.rc2[ti];
+        a12_1 = tab.c12x12[ti + nsp - 1]; a6_1 = tab.c6x6[ti + nsp - 1]; rc_1 = tab.rc2[ti + nsp - 1];
+    }
+    constexpr int U = (sizeof(R) == 4 && !EV) ? WIN_UNROLL32 : WIN_UNROLL64;
+    int k = 0;
+    unsigned ww[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) ww[u] = ld_stream_u32(row + (size_t)min(u, max(nw - 1, 0)) * 32);
+    for (; k + U <= nw; k += U) {
+        P4 pp[2 * U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            pp[2 * u] = win[ww[u] & 0xffffu];
+            pp[2 * u + 1] = win[ww[u] >> 16];
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) ww[u] = ld_stream_u32(row + (size_t)min(k + U + u, nw - 1) * 32);
+#pragma unroll
+        for (int u = 0; u < 2 * U; u++) B2_PAIR(pp[u])
+    }
+    for (; k < nw; k++) {
+        const unsigned w = ld_stream_u32(row + (size_t)k * 32);
+        const P4 p0 = win[w & 0xffffu], p1 = win[w >> 16];
+        B2_PAIR(p0)
+        B2_PAIR(p1)
+    }
+}
+#undef B2_PAIR
+
+template <typename R> struct WinArgs {
+    Grid g;
+    const int *b8start, *tile_base;
+    const unsigned *nbr32;
+};
+
+// The fused velocity-Verlet step of k_step_nve on the windowed list: one block per super-block.
+template <typename R, bool NVT>
+__global__ void __launch_bounds__(WIN_THREADS, (sizeof(R) == 4 ? WIN_MINBLK32 : WIN_MINBLK64))
+k_step_win(StepArgs<R> a, WinArgs<R> wa)
+{
+    typedef typename Vec4<R>::type V4;
+    typedef typename Pos4<R>::type P4;
+    extern __shared__ __align__(128) unsigned char win_raw[];
+    Ctl *ctl = a.ctl;
+    if (ctl->halt_rebuild | ctl->overflow | ctl->done) {
+        if (a.dd && blockIdx.x == 0 && threadIdx.x == 0) *a.vmax_out = 0.f;
+        return;
+    }
+    __shared__ PairTab<R> tab;
+    __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
+    load_pair_table(tab);
+    const unsigned cur = ctl->cur;
+    const P4 *__restrict__ pos = cur ? a.pos[1] : a.pos[0];
+    P4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
+    P4 *win = reinterpret_cast<P4 *>(win_raw);
+    const WinInfo wi = win_stage<R>(wa.g, a.box, wa.b8start, wa.tile_base, pos, win, sP, sS);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ntile = (wi.cnt + 31) >> 5;
+    const int nsp = g_pair.nsp;
+    const R th_a = NVT ? (R)ctl->th_a : (R)1, th_b = NVT ? (R)ctl->th_b : (R)1;
+    float v2 = 0.f;
+    double mv2 = 0.0;
+    for (int t = warp; t < ntile; t += WIN_THREADS / 32) {
+        const int li = t * 32 + lane;
+        if (li >= wi.cnt) continue;
+        const int i = wi.first + li;
+        const P4 pi = pos[i];
+        if (is_ghost(pi)) {
+            posn[i] = pi;
+            continue;
+        }
+        R fx = 0, fy = 0, fz = 0;
+        double pe = 0, vir = 0;
+        const unsigned *row = wa.nbr32 + ((size_t)(wi.tbase + t) * (size_t)(a.cap >> 1)) * 32 + lane;
+        const int nw = (a.nnb[i] + 1) >> 1;
+        if (nsp <= 2) pair_row_win<R, false, false, true>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        else pair_row_win<R, false, false, false>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        V4 v = a.vel[i];
+        R s = a.kick / v.w;
+        if (NVT) {
+            s *= th_b;
+            v.x = th_a * v.x + s * fx; v.y = th_a * v.y + s * fy; v.z = th_a * v.z + s * fz;
+            mv2 += (double)v.w * ((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+        } else {
+            v.x += s * fx; v.y += s * fy; v.z += s * fz;
+        }
+        int kx, ky, kz;
+        posn[i] = advance(pi, a.drift * v.x, a.drift * v.y, a.drift * v.z, a.box, kx, ky, kz);
+        if (kx | ky | kz) {
+            int *im = a.img + 3 * (size_t)a.orig[i];
+            im[0] += kx; im[1] += ky; im[2] += kz;
+        }
+        a.vel[i] = v;
+        v2 = fmaxf(v2, __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z));
+    }
+    step_epilogue<R, NVT, WIN_THREADS>(a, ctl, cur, v2, mv2);
+}
+
+// Forces (+ per-particle energy / virial, + stress partials) on the windowed list: k_force's twin.
+template <typename R, bool EV, bool STRESS>
+__global__ void __launch_bounds__(WIN_THREADS)
+k_force_win(ForceArgs<R> a, WinArgs<R> wa)
+{
+    typedef typename Pos4<R>::type P4;
+    extern __shared__ __align__(128) unsigned char win_raw[];
+    const Ctl *ctl = a.ctl;
+    if (a.guarded && (ctl->halt_rebuild | ctl->overflow | ctl->done)) return;
+    __shared__ PairTab<R> tab;
+    __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
+    load_pair_table(tab);
+    const P4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
+    P4 *win = reinterpret_cast<P4 *>(win_raw);
+    const WinInfo wi = win_stage<R>(wa.g, a.box, wa.b8start, wa.tile_base, pos, win, sP, sS);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ntile = (wi.cnt + 31) >> 5;
+    const int nsp = g_pair.nsp;
+    double st[6] = {0, 0, 0, 0, 0, 0};
+    for (int t = warp; t < ntile; t += WIN_THREADS / 32) {
+        const int li = t * 32 + lane;
+        if (li >= wi.cnt) continue;
+        const int i = wi.first + li;
+        const P4 pi = pos[i];
+        R fx = 0, fy = 0, fz = 0;
+        double pe = 0, vir = 0;
+        const unsigned *row = wa.nbr32 + ((size_t)(wi.tbase + t) * (size_t)(a.cap >> 1)) * 32 + lane;
+        const int nw = (a.nnb[i] + 1) >> 1;
+        if (nsp <= 2) pair_row_win<R, EV, STRESS, true>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        else pair_row_win<R, EV, STRESS, false>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
+        if (EV) a.vir[i] = (R)(0.5 * vir);
+    }
+    if (STRESS) {
+        __shared__ double s_st[WIN_THREADS / 32][6];
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+            double v = warp_sum(st[q]);
+            if (lane == 0) s_st[warp][q] = v;
+        }
+        __syncthreads();
+        if (threadIdx.x < 6) {
+            double v = 0;
+            for (int ww = 0; ww < WIN_THREADS / 32; ww++) v += s_st[ww][threadIdx.x];
+            a.partial[(size_t)blockIdx.x * 6 + threadIdx.x] = 0.5 * v;
+        }
+    }
+}
+
+// export of the windowed list in original numbering (b2_neighbors): one block per super-block
+__global__ void __launch_bounds__(WIN_THREADS)
+k_export_list_win(Grid g, const int *__restrict__ b8start, const int *__restrict__ tile_base,
+                  const unsigned short *__restrict__ nbr16, const int *__restrict__ nnb,
+                  const int *__restrict__ orig, int cap, int stride, int *__restrict__ ocount, int *__restrict__ onbr)
+{
+    __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
+    int sx, sy, sz;
+    sb_coords(g, blockIdx.x, sx, sy, sz);
+    if (threadIdx.x < 32) win_layout(g, sx, sy, sz, threadIdx.x, b8start, sP, sS);
+    __syncthreads();
+    const uint32_t code = morton3(sx, sy, sz);
+    const int first = b8start[code << 3], cnt = b8start[(code + 1) << 3] - first, tbase = tile_base[blockIdx.x];
+    for (int li = threadIdx.x; li < cnt; li += blockDim.x) {
+        const int s = first + li, o = orig[s], c = nnb[s];
+        ocount[o] = c;
+        if (!onbr) continue;
+        const unsigned short *row = nbr16 + (((size_t)(tbase + (li >> 5)) * (size_t)(cap >> 1)) * 32 + (li & 31)) * 2;
+        for (int k = 0; k < c; k++)
+            onbr[(size_t)o * stride + k] = orig[win_slot_of(sP, sS, (int)row[(size_t)(k >> 1) * 64 + (k & 1)])];
+    }
+}

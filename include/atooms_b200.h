@@ -81,7 +81,8 @@ extern "C" {
 #define B2_S_LAUNCHES    2   /* kernels launched by this library since create         */
 #define B2_S_MAX_NEIGH   3   /* largest neighbour count in the current list           */
 #define B2_S_NEIGH_CAP   4   /* slots per particle in the current list                */
-#define B2_S_LIST_MODE   5   /* 0 = cell list, 1 = all-pairs (box < 3 cells wide)     */
+#define B2_S_LIST_MODE   5   /* 0 = cell list, 1 = all-pairs (box < 3 cells wide),
+                                2 = cell list with windowed rows (CUDA engine, >= 8 cells per axis) */
 #define B2_S_NCELLS      6
 #define B2_S_LEN        16
 

@@ -76,7 +76,7 @@ def test_single_point_and_list_at_bench_shape(cuda_lib, oracle_lib, workload, pr
     assert cnt.shape == (n,) and numpy.array_equal(cnt, rcnt)
     assert nbr.shape == rnbr.shape and numpy.array_equal(nbr, rnbr)
     st = eng.stats()
-    assert st['list_mode'] == 0 and st['max_neighbors'] == int(cnt.max())
+    assert st['list_mode'] == 2 and st['max_neighbors'] == int(cnt.max())     # 2: the windowed list (b2_win.cuh)
     eng.close()
 
 
