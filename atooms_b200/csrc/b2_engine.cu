@@ -516,7 +516,7 @@ template <typename R> struct Impl {
         w.g = c->grid;
         w.b8start = c->b8start;
         w.tile_base = c->tile_base;
-        w.nbr32 = (const unsigned *)c->nbr;
+        w.nbr16 = (const unsigned short *)c->nbr;
         return w;
     }
 

@@ -51,6 +51,7 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
 // Body of one pair evaluation, shared by the row walkers (pair_row here, pair_row_win in
 // b2_win.cuh).  Uses the caller's pi, box, tab, ti, the register-held table row (a12_0 ...),
 // the accumulators fx fy fz pe vir st.  #undef'd at the end of b2_win.cuh.
+#define B2_RCP(x) r_rcp(x)
 #define B2_PAIR(PJ)                                                                   \
     {                                                                                 \
         R dx, dy, dz;                                                                 \
@@ -63,7 +64,7 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
         } else {                                                                      \
             a12 = tab.c12x12[ti + tj]; a6 = tab.c6x6[ti + tj]; rc2 = tab.rc2[ti + tj]; \
         }                                                                             \
-        R r2inv = r_rcp(r2);                                                          \
+        R r2inv = B2_RCP(r2);                                                         \
         R r6inv = r2inv * r2inv * r2inv;                                              \
         R fp = r6inv * (a12 * r6inv - a6) * r2inv;                                    \
         if (EV || STRESS) {                                                           \

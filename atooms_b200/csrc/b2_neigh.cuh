@@ -416,7 +416,7 @@ struct ScWindow {
 
 __device__ __forceinline__ void sc_append16(bool hit, unsigned short *row, int &cnt, int cap, int off)
 {
-    unsigned short *dst = row + ((cnt >> 1) << 6) + (cnt & 1);
+    unsigned short *dst = row + (size_t)cnt * 32;
     asm volatile("{\n\t.reg .pred q, s;\n\tsetp.ne.s32 q, %1, 0;\n\tsetp.lt.and.s32 s, %0, %2, q;\n\t"
                  "@s st.global.b16 [%3], %4;\n\t@q add.s32 %0, %0, 1;\n\t}"
                  : "+r"(cnt) : "r"((int)hit), "r"(cap), "l"(dst), "h"((unsigned short)off) : "memory");
@@ -468,8 +468,8 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
         const int r_own = (((((bz & 2) + 2) >> 1) * 4) + (((by & 2) + 2) >> 1)) * 4 + (((bx & 2) + 2) >> 1);
         self_base = sw.wP[r_own] - sw.wS[r_own];      // offset of slot s = self_base + s
         if (lane == 0) {
-            atomicMax(&ctl->win_max, (unsigned)(W + 1));
-            if (W + 1 > g.wcap || W >= 65535) ctl->overflow = 1u;
+            atomicMax(&ctl->win_max, (unsigned)W);
+            if (W > g.wcap || W > 65535) ctl->overflow = 1u;
         }
     }
     // candidate cells: where each starts, and the running count of candidates before it
@@ -533,7 +533,7 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
         int *row = nbr + ((size_t)(slot >> 5) * cap) * 32 + (slot & 31);
         const int li = slot - sb_first;                   // windowed: rows live in tiles local to the super-block
         unsigned short *row16 = reinterpret_cast<unsigned short *>(nbr) +
-                                (((size_t)(tbase + (li >> 5)) * (size_t)(cap >> 1)) * 32 + (li & 31)) * 2;
+                                ((size_t)(tbase + (li >> 5)) * (size_t)cap) * 32 + (li & 31);
         const int self = WIN ? self_base + slot : slot;   // the name candidates carry: window offset or slot
         int cnt = 0;
         float near = -1.f;        // > 0 once a listed pair sits inside the band around its threshold
@@ -652,7 +652,7 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
             const int lim = min(cnt, cap);
             int kept = 0;
             for (int k = 0; k < lim; k++) {
-                const int name = WIN ? (int)row16[(size_t)(k >> 1) * 64 + (k & 1)] : row[(size_t)k * 32];
+                const int name = WIN ? (int)row16[(size_t)k * 32] : row[(size_t)k * 32];
                 const int e = WIN ? win_slot_of(sw.wP, sw.wS, name) : name;
                 const P4 pj = pos[e];
                 const int tj = ptype(pj);
@@ -662,7 +662,7 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
                 bool keep = true;
                 if (dx * dx + dy * dy + dz * dz > lo_row[tj]) keep = r2_canon(pi, pj, box) < s_rl2[ti * nsp + tj];
                 if (keep) {
-                    if (WIN) row16[(size_t)(kept >> 1) * 64 + (kept & 1)] = (unsigned short)name;
+                    if (WIN) row16[(size_t)kept * 32] = (unsigned short)name;
                     else row[(size_t)kept * 32] = e;
                     kept++;
                 }
@@ -672,8 +672,6 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
         if (valid) {
             nnb[slot] = min(cnt, cap);
             if (cnt > cap) ctl->overflow = 1u;
-            // an odd row ends with the dummy record behind the window (cap is even)
-            if (WIN && (cnt & 1) && cnt < cap) row16[(size_t)(cnt >> 1) * 64 + 1] = (unsigned short)W;
         }
         int mx = valid ? cnt : 0;
 #pragma unroll

@@ -8,18 +8,18 @@
 // cells around it: 4x4x4 aligned 2x2x2 blocks of cells ("B8"), each of which is again one run of
 // slots.  A thread block takes one super-block, copies the 64 runs of its window into shared
 // memory with bulk asynchronous copies (cp.async.bulk, completion on an mbarrier) and walks
-// neighbour rows whose entries are 16-BIT OFFSETS INTO THE WINDOW, two per 32-bit word: the index
-// stream is half as long, and the position reads are LDS.128 instead of global gathers.
+// neighbour rows whose entries are 16-BIT OFFSETS INTO THE WINDOW: the index stream is half as
+// long, and the position reads are LDS.128 instead of global gathers.  The step kernel first turns
+// the staged records into coordinates RELATIVE TO THE SUPER-BLOCK'S CENTRE in the working
+// precision (one pass over the window, in place): a pair separation is then three subtractions,
+// with no minimum-image arithmetic and no integer-to-float conversion per pair.
 //
 //   window order   run r = (rz * 4 + ry) * 4 + rx, B8 block (2 sx - 1 + rx, ...) wrapped
 //                  periodically; offset of slot j of run r = P[r] + (j - start[r]), P = exclusive
 //                  prefix of the run lengths.  The list build computes the same numbers.
 //   rows           tiles of 32 lanes are LOCAL to a super-block (tile_base[] = prefix over the
-//                  super-blocks of ceil(count / 32)); word k of a lane sits at
-//                  nbr32[((tile_base + t) * cap / 2 + k) * 32 + lane] = off[2k] | off[2k + 1] << 16
-//   odd counts     are padded by the build with the offset W of a DUMMY record that the kernels
-//                  place behind the window, half a box away from the super-block in every
-//                  direction: it contributes nothing, and the row walk needs no tail predicate.
+//                  super-blocks of ceil(count / 32)); entry k of a lane sits at
+//                  nbr16[((tile_base + t) * cap + k) * 32 + lane]: a warp reads one 64-byte row per k
 //
 // Requirements (else the context keeps the global-index list): half-width cells (m = 2), a whole
 // number of super-blocks per axis and at least two of them (setup_grid shrinks the cell count to a
@@ -33,10 +33,10 @@
 #define WIN_THREADS 256
 #endif
 #ifndef WIN_UNROLL32
-#define WIN_UNROLL32 3          // index WORDS in flight per lane (two neighbours each)
+#define WIN_UNROLL32 6          // neighbours in flight per lane (index -> record -> pair arithmetic)
 #endif
 #ifndef WIN_UNROLL64
-#define WIN_UNROLL64 2
+#define WIN_UNROLL64 4
 #endif
 #ifndef WIN_MINBLK32
 #define WIN_MINBLK32 4
@@ -188,33 +188,12 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// a record half a box away (in every direction) from the centre of super-block (sx, sy, sz)
-__device__ __forceinline__ int4 win_dummy(const Grid &g, const Box<float> &, int sx, int sy, int sz)
-{
-    // fixed point: u = x + 2^31 is the fraction of the box from its lower face; the centre's u IS the
-    // coordinate of the point half a box further
-    const unsigned ux = (unsigned)((((unsigned long long)(4 * sx + 2)) << 32) / (unsigned)(4 * g.nsb[0]));
-    const unsigned uy = (unsigned)((((unsigned long long)(4 * sy + 2)) << 32) / (unsigned)(4 * g.nsb[1]));
-    const unsigned uz = (unsigned)((((unsigned long long)(4 * sz + 2)) << 32) / (unsigned)(4 * g.nsb[2]));
-    return make_int4((int)ux, (int)uy, (int)uz, 0);
-}
-__device__ __forceinline__ double4 win_dummy(const Grid &g, const Box<double> &box, int sx, int sy, int sz)
-{
-    double x = (double)(4 * sx + 2) / (double)(4 * g.nsb[0]) * box.Ld[0];      // centre + L/2, from the lower face - L/2
-    double y = (double)(4 * sy + 2) / (double)(4 * g.nsb[1]) * box.Ld[1];
-    double z = (double)(4 * sz + 2) / (double)(4 * g.nsb[2]) * box.Ld[2];
-    if (x > 0.5 * box.Ld[0]) x -= box.Ld[0];
-    if (y > 0.5 * box.Ld[1]) y -= box.Ld[1];
-    if (z > 0.5 * box.Ld[2]) z -= box.Ld[2];
-    return make_double4(x, y, z, __longlong_as_double(0LL));
-}
-
 struct WinInfo { int first, cnt, tbase, W; };
 
 // Block prologue: warp 0 lays the window out and starts the copies; everybody waits for them.
-// On return the window (and the dummy behind it) is readable by every thread of the block.
+// On return the window is readable by every thread of the block.
 template <typename R>
-__device__ __forceinline__ WinInfo win_stage(const Grid &g, const Box<R> &box, const int *__restrict__ b8start,
+__device__ __forceinline__ WinInfo win_stage(const Grid &g, const int *__restrict__ b8start,
                                              const int *__restrict__ tile_base,
                                              const typename Pos4<R>::type *__restrict__ pos,
                                              typename Pos4<R>::type *win, int *sP, int *sS)
@@ -239,7 +218,6 @@ __device__ __forceinline__ WinInfo win_stage(const Grid &g, const Box<R> &box, c
             wi.W = W;
             s_info = wi;
             mbar_expect_tx(&s_bar, (unsigned)W * (unsigned)sizeof(P4));
-            win[W] = win_dummy(g, box, sx, sy, sz);
         }
         __syncwarp();
 #pragma unroll
@@ -254,22 +232,107 @@ __device__ __forceinline__ WinInfo win_stage(const Grid &g, const Box<R> &box, c
     return s_info;
 }
 
-__device__ __forceinline__ unsigned ld_stream_u32(const unsigned *p)
+__device__ __forceinline__ unsigned ld_stream_u16(const unsigned short *p)
 {
-    unsigned v;
-    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    unsigned v;                 // zero-extended by the load itself
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
 
-// One particle against its row of window offsets (nw words, two neighbours each; odd counts are
-// padded with the dummy).  Pair arithmetic: B2_PAIR of b2_force.cuh, unchanged.
-template <typename R, bool EV, bool STRESS, bool FAST2>
-__device__ __forceinline__ void pair_row_win(const typename Pos4<R>::type *win, const unsigned *__restrict__ row, int nw,
-                                             typename Pos4<R>::type pi, const Box<R> &box,
-                                             const PairTab<R> &tab, int nsp,
+// ---- coordinates relative to the super-block's centre -----------------------------------------
+// Same size as the stored records (converted in place): (x, y, z, species bits).
+struct __align__(16) relf4 { float x, y, z; int t; };
+struct __align__(16) reld4 { double x, y, z; long long t; };
+template <typename R> struct Rel4;
+template <> struct Rel4<float>  { typedef relf4 type; };
+template <> struct Rel4<double> { typedef reld4 type; };
+
+__device__ __forceinline__ int ptype(const relf4 &p) { return p.t & 0xff; }
+__device__ __forceinline__ int ptype(const reld4 &p) { return (int)p.t & 0xff; }
+__device__ __forceinline__ void delta(const relf4 &a, const relf4 &b, const Box<float> &, float &dx, float &dy, float &dz)
+{
+    dx = a.x - b.x; dy = a.y - b.y; dz = a.z - b.z;
+}
+__device__ __forceinline__ void delta(const reld4 &a, const reld4 &b, const Box<double> &, double &dx, double &dy, double &dz)
+{
+    dx = a.x - b.x; dy = a.y - b.y; dz = a.z - b.z;
+}
+// (only to keep the observable branch of B2_PAIR well-formed: relative records are used by the step kernels, which
+// evaluate no observables)
+__device__ __forceinline__ void delta_d(const relf4 &a, const relf4 &b, const Box<float> &, double &dx, double &dy, double &dz)
+{
+    dx = (double)a.x - (double)b.x; dy = (double)a.y - (double)b.y; dz = (double)a.z - (double)b.z;
+}
+__device__ __forceinline__ void delta_d(const reld4 &a, const reld4 &b, const Box<double> &, double &dx, double &dy, double &dz)
+{
+    dx = a.x - b.x; dy = a.y - b.y; dz = a.z - b.z;
+}
+
+template <typename R> struct WinOrigin;
+template <> struct WinOrigin<float>  { unsigned u[3]; };      // fixed point, as stored
+template <> struct WinOrigin<double> { double d[3]; };
+
+// centre of super-block (sx, sy, sz)
+__device__ __forceinline__ WinOrigin<float> win_origin(const Grid &g, const Box<float> &, int sx, int sy, int sz)
+{
+    WinOrigin<float> o;
+    // u = x + 2^31 is the fraction of the box from its lower face (cell_of)
+    o.u[0] = (unsigned)((((unsigned long long)(4 * sx + 2)) << 32) / (unsigned)(4 * g.nsb[0])) - 0x80000000u;
+    o.u[1] = (unsigned)((((unsigned long long)(4 * sy + 2)) << 32) / (unsigned)(4 * g.nsb[1])) - 0x80000000u;
+    o.u[2] = (unsigned)((((unsigned long long)(4 * sz + 2)) << 32) / (unsigned)(4 * g.nsb[2])) - 0x80000000u;
+    return o;
+}
+__device__ __forceinline__ WinOrigin<double> win_origin(const Grid &g, const Box<double> &box, int sx, int sy, int sz)
+{
+    WinOrigin<double> o;
+    o.d[0] = ((double)(4 * sx + 2) / (double)(4 * g.nsb[0]) - 0.5) * box.Ld[0];
+    o.d[1] = ((double)(4 * sy + 2) / (double)(4 * g.nsb[1]) - 0.5) * box.Ld[1];
+    o.d[2] = ((double)(4 * sz + 2) / (double)(4 * g.nsb[2]) - 0.5) * box.Ld[2];
+    return o;
+}
+// the wrap-around of the fixed-point difference IS the minimum image; every record of a window lies within
+// 4 cells of the centre, far inside half a box
+__device__ __forceinline__ relf4 to_rel(const int4 &p, const WinOrigin<float> &o, const Box<float> &box)
+{
+    relf4 r;
+    r.x = (float)(int)((unsigned)p.x - o.u[0]) * box.s[0];
+    r.y = (float)(int)((unsigned)p.y - o.u[1]) * box.s[1];
+    r.z = (float)(int)((unsigned)p.z - o.u[2]) * box.s[2];
+    r.t = p.w;
+    return r;
+}
+__device__ __forceinline__ reld4 to_rel(const double4 &p, const WinOrigin<double> &o, const Box<double> &box)
+{
+    reld4 r;
+    double dx = p.x - o.d[0], dy = p.y - o.d[1], dz = p.z - o.d[2];
+    r.x = dx - box.L[0] * rint(dx * box.invL[0]);
+    r.y = dy - box.L[1] * rint(dy * box.invL[1]);
+    r.z = dz - box.L[2] * rint(dz * box.invL[2]);
+    r.t = __double_as_longlong(p.w);
+    return r;
+}
+
+// reciprocal of the step kernels in fp32: the hardware approximation alone (1 ulp; the forces of a step are never
+// reported, and the neighbour's coordinates carry a comparable rounding already).  fp64 keeps the full sequence.
+template <bool FAST> __device__ __forceinline__ float win_rcp(float x)
+{
+    if (!FAST) return r_rcp(x);
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+template <bool FAST> __device__ __forceinline__ double win_rcp(double x) { return r_rcp(x); }
+#undef B2_RCP
+#define B2_RCP(x) win_rcp<FASTRCP>(x)
+
+// One particle against its row of window offsets.  P is the record type of the window: the stored
+// positions (force kernels: exact arithmetic, observables in fp64) or relative coordinates (step
+// kernels).  Pair arithmetic: B2_PAIR of b2_force.cuh.
+template <typename R, typename P, bool EV, bool STRESS, bool FAST2, bool FASTRCP>
+__device__ __forceinline__ void pair_row_win(const P *win, const unsigned short *__restrict__ row, int cnt,
+                                             P pi, const Box<R> &box, const PairTab<R> &tab, int nsp,
                                              R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
 {
-    typedef typename Pos4<R>::type P4;
     const int ti = ptype(pi) * nsp;
     R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
     if (FAST2) {
@@ -278,34 +341,30 @@ __device__ __forceinline__ void pair_row_win(const typename Pos4<R>::type *win, 
     }
     constexpr int U = (sizeof(R) == 4 && !EV) ? WIN_UNROLL32 : WIN_UNROLL64;
     int k = 0;
-    unsigned ww[U];
+    unsigned jj[U];
 #pragma unroll
-    for (int u = 0; u < U; u++) ww[u] = ld_stream_u32(row + (size_t)min(u, max(nw - 1, 0)) * 32);
-    for (; k + U <= nw; k += U) {
-        P4 pp[2 * U];
+    for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)min(u, max(cnt - 1, 0)) * 32);
+    for (; k + U <= cnt; k += U) {
+        P pp[U];
 #pragma unroll
-        for (int u = 0; u < U; u++) {
-            pp[2 * u] = win[ww[u] & 0xffffu];
-            pp[2 * u + 1] = win[ww[u] >> 16];
-        }
+        for (int u = 0; u < U; u++) pp[u] = win[jj[u]];
 #pragma unroll
-        for (int u = 0; u < U; u++) ww[u] = ld_stream_u32(row + (size_t)min(k + U + u, nw - 1) * 32);
+        for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)min(k + U + u, cnt - 1) * 32);
 #pragma unroll
-        for (int u = 0; u < 2 * U; u++) B2_PAIR(pp[u])
+        for (int u = 0; u < U; u++) B2_PAIR(pp[u])
     }
-    for (; k < nw; k++) {
-        const unsigned w = ld_stream_u32(row + (size_t)k * 32);
-        const P4 p0 = win[w & 0xffffu], p1 = win[w >> 16];
+    for (; k < cnt; k++) {
+        const P p0 = win[ld_stream_u16(row + (size_t)k * 32)];
         B2_PAIR(p0)
-        B2_PAIR(p1)
     }
 }
 #undef B2_PAIR
+#undef B2_RCP
 
 template <typename R> struct WinArgs {
     Grid g;
     const int *b8start, *tile_base;
-    const unsigned *nbr32;
+    const unsigned short *nbr16;
 };
 
 // The fused velocity-Verlet step of k_step_nve on the windowed list: one block per super-block.
@@ -315,6 +374,8 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
 {
     typedef typename Vec4<R>::type V4;
     typedef typename Pos4<R>::type P4;
+    typedef typename Rel4<R>::type Q4;
+    static_assert(sizeof(P4) == sizeof(Q4), "relative records replace the stored ones in place");
     extern __shared__ __align__(128) unsigned char win_raw[];
     Ctl *ctl = a.ctl;
     if (ctl->halt_rebuild | ctl->overflow | ctl->done) {
@@ -328,7 +389,16 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
     const P4 *__restrict__ pos = cur ? a.pos[1] : a.pos[0];
     P4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
     P4 *win = reinterpret_cast<P4 *>(win_raw);
-    const WinInfo wi = win_stage<R>(wa.g, a.box, wa.b8start, wa.tile_base, pos, win, sP, sS);
+    Q4 *rel = reinterpret_cast<Q4 *>(win_raw);
+    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, sP, sS);
+    int sx, sy, sz;
+    sb_coords(wa.g, blockIdx.x, sx, sy, sz);
+    const WinOrigin<R> org = win_origin(wa.g, a.box, sx, sy, sz);
+    for (int k = threadIdx.x; k < wi.W; k += WIN_THREADS) {
+        const P4 p = win[k];
+        rel[k] = to_rel(p, org, a.box);          // same address, same thread
+    }
+    __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ntile = (wi.cnt + 31) >> 5;
     const int nsp = g_pair.nsp;
@@ -346,10 +416,11 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
         }
         R fx = 0, fy = 0, fz = 0;
         double pe = 0, vir = 0;
-        const unsigned *row = wa.nbr32 + ((size_t)(wi.tbase + t) * (size_t)(a.cap >> 1)) * 32 + lane;
-        const int nw = (a.nnb[i] + 1) >> 1;
-        if (nsp <= 2) pair_row_win<R, false, false, true>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
-        else pair_row_win<R, false, false, false>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        const unsigned short *row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
+        const int cnt = a.nnb[i];
+        const Q4 qi = to_rel(pi, org, a.box);
+        if (nsp <= 2) pair_row_win<R, Q4, false, false, true, true>(rel, row, cnt, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        else pair_row_win<R, Q4, false, false, false, true>(rel, row, cnt, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
         V4 v = a.vel[i];
         R s = a.kick / v.w;
         if (NVT) {
@@ -372,6 +443,7 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
 }
 
 // Forces (+ per-particle energy / virial, + stress partials) on the windowed list: k_force's twin.
+// The window keeps the stored positions: reported forces and observables use the exact arithmetic.
 template <typename R, bool EV, bool STRESS>
 __global__ void __launch_bounds__(WIN_THREADS)
 k_force_win(ForceArgs<R> a, WinArgs<R> wa)
@@ -385,7 +457,7 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
     load_pair_table(tab);
     const P4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
     P4 *win = reinterpret_cast<P4 *>(win_raw);
-    const WinInfo wi = win_stage<R>(wa.g, a.box, wa.b8start, wa.tile_base, pos, win, sP, sS);
+    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, sP, sS);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ntile = (wi.cnt + 31) >> 5;
     const int nsp = g_pair.nsp;
@@ -397,10 +469,10 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
         const P4 pi = pos[i];
         R fx = 0, fy = 0, fz = 0;
         double pe = 0, vir = 0;
-        const unsigned *row = wa.nbr32 + ((size_t)(wi.tbase + t) * (size_t)(a.cap >> 1)) * 32 + lane;
-        const int nw = (a.nnb[i] + 1) >> 1;
-        if (nsp <= 2) pair_row_win<R, EV, STRESS, true>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
-        else pair_row_win<R, EV, STRESS, false>(win, row, nw, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        const unsigned short *row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
+        const int cnt = a.nnb[i];
+        if (nsp <= 2) pair_row_win<R, P4, EV, STRESS, true, false>(win, row, cnt, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        else pair_row_win<R, P4, EV, STRESS, false, false>(win, row, cnt, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
         a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
         if (EV) a.vir[i] = (R)(0.5 * vir);
     }
@@ -437,8 +509,8 @@ k_export_list_win(Grid g, const int *__restrict__ b8start, const int *__restrict
         const int s = first + li, o = orig[s], c = nnb[s];
         ocount[o] = c;
         if (!onbr) continue;
-        const unsigned short *row = nbr16 + (((size_t)(tbase + (li >> 5)) * (size_t)(cap >> 1)) * 32 + (li & 31)) * 2;
+        const unsigned short *row = nbr16 + ((size_t)(tbase + (li >> 5)) * (size_t)cap) * 32 + (li & 31);
         for (int k = 0; k < c; k++)
-            onbr[(size_t)o * stride + k] = orig[win_slot_of(sP, sS, (int)row[(size_t)(k >> 1) * 64 + (k & 1)])];
+            onbr[(size_t)o * stride + k] = orig[win_slot_of(sP, sS, (int)row[(size_t)k * 32])];
     }
 }
