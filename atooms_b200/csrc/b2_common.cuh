@@ -68,6 +68,8 @@ struct PairConst {
     double rc2[B2_MAXSP * B2_MAXSP], ushift[B2_MAXSP * B2_MAXSP];
     double rl2_d[B2_MAXSP * B2_MAXSP];   // (rcut + skin)^2 evaluated in double
     float  rl2_f[B2_MAXSP * B2_MAXSP];   // ((float)(rcut + skin))^2 evaluated in float
+    // force coefficients as the kernels use them: 12 c12, 6 c6, rc^2 in float (the fp64 kernels multiply themselves)
+    float  f12[B2_MAXSP * B2_MAXSP], f6[B2_MAXSP * B2_MAXSP], frc2[B2_MAXSP * B2_MAXSP];
 };
 
 // single translation unit: the table is defined here, once

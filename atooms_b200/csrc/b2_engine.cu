@@ -197,6 +197,9 @@ static void rebuild_table(b2_ctx *c)
         c->pc.rl2_d[a] = rl * rl;
         float rlf = (float)rl;
         c->pc.rl2_f[a] = rlf * rlf;
+        c->pc.f12[a] = (float)(12.0 * c->pc.c12[a]);      // = what load_pair_table computes per block
+        c->pc.f6[a] = (float)(6.0 * c->pc.c6[a]);
+        c->pc.frc2[a] = (float)c->pc.rc2[a];
     }
     c->const_serial = ++g_serial;
 }
@@ -348,7 +351,7 @@ template <typename R> struct Impl {
     static size_t list_ints(const b2_ctx *c, int cap)
     {
         if (c->grid.win)      // 16-bit entries in tiles local to the super-blocks: at most one partial tile each
-            return ((size_t)cdiv(c->ncap, 32) + (size_t)c->nsb_total + 1) * (size_t)cap * 16;
+            return ((size_t)cdiv(c->ncap, 32) + (size_t)c->nsb_total + 1) * (size_t)cap * 16 + 1024;   // + slack: rows are read ahead
         return (size_t)cdiv(c->ncap, 32) * (size_t)cap * 32;
     }
 
@@ -503,12 +506,14 @@ template <typename R> struct Impl {
         a.box = make_box<R>(c);
         if (c->grid.win) {
             auto kern = k_force_win<R, EV, STRESS>;
-            LAUNCH_SMEM(kern, c->nsb_total, WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
+            LAUNCH_SMEM(kern, win_grid(c), WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
             return;
         }
         auto kern = k_force<R, EV, STRESS>;
         LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
     }
+
+    static dim3 win_grid(const b2_ctx *c) { return dim3(c->grid.nsb[0], c->grid.nsb[1], c->grid.nsb[2]); }
 
     static WinArgs<R> win_args(const b2_ctx *c)
     {
@@ -528,7 +533,7 @@ template <typename R> struct Impl {
     {
         if (c->grid.win) {
             auto kern = k_step_win<R, NVT>;
-            LAUNCH_SMEM(kern, c->nsb_total, WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
+            LAUNCH_SMEM(kern, win_grid(c), WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
         } else {
             auto kern = k_step_nve<R, NVT>;
             LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
@@ -871,7 +876,7 @@ int Impl<R>::neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, 
     int *ocount = c->stage_i, *onbr = nullptr;
     if (nbr) CU(cudaMalloc((void **)&onbr, (size_t)n * stride * sizeof(int)));
     if (c->grid.win)
-        LAUNCH(k_export_list_win, c->nsb_total, WIN_THREADS, c->grid, c->b8start, c->tile_base,
+        LAUNCH(k_export_list_win, win_grid(c), WIN_THREADS, c->grid, c->b8start, c->tile_base,
                (const unsigned short *)c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
     else
         LAUNCH(k_export_list, cdiv(n, 128), 128, (int)n, c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);

@@ -251,6 +251,9 @@ __device__ __forceinline__ void step_epilogue(const StepArgs<R> &a, Ctl *ctl, un
 {
     __shared__ float s_v2[THREADS / 32];
     __shared__ bool s_last;
+    // (the windowed kernels run on a 3-D grid of super-blocks)
+    const unsigned nblk = gridDim.x * gridDim.y * gridDim.z;
+    const unsigned bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
     __shared__ double s_ke[THREADS / 32];
     if (NVT) {
         mv2 = warp_sum(mv2);
@@ -265,12 +268,12 @@ __device__ __forceinline__ void step_epilogue(const StepArgs<R> &a, Ctl *ctl, un
         if (NVT) {
             double k = 0;
             for (int w = 0; w < THREADS / 32; w++) k += s_ke[w];
-            a.ke_partial[blockIdx.x] = k;
+            a.ke_partial[bid] = k;
         }
         atomicMax(&ctl->vmax2_bits, __float_as_uint(m));
         __threadfence();
         unsigned ticket = atomicAdd(&ctl->blocks_done, 1u);
-        s_last = (ticket == gridDim.x - 1);
+        s_last = (ticket == nblk - 1);
         if (s_last && a.dd) {
             __threadfence();
             const float vm2 = __uint_as_float(atomicExch(&ctl->vmax2_bits, 0u));
@@ -295,7 +298,7 @@ __device__ __forceinline__ void step_epilogue(const StepArgs<R> &a, Ctl *ctl, un
         __syncthreads();
         if (s_last) {
             double k = 0;
-            for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) k += __ldcg(a.ke_partial + b);
+            for (int b = threadIdx.x; b < (int)nblk; b += blockDim.x) k += __ldcg(a.ke_partial + b);
             k = warp_sum(k);
             __syncthreads();
             if ((threadIdx.x & 31) == 0) s_ke[threadIdx.x >> 5] = k;

@@ -59,11 +59,12 @@ __device__ __forceinline__ void win_run(const Grid &g, int sx, int sy, int sz, i
     len = b8start[code + 1] - start;
 }
 
-// warp-level: the 64 runs (two per lane), their exclusive prefix; returns the window size W
-__device__ __forceinline__ int win_layout(const Grid &g, int sx, int sy, int sz, int lane,
-                                          const int *__restrict__ b8start, int *sP, int *sS)
+// warp-level: the 64 runs (two per lane: r = lane and lane + 32) with their exclusive prefix, in
+// registers; returns the window size W
+__device__ __forceinline__ int win_layout_regs(const Grid &g, int sx, int sy, int sz, int lane,
+                                               const int *__restrict__ b8start,
+                                               int &p0, int &st0, int &ln0, int &p1, int &st1, int &ln1)
 {
-    int st0, ln0, st1, ln1;
     win_run(g, sx, sy, sz, lane, b8start, st0, ln0);
     win_run(g, sx, sy, sz, lane + 32, b8start, st1, ln1);
     int i0 = ln0, i1 = ln1;
@@ -73,11 +74,21 @@ __device__ __forceinline__ int win_layout(const Grid &g, int sx, int sy, int sz,
         if (lane >= o) { i0 += v0; i1 += v1; }
     }
     const int tot0 = __shfl_sync(0xffffffffu, i0, 31);
-    sP[lane] = i0 - ln0;
-    sP[lane + 32] = tot0 + i1 - ln1;
+    p0 = i0 - ln0;
+    p1 = tot0 + i1 - ln1;
+    return tot0 + __shfl_sync(0xffffffffu, i1, 31);
+}
+
+// the same, left in shared memory for look-ups by offset (list build, export)
+__device__ __forceinline__ int win_layout(const Grid &g, int sx, int sy, int sz, int lane,
+                                          const int *__restrict__ b8start, int *sP, int *sS)
+{
+    int p0, st0, ln0, p1, st1, ln1;
+    const int W = win_layout_regs(g, sx, sy, sz, lane, b8start, p0, st0, ln0, p1, st1, ln1);
+    sP[lane] = p0;
+    sP[lane + 32] = p1;
     sS[lane] = st0;
     sS[lane + 32] = st1;
-    const int W = tot0 + __shfl_sync(0xffffffffu, i1, 31);
     if (lane == 0) sP[WIN_RUNS] = W;
     return W;
 }
@@ -190,47 +201,38 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
 
 struct WinInfo { int first, cnt, tbase, W; };
 
-// Block prologue: warp 0 lays the window out and starts the copies; everybody waits for them.
-// On return the window is readable by every thread of the block.
+// Block prologue (grid = super-blocks, x fastest).  No warp waits for another: after the barrier
+// that publishes the initialised mbarrier, EVERY warp lays the window out for itself in registers
+// (4 loads per lane and two scans) and starts its share of the 64 bulk copies (run r goes to warp
+// r mod #warps).  The caller requests whatever else it needs from global memory and then calls
+// win_wait().  (With one warp doing the layout and all 64 copies, the other seven spent a third
+// of the kernel's warp-time at the hand-over barrier: profiles/r02_ncu_k_step_win_v1.txt.)
 template <typename R>
 __device__ __forceinline__ WinInfo win_stage(const Grid &g, const int *__restrict__ b8start,
                                              const int *__restrict__ tile_base,
                                              const typename Pos4<R>::type *__restrict__ pos,
-                                             typename Pos4<R>::type *win, int *sP, int *sS)
+                                             typename Pos4<R>::type *win, unsigned long long *bar)
 {
     typedef typename Pos4<R>::type P4;
-    __shared__ __align__(8) unsigned long long s_bar;
-    __shared__ WinInfo s_info;
-    int sx, sy, sz;
-    sb_coords(g, blockIdx.x, sx, sy, sz);
-    if (threadIdx.x < 32) {
-        const int lane = threadIdx.x;
-        if (lane == 0) mbar_init(&s_bar, 1);
-        __syncwarp();
-        const int W = win_layout(g, sx, sy, sz, lane, b8start, sP, sS);
-        __syncwarp();
-        const uint32_t code = morton3(sx, sy, sz);
-        if (lane == 0) {
-            WinInfo wi;
-            wi.first = b8start[code << 3];
-            wi.cnt = b8start[(code + 1) << 3] - wi.first;
-            wi.tbase = tile_base[blockIdx.x];
-            wi.W = W;
-            s_info = wi;
-            mbar_expect_tx(&s_bar, (unsigned)W * (unsigned)sizeof(P4));
-        }
-        __syncwarp();
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-            const int r = lane + 32 * h;
-            const int len = sP[r + 1] - sP[r];
-            if (len > 0) bulk_g2s(win + sP[r], pos + sS[r], (unsigned)len * (unsigned)sizeof(P4), &s_bar);
-        }
-    }
+    const int sx = blockIdx.x, sy = blockIdx.y, sz = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    if (threadIdx.x == 0) mbar_init(bar, 1);
     __syncthreads();
-    mbar_wait(&s_bar, 0u);
-    return s_info;
+    int p[2], st[2], ln[2];
+    WinInfo wi;
+    wi.W = win_layout_regs(g, sx, sy, sz, lane, b8start, p[0], st[0], ln[0], p[1], st[1], ln[1]);
+    if (threadIdx.x == 0) mbar_expect_tx(bar, (unsigned)wi.W * (unsigned)sizeof(P4));
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+        if ((lane + 32 * h) % nwarp == warp && ln[h] > 0)
+            bulk_g2s(win + p[h], pos + st[h], (unsigned)ln[h] * (unsigned)sizeof(P4), bar);
+    const uint32_t code = morton3(sx, sy, sz);
+    wi.first = b8start[code << 3];
+    wi.cnt = b8start[(code + 1) << 3] - wi.first;
+    wi.tbase = tile_base[(sz * gridDim.y + sy) * gridDim.x + sx];
+    return wi;
 }
+__device__ __forceinline__ void win_wait(unsigned long long *bar) { mbar_wait(bar, 0u); }
 
 __device__ __forceinline__ unsigned ld_stream_u16(const unsigned short *p)
 {
@@ -325,38 +327,62 @@ template <bool FAST> __device__ __forceinline__ double win_rcp(double x) { retur
 #undef B2_RCP
 #define B2_RCP(x) win_rcp<FASTRCP>(x)
 
+// coefficients of pair (a) as the force loop uses them, from the constant table
+__device__ __forceinline__ void pair_coef(int a, float &a12, float &a6, float &rc2)
+{
+    a12 = g_pair.f12[a]; a6 = g_pair.f6[a]; rc2 = g_pair.frc2[a];
+}
+__device__ __forceinline__ void pair_coef(int a, double &a12, double &a6, double &rc2)
+{
+    a12 = 12.0 * g_pair.c12[a]; a6 = 6.0 * g_pair.c6[a]; rc2 = g_pair.rc2[a];
+}
+
+template <typename R, bool EV> struct WinUnroll {
+    static constexpr int U = (sizeof(R) == 4 && !EV) ? WIN_UNROLL32 : WIN_UNROLL64;
+};
+
+// the first U entries of a row, requested ahead of use.  Reads may run up to U rows past the lane's
+// count (into the next tile's rows, or the slack behind the list): such entries are never used.
+template <int U>
+__device__ __forceinline__ void win_row_begin(const unsigned short *__restrict__ row, unsigned (&jj)[U])
+{
+#pragma unroll
+    for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)u * 32);
+}
+
 // One particle against its row of window offsets.  P is the record type of the window: the stored
 // positions (force kernels: exact arithmetic, observables in fp64) or relative coordinates (step
-// kernels).  Pair arithmetic: B2_PAIR of b2_force.cuh.
+// kernels).  `jj` holds the row's first U entries (win_row_begin).  Pair arithmetic: B2_PAIR.
 template <typename R, typename P, bool EV, bool STRESS, bool FAST2, bool FASTRCP>
 __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short *__restrict__ row, int cnt,
+                                             unsigned (&jj)[WinUnroll<R, EV>::U],
                                              P pi, const Box<R> &box, const PairTab<R> &tab, int nsp,
                                              R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
 {
+    constexpr int U = WinUnroll<R, EV>::U;
     const int ti = ptype(pi) * nsp;
     R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
     if (FAST2) {
-        a12_0 = tab.c12x12[ti]; a6_0 = tab.c6x6[ti]; rc_0 = tab.rc2[ti];
-        a12_1 = tab.c12x12[ti + nsp - 1]; a6_1 = tab.c6x6[ti + nsp - 1]; rc_1 = tab.rc2[ti + nsp - 1];
+        pair_coef(ti, a12_0, a6_0, rc_0);
+        pair_coef(ti + nsp - 1, a12_1, a6_1, rc_1);
     }
-    constexpr int U = (sizeof(R) == 4 && !EV) ? WIN_UNROLL32 : WIN_UNROLL64;
     int k = 0;
-    unsigned jj[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)min(u, max(cnt - 1, 0)) * 32);
     for (; k + U <= cnt; k += U) {
         P pp[U];
 #pragma unroll
         for (int u = 0; u < U; u++) pp[u] = win[jj[u]];
 #pragma unroll
-        for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)min(k + U + u, cnt - 1) * 32);
+        for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)(k + U + u) * 32);
 #pragma unroll
         for (int u = 0; u < U; u++) B2_PAIR(pp[u])
     }
-    for (; k < cnt; k++) {
-        const P p0 = win[ld_stream_u16(row + (size_t)k * 32)];
-        B2_PAIR(p0)
-    }
+    // fewer than U entries left: their offsets are here already
+#pragma unroll
+    for (int u = 0; u < U - 1; u++)
+        if (k + u < cnt) {
+            const P p0 = win[jj[u]];
+            B2_PAIR(p0)
+        }
 }
 #undef B2_PAIR
 #undef B2_RCP
@@ -367,7 +393,8 @@ template <typename R> struct WinArgs {
     const unsigned short *nbr16;
 };
 
-// The fused velocity-Verlet step of k_step_nve on the windowed list: one block per super-block.
+// The fused velocity-Verlet step of k_step_nve on the windowed list: one block per super-block
+// (3-D grid of super-blocks).
 template <typename R, bool NVT>
 __global__ void __launch_bounds__(WIN_THREADS, (sizeof(R) == 4 ? WIN_MINBLK32 : WIN_MINBLK64))
 k_step_win(StepArgs<R> a, WinArgs<R> wa)
@@ -375,69 +402,88 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
     typedef typename Vec4<R>::type V4;
     typedef typename Pos4<R>::type P4;
     typedef typename Rel4<R>::type Q4;
+    constexpr int U = WinUnroll<R, false>::U;
     static_assert(sizeof(P4) == sizeof(Q4), "relative records replace the stored ones in place");
     extern __shared__ __align__(128) unsigned char win_raw[];
     Ctl *ctl = a.ctl;
     if (ctl->halt_rebuild | ctl->overflow | ctl->done) {
-        if (a.dd && blockIdx.x == 0 && threadIdx.x == 0) *a.vmax_out = 0.f;
+        if (a.dd && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) *a.vmax_out = 0.f;
         return;
     }
-    __shared__ PairTab<R> tab;
-    __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
-    load_pair_table(tab);
+    __shared__ __align__(8) unsigned long long s_bar;
+    __shared__ PairTab<R> tab;                        // more than two species only
+    const int nsp = g_pair.nsp;
+    if (nsp > 2) load_pair_table(tab);
     const unsigned cur = ctl->cur;
     const P4 *__restrict__ pos = cur ? a.pos[1] : a.pos[0];
     P4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
     P4 *win = reinterpret_cast<P4 *>(win_raw);
     Q4 *rel = reinterpret_cast<Q4 *>(win_raw);
-    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, sP, sS);
-    int sx, sy, sz;
-    sb_coords(wa.g, blockIdx.x, sx, sy, sz);
-    const WinOrigin<R> org = win_origin(wa.g, a.box, sx, sy, sz);
+    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, &s_bar);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ntile = (wi.cnt + 31) >> 5;
+    // the first tile's own data, on its way while the window arrives
+    int t = warp;
+    bool valid = t < ntile && t * 32 + lane < wi.cnt;
+    int i = wi.first + t * 32 + lane;
+    const unsigned short *row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
+    P4 pi;
+    int cnt = 0;
+    unsigned jj[U];
+    if (valid) {
+        pi = pos[i];
+        cnt = a.nnb[i];
+        win_row_begin<U>(row, jj);
+    }
+    const WinOrigin<R> org = win_origin(wa.g, a.box, blockIdx.x, blockIdx.y, blockIdx.z);
+    win_wait(&s_bar);
     for (int k = threadIdx.x; k < wi.W; k += WIN_THREADS) {
         const P4 p = win[k];
         rel[k] = to_rel(p, org, a.box);          // same address, same thread
     }
     __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int ntile = (wi.cnt + 31) >> 5;
-    const int nsp = g_pair.nsp;
     const R th_a = NVT ? (R)ctl->th_a : (R)1, th_b = NVT ? (R)ctl->th_b : (R)1;
     float v2 = 0.f;
     double mv2 = 0.0;
-    for (int t = warp; t < ntile; t += WIN_THREADS / 32) {
-        const int li = t * 32 + lane;
-        if (li >= wi.cnt) continue;
-        const int i = wi.first + li;
-        const P4 pi = pos[i];
-        if (is_ghost(pi)) {
-            posn[i] = pi;
-            continue;
+    for (;;) {
+        if (valid) {
+            if (is_ghost(pi)) {
+                posn[i] = pi;
+            } else {
+                R fx = 0, fy = 0, fz = 0;
+                double pe = 0, vir = 0;
+                const Q4 qi = to_rel(pi, org, a.box);
+                if (nsp <= 2) pair_row_win<R, Q4, false, false, true, true>(rel, row, cnt, jj, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+                else pair_row_win<R, Q4, false, false, false, true>(rel, row, cnt, jj, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+                V4 v = a.vel[i];
+                R s = a.kick / v.w;
+                if (NVT) {
+                    s *= th_b;
+                    v.x = th_a * v.x + s * fx; v.y = th_a * v.y + s * fy; v.z = th_a * v.z + s * fz;
+                    mv2 += (double)v.w * ((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+                } else {
+                    v.x += s * fx; v.y += s * fy; v.z += s * fz;
+                }
+                int kx, ky, kz;
+                posn[i] = advance(pi, a.drift * v.x, a.drift * v.y, a.drift * v.z, a.box, kx, ky, kz);
+                if (kx | ky | kz) {
+                    int *im = a.img + 3 * (size_t)a.orig[i];
+                    im[0] += kx; im[1] += ky; im[2] += kz;
+                }
+                a.vel[i] = v;
+                v2 = fmaxf(v2, __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z));
+            }
         }
-        R fx = 0, fy = 0, fz = 0;
-        double pe = 0, vir = 0;
-        const unsigned short *row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
-        const int cnt = a.nnb[i];
-        const Q4 qi = to_rel(pi, org, a.box);
-        if (nsp <= 2) pair_row_win<R, Q4, false, false, true, true>(rel, row, cnt, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
-        else pair_row_win<R, Q4, false, false, false, true>(rel, row, cnt, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
-        V4 v = a.vel[i];
-        R s = a.kick / v.w;
-        if (NVT) {
-            s *= th_b;
-            v.x = th_a * v.x + s * fx; v.y = th_a * v.y + s * fy; v.z = th_a * v.z + s * fz;
-            mv2 += (double)v.w * ((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
-        } else {
-            v.x += s * fx; v.y += s * fy; v.z += s * fz;
+        t += WIN_THREADS / 32;
+        if (t >= ntile) break;
+        valid = t * 32 + lane < wi.cnt;
+        i = wi.first + t * 32 + lane;
+        row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
+        if (valid) {
+            pi = pos[i];
+            cnt = a.nnb[i];
+            win_row_begin<U>(row, jj);
         }
-        int kx, ky, kz;
-        posn[i] = advance(pi, a.drift * v.x, a.drift * v.y, a.drift * v.z, a.box, kx, ky, kz);
-        if (kx | ky | kz) {
-            int *im = a.img + 3 * (size_t)a.orig[i];
-            im[0] += kx; im[1] += ky; im[2] += kz;
-        }
-        a.vel[i] = v;
-        v2 = fmaxf(v2, __double2float_ru((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z));
     }
     step_epilogue<R, NVT, WIN_THREADS>(a, ctl, cur, v2, mv2);
 }
@@ -449,18 +495,21 @@ __global__ void __launch_bounds__(WIN_THREADS)
 k_force_win(ForceArgs<R> a, WinArgs<R> wa)
 {
     typedef typename Pos4<R>::type P4;
+    constexpr int U = WinUnroll<R, EV>::U;
     extern __shared__ __align__(128) unsigned char win_raw[];
     const Ctl *ctl = a.ctl;
     if (a.guarded && (ctl->halt_rebuild | ctl->overflow | ctl->done)) return;
+    __shared__ __align__(8) unsigned long long s_bar;
     __shared__ PairTab<R> tab;
-    __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
-    load_pair_table(tab);
+    const int nsp = g_pair.nsp;
+    if (nsp > 2) load_pair_table(tab);
     const P4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
     P4 *win = reinterpret_cast<P4 *>(win_raw);
-    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, sP, sS);
+    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, &s_bar);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ntile = (wi.cnt + 31) >> 5;
-    const int nsp = g_pair.nsp;
+    win_wait(&s_bar);
+    __syncthreads();                 // the table of the many-species path
     double st[6] = {0, 0, 0, 0, 0, 0};
     for (int t = warp; t < ntile; t += WIN_THREADS / 32) {
         const int li = t * 32 + lane;
@@ -471,8 +520,10 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
         double pe = 0, vir = 0;
         const unsigned short *row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
         const int cnt = a.nnb[i];
-        if (nsp <= 2) pair_row_win<R, P4, EV, STRESS, true, false>(win, row, cnt, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
-        else pair_row_win<R, P4, EV, STRESS, false, false>(win, row, cnt, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        unsigned jj[U];
+        win_row_begin<U>(row, jj);
+        if (nsp <= 2) pair_row_win<R, P4, EV, STRESS, true, false>(win, row, cnt, jj, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        else pair_row_win<R, P4, EV, STRESS, false, false>(win, row, cnt, jj, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
         a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
         if (EV) a.vir[i] = (R)(0.5 * vir);
     }
@@ -487,7 +538,8 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
         if (threadIdx.x < 6) {
             double v = 0;
             for (int ww = 0; ww < WIN_THREADS / 32; ww++) v += s_st[ww][threadIdx.x];
-            a.partial[(size_t)blockIdx.x * 6 + threadIdx.x] = 0.5 * v;
+            const size_t bid = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+            a.partial[bid * 6 + threadIdx.x] = 0.5 * v;
         }
     }
 }
@@ -499,12 +551,12 @@ k_export_list_win(Grid g, const int *__restrict__ b8start, const int *__restrict
                   const int *__restrict__ orig, int cap, int stride, int *__restrict__ ocount, int *__restrict__ onbr)
 {
     __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
-    int sx, sy, sz;
-    sb_coords(g, blockIdx.x, sx, sy, sz);
+    const int sx = blockIdx.x, sy = blockIdx.y, sz = blockIdx.z;
     if (threadIdx.x < 32) win_layout(g, sx, sy, sz, threadIdx.x, b8start, sP, sS);
     __syncthreads();
     const uint32_t code = morton3(sx, sy, sz);
-    const int first = b8start[code << 3], cnt = b8start[(code + 1) << 3] - first, tbase = tile_base[blockIdx.x];
+    const int first = b8start[code << 3], cnt = b8start[(code + 1) << 3] - first;
+    const int tbase = tile_base[(sz * gridDim.y + sy) * gridDim.x + sx];
     for (int li = threadIdx.x; li < cnt; li += blockDim.x) {
         const int s = first + li, o = orig[s], c = nnb[s];
         ocount[o] = c;
