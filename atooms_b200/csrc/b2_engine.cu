@@ -80,7 +80,7 @@ struct b2_ctx {
     int *nbr = nullptr, *nnb = nullptr;
     int cap = 0;
     // windowed list (b2_win.cuh)
-    int *b8start = nullptr, *tile_base = nullptr;
+    int *b8start = nullptr, *tile_base = nullptr, *sbt = nullptr;
     int nb8codes = 0, nsb_total = 0, win_tab_alloc = 0, win_sb_alloc = 0;
     bool win_off = false;            // windows do not fit: this context keeps the global-index list
     size_t smem_optin = 0;
@@ -329,6 +329,7 @@ template <typename R> struct Impl {
             }
             if (c->nsb_total + 1 > c->win_sb_alloc) {
                 if ((rc = dev_alloc(c, &c->tile_base, (size_t)c->nsb_total + 1))) return rc;
+                if ((rc = dev_alloc(c, &c->sbt, (size_t)c->nsb_total * SBT_STRIDE))) return rc;
                 c->win_sb_alloc = c->nsb_total + 1;
             }
             if ((rc = win_attributes(c))) return rc;
@@ -427,6 +428,7 @@ template <typename R> struct Impl {
             if (c->grid.win) {
                 LAUNCH(k_b8_bounds, cdiv(c->nb8codes + 1, 256), 256, c->ctl, c->keys[src], n, c->nb8codes, c->b8start);
                 LAUNCH(k_sb_tiles, 1, 1024, c->ctl, c->grid, c->b8start, c->tile_base);
+                LAUNCH(k_sb_table<R>, cdiv(c->nsb_total, 8), 256, c->ctl, c->grid, box, c->b8start, c->tile_base, c->sbt);
             }
         }
         // one warp per 2x2x2 block of cells when the grid allows it (at least 7 cells per axis: the
@@ -440,7 +442,7 @@ template <typename R> struct Impl {
             // one warp per code (a strided grid of a few blocks per SM was measured 10 % slower:
             // the valid codes are unevenly spread over the Morton range)
             LAUNCH(build, cdiv(codes, SC_WARPS), SC_WARPS * 32, c->ctl, p0, p1, n, box, c->grid,
-                   c->cell_start, c->cell_end, c->nbr, c->nnb, c->cap, c->b8start, c->tile_base);
+                   c->cell_start, c->cell_end, c->nbr, c->nnb, c->cap, c->sbt);
         } else {
             auto build = g.m == 2 ? k_build_list<R, 2> : (g.m == 1 ? k_build_list<R, 1> : k_build_list<R, 0>);
             LAUNCH(build, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
@@ -519,8 +521,7 @@ template <typename R> struct Impl {
     {
         WinArgs<R> w;
         w.g = c->grid;
-        w.b8start = c->b8start;
-        w.tile_base = c->tile_base;
+        w.sbt = c->sbt;
         w.nbr16 = (const unsigned short *)c->nbr;
         return w;
     }
@@ -876,8 +877,7 @@ int Impl<R>::neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, 
     int *ocount = c->stage_i, *onbr = nullptr;
     if (nbr) CU(cudaMalloc((void **)&onbr, (size_t)n * stride * sizeof(int)));
     if (c->grid.win)
-        LAUNCH(k_export_list_win, win_grid(c), WIN_THREADS, c->grid, c->b8start, c->tile_base,
-               (const unsigned short *)c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
+        LAUNCH(k_export_list_win, win_grid(c), WIN_THREADS, c->sbt, (const unsigned short *)c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
     else
         LAUNCH(k_export_list, cdiv(n, 128), 128, (int)n, c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
     std::vector<int32_t> hc((size_t)n);
@@ -1218,7 +1218,7 @@ int b2_destroy(b2_ctx *c)
     void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv, c->halo_buf, c->dd_vmax,
                     c->img, c->ref, c->mvel, c->ke_partial, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i, c->b8start,
-                    c->tile_base};
+                    c->tile_base, c->sbt};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);

@@ -423,8 +423,7 @@ __device__ __forceinline__ void sc_append16(bool hit, unsigned short *row, int &
 }
 
 // forward declarations (b2_win.cuh)
-__device__ __forceinline__ int win_layout(const Grid &g, int sx, int sy, int sz, int lane,
-                                          const int *__restrict__ b8start, int *sP, int *sS);
+__device__ __forceinline__ int win_layout_load(const int *__restrict__ T, int lane, int *sP, int *sS);
 __device__ __forceinline__ int win_slot_of(const int *sP, const int *sS, int off);
 
 // one block of cells (Morton code ms), one warp
@@ -434,7 +433,7 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
                                          const Box<R> &box, const Grid &g, const int *__restrict__ cell_start,
                                          const int *__restrict__ cell_end, int *__restrict__ nbr,
                                          int *__restrict__ nnb, int cap,
-                                         const int *__restrict__ b8start, const int *__restrict__ tile_base)
+                                         const int *__restrict__ sbt)
 {
     typedef typename Pos4<R>::type P4;
     const int bx = 2 * (int)compact3(ms), by = 2 * (int)compact3(ms >> 1), bz = 2 * (int)compact3(ms >> 2);
@@ -460,10 +459,11 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
     int W = 0, sb_first = 0, tbase = 0, self_base = 0;
     if (WIN) {
         const int sx = bx >> 2, sy = by >> 2, sz = bz >> 2;
-        W = win_layout(g, sx, sy, sz, lane, b8start, sw.wP, sw.wS);
+        const int *__restrict__ T = sbt + (size_t)((sz * g.nsb[1] + sy) * g.nsb[0] + sx) * (12 + 2 * 64);   // SBT_STRIDE
+        W = win_layout_load(T, lane, sw.wP, sw.wS);
         __syncwarp();
-        sb_first = b8start[(ms >> 3) << 3];
-        tbase = tile_base[(sz * g.nsb[1] + sy) * g.nsb[0] + sx];
+        sb_first = T[0];
+        tbase = T[2];
         // the block's own run: B8 block ((bx & 2) + 2) / 2 ... of the window
         const int r_own = (((((bz & 2) + 2) >> 1) * 4) + (((by & 2) + 2) >> 1)) * 4 + (((bx & 2) + 2) >> 1);
         self_base = sw.wP[r_own] - sw.wS[r_own];      // offset of slot s = self_base + s
@@ -687,7 +687,7 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
                 const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
                 const int *__restrict__ cell_start, const int *__restrict__ cell_end,
                 int *__restrict__ nbr, int *__restrict__ nnb, int cap,
-                const int *__restrict__ b8start, const int *__restrict__ tile_base)
+                const int *__restrict__ sbt)
 {
     if (!ctl->halt_rebuild) return;
     typedef typename Pos4<R>::type P4;
@@ -710,7 +710,7 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     const uint32_t codes = 1u << (3 * g.cellbits - 3);
     for (uint32_t ms = blockIdx.x * SC_WARPS + warp; ms < codes; ms += gridDim.x * SC_WARPS) {
         sc_block<R, FAST2, WIN>(ms, lane, s_warp[warp], s_win[WIN ? warp : 0], s_rl2, s_hi, s_lo, ctl, pos, box, g,
-                                cell_start, cell_end, nbr, nnb, cap, b8start, tile_base);
+                                cell_start, cell_end, nbr, nnb, cap, sbt);
         __syncwarp();
     }
 }

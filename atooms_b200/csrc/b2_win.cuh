@@ -79,16 +79,23 @@ __device__ __forceinline__ int win_layout_regs(const Grid &g, int sx, int sy, in
     return tot0 + __shfl_sync(0xffffffffu, i1, 31);
 }
 
-// the same, left in shared memory for look-ups by offset (list build, export)
-__device__ __forceinline__ int win_layout(const Grid &g, int sx, int sy, int sz, int lane,
-                                          const int *__restrict__ b8start, int *sP, int *sS)
+// Per super-block table, written once per list refresh (k_sb_table) and read by every kernel that
+// needs a window:  [0] first slot  [1] particles  [2] tile base  [3] window size W
+// [4..9] the super-block's centre in the working precision (3 fixed-point words or 3 doubles),
+// then from [SBT_HEAD] for each run r: its first slot, and (offset P of the run in the window) | (length << 16).
+#define SBT_HEAD 12
+#define SBT_STRIDE (SBT_HEAD + 2 * WIN_RUNS)
+
+// the table's runs, left in shared memory for look-ups by offset (list build, export); one warp
+__device__ __forceinline__ int win_layout_load(const int *__restrict__ T, int lane, int *sP, int *sS)
 {
-    int p0, st0, ln0, p1, st1, ln1;
-    const int W = win_layout_regs(g, sx, sy, sz, lane, b8start, p0, st0, ln0, p1, st1, ln1);
-    sP[lane] = p0;
-    sP[lane + 32] = p1;
-    sS[lane] = st0;
-    sS[lane + 32] = st1;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int r = lane + 32 * h;
+        sS[r] = T[SBT_HEAD + 2 * r];
+        sP[r] = T[SBT_HEAD + 1 + 2 * r] & 0xffff;
+    }
+    const int W = T[3];
     if (lane == 0) sP[WIN_RUNS] = W;
     return W;
 }
@@ -201,35 +208,36 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
 
 struct WinInfo { int first, cnt, tbase, W; };
 
-// Block prologue (grid = super-blocks, x fastest).  No warp waits for another: after the barrier
-// that publishes the initialised mbarrier, EVERY warp lays the window out for itself in registers
-// (4 loads per lane and two scans) and starts its share of the 64 bulk copies (run r goes to warp
-// r mod #warps).  The caller requests whatever else it needs from global memory and then calls
-// win_wait().  (With one warp doing the layout and all 64 copies, the other seven spent a third
-// of the kernel's warp-time at the hand-over barrier: profiles/r02_ncu_k_step_win_v1.txt.)
+// Block prologue (3-D grid of super-blocks).  No warp waits for another: after the barrier that
+// publishes the initialised mbarrier every warp reads the block's row of the table and starts its
+// share of the 64 bulk copies (run r goes to warp r mod #warps).  The caller requests whatever
+// else it needs from global memory and then calls win_wait().  (With one warp laying the window
+// out and issuing all 64 copies, the other seven spent a third of the kernel's warp-time at the
+// hand-over barrier; with every warp computing the layout itself, a fifth of the instructions
+// were prologue: profiles/r02_ncu_k_step_win_v1.txt, _v2.txt.)
 template <typename R>
-__device__ __forceinline__ WinInfo win_stage(const Grid &g, const int *__restrict__ b8start,
-                                             const int *__restrict__ tile_base,
+__device__ __forceinline__ WinInfo win_stage(const int *__restrict__ sbt,
                                              const typename Pos4<R>::type *__restrict__ pos,
                                              typename Pos4<R>::type *win, unsigned long long *bar)
 {
     typedef typename Pos4<R>::type P4;
-    const int sx = blockIdx.x, sy = blockIdx.y, sz = blockIdx.z;
+    const int gi = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    const int *__restrict__ T = sbt + (size_t)gi * SBT_STRIDE;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
     if (threadIdx.x == 0) mbar_init(bar, 1);
     __syncthreads();
-    int p[2], st[2], ln[2];
     WinInfo wi;
-    wi.W = win_layout_regs(g, sx, sy, sz, lane, b8start, p[0], st[0], ln[0], p[1], st[1], ln[1]);
+    wi.first = T[0];
+    wi.cnt = T[1];
+    wi.tbase = T[2];
+    wi.W = T[3];
     if (threadIdx.x == 0) mbar_expect_tx(bar, (unsigned)wi.W * (unsigned)sizeof(P4));
-#pragma unroll
-    for (int h = 0; h < 2; h++)
-        if ((lane + 32 * h) % nwarp == warp && ln[h] > 0)
-            bulk_g2s(win + p[h], pos + st[h], (unsigned)ln[h] * (unsigned)sizeof(P4), bar);
-    const uint32_t code = morton3(sx, sy, sz);
-    wi.first = b8start[code << 3];
-    wi.cnt = b8start[(code + 1) << 3] - wi.first;
-    wi.tbase = tile_base[(sz * gridDim.y + sy) * gridDim.x + sx];
+    if (lane < WIN_RUNS / nwarp) {
+        const int r = warp + nwarp * lane;
+        const int st = T[SBT_HEAD + 2 * r], pl = T[SBT_HEAD + 1 + 2 * r];
+        const int len = (int)((unsigned)pl >> 16);
+        if (len > 0) bulk_g2s(win + (pl & 0xffff), pos + st, (unsigned)len * (unsigned)sizeof(P4), bar);
+    }
     return wi;
 }
 __device__ __forceinline__ void win_wait(unsigned long long *bar) { mbar_wait(bar, 0u); }
@@ -292,6 +300,55 @@ __device__ __forceinline__ WinOrigin<double> win_origin(const Grid &g, const Box
     o.d[2] = ((double)(4 * sz + 2) / (double)(4 * g.nsb[2]) - 0.5) * box.Ld[2];
     return o;
 }
+__device__ __forceinline__ void win_origin_store(int *T, const WinOrigin<float> &o)
+{
+    T[4] = (int)o.u[0]; T[5] = (int)o.u[1]; T[6] = (int)o.u[2];
+}
+__device__ __forceinline__ void win_origin_store(int *T, const WinOrigin<double> &o)
+{
+    double *D = reinterpret_cast<double *>(T + 4);        // 8-byte aligned: SBT_STRIDE is even
+    D[0] = o.d[0]; D[1] = o.d[1]; D[2] = o.d[2];
+}
+__device__ __forceinline__ void win_origin_load(const int *__restrict__ T, WinOrigin<float> &o)
+{
+    o.u[0] = (unsigned)T[4]; o.u[1] = (unsigned)T[5]; o.u[2] = (unsigned)T[6];
+}
+__device__ __forceinline__ void win_origin_load(const int *__restrict__ T, WinOrigin<double> &o)
+{
+    const double *D = reinterpret_cast<const double *>(T + 4);
+    o.d[0] = D[0]; o.d[1] = D[1]; o.d[2] = D[2];
+}
+
+// one warp per super-block: its row of the table
+template <typename R>
+__global__ void __launch_bounds__(256)
+k_sb_table(const Ctl *__restrict__ ctl, Grid g, Box<R> box, const int *__restrict__ b8start,
+           const int *__restrict__ tile_base, int *__restrict__ sbt)
+{
+    if (!ctl->halt_rebuild) return;
+    const int lane = threadIdx.x & 31;
+    const int gi = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (gi >= g.nsb[0] * g.nsb[1] * g.nsb[2]) return;
+    int sx, sy, sz;
+    sb_coords(g, gi, sx, sy, sz);
+    int p0, st0, ln0, p1, st1, ln1;
+    const int W = win_layout_regs(g, sx, sy, sz, lane, b8start, p0, st0, ln0, p1, st1, ln1);
+    int *T = sbt + (size_t)gi * SBT_STRIDE;
+    T[SBT_HEAD + 2 * lane] = st0;
+    T[SBT_HEAD + 1 + 2 * lane] = (p0 & 0xffff) | (ln0 << 16);
+    T[SBT_HEAD + 2 * (lane + 32)] = st1;
+    T[SBT_HEAD + 1 + 2 * (lane + 32)] = (p1 & 0xffff) | (ln1 << 16);
+    if (lane == 0) {
+        const uint32_t code = morton3(sx, sy, sz);
+        const int first = b8start[code << 3];
+        T[0] = first;
+        T[1] = b8start[(code + 1) << 3] - first;
+        T[2] = tile_base[gi];
+        T[3] = W;
+        win_origin_store(T, win_origin(g, box, sx, sy, sz));
+    }
+}
+
 // the wrap-around of the fixed-point difference IS the minimum image; every record of a window lies within
 // 4 cells of the centre, far inside half a box
 __device__ __forceinline__ relf4 to_rel(const int4 &p, const WinOrigin<float> &o, const Box<float> &box)
@@ -389,7 +446,7 @@ __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short 
 
 template <typename R> struct WinArgs {
     Grid g;
-    const int *b8start, *tile_base;
+    const int *sbt;
     const unsigned short *nbr16;
 };
 
@@ -419,7 +476,7 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
     P4 *__restrict__ posn = cur ? a.pos[0] : a.pos[1];
     P4 *win = reinterpret_cast<P4 *>(win_raw);
     Q4 *rel = reinterpret_cast<Q4 *>(win_raw);
-    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, &s_bar);
+    const WinInfo wi = win_stage<R>(wa.sbt, pos, win, &s_bar);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ntile = (wi.cnt + 31) >> 5;
     // the first tile's own data, on its way while the window arrives
@@ -435,7 +492,8 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
         cnt = a.nnb[i];
         win_row_begin<U>(row, jj);
     }
-    const WinOrigin<R> org = win_origin(wa.g, a.box, blockIdx.x, blockIdx.y, blockIdx.z);
+    WinOrigin<R> org;
+    win_origin_load(wa.sbt + (size_t)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * SBT_STRIDE, org);
     win_wait(&s_bar);
     for (int k = threadIdx.x; k < wi.W; k += WIN_THREADS) {
         const P4 p = win[k];
@@ -505,7 +563,7 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
     if (nsp > 2) load_pair_table(tab);
     const P4 *__restrict__ pos = ctl->cur ? a.pos[1] : a.pos[0];
     P4 *win = reinterpret_cast<P4 *>(win_raw);
-    const WinInfo wi = win_stage<R>(wa.g, wa.b8start, wa.tile_base, pos, win, &s_bar);
+    const WinInfo wi = win_stage<R>(wa.sbt, pos, win, &s_bar);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ntile = (wi.cnt + 31) >> 5;
     win_wait(&s_bar);
@@ -546,17 +604,15 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
 
 // export of the windowed list in original numbering (b2_neighbors): one block per super-block
 __global__ void __launch_bounds__(WIN_THREADS)
-k_export_list_win(Grid g, const int *__restrict__ b8start, const int *__restrict__ tile_base,
-                  const unsigned short *__restrict__ nbr16, const int *__restrict__ nnb,
+k_export_list_win(const int *__restrict__ sbt, const unsigned short *__restrict__ nbr16, const int *__restrict__ nnb,
                   const int *__restrict__ orig, int cap, int stride, int *__restrict__ ocount, int *__restrict__ onbr)
 {
     __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
-    const int sx = blockIdx.x, sy = blockIdx.y, sz = blockIdx.z;
-    if (threadIdx.x < 32) win_layout(g, sx, sy, sz, threadIdx.x, b8start, sP, sS);
+    const int gi = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    const int *__restrict__ T = sbt + (size_t)gi * SBT_STRIDE;
+    if (threadIdx.x < 32) win_layout_load(T, threadIdx.x, sP, sS);
     __syncthreads();
-    const uint32_t code = morton3(sx, sy, sz);
-    const int first = b8start[code << 3], cnt = b8start[(code + 1) << 3] - first;
-    const int tbase = tile_base[(sz * gridDim.y + sy) * gridDim.x + sx];
+    const int first = T[0], cnt = T[1], tbase = T[2];
     for (int li = threadIdx.x; li < cnt; li += blockDim.x) {
         const int s = first + li, o = orig[s], c = nnb[s];
         ocount[o] = c;
