@@ -263,9 +263,9 @@ struct Grid {
     int m;             // cells are (r_list,max / m) wide; the stencil reaches m cells (1 or 2)
     float w[3];        // cell widths
     float reach2;      // (r_list,max)^2, padded: cells farther than this cannot hold a neighbour
-    // windowed list (b2_win.cuh): the grid is a whole number of 4x4x4-cell super-blocks per axis
+    // windowed list (b2_win.cuh): an even number of cells per axis, in super-blocks of 4x4x4 cells
     int win;           // 1: list entries are 16-bit offsets into the super-block's candidate window
-    int nsb[3];        // super-blocks per axis (nc / 4)
+    int nsb[3];        // super-blocks per axis (ceil(nc / 4), nc even)
     int wcap;          // records a window may hold, the dummy included (shared memory of the step kernel)
 };
 

@@ -279,27 +279,27 @@ template <typename R> struct Impl {
             mx = std::max(mx, g.nc[d]);
             g.w[d] = (float)(c->side[d] / g.nc[d]);
         }
-        // windowed list (b2_win.cuh): a whole number (>= 2) of 4x4x4-cell super-blocks per axis; the cells
-        // grow by at most 3 / nc to make it so.  B2_LIST_GLOBAL=1 keeps the global-index list (A/B timing).
+        // windowed list (b2_win.cuh): an even number (>= 8) of cells per axis, cut into super-blocks of 4 (the
+        // last one of an axis may hold 2); the cells grow by at most 1 / nc to make it so.  B2_LIST_GLOBAL=1 keeps the global-index list (A/B timing).
         static const bool force_global = getenv("B2_LIST_GLOBAL") && atoi(getenv("B2_LIST_GLOBAL")) != 0;
         g.win = 0;
         g.nsb[0] = g.nsb[1] = g.nsb[2] = 0;
         if (!g.allpairs && g.m == 2 && !c->win_off && !force_global && g.nc[0] >= 8 && g.nc[1] >= 8 && g.nc[2] >= 8) {
             double cellvol = 1.0;
-            for (int d = 0; d < 3; d++) cellvol *= c->side[d] / (g.nc[d] / 4 * 4);
+            for (int d = 0; d < 3; d++) cellvol *= c->side[d] / (g.nc[d] & ~1);
             // records of a window (8^3 cells) at the mean density, with room for fluctuations; a slab of a
             // decomposed system is denser than its global mean: the first build reports what it needs
             const double expect = (double)c->n / (c->side[0] * c->side[1] * c->side[2]) * 512.0 * cellvol;
             int wcap = std::max(g.wcap, ((int)(1.25 * expect) + 128 + 7) / 8 * 8);
             const size_t rec = c->precision == B2_FP32 ? 16 : 32;
             const size_t lim = std::min<size_t>((c->smem_optin > 4096 ? c->smem_optin - 4096 : 0) / rec, 65528);
-            const size_t nsbt = (size_t)(g.nc[0] / 4) * (g.nc[1] / 4) * (g.nc[2] / 4);
+            const size_t nsbt = (size_t)((g.nc[0] + 3) / 4) * ((g.nc[1] + 3) / 4) * ((g.nc[2] + 3) / 4);
             if ((size_t)wcap <= lim && nsbt <= (size_t)c->ncap / 8 + 64) {
                 g.win = 1;
                 g.wcap = wcap;
                 for (int d = 0; d < 3; d++) {
-                    g.nc[d] = g.nc[d] / 4 * 4;
-                    g.nsb[d] = g.nc[d] / 4;
+                    g.nc[d] &= ~1;
+                    g.nsb[d] = (g.nc[d] + 3) / 4;
                 }
                 mx = 1;
                 for (int d = 0; d < 3; d++) {

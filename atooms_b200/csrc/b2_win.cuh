@@ -21,9 +21,10 @@
 //                  super-blocks of ceil(count / 32)); entry k of a lane sits at
 //                  nbr16[((tile_base + t) * cap + k) * 32 + lane]: a warp reads one 64-byte row per k
 //
-// Requirements (else the context keeps the global-index list): half-width cells (m = 2), a whole
-// number of super-blocks per axis and at least two of them (setup_grid shrinks the cell count to a
-// multiple of 4), windows of fewer than 65535 particles that fit the shared memory of an SM.
+// Requirements (else the context keeps the global-index list): half-width cells (m = 2), an EVEN
+// number of cells per axis, at least 8 (setup_grid drops one cell where needed; the last super-
+// block of an axis may then be two cells wide, its window wraps onto the first B8 blocks),
+// windows of fewer than 65535 particles that fit the shared memory of an SM.
 #pragma once
 #include "b2_common.cuh"
 #include "b2_force.cuh"
@@ -51,9 +52,9 @@ __device__ __forceinline__ int wrap_b8(int b, int nb) { return b < 0 ? b + nb : 
 __device__ __forceinline__ void win_run(const Grid &g, int sx, int sy, int sz, int r,
                                         const int *__restrict__ b8start, int &start, int &len)
 {
-    const int bx = wrap_b8(2 * sx - 1 + (r & 3), 2 * g.nsb[0]);
-    const int by = wrap_b8(2 * sy - 1 + ((r >> 2) & 3), 2 * g.nsb[1]);
-    const int bz = wrap_b8(2 * sz - 1 + (r >> 4), 2 * g.nsb[2]);
+    const int bx = wrap_b8(2 * sx - 1 + (r & 3), g.nc[0] >> 1);
+    const int by = wrap_b8(2 * sy - 1 + ((r >> 2) & 3), g.nc[1] >> 1);
+    const int bz = wrap_b8(2 * sz - 1 + (r >> 4), g.nc[2] >> 1);
     const uint32_t code = morton3(bx, by, bz);
     start = b8start[code];
     len = b8start[code + 1] - start;
@@ -287,17 +288,17 @@ __device__ __forceinline__ WinOrigin<float> win_origin(const Grid &g, const Box<
 {
     WinOrigin<float> o;
     // u = x + 2^31 is the fraction of the box from its lower face (cell_of)
-    o.u[0] = (unsigned)((((unsigned long long)(4 * sx + 2)) << 32) / (unsigned)(4 * g.nsb[0])) - 0x80000000u;
-    o.u[1] = (unsigned)((((unsigned long long)(4 * sy + 2)) << 32) / (unsigned)(4 * g.nsb[1])) - 0x80000000u;
-    o.u[2] = (unsigned)((((unsigned long long)(4 * sz + 2)) << 32) / (unsigned)(4 * g.nsb[2])) - 0x80000000u;
+    o.u[0] = (unsigned)((((unsigned long long)(4 * sx + 2)) << 32) / (unsigned)g.nc[0]) - 0x80000000u;
+    o.u[1] = (unsigned)((((unsigned long long)(4 * sy + 2)) << 32) / (unsigned)g.nc[1]) - 0x80000000u;
+    o.u[2] = (unsigned)((((unsigned long long)(4 * sz + 2)) << 32) / (unsigned)g.nc[2]) - 0x80000000u;
     return o;
 }
 __device__ __forceinline__ WinOrigin<double> win_origin(const Grid &g, const Box<double> &box, int sx, int sy, int sz)
 {
     WinOrigin<double> o;
-    o.d[0] = ((double)(4 * sx + 2) / (double)(4 * g.nsb[0]) - 0.5) * box.Ld[0];
-    o.d[1] = ((double)(4 * sy + 2) / (double)(4 * g.nsb[1]) - 0.5) * box.Ld[1];
-    o.d[2] = ((double)(4 * sz + 2) / (double)(4 * g.nsb[2]) - 0.5) * box.Ld[2];
+    o.d[0] = ((double)(4 * sx + 2) / (double)g.nc[0] - 0.5) * box.Ld[0];
+    o.d[1] = ((double)(4 * sy + 2) / (double)g.nc[1] - 0.5) * box.Ld[1];
+    o.d[2] = ((double)(4 * sz + 2) / (double)g.nc[2] - 0.5) * box.Ld[2];
     return o;
 }
 __device__ __forceinline__ void win_origin_store(int *T, const WinOrigin<float> &o)
@@ -427,7 +428,11 @@ __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short 
     for (; k + U <= cnt; k += U) {
         P pp[U];
 #pragma unroll
+#ifdef WIN_EXPERIMENT_NO_CONFLICT      // timing experiment only (wrong physics): what would conflict-free reads buy?
+        for (int u = 0; u < U; u++) pp[u] = win[(jj[u] & ~7u) | (threadIdx.x & 7u)];
+#else
         for (int u = 0; u < U; u++) pp[u] = win[jj[u]];
+#endif
 #pragma unroll
         for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)(k + U + u) * 32);
 #pragma unroll

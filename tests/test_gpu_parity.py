@@ -103,8 +103,9 @@ def test_single_point_replicated(cuda_lib, oracle_lib, precision):
     ref = make_engine(oracle_lib, d, ka, 64).compute(per_particle=True, stress=True)
     assert_observables(got, ref, precision)
     st = eng.stats()
-    # half-width cells (r_list / 2), a whole number of 4-cell super-blocks per axis: the windowed list
-    assert st['list_mode'] == 2 and st['ncells'] == 12 ** 3
+    # half-width cells (r_list / 2), an even number per axis (here 14 = 3 super-blocks of 4 and one of 2):
+    # the windowed list
+    assert st['list_mode'] == 2 and st['ncells'] == 14 ** 3
 
 
 @pytest.mark.parametrize('precision', [64, 32])
