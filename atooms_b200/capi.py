@@ -63,6 +63,8 @@ SYMBOLS = {
     'b2_last_timing': (_int, [_vp, _c_dp, _c_lp]),
     'b2_set_profile': (_int, [_vp, _int]),
     'b2_profile': (_int, [_vp, _c_dp]),
+    'b2_host_alloc': (_int, [ctypes.POINTER(_vp), _i64]),
+    'b2_host_free': (_int, [_vp]),
     'b2_kinetic_static': (_int, [_vp, _i64, _int, _vp, _vp]),
     'b2_upload_device': (_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
     'b2_download_device': (_int, [_vp, _vp, _vp, _vp]),
@@ -137,6 +139,19 @@ class Library(object):
         if version != ABI_VERSION:
             raise OSError('atooms_b200: %s has ABI version %d, expected %d' % (path, version, ABI_VERSION))
         self.name = self.dll.b2_backend_name().decode()
+
+    def host_empty(self, shape, dtype=numpy.float64):
+        """A numpy array in page-locked host memory (b2_host_alloc), freed with the array: host
+        mirrors in such memory are copied to and from the device by DMA, asynchronously."""
+        import weakref
+        shape = tuple(int(x) for x in (shape if hasattr(shape, '__len__') else (shape,)))
+        nbytes = int(numpy.prod(shape, dtype=numpy.int64)) * numpy.dtype(dtype).itemsize
+        ptr = _vp()
+        self.check(self.dll.b2_host_alloc(ctypes.byref(ptr), nbytes))
+        buf = (ctypes.c_char * max(nbytes, 1)).from_address(ptr.value)
+        arr = numpy.frombuffer(buf, dtype=dtype, count=int(numpy.prod(shape, dtype=numpy.int64))).reshape(shape)
+        weakref.finalize(buf, self.dll.b2_host_free, ptr.value)    # buf lives as long as any view of it
+        return arr
 
     def check(self, code, handle=None):
         if code == 0:

@@ -1513,6 +1513,21 @@ int b2_dd_unpack(b2_ctx *c, int64_t first_id, int64_t n, const double *in_dev)
     return DISPATCH(dd_unpack, c, first_id, n, in_dev);
 }
 
+int b2_host_alloc(void **out, int64_t bytes)
+{
+    if (!out || bytes < 0) return fail(nullptr, B2_EINVAL, "b2_host_alloc: bad argument");
+    *out = nullptr;
+    cudaError_t e = cudaMallocHost(out, (size_t)std::max<int64_t>(bytes, 1));
+    if (e != cudaSuccess) return fail(nullptr, B2_ENOMEM, "b2_host_alloc: %s", cudaGetErrorString(e));
+    return B2_OK;
+}
+
+int b2_host_free(void *ptr)
+{
+    if (ptr) cudaFreeHost(ptr);
+    return B2_OK;
+}
+
 int b2_set_profile(b2_ctx *c, int on)
 {
     if (!c) return fail(nullptr, B2_EINVAL, "NULL context");

@@ -428,10 +428,14 @@ __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short 
     for (; k + U <= cnt; k += U) {
         P pp[U];
 #pragma unroll
-#ifdef WIN_EXPERIMENT_NO_CONFLICT      // timing experiment only (wrong physics): what would conflict-free reads buy?
-        for (int u = 0; u < U; u++) pp[u] = win[(jj[u] & ~7u) | (threadIdx.x & 7u)];
-#else
         for (int u = 0; u < U; u++) pp[u] = win[jj[u]];
+#ifdef WIN_EXPERIMENT_DOUBLE_LDS       // timing experiment only (same physics): every record is read twice
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            unsigned d0, d1, d2, d3;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(d0), "=r"(d1), "=r"(d2), "=r"(d3)
+                         : "r"(smem_u32(win + jj[u])));
+        }
 #endif
 #pragma unroll
         for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)(k + U + u) * 32);

@@ -143,11 +143,16 @@ class System(object):
         if position.ndim != 2 or position.shape[1] != 3:
             raise ValueError('position must be (N, 3); only three dimensions are supported')
         n = position.shape[0]
-        self._pos = numpy.ascontiguousarray(position)
-        self._vel = numpy.zeros((n, 3)) if velocity is None else numpy.array(velocity, dtype=numpy.float64)
+        # host mirrors in page-locked memory: the push / pull around run() with views handed out is DMA
+        lib = library if library is not None else capi.load()
+        self._pos = lib.host_empty((n, 3))
+        self._pos[:] = position
+        self._vel = lib.host_empty((n, 3))
+        self._vel[:] = 0.0 if velocity is None else numpy.asarray(velocity, dtype=numpy.float64)
         self._mass = numpy.ones(n) if mass is None else numpy.array(mass, dtype=numpy.float64)
         self._radius = numpy.full(n, 0.5) if radius is None else numpy.array(radius, dtype=numpy.float64)
-        self._img = numpy.zeros((n, 3), dtype=numpy.int32)
+        self._img = lib.host_empty((n, 3), numpy.int32)
+        self._img[:] = 0
         self.cell = cell if hasattr(cell, 'side') else Cell(cell)
         self.model = models.get(model)
         # species names -> 0-based ids in table order
@@ -339,12 +344,25 @@ class System(object):
         self._engine.scale_velocities(factor)
         self._advanced()
 
+    # properties, as in the reference (system.py:361-369)
+    @property
     def cm_velocity(self):
         t = self._get_thermo()
         return t['momentum'] / t['mass']
 
+    @property
+    def cm_position(self):
+        """Mass-weighted mean of the (folded) positions, system.py:350-369."""
+        self._pull()
+        return (self._mass[:, None] * self._pos).sum(axis=0) / self._mass.sum()
+
+    def cm(self, what):
+        if what not in ('position', 'velocity'):
+            raise ValueError('cm of %r is not defined for the array-backed system' % what)
+        return self.cm_position if what == 'position' else self.cm_velocity
+
     def fix_momentum(self):
-        vcm = self.cm_velocity()
+        vcm = self.cm_velocity
         self._pull()
         self._vel -= vcm
         self._host_vel_dirty = True
@@ -460,8 +478,17 @@ class System(object):
                      precision=self.precision, skin=self._skin(), device=self._engine.device,
                      library=self._engine.lib)
         new.thermostat = copy.deepcopy(self.thermostat, memo)
+        new.barostat = copy.deepcopy(self.barostat, memo)
+        new.reservoir = copy.deepcopy(self.reservoir, memo)
+        new._img[:] = self._img
         if self.interaction is not None:
-            new.interaction = self.interaction.__class__(self.model)
+            it = self.interaction
+            # same engine settings as the original, not the defaults
+            new.interaction = it.__class__(self.model, precision=getattr(it, 'precision', self.precision),
+                                           skin=getattr(it, 'skin', self._skin()),
+                                           device=getattr(it, 'device', self._engine.device),
+                                           species=getattr(it, 'species', None),
+                                           library=getattr(it, '_library', None) or self._engine.lib)
         return new
 
     def _skin(self):

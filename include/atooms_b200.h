@@ -315,6 +315,15 @@ int b2_batch_get_state(b2_batch *batch, double *vel, int32_t *image);
 int b2_set_profile(b2_ctx *ctx, int on);
 int b2_profile(b2_ctx *ctx, double out[8]);
 
+/* Host buffers the engine can copy to and from at full PCIe / C2C speed (page-locked memory).
+ * The reference's System marshals through ordinary numpy arrays (atooms/system/system.py:398-530);
+ * the array-backed System of this package keeps its host mirrors of position / velocity in such
+ * buffers, so that the push before and the pull after every backend.run(n) with views handed out
+ * (docs/simulations.org:302-308) are asynchronous DMA transfers.  b2_upload / b2_update /
+ * b2_download accept any host pointer; these only make them faster.                          */
+int b2_host_alloc(void **out, int64_t bytes);
+int b2_host_free(void *ptr);
+
 /* No counterpart in the reference.  Kinetic energy, total momentum and total
  * mass of n particles straight from a caller-owned DEVICE array, without a
  * context and without allocating anything: for hosts whose own allocator owns

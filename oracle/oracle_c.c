@@ -806,6 +806,14 @@ int b2_last_timing(b2_ctx *c, double *ms, int64_t *launches)
     return B2_OK;
 }
 
+int b2_host_alloc(void **out, int64_t bytes)
+{
+    if (!out || bytes < 0) return fail(NULL, B2_EINVAL, "b2_host_alloc: bad argument");
+    *out = malloc((size_t)(bytes > 0 ? bytes : 1));
+    return *out ? B2_OK : fail(NULL, B2_ENOMEM, "b2_host_alloc: out of memory");
+}
+int b2_host_free(void *ptr) { free(ptr); return B2_OK; }
+
 int b2_set_profile(b2_ctx *c, int on) { (void)c; (void)on; return B2_OK; }
 
 int b2_profile(b2_ctx *c, double out[8])

@@ -160,7 +160,8 @@ def test_sync_contract(oracle_lib):
     # velocities: set_temperature hits the target exactly, scale_velocities runs on the device
     s.set_temperature(1.5, seed=1)
     assert abs(s.temperature - 1.5) < 1e-10
-    assert numpy.abs(s.cm_velocity()).max() < 1e-12
+    assert numpy.abs(s.cm_velocity).max() < 1e-12      # a property, as in the reference (system.py:361-364)
+    assert numpy.allclose(s.cm_position, (s.mass[:, None] * s.dump('position')).sum(axis=0) / s.mass.sum())
     s.scale_velocities(2.0)
     assert abs(s.temperature - 6.0) < 1e-9
     assert abs(numpy.sum(s.dump('velocity') ** 2) / (3 * 255) - 6.0) < 1e-9
