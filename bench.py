@@ -19,9 +19,12 @@ After the timed region the N-rank run is checked against a single-domain run of
 the same engine (`parity` block of the JSON line); out of tolerance => rc != 0.
 
 value : device-resident throughput (CUDA events on the launching stream).
-e2e   : the same chunk through the C ABI with HOST buffers: positions and
-        velocities are pushed from pinned host memory before, and pulled
-        back (plus the thermodynamic scalars) after every chunk.
+e2e   : the same metric through the plugin, as a user of the reference runs it:
+        atooms.simulation.Simulation(B200(System(...))).run() with the reference's
+        own driver (baseline/_ref), speedometer and write_thermo on, and an observer
+        holding host views of positions and velocities, which the System pushes
+        from page-locked host memory before and pulls back after every
+        backend.run().  detail.e2e_capi: the same through the C ABI alone.
 roofline : the fused step kernel k_step_nve against the measured HBM peak,
         algorithmic bytes = 7 P + 4 nbar per particle-step.
 cpu_baseline : the C/OpenMP oracle (oracle/oracle_c.c) on this box's cores, on
@@ -311,6 +314,101 @@ def dd_parity(lib, rank, world, steps=120):
     return block if rank == 0 else None
 
 
+def reference_drivers():
+    """atooms.simulation from the unmodified reference installed under baseline/_ref (it travels to the
+    GPU box; tools/install_reference.py), or None.  The DRIVER only: the engine underneath is ours."""
+    ref = os.path.join(ROOT, 'baseline', '_ref')
+    if os.path.isdir(os.path.join(ref, 'atooms')) and ref not in sys.path:
+        sys.path.insert(0, ref)
+    try:
+        if not hasattr(numpy, 'set_string_function'):          # numpy >= 2 (atooms/trajectory/xyz.py:472-474)
+            numpy.set_string_function = lambda *a, **k: None
+        from atooms import simulation
+        return simulation
+    except Exception:
+        return None
+
+
+def plugin_e2e(lib, precision, pos, spe, side, vel, chunks, device=0, views=True):
+    """The metric measured END TO END THROUGH THE PLUGIN, the call a user of the reference makes:
+        Simulation(B200(System(...))).run(steps)         (atooms/simulation/core.py:308-425)
+    with the reference's own driver, its speedometer on (which cuts the run into steps / 20 chunks,
+    core.py:107-109), write_thermo every INNER steps, and — `views` — an observer that works on the
+    host arrays the way docs/simulations.org:274-308 teaches (system.view(...)): while such views are in
+    user hands the System pushes positions and velocities host -> device before every backend.run() and
+    pulls them back after it.  Host mirrors are page-locked (b2_host_alloc).  Copies are counted where they
+    happen (Engine.update / download_into).  Returns rate, seconds, bytes per INNER steps, driver name."""
+    import shutil
+    from atooms_b200 import B200, System, Cell
+    model = atooms_model()
+    names = numpy.array(['A', 'B'])[spe]
+    system = System(pos, names, Cell(side), velocity=vel, model=model, precision=precision, skin=SKIN,
+                    device=device, library=lib)
+    bck = B200(system, model, dt=DT, skin=SKIN, precision=precision, device=device, library=lib)
+    eng = system._engine
+    count = {'h2d': 0, 'd2h': 0, 'runs': 0}
+    upd, dwn, run = eng.update, eng.download_into, bck.run
+
+    def update(position=None, velocity=None):
+        count['h2d'] += sum(a.nbytes for a in (position, velocity) if a is not None)
+        return upd(position, velocity)
+
+    def download_into(position, velocity=None, image=None):
+        count['d2h'] += sum(a.nbytes for a in (position, velocity, image) if a is not None)
+        return dwn(position, velocity, image)
+
+    def counted_run(steps):
+        count['runs'] += 1
+        return run(steps)
+    eng.update, eng.download_into, bck.run = update, download_into, counted_run
+    seen = []
+
+    def host_observer(sim):
+        x, v = sim.system.view('position'), sim.system.view('velocity')
+        seen.append(float(x[0, 0]) + float(v[0, 0]))
+    simulation = reference_drivers()
+    n = len(spe)
+    tmp = tempfile.mkdtemp()
+    try:
+        if simulation is not None:
+            sim = simulation.Simulation(bck, output_path=os.path.join(tmp, 'run'), enable_speedometer=True)
+            sim.add(simulation.write_thermo, simulation.Scheduler(INNER))
+            if views:
+                sim.add(host_observer, simulation.Scheduler(INNER))
+            sim.run(INNER)                                   # warm-up chunk(s)
+            for k in count:
+                count[k] = 0
+            t0 = time.perf_counter()
+            sim.run(INNER * chunks)
+            elapsed = time.perf_counter() - t0
+            driver = 'atooms.simulation.Simulation (reference driver, speedometer on, write_thermo)'
+        else:
+            class _Sim(object):
+                pass
+            sim = _Sim()
+            sim.system = bck.system
+            bck.run(INNER)
+            for k in count:
+                count[k] = 0
+            t0 = time.perf_counter()
+            for _ in range(chunks):
+                bck.run(INNER)
+                s = bck.system
+                seen.append(s.temperature + s.potential_energy(per_particle=True) + s.pressure)
+                count['d2h'] += 9 * 8
+                if views:
+                    host_observer(sim)
+            elapsed = time.perf_counter() - t0
+            driver = 'chunk loop (reference not installed under baseline/_ref)'
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    out = {'value': n * INNER * chunks / elapsed, 'seconds': elapsed, 'h2d': count['h2d'] // chunks,
+           'd2h': count['d2h'] // chunks + 9 * 8, 'backend_run_calls': count['runs'], 'driver': driver,
+           'energy': float(bck.system.total_energy(per_particle=True, cache=True))}
+    bck.system.close()
+    return out
+
+
 def atooms_model():
     from atooms_b200 import models
     return models.PairModel(KA_EPS, KA_SIG, 2.5 * KA_SIG, True, name='kob_andersen')
@@ -496,6 +594,12 @@ def main():
                                   e2e_steps=e2e_steps, stats=st, h2d=2 * 3 * n * 8, d2h=2 * 3 * n * 8 + 16 * 8,
                                   energy=(th['kinetic'] + th['potential']) / n, ntot=n, halo_bytes=0)
         eng.close()
+        if primary:
+            # the headline end-to-end number: through the plugin, driven by the reference's Simulation
+            results[precision]['plugin'] = plugin_e2e(lib, precision, pos, spe, side, vel, e2e_steps,
+                                                      device=local_rank, views=True)
+            results[precision]['plugin_resident'] = plugin_e2e(lib, precision, pos, spe, side, vel, e2e_steps,
+                                                               device=local_rank, views=False)
 
     parity = dd_parity(lib, rank, world) if world > 1 else None
 
@@ -517,9 +621,16 @@ def main():
             'ms_per_step': r['ms'] / args.steps, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32' if args.precision == 32 else 'f64', 'data': 'synthetic',
             'config': workload_config(n, INNER, world, r['halo_bytes'], r.get('comm')),
-            'e2e': {'value': r['e2e'], 'unit': 'particle-timesteps/s',
-                    'h2d_bytes_per_step': int(r['h2d']), 'd2h_bytes_per_step': int(r['d2h']),
-                    'steps': r['e2e_steps']},
+            'e2e': ({'value': r['plugin']['value'], 'unit': 'particle-timesteps/s',
+                     'h2d_bytes_per_step': int(r['plugin']['h2d']), 'd2h_bytes_per_step': int(r['plugin']['d2h']),
+                     'steps': r['e2e_steps'], 'backend_run_calls': r['plugin']['backend_run_calls'],
+                     'through': 'Simulation(B200(System)).run(): ' + r['plugin']['driver'] +
+                                ', host views of position and velocity held by an observer (pushed before and '
+                                'pulled after every backend.run)'}
+                    if 'plugin' in r else
+                    {'value': r['e2e'], 'unit': 'particle-timesteps/s',
+                     'h2d_bytes_per_step': int(r['h2d']), 'd2h_bytes_per_step': int(r['d2h']),
+                     'steps': r['e2e_steps'], 'through': 'SlabDomain.load_host / run / store_host'}),
             'gpu_launches': int(r['launches']),
             'clocks': clocks,
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
@@ -539,6 +650,15 @@ def main():
                                       'total_energy_per_particle': results[p]['energy']}
                        for p in results},
         }
+        if 'plugin' in r:
+            # the same chunk through the C ABI alone (push, b2_run_nve, pull, thermo), and through the plugin
+            # with the state left resident (observers read scalars only)
+            line['detail']['e2e_capi'] = {'value': r['e2e'], 'h2d_bytes_per_step': int(r['h2d']),
+                                          'd2h_bytes_per_step': int(r['d2h'])}
+            pr = r['plugin_resident']
+            line['detail']['e2e_plugin_resident'] = {'value': pr['value'], 'h2d_bytes_per_step': int(pr['h2d']),
+                                                     'd2h_bytes_per_step': int(pr['d2h']),
+                                                     'backend_run_calls': pr['backend_run_calls']}
         if parity is not None:
             line['parity'] = parity
         if not args.no_cpu_baseline:
