@@ -191,6 +191,11 @@ class System(object):
         """Build from an `atooms.system.System` (or anything with .particle / .cell)."""
         if isinstance(system, cls):
             return system
+        from .trajectory import Snapshot
+        if isinstance(system, Snapshot):                  # array-backed frame: no Particle objects
+            return cls(position=system.position, species=system.species.tolist(),
+                       cell=Cell(system.cell.side, getattr(system.cell, 'center', None)),
+                       velocity=system.velocity, mass=system.mass, radius=system.radius, **kwargs)
         particle = system.particle
         if system.cell is None:
             raise ValueError('the B200 backend needs a periodic cell')

@@ -1,25 +1,194 @@
 """
-Vectorised xyz trajectory writer for the array-backed System.
+Trajectory fast path for the array-backed System.
 
-The reference's `TrajectoryXYZ.write_system` formats one particle at a time
-with `str.format` and relies on `numpy.set_string_function`, which numpy >= 2
-removed (atooms/trajectory/xyz.py:437-474).  This class writes
-the same layout (`N`, then `step:.. columns:.. dt:.. cell:..`, then one line
-per particle) from the flat arrays, so the reference's reader parses it back.
-It provides the members `Simulation`'s observers use
-(atooms/simulation/observers.py:167-207): `timestep`, `precision`,
-`variables`, `write(system, step)`, `close()`, context manager.
+The reference's writers format one particle at a time with `str.format`
+(atooms/trajectory/xyz.py:437-474, rumd.py:88-98) and `TrajectoryXYZ` relies on
+`numpy.set_string_function`, which numpy >= 2 removed; its
+in-memory trajectory deep-copies N Particle objects per frame
+(atooms/trajectory/ram.py:22-33).  With an engine at ~1e10 particle-steps/s those
+loops are the wall time at any realistic cadence.  Here
+
+  Trajectory        xyz files in the reference's layout (`N`, then
+                    `step:.. columns:.. dt:.. cell:..`, then one line per particle), written
+                    from the flat arrays with ONE formatting call per block of 65536 particles,
+                    and read back the same way (mode 'r': `steps`, `len`, indexing, iteration);
+                    the reference's reader parses what this writes, and vice versa.
+  TrajectoryRUMD    the same for RUMD's xyz dialect (integer types, `ioformat=1 ...` header,
+                    atooms/trajectory/rumd.py:69-98).
+  TrajectoryRam     frames kept in memory as array snapshots (ram.py's interface: write, update
+                    of an existing step, `th[i]` returns a copy, `th[i] = system`).
+  Snapshot          what reading returns: an array-backed frame with the members the reference's
+                    System offers to analysis code (`particle` materialised lazily, `cell`,
+                    `dump`, `density`, ...); `System.from_atooms` / `B200(...)` accept it.
+
+All provide what `Simulation`'s observers use (atooms/simulation/observers.py:167-207):
+`timestep`, `precision`, `variables`, `write(system, step)`, `close()`, context manager.
 """
+import copy
 import os
 
 import numpy
 
-__all__ = ['Trajectory', 'TrajectoryNeighbors']
+__all__ = ['Trajectory', 'TrajectoryRUMD', 'TrajectoryRam', 'TrajectoryNeighbors', 'Snapshot']
+
+_BLOCK = 65536        # particles formatted per call
+
+_ALIASES = {'pos': 'position', 'vel': 'velocity', 'spe': 'species', 'rad': 'radius', 'particle.position': 'position',
+            'particle.velocity': 'velocity', 'particle.species': 'species', 'particle.mass': 'mass',
+            'particle.radius': 'radius'}
+_WIDTH = {'position': 3, 'velocity': 3, 'species': 1, 'mass': 1, 'radius': 1}
+
+
+class _Cell(object):
+
+    def __init__(self, side, center=None):
+        self.side = numpy.array(side, dtype=numpy.float64)
+        self.center = numpy.zeros_like(self.side) if center is None else numpy.array(center, dtype=numpy.float64)
+        self.shape = 'cubic'
+        self.periodic = numpy.ones(self.side.size, dtype=bool)
+
+    @property
+    def volume(self):
+        return float(numpy.prod(self.side))
+
+
+class Snapshot(object):
+
+    """One frame as flat arrays.  `particle` builds Particle objects only when indexed."""
+
+    def __init__(self, position, species, cell, velocity=None, mass=None, radius=None, step=0):
+        self.position = numpy.array(position, dtype=numpy.float64).reshape(-1, 3)
+        n = len(self.position)
+        self.species = numpy.array(species)
+        self.velocity = numpy.zeros((n, 3)) if velocity is None else numpy.array(velocity, dtype=numpy.float64).reshape(n, 3)
+        self.mass = numpy.ones(n) if mass is None else numpy.array(mass, dtype=numpy.float64)
+        self.radius = numpy.full(n, 0.5) if radius is None else numpy.array(radius, dtype=numpy.float64)
+        self.cell = cell if hasattr(cell, 'side') else _Cell(cell)
+        self.step = step
+        self.thermostat = self.barostat = self.reservoir = self.interaction = None
+
+    @classmethod
+    def of(cls, system, step=0):
+        """Copy of the state of a System of this package, a Snapshot, or a reference System."""
+        if isinstance(system, Snapshot):
+            out = copy.deepcopy(system)
+            out.step = step
+            return out
+        if hasattr(system, 'dump') and hasattr(system, '_ids'):          # atooms_b200.System: arrays, no objects
+            return cls(system.dump('position'), system.species, _Cell(system.cell.side, system.cell.center),
+                       system.dump('velocity'), system.dump('mass'), system.dump('radius'), step)
+        p = system.particle
+        return cls([q.position for q in p], [q.species for q in p],
+                   _Cell(system.cell.side, getattr(system.cell, 'center', None)),
+                   [q.velocity for q in p], [q.mass for q in p], [getattr(q, 'radius', 0.5) for q in p], step)
+
+    def __len__(self):
+        return len(self.position)
+
+    number_of_dimensions = 3
+
+    @property
+    def particle(self):
+        return _Particles(self)
+
+    @property
+    def distinct_species(self):
+        return sorted(set(self.species.tolist()))
+
+    @property
+    def composition(self):
+        names, counts = numpy.unique(self.species, return_counts=True)
+        return {str(k): int(v) for k, v in zip(names, counts)}
+
+    @property
+    def density(self):
+        return len(self) / self.cell.volume if len(self) else 0.0
+
+    def dump(self, what=None, order='C', dtype=None, view=False, clear=False, flat=False):
+        what = _ALIASES.get(what, what)
+        if what in ('cell.side', 'box'):
+            data = self.cell.side
+        elif what in _WIDTH:
+            data = getattr(self, what)
+        else:
+            raise ValueError('Unknown attribute %s' % what)
+        data = data if view else numpy.array(data, dtype=dtype)
+        if data.ndim == 2 and order == 'F':
+            data = data.T
+        return data.flatten(order=order) if flat else data
+
+    view = dump
+
+    def update(self, other, full=False, exclude=None, only=None):
+        other = Snapshot.of(other, self.step)
+        self.position[:], self.velocity[:] = other.position, other.velocity
+        self.species, self.mass, self.radius = other.species, other.mass, other.radius
+        self.cell = other.cell
+
+
+class _Particles(object):
+
+    def __init__(self, frame):
+        self._f = frame
+
+    def __len__(self):
+        return len(self._f)
+
+    def _make(self, i):
+        from .system import _particle_class
+        f = self._f
+        sp = f.species[i]
+        return _particle_class()(position=f.position[i], velocity=f.velocity[i],
+                                 species=sp.item() if hasattr(sp, 'item') else sp, mass=f.mass[i], radius=f.radius[i])
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self._make(k) for k in range(*i.indices(len(self)))]
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError('particle index out of range')
+        return self._make(i)
+
+    def __iter__(self):
+        return (self._make(i) for i in range(len(self)))
+
+
+def _columns(variables):
+    return [_ALIASES.get(v, v).replace('particle.', '') for v in variables]
+
+
+def _format_rows(handle, blocks, formats):
+    """Write len(blocks[0]) lines; blocks are 1-d (strings / integers) or 2-d (floats) arrays and `formats`
+    their per-value format.  One `%` call per _BLOCK lines: no per-particle Python."""
+    n = len(blocks[0])
+    row = ' '.join(' '.join([f] * (1 if b.ndim == 1 else b.shape[1])) for b, f in zip(blocks, formats)) + '\n'
+    width = sum(1 if b.ndim == 1 else b.shape[1] for b in blocks)
+    for lo in range(0, n, _BLOCK):
+        hi = min(n, lo + _BLOCK)
+        cells = numpy.empty((hi - lo, width), dtype=object)
+        k = 0
+        for b in blocks:
+            w = 1 if b.ndim == 1 else b.shape[1]
+            cells[:, k:k + w] = b[lo:hi].reshape(hi - lo, w)       # numpy scalars -> Python objects, in C
+            k += w
+        handle.write((row * (hi - lo)) % tuple(cells.ravel().tolist()))
+
+
+def _arrays_of(system, columns):
+    """The columns of `system` as arrays: a System of this package, a Snapshot, or a reference System."""
+    if not (hasattr(system, '_ids') or isinstance(system, Snapshot)):
+        system = Snapshot.of(system)                       # a reference System: one pass over its Particle list
+    return [numpy.asarray(system.dump(c)) for c in columns]
 
 
 class Trajectory(object):
 
+    """xyz trajectory in the reference's layout (atooms/trajectory/xyz.py:135-474)."""
+
     suffix = 'xyz'
+    _names = {'id': 'species', 'name': 'species', 'type': 'species', 'spe': 'species', 'pos': 'position',
+              'vel': 'velocity', 'rad': 'radius'}
 
     def __init__(self, filename, mode='r'):
         self.filename = filename
@@ -28,12 +197,16 @@ class Trajectory(object):
         self.precision = 6
         self.variables = ['species', 'position']
         self._fh = None
+        self._frames = []                      # read mode: (step, offset of the first particle line, n, header dict)
         if mode in ('w', 'a'):
             base = os.path.dirname(filename)
             if base and not os.path.exists(base):
                 os.makedirs(base)
             self._fh = open(filename, mode)
-        elif mode != 'r':
+        elif mode == 'r':
+            self._fh = open(filename, 'r')
+            self._index()
+        else:
             raise ValueError('unknown mode %r' % mode)
 
     def __enter__(self):
@@ -42,32 +215,206 @@ class Trajectory(object):
     def __exit__(self, *exc):
         self.close()
 
-    def write(self, system, step):
-        if self._fh is None:
-            raise IOError('trajectory %s is not open for writing' % self.filename)
-        n = len(system.particle) if not hasattr(system, '_ids') else len(system)
-        columns = [v.replace('particle.', '') for v in self.variables]
-        blocks = []
-        for var in columns:
-            data = numpy.asarray(system.dump(var))
-            if data.dtype.kind in 'fc':
-                fmt = '%.{}f'.format(self.precision)
-                data = data.reshape(n, -1)
-                blocks.append([' '.join(fmt % x for x in row) for row in data])
-            else:
-                blocks.append([str(x) for x in data])
-        line = 'step:{} columns:{} '.format(step, ','.join(columns))
-        if self.timestep is not None:
-            line += 'dt:{:g} '.format(self.timestep)
-        line += 'cell:{} '.format(','.join(repr(float(x)) for x in system.cell.side))
-        self._fh.write('%d\n%s\n' % (n, line))
-        self._fh.write('\n'.join(' '.join(fields) for fields in zip(*blocks)))
-        self._fh.write('\n')
-
     def close(self):
         if self._fh is not None:
             self._fh.close()
             self._fh = None
+
+    # ---- writing ---------------------------------------------------------------------
+    def _header(self, step, columns, system):
+        line = 'step:{} columns:{} '.format(step, ','.join(columns))
+        if self.timestep is not None:
+            line += 'dt:{:g} '.format(self.timestep)
+        return line + 'cell:{} '.format(','.join(repr(float(x)) for x in system.cell.side))
+
+    def _species_column(self, names):
+        return names.astype(object) if names.dtype.kind in 'US' else names
+
+    def write(self, system, step):
+        if self._fh is None or self.mode == 'r':
+            raise IOError('trajectory %s is not open for writing' % self.filename)
+        columns = _columns(self.variables)
+        blocks = _arrays_of(system, columns)
+        n = len(blocks[0]) if blocks else 0
+        formats = []
+        for k, (c, b) in enumerate(zip(columns, blocks)):
+            if c == 'species':
+                blocks[k], fmt = self._species_column(b), '%s'
+            else:
+                fmt = '%.{}f'.format(self.precision) if b.dtype.kind == 'f' else '%s'
+            formats.append(fmt)
+        self._fh.write('%d\n%s\n' % (n, self._header(step, columns, system)))
+        if n:
+            _format_rows(self._fh, blocks, formats)
+
+    # ---- reading ---------------------------------------------------------------------
+    def _parse_header(self, line):
+        meta = {}
+        for token in line.replace('=', ':').split():
+            if ':' in token:
+                key, value = token.split(':', 1)
+                meta[key] = value
+        return meta
+
+    def _index(self):
+        fh = self._fh
+        fh.seek(0)
+        while True:
+            first = fh.readline()
+            if not first.strip():
+                break
+            n = int(first)
+            meta = self._parse_header(fh.readline())
+            start = fh.tell()
+            for _ in range(n):
+                fh.readline()
+            step = int(meta.get('step', meta.get('timeStepIndex', len(self._frames))))
+            self._frames.append((step, start, n, meta))
+        if self._frames and 'dt' in self._frames[0][3]:
+            self.timestep = float(self._frames[0][3]['dt'])
+
+    @property
+    def steps(self):
+        return [f[0] for f in self._frames]
+
+    def __len__(self):
+        return len(self._frames)
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+    def _layout(self, meta, ncol):
+        cols = [self._names.get(c, c) for c in meta['columns'].split(',')] if 'columns' in meta else \
+            (['species', 'position'] if ncol < 7 else ['species', 'position', 'velocity'])
+        return cols
+
+    def _build(self, meta, names, table, step):
+        """A Snapshot from the columns named in the header; `table` holds the numeric columns."""
+        cols, k, got = self._layout(meta, table.shape[1] + 1), 0, {}
+        for c in cols:
+            if c == 'species':
+                continue
+            w = _WIDTH.get(c, 1)
+            got[c] = table[:, k:k + w]
+            k += w
+        side = numpy.array([float(x) for x in meta.get('cell', meta.get('boxLengths', '0,0,0')).split(',')])
+        snap = Snapshot(got['position'], names, _Cell(side), got.get('velocity'),
+                        got['mass'][:, 0] if 'mass' in got else None,
+                        got['radius'][:, 0] if 'radius' in got else None, step)
+        snap.extra = {c: v for c, v in got.items() if c not in _WIDTH}
+        return snap
+
+    def __getitem__(self, i):
+        if self._fh is None or self.mode != 'r':
+            raise IOError('trajectory %s is not open for reading' % self.filename)
+        if i < 0:
+            i += len(self._frames)
+        step, start, n, meta = self._frames[i]
+        self._fh.seek(start)
+        tokens = numpy.array(''.join(self._fh.readline() for _ in range(n)).split())
+        ncol = len(tokens) // max(n, 1)
+        tokens = tokens.reshape(n, ncol)
+        return self._build(meta, self._read_species(tokens[:, 0]), tokens[:, 1:].astype(numpy.float64), step)
+
+    def _read_species(self, column):
+        return column
+
+    read = __getitem__
+
+
+class TrajectoryRUMD(Trajectory):
+
+    """RUMD's dialect (atooms/trajectory/rumd.py:10-98): integer types in the first column (the position of
+    the species in the sorted list of distinct species), header `ioformat=1 dt=.. timeStepIndex=..
+    boxLengths=.. numTypes=.. mass=.. columns=type,x,y,z,vx,vy,vz`."""
+
+    def __init__(self, filename, mode='r'):
+        Trajectory.__init__(self, filename, mode)
+        self.variables = ['species', 'position', 'velocity']
+        self.precision = 9
+
+    def _header(self, step, columns, system):
+        names = numpy.asarray(system.dump('species'))
+        mass = numpy.asarray(system.dump('mass'))
+        distinct = sorted(set(names.tolist()))
+        first = [float(mass[numpy.argmax(names == s)]) for s in distinct]
+        names = {'position': 'x,y,z', 'velocity': 'vx,vy,vz', 'species': 'type'}
+        return 'ioformat=1 dt=%g timeStepIndex=%d boxLengths=%s numTypes=%d mass=%s columns=%s' % (
+            self.timestep if self.timestep is not None else 1.0, step,
+            ','.join('%.12f' % x for x in system.cell.side), len(distinct), ','.join('%g' % m for m in first),
+            ','.join(names.get(c, c) for c in columns))
+
+    def _species_column(self, names):
+        distinct = sorted(set(names.tolist()))
+        return numpy.searchsorted(numpy.array(distinct), names).astype(object)
+
+    def _layout(self, meta, ncol):
+        out, skip = [], 0
+        for c in meta.get('columns', 'type,x,y,z').split(','):
+            if skip:
+                skip -= 1
+                continue
+            if c == 'type':
+                out.append('species')
+            elif c == 'x':
+                out.append('position')
+                skip = 2
+            elif c == 'vx':
+                out.append('velocity')
+                skip = 2
+            else:
+                out.append(c)
+        return out
+
+
+class TrajectoryRam(object):
+
+    """Frames kept in memory as array snapshots: the interface of atooms/trajectory/ram.py:7-47 (write
+    replaces the frame of a step already present, `th[i]` returns a copy, `th[i] = system` writes)
+    without a deep copy of N Particle objects per frame."""
+
+    def __init__(self, filename=None, mode='w'):
+        self.filename, self.mode = filename, mode
+        self.timestep = None
+        self.precision = None
+        self.variables = ['species', 'position', 'velocity']
+        self.steps = []
+        self._frames = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def close(self):
+        pass
+
+    def write(self, system, step):
+        frame = Snapshot.of(system, step)
+        if step in self.steps:
+            self._frames[self.steps.index(step)] = frame
+        else:
+            self.steps.append(step)
+            self._frames.append(frame)
+
+    def __len__(self):
+        return len(self._frames)
+
+    def __getitem__(self, i):
+        return copy.deepcopy(self._frames[i])
+
+    read = __getitem__
+
+    def __setitem__(self, i, value):
+        try:
+            step = self.steps[i]
+        except IndexError:
+            step = self.steps[-1] + 1 if self.steps else 0
+        self.write(value, step)
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
 
 
 class TrajectoryNeighbors(Trajectory):

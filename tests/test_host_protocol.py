@@ -281,6 +281,60 @@ def test_trajectory_writer(oracle_lib, tmp_path):
         assert [p.species for p in back.particle] == list(s.species)
 
 
+def test_trajectory_fast_path(oracle_lib, tmp_path):
+    """block-formatted writer, read mode, RUMD dialect, in-memory snapshots — none of
+    them builds Particle objects."""
+    from atooms_b200 import TrajectoryRUMD, TrajectoryRam, Snapshot
+    s = make_system('ka_N256_rumd', oracle_lib, 'kob_andersen')
+    path = str(tmp_path / 'fast.xyz')
+    with Trajectory(path, 'w') as th:
+        th.timestep, th.precision, th.variables = 0.002, 9, ['species', 'position', 'velocity']
+        th.write(s, 0)
+        th.write(s, 25)
+    with Trajectory(path) as th:                       # read mode
+        assert th.steps == [0, 25] and len(th) == 2 and th.timestep == 0.002
+        back = th[-1]
+        assert isinstance(back, Snapshot) and len(back) == 256 and back.step == 25
+        assert numpy.abs(back.position - s.dump('position')).max() < 1e-9
+        assert numpy.abs(back.velocity - s.dump('velocity')).max() < 1e-9
+        assert list(back.species) == list(s.species) and numpy.allclose(back.cell.side, s.cell.side)
+        assert back.particle[3].species == s.species[3] and len(back.particle) == 256
+        assert [f.step for f in th] == [0, 25]
+    # a frame read back starts a backend like any other system
+    again = B200(back, 'kob_andersen', library=oracle_lib)
+    assert abs(again.system.potential_energy() - B200(s, 'kob_andersen', library=oracle_lib).system.potential_energy()) < 1e-5
+    # RUMD dialect: integer types, ioformat header
+    rpath = str(tmp_path / 'conf.xyz')
+    with TrajectoryRUMD(rpath, 'w') as th:
+        th.timestep = 0.005
+        th.write(s, 7)
+    head = open(rpath).read().splitlines()[:3]
+    assert head[0] == '256' and head[1].startswith('ioformat=1 dt=0.005 timeStepIndex=7 boxLengths=6.0')
+    assert 'numTypes=2 mass=1,1 columns=type,x,y,z,vx,vy,vz' in head[1] and head[2].split()[0] in ('0', '1')
+    with TrajectoryRUMD(rpath) as th:
+        b = th[0]
+        assert th.steps == [7] and numpy.abs(b.position - s.dump('position')).max() < 1e-8
+        assert list(b.species.astype(int)) == list(s._ids)
+    if HAVE_REF:                                        # and the reference's own readers parse both files
+        from atooms.trajectory import TrajectoryXYZ, TrajectoryRUMD as RefRUMD
+        for cls, p, species in ((TrajectoryXYZ, path, s.species[5]), (RefRUMD, rpath, str(s._ids[5]))):
+            th = cls(p)
+            ref = th[0]
+            th.close()
+            assert numpy.abs(ref.particle[5].position - s.dump('position')[5]).max() < 1e-8
+            assert str(ref.particle[5].species) == species
+    # in-memory trajectory (ram.py's interface)
+    ram = TrajectoryRam()
+    ram.write(s, 0)
+    ram.write(s, 10)
+    ram[1] = s                                           # rewrites step 10
+    ram[5] = s                                           # appends step 11
+    assert ram.steps == [0, 10, 11] and len(ram) == 3
+    f = ram[0]
+    f.position[0, 0] += 1.0
+    assert ram[0].position[0, 0] != f.position[0, 0]    # copies, as TrajectoryRam returns
+
+
 # ---- the reference's own drivers on top of our backend -------------------------------
 @needs_ref
 def test_reference_simulation_driver(oracle_lib, pins, tmp_path):
