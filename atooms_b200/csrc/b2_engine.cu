@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #define MAX_RED_BLOCKS 1024
@@ -102,8 +103,49 @@ struct b2_ctx {
 };
 
 static char g_err[512] = "";
+// The pair table sits in ONE __constant__ object per device, shared by every context (and replica
+// batch) on it.  Ownership changes are serialised by a mutex and ORDERED ON THE DEVICE: every entry
+// point that launches kernels leaves an event on its stream (TableGuard), and a new owner makes its
+// stream wait for that event before it overwrites the table — kernels of the previous owner still
+// queued on another stream keep reading their own coefficients.
 static uint64_t g_const_owner[64];      // per device: serial of the ctx whose table is resident
+static cudaEvent_t g_const_event[64];   // per device: after the owner's last launches
+static bool g_const_event_set[64];
 static uint64_t g_serial = 0;
+static std::mutex g_const_mutex;
+
+// make `serial` the owner of the device's table (the copy is enqueued on `stream`)
+static cudaError_t table_acquire(int device, uint64_t serial, const PairConst *pc, cudaStream_t stream)
+{
+    std::lock_guard<std::mutex> lock(g_const_mutex);
+    if (g_const_owner[device] == serial) return cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    if (g_const_event_set[device]) e = cudaStreamWaitEvent(stream, g_const_event[device], 0);
+    if (e == cudaSuccess) e = cudaMemcpyToSymbolAsync(g_pair, pc, sizeof(PairConst), 0, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) g_const_owner[device] = serial;
+    return e;
+}
+
+// mark the end of the owner's launches on `stream`
+static void table_release(int device, uint64_t serial, cudaStream_t stream)
+{
+    std::lock_guard<std::mutex> lock(g_const_mutex);
+    if (g_const_owner[device] != serial) return;
+    if (!g_const_event[device] && cudaEventCreateWithFlags(&g_const_event[device], cudaEventDisableTiming) != cudaSuccess) return;
+    g_const_event_set[device] = cudaEventRecord(g_const_event[device], stream) == cudaSuccess;
+}
+
+static uint64_t next_serial()
+{
+    std::lock_guard<std::mutex> lock(g_const_mutex);
+    return ++g_serial;
+}
+
+static void table_forget(int device, uint64_t serial)
+{
+    std::lock_guard<std::mutex> lock(g_const_mutex);
+    if (g_const_owner[device] == serial) g_const_owner[device] = 0;
+}
 
 struct NcclApi {
     void *handle = nullptr;
@@ -183,12 +225,17 @@ static int bind_device(b2_ctx *c)
 // context used the device since our last launch
 static int bind_table(b2_ctx *c)
 {
-    if (g_const_owner[c->device] != c->const_serial) {
-        CU(cudaMemcpyToSymbolAsync(g_pair, &c->pc, sizeof(PairConst), 0, cudaMemcpyHostToDevice, c->stream));
-        g_const_owner[c->device] = c->const_serial;
-    }
+    CU(table_acquire(c->device, c->const_serial, &c->pc, c->stream));
     return B2_OK;
 }
+
+// Every entry point that may launch kernels: the table is ours on entry, and the end of our launches is
+// marked on leaving.
+struct TableGuard {
+    b2_ctx *c;
+    explicit TableGuard(b2_ctx *ctx) : c(ctx) {}
+    ~TableGuard() { if (c && c->have_table) table_release(c->device, c->const_serial, c->stream); }
+};
 
 static void rebuild_table(b2_ctx *c)
 {
@@ -201,7 +248,7 @@ static void rebuild_table(b2_ctx *c)
         c->pc.f6[a] = (float)(6.0 * c->pc.c6[a]);
         c->pc.frc2[a] = (float)c->pc.rc2[a];
     }
-    c->const_serial = ++g_serial;
+    c->const_serial = next_serial();
 }
 
 static int pull_ctl(b2_ctx *c)
@@ -1240,7 +1287,7 @@ int b2_destroy(b2_ctx *c)
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     for (cudaEvent_t e : c->pev) cudaEventDestroy(e);
-    if (g_const_owner[c->device] == c->const_serial) g_const_owner[c->device] = 0;
+    table_forget(c->device, c->const_serial);
     delete c;
     return B2_OK;
 }
@@ -1313,7 +1360,9 @@ int b2_set_skin(b2_ctx *c, double skin)
 #define NEED_PARTICLES(who)                                                                   \
     if (!c) return fail(nullptr, B2_EINVAL, who ": NULL context");                            \
     if (!c->pos[0]) return fail(c, B2_ESTATE, who ": no particles resident (call b2_upload)"); \
-    { int rc_ = bind_device(c); if (rc_) return rc_; }
+    { int rc_ = bind_device(c); if (rc_) return rc_; }                                        \
+    if (c->have_table) { int rc_ = bind_table(c); if (rc_) return rc_; }                      \
+    TableGuard table_guard_(c);
 
 int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel, const int32_t *species,
               const double *mass)
@@ -1873,10 +1922,11 @@ template <typename R> struct BatchImpl {
     {
         b2_ctx *c = nullptr;
         if (b->nrep == 0) return B2_OK;
-        if (g_const_owner[b->device] != b->const_serial) {
-            CU(cudaMemcpyToSymbol(g_pair, &b->pc, sizeof(PairConst)));
-            g_const_owner[b->device] = b->const_serial;
-        }
+        CU(table_acquire(b->device, b->const_serial, &b->pc, (cudaStream_t)0));
+        struct Release {
+            b2_batch *b;
+            ~Release() { table_release(b->device, b->const_serial, (cudaStream_t)0); }
+        } release_on_return{b};
         BatchArgs<R> a;
         a.pos = (P4 *)b->pos;
         a.vel = (const V4 *)b->vel;
@@ -1923,10 +1973,11 @@ template <typename R> struct BatchImpl {
     {
         b2_ctx *c = nullptr;
         if (b->nrep == 0) return B2_OK;
-        if (g_const_owner[b->device] != b->const_serial) {
-            CU(cudaMemcpyToSymbol(g_pair, &b->pc, sizeof(PairConst)));
-            g_const_owner[b->device] = b->const_serial;
-        }
+        CU(table_acquire(b->device, b->const_serial, &b->pc, (cudaStream_t)0));
+        struct Release {
+            b2_batch *b;
+            ~Release() { table_release(b->device, b->const_serial, (cudaStream_t)0); }
+        } release_on_return{b};
         BatchNveArgs<R> a;
         a.pos = (P4 *)b->pos;
         a.vel = (V4 *)b->vel;
@@ -2020,7 +2071,7 @@ int b2_batch_destroy(b2_batch *b)
     cudaSetDevice(b->device);
     void *ptrs[] = {b->pos, b->frc, b->vel, b->img, b->stage, b->stage_i, b->d_steps, b->d_conv, b->d_out};
     for (void *p : ptrs) if (p) cudaFree(p);
-    if (g_const_owner[b->device] == b->const_serial) g_const_owner[b->device] = 0;
+    table_forget(b->device, b->const_serial);
     delete b;
     return B2_OK;
 }
@@ -2045,7 +2096,7 @@ int b2_batch_set_model(b2_batch *b, const double side[3], int nsp, const double 
         double ir2 = 1.0 / b->pc.rc2[a], ir6 = ir2 * ir2 * ir2;
         b->pc.ushift[a] = shifted ? ir6 * (b->pc.c12[a] * ir6 - b->pc.c6[a]) : 0.0;
     }
-    b->const_serial = ++g_serial;
+    b->const_serial = next_serial();
     b->have_model = true;
     return B2_OK;
 }

@@ -384,6 +384,39 @@ def test_reupload_with_more_particles(cuda_lib, oracle_lib):
     assert_observables(eng.compute(), make_engine(oracle_lib, small, ka, 64, velocities=False).compute(), 64)
 
 
+def test_two_contexts_with_different_tables_interleaved(cuda_lib):
+    """The pair table is one __constant__ object per GPU.  Two contexts with different models, on
+    different streams, stepping in turns must each keep reading their own coefficients (ADVICE r01:
+    the overwrite for the next owner is ordered after the previous owner's queued kernels)."""
+    import torch
+    ka, lj = onp.kob_andersen(), onp.lennard_jones(3.0, True)
+    da = dict(golden('ka_N1200').items(), velocity=onp.maxwell_boltzmann(1200, 0.8, 1.0, seed=3))
+    db = golden('lj_N1000')
+
+    def pair(streams):
+        a, b = make_engine(cuda_lib, da, ka, 64), make_engine(cuda_lib, db, lj, 64, skin=0.25)
+        if streams:
+            sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+            a.set_stream(sa.cuda_stream)
+            b.set_stream(sb.cuda_stream)
+            a._keep = (sa, sb)
+        return a, b
+    a, b = pair(True)
+    for _ in range(12):                       # interleaved: ownership of the table changes 24 times
+        a.run_nve(5, 0.002)
+        b.run_nve(5, 0.004)
+    ea, eb = a.compute(), b.compute()
+    pa, pb = a.download()[0], b.download()[0]
+    a2, _unused = pair(False)
+    a2.run_nve(60, 0.002)                     # each alone
+    _unused.close()
+    b2 = make_engine(cuda_lib, db, lj, 64, skin=0.25)
+    b2.run_nve(60, 0.004)
+    assert numpy.abs(pa - a2.download()[0]).max() < 1e-9 and numpy.abs(pb - b2.download()[0]).max() < 1e-9
+    assert abs(ea['energy'] - a2.compute()['energy']) < 1e-9 * abs(ea['energy'])
+    assert abs(eb['energy'] - b2.compute()['energy']) < 1e-9 * abs(eb['energy'])
+
+
 def test_edge_cases(cuda_lib):
     lj = onp.lennard_jones(2.5, True)
     base = {'side': numpy.array([10., 10., 10.]), 'center': numpy.zeros(3)}
