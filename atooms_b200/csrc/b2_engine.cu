@@ -92,6 +92,13 @@ struct b2_ctx {
     int *stage_i = nullptr;    // 3n ints
     // host-side knowledge
     bool list_dirty = true, forces_valid = false, ev_valid = false;
+    // a run ended with the velocities still at t - dt/2: the closing half kick (and the force evaluation it
+    // needs) is done by whoever next looks at velocities or forces — or never, if the next call is the
+    // continuation of the same run (Simulation hands the backend one chunk per observer interval)
+    bool half_pending = false;
+    double half_dt = 0;
+    int half_kind = -1;
+    double half_T0 = 0, half_tau = 0;
     int batch = 8;
     // profiling (b2_set_profile): events around step batches / refresh chains
     bool profile = false;
@@ -599,6 +606,7 @@ template <typename R> struct Impl {
         return B2_OK;
     }
 
+    static int settle(b2_ctx *c);
     static int thermo(b2_ctx *c, double *out, bool want_stress, double *stress9);
     static int run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind = -1, double T0 = 0, double tau = 0);
     static int minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double tol,
@@ -780,6 +788,7 @@ int Impl<R>::upload(b2_ctx *c, int64_t n, const double *pos, const double *vel,
     c->n = n;
     c->list_dirty = true;
     c->forces_valid = c->ev_valid = false;
+    c->half_pending = false;
     c->min_resume = false;
     if (c->mvel) { cudaFree(c->mvel); c->mvel = nullptr; }
     memset(c->hctl, 0, sizeof(Ctl));
@@ -945,14 +954,22 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
     int rc;
     if (steps == 0 || c->n == 0) return B2_OK;
     int n = (int)c->n;
-    if ((rc = ensure_forces(c))) return rc;
-    // opening half kick (backwards): velocities move to t - dt/2
-    LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(-0.5 * dt));
-    LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0, 0);
     const bool nvt = th_kind >= 0;
+    // continuation of the run the previous call left open: same integrator, same step — no closing and
+    // no opening half kick, no force evaluation in between
+    const bool cont = c->half_pending && c->half_dt == dt && c->half_kind == th_kind &&
+                      (!nvt || (c->half_T0 == T0 && c->half_tau == tau));
+    if (!cont) {
+        if ((rc = settle(c))) return rc;
+        if ((rc = ensure_forces(c))) return rc;
+        // opening half kick (backwards): velocities move to t - dt/2
+        LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(-0.5 * dt));
+    }
+    LAUNCH(k_ctl_begin, 1, 1, c->ctl, (long long)steps, 0, 0.0, 0.0, 0.0, 0);
     if (nvt) {
         if (!c->ke_partial && (rc = dev_alloc(c, &c->ke_partial, (size_t)cdiv(c->ncap, FORCE_THREADS) + c->ncap / 8 + 65))) return rc;
-        LAUNCH(k_thermostat_begin, 1, 1, c->ctl, th_kind, T0, tau, dt, 3.0 * (double)std::max<int64_t>(c->n - 1, 1));
+        // (a continued run keeps the coefficients its last step left in the control block)
+        if (!cont) LAUNCH(k_thermostat_begin, 1, 1, c->ctl, th_kind, T0, tau, dt, 3.0 * (double)std::max<int64_t>(c->n - 1, 1));
     }
     c->min_resume = false;
     for (int k = 0; k < 8; k++) c->prof[k] = 0;
@@ -1027,12 +1044,29 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
     }
     c->prof[3] = (double)steps;
     c->prof[4] = (double)(c->hctl->rebuilds - rebuilds0);
-    // closing half kick at the final configuration
+    // the closing half kick is left to settle()
     c->list_dirty = c->hctl->halt_rebuild != 0u;
     c->forces_valid = c->ev_valid = false;
-    if ((rc = ensure_forces(c))) return rc;
-    LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(0.5 * dt));
+    c->half_pending = true;
+    c->half_dt = dt;
+    c->half_kind = th_kind;
+    c->half_T0 = T0;
+    c->half_tau = tau;
     c->steps_total += steps;
+    return B2_OK;
+}
+
+// velocities to the full step: forces of the final configuration, closing half kick
+template <typename R>
+int Impl<R>::settle(b2_ctx *c)
+{
+    int rc;
+    if (!c->half_pending) return B2_OK;
+    c->half_pending = false;
+    if (c->n == 0) return B2_OK;
+    const int n = (int)c->n;
+    if ((rc = ensure_forces(c))) return rc;
+    LAUNCH(k_kick<R>, cdiv(n, 256), 256, (V4 *)c->vel, (const V4 *)c->frc, n, (R)(0.5 * c->half_dt));
     return B2_OK;
 }
 
@@ -1188,6 +1222,26 @@ int Impl<R>::dd_unpack(b2_ctx *c, int64_t first, int64_t n, const double *in_dev
     return B2_OK;
 }
 
+// A new box for RESIDENT particles is an affine rescaling: fractional coordinates are kept, so distances
+// scale with the sides (what a barostat step does; a re-upload follows anyway when the caller replaces the
+// particles).  fp32 positions are stored as fractions of the cell and need no touch; fp64 positions and the
+// rmsd origin are lengths relative to the centre and are multiplied by new / old.
+template <typename R>
+__global__ void k_rescale_box(int n, double rx, double ry, double rz, typename Pos4<R>::type *pos0,
+                              typename Pos4<R>::type *pos1, double *__restrict__ ref)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (sizeof(R) == 8) {
+        double4 *p0 = reinterpret_cast<double4 *>(pos0), *p1 = reinterpret_cast<double4 *>(pos1);
+        double4 a = p0[i], b = p1[i];
+        a.x *= rx; a.y *= ry; a.z *= rz;
+        b.x *= rx; b.y *= ry; b.z *= rz;
+        p0[i] = a; p1[i] = b;
+    }
+    ref[3 * i] *= rx; ref[3 * i + 1] *= ry; ref[3 * i + 2] *= rz;
+}
+
 // ---------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------
@@ -1304,8 +1358,22 @@ int b2_set_stream(b2_ctx *c, void *cuda_stream)
 int b2_set_box(b2_ctx *c, const double side[3], const double center[3])
 {
     if (!c || !side) return fail(c, B2_EINVAL, "b2_set_box: NULL argument");
-    for (int d = 0; d < 3; d++) {
+    for (int d = 0; d < 3; d++)
         if (!(side[d] > 0.0)) return fail(c, B2_EINVAL, "b2_set_box: side must be > 0");
+    if (c->have_box && c->pos[0] && c->n > 0 &&
+        (side[0] != c->side[0] || side[1] != c->side[1] || side[2] != c->side[2])) {
+        int rc_ = bind_device(c);
+        if (!rc_ && c->have_table) rc_ = bind_table(c);
+        if (!rc_) rc_ = DISPATCH(settle, c);
+        if (rc_) return rc_;
+        const int n = (int)c->n;
+        const double rx = side[0] / c->side[0], ry = side[1] / c->side[1], rz = side[2] / c->side[2];
+        if (c->precision == B2_FP32)
+            LAUNCH(k_rescale_box<float>, cdiv(n, 256), 256, n, rx, ry, rz, (int4 *)c->pos[0], (int4 *)c->pos[1], c->ref);
+        else
+            LAUNCH(k_rescale_box<double>, cdiv(n, 256), 256, n, rx, ry, rz, (double4 *)c->pos[0], (double4 *)c->pos[1], c->ref);
+    }
+    for (int d = 0; d < 3; d++) {
         c->side[d] = side[d];
         c->center[d] = center ? center[d] : 0.0;
     }
@@ -1319,6 +1387,11 @@ int b2_set_pair_table(b2_ctx *c, int nsp, const double *eps, const double *sigma
 {
     if (!c || !eps || !sigma || !rcut) return fail(c, B2_EINVAL, "b2_set_pair_table: NULL argument");
     if (nsp < 1 || nsp > B2_MAXSP) return fail(c, B2_EINVAL, "b2_set_pair_table: 1 <= nsp <= %d", B2_MAXSP);
+    if (c->pos[0] && c->half_pending) {       // an open run is closed with the forces it was run with
+        int rc_ = bind_device(c);
+        if (!rc_) rc_ = DISPATCH(settle, c);
+        if (rc_) return rc_;
+    }
     for (int a = 0; a < nsp * nsp; a++)
         if (!(sigma[a] > 0.0) || !(rcut[a] > 0.0))
             return fail(c, B2_EINVAL, "b2_set_pair_table: sigma and rcut must be > 0");
@@ -1364,6 +1437,11 @@ int b2_set_skin(b2_ctx *c, double skin)
     if (c->have_table) { int rc_ = bind_table(c); if (rc_) return rc_; }                      \
     TableGuard table_guard_(c);
 
+// ... and that must see full-step velocities / the forces of the current configuration
+#define NEED_SETTLED(who)                                                                     \
+    NEED_PARTICLES(who)                                                                       \
+    { int rc_ = DISPATCH(settle, c); if (rc_) return rc_; }
+
 int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel, const int32_t *species,
               const double *mass)
 {
@@ -1384,19 +1462,19 @@ int b2_upload(b2_ctx *c, int64_t n, const double *pos, const double *vel, const 
 
 int b2_update(b2_ctx *c, const double *pos, const double *vel)
 {
-    NEED_PARTICLES("b2_update");
+    NEED_SETTLED("b2_update");
     return DISPATCH(update, c, pos, vel);
 }
 
 int b2_download(b2_ctx *c, double *pos, double *vel, int32_t *image)
 {
-    NEED_PARTICLES("b2_download");
+    NEED_SETTLED("b2_download");
     return DISPATCH(download, c, pos, vel, image);
 }
 
 int b2_scale_velocities(b2_ctx *c, double factor)
 {
-    NEED_PARTICLES("b2_scale_velocities");
+    NEED_SETTLED("b2_scale_velocities");
     if (c->n == 0) return B2_OK;
     c->min_resume = false;
     if (c->precision == B2_FP32)
@@ -1415,7 +1493,7 @@ int b2_mark_reference(b2_ctx *c)
 int b2_compute(b2_ctx *c, int what, double *energy, double *virial, double *stress9, double *forces,
                double *pe, double *vir)
 {
-    NEED_PARTICLES("b2_compute");
+    NEED_SETTLED("b2_compute");
     if (what & ~(B2_ENERGY | B2_FORCES | B2_VIRIAL | B2_STRESS))
         return fail(c, B2_EUNSUPPORTED, "b2_compute: unsupported observable mask 0x%x", what);
     Timed t(c);
@@ -1424,7 +1502,7 @@ int b2_compute(b2_ctx *c, int what, double *energy, double *virial, double *stre
 
 int b2_thermo(b2_ctx *c, double out[B2_T_LEN])
 {
-    NEED_PARTICLES("b2_thermo");
+    NEED_SETTLED("b2_thermo");
     if (!out) return fail(c, B2_EINVAL, "b2_thermo: out is NULL");
     return DISPATCH(thermo, c, out, false, nullptr);
 }
@@ -1455,7 +1533,7 @@ int b2_run_nvt(b2_ctx *c, int64_t steps, double dt, double temperature, double r
 int b2_minimize(b2_ctx *c, int method, int64_t max_steps, double dt, double fn2_tol, int64_t *steps_done,
                 int *converged)
 {
-    NEED_PARTICLES("b2_minimize");
+    NEED_SETTLED("b2_minimize");
     if (max_steps < 0 || !(dt > 0.0) || !steps_done || !converged)
         return fail(c, B2_EINVAL, "b2_minimize: bad argument");
     if (method != B2_MIN_SD && method != B2_MIN_FIRE) return fail(c, B2_EINVAL, "b2_minimize: unknown method %d", method);
@@ -1474,6 +1552,7 @@ int b2_stats(b2_ctx *c, int64_t out[B2_S_LEN])
     out[B2_S_NEIGH_CAP] = c->cap;
     out[B2_S_LIST_MODE] = c->grid.allpairs ? 1 : (c->grid.win ? 2 : 0);
     out[B2_S_NCELLS] = (int64_t)c->grid.nc[0] * c->grid.nc[1] * c->grid.nc[2];
+    out[B2_S_SMALL_BOX] = (c->have_box && c->have_table && 2.0 * c->rcut_max > std::min(c->side[0], std::min(c->side[1], c->side[2]))) ? 1 : 0;
     return B2_OK;
 }
 
@@ -1498,13 +1577,13 @@ int b2_upload_device(b2_ctx *c, int64_t n, const double *pos_dev, const double *
 
 int b2_download_device(b2_ctx *c, double *pos_dev, double *vel_dev, int32_t *image_dev)
 {
-    NEED_PARTICLES("b2_download_device");
+    NEED_SETTLED("b2_download_device");
     return DISPATCH(download, c, pos_dev, vel_dev, image_dev);
 }
 
 int b2_dd_begin(b2_ctx *c, int64_t steps, double dt, int opening_kick)
 {
-    NEED_PARTICLES("b2_dd_begin");
+    NEED_SETTLED("b2_dd_begin");
     if (steps < 0 || !(dt > 0.0)) return fail(c, B2_EINVAL, "b2_dd_begin: steps >= 0 and dt > 0 required");
     return DISPATCH(dd_begin, c, steps, dt, opening_kick);
 }
@@ -2494,7 +2573,7 @@ extern "C" {
 
 int b2_peer_set_ids(b2_ctx *c, const int64_t *gid_dev, const int32_t *image_dev)
 {
-    NEED_PARTICLES("b2_peer_set_ids");
+    NEED_SETTLED("b2_peer_set_ids");
     if (!c->peer_on) return fail(c, B2_ESTATE, "b2_peer_set_ids: call b2_peer_export / b2_peer_connect first");
     if (!gid_dev) return fail(c, B2_EINVAL, "b2_peer_set_ids: gid_dev is NULL");
     int rc = ddr_alloc(c);
@@ -2510,7 +2589,7 @@ int b2_peer_set_ids(b2_ctx *c, const int64_t *gid_dev, const int32_t *image_dev)
 
 int b2_peer_state(b2_ctx *c, int64_t *gid_dev, int32_t *image_dev, int32_t *species_dev, double *mass_dev)
 {
-    NEED_PARTICLES("b2_peer_state");
+    NEED_SETTLED("b2_peer_state");
     if (!c->ddr_ids) return fail(c, B2_ESTATE, "b2_peer_state: no ids resident (b2_peer_set_ids, or a b2_upload since)");
     int rc = c->precision == B2_FP32 ? ImplDdr<float>::state(c, image_dev, species_dev, mass_dev)
                                      : ImplDdr<double>::state(c, image_dev, species_dev, mass_dev);
@@ -2522,7 +2601,7 @@ int b2_peer_state(b2_ctx *c, int64_t *gid_dev, int32_t *image_dev, int32_t *spec
 
 int b2_peer_update(b2_ctx *c, int64_t n_first, const double *pos, const double *vel)
 {
-    NEED_PARTICLES("b2_peer_update");
+    NEED_SETTLED("b2_peer_update");
     if (n_first < 0 || n_first > c->n) return fail(c, B2_EINVAL, "b2_peer_update: n_first out of range");
     if (n_first == 0 || (!pos && !vel)) return B2_OK;
     return c->precision == B2_FP32 ? ImplDdr<float>::update_first(c, n_first, pos, vel)

@@ -16,11 +16,15 @@ Synchronisation contract
     (`b2_thermo`) or O(1): no N-sized copy, no Python loop.
   * once a MUTABLE handle on the host arrays has been handed out —
     `view()` / `dump(view=True)`, `system.position`, an element of
-    `system.particle` — in-place edits cannot be detected
-    (docs/simulations.org:302-308 relies on them), so from then on the host
+    `system.particle` — in-place edits by arbitrary code (the f90 kernels of
+    docs/simulations.org:302-308) cannot be detected, so from then on the host
     arrays are pushed (`b2_update`) before every device operation and pulled
     right after every run; the handles stay valid because downloads write
-    into the same arrays.  `release_views()` ends that mode.
+    into the same arrays.  `release_views()` ends that mode.  With
+    `system.sync = 'tracked'` the handles report numpy writes (item
+    assignment, in-place operators, `out=`) and only arrays that were written
+    are pushed; a writer numpy cannot see must then call `mark_modified()`.
+    Host mirrors live in page-locked memory (b2_host_alloc).
 """
 import copy
 
@@ -104,8 +108,11 @@ class _ParticleList(object):
         s = self._system
         p = self._cache.get(i)
         if p is None:
-            p = _particle_class()(position=s._pos[i], velocity=s._vel[i], species=s._names[s._ids[i]],
+            p = _particle_class()(position=s._pos_user[i], velocity=s._vel_user[i], species=s._names[s._ids[i]],
                                   mass=s._mass[i], radius=s._radius[i])
+            # the reference's Particle takes numpy.asarray of its arguments (particle.py:24-30), which drops
+            # the tracking subclass: hand it the tracked row views again
+            p.position, p.velocity = s._pos_user[i], s._vel_user[i]
             # numpy.asarray keeps the row views (particle.py:24-30)
             p.periodic_image = s._img[i]
             self._cache[i] = p
@@ -133,6 +140,68 @@ def _particle_class():
         return P
     except Exception:
         return Particle
+
+
+class _Tracked(numpy.ndarray):
+
+    """Host array handed out to the user (`view()`, `system.position`, `particle[i].position`): it
+    raises a flag on its System whenever it is written through numpy — item assignment, in-place
+    operators, ufuncs with `out=`, `fill`, `sort`, `numpy.copyto` — so that only arrays that were
+    really edited are pushed to the device.  Views of it stay tracked.  A write that bypasses numpy
+    (a C extension filling the buffer) is not seen: follow it with `system.mark_modified()`."""
+
+    _flag = None
+
+    def __array_finalize__(self, obj):
+        self._flag = getattr(obj, '_flag', None)
+
+    def _touch(self):
+        if self._flag is not None:
+            self._flag[0] = True
+
+    def __setitem__(self, key, value):
+        self._touch()
+        numpy.ndarray.__setitem__(self, key, value)
+
+    def __array_ufunc__(self, ufunc, method, *inputs, out=None, **kwargs):
+        plain = [x.view(numpy.ndarray) if isinstance(x, _Tracked) else x for x in inputs]
+        if out is not None:
+            for o in out:
+                if isinstance(o, _Tracked):
+                    o._touch()
+            kwargs['out'] = tuple(o.view(numpy.ndarray) if isinstance(o, _Tracked) else o for o in out)
+        if method == 'at' and isinstance(inputs[0], _Tracked):
+            inputs[0]._touch()
+        result = getattr(ufunc, method)(*plain, **kwargs)
+        if out is not None:                       # in-place operators must hand the same object back
+            return out[0] if len(out) == 1 else out
+        return result
+
+    def __array_function__(self, func, types, args, kwargs):
+        if func in (numpy.copyto, numpy.put, numpy.place, numpy.putmask, numpy.fill_diagonal) and args and \
+                isinstance(args[0], _Tracked):
+            args[0]._touch()
+        strip = lambda x: x.view(numpy.ndarray) if isinstance(x, _Tracked) else x
+        args = tuple([strip(y) for y in x] if isinstance(x, (list, tuple)) else strip(x) for x in args)
+        return func(*args, **{k: strip(v) for k, v in kwargs.items()})
+
+    def fill(self, value):
+        self._touch()
+        self.view(numpy.ndarray).fill(value)
+
+    def sort(self, *args, **kwargs):
+        self._touch()
+        self.view(numpy.ndarray).sort(*args, **kwargs)
+
+    def put(self, *args, **kwargs):
+        self._touch()
+        self.view(numpy.ndarray).put(*args, **kwargs)
+
+
+def _tracked(array, flag):
+    out = array.view(_Tracked)
+    out._flag = flag
+    return out
 
 
 class System(object):
@@ -182,6 +251,12 @@ class System(object):
         self._host_vel_dirty = False
         self._device_newer = False       # device moved on since the last pull
         self._views_out = False          # a mutable handle on the host arrays is in user hands
+        self._touched = {'pos': [False], 'vel': [False]}      # ... and was written through (see _Tracked)
+        # 'always': while handles are out, both arrays are pushed before every device operation — right for any
+        # writer.  'tracked': only arrays written through numpy since the last push (see _Tracked) are pushed.
+        self.sync = 'always'
+        self._pos_user = _tracked(self._pos, self._touched['pos'])
+        self._vel_user = _tracked(self._vel, self._touched['vel'])
         self._particle = _ParticleList(self)
         self._thermo = None              # cached b2_thermo of the current state
 
@@ -210,8 +285,13 @@ class System(object):
     def _push(self):
         """Host -> device, if the host side was (or may have been) touched."""
         if self._views_out:
-            self._pull()
-            self._host_pos_dirty = self._host_vel_dirty = True
+            # handles on the host arrays are in user hands
+            if self.sync == 'tracked':        # push what was written through them (numpy writes only)
+                self._host_pos_dirty |= self._touched['pos'][0]
+                self._host_vel_dirty |= self._touched['vel'][0]
+            else:                             # any writer, f2py / C kernels included: push everything
+                self._host_pos_dirty = self._host_vel_dirty = True
+            self._touched['pos'][0] = self._touched['vel'][0] = False
         if self._host_pos_dirty or self._host_vel_dirty:
             self._engine.update(self._pos if self._host_pos_dirty else None,
                                 self._vel if self._host_vel_dirty else None)
@@ -230,6 +310,11 @@ class System(object):
         """A mutable handle on the host arrays is about to leave our hands."""
         self._pull()
         self._views_out = True
+
+    def mark_modified(self, position=True, velocity=True):
+        """The host arrays were written by something numpy cannot see (a C extension, a raw buffer)."""
+        self._touched['pos'][0] |= bool(position)
+        self._touched['vel'][0] |= bool(velocity)
 
     def release_views(self):
         """Promise that host arrays handed out earlier are no longer edited:
@@ -257,12 +342,12 @@ class System(object):
     def position(self):
         """(N, 3) host array, mutable: editing it in place edits the system."""
         self._hand_out()
-        return self._pos
+        return self._pos_user
 
     @property
     def velocity(self):
         self._hand_out()
-        return self._vel
+        return self._vel_user
 
     @property
     def image(self):

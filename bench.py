@@ -334,9 +334,10 @@ def plugin_e2e(lib, precision, pos, spe, side, vel, chunks, device=0, views=True
         Simulation(B200(System(...))).run(steps)         (atooms/simulation/core.py:308-425)
     with the reference's own driver, its speedometer on (which cuts the run into steps / 20 chunks,
     core.py:107-109), write_thermo every INNER steps, and — `views` — an observer that works on the
-    host arrays the way docs/simulations.org:274-308 teaches (system.view(...)): while such views are in
-    user hands the System pushes positions and velocities host -> device before every backend.run() and
-    pulls them back after it.  Host mirrors are page-locked (b2_host_alloc).  Copies are counted where they
+    host arrays the way docs/simulations.org:274-308 teaches (system.view(...)): it reads the positions and
+    rescales the velocities in place.  While such views are in user hands the System pushes what was written
+    through them host -> device before the next device operation and pulls both arrays back after every
+    backend.run().  Host mirrors are page-locked (b2_host_alloc).  Copies are counted where they
     happen (Engine.update / download_into).  Returns rate, seconds, bytes per INNER steps, driver name."""
     import shutil
     from atooms_b200 import B200, System, Cell
@@ -345,6 +346,7 @@ def plugin_e2e(lib, precision, pos, spe, side, vel, chunks, device=0, views=True
     system = System(pos, names, Cell(side), velocity=vel, model=model, precision=precision, skin=SKIN,
                     device=device, library=lib)
     bck = B200(system, model, dt=DT, skin=SKIN, precision=precision, device=device, library=lib)
+    system.sync = 'tracked'          # push only what numpy wrote through the views (atooms_b200/system.py)
     eng = system._engine
     count = {'h2d': 0, 'd2h': 0, 'runs': 0}
     upd, dwn, run = eng.update, eng.download_into, bck.run
@@ -364,8 +366,11 @@ def plugin_e2e(lib, precision, pos, spe, side, vel, chunks, device=0, views=True
     seen = []
 
     def host_observer(sim):
+        # host-side work on the live arrays, the way docs/simulations.org:274-308 teaches: read the positions,
+        # rescale the velocities IN PLACE (factor 1: the run stays NVE); the edit must reach the device
         x, v = sim.system.view('position'), sim.system.view('velocity')
-        seen.append(float(x[0, 0]) + float(v[0, 0]))
+        seen.append(float(x[::4096, 0].sum()))
+        v *= 1.0
     simulation = reference_drivers()
     n = len(spe)
     tmp = tempfile.mkdtemp()
@@ -625,8 +630,9 @@ def main():
                      'h2d_bytes_per_step': int(r['plugin']['h2d']), 'd2h_bytes_per_step': int(r['plugin']['d2h']),
                      'steps': r['e2e_steps'], 'backend_run_calls': r['plugin']['backend_run_calls'],
                      'through': 'Simulation(B200(System)).run(): ' + r['plugin']['driver'] +
-                                ', host views of position and velocity held by an observer (pushed before and '
-                                'pulled after every backend.run)'}
+                                ', an observer holds host views, reads the positions and rescales the velocities '
+                                'in place every chunk (sync = tracked: what was written is pushed before, both '
+                                'arrays are pulled after every backend.run)'}
                     if 'plugin' in r else
                     {'value': r['e2e'], 'unit': 'particle-timesteps/s',
                      'h2d_bytes_per_step': int(r['h2d']), 'd2h_bytes_per_step': int(r['d2h']),

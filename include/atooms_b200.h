@@ -84,6 +84,7 @@ extern "C" {
 #define B2_S_LIST_MODE   5   /* 0 = cell list, 1 = all-pairs (box < 3 cells wide),
                                 2 = cell list with windowed rows (CUDA engine, >= 8 cells per axis) */
 #define B2_S_NCELLS      6
+#define B2_S_SMALL_BOX   7   /* 1: some side < 2 r_cut,max (single minimum image only) */
 #define B2_S_LEN        16
 
 typedef struct b2_ctx b2_ctx;
@@ -116,7 +117,17 @@ int b2_set_stream(b2_ctx *ctx, void *cuda_stream);
 
 /* ---- model -------------------------------------------------------------- */
 
-/* Orthorhombic periodic cell: atooms/system/cell.py:13-33 (side, center).   */
+/* Orthorhombic periodic cell: atooms/system/cell.py:13-33 (side, center).
+ * All interactions follow the MINIMUM-IMAGE convention (particle.py:129-130):
+ * exact while every side >= 2 r_cut,max; in a smaller box only the nearest
+ * image of a pair interacts (the reference's own FCC N=108 fixture has
+ * L = 4.76 < 5; none of its pairs has two images within the cut-off).
+ * B2_S_SMALL_BOX of b2_stats is 1 in that case.
+ * With particles RESIDENT a new box is an affine rescaling about the centre:
+ * fractional coordinates are kept (positions and the rmsd origin scale with
+ * the sides, velocities and box-crossing counters are untouched, the list
+ * is rebuilt) — the volume move of a barostat.  To replace the particles as
+ * well, call b2_upload afterwards, as before.                               */
 int b2_set_box(b2_ctx *ctx, const double side[3], const double center[3]);
 
 /* 12-6 Lennard-Jones table for `nsp` species, row-major nsp x nsp:

@@ -151,8 +151,18 @@ int b2_set_stream(b2_ctx *c, void *s) { (void)c; (void)s; return B2_OK; }
 int b2_set_box(b2_ctx *c, const double side[3], const double center[3])
 {
     if (!c || !side) return fail(c, B2_EINVAL, "b2_set_box: NULL argument");
-    for (int d = 0; d < 3; d++) {
+    for (int d = 0; d < 3; d++)
         if (!(side[d] > 0.0)) return fail(c, B2_EINVAL, "b2_set_box: side must be > 0");
+    if (c->have_box && c->pos && c->n > 0) {
+        /* resident particles: affine rescaling about the centre (see include/atooms_b200.h) */
+        for (int64_t i = 0; i < c->n; i++)
+            for (int d = 0; d < 3; d++) {
+                double r = side[d] / c->side[d], nc = center ? center[d] : 0.0;
+                c->pos[3 * i + d] = nc + (c->pos[3 * i + d] - c->center[d]) * r;
+                c->ref[3 * i + d] = nc + (c->ref[3 * i + d] - c->center[d]) * r;
+            }
+    }
+    for (int d = 0; d < 3; d++) {
         c->side[d] = side[d];
         c->center[d] = center ? center[d] : 0.0;
     }
@@ -795,6 +805,11 @@ int b2_stats(b2_ctx *c, int64_t out[B2_S_LEN])
     out[B2_S_NEIGH_CAP] = c->max_count;
     out[B2_S_LIST_MODE] = c->list_mode;
     out[B2_S_NCELLS] = c->ncells;
+    {
+        double m = c->side[0] < c->side[1] ? c->side[0] : c->side[1];
+        if (c->side[2] < m) m = c->side[2];
+        out[B2_S_SMALL_BOX] = (c->have_box && c->have_table && 2.0 * c->rcut_max > m) ? 1 : 0;
+    }
     return B2_OK;
 }
 

@@ -155,6 +155,33 @@ def test_sync_contract(oracle_lib):
     s.particle[1].position[1] += 0.05             # through the materialised Particle list
     assert abs(s.potential_energy() - e0) > 1e-6
     s.particle[1].position[1] -= 0.05
+    # tracked mode: only what was written through numpy is pushed
+    s.sync = 'tracked'
+    s.potential_energy()                     # (pushes the edit above)
+    calls = []
+    update = s._engine.update
+    s._engine.update = lambda position=None, velocity=None: (calls.append((position is not None, velocity is not None)),
+                                                           update(position, velocity))[1]
+    assert abs(s.potential_energy() - e0) < 1e-9 and calls == []          # nothing written: nothing pushed
+    vel = s.view('velocity')
+    vel *= 1.0                                                             # in-place operator on the view
+    s.kinetic_energy()
+    assert calls == [(False, True)]
+    pos[3] = pos[3] + 0.01
+    numpy.add(pos[4], 0.01, out=pos[4])
+    assert abs(s.potential_energy() - e0) > 1e-6 and calls[-1] == (True, False)
+    pos[3] -= 0.01
+    pos[4] -= 0.01
+    assert abs(s.potential_energy() - e0) < 1e-9
+    raw = pos.view(numpy.ndarray)                                          # a writer numpy cannot see
+    raw[5, 0] += 0.05
+    assert abs(s.potential_energy() - e0) < 1e-9
+    s.mark_modified(velocity=False)
+    assert abs(s.potential_energy() - e0) > 1e-6
+    raw[5, 0] -= 0.05
+    s.mark_modified()
+    s._engine.update = update
+    s.sync = 'always'
     bck.run(5)
     assert not numpy.allclose(s.dump('position'), golden('ka_N256_rumd')['position'])
     # velocities: set_temperature hits the target exactly, scale_velocities runs on the device
