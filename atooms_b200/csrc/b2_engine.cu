@@ -335,10 +335,16 @@ template <typename R> struct Impl {
         }
         // windowed list (b2_win.cuh): an even number (>= 8) of cells per axis, cut into super-blocks of 4 (the
         // last one of an axis may hold 2); the cells grow by at most 1 / nc to make it so.  B2_LIST_GLOBAL=1 keeps the global-index list (A/B timing).
-        static const bool force_global = getenv("B2_LIST_GLOBAL") && atoi(getenv("B2_LIST_GLOBAL")) != 0;
+        const bool force_global = getenv("B2_LIST_GLOBAL") && atoi(getenv("B2_LIST_GLOBAL")) != 0;
         g.win = 0;
         g.nsb[0] = g.nsb[1] = g.nsb[2] = 0;
-        if (!g.allpairs && g.m == 2 && !c->win_off && !force_global && g.nc[0] >= 8 && g.nc[1] >= 8 && g.nc[2] >= 8) {
+        // Measured: fp32, one domain filling its box: step 0.190 ms against 0.207 with the global
+        // list.  fp64 windows are twice as large (3 blocks per SM): 0.61 against 0.47 ms, so fp64 keeps the
+        // global list unless B2_LIST_WINDOWED=1; so does a domain that fills only part of its box (a slab of a
+        // decomposed system: half of the super-blocks are empty launches), see grow_after_overflow.
+        const bool force_win = getenv("B2_LIST_WINDOWED") && atoi(getenv("B2_LIST_WINDOWED")) != 0;
+        if (!g.allpairs && g.m == 2 && !c->win_off && !force_global && (c->precision == B2_FP32 || force_win) &&
+            g.nc[0] >= 8 && g.nc[1] >= 8 && g.nc[2] >= 8) {
             double cellvol = 1.0;
             for (int d = 0; d < 3; d++) cellvol *= c->side[d] / (g.nc[d] & ~1);
             // records of a window (8^3 cells) at the mean density, with room for fluctuations; a slab of a
@@ -419,7 +425,13 @@ template <typename R> struct Impl {
             const size_t rec = sizeof(P4);
             const size_t lim = std::min<size_t>((c->smem_optin > 4096 ? c->smem_optin - 4096 : 0) / rec, 65528);
             const size_t want = ((size_t)(c->hctl->win_max * 1.1) + 64 + 7) / 8 * 8;
-            if (want > lim) {
+            // windows far above the mean density: the particles fill only part of the box (a slab of a decomposed
+            // system, a droplet) and many super-blocks are empty — the global list serves such systems better
+            const bool force_win = getenv("B2_LIST_WINDOWED") && atoi(getenv("B2_LIST_WINDOWED")) != 0;
+            const double expect = (double)c->n / (c->side[0] * c->side[1] * c->side[2]) * 512.0 *
+                                  (c->side[0] / g.nc[0]) * (c->side[1] / g.nc[1]) * (c->side[2] / g.nc[2]);
+            const bool sparse = (double)c->hctl->win_max > 1.6 * expect + 256.0 && !force_win;
+            if (want > lim || sparse) {
                 c->win_off = true;
                 c->cap = 0;
                 if ((rc = setup_grid(c))) return rc;

@@ -76,7 +76,8 @@ def test_single_point_and_list_at_bench_shape(cuda_lib, oracle_lib, workload, pr
     assert cnt.shape == (n,) and numpy.array_equal(cnt, rcnt)
     assert nbr.shape == rnbr.shape and numpy.array_equal(nbr, rnbr)
     st = eng.stats()
-    assert st['list_mode'] == 2 and st['max_neighbors'] == int(cnt.max())     # 2: the windowed list (b2_win.cuh)
+    # fp32: the windowed list (b2_win.cuh), fp64: the global-index list
+    assert st['list_mode'] == (2 if precision == 32 else 0) and st['max_neighbors'] == int(cnt.max())
     eng.close()
 
 

@@ -103,9 +103,30 @@ def test_single_point_replicated(cuda_lib, oracle_lib, precision):
     ref = make_engine(oracle_lib, d, ka, 64).compute(per_particle=True, stress=True)
     assert_observables(got, ref, precision)
     st = eng.stats()
-    # half-width cells (r_list / 2), an even number per axis (here 14 = 3 super-blocks of 4 and one of 2):
-    # the windowed list
-    assert st['list_mode'] == 2 and st['ncells'] == 14 ** 3
+    # half-width cells (r_list / 2), an even number per axis (here 14 = 3 super-blocks of 4 and one of 2);
+    # fp32 runs on the windowed list, fp64 on the global-index list
+    assert st['list_mode'] == (2 if precision == 32 else 0) and st['ncells'] == 14 ** 3
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+@pytest.mark.parametrize('kind', ['windowed', 'global'])
+def test_both_list_formats_in_both_precisions(cuda_lib, oracle_lib, precision, kind, monkeypatch):
+    """The defaults pick one list format per precision; the other one stays a supported
+    path (B2_LIST_WINDOWED / B2_LIST_GLOBAL) and must give the same physics: single point, bit-exact
+    list, and an NVE stretch with refreshes whose final configuration is re-evaluated from scratch."""
+    monkeypatch.setenv('B2_LIST_WINDOWED' if kind == 'windowed' else 'B2_LIST_GLOBAL', '1')
+    d = rounded(replicated('ka_N1200', 2, 0.01, 2), precision)
+    ka = onp.kob_andersen()
+    eng = make_engine(cuda_lib, d, ka, precision)
+    got = eng.compute(per_particle=True, stress=True)
+    assert eng.stats()['list_mode'] == (2 if kind == 'windowed' else 0)
+    assert_observables(got, make_engine(oracle_lib, d, ka, 64).compute(per_particle=True, stress=True), precision)
+    for a, b in zip(eng.neighbors(), make_engine(oracle_lib, d, ka, precision).neighbors()):
+        assert numpy.array_equal(a, b)
+    eng.run_nve(300, 0.002)
+    assert eng.stats()['rebuilds'] >= 4
+    pos, vel, _ = eng.download()
+    assert_observables(eng.compute(), make_engine(oracle_lib, dict(d, position=pos, velocity=vel), ka, 64).compute(), precision)
 
 
 @pytest.mark.parametrize('precision', [64, 32])
