@@ -414,6 +414,131 @@ def plugin_e2e(lib, precision, pos, spe, side, vel, chunks, device=0, views=True
     return out
 
 
+def c5_strong(lib, rank, world, local_rank, steps=200, warmup=100, precision=32, cells=126):
+    """BASELINE.json configs[4]: LJ FCC N = 4 * 126^3 = 8 001 504, rho = 0.85, cut &
+    shifted 2.5, NVE dt = 0.005, skin 0.3, jitter +-0.05 a, T = 1.0 — ONE system over all ranks (strong
+    scaling: the total is fixed), slabs along x; with one rank the plain engine holds all 8M particles.
+    The configuration north_star quotes the 8-GPU target on.  Returns the detail block (rank 0)."""
+    import torch
+    import torch.distributed as dist
+    from atooms_b200 import capi, models
+    a = (4.0 / 0.85) ** (1.0 / 3.0)
+    L = cells * a
+    basis = numpy.array([[0, 0, 0], [0.5, 0.5, 0], [0.5, 0, 0.5], [0, 0.5, 0.5]])
+    lo, hi = (rank * cells) // world, ((rank + 1) * cells) // world
+    grid = numpy.stack(numpy.meshgrid(numpy.arange(lo, hi), numpy.arange(cells), numpy.arange(cells),
+                                      indexing='ij'), -1).reshape(-1, 3)
+    pos = ((grid[:, None, :] + basis[None, :, :]) * a).reshape(-1, 3) - 0.5 * L
+    gid = (((grid[:, 0] * cells + grid[:, 1]) * cells + grid[:, 2])[:, None] * 4 + numpy.arange(4)[None, :]).reshape(-1)
+    pos += numpy.random.default_rng(5 + 1000 * rank).uniform(-0.05 * a, 0.05 * a, size=pos.shape)
+    vel = numpy.random.default_rng(6 + 1000 * rank).normal(0.0, 1.0, size=pos.shape)
+    vel -= vel.mean(axis=0)
+    vel *= numpy.sqrt(1.0 / (numpy.sum(vel * vel) / (3 * (len(vel) - 1))))
+    spe = numpy.zeros(len(pos), dtype=numpy.int32)
+    side = numpy.array([L, L, L])
+    model = models.lennard_jones(2.5, True)
+    dt = 0.005
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        from atooms_b200.dd import SlabDomain
+        dom = SlabDomain(pos, vel, spe, side, model=model, dt=dt, skin=SKIN, precision=precision, gid=gid, library=lib)
+        t0 = dom.thermo()
+        dom.run(warmup)
+        r0 = dom.refreshes
+        torch.cuda.synchronize()
+        dist.barrier()
+        ev0.record()
+        dom.run(steps)
+        ev1.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        ms = torch.tensor([ev0.elapsed_time(ev1)], device='cuda')
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = float(ms)
+        t1 = dom.thermo()
+        ntot, refreshes = t1['n'], dom.refreshes - r0
+        comm = 'peer-memory mailboxes' if dom._peer else ('NCCL from C' if dom._fast else 'torch.distributed')
+        dom.close()
+    else:
+        eng = capi.Engine(precision, device=local_rank, library=lib)
+        eng.set_box(side)
+        eng.set_pair_table(model.eps, model.sigma, model.rcut, True)
+        eng.set_skin(SKIN)
+        eng.upload(pos, spe, vel)
+        t0 = eng.thermo()
+        eng.run_nve(warmup, dt)
+        r0 = eng.stats()['rebuilds']
+        ms = 0.0
+        for _ in range(max(1, steps // 100)):
+            eng.run_nve(100, dt)
+            ms += eng.last_timing()[0]
+        steps = max(1, steps // 100) * 100
+        t1 = eng.thermo()
+        ntot, refreshes, comm = len(spe), eng.stats()['rebuilds'] - r0, 'none'
+        eng.close()
+    if rank != 0:
+        return None
+    return {'config': 'LJ FCC N=%d rho=0.85 NVE dt=0.005 skin 0.3, cut&shifted 2.5 (BASELINE.json configs[4])' % ntot,
+            'scaling': 'strong', 'value': ntot * steps / (ms * 1e-3), 'unit': 'particle-timesteps/s',
+            'ms_per_md_step': ms / steps, 'md_steps': steps, 'refreshes': int(refreshes), 'comm': comm,
+            'dtype': 'f%d' % precision,
+            'E_per_particle_start': (t0['kinetic'] + t0['potential']) / ntot,
+            'E_per_particle_end': (t1['kinetic'] + t1['potential']) / ntot}
+
+
+def c4_replicas(lib, rank, world, local_rank, nrep=4096, check=16):
+    """BASELINE.json configs[3]: FIRE minimisation of 4096 Kob-Andersen N=150 replicas
+    (frame k mod 80 of the reference's data/ka_N150_rho1.200.xyz, jitter +-0.05, seed 100 + k) to
+    sum F^2 / N < 1e-10, dealt round-robin over the ranks with no communication ("replicas only").  The
+    first `check` replicas of rank 0 are minimised by the CPU oracle as well and compared."""
+    import torch
+    import torch.distributed as dist
+    from atooms_b200 import capi
+    from atooms_b200.batch import ReplicaEnsemble
+    fr = numpy.load(os.path.join(ROOT, 'tests', 'golden', 'ka_N150_frames.npz'))
+    mine = numpy.arange(nrep)[rank::world]
+    pos = numpy.empty((len(mine), 150, 3))
+    for q, k in enumerate(mine):
+        pos[q] = fr['position'][k % 80] + numpy.random.default_rng(100 + int(k)).uniform(-0.05, 0.05, size=(150, 3))
+    out = {}
+    for precision, tol in ((64, 1e-10), (32, 1e-7)):
+        ens = ReplicaEnsemble(pos, fr['species'], fr['side'], 'kob_andersen', precision=precision, device=local_rank,
+                              library=lib)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        r = ens.minimize('fire', tolerance=tol, steps=100000)
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        tot = torch.tensor([float(r['steps'].sum()), float(r['converged'].sum()), float(r['energy'].sum())],
+                           dtype=torch.float64, device='cuda')
+        w = torch.tensor([wall], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(tot)
+            dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        wall = float(w)
+        it = float(tot[0])
+        block = {'tolerance': tol, 'seconds': wall, 'replicas_per_s': nrep / wall, 'converged': int(tot[1]),
+                 'iterations_total': int(it), 'particle_iterations_per_s': it * 150 / wall,
+                 'pair_evaluations_per_s': it * 150 * 149 / wall, 'mean_U_per_particle': float(tot[2]) / nrep / 150}
+        if rank == 0 and precision == 64 and check:
+            olib, _ = oracle_library(host_cores())
+            ref = ReplicaEnsemble(pos[:check], fr['species'], fr['side'], 'kob_andersen', precision=64, library=olib)
+            ro = ref.minimize('fire', tolerance=tol, steps=100000)
+            block['parity'] = {'replicas_checked': check,
+                               'max_abs_dU_per_particle': float(numpy.abs(r['energy'][:check] - ro['energy']).max() / 150),
+                               'iterations_equal': bool(numpy.array_equal(r['steps'][:check], ro['steps']))}
+            ref.close()
+        out['fp%d' % precision] = block
+        ens.close()
+    if rank != 0:
+        return None
+    out['config'] = '%d x Kob-Andersen N=150 (rho 1.2, L=5) FIRE to sum F^2/N < tol (BASELINE.json configs[3]), ' \
+                    'replica k on rank k mod %d, no communication' % (nrep, world)
+    return out
+
+
 def atooms_model():
     from atooms_b200 import models
     return models.PairModel(KA_EPS, KA_SIG, 2.5 * KA_SIG, True, name='kob_andersen')
@@ -427,6 +552,7 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--precision', type=int, default=32, choices=[32, 64])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--headline-only', action='store_true', help='skip the C4 / C5 legs (detail.c4_replicas, detail.c5_strong)')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
 
@@ -611,6 +737,10 @@ def main():
             results[precision]['plugin']['chunks'] = pchunks
 
     parity = dd_parity(lib, rank, world) if world > 1 else None
+    extra = {}
+    if not args.headline_only:
+        extra['c5_strong'] = c5_strong(lib, rank, world, local_rank)
+        extra['c4_replicas'] = c4_replicas(lib, rank, world, local_rank)
 
     if rank == 0:
         r = results[args.precision]
@@ -669,6 +799,9 @@ def main():
             line['detail']['e2e_plugin_resident'] = {'value': pr['value'], 'h2d_bytes_per_step': int(pr['h2d']),
                                                      'd2h_bytes_per_step': int(pr['d2h']),
                                                      'backend_run_calls': pr['backend_run_calls']}
+        for key, block in extra.items():
+            if block is not None:
+                line['detail'][key] = block
         if parity is not None:
             line['parity'] = parity
         if not args.no_cpu_baseline:
