@@ -146,10 +146,10 @@ def measured_peak():
     return 6650.0, 'fallback (B200_PROFILING.md: 6.65 TB/s)'
 
 
-def ncu_traffic(precision, n):
-    """DRAM bytes per k_step_nve launch from the committed ncu capture (same workload), else None."""
+def ncu_traffic(kernel, precision, n):
+    """DRAM bytes per launch of the step kernel from the committed ncu capture (same workload), else None."""
     try:
-        t = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))['k_step_nve_fp%d' % precision]
+        t = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))['%s_fp%d' % (kernel, precision)]
         return float(t['bytes_per_launch']) if int(t['particles']) == int(n) else None
     except Exception:
         return None
@@ -754,6 +754,8 @@ def main():
         else:
             kernel_ms = r['ms'] / (args.steps * INNER)
         achieved = B_ALG[args.precision] * (r['ntot'] / world) / (kernel_ms * 1e-3) / 1e9
+        # list_mode 2: the windowed list and its kernels (csrc/b2_win.cuh); else the global-index list
+        step_kernel = 'k_step_win' if r['stats'].get('list_mode') == 2 else 'k_step_nve'
         line = {
             'metric': 'particle-timesteps/s', 'value': r['value'], 'unit': 'particle-timesteps/s',
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
@@ -774,8 +776,9 @@ def main():
             'gpu_launches': int(r['launches']),
             'clocks': clocks,
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                         'frac': achieved / peak, 'traffic': ncu_traffic(args.precision, n) if world == 1 else None,
-                         'kernel': 'k_step_nve',
+                         'frac': achieved / peak,
+                         'traffic': ncu_traffic(step_kernel, args.precision, n) if world == 1 else None,
+                         'kernel': step_kernel,
                          'kernel_ms': kernel_ms, 'bytes_per_particle_step': B_ALG[args.precision],
                          'peak_source': peak_src,
                          'step_kernel_share': (r['prof']['ms_steps'] / r['ms']) if world == 1 else None,
