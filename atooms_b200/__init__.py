@@ -10,7 +10,7 @@ __version__ = '0.1.0'
 
 from . import capi, models                                   # noqa: E402,F401
 from .models import PairModel, lennard_jones, kob_andersen   # noqa: E402,F401
-from .system import System, Cell, Particle, Thermostat       # noqa: E402,F401
+from .system import System, Cell, Particle, Thermostat, Barostat   # noqa: E402,F401
 from .interaction import Interaction                          # noqa: E402,F401
 from .trajectory import (Trajectory, TrajectoryRUMD, TrajectoryRam, TrajectoryNeighbors,  # noqa: E402,F401
                          Snapshot)

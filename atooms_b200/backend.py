@@ -59,13 +59,17 @@ class B200(object):
     version = __version__
 
     def __init__(self, inp, model='lennard_jones', dt=0.002, skin=0.3, precision='fp64', device=0,
-                 library=None, thermostat='nose-hoover'):
+                 library=None, thermostat='nose-hoover', compressibility=0.1, barostat_interval=10):
         """`thermostat` names the scheme used WHEN `system.thermostat` is set (the reference's
         backends switch to NVT on that attribute, atooms/backends/lammps.py:229-241):
         'nose-hoover' (LAMMPS `fix nvt`, RUMD IntegratorNVT) or 'berendsen'."""
         if thermostat not in ('nose-hoover', 'berendsen'):
             raise ValueError("thermostat must be 'nose-hoover' or 'berendsen'")
         self.thermostat_kind = capi.NVT_NOSE_HOOVER if thermostat == 'nose-hoover' else capi.NVT_BERENDSEN
+        # NPT (system.barostat set as well): isotropic weak-coupling volume moves every `barostat_interval`
+        # steps, mu^3 = 1 - compressibility * (interval * dt / relaxation_time) * (P0 - P)
+        self.compressibility = float(compressibility)
+        self.barostat_interval = int(barostat_interval)
         self.model = models.get(model)
         self.timestep = float(dt)
         self.skin = float(skin)
@@ -110,7 +114,13 @@ class B200(object):
         s = self._system
         s._push()
         th = s.thermostat
-        if th is not None and getattr(th, 'temperature', None) is not None:
+        ba = getattr(s, 'barostat', None)
+        if ba is not None and getattr(ba, 'pressure', None) is not None:
+            # NPT: `fix 1 all npt temp T T tau_T iso P P tau_P` in the reference (lammps.py:229-233)
+            if th is None or getattr(th, 'temperature', None) is None:
+                raise ValueError('a barostat needs a thermostat as well (NPT), as in atooms/backends/lammps.py:229-233')
+            self._run_npt(int(steps), th, ba)
+        elif th is not None and getattr(th, 'temperature', None) is not None:
             # NVT: `fix 1 all nvt temp T T relaxation_time` (lammps.py:233-235)
             s._engine.run_nvt(int(steps), self.timestep, th.temperature,
                               getattr(th, 'relaxation_time', None) or 100 * self.timestep, self.thermostat_kind)
@@ -119,6 +129,25 @@ class B200(object):
         if steps > 0:
             s._advanced()
         self.steps += int(steps)
+
+    def _run_npt(self, steps, th, ba):
+        """Thermostatted dynamics (the fused NVT step kernel) with an isotropic Berendsen barostat: every
+        `barostat_interval` steps the instantaneous pressure (device reduction) rescales the box and, affinely,
+        the particles (b2_set_box on resident particles; the list is rebuilt).  Weak coupling relaxes <P> to
+        the target like the reference's `fix npt` does, with smaller volume fluctuations than its
+        Nose-Hoover barostat: the same state point, not the same fluctuation spectrum."""
+        s = self._system
+        tau_t = getattr(th, 'relaxation_time', None) or 100 * self.timestep
+        tau_p = getattr(ba, 'relaxation_time', None) or 1000 * self.timestep
+        done = 0
+        while done < steps:
+            n = min(self.barostat_interval, steps - done)
+            s._engine.run_nvt(n, self.timestep, th.temperature, tau_t, self.thermostat_kind)
+            s._advanced()
+            done += n
+            mu3 = 1.0 - self.compressibility * (n * self.timestep / tau_p) * (ba.pressure - s.pressure)
+            mu3 = min(max(mu3, 0.97), 1.03)                 # at most 1 % in length per move
+            s.set_box(s.cell.side * mu3 ** (1.0 / 3.0))
 
     # binary checkpoints: the reference's fallback goes through TrajectoryXYZ and
     # breaks under numpy >= 2 (simulation/core.py:225-234; SURVEY.md 3.3b)

@@ -32,7 +32,7 @@ import numpy
 
 from . import capi, models
 
-__all__ = ['System', 'Cell', 'Particle', 'Thermostat']
+__all__ = ['System', 'Cell', 'Particle', 'Thermostat', 'Barostat']
 
 
 class Cell(object):
@@ -86,6 +86,20 @@ class Thermostat(object):
 
     def __init__(self, temperature=None, relaxation_time=1.0):
         self.temperature = temperature
+        self.relaxation_time = relaxation_time
+
+
+class Barostat(object):
+    """Target pressure and coupling time, the attributes of atooms.system.reservoir.Barostat
+    (reservoir.py:43-54) that backends read (lammps.py:229-233).  With `system.thermostat` AND
+    `system.barostat` set, `B200.run` samples the NPT ensemble, as the reference's backends do."""
+
+    def __init__(self, pressure, name='', mass=1.0, coordinate=1.0, momentum=1.0, relaxation_time=1.0):
+        self.name = name
+        self.pressure = pressure
+        self.coordinate = numpy.asarray(coordinate)
+        self.momentum = numpy.asarray(momentum)
+        self.mass = numpy.asarray(mass)
         self.relaxation_time = relaxation_time
 
 
@@ -427,6 +441,20 @@ class System(object):
         t_old = self.temperature
         if t_old > 0.0:
             self.scale_velocities((temperature / t_old) ** 0.5)
+
+    def set_box(self, side):
+        """New cell sides with the particles following affinely (fractional coordinates kept): the volume
+        move of a barostat, `System.set_density` of the reference (system.py:150-157).  On the device."""
+        self._push()
+        side = numpy.asarray(side, dtype=numpy.float64) * numpy.ones(3)
+        self._engine.set_box(side, self.cell.center)
+        self.cell.side = side.copy()
+        if self.interaction is not None:
+            self.interaction._invalidate()
+        self._advanced()
+
+    def set_density(self, rho):
+        self.set_box(self.cell.side * (self.density / rho) ** (1.0 / 3.0))
 
     def scale_velocities(self, factor):
         # system.py:227-230, on the device

@@ -211,6 +211,39 @@ def test_thermostat_switches_the_backend_to_nvt(oracle_lib, pins):
         B200(bck.system, model, thermostat='langevin', library=oracle_lib)
 
 
+def test_barostat_switches_the_backend_to_npt(oracle_lib):
+    """`system.thermostat` and `system.barostat` together turn the run into NPT, as in the reference's
+    backends (atooms/backends/lammps.py:229-233): the pressure relaxes to the target, the box follows."""
+    from atooms_b200 import Thermostat, Barostat
+    model = atooms_b200.lennard_jones(2.5, shifted=True)
+    bck = B200(make_system('lj_N1000', oracle_lib, model), model, dt=0.004, library=oracle_lib)
+    s = bck.system
+    s.set_temperature(2.0, seed=1)
+    s.thermostat = Thermostat(2.0, relaxation_time=0.2)
+    bck.run(300)
+    p_nvt, v0 = s.pressure, s.cell.volume
+    assert p_nvt > 10.0 and abs(s.density - 1.0) < 1e-12
+    s.barostat = Barostat(4.0, relaxation_time=0.5)
+    P = []
+    for _ in range(24):
+        bck.run(100)
+        P.append(s.pressure)
+    assert abs(numpy.mean(P[12:]) - 4.0) < 0.4                    # <P> -> target
+    assert s.cell.volume > 1.2 * v0 and abs(s.density - 1000 / s.cell.volume) < 1e-12
+    pos = s.dump('position')
+    assert numpy.abs(pos).max() <= 0.5 * s.cell.side[0] * (1 + 1e-9)   # the particles followed the box
+    # the affine move itself: fractional coordinates kept, energy is that of the scaled configuration
+    frac = s.dump('position') / s.cell.side
+    s.set_density(0.9)
+    assert abs(s.density - 0.9) < 1e-12 and numpy.abs(s.dump('position') / s.cell.side - frac).max() < 1e-9
+    ref = System(s.dump('position'), s.species, Cell(s.cell.side), model=model, library=oracle_lib)
+    ref.interaction = Interaction(model, library=oracle_lib)
+    assert abs(s.potential_energy() - ref.potential_energy()) < 1e-6 * abs(ref.potential_energy())
+    s.thermostat = None
+    with pytest.raises(ValueError):
+        bck.run(10)                                              # a barostat alone is not an ensemble we run
+
+
 def test_deepcopy_and_reassign(oracle_lib):
     """tests/test_rumd.py:178-194."""
     bck = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib)
