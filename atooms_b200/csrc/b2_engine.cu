@@ -21,7 +21,6 @@
 #include <vector>
 
 #define MAX_RED_BLOCKS 1024
-#define WIN_PAD_INTS 1024         // windowed list: unused ints before and behind the rows (read-ahead of the row walks)
 
 struct b2_ctx {
     int device = 0, precision = 64, sms = 148;
@@ -82,8 +81,7 @@ struct b2_ctx {
     int *nbr = nullptr, *nnb = nullptr;
     int cap = 0;
     // windowed list (b2_win.cuh)
-    int *b8start = nullptr, *tile_base = nullptr, *sbt = nullptr, *sb_li = nullptr, *sb_slot = nullptr;
-    size_t sb_slot_alloc = 0;
+    int *b8start = nullptr, *tile_base = nullptr, *sbt = nullptr;
     int nb8codes = 0, nsb_total = 0, win_tab_alloc = 0, win_sb_alloc = 0;
     bool win_off = false;            // windows do not fit: this context keeps the global-index list
     size_t smem_optin = 0;
@@ -394,12 +392,6 @@ template <typename R> struct Impl {
                 if ((rc = dev_alloc(c, &c->sbt, (size_t)c->nsb_total * SBT_STRIDE))) return rc;
                 c->win_sb_alloc = c->nsb_total + 1;
             }
-            const size_t lanes = ((size_t)cdiv(c->ncap, 32) + (size_t)c->nsb_total + 1) * 32;
-            if (lanes > c->sb_slot_alloc) {
-                if ((rc = dev_alloc(c, &c->sb_slot, lanes))) return rc;
-                if ((rc = dev_alloc(c, &c->sb_li, (size_t)c->ncap + 32))) return rc;
-                c->sb_slot_alloc = lanes;
-            }
             if ((rc = win_attributes(c))) return rc;
         }
         return B2_OK;
@@ -420,7 +412,7 @@ template <typename R> struct Impl {
     static size_t list_ints(const b2_ctx *c, int cap)
     {
         if (c->grid.win)      // 16-bit entries in tiles local to the super-blocks: at most one partial tile each
-            return ((size_t)cdiv(c->ncap, 32) + (size_t)c->nsb_total + 1) * (size_t)cap * 16 + 2 * WIN_PAD_INTS;   // + slack at both ends: rows are read ahead
+            return ((size_t)cdiv(c->ncap, 32) + (size_t)c->nsb_total + 1) * (size_t)cap * 16 + 1024;   // + slack: rows are read ahead
         return (size_t)cdiv(c->ncap, 32) * (size_t)cap * 32;
     }
 
@@ -503,7 +495,6 @@ template <typename R> struct Impl {
                 LAUNCH(k_b8_bounds, cdiv(c->nb8codes + 1, 256), 256, c->ctl, c->keys[src], n, c->nb8codes, c->b8start);
                 LAUNCH(k_sb_tiles, 1, 1024, c->ctl, c->grid, c->b8start, c->tile_base);
                 LAUNCH(k_sb_table<R>, cdiv(c->nsb_total, 8), 256, c->ctl, c->grid, box, c->b8start, c->tile_base, c->sbt);
-                LAUNCH(k_sb_lanes<R>, cdiv(c->nsb_total, 8), 256, c->ctl, c->nsb_total, c->sbt, p0, p1, c->sb_li, c->sb_slot);
             }
         }
         // one warp per 2x2x2 block of cells when the grid allows it (at least 7 cells per axis: the
@@ -517,7 +508,7 @@ template <typename R> struct Impl {
             // one warp per code (a strided grid of a few blocks per SM was measured 10 % slower:
             // the valid codes are unevenly spread over the Morton range)
             LAUNCH(build, cdiv(codes, SC_WARPS), SC_WARPS * 32, c->ctl, p0, p1, n, box, c->grid,
-                   c->cell_start, c->cell_end, g.win ? c->nbr + WIN_PAD_INTS : c->nbr, c->nnb, c->cap, c->sbt, c->sb_li);
+                   c->cell_start, c->cell_end, c->nbr, c->nnb, c->cap, c->sbt);
         } else {
             auto build = g.m == 2 ? k_build_list<R, 2> : (g.m == 1 ? k_build_list<R, 1> : k_build_list<R, 0>);
             LAUNCH(build, cdiv(n, 128), 128, c->ctl, p0, p1, n, box, c->grid, c->cell_start, c->cell_end,
@@ -597,8 +588,7 @@ template <typename R> struct Impl {
         WinArgs<R> w;
         w.g = c->grid;
         w.sbt = c->sbt;
-        w.sb_slot = c->sb_slot;
-        w.nbr16 = (const unsigned short *)(c->nbr + WIN_PAD_INTS);
+        w.nbr16 = (const unsigned short *)c->nbr;
         return w;
     }
 
@@ -955,7 +945,7 @@ int Impl<R>::neighbors(b2_ctx *c, int32_t *count, int32_t *nbr, int32_t stride, 
     int *ocount = c->stage_i, *onbr = nullptr;
     if (nbr) CU(cudaMalloc((void **)&onbr, (size_t)n * stride * sizeof(int)));
     if (c->grid.win)
-        LAUNCH(k_export_list_win, win_grid(c), WIN_THREADS, c->sbt, c->sb_slot, c->nsp, (const unsigned short *)(c->nbr + WIN_PAD_INTS), c->nnb, c->orig, c->cap, stride, ocount, onbr);
+        LAUNCH(k_export_list_win, win_grid(c), WIN_THREADS, c->sbt, (const unsigned short *)c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
     else
         LAUNCH(k_export_list, cdiv(n, 128), 128, (int)n, c->nbr, c->nnb, c->orig, c->cap, stride, ocount, onbr);
     std::vector<int32_t> hc((size_t)n);
@@ -1341,7 +1331,7 @@ int b2_destroy(b2_ctx *c)
     void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv, c->halo_buf, c->dd_vmax,
                     c->img, c->ref, c->mvel, c->ke_partial, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i, c->b8start,
-                    c->tile_base, c->sbt, c->sb_li, c->sb_slot};
+                    c->tile_base, c->sbt};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);

@@ -59,11 +59,7 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
         R r2 = dx * dx + dy * dy + dz * dz;                                           \
         const int tj = ptype(PJ);                                                     \
         R a12, a6, rc2;                                                               \
-        if (FAST2 && SEL == 1) {        /* rows split by species: region of the first */ \
-            a12 = a12_0; a6 = a6_0; rc2 = rc_0;                                       \
-        } else if (FAST2 && SEL == 2) { /* ... of the second                          */ \
-            a12 = a12_1; a6 = a6_1; rc2 = rc_1;                                       \
-        } else if (FAST2) {                                                           \
+        if (FAST2) {                                                                  \
             a12 = tj ? a12_1 : a12_0; a6 = tj ? a6_1 : a6_0; rc2 = tj ? rc_1 : rc_0;  \
         } else {                                                                      \
             a12 = tab.c12x12[ti + tj]; a6 = tab.c6x6[ti + tj]; rc2 = tab.rc2[ti + tj]; \
@@ -125,7 +121,6 @@ __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restric
         a12_1 = tab.c12x12[ti + nsp - 1]; a6_1 = tab.c6x6[ti + nsp - 1]; rc_1 = tab.rc2[ti + nsp - 1];
     }
     int k = 0;
-    constexpr int SEL = 0;      // (rows of the global-index list are not split by species)
     // the deeper pipeline only where the registers are there for it: the step kernel (no energies)
     constexpr int B2_UNROLL = (sizeof(R) == 4 && !EV) ? B2_UNROLL32 : B2_UNROLL64;
 #if B2_PIPE

@@ -414,10 +414,9 @@ struct ScWindow {
     int woff[SC_CELLS + 8];
 };
 
-// (stride +32: a region growing up from the row's first entry; -32: down from its last, see SPLIT below)
-__device__ __forceinline__ void sc_append16(bool hit, unsigned short *row, int &cnt, int cap, int off, int stride = 32)
+__device__ __forceinline__ void sc_append16(bool hit, unsigned short *row, int &cnt, int cap, int off)
 {
-    unsigned short *dst = row + (ptrdiff_t)cnt * stride;
+    unsigned short *dst = row + (size_t)cnt * 32;
     asm volatile("{\n\t.reg .pred q, s;\n\tsetp.ne.s32 q, %1, 0;\n\tsetp.lt.and.s32 s, %0, %2, q;\n\t"
                  "@s st.global.b16 [%3], %4;\n\t@q add.s32 %0, %0, 1;\n\t}"
                  : "+r"(cnt) : "r"((int)hit), "r"(cap), "l"(dst), "h"((unsigned short)off) : "memory");
@@ -434,7 +433,7 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
                                          const Box<R> &box, const Grid &g, const int *__restrict__ cell_start,
                                          const int *__restrict__ cell_end, int *__restrict__ nbr,
                                          int *__restrict__ nnb, int cap,
-                                         const int *__restrict__ sbt, const int *__restrict__ sb_li)
+                                         const int *__restrict__ sbt)
 {
     typedef typename Pos4<R>::type P4;
     const int bx = 2 * (int)compact3(ms), by = 2 * (int)compact3(ms >> 1), bz = 2 * (int)compact3(ms >> 2);
@@ -457,12 +456,13 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
     n_own = __shfl_sync(0xffffffffu, n_own, 0);
     if (n_own == 0) return;
     // windowed list: entries are offsets into the window of this block's super-block
-    int W = 0, tbase = 0, self_base = 0;
+    int W = 0, sb_first = 0, tbase = 0, self_base = 0;
     if (WIN) {
         const int sx = bx >> 2, sy = by >> 2, sz = bz >> 2;
         const int *__restrict__ T = sbt + (size_t)((sz * g.nsb[1] + sy) * g.nsb[0] + sx) * (12 + 2 * 64);   // SBT_STRIDE
         W = win_layout_load(T, lane, sw.wP, sw.wS);
         __syncwarp();
+        sb_first = T[0];
         tbase = T[2];
         // the block's own run: B8 block ((bx & 2) + 2) / 2 ... of the window
         const int r_own = (((((bz & 2) + 2) >> 1) * 4) + (((by & 2) + 2) >> 1)) * 4 + (((bx & 2) + 2) >> 1);
@@ -531,17 +531,10 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
         const float *lo_row = s_lo + ti * nsp;
         const float lo0 = lo_row[0], lo1 = lo_row[nsp > 1 ? 1 : 0];
         int *row = nbr + ((size_t)(slot >> 5) * cap) * 32 + (slot & 31);
-        // windowed: rows live in tiles local to the super-block, lanes grouped by species (k_sb_lanes)
-        const int li = WIN ? sb_li[valid ? slot : first] : 0;
+        const int li = slot - sb_first;                   // windowed: rows live in tiles local to the super-block
         unsigned short *row16 = reinterpret_cast<unsigned short *>(nbr) +
                                 ((size_t)(tbase + (li >> 5)) * (size_t)cap) * 32 + (li & 31);
         const int self = WIN ? self_base + slot : slot;   // the name candidates carry: window offset or slot
-        // SPLIT (windowed rows of a one- or two-species model): neighbours of the FIRST species fill the row from
-        // its first entry upwards, those of the second from its last entry downwards, so that the force loops
-        // walk each region with its coefficients in registers and no per-pair selection.  nnb = cnt | cnt1 << 16.
-        constexpr bool SPLIT = WIN && FAST2;
-        unsigned short *row16_top = row16 + (size_t)(cap - 1) * 32;
-        int cnt1 = 0;
         int cnt = 0;
         float near = -1.f;        // > 0 once a listed pair sits inside the band around its threshold
         for (int c0 = 0; c0 < total; c0 += SC_TAKE) {
@@ -608,32 +601,30 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
             const int e0 = (n0 + 3) & ~3;
             if (FAST2) {
                 float far0 = 0.f, far1 = 0.f;         // largest listed r^2 of either stretch
-#define SC_TEST(Q, HI, FAR, SECOND)                                                \
+#define SC_TEST(Q, HI, FAR)                                                        \
                 {                                                                  \
                     const float dx = Q.x - px, dy = Q.y - py, dz = Q.z - pz;       \
                     const float r2 = dx * dx + dy * dy + dz * dz;                  \
                     const int j = __float_as_int(Q.w);                             \
                     const bool hit = r2 < HI && j != self;                         \
-                    if (SPLIT && SECOND) sc_append16(hit, row16_top, cnt1, lim, j, -32); \
-                    else if (WIN) sc_append16(hit, row16, cnt, lim, j);            \
+                    if (WIN) sc_append16(hit, row16, cnt, cap, j);                 \
                     else sc_append(hit, row, cnt, cap, j);                         \
                     FAR = fmaxf(FAR, hit ? r2 : 0.f);                              \
                 }
                 // four candidates per round, the next four already on their way from shared memory
                 // (the reads run up to 4 records past a stretch: the chunk is padded for that)
-#define SC_STRETCH(FIRST, LAST, HI, FAR, SECOND)                                   \
+#define SC_STRETCH(FIRST, LAST, HI, FAR)                                           \
                 if ((FIRST) < (LAST)) {                                            \
-                    const int lim = SPLIT ? cap - ((SECOND) ? cnt : cnt1) : cap;   \
                     float4 q0 = cand[FIRST], q1 = cand[(FIRST) + 1], q2 = cand[(FIRST) + 2], q3 = cand[(FIRST) + 3]; \
                     _Pragma("unroll 1")                                            \
                     for (int r = (FIRST); r < (LAST); r += 4) {                    \
                         const float4 n0_ = cand[r + 4], n1_ = cand[r + 5], n2_ = cand[r + 6], n3_ = cand[r + 7]; \
-                        SC_TEST(q0, HI, FAR, SECOND) SC_TEST(q1, HI, FAR, SECOND) SC_TEST(q2, HI, FAR, SECOND) SC_TEST(q3, HI, FAR, SECOND) \
+                        SC_TEST(q0, HI, FAR) SC_TEST(q1, HI, FAR) SC_TEST(q2, HI, FAR) SC_TEST(q3, HI, FAR) \
                         q0 = n0_; q1 = n1_; q2 = n2_; q3 = n3_;                    \
                     }                                                              \
                 }
-                SC_STRETCH(0, e0, hi0, far0, false)
-                SC_STRETCH(SC_CHUNK - ((n1 + 3) & ~3), SC_CHUNK, hi1, far1, true)
+                SC_STRETCH(0, e0, hi0, far0)
+                SC_STRETCH(SC_CHUNK - ((n1 + 3) & ~3), SC_CHUNK, hi1, far1)
 #undef SC_STRETCH
 #undef SC_TEST
                 near = fmaxf(near, fmaxf(far0 - lo0, far1 - lo1));
@@ -658,38 +649,30 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
             // Some listed pair is inside the band around its threshold: settle those with the
             // canonical predicate and close the gaps (about one particle in a thousand).  Pairs
             // beyond the band were rejected by the float test.
-            // (SPLIT: the two regions one after the other, each closed up on its own)
-            const bool fits = cnt + cnt1 <= cap;
-            for (int region = 0; region < (SPLIT ? 2 : 1); region++) {
-                unsigned short *base = region ? row16_top : row16;
-                const int stride = region ? -32 : 32;
-                const int lim = min(region ? cnt1 : cnt, fits ? cap : 0);
-                int kept = 0;
-                for (int k = 0; k < lim; k++) {
-                    const int name = WIN ? (int)base[(ptrdiff_t)k * stride] : row[(size_t)k * 32];
-                    const int e = WIN ? win_slot_of(sw.wP, sw.wS, name) : name;
-                    const P4 pj = pos[e];
-                    const int tj = ptype(pj);
-                    float qx, qy, qz;
-                    rel_to(pj, box, org, qx, qy, qz);
-                    const float dx = qx - px, dy = qy - py, dz = qz - pz;
-                    bool keep = true;
-                    if (dx * dx + dy * dy + dz * dz > lo_row[tj]) keep = r2_canon(pi, pj, box) < s_rl2[ti * nsp + tj];
-                    if (keep) {
-                        if (WIN) base[(ptrdiff_t)kept * stride] = (unsigned short)name;
-                        else row[(size_t)kept * 32] = e;
-                        kept++;
-                    }
+            const int lim = min(cnt, cap);
+            int kept = 0;
+            for (int k = 0; k < lim; k++) {
+                const int name = WIN ? (int)row16[(size_t)k * 32] : row[(size_t)k * 32];
+                const int e = WIN ? win_slot_of(sw.wP, sw.wS, name) : name;
+                const P4 pj = pos[e];
+                const int tj = ptype(pj);
+                float qx, qy, qz;
+                rel_to(pj, box, org, qx, qy, qz);
+                const float dx = qx - px, dy = qy - py, dz = qz - pz;
+                bool keep = true;
+                if (dx * dx + dy * dy + dz * dz > lo_row[tj]) keep = r2_canon(pi, pj, box) < s_rl2[ti * nsp + tj];
+                if (keep) {
+                    if (WIN) row16[(size_t)kept * 32] = (unsigned short)name;
+                    else row[(size_t)kept * 32] = e;
+                    kept++;
                 }
-                if (fits) { if (region) cnt1 = kept; else cnt = kept; }
             }
+            if (cnt <= cap) cnt = kept;
         }
         if (valid) {
-            const int tot = cnt + cnt1;
-            nnb[slot] = tot > cap ? 0 : (SPLIT ? (cnt | (cnt1 << 16)) : cnt);
-            if (tot > cap) ctl->overflow = 1u;
+            nnb[slot] = min(cnt, cap);
+            if (cnt > cap) ctl->overflow = 1u;
         }
-        cnt += cnt1;
         int mx = valid ? cnt : 0;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -704,7 +687,7 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
                 const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
                 const int *__restrict__ cell_start, const int *__restrict__ cell_end,
                 int *__restrict__ nbr, int *__restrict__ nnb, int cap,
-                const int *__restrict__ sbt, const int *__restrict__ sb_li)
+                const int *__restrict__ sbt)
 {
     if (!ctl->halt_rebuild) return;
     typedef typename Pos4<R>::type P4;
@@ -727,7 +710,7 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     const uint32_t codes = 1u << (3 * g.cellbits - 3);
     for (uint32_t ms = blockIdx.x * SC_WARPS + warp; ms < codes; ms += gridDim.x * SC_WARPS) {
         sc_block<R, FAST2, WIN>(ms, lane, s_warp[warp], s_win[WIN ? warp : 0], s_rl2, s_hi, s_lo, ctl, pos, box, g,
-                                cell_start, cell_end, nbr, nnb, cap, sbt, sb_li);
+                                cell_start, cell_end, nbr, nnb, cap, sbt);
         __syncwarp();
     }
 }

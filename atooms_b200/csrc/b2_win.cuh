@@ -350,46 +350,6 @@ k_sb_table(const Ctl *__restrict__ ctl, Grid g, Box<R> box, const int *__restric
     }
 }
 
-// Lanes of a super-block, grouped by species: its particles of the first species take lanes 0 .. n0 - 1 of
-// the super-block's tiles, the others follow.  Neighbour counts differ by species (Kob-Andersen: 100 for A,
-// 65 for B), and a warp walks its rows as long as its longest one: with one species per warp, fewer lanes idle.
-//   sb_li[slot]                  lane index of a slot within its super-block (tile = li / 32, lane = li % 32)
-//   sb_slot[tile * 32 + lane]    the slot a lane works on, -1 for the unused lanes of a last tile
-template <typename R>
-__global__ void __launch_bounds__(256)
-k_sb_lanes(const Ctl *__restrict__ ctl, int nsb, const int *__restrict__ sbt, const typename Pos4<R>::type *pos0,
-           const typename Pos4<R>::type *pos1, int *__restrict__ sb_li, int *__restrict__ sb_slot)
-{
-    if (!ctl->halt_rebuild) return;
-    const typename Pos4<R>::type *pos = ctl->cur ? pos1 : pos0;
-    const int lane = threadIdx.x & 31;
-    const int gi = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (gi >= nsb) return;
-    const int *__restrict__ T = sbt + (size_t)gi * SBT_STRIDE;
-    const int first = T[0], cnt = T[1], tbase = T[2];
-    int n0 = 0;
-    for (int b = 0; b < cnt; b += 32) {
-        const bool is0 = b + lane < cnt && ptype(pos[first + b + lane]) == 0;
-        n0 += __popc(__ballot_sync(0xffffffffu, is0));
-    }
-    int run0 = 0, run1 = n0;
-    for (int b = 0; b < cnt; b += 32) {
-        const bool in = b + lane < cnt;
-        const bool is0 = in && ptype(pos[first + b + lane]) == 0;
-        const unsigned m0 = __ballot_sync(0xffffffffu, is0), m1 = __ballot_sync(0xffffffffu, in && !is0);
-        const unsigned below = (1u << lane) - 1u;
-        if (in) {
-            const int li = is0 ? run0 + __popc(m0 & below) : run1 + __popc(m1 & below);
-            sb_li[first + b + lane] = li;
-            sb_slot[(size_t)(tbase + (li >> 5)) * 32 + (li & 31)] = first + b + lane;
-        }
-        run0 += __popc(m0);
-        run1 += __popc(m1);
-    }
-    const int padded = (cnt + 31) & ~31;
-    for (int li = cnt + lane; li < padded; li += 32) sb_slot[(size_t)(tbase + (li >> 5)) * 32 + (li & 31)] = -1;
-}
-
 // the wrap-around of the fixed-point difference IS the minimum image; every record of a window lies within
 // 4 cells of the centre, far inside half a box
 __device__ __forceinline__ relf4 to_rel(const int4 &p, const WinOrigin<float> &o, const Box<float> &box)
@@ -440,21 +400,18 @@ template <typename R, bool EV> struct WinUnroll {
 };
 
 // the first U entries of a row, requested ahead of use.  Reads may run up to U rows past the lane's
-// count (into the next tile's rows, or the slack around the list): such entries are never used.
-// STRIDE = 32: a region growing up from the row's first entry; -32: down from its last one.
-template <int U, int STRIDE>
+// count (into the next tile's rows, or the slack behind the list): such entries are never used.
+template <int U>
 __device__ __forceinline__ void win_row_begin(const unsigned short *__restrict__ row, unsigned (&jj)[U])
 {
 #pragma unroll
-    for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (ptrdiff_t)u * STRIDE);
+    for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)u * 32);
 }
 
-// One particle against (a region of) its row of window offsets.  P is the record type of the
-// window: the stored positions (force kernels: exact arithmetic, observables in fp64) or relative
-// coordinates (step kernels).  `jj` holds the region's first U entries (win_row_begin).
-// SEL = 1 / 2: the region holds neighbours of the first / second species only (rows split by the
-// list build), the coefficients stay in registers; 0: selected per pair by the neighbour's species.
-template <typename R, typename P, bool EV, bool STRESS, bool FAST2, bool FASTRCP, int SEL, int STRIDE>
+// One particle against its row of window offsets.  P is the record type of the window: the stored
+// positions (force kernels: exact arithmetic, observables in fp64) or relative coordinates (step
+// kernels).  `jj` holds the row's first U entries (win_row_begin).  Pair arithmetic: B2_PAIR.
+template <typename R, typename P, bool EV, bool STRESS, bool FAST2, bool FASTRCP>
 __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short *__restrict__ row, int cnt,
                                              unsigned (&jj)[WinUnroll<R, EV>::U],
                                              P pi, const Box<R> &box, const PairTab<R> &tab, int nsp,
@@ -464,16 +421,24 @@ __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short 
     const int ti = ptype(pi) * nsp;
     R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
     if (FAST2) {
-        if (SEL != 2) pair_coef(ti, a12_0, a6_0, rc_0);
-        if (SEL != 1) pair_coef(ti + nsp - 1, a12_1, a6_1, rc_1);
+        pair_coef(ti, a12_0, a6_0, rc_0);
+        pair_coef(ti + nsp - 1, a12_1, a6_1, rc_1);
     }
     int k = 0;
     for (; k + U <= cnt; k += U) {
         P pp[U];
 #pragma unroll
         for (int u = 0; u < U; u++) pp[u] = win[jj[u]];
+#ifdef WIN_EXPERIMENT_DOUBLE_LDS       // timing experiment only (same physics): every record is read twice
 #pragma unroll
-        for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (ptrdiff_t)(k + U + u) * STRIDE);
+        for (int u = 0; u < U; u++) {
+            unsigned d0, d1, d2, d3;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(d0), "=r"(d1), "=r"(d2), "=r"(d3)
+                         : "r"(smem_u32(win + jj[u])));
+        }
+#endif
+#pragma unroll
+        for (int u = 0; u < U; u++) jj[u] = ld_stream_u16(row + (size_t)(k + U + u) * 32);
 #pragma unroll
         for (int u = 0; u < U; u++) B2_PAIR(pp[u])
     }
@@ -485,33 +450,12 @@ __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short 
             B2_PAIR(p0)
         }
 }
-
-// a whole row: both regions of a split row (one- and two-species models), or the unsplit row
-template <typename R, typename P, bool EV, bool STRESS, bool FASTRCP, bool BYREGION>
-__device__ __forceinline__ void pair_rows_win(const P *win, const unsigned short *__restrict__ row, int cap, int nnb,
-                                              unsigned (&jj)[WinUnroll<R, EV>::U], P pi, const Box<R> &box,
-                                              const PairTab<R> &tab, int nsp,
-                                              R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
-{
-    constexpr int U = WinUnroll<R, EV>::U;
-    if (nsp <= 2) {
-        const int c0 = nnb & 0xffff, c1 = nnb >> 16;
-        pair_row_win<R, P, EV, STRESS, true, FASTRCP, BYREGION ? 1 : 0, 32>(win, row, c0, jj, pi, box, tab, nsp, fx, fy, fz, pe, vir, st);
-        if (c1 > 0) {
-            const unsigned short *top = row + (size_t)(cap - 1) * 32;
-            win_row_begin<U, -32>(top, jj);
-            pair_row_win<R, P, EV, STRESS, true, FASTRCP, BYREGION ? 2 : 0, -32>(win, top, c1, jj, pi, box, tab, nsp, fx, fy, fz, pe, vir, st);
-        }
-    } else {
-        pair_row_win<R, P, EV, STRESS, false, FASTRCP, 0, 32>(win, row, nnb, jj, pi, box, tab, nsp, fx, fy, fz, pe, vir, st);
-    }
-}
 #undef B2_PAIR
 #undef B2_RCP
 
 template <typename R> struct WinArgs {
     Grid g;
-    const int *sbt, *sb_slot;
+    const int *sbt;
     const unsigned short *nbr16;
 };
 
@@ -546,8 +490,8 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
     const int ntile = (wi.cnt + 31) >> 5;
     // the first tile's own data, on its way while the window arrives
     int t = warp;
-    int i = t < ntile ? wa.sb_slot[(size_t)(wi.tbase + t) * 32 + lane] : -1;     // lanes are grouped by species
-    bool valid = i >= 0;
+    bool valid = t < ntile && t * 32 + lane < wi.cnt;
+    int i = wi.first + t * 32 + lane;
     const unsigned short *row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
     P4 pi;
     int cnt = 0;
@@ -555,7 +499,7 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
     if (valid) {
         pi = pos[i];
         cnt = a.nnb[i];
-        win_row_begin<U, 32>(row, jj);
+        win_row_begin<U>(row, jj);
     }
     WinOrigin<R> org;
     win_origin_load(wa.sbt + (size_t)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * SBT_STRIDE, org);
@@ -576,7 +520,8 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
                 R fx = 0, fy = 0, fz = 0;
                 double pe = 0, vir = 0;
                 const Q4 qi = to_rel(pi, org, a.box);
-                pair_rows_win<R, Q4, false, false, true, true>(rel, row, a.cap, cnt, jj, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+                if (nsp <= 2) pair_row_win<R, Q4, false, false, true, true>(rel, row, cnt, jj, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+                else pair_row_win<R, Q4, false, false, false, true>(rel, row, cnt, jj, qi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
                 V4 v = a.vel[i];
                 R s = a.kick / v.w;
                 if (NVT) {
@@ -598,13 +543,13 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
         }
         t += WIN_THREADS / 32;
         if (t >= ntile) break;
-        i = wa.sb_slot[(size_t)(wi.tbase + t) * 32 + lane];
-        valid = i >= 0;
+        valid = t * 32 + lane < wi.cnt;
+        i = wi.first + t * 32 + lane;
         row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
         if (valid) {
             pi = pos[i];
             cnt = a.nnb[i];
-            win_row_begin<U, 32>(row, jj);
+            win_row_begin<U>(row, jj);
         }
     }
     step_epilogue<R, NVT, WIN_THREADS>(a, ctl, cur, v2, mv2);
@@ -634,16 +579,18 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
     __syncthreads();                 // the table of the many-species path
     double st[6] = {0, 0, 0, 0, 0, 0};
     for (int t = warp; t < ntile; t += WIN_THREADS / 32) {
-        const int i = wa.sb_slot[(size_t)(wi.tbase + t) * 32 + lane];
-        if (i < 0) continue;
+        const int li = t * 32 + lane;
+        if (li >= wi.cnt) continue;
+        const int i = wi.first + li;
         const P4 pi = pos[i];
         R fx = 0, fy = 0, fz = 0;
         double pe = 0, vir = 0;
         const unsigned short *row = wa.nbr16 + ((size_t)(wi.tbase + t) * (size_t)a.cap) * 32 + lane;
         const int cnt = a.nnb[i];
         unsigned jj[U];
-        win_row_begin<U, 32>(row, jj);
-        pair_rows_win<R, P4, EV, STRESS, false, true>(win, row, a.cap, cnt, jj, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        win_row_begin<U>(row, jj);
+        if (nsp <= 2) pair_row_win<R, P4, EV, STRESS, true, false>(win, row, cnt, jj, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        else pair_row_win<R, P4, EV, STRESS, false, false>(win, row, cnt, jj, pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
         a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
         if (EV) a.vir[i] = (R)(0.5 * vir);
     }
@@ -666,8 +613,7 @@ k_force_win(ForceArgs<R> a, WinArgs<R> wa)
 
 // export of the windowed list in original numbering (b2_neighbors): one block per super-block
 __global__ void __launch_bounds__(WIN_THREADS)
-k_export_list_win(const int *__restrict__ sbt, const int *__restrict__ sb_slot, int nsp,
-                  const unsigned short *__restrict__ nbr16, const int *__restrict__ nnb,
+k_export_list_win(const int *__restrict__ sbt, const unsigned short *__restrict__ nbr16, const int *__restrict__ nnb,
                   const int *__restrict__ orig, int cap, int stride, int *__restrict__ ocount, int *__restrict__ onbr)
 {
     __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
@@ -675,18 +621,13 @@ k_export_list_win(const int *__restrict__ sbt, const int *__restrict__ sb_slot, 
     const int *__restrict__ T = sbt + (size_t)gi * SBT_STRIDE;
     if (threadIdx.x < 32) win_layout_load(T, threadIdx.x, sP, sS);
     __syncthreads();
-    const int cnt = T[1], tbase = T[2];
-    for (int li = threadIdx.x; li < ((cnt + 31) & ~31); li += blockDim.x) {
-        const int s = sb_slot[(size_t)(tbase + (li >> 5)) * 32 + (li & 31)];
-        if (s < 0) continue;
-        const int o = orig[s], c01 = nnb[s];
-        const int c0 = nsp <= 2 ? (c01 & 0xffff) : c01, c1 = nsp <= 2 ? (c01 >> 16) : 0;     // split rows
-        ocount[o] = c0 + c1;
+    const int first = T[0], cnt = T[1], tbase = T[2];
+    for (int li = threadIdx.x; li < cnt; li += blockDim.x) {
+        const int s = first + li, o = orig[s], c = nnb[s];
+        ocount[o] = c;
         if (!onbr) continue;
         const unsigned short *row = nbr16 + ((size_t)(tbase + (li >> 5)) * (size_t)cap) * 32 + (li & 31);
-        for (int k = 0; k < c0; k++)
+        for (int k = 0; k < c; k++)
             onbr[(size_t)o * stride + k] = orig[win_slot_of(sP, sS, (int)row[(size_t)k * 32])];
-        for (int k = 0; k < c1; k++)
-            onbr[(size_t)o * stride + c0 + k] = orig[win_slot_of(sP, sS, (int)row[(size_t)(cap - 1 - k) * 32])];
     }
 }
