@@ -47,6 +47,7 @@ SYMBOLS = {
     'b2_set_stream': (_int, [_vp, _vp]),
     'b2_set_box': (_int, [_vp, _c_dp, _c_dp]),
     'b2_set_pair_table': (_int, [_vp, _int, _c_dp, _c_dp, _c_dp, _int]),
+    'b2_set_pair_tabulated': (_int, [_vp, _int, _int, _c_dp, _c_dp, _c_dp]),
     'b2_set_skin': (_int, [_vp, _dbl]),
     'b2_upload': (_int, [_vp, _i64, _c_dp, _c_dp, _c_ip, _c_dp]),
     'b2_update': (_int, [_vp, _c_dp, _c_dp]),
@@ -267,6 +268,24 @@ class Engine(object):
         if not (eps.shape == sigma.shape == rcut.shape == (nsp, nsp)):
             raise ValueError('eps, sigma, rcut must be square matrices of the same size')
         self._call('b2_set_pair_table', nsp, _dp(eps), _dp(sigma), _dp(rcut), int(bool(shifted)))
+
+    def set_pair_tabulated(self, rcut, u, w):
+        """rcut (nsp, nsp); u, w (nsp, nsp, npoints) sampled uniformly in r^2 over [0, rcut^2] (b2_set_pair_tabulated)."""
+        rcut = numpy.atleast_2d(numpy.ascontiguousarray(rcut, dtype=numpy.float64))
+        u = numpy.ascontiguousarray(u, dtype=numpy.float64)
+        w = numpy.ascontiguousarray(w, dtype=numpy.float64)
+        nsp = rcut.shape[0]
+        if rcut.shape != (nsp, nsp) or u.shape != w.shape or u.shape[:2] != (nsp, nsp) or u.ndim != 3:
+            raise ValueError('rcut must be (nsp, nsp), u and w (nsp, nsp, npoints)')
+        self._call('b2_set_pair_tabulated', nsp, int(u.shape[2]), _dp(rcut), _dp(u), _dp(w))
+
+    def set_model(self, model):
+        """Bind a model of atooms_b200.models: the 12-6 table or lookup tables."""
+        if getattr(model, 'tabulated', False):
+            u, w = model.tables()
+            self.set_pair_tabulated(model.rcut, u, w)
+        else:
+            self.set_pair_table(model.eps, model.sigma, model.rcut, model.shifted)
 
     def set_skin(self, skin):
         self._call('b2_set_skin', float(skin))

@@ -70,6 +70,12 @@ struct PairConst {
     float  rl2_f[B2_MAXSP * B2_MAXSP];   // ((float)(rcut + skin))^2 evaluated in float
     // force coefficients as the kernels use them: 12 c12, 6 c6, rc^2 in float (the fp64 kernels multiply themselves)
     float  f12[B2_MAXSP * B2_MAXSP], f6[B2_MAXSP * B2_MAXSP], frc2[B2_MAXSP * B2_MAXSP];
+    // tabulated pair potentials (b2_set_pair_tabulated): per pair tab_np samples, uniform in r^2 over
+    // [0, rc^2]; u = energy, w = -r du/dr = r.F; linear interpolation in r^2.  Tables live in global memory.
+    int tab_np, tab_pad_;
+    const double *tab_u, *tab_w;         // [nsp * nsp][tab_np]
+    const float *tab_wf;                 // w in float, for the fp32 force loops
+    double tab_scale[B2_MAXSP * B2_MAXSP];   // (tab_np - 1) / rc^2
 };
 
 // single translation unit: the table is defined here, once

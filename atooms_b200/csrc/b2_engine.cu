@@ -33,6 +33,9 @@ struct b2_ctx {
     double rcut[64], rcut_max = 0, skin = 0.3;
     PairConst pc;
     uint64_t const_serial = 0;
+    bool tabulated = false;                  // b2_set_pair_tabulated: tables in tab_u / tab_w / tab_wf (device)
+    double *tab_u = nullptr, *tab_w = nullptr;
+    float *tab_wf = nullptr;
     // particles (sorted order unless noted)
     int64_t n = 0, ncap = 0;   // particles resident / allocated
     size_t nbr_alloc = 0;
@@ -343,7 +346,7 @@ template <typename R> struct Impl {
         // global list unless B2_LIST_WINDOWED=1; so does a domain that fills only part of its box (a slab of a
         // decomposed system: half of the super-blocks are empty launches), see grow_after_overflow.
         const bool force_win = getenv("B2_LIST_WINDOWED") && atoi(getenv("B2_LIST_WINDOWED")) != 0;
-        if (!g.allpairs && g.m == 2 && !c->win_off && !force_global && (c->precision == B2_FP32 || force_win) &&
+        if (!g.allpairs && g.m == 2 && !c->win_off && !c->tabulated && !force_global && (c->precision == B2_FP32 || force_win) &&
             g.nc[0] >= 8 && g.nc[1] >= 8 && g.nc[2] >= 8) {
             double cellvol = 1.0;
             for (int d = 0; d < 3; d++) cellvol *= c->side[d] / (g.nc[d] & ~1);
@@ -577,7 +580,7 @@ template <typename R> struct Impl {
             LAUNCH_SMEM(kern, win_grid(c), WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
             return;
         }
-        auto kern = k_force<R, EV, STRESS>;
+        auto kern = c->tabulated ? k_force<R, EV, STRESS, true> : k_force<R, EV, STRESS, false>;
         LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
     }
 
@@ -602,7 +605,7 @@ template <typename R> struct Impl {
             auto kern = k_step_win<R, NVT>;
             LAUNCH_SMEM(kern, win_grid(c), WIN_THREADS, (size_t)c->grid.wcap * sizeof(P4), a, win_args(c));
         } else {
-            auto kern = k_step_nve<R, NVT>;
+            auto kern = c->tabulated ? k_step_nve<R, NVT, true> : k_step_nve<R, NVT, false>;
             LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
         }
     }
@@ -1331,7 +1334,7 @@ int b2_destroy(b2_ctx *c)
     void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv, c->halo_buf, c->dd_vmax,
                     c->img, c->ref, c->mvel, c->ke_partial, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i, c->b8start,
-                    c->tile_base, c->sbt};
+                    c->tile_base, c->sbt, c->tab_u, c->tab_w, c->tab_wf};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
@@ -1408,6 +1411,7 @@ int b2_set_pair_table(b2_ctx *c, int nsp, const double *eps, const double *sigma
         if (!(sigma[a] > 0.0) || !(rcut[a] > 0.0))
             return fail(c, B2_EINVAL, "b2_set_pair_table: sigma and rcut must be > 0");
     memset(&c->pc, 0, sizeof(PairConst));
+    c->tabulated = false;
     c->nsp = c->pc.nsp = nsp;
     c->shifted = shifted;
     c->rcut_max = 0;
@@ -1422,6 +1426,52 @@ int b2_set_pair_table(b2_ctx *c, int nsp, const double *eps, const double *sigma
         double ir2 = 1.0 / c->pc.rc2[a];
         double ir6 = ir2 * ir2 * ir2;
         c->pc.ushift[a] = shifted ? ir6 * (c->pc.c12[a] * ir6 - c->pc.c6[a]) : 0.0;
+        c->rcut_max = std::max(c->rcut_max, rcut[a]);
+    }
+    rebuild_table(c);
+    c->have_table = true;
+    c->list_dirty = true;
+    c->forces_valid = c->ev_valid = false;
+    c->cap = 0;
+    return B2_OK;
+}
+
+int b2_set_pair_tabulated(b2_ctx *c, int nsp, int npoints, const double *rcut, const double *u, const double *w)
+{
+    if (!c || !rcut || !u || !w) return fail(c, B2_EINVAL, "b2_set_pair_tabulated: NULL argument");
+    if (nsp < 1 || nsp > B2_MAXSP) return fail(c, B2_EINVAL, "b2_set_pair_tabulated: 1 <= nsp <= %d", B2_MAXSP);
+    if (npoints < 2 || npoints > (1 << 24)) return fail(c, B2_EINVAL, "b2_set_pair_tabulated: 2 <= npoints <= 2^24");
+    for (int a = 0; a < nsp * nsp; a++)
+        if (!(rcut[a] > 0.0)) return fail(c, B2_EINVAL, "b2_set_pair_tabulated: rcut must be > 0");
+    { int rc_ = bind_device(c); if (rc_) return rc_; }
+    if (c->pos[0] && c->half_pending) { int rc_ = DISPATCH(settle, c); if (rc_) return rc_; }
+    const size_t count = (size_t)nsp * nsp * npoints;
+    if (c->tab_u) cudaFree(c->tab_u);
+    if (c->tab_w) cudaFree(c->tab_w);
+    if (c->tab_wf) cudaFree(c->tab_wf);
+    c->tab_u = c->tab_w = nullptr;
+    c->tab_wf = nullptr;
+    CU(cudaMalloc((void **)&c->tab_u, count * sizeof(double)));
+    CU(cudaMalloc((void **)&c->tab_w, count * sizeof(double)));
+    CU(cudaMalloc((void **)&c->tab_wf, count * sizeof(float)));
+    std::vector<float> wf(count);
+    for (size_t k = 0; k < count; k++) wf[k] = (float)w[k];
+    CU(cudaMemcpy(c->tab_u, u, count * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->tab_w, w, count * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->tab_wf, wf.data(), count * sizeof(float), cudaMemcpyHostToDevice));
+    memset(&c->pc, 0, sizeof(PairConst));
+    c->tabulated = true;
+    c->nsp = c->pc.nsp = nsp;
+    c->shifted = 0;
+    c->rcut_max = 0;
+    c->pc.tab_np = npoints;
+    c->pc.tab_u = c->tab_u;
+    c->pc.tab_w = c->tab_w;
+    c->pc.tab_wf = c->tab_wf;
+    for (int a = 0; a < nsp * nsp; a++) {
+        c->rcut[a] = rcut[a];
+        c->pc.rc2[a] = rcut[a] * rcut[a];
+        c->pc.tab_scale[a] = (double)(npoints - 1) / c->pc.rc2[a];
         c->rcut_max = std::max(c->rcut_max, rcut[a]);
     }
     rebuild_table(c);

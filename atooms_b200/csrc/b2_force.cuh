@@ -51,6 +51,34 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
 // Body of one pair evaluation, shared by the row walkers (pair_row here, pair_row_win in
 // b2_win.cuh).  Uses the caller's pi, box, tab, ti, the register-held table row (a12_0 ...),
 // the accumulators fx fy fz pe vir st.  #undef'd at the end of b2_win.cuh.
+// tabulated potentials: value at r2 by linear interpolation between the two samples around it
+__device__ __forceinline__ float tab_w(float, int a, float r2)
+{
+    const float t = r2 * (float)g_pair.tab_scale[a];
+    const int k = min((int)t, g_pair.tab_np - 2);
+    const float *w = g_pair.tab_wf + (size_t)a * g_pair.tab_np + k;
+    const float w0 = __ldg(w), w1 = __ldg(w + 1);
+    return fmaf(t - (float)k, w1 - w0, w0);
+}
+__device__ __forceinline__ double tab_w(double, int a, double r2)
+{
+    const double t = r2 * g_pair.tab_scale[a];
+    const int k = min((int)t, g_pair.tab_np - 2);
+    const double *w = g_pair.tab_w + (size_t)a * g_pair.tab_np + k;
+    const double w0 = __ldg(w), w1 = __ldg(w + 1);
+    return w0 + (t - (double)k) * (w1 - w0);
+}
+__device__ __forceinline__ void tab_uw(int a, double r2, double &u, double &w)
+{
+    const double t = r2 * g_pair.tab_scale[a];
+    const int k = min((int)t, g_pair.tab_np - 2);
+    const double f = t - (double)k;
+    const double *pu = g_pair.tab_u + (size_t)a * g_pair.tab_np + k, *pw = g_pair.tab_w + (size_t)a * g_pair.tab_np + k;
+    const double u0 = __ldg(pu), u1 = __ldg(pu + 1), w0 = __ldg(pw), w1 = __ldg(pw + 1);
+    u = u0 + f * (u1 - u0);
+    w = w0 + f * (w1 - w0);
+}
+
 #define B2_RCP(x) r_rcp(x)
 #define B2_PAIR(PJ)                                                                   \
     {                                                                                 \
@@ -65,8 +93,15 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
             a12 = tab.c12x12[ti + tj]; a6 = tab.c6x6[ti + tj]; rc2 = tab.rc2[ti + tj]; \
         }                                                                             \
         R r2inv = B2_RCP(r2);                                                         \
-        R r6inv = r2inv * r2inv * r2inv;                                              \
-        R fp = r6inv * (a12 * r6inv - a6) * r2inv;                                    \
+        R fp;                                                                         \
+        if (TAB) {                                                                    \
+            /* tabulated: w = r.F interpolated linearly in r^2, F = (w / r^2) d */    \
+            rc2 = (R)g_pair.rc2[ti + tj];                                             \
+            fp = tab_w((R)0, ti + tj, r2) * r2inv;                                    \
+        } else {                                                                      \
+            R r6inv = r2inv * r2inv * r2inv;                                          \
+            fp = r6inv * (a12 * r6inv - a6) * r2inv;                                  \
+        }                                                                             \
         if (EV || STRESS) {                                                           \
             /* observables: fp64 pair arithmetic on the stored positions, in both */ \
             /* precisions (totals cancel heavily; fp32 would leave systematic    */ \
@@ -82,10 +117,16 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
             fp = inside ? fp : (R)0;                                                  \
             if (inside) {                                                             \
                 double q2inv = 1.0 / q2;                                              \
-                double q6inv = q2inv * q2inv * q2inv;                                 \
-                double d12 = g_pair.c12[a], d6 = g_pair.c6[a];                        \
-                double wd = q6inv * (12.0 * d12 * q6inv - 6.0 * d6);                  \
-                if (EV) { pe += q6inv * (d12 * q6inv - d6) - g_pair.ushift[a]; vir += wd; } \
+                double wd, ud;                                                        \
+                if (TAB) {                                                            \
+                    tab_uw(a, q2, ud, wd);                                            \
+                } else {                                                              \
+                    double q6inv = q2inv * q2inv * q2inv;                             \
+                    double d12 = g_pair.c12[a], d6 = g_pair.c6[a];                    \
+                    wd = q6inv * (12.0 * d12 * q6inv - 6.0 * d6);                     \
+                    ud = q6inv * (d12 * q6inv - d6) - g_pair.ushift[a];               \
+                }                                                                     \
+                if (EV) { pe += ud; vir += wd; }                                      \
                 if (STRESS) {                                                         \
                     double gp = wd * q2inv;                                           \
                     double gx = gp * ex, gy = gp * ey, gz = gp * ez;                  \
@@ -106,7 +147,7 @@ __device__ __forceinline__ void load_pair_table(PairTab<R> &t)
 // The force part is branch-free (pairs beyond the cut-off contribute a zero
 // through a select).  FAST2: at most two species — the particle's row of the
 // table sits in registers and is picked with selects instead of shared loads.
-template <typename R, bool EV, bool STRESS, bool FAST2>
+template <typename R, bool EV, bool STRESS, bool FAST2, bool TAB>
 __device__ __forceinline__ void pair_row(const typename Pos4<R>::type *__restrict__ pos,
                                          const int *__restrict__ row, int cnt,
                                          typename Pos4<R>::type pi, const Box<R> &box,
@@ -170,7 +211,7 @@ template <typename R> struct ForceArgs {
 
 // Forces (+ per-particle energy / virial, + stress partials) of the current
 // configuration, stored.  `guarded` launches obey the speculative-batch flags.
-template <typename R, bool EV, bool STRESS>
+template <typename R, bool EV, bool STRESS, bool TAB>
 __global__ void __launch_bounds__(FORCE_THREADS)
 k_force(ForceArgs<R> a)
 {
@@ -190,8 +231,9 @@ k_force(ForceArgs<R> a)
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
         const int nsp = g_pair.nsp;
         // (a ghost has an empty row: nnb == 0)
-        if (nsp <= 2) pair_row<R, EV, STRESS, true>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
-        else pair_row<R, EV, STRESS, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        if (TAB) pair_row<R, EV, STRESS, false, true>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        else if (nsp <= 2) pair_row<R, EV, STRESS, true, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
+        else pair_row<R, EV, STRESS, false, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, st);
         a.frc[i] = make4(fx, fy, fz, (R)(0.5 * pe));
         if (EV) a.vir[i] = (R)(0.5 * vir);
     }
@@ -337,7 +379,7 @@ __device__ __forceinline__ void step_epilogue(const StepArgs<R> &a, Ctl *ctl, un
 //   Nose-Hoover    xi += dt/tau^2 (T/T0 - 1), h = xi dt/2,           a = (1-h)/(1+h), b = 1/(1+h)
 // (the leap-frog form used by RUMD's IntegratorNVT); T is the kinetic temperature of the
 // half-step velocities, (N-1) d degrees of freedom (atooms/system/system.py:164-179).
-template <typename R, bool NVT>
+template <typename R, bool NVT, bool TAB>
 __global__ void __launch_bounds__(FORCE_THREADS, (sizeof(R) == 4 ? B2_MINBLK32 : B2_MINBLK64))
 k_step_nve(StepArgs<R> a)
 {
@@ -369,8 +411,9 @@ k_step_nve(StepArgs<R> a)
         double pe = 0, vir = 0;
         const int *row = a.nbr + ((size_t)(i >> 5) * a.cap) * 32 + (i & 31);
         const int nsp = g_pair.nsp;
-        if (nsp <= 2) pair_row<R, false, false, true>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
-        else pair_row<R, false, false, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        if (TAB) pair_row<R, false, false, false, true>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        else if (nsp <= 2) pair_row<R, false, false, true, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
+        else pair_row<R, false, false, false, false>(pos, row, a.nnb[i], pi, a.box, tab, nsp, fx, fy, fz, pe, vir, nullptr);
         V4 v = a.vel[i];
         R s = a.kick / v.w;
         if (NVT) {

@@ -418,6 +418,7 @@ __device__ __forceinline__ void pair_row_win(const P *win, const unsigned short 
                                              R &fx, R &fy, R &fz, double &pe, double &vir, double *st)
 {
     constexpr int U = WinUnroll<R, EV>::U;
+    constexpr bool TAB = false;          // tabulated potentials run on the global-index list
     const int ti = ptype(pi) * nsp;
     R a12_0 = 0, a6_0 = 0, rc_0 = 0, a12_1 = 0, a6_1 = 0, rc_1 = 0;
     if (FAST2) {

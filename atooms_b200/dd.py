@@ -62,7 +62,7 @@ class SlabDomain(object):
         if on_gpu:
             self.engine.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
         self.engine.set_box(self.side, self.center)
-        self.engine.set_pair_table(self.model.eps, self.model.sigma, self.model.rcut, self.model.shifted)
+        self.engine.set_model(self.model)
         self.engine.set_skin(self.skin)
         f64 = dict(dtype=torch.float64, device=self.dev)
         n = len(species)

@@ -103,7 +103,7 @@ class Interaction(_Base):
                 self._engine.close()
             self._engine = capi.Engine(self.precision, device=self.device, library=self._library)
             self._engine.set_box(cell.side, cell.center)
-            self._engine.set_pair_table(self.model.eps, self.model.sigma, self.model.rcut, self.model.shifted)
+            self._engine.set_model(self.model)
             self._engine.set_skin(self.skin)
             self._key = key
         # host -> device: the whole configuration, every call (the generic protocol is stateless)

@@ -258,7 +258,7 @@ class System(object):
         self._skin_value = float(skin)
         self._engine = capi.Engine(self.precision, device=device, library=library)
         self._engine.set_box(self.cell.side, self.cell.center)
-        self._engine.set_pair_table(self.model.eps, self.model.sigma, self.model.rcut, self.model.shifted)
+        self._engine.set_model(self.model)
         self._engine.set_skin(skin)
         self._engine.upload(self._pos, self._ids, self._vel, self._mass)
         self._host_pos_dirty = False     # host positions changed since the last push

@@ -138,6 +138,18 @@ int b2_set_box(b2_ctx *ctx, const double side[3], const double center[3]);
 int b2_set_pair_table(b2_ctx *ctx, int nsp, const double *eps,
                       const double *sigma, const double *rcut, int shifted);
 
+/* General pair potentials as lookup tables.  The reference describes an interaction as
+ * func / params / species / cutoff with `npoints` = 20000 tabulation points
+ * (atooms/trajectory/hdf5.py:21-43: _PairPotential, _CutOff; "potential tabulation",
+ * CHANGELOG.md:151) and leaves the evaluation to its engines.  Here the caller samples
+ *   u[a][k] = u_ab(r),  w[a][k] = -r du_ab/dr   at  r^2 = k rcut_ab^2 / (npoints - 1),
+ * a = ti * nsp + tj, k = 0 .. npoints - 1 (whatever cut-off scheme it wants is already in u),
+ * and the kernels interpolate linearly in r^2: F_i = (w / r^2) (r_i - r_j) for r < rcut_ab.
+ * The first samples (r -> 0) may hold any finite value.  Replaces b2_set_pair_table for this
+ * context; replica batches (b2_batch_*) stay 12-6 Lennard-Jones.                              */
+int b2_set_pair_tabulated(b2_ctx *ctx, int nsp, int npoints, const double *rcut,
+                          const double *u, const double *w);
+
 /* Verlet skin (LAMMPS `neighbor 0.3 bin`, tests/test_lammps.py:27).         */
 int b2_set_skin(b2_ctx *ctx, double skin);
 

@@ -48,6 +48,9 @@ struct b2_ctx {
     int nsp, shifted;
     double c6[MAXSP * MAXSP], c12[MAXSP * MAXSP], rc2[MAXSP * MAXSP], ushift[MAXSP * MAXSP];
     double rcut[MAXSP * MAXSP], rcut_max;
+    /* tabulated potentials (b2_set_pair_tabulated): uniform in r^2 over [0, rc^2], linear interpolation */
+    int tab_np;
+    double *tab_u, *tab_w, tab_scale[MAXSP * MAXSP];
     double skin;
     double *pos, *vel, *mass, *frc, *pe, *vir, *ref;
     int32_t *spe, *img, *img_ref;
@@ -142,6 +145,7 @@ int b2_destroy(b2_ctx *c)
 {
     if (!c) return B2_OK;
     free_particles(c);
+    free(c->tab_u); free(c->tab_w);
     free(c);
     return B2_OK;
 }
@@ -176,6 +180,7 @@ int b2_set_pair_table(b2_ctx *c, int nsp, const double *eps, const double *sigma
 {
     if (!c || !eps || !sigma || !rcut) return fail(c, B2_EINVAL, "b2_set_pair_table: NULL argument");
     if (nsp < 1 || nsp > MAXSP) return fail(c, B2_EINVAL, "b2_set_pair_table: 1 <= nsp <= 8");
+    c->tab_np = 0;
     c->nsp = nsp;
     c->shifted = shifted;
     c->rcut_max = 0.0;
@@ -192,6 +197,34 @@ int b2_set_pair_table(b2_ctx *c, int nsp, const double *eps, const double *sigma
         double ir2 = 1.0 / c->rc2[a];
         double ir6 = ir2 * ir2 * ir2;
         c->ushift[a] = shifted ? ir6 * (c->c12[a] * ir6 - c->c6[a]) : 0.0;
+        if (rcut[a] > c->rcut_max) c->rcut_max = rcut[a];
+    }
+    c->have_table = 1;
+    c->list_valid = c->forces_valid = 0;
+    return B2_OK;
+}
+
+int b2_set_pair_tabulated(b2_ctx *c, int nsp, int npoints, const double *rcut, const double *u, const double *w)
+{
+    if (!c || !rcut || !u || !w) return fail(c, B2_EINVAL, "b2_set_pair_tabulated: NULL argument");
+    if (nsp < 1 || nsp > MAXSP || npoints < 2) return fail(c, B2_EINVAL, "b2_set_pair_tabulated: bad sizes");
+    size_t count = (size_t)nsp * nsp * npoints;
+    free(c->tab_u); free(c->tab_w);
+    c->tab_u = (double *)malloc(count * sizeof(double));
+    c->tab_w = (double *)malloc(count * sizeof(double));
+    if (!c->tab_u || !c->tab_w) return fail(c, B2_ENOMEM, "b2_set_pair_tabulated: out of memory");
+    memcpy(c->tab_u, u, count * sizeof(double));
+    memcpy(c->tab_w, w, count * sizeof(double));
+    c->tab_np = npoints;
+    c->nsp = nsp;
+    c->shifted = 0;
+    c->rcut_max = 0.0;
+    for (int a = 0; a < nsp * nsp; a++) {
+        if (!(rcut[a] > 0.0)) return fail(c, B2_EINVAL, "b2_set_pair_tabulated: rcut must be > 0");
+        c->rcut[a] = rcut[a];
+        c->rc2[a] = rcut[a] * rcut[a];
+        c->tab_scale[a] = (double)(npoints - 1) / c->rc2[a];
+        c->c6[a] = c->c12[a] = c->ushift[a] = 0.0;
         if (rcut[a] > c->rcut_max) c->rcut_max = rcut[a];
     }
     c->have_table = 1;
@@ -486,9 +519,20 @@ static int compute_forces(b2_ctx *c, const double *pos, double *frc, double *pe,
             double r2 = (dx * dx + dy * dy) + dz * dz;
             if (r2 < c->rc2[a]) {
                 double r2inv = 1.0 / r2;
-                double r6inv = r2inv * r2inv * r2inv;
-                double u = r6inv * (c->c12[a] * r6inv - c->c6[a]) - c->ushift[a];
-                double w = r6inv * (12.0 * c->c12[a] * r6inv - 6.0 * c->c6[a]);
+                double u, w;
+                if (c->tab_np) {
+                    double t = r2 * c->tab_scale[a];
+                    int kk = (int)t;
+                    if (kk > c->tab_np - 2) kk = c->tab_np - 2;
+                    double f = t - (double)kk;
+                    const double *pu = c->tab_u + (size_t)a * c->tab_np + kk, *pw = c->tab_w + (size_t)a * c->tab_np + kk;
+                    u = pu[0] + f * (pu[1] - pu[0]);
+                    w = pw[0] + f * (pw[1] - pw[0]);
+                } else {
+                    double r6inv = r2inv * r2inv * r2inv;
+                    u = r6inv * (c->c12[a] * r6inv - c->c6[a]) - c->ushift[a];
+                    w = r6inv * (12.0 * c->c12[a] * r6inv - 6.0 * c->c6[a]);
+                }
                 double fp = w * r2inv;
                 fx += fp * dx; fy += fp * dy; fz += fp * dz;
                 ei += u; wi += w;

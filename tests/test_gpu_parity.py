@@ -405,6 +405,41 @@ def test_reupload_with_more_particles(cuda_lib, oracle_lib):
     assert_observables(eng.compute(), make_engine(oracle_lib, small, ka, 64, velocities=False).compute(), 64)
 
 
+@pytest.mark.parametrize('precision', [64, 32])
+def test_tabulated_potential_against_the_oracle(cuda_lib, oracle_lib, precision):
+    """b2_set_pair_tabulated: same tables, same interpolation on both sides, so the usual tolerances hold
+    (fp64 1e-10 / 1e-12, fp32 1e-5 / 1e-6); then NVE on the tabulated forces with list refreshes."""
+    from atooms_b200 import models
+    model = models.from_potentials([
+        dict(func='gaussian', params={'epsilon': 2.0, 'sigma': 1.0}, species=[1, 1], cutoff={'scheme': 'cs', 'radius': 3.0}),
+        dict(func='inverse_power', params={'epsilon': 1.0, 'sigma': 0.9, 'exponent': 9}, species=[1, 2],
+             cutoff={'scheme': 'cf', 'radius': 2.2}),
+        dict(func='lennard_jones', params={'epsilon': 0.5, 'sigma': 0.88}, species=[2, 2], cutoff={'scheme': 'cs', 'radius': 2.2})])
+    d = rounded(replicated('ka_N1200', 2, 0.01, 2), precision)
+
+    def engine(lib, prec):
+        e = capi.Engine(prec, library=lib)
+        e.set_box(d['side'], d['center'])
+        e.set_model(model)
+        e.upload(d['position'], d['species'], d['velocity'])
+        return e
+    eng = engine(cuda_lib, precision)
+    got = eng.compute(per_particle=True, stress=True)
+    assert_observables(got, engine(oracle_lib, 64).compute(per_particle=True, stress=True), precision)
+    assert eng.stats()['list_mode'] == 0                      # tabulated potentials run on the global-index list
+    for a, b in zip(eng.neighbors(), engine(oracle_lib, precision).neighbors()):
+        assert numpy.array_equal(a, b)
+    t0 = eng.thermo()
+    eng.run_nve(400, 0.002)
+    t1 = eng.thermo()
+    assert eng.stats()['rebuilds'] >= 3
+    assert abs((t1['kinetic'] + t1['potential']) - (t0['kinetic'] + t0['potential'])) / eng.n < (2e-4 if precision == 64 else 1e-3)
+    pos, vel, _ = eng.download()
+    ref = engine(oracle_lib, 64)
+    ref.update(position=pos, velocity=vel)
+    assert_observables(eng.compute(), ref.compute(), precision)
+
+
 def test_two_contexts_with_different_tables_interleaved(cuda_lib):
     """The pair table is one __constant__ object per GPU.  Two contexts with different models, on
     different streams, stepping in turns must each keep reading their own coefficients (ADVICE r01:

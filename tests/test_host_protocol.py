@@ -109,8 +109,7 @@ def test_model_registry_and_reference_schema(oracle_lib):
                  'cutoff': {'scheme': 'c', 'radius': 2.5}}]
     lj = models.from_potentials(as_dicts)
     assert lj.nsp == 1 and not lj.shifted and lj.rcut[0, 0] == 2.5
-    with pytest.raises(ValueError):
-        models.from_potentials([dict(as_dicts[0], func='gaussian')])
+    assert models.from_potentials([dict(as_dicts[0], func='gaussian')]).tabulated     # other functions: lookup tables
     with pytest.raises(ValueError):
         models.get('no_such_model')
     inter = Interaction('kob_andersen', library=oracle_lib)
@@ -122,6 +121,54 @@ def test_model_registry_and_reference_schema(oracle_lib):
         return B200(s, 'wca', library=oracle_lib).system.potential_energy()
     assert abs(pair_energy(1.0) - 1.0) < 1e-12
     assert pair_energy(1.13) == 0.0
+
+
+def test_tabulated_potentials(oracle_lib):
+    """any pair potential of the reference's schema (func / params / species / cutoff /
+    npoints, atooms/trajectory/hdf5.py:21-43) through lookup tables."""
+    from atooms_b200 import models
+    ka = models.get('kob_andersen')
+    records = [dict(func='lennard_jones', params=p.params, species=p.species,
+                    cutoff={'scheme': 'cs', 'radius': p.cutoff.radius}, npoints=20000) for p in ka.potentials()]
+    assert isinstance(models.from_potentials(records), models.PairModel)          # representable natively
+    tab = models.TabulatedModel(records)
+    assert tab.tabulated and tab.nsp == 2 and numpy.allclose(tab.rcut, ka.rcut) and tab.npoints == 20000
+    native = B200(make_system('ka_N256_rumd', oracle_lib, ka), ka, library=oracle_lib).system
+    tabbed = B200(make_system('ka_N256_rumd', oracle_lib, tab), tab, library=oracle_lib).system
+    assert abs(tabbed.potential_energy() - native.potential_energy()) < 1e-6 * abs(native.potential_energy())
+    assert abs(tabbed.virial(False) - native.virial(False)) < 1e-5 * abs(native.virial(False))
+    # a model the 12-6 table cannot hold: Gaussian core + inverse power cross term, force-shifted cut-off
+    mixed = [dict(func='gaussian', params={'epsilon': 2.0, 'sigma': 1.0}, species=[1, 1], cutoff={'scheme': 'cs', 'radius': 3.0}),
+             dict(func='inverse_power', params={'epsilon': 1.0, 'sigma': 0.9, 'exponent': 9}, species=[1, 2],
+                  cutoff={'scheme': 'cf', 'radius': 2.2}),
+             dict(func=lambda r, a=1.0: a * numpy.exp(-r) / r, params={'a': 0.5}, species=[2, 2],
+                  cutoff={'scheme': 'cs', 'radius': 2.5})]
+    model = models.from_potentials(mixed)
+    assert isinstance(model, models.TabulatedModel) and model.nsp == 2
+    u, w = model.tables()
+    assert u.shape == (2, 2, 20000) and abs(u[0, 0, -1]) < 1e-12 and abs(u[0, 1, -1]) < 1e-12 and abs(w[0, 1, -1]) < 1e-12
+    k = 12345
+    r = numpy.sqrt(k * 9.0 / 19999)
+    assert abs(u[0, 0, k] - (2.0 * numpy.exp(-r * r) - 2.0 * numpy.exp(-9.0))) < 1e-12
+    bck = B200(make_system('ka_N256_rumd', oracle_lib, model), model, dt=0.002, library=oracle_lib)
+    s = bck.system
+    e0 = s.total_energy(per_particle=True)
+    f = s.interaction.forces if s.interaction.forces is not None else None
+    bck.run(300)
+    assert abs(s.total_energy(per_particle=True) - e0) < 2e-4          # NVE on the tabulated forces
+    # numerical check of the forces against the tabulated energy: dU = -F.dx
+    s2 = B200(make_system('ka_N256_rumd', oracle_lib, model), model, library=oracle_lib).system
+    s2.compute_interaction('forces')
+    frc = s2.interaction.forces.T.copy()
+    x = s2.view('position')
+    h = 1e-3            # (several table cells wide: u and w are interpolated independently)
+    x[7, 1] += h
+    ep = s2.potential_energy()
+    x[7, 1] -= 2 * h
+    em = s2.potential_energy()
+    assert abs(-(ep - em) / (2 * h) - frc[7, 1]) < 1e-3 * max(1.0, abs(frc[7, 1]))
+    with pytest.raises(ValueError):
+        models.from_potentials([dict(mixed[0], func='no_such_function')])
 
 
 def test_observers_accessors(oracle_lib, pins):
