@@ -152,13 +152,19 @@ class B200(object):
     # binary checkpoints: the reference's fallback goes through TrajectoryXYZ and
     # breaks under numpy >= 2 (simulation/core.py:225-234)
     def write_checkpoint(self, output_path):
+        """Everything a restart needs: positions, velocities, box-crossing counters, the rmsd origin, the
+        thermostat's friction, and what identifies the system (species, masses, cell)."""
         s = self._system
         s._pull()
         numpy.savez(output_path + '.chk.npz', position=s._pos, velocity=s._vel, image=s._img, ids=s._ids,
                     names=numpy.array(s._names), mass=s._mass, radius=s._radius, side=s.cell.side,
-                    center=s.cell.center, steps=self.steps)
+                    center=s.cell.center, steps=self.steps, reference=s._engine.reference(),
+                    thermostat_xi=s._engine.thermostat_state())
 
     def read_checkpoint(self, output_path):
+        """Restore the state written by write_checkpoint into THIS system: run(a), checkpoint, restore,
+        run(b) continues as run(a + b) would, rmsd and NVT included.  The checkpoint must describe the same
+        particles (species, count) in the same cell shape; the cell's size is taken from it (NPT)."""
         path = output_path + '.chk.npz'
         if not os.path.exists(path):
             return
@@ -166,10 +172,24 @@ class B200(object):
         s = self._system
         if len(d['ids']) != len(s):
             raise ValueError('checkpoint %s holds %d particles, the system %d' % (path, len(d['ids']), len(s)))
+        if not numpy.array_equal(numpy.array(d['names'])[d['ids']], numpy.array(s._names)[s._ids]):
+            raise ValueError('checkpoint %s holds other species than the system' % path)
+        if not numpy.allclose(d['mass'], s._mass):
+            raise ValueError('checkpoint %s holds other masses than the system' % path)
+        if not numpy.allclose(d['side'], s.cell.side):
+            s.set_box(d['side'])
         s._pull()
         s._pos[:], s._vel[:] = d['position'], d['velocity']
         s._host_pos_dirty = s._host_vel_dirty = True
         s._thermo = None
+        s._push()
+        if 'image' in d:
+            s._engine.set_images(d['image'])           # after the push: b2_update counts folds on top
+            s._img[:] = d['image']
+        if 'reference' in d:
+            s._engine.set_reference(d['reference'])
+        if 'thermostat_xi' in d:
+            s._engine.set_thermostat_state(float(d['thermostat_xi']))
         self.steps = int(d['steps'])
 
 

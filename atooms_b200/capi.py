@@ -64,6 +64,11 @@ SYMBOLS = {
     'b2_last_timing': (_int, [_vp, _c_dp, _c_lp]),
     'b2_set_profile': (_int, [_vp, _int]),
     'b2_profile': (_int, [_vp, _c_dp]),
+    'b2_set_images': (_int, [_vp, _c_ip]),
+    'b2_get_reference': (_int, [_vp, _c_dp]),
+    'b2_set_reference': (_int, [_vp, _c_dp]),
+    'b2_get_thermostat': (_int, [_vp, _c_dp]),
+    'b2_set_thermostat': (_int, [_vp, _dbl]),
     'b2_host_alloc': (_int, [ctypes.POINTER(_vp), _i64]),
     'b2_host_free': (_int, [_vp]),
     'b2_kinetic_static': (_int, [_vp, _i64, _int, _vp, _vp]),
@@ -328,6 +333,28 @@ class Engine(object):
 
     def mark_reference(self):
         self._call('b2_mark_reference')
+
+    # -- restart state (see include/atooms_b200.h) ------------------------------------------------
+    def set_images(self, image):
+        image = numpy.ascontiguousarray(image, dtype=numpy.int32).reshape(self.n, 3)
+        self._call('b2_set_images', _ip(image))
+
+    def reference(self):
+        ref = numpy.empty((self.n, 3))
+        self._call('b2_get_reference', _dp(ref))
+        return ref
+
+    def set_reference(self, ref):
+        ref = numpy.ascontiguousarray(ref, dtype=numpy.float64).reshape(self.n, 3)
+        self._call('b2_set_reference', _dp(ref))
+
+    def thermostat_state(self):
+        xi = ctypes.c_double()
+        self._call('b2_get_thermostat', ctypes.byref(xi))
+        return xi.value
+
+    def set_thermostat_state(self, xi):
+        self._call('b2_set_thermostat', float(xi))
 
     # -- single point -----------------------------------------------------
     def compute(self, what=ENERGY | FORCES | VIRIAL, forces=True, per_particle=False, stress=False):

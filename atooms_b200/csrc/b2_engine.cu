@@ -1703,6 +1703,56 @@ int b2_dd_unpack(b2_ctx *c, int64_t first_id, int64_t n, const double *in_dev)
     return DISPATCH(dd_unpack, c, first_id, n, in_dev);
 }
 
+int b2_set_images(b2_ctx *c, const int32_t *image)
+{
+    NEED_PARTICLES("b2_set_images");
+    if (!image) return fail(c, B2_EINVAL, "b2_set_images: NULL argument");
+    if (c->n > 0) CU(cudaMemcpyAsync(c->img, image, 3 * (size_t)c->n * sizeof(int32_t), cudaMemcpyDefault, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return B2_OK;
+}
+
+int b2_get_reference(b2_ctx *c, double *ref)
+{
+    NEED_PARTICLES("b2_get_reference");
+    if (!ref) return fail(c, B2_EINVAL, "b2_get_reference: NULL argument");
+    const size_t n3 = 3 * (size_t)c->n;
+    if (n3) CU(cudaMemcpyAsync(ref, c->ref, n3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    for (size_t k = 0; k < n3; k++) ref[k] += c->center[k % 3];          // stored relative to the centre
+    return B2_OK;
+}
+
+int b2_set_reference(b2_ctx *c, const double *ref)
+{
+    NEED_PARTICLES("b2_set_reference");
+    if (!ref) return fail(c, B2_EINVAL, "b2_set_reference: NULL argument");
+    const size_t n3 = 3 * (size_t)c->n;
+    std::vector<double> rel(n3);
+    for (size_t k = 0; k < n3; k++) rel[k] = ref[k] - c->center[k % 3];
+    if (n3) CU(cudaMemcpy(c->ref, rel.data(), n3 * sizeof(double), cudaMemcpyHostToDevice));
+    return B2_OK;
+}
+
+int b2_get_thermostat(b2_ctx *c, double *xi)
+{
+    NEED_PARTICLES("b2_get_thermostat");
+    if (!xi) return fail(c, B2_EINVAL, "b2_get_thermostat: NULL argument");
+    int rc = pull_ctl(c);
+    if (rc) return rc;
+    *xi = c->hctl->th_xi;
+    return B2_OK;
+}
+
+int b2_set_thermostat(b2_ctx *c, double xi)
+{
+    NEED_SETTLED("b2_set_thermostat");
+    int rc = pull_ctl(c);
+    if (rc) return rc;
+    c->hctl->th_xi = xi;
+    return push_ctl(c);
+}
+
 int b2_host_alloc(void **out, int64_t bytes)
 {
     if (!out || bytes < 0) return fail(nullptr, B2_EINVAL, "b2_host_alloc: bad argument");

@@ -338,6 +338,19 @@ int b2_batch_get_state(b2_batch *batch, double *vel, int32_t *image);
 int b2_set_profile(b2_ctx *ctx, int on);
 int b2_profile(b2_ctx *ctx, double out[8]);
 
+/* State that a restart must carry besides positions and velocities (the reference's fallback
+ * checkpoint restores the whole System through a trajectory file, simulation/core.py:225-273; its RUMD
+ * backend writes the engine's own restart file, backends/rumd.py:179-187):
+ *   images     box-crossing counters, 3n int32 by particle (b2_download returns them)
+ *   reference  the unfolded rmsd origin set by b2_mark_reference, 3n doubles, absolute coordinates
+ *   thermostat the Nose-Hoover friction xi carried between b2_run_nvt calls
+ * Set them after b2_upload: run(a); save; restore; run(b) then equals run(a + b), rmsd included.       */
+int b2_set_images(b2_ctx *ctx, const int32_t *image);
+int b2_get_reference(b2_ctx *ctx, double *ref);
+int b2_set_reference(b2_ctx *ctx, const double *ref);
+int b2_get_thermostat(b2_ctx *ctx, double *xi);
+int b2_set_thermostat(b2_ctx *ctx, double xi);
+
 /* Host buffers the engine can copy to and from at full PCIe / C2C speed (page-locked memory).
  * The reference's System marshals through ordinary numpy arrays (atooms/system/system.py:398-530);
  * the array-backed System of this package keeps its host mirrors of position / velocity in such

@@ -865,6 +865,38 @@ int b2_last_timing(b2_ctx *c, double *ms, int64_t *launches)
     return B2_OK;
 }
 
+int b2_set_images(b2_ctx *c, const int32_t *image)
+{
+    if (!c || !c->pos || !image) return fail(c, B2_EINVAL, "b2_set_images: bad argument");
+    memcpy(c->img, image, (size_t)c->n * 3 * sizeof(int32_t));
+    return B2_OK;
+}
+int b2_get_reference(b2_ctx *c, double *ref)
+{
+    if (!c || !c->pos || !ref) return fail(c, B2_EINVAL, "b2_get_reference: bad argument");
+    for (int64_t k = 0; k < 3 * c->n; k++) ref[k] = c->ref[k] + c->img_ref[k] * c->side[k % 3];
+    return B2_OK;
+}
+int b2_set_reference(b2_ctx *c, const double *ref)
+{
+    if (!c || !c->pos || !ref) return fail(c, B2_EINVAL, "b2_set_reference: bad argument");
+    memcpy(c->ref, ref, (size_t)c->n * 3 * sizeof(double));
+    memset(c->img_ref, 0, (size_t)c->n * 3 * sizeof(int32_t));
+    return B2_OK;
+}
+int b2_get_thermostat(b2_ctx *c, double *xi)
+{
+    if (!c || !xi) return fail(c, B2_EINVAL, "b2_get_thermostat: bad argument");
+    *xi = c->th_xi;
+    return B2_OK;
+}
+int b2_set_thermostat(b2_ctx *c, double xi)
+{
+    if (!c) return fail(c, B2_EINVAL, "b2_set_thermostat: bad argument");
+    c->th_xi = xi;
+    return B2_OK;
+}
+
 int b2_host_alloc(void **out, int64_t bytes)
 {
     if (!out || bytes < 0) return fail(NULL, B2_EINVAL, "b2_host_alloc: bad argument");

@@ -322,6 +322,35 @@ def test_checkpoint_roundtrip(oracle_lib, tmp_path):
     assert numpy.abs(bck.system.dump('position') - after).max() < 1e-9
 
 
+def test_checkpoint_restores_images_rmsd_and_thermostat(oracle_lib, tmp_path):
+    """run(a), checkpoint, restore into a FRESH backend, run(b) == run(a + b): unfolded
+    coordinates (box-crossing counters), backend.rmsd (targeted-rmsd runs) and the Nose-Hoover friction."""
+    from atooms_b200 import Thermostat
+
+    def fresh():
+        bck = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', dt=0.004, library=oracle_lib)
+        bck.system.set_temperature(2.0, seed=3)
+        bck.system.thermostat = Thermostat(1.5, relaxation_time=0.1)
+        return bck
+    one = fresh()
+    one.run(300)
+    two = fresh()
+    two.run(120)
+    path = str(tmp_path / 'restart')
+    two.write_checkpoint(path)
+    assert numpy.abs(two.system.image).max() >= 1                 # particles did cross the box
+    three = fresh()                                               # a new process would start like this
+    three.read_checkpoint(path)
+    assert three.steps == 120 and abs(three.rmsd - two.rmsd) < 1e-12
+    three.run(180)
+    assert numpy.abs(three.system.dump('position') - one.system.dump('position')).max() < 1e-8
+    assert numpy.array_equal(three.system.image, one.system.image)
+    assert abs(three.rmsd - one.rmsd) < 1e-9 and abs(three.system.temperature - one.system.temperature) < 1e-9
+    other = B200(make_system('lj_N256', oracle_lib, 'lennard_jones'), 'lennard_jones', library=oracle_lib)
+    with pytest.raises(ValueError):
+        other.read_checkpoint(path)                               # not the same particles
+
+
 def test_minimisation_backend(oracle_lib, pins):
     """tests/test_optimization.py:20-35 without the driver: reached_steps semantics."""
     pin = pins['lj_N256_minimised']
