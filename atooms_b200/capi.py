@@ -69,6 +69,7 @@ SYMBOLS = {
     'b2_set_reference': (_int, [_vp, _c_dp]),
     'b2_get_thermostat': (_int, [_vp, _c_dp]),
     'b2_set_thermostat': (_int, [_vp, _dbl]),
+    'b2_hessian': (_int, [_vp, _c_dp]),
     'b2_host_alloc': (_int, [ctypes.POINTER(_vp), _i64]),
     'b2_host_free': (_int, [_vp]),
     'b2_kinetic_static': (_int, [_vp, _i64, _int, _vp, _vp]),
@@ -333,6 +334,12 @@ class Engine(object):
 
     def mark_reference(self):
         self._call('b2_mark_reference')
+
+    def hessian(self):
+        """(3, N, 3, N) second derivatives of the potential energy (b2_hessian)."""
+        out = numpy.empty((3, self.n, 3, self.n))
+        self._call('b2_hessian', _dp(out))
+        return out
 
     # -- restart state (see include/atooms_b200.h) ------------------------------------------------
     def set_images(self, image):

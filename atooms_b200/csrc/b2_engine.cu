@@ -1257,6 +1257,58 @@ __global__ void k_rescale_box(int n, double rx, double ry, double rz, typename P
     ref[3 * i] *= rx; ref[3 * i + 1] *= ry; ref[3 * i + 2] *= rz;
 }
 
+// Hessian of the pair energy, dense (b2_hessian): block i takes particle with ORIGINAL id i, its threads
+// the partners j; the diagonal block is minus the sum of the off-diagonal ones of the row.
+template <typename R>
+__global__ void __launch_bounds__(128)
+k_hessian(const Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0, const typename Pos4<R>::type *pos1,
+          const int *__restrict__ inv, int n, Box<R> box, double *__restrict__ out)
+{
+    typedef typename Pos4<R>::type P4;
+    const P4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
+    const int i = blockIdx.x;
+    const P4 pi = pos[inv[i]];
+    const int ti = ptype(pi) * g_pair.nsp;
+    double diag[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const size_t N = (size_t)n;
+    for (int j = threadIdx.x; j < n; j += blockDim.x) {
+        double h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        if (j != i) {
+            const P4 pj = pos[inv[j]];
+            const int a = ti + ptype(pj);
+            double d[3];
+            delta_d(pi, pj, box, d[0], d[1], d[2]);
+            const double r2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+            if (r2 < g_pair.rc2[a]) {
+                const double i2 = 1.0 / r2, i6 = i2 * i2 * i2;
+                const double c12 = g_pair.c12[a], c6 = g_pair.c6[a];
+                const double up_r = (-12.0 * c12 * i6 + 6.0 * c6) * i6 * i2;        // u'(r) / r
+                const double upp = (156.0 * c12 * i6 - 42.0 * c6) * i6 * i2;        // u''(r)
+                const double k = (upp - up_r) * i2;
+                for (int p = 0; p < 3; p++)
+                    for (int q = 0; q < 3; q++) {
+                        const double v = k * d[p] * d[q] + (p == q ? up_r : 0.0);   // d2u / dx_ip dx_iq
+                        h[3 * p + q] = -v;                                          // ... / dx_ip dx_jq
+                        diag[3 * p + q] += v;
+                    }
+            }
+        }
+        if (j != i)
+            for (int p = 0; p < 3; p++)
+                for (int q = 0; q < 3; q++) out[((p * N + i) * 3 + q) * N + j] = h[3 * p + q];
+    }
+    __shared__ double s_d[4][9];
+    for (int k = 0; k < 9; k++) {
+        const double v = warp_sum(diag[k]);
+        if ((threadIdx.x & 31) == 0) s_d[threadIdx.x >> 5][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 9) {
+        const int p = threadIdx.x / 3, q = threadIdx.x % 3;
+        out[((p * N + i) * 3 + q) * N + i] = s_d[0][threadIdx.x] + s_d[1][threadIdx.x] + s_d[2][threadIdx.x] + s_d[3][threadIdx.x];
+    }
+}
+
 // ---------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------
@@ -1751,6 +1803,32 @@ int b2_set_thermostat(b2_ctx *c, double xi)
     if (rc) return rc;
     c->hctl->th_xi = xi;
     return push_ctl(c);
+}
+
+int b2_hessian(b2_ctx *c, double *out)
+{
+    NEED_PARTICLES("b2_hessian");
+    if (!out) return fail(c, B2_EINVAL, "b2_hessian: NULL argument");
+    if (c->tabulated) return fail(c, B2_EUNSUPPORTED, "b2_hessian: analytic second derivatives exist for the 12-6 table only");
+    const int64_t n = c->n;
+    if (n > B2_HESSIAN_MAX_PARTICLES)
+        return fail(c, B2_EINVAL, "b2_hessian: n = %lld exceeds B2_HESSIAN_MAX_PARTICLES = %d (the matrix is dense: 9 n^2 doubles)",
+                    (long long)n, B2_HESSIAN_MAX_PARTICLES);
+    if (n == 0) return B2_OK;
+    double *dev = nullptr;
+    const size_t count = 9 * (size_t)n * (size_t)n;
+    CU(cudaMalloc((void **)&dev, count * sizeof(double)));
+    if (c->precision == B2_FP32)
+        LAUNCH(k_hessian<float>, (int)n, 128, c->ctl, (const int4 *)c->pos[0], (const int4 *)c->pos[1], c->inv, (int)n,
+               make_box<float>(c), dev);
+    else
+        LAUNCH(k_hessian<double>, (int)n, 128, c->ctl, (const double4 *)c->pos[0], (const double4 *)c->pos[1], c->inv, (int)n,
+               make_box<double>(c), dev);
+    cudaError_t e = cudaMemcpyAsync(out, dev, count * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(dev);
+    if (e != cudaSuccess) return fail(c, B2_ECUDA, "b2_hessian: %s", cudaGetErrorString(e));
+    return B2_OK;
 }
 
 int b2_host_alloc(void **out, int64_t bytes)

@@ -6,7 +6,7 @@ Drop-in for the reference's interaction protocol
 arrive as keyword arguments from `System.compute_interaction`
 (atooms/system/system.py:245-259); results are left as attributes `energy`,
 `virial`, `forces` ((ndim, N), Fortran order, like `zeros_like(position)`),
-`stress` ((ndim, ndim)).  `hessian` is out of scope.
+`stress` ((ndim, ndim)), `hessian` ((ndim, N, ndim, N), dense: small systems only).
 
 Two ways in:
   * `compute(observable, position, particle, cell)` — the generic protocol,
@@ -87,8 +87,6 @@ class Interaction(_Base):
         if observable is None:
             observable = 'forces'
         assert observable in self.observable, 'unsupported observable {}'.format(observable)
-        if observable == 'hessian':
-            raise NotImplementedError('the hessian observable is out of scope of the B200 engine')
         ndim, n = position.shape
         if ndim != 3:
             raise ValueError('the B200 engine is three-dimensional')
@@ -108,6 +106,9 @@ class Interaction(_Base):
             self._key = key
         # host -> device: the whole configuration, every call (the generic protocol is stateless)
         self._engine.upload(position, ids, None, mass)
+        if observable == 'hessian':                  # interaction.py:76-82: shape (ndim, N, ndim, N)
+            self.hessian = self._engine.hessian()
+            return
         self._fill(observable, self._engine, position)
 
     def _fill(self, observable, engine, like=None):
@@ -141,7 +142,9 @@ class Interaction(_Base):
             observable = 'forces'
         assert observable in self.observable, 'unsupported observable {}'.format(observable)
         if observable == 'hessian':
-            raise NotImplementedError('the hessian observable is out of scope of the B200 engine')
+            system._push()
+            self.hessian = system._engine.hessian()
+            return
         th = system._get_thermo()            # one device reduction, cached until the state changes
         self.energy = th['potential']
         if observable == 'energy':

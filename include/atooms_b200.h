@@ -43,7 +43,7 @@ extern "C" {
 #define B2_ECUDA        -2   /* CUDA runtime failure                                 */
 #define B2_ENOMEM       -3   /* allocation failed                                    */
 #define B2_ESTATE       -4   /* call order: box / table / particles not set yet      */
-#define B2_EUNSUPPORTED -5   /* e.g. observable 'hessian'                             */
+#define B2_EUNSUPPORTED -5   /* e.g. the hessian of a tabulated potential               */
 #define B2_ENOCUDA      -6   /* no CUDA device / driver: the product has no CPU path */
 
 /* arithmetic the path computes in */
@@ -52,7 +52,7 @@ extern "C" {
 
 /* `what` bit mask for b2_compute; mirrors the observable names asserted at
  * atooms/system/interaction.py:65-66 ('energy','forces','virial','stress').
- * 'hessian' is out of scope -> B2_EUNSUPPORTED.           */
+ * 'hessian' has an entry point of its own: b2_hessian.                      */
 #define B2_ENERGY  1
 #define B2_FORCES  2
 #define B2_VIRIAL  4
@@ -337,6 +337,15 @@ int b2_batch_get_state(b2_batch *batch, double *vel, int32_t *image);
  * out[2] step-kernel launches, out[3] steps done, out[4] refreshes done.   */
 int b2_set_profile(b2_ctx *ctx, int on);
 int b2_profile(b2_ctx *ctx, double out[8]);
+
+/* The 'hessian' observable of the reference's protocol (atooms/system/interaction.py:33,76-82: shape
+ * (d, N, d, N)): second derivatives of the potential energy of the current configuration,
+ *   out[((a * N + i) * 3 + b) * N + j] = d^2 U / dx_ia dx_jb ,
+ * from the analytic pair terms, all pairs within the cut-off (minimum image), particles in the caller's
+ * numbering.  Dense: 9 N^2 doubles, so n <= B2_HESSIAN_MAX_PARTICLES, else B2_EINVAL; the 12-6 table only
+ * (B2_EUNSUPPORTED after b2_set_pair_tabulated).                                                      */
+#define B2_HESSIAN_MAX_PARTICLES 4096
+int b2_hessian(b2_ctx *ctx, double *out);
 
 /* State that a restart must carry besides positions and velocities (the reference's fallback
  * checkpoint restores the whole System through a trajectory file, simulation/core.py:225-273; its RUMD

@@ -897,6 +897,39 @@ int b2_set_thermostat(b2_ctx *c, double xi)
     return B2_OK;
 }
 
+int b2_hessian(b2_ctx *c, double *out)
+{
+    if (!c || !c->pos || !out) return fail(c, B2_EINVAL, "b2_hessian: bad argument");
+    if (c->tab_np) return fail(c, B2_EUNSUPPORTED, "b2_hessian: 12-6 table only");
+    int64_t n = c->n;
+    if (n > B2_HESSIAN_MAX_PARTICLES) return fail(c, B2_EINVAL, "b2_hessian: n exceeds B2_HESSIAN_MAX_PARTICLES");
+    memset(out, 0, (size_t)(9 * n * n) * sizeof(double));
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++)
+        for (int64_t j = 0; j < n; j++) {
+            if (j == i) continue;
+            int a = TYPE(c, i) * c->nsp + TYPE(c, j);
+            double d[3];
+            for (int k = 0; k < 3; k++) {
+                d[k] = c->pos[3 * i + k] - c->pos[3 * j + k];
+                d[k] -= rint(d[k] / c->side[k]) * c->side[k];
+            }
+            double r2 = (d[0] * d[0] + d[1] * d[1]) + d[2] * d[2];
+            if (!(r2 < c->rc2[a])) continue;
+            double i2 = 1.0 / r2, i6 = i2 * i2 * i2;
+            double up_r = (-12.0 * c->c12[a] * i6 + 6.0 * c->c6[a]) * i6 * i2;
+            double upp = (156.0 * c->c12[a] * i6 - 42.0 * c->c6[a]) * i6 * i2;
+            double kk = (upp - up_r) * i2;
+            for (int p = 0; p < 3; p++)
+                for (int q = 0; q < 3; q++) {
+                    double v = kk * d[p] * d[q] + (p == q ? up_r : 0.0);
+                    out[((p * n + i) * 3 + q) * n + j] = -v;
+                    out[((p * n + i) * 3 + q) * n + i] += v;
+                }
+        }
+    return B2_OK;
+}
+
 int b2_host_alloc(void **out, int64_t bytes)
 {
     if (!out || bytes < 0) return fail(NULL, B2_EINVAL, "b2_host_alloc: bad argument");

@@ -389,8 +389,22 @@ def test_generic_interaction_protocol(oracle_lib):
     assert inter.stress.shape == (3, 3) and abs(numpy.trace(inter.stress) - inter.virial) < 1e-8
     with pytest.raises(AssertionError):
         inter.compute('bogus', position, particle, Cell(d['side']))
-    with pytest.raises(NotImplementedError):
-        inter.compute('hessian', position, particle, Cell(d['side']))
+    # hessian (interaction.py:33,76-82): (d, N, d, N), symmetric, rows sum to zero, and equal to minus the
+    # derivative of the forces (central differences on one coordinate)
+    inter.compute('hessian', position, particle, Cell(d['side']))
+    H = inter.hessian
+    assert H.shape == (3, 256, 3, 256)
+    M = H.reshape(768, 768)
+    assert numpy.abs(M - M.T).max() < 1e-9 * numpy.abs(M).max() and numpy.abs(H.sum(axis=3)).max() < 1e-8 * numpy.abs(M).max()
+    h, (i, a) = 1e-5, (17, 2)
+    shifted = position.copy(order='F')
+    shifted[a, i] += h
+    inter.compute('forces', shifted, particle, Cell(d['side']))
+    fp = inter.forces.copy()
+    shifted[a, i] -= 2 * h
+    inter.compute('forces', shifted, particle, Cell(d['side']))
+    numeric = -(fp - inter.forces) / (2 * h)                       # d2U / dx_jb dx_ia = -dF_jb / dx_ia
+    assert numpy.abs(numeric - H[:, :, a, i]).max() < 1e-5 * numpy.abs(H[:, :, a, i]).max()
     total = inter + inter                                      # interaction.py:37-55
     assert abs(total.energy - 2 * inter.energy) < 1e-9
 
