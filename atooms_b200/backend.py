@@ -59,7 +59,8 @@ class B200(object):
     version = __version__
 
     def __init__(self, inp, model='lennard_jones', dt=0.002, skin=0.3, precision='fp64', device=0,
-                 library=None, thermostat='nose-hoover', compressibility=0.1, barostat_interval=10):
+                 library=None, thermostat='nose-hoover', compressibility=0.1, barostat_interval=10,
+                 small_system_kernel=True):
         """`thermostat` names the scheme used WHEN `system.thermostat` is set (the reference's
         backends switch to NVT on that attribute, atooms/backends/lammps.py:229-241):
         'nose-hoover' (LAMMPS `fix nvt`, RUMD IntegratorNVT) or 'berendsen'."""
@@ -70,6 +71,11 @@ class B200(object):
         # steps, mu^3 = 1 - compressibility * (interval * dt / relaxation_time) * (P0 - P)
         self.compressibility = float(compressibility)
         self.barostat_interval = int(barostat_interval)
+        # NVE of a system of at most SMALL particles: the whole run() in ONE kernel launch (one thread block,
+        # configuration in shared memory, all pairs: b2_batch_run_nve) instead of one launch per step, which
+        # at this size is pure launch latency (LJ N = 256: 13.6 against 23 us per step)
+        self.small_system_kernel = bool(small_system_kernel)
+        self._small = None
         self.model = models.get(model)
         self.timestep = float(dt)
         self.skin = float(skin)
@@ -124,11 +130,42 @@ class B200(object):
             # NVT: `fix 1 all nvt temp T T relaxation_time` (lammps.py:233-235)
             s._engine.run_nvt(int(steps), self.timestep, th.temperature,
                               getattr(th, 'relaxation_time', None) or 100 * self.timestep, self.thermostat_kind)
+        elif self._small_ok(steps):
+            self._run_small(int(steps))
         else:
             s._engine.run_nve(int(steps), self.timestep)
         if steps > 0:
             s._advanced()
         self.steps += int(steps)
+
+    SMALL = 1024
+
+    def _small_ok(self, steps):
+        s = self._system
+        return (self.small_system_kernel and steps >= 20 and 2 <= len(s) <= self.SMALL
+                and not getattr(self.model, 'tabulated', False)
+                and numpy.all(s.cell.side >= 2.0 * self.model.rcut.max())           # one minimum image, all pairs
+                and numpy.allclose(s.cell.center, 0.0))
+
+    def _run_small(self, steps):
+        """The run as one launch of the replica kernel on a copy of the state (a few KB each way), then the
+        engine takes positions, velocities and box crossings back: observables, rmsd and later runs see one
+        continuous trajectory."""
+        s = self._system
+        s._pull()
+        if self._small is None:
+            self._small = capi.Batch(s.cell.side, self.model.eps, self.model.sigma, self.model.rcut,
+                                     self.model.shifted, precision=self.precision, device=self.device,
+                                     library=s._engine.lib)
+        b = self._small
+        b.upload(s._pos[None], s._ids[None], s._mass[None])
+        b.set_velocities(s._vel[None])
+        b.run_nve(steps, self.timestep)
+        pos = b.download()[0]
+        vel, img = b.state()
+        image = s._img + img[0]
+        s._engine.update(pos, vel[0])
+        s._engine.set_images(image)
 
     def _run_npt(self, steps, th, ba):
         """Thermostatted dynamics (the fused NVT step kernel) with an isotropic Berendsen barostat: every

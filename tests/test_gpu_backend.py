@@ -19,7 +19,7 @@ from atooms_b200 import B200, EnergyMinimization, System, Cell
 pytestmark = pytest.mark.gpu
 
 PROTOCOL_TESTS = [hp.test_backend_surface, hp.test_nve_pin_through_the_backend, hp.test_observers_accessors,
-                  hp.test_sync_contract, hp.test_thermostat_switches_the_backend_to_nvt, hp.test_barostat_switches_the_backend_to_npt, hp.test_deepcopy_and_reassign, hp.test_checkpoint_roundtrip, hp.test_checkpoint_restores_images_rmsd_and_thermostat,
+                  hp.test_sync_contract, hp.test_thermostat_switches_the_backend_to_nvt, hp.test_barostat_switches_the_backend_to_npt, hp.test_deepcopy_and_reassign, hp.test_small_systems_run_in_one_launch, hp.test_checkpoint_roundtrip, hp.test_checkpoint_restores_images_rmsd_and_thermostat,
                   hp.test_minimisation_backend, hp.test_generic_interaction_protocol, hp.test_trajectory_writer,
                   hp.test_model_registry_and_reference_schema, hp.test_trajectory_fast_path, hp.test_tabulated_potentials]
 # the reference's OWN drivers (Simulation, Optimization, composite Interaction, its trajectory readers,

@@ -291,6 +291,31 @@ def test_barostat_switches_the_backend_to_npt(oracle_lib):
         bck.run(10)                                              # a barostat alone is not an ensemble we run
 
 
+def test_small_systems_run_in_one_launch(oracle_lib):
+    """configs[0] (LJ N = 256): B200.run hands NVE runs of small systems to the one-block replica kernel
+    (one launch per run() instead of one per step); the trajectory, the box-crossing counters and the rmsd
+    are those of the step-by-step path."""
+    d = golden('lj_N256')
+    vel = numpy.random.default_rng(4).normal(0.0, 1.4, size=(256, 3))
+    vel -= vel.mean(axis=0)
+
+    def backend(small):
+        s = System(d['position'], d['species_names'][d['species']], Cell(d['side']), velocity=vel, model='lennard_jones',
+                   library=oracle_lib)
+        return B200(s, 'lennard_jones', dt=0.004, library=oracle_lib, small_system_kernel=small)
+    fast, slow = backend(True), backend(False)
+    assert fast._small_ok(100) and not slow._small_ok(100) and not fast._small_ok(5)
+    for _ in range(3):
+        fast.run(100)
+        slow.run(100)
+    assert fast._small is not None and slow._small is None
+    assert numpy.abs(fast.system.dump('position') - slow.system.dump('position')).max() < 1e-8
+    assert numpy.abs(fast.system.dump('velocity') - slow.system.dump('velocity')).max() < 1e-7
+    assert numpy.array_equal(fast.system.image, slow.system.image) and numpy.abs(slow.system.image).max() >= 1
+    assert abs(fast.rmsd - slow.rmsd) < 1e-8 and fast.steps == 300
+    assert abs(fast.system.total_energy() - slow.system.total_energy()) < 1e-6
+
+
 def test_deepcopy_and_reassign(oracle_lib):
     """tests/test_rumd.py:178-194."""
     bck = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib)
