@@ -261,6 +261,11 @@ class System(object):
         self._engine.set_model(self.model)
         self._engine.set_skin(skin)
         self._engine.upload(self._pos, self._ids, self._vel, self._mass)
+        if numpy.any(self.cell.side < 2.0 * self.model.rcut.max()):
+            import warnings
+            warnings.warn('cell side %g is below 2 r_cut = %g: only the nearest image of each pair interacts '
+                          '(minimum-image convention, include/atooms_b200.h)'
+                          % (self.cell.side.min(), 2.0 * self.model.rcut.max()), stacklevel=2)
         self._host_pos_dirty = False     # host positions changed since the last push
         self._host_vel_dirty = False
         self._device_newer = False       # device moved on since the last pull

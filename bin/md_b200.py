@@ -3,7 +3,7 @@
 Molecular dynamics driver for the B200 backend.
 
 Same command line as the reference's bin/md.py (which drives the RUMD
-backend, bin/md.py:12-81): input file, -T (switches to NVT), --dt, -n steps,
+backend, bin/md.py:12-81): input file, -T (switches to NVT), -P (with -T: NPT), --dt, -n steps,
 -t thermo interval, -c config interval, -C checkpoint interval, -r restart,
 output directory.  In place of RUMD's `.ff` potential script, --model names a
 registered pair model (lennard_jones, kob_andersen; atooms_b200/models.py).
@@ -24,7 +24,7 @@ def main(params):
         numpy.set_string_function = lambda *a, **k: None
     from atooms.simulation import Simulation, Scheduler, write_thermo, write_config
     from atooms.core.utils import setup_logging, mkdir
-    from atooms_b200 import B200, Thermostat
+    from atooms_b200 import B200, Thermostat, Barostat
 
     if params.verbose:
         setup_logging(level=20)
@@ -38,6 +38,10 @@ def main(params):
         if params.T is None:
             raise SystemExit('-I nvt needs a temperature (-T)')
         backend.system.thermostat = Thermostat(params.T, relaxation_time=params.tau)
+    if getattr(params, 'P', None) is not None:
+        if params.T is None:
+            raise SystemExit('-P (NPT) needs a temperature (-T) as well')
+        backend.system.barostat = Barostat(params.P, relaxation_time=getattr(params, 'tau_p', 1.0))
     sim = Simulation(backend, output_path=output_base, steps=params.steps,
                      checkpoint_interval=params.checkpoint_interval, restart=params.restart)
     if params.thermo_interval > 0:
@@ -53,6 +57,8 @@ def main(params):
 if __name__ == '__main__':
     parser = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     parser.add_argument('-T', dest='T', type=float, help='temperature (switches to NVT)')
+    parser.add_argument('-P', dest='P', type=float, help='pressure (with -T: NPT)')
+    parser.add_argument('--tau-p', dest='tau_p', type=float, default=1.0, help='barostat relaxation time')
     parser.add_argument('--dt', dest='dt', type=float, default=0.002, help='time step')
     parser.add_argument('-i', dest='input_file', required=True, help='input file (any atooms trajectory format)')
     parser.add_argument('-I', dest='integrator', default='nve', choices=['nve', 'nvt'], help='integrator')

@@ -24,7 +24,7 @@ PROTOCOL_TESTS = [hp.test_backend_surface, hp.test_nve_pin_through_the_backend, 
                   hp.test_model_registry_and_reference_schema, hp.test_trajectory_fast_path, hp.test_tabulated_potentials]
 # the reference's OWN drivers (Simulation, Optimization, composite Interaction, its trajectory readers,
 # the md.py look-alike) on the CUDA engine; the reference comes from baseline/_ref on the GPU box
-REFERENCE_DRIVER_TESTS = [hp.test_reference_simulation_driver, hp.test_reference_optimization_driver,
+REFERENCE_DRIVER_TESTS = [hp.test_reference_simulation_driver, hp.test_integration_shim, hp.test_reference_optimization_driver,
                           hp.test_interaction_with_reference_system,
                           hp.test_neighbors_export_round_trips_through_the_reference_reader,
                           hp.test_command_line_driver]

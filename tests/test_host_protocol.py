@@ -174,7 +174,9 @@ def test_tabulated_potentials(oracle_lib):
 def test_observers_accessors(oracle_lib, pins):
     """What write_thermo reads (simulation/observers.py:247-256) + the energy pins."""
     model = atooms_b200.lennard_jones(2.5, shifted=False)
-    s = B200(make_system('lj_fcc_N108', oracle_lib, model, velocities=False), model, library=oracle_lib).system
+    with pytest.warns(UserWarning, match='nearest image'):        # L = 4.76 < 2 r_cut: said, not silent (ADVICE r01)
+        s = B200(make_system('lj_fcc_N108', oracle_lib, model, velocities=False), model, library=oracle_lib).system
+    assert s._engine.stats()['small_box']
     assert round(abs(s.potential_energy(per_particle=True) - pins['lj_fcc_N108_unshifted_U_per_particle']['value']), 7) == 0
     assert round(abs(s.pressure - pins['lj_fcc_N108_unshifted_pressure']['value']), 7) == 0   # T = 0
     assert round(abs(s.force_norm(per_particle=True) - 4.2e-11), 2) == 0
@@ -537,6 +539,24 @@ def test_reference_simulation_driver(oracle_lib, pins, tmp_path):
     assert sim2.current_step == 30
     bck.run(10)
     assert numpy.abs(bck2.system.dump('position') - bck.system.dump('position')).max() < 1e-9
+
+
+@needs_ref
+def test_integration_shim(oracle_lib, pins, tmp_path):
+    """integration/b200.py under the name a maintainer gives it, atooms.backends.b200, driven by the
+    reference's Simulation."""
+    import importlib.util
+    import atooms.backends
+    from atooms.simulation import Simulation
+    spec = importlib.util.spec_from_file_location('atooms.backends.b200', os.path.join(ROOT, 'integration', 'b200.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.B200 is B200 and mod.EnergyMinimization is EnergyMinimization
+    pin = pins['lj_N1000_nve_x0']
+    bck = mod.B200(ref_data('lj_N1000_rho1.0.xyz', tmp_path), atooms_b200.lennard_jones(2.5, shifted=False),
+                   dt=pin['dt'], library=oracle_lib)
+    Simulation(bck, enable_speedometer=False).run(10)
+    assert round(abs(bck.system.particle[0].position[0] - pin['value'][1]), 5) == 0
 
 
 @needs_ref
