@@ -152,7 +152,7 @@ class B200(object):
         engine takes positions, velocities and box crossings back: observables, rmsd and later runs see one
         continuous trajectory."""
         s = self._system
-        s._pull()
+        s._pull_image()
         if self._small is None:
             self._small = capi.Batch(s.cell.side, self.model.eps, self.model.sigma, self.model.rcut,
                                      self.model.shifted, precision=self.precision, device=self.device,
@@ -192,7 +192,7 @@ class B200(object):
         """Everything a restart needs: positions, velocities, box-crossing counters, the rmsd origin, the
         thermostat's friction, and what identifies the system (species, masses, cell)."""
         s = self._system
-        s._pull()
+        s._pull_image()
         numpy.savez(output_path + '.chk.npz', position=s._pos, velocity=s._vel, image=s._img, ids=s._ids,
                     names=numpy.array(s._names), mass=s._mass, radius=s._radius, side=s.cell.side,
                     center=s.cell.center, steps=self.steps, reference=s._engine.reference(),
@@ -223,6 +223,7 @@ class B200(object):
         if 'image' in d:
             s._engine.set_images(d['image'])           # after the push: b2_update counts folds on top
             s._img[:] = d['image']
+            s._img_stale = False
         if 'reference' in d:
             s._engine.set_reference(d['reference'])
         if 'thermostat_xi' in d:

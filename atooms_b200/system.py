@@ -128,6 +128,8 @@ class _ParticleList(object):
             # the tracking subclass: hand it the tracked row views again
             p.position, p.velocity = s._pos_user[i], s._vel_user[i]
             # numpy.asarray keeps the row views (particle.py:24-30)
+            s._pull_image()
+            s._img_out = True                # a view of the counters is in user hands from now on
             p.periodic_image = s._img[i]
             self._cache[i] = p
         return p
@@ -270,6 +272,8 @@ class System(object):
         self._host_vel_dirty = False
         self._device_newer = False       # device moved on since the last pull
         self._views_out = False          # a mutable handle on the host arrays is in user hands
+        self._img_stale = False
+        self._img_out = False
         self._touched = {'pos': [False], 'vel': [False]}      # ... and was written through (see _Tracked)
         # 'always': while handles are out, both arrays are pushed before every device operation — right for any
         # writer.  'tracked': only arrays written through numpy since the last push (see _Tracked) are pushed.
@@ -322,8 +326,16 @@ class System(object):
     def _pull(self):
         """Device -> host (in place), if the device moved on."""
         if self._device_newer:
-            self._engine.download_into(self._pos, self._vel, self._img)
+            # (the box-crossing counters follow only when somebody looks at them: _pull_image)
+            self._engine.download_into(self._pos, self._vel, None)
             self._device_newer = False
+            self._img_stale = True
+
+    def _pull_image(self):
+        self._pull()
+        if self._img_stale:
+            self._engine.download_into(None, None, self._img)
+            self._img_stale = False
 
     def _hand_out(self):
         """A mutable handle on the host arrays is about to leave our hands."""
@@ -349,6 +361,8 @@ class System(object):
             self.interaction._invalidate()
         if self._views_out:
             self._pull()
+            if self._img_out:
+                self._pull_image()
 
     def _get_thermo(self):
         self._push()
@@ -370,7 +384,7 @@ class System(object):
 
     @property
     def image(self):
-        self._pull()
+        self._pull_image()
         return self._img
 
     @property
@@ -603,6 +617,7 @@ class System(object):
         new.thermostat = copy.deepcopy(self.thermostat, memo)
         new.barostat = copy.deepcopy(self.barostat, memo)
         new.reservoir = copy.deepcopy(self.reservoir, memo)
+        self._pull_image()
         new._img[:] = self._img
         if self.interaction is not None:
             it = self.interaction

@@ -367,10 +367,11 @@ def plugin_e2e(lib, precision, pos, spe, side, vel, chunks, device=0, views=True
 
     def host_observer(sim):
         # host-side work on the live arrays, the way docs/simulations.org:274-308 teaches: read the positions,
-        # rescale the velocities IN PLACE (factor 1: the run stays NVE); the edit must reach the device
+        # edit the velocities of some particles IN PLACE (factor 1: the run stays NVE); the edit must reach the
+        # device, which takes the whole velocity array (what was written where is not tracked)
         x, v = sim.system.view('position'), sim.system.view('velocity')
         seen.append(float(x[::4096, 0].sum()))
-        v *= 1.0
+        v[:4096] *= 1.0
     simulation = reference_drivers()
     n = len(spe)
     tmp = tempfile.mkdtemp()
@@ -766,7 +767,7 @@ def main():
                      'h2d_bytes_per_step': int(r['plugin']['h2d']), 'd2h_bytes_per_step': int(r['plugin']['d2h']),
                      'steps': r['plugin']['chunks'], 'backend_run_calls': r['plugin']['backend_run_calls'],
                      'through': 'Simulation(B200(System)).run(): ' + r['plugin']['driver'] +
-                                ', an observer holds host views, reads the positions and rescales the velocities '
+                                ', an observer holds host views, reads positions and edits velocities '
                                 'in place every chunk (sync = tracked: what was written is pushed before, both '
                                 'arrays are pulled after every backend.run)'}
                     if 'plugin' in r else
