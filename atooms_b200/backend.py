@@ -25,6 +25,34 @@ _PRECISION = {'fp32': 32, 'f32': 32, 'float32': 32, 'single': 32, 32: 32,
               'fp64': 64, 'f64': 64, 'float64': 64, 'double': 64, 64: 64}
 
 
+def _save_arrays(path, **arrays):
+    """Named arrays in one file: a JSON header line, then the raw buffers.  (numpy.savez goes through
+    zipfile, whose CRC-32 pass alone takes ~0.1 s on the 130 MB of a million-particle checkpoint — as much
+    as 400 MD steps — and Simulation writes one at the end of every run(), simulation/core.py:409-415.)"""
+    import json
+    meta, blobs = [], []
+    for name, a in arrays.items():
+        a = numpy.ascontiguousarray(a)
+        meta.append({'name': name, 'dtype': a.dtype.str, 'shape': list(a.shape), 'bytes': int(a.nbytes)})
+        blobs.append(a)
+    with open(path, 'wb') as fh:
+        fh.write((json.dumps(meta) + '\n').encode())
+        for a in blobs:
+            fh.write(a.data if a.nbytes else b'')
+
+
+def _load_arrays(path):
+    import json
+    with open(path, 'rb') as fh:
+        first = fh.readline()
+        if first[:2] == b'PK':                      # a round-1 checkpoint (numpy.savez)
+            return numpy.load(path)
+        out = {}
+        for m in json.loads(first.decode()):
+            out[m['name']] = numpy.frombuffer(fh.read(m['bytes']), dtype=numpy.dtype(m['dtype'])).reshape(m['shape']).copy()
+    return out
+
+
 def _last_frame(inp):
     """A System, a Trajectory (last frame) or a path, as LAMMPS.__init__ accepts
     (atooms/backends/lammps.py:151-188)."""
@@ -193,10 +221,10 @@ class B200(object):
         thermostat's friction, and what identifies the system (species, masses, cell)."""
         s = self._system
         s._pull_image()
-        numpy.savez(output_path + '.chk.npz', position=s._pos, velocity=s._vel, image=s._img, ids=s._ids,
-                    names=numpy.array(s._names), mass=s._mass, radius=s._radius, side=s.cell.side,
-                    center=s.cell.center, steps=self.steps, reference=s._engine.reference(),
-                    thermostat_xi=s._engine.thermostat_state())
+        _save_arrays(output_path + '.chk.npz', position=s._pos, velocity=s._vel, image=s._img, ids=s._ids,
+                     names=numpy.array(s._names), mass=s._mass, radius=s._radius, side=s.cell.side,
+                     center=s.cell.center, steps=numpy.array(self.steps), reference=s._engine.reference(),
+                     thermostat_xi=numpy.array(s._engine.thermostat_state()))
 
     def read_checkpoint(self, output_path):
         """Restore the state written by write_checkpoint into THIS system: run(a), checkpoint, restore,
@@ -205,7 +233,7 @@ class B200(object):
         path = output_path + '.chk.npz'
         if not os.path.exists(path):
             return
-        d = numpy.load(path)
+        d = _load_arrays(path)
         s = self._system
         if len(d['ids']) != len(s):
             raise ValueError('checkpoint %s holds %d particles, the system %d' % (path, len(d['ids']), len(s)))
@@ -227,8 +255,8 @@ class B200(object):
         if 'reference' in d:
             s._engine.set_reference(d['reference'])
         if 'thermostat_xi' in d:
-            s._engine.set_thermostat_state(float(d['thermostat_xi']))
-        self.steps = int(d['steps'])
+            s._engine.set_thermostat_state(float(numpy.asarray(d['thermostat_xi']).reshape(-1)[0]))
+        self.steps = int(numpy.asarray(d['steps']).reshape(-1)[0])
 
 
 class EnergyMinimization(B200):
