@@ -10,7 +10,6 @@ import pytest
 
 from conftest import golden
 from oracle import oracle_np as onp
-from atooms_b200 import capi
 from atooms_b200.batch import ReplicaEnsemble
 
 

@@ -13,7 +13,6 @@ import pytest
 import test_host_protocol as hp
 from conftest import golden
 from test_gpu_parity import replicated
-import atooms_b200
 from atooms_b200 import B200, EnergyMinimization, System, Cell
 
 pytestmark = pytest.mark.gpu

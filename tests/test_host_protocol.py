@@ -546,7 +546,6 @@ def test_integration_shim(oracle_lib, pins, tmp_path):
     """integration/b200.py under the name a maintainer gives it, atooms.backends.b200, driven by the
     reference's Simulation."""
     import importlib.util
-    import atooms.backends
     from atooms.simulation import Simulation
     spec = importlib.util.spec_from_file_location('atooms.backends.b200', os.path.join(ROOT, 'integration', 'b200.py'))
     mod = importlib.util.module_from_spec(spec)
