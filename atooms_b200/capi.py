@@ -70,6 +70,8 @@ SYMBOLS = {
     'b2_get_thermostat': (_int, [_vp, _c_dp]),
     'b2_set_thermostat': (_int, [_vp, _dbl]),
     'b2_hessian': (_int, [_vp, _c_dp]),
+    'b2_format_xyz': (_int, [ctypes.c_char_p, _i64, ctypes.POINTER(_i64), _i64, _c_ip, _int, ctypes.POINTER(ctypes.c_char_p),
+                      _c_dp, _c_dp, _int]),
     'b2_host_alloc': (_int, [ctypes.POINTER(_vp), _i64]),
     'b2_host_free': (_int, [_vp]),
     'b2_kinetic_static': (_int, [_vp, _i64, _int, _vp, _vp]),
@@ -146,6 +148,21 @@ class Library(object):
         if version != ABI_VERSION:
             raise OSError('atooms_b200: %s has ABI version %d, expected %d' % (path, version, ABI_VERSION))
         self.name = self.dll.b2_backend_name().decode()
+
+    def format_xyz(self, ids, names, position, velocity=None, precision=6):
+        """The particle lines of an xyz frame as bytes (b2_format_xyz: formatted on all host cores)."""
+        ids = numpy.ascontiguousarray(ids, dtype=numpy.int32)
+        pos = numpy.ascontiguousarray(position, dtype=numpy.float64)
+        vel = None if velocity is None else numpy.ascontiguousarray(velocity, dtype=numpy.float64)
+        n = len(ids)
+        raw = [str(s).encode() for s in names]
+        arr = (ctypes.c_char_p * len(raw))(*raw)
+        written = _i64()
+        args = (n, _ip(ids), len(raw), arr, _dp(pos), _dp(vel), int(precision))
+        self.check(self.dll.b2_format_xyz(None, 0, ctypes.byref(written), *args))          # size query
+        buf = numpy.empty(max(written.value, 1), dtype=numpy.uint8)
+        self.check(self.dll.b2_format_xyz(buf.ctypes.data_as(ctypes.c_char_p), buf.size, ctypes.byref(written), *args))
+        return memoryview(buf[:written.value])
 
     def host_empty(self, shape, dtype=numpy.float64):
         """A numpy array in page-locked host memory (b2_host_alloc), freed with the array: host

@@ -17,7 +17,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #define MAX_RED_BLOCKS 1024
@@ -1843,6 +1845,66 @@ int b2_hessian(b2_ctx *c, double *out)
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(dev);
     if (e != cudaSuccess) return fail(c, B2_ECUDA, "b2_hessian: %s", cudaGetErrorString(e));
+    return B2_OK;
+}
+
+int b2_format_xyz(char *out, int64_t cap, int64_t *written, int64_t n, const int32_t *ids, int nnames,
+                  const char *const *names, const double *pos, const double *vel, int precision)
+{
+    if (!written || n < 0 || (n > 0 && (!ids || !names || !pos)) || precision < 0 || precision > 17)
+        return fail(nullptr, B2_EINVAL, "b2_format_xyz: bad argument");
+    *written = 0;
+    const int per = vel ? 6 : 3;
+    size_t longest = 1;
+    for (int k = 0; k < nnames; k++) { size_t l = strlen(names[k]); if (l > longest) longest = l; }
+    /* upper bound of one line from the largest magnitude: ' -' + integer digits + '.' + decimals per number */
+    double big = 1.0;
+    for (int64_t i = 0; i < 3 * n; i++) {
+        double a = fabs(pos[i]), b = vel ? fabs(vel[i]) : 0.0;
+        if (isfinite(a) && a > big) big = a;                             /* inf and nan print in four characters */
+        if (isfinite(b) && b > big) big = b;
+    }
+    const size_t digits = (size_t)log10(big) + 2;
+    const size_t line = longest + (size_t)per * (digits + (size_t)precision + 3) + 2;
+    if (!out) { *written = (int64_t)(line * (size_t)n); return B2_OK; }       /* size query */
+    if ((int64_t)(line * (size_t)n) > cap) return fail(nullptr, B2_EINVAL, "b2_format_xyz: output buffer too small");
+    /* every chunk of rows is formatted at its worst-case offset, then the chunks are closed up in order */
+    const int64_t chunk = 4096;
+    const int64_t nchunk = (n + chunk - 1) / chunk;
+    int64_t *len = (int64_t *)malloc((size_t)(nchunk > 0 ? nchunk : 1) * sizeof(int64_t));
+    if (!len) return fail(nullptr, B2_ENOMEM, "b2_format_xyz: out of memory");
+    auto work = [&](int64_t c) {
+        char *p = out + (size_t)c * chunk * line, *p0 = p;
+        const int64_t hi = (c + 1) * chunk < n ? (c + 1) * chunk : n;
+        for (int64_t i = c * chunk; i < hi; i++) {
+            const int id = ids[i];
+            const char *name = (id >= 0 && id < nnames) ? names[id] : "?";
+            size_t l = strlen(name);
+            memcpy(p, name, l);
+            p += l;
+            for (int k = 0; k < 3; k++) p += snprintf(p, digits + (size_t)precision + 4, " %.*f", precision, pos[3 * i + k]);
+            if (vel)
+                for (int k = 0; k < 3; k++) p += snprintf(p, digits + (size_t)precision + 4, " %.*f", precision, vel[3 * i + k]);
+            *p++ = '\n';
+        }
+        len[c] = (int64_t)(p - p0);
+    };
+    {
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const int nthreads = (int)std::min<int64_t>((int64_t)std::min(hw, 64u), std::max<int64_t>(nchunk, 1));
+        std::atomic<int64_t> next(0);
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthreads; t++)
+            pool.emplace_back([&]() { for (int64_t c = next++; c < nchunk; c = next++) work(c); });
+        for (auto &th : pool) th.join();
+    }
+    int64_t at = 0;
+    for (int64_t c = 0; c < nchunk; c++) {
+        if (at != c * chunk * (int64_t)line) memmove(out + at, out + (size_t)c * chunk * line, (size_t)len[c]);
+        at += len[c];
+    }
+    free(len);
+    *written = at;
     return B2_OK;
 }
 

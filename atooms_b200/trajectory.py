@@ -244,8 +244,25 @@ class Trajectory(object):
                 fmt = '%.{}f'.format(self.precision) if b.dtype.kind == 'f' else '%s'
             formats.append(fmt)
         self._fh.write('%d\n%s\n' % (n, self._header(step, columns, system)))
-        if n:
+        if n and not self._write_native(columns, blocks):
             _format_rows(self._fh, blocks, formats)
+
+    def _write_native(self, columns, blocks):
+        """species + position [+ velocity] in three dimensions go through b2_format_xyz (all host cores)."""
+        if columns not in (['species', 'position'], ['species', 'position', 'velocity']):
+            return False
+        if any(b.ndim != 2 or b.shape[1] != 3 or b.dtype.kind != 'f' for b in blocks[1:]):
+            return False
+        try:
+            from . import capi
+            lib = capi.load()
+        except Exception:                                 # library not built: the Python formatter below
+            return False
+        names, ids = numpy.unique(numpy.asarray(blocks[0]).astype(str), return_inverse=True)
+        raw = lib.format_xyz(ids, list(names), blocks[1], blocks[2] if len(blocks) > 2 else None, self.precision)
+        self._fh.flush()
+        self._fh.buffer.write(raw)
+        return True
 
     # ---- reading ---------------------------------------------------------------------
     def _parse_header(self, line):

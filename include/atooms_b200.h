@@ -360,6 +360,15 @@ int b2_set_reference(b2_ctx *ctx, const double *ref);
 int b2_get_thermostat(b2_ctx *ctx, double *xi);
 int b2_set_thermostat(b2_ctx *ctx, double xi);
 
+/* Text formatting of a frame on the host cores, for the trajectory writers.  The reference formats
+ * one particle at a time in Python (atooms/trajectory/xyz.py:437-474: seconds per frame at a million
+ * particles); this writes the particle lines of its xyz layout, `NAME x y z [vx vy vz]\n` with
+ * `precision` decimals, for all n particles into `out` (all host cores), and returns the number of
+ * bytes in *written.  names[ids[i]] is the first column.  With out == NULL it only returns in
+ * *written a capacity that is enough for these values; B2_EINVAL when `cap` is smaller.          */
+int b2_format_xyz(char *out, int64_t cap, int64_t *written, int64_t n, const int32_t *ids, int nnames,
+                  const char *const *names, const double *pos, const double *vel, int precision);
+
 /* Host buffers the engine can copy to and from at full PCIe / C2C speed (page-locked memory).
  * The reference's System marshals through ordinary numpy arrays (atooms/system/system.py:398-530);
  * the array-backed System of this package keeps its host mirrors of position / velocity in such

@@ -458,6 +458,50 @@ def test_trajectory_writer(oracle_lib, tmp_path):
         assert [p.species for p in back.particle] == list(s.species)
 
 
+def test_trajectory_native_formatter(oracle_lib, tmp_path, monkeypatch):
+    """b2_format_xyz (frame text on all host cores) writes byte for byte what the `%` formatter writes,
+    in both dialects, with and without velocities, and answers its size query."""
+    from atooms_b200 import TrajectoryRUMD, capi
+    s = make_system('ka_N256_rumd', oracle_lib, 'kob_andersen')
+    s.view('position')[7] = [-2.9999999996, 1e-12, 2.5]
+    monkeypatch.setattr(capi, 'load', lambda path=None: oracle_lib)
+    calls, native = [], [True]
+    real_format, real_write = oracle_lib.format_xyz, Trajectory._write_native
+    monkeypatch.setattr(oracle_lib, 'format_xyz', lambda *a, **k: calls.append(1) or real_format(*a, **k), raising=False)
+    monkeypatch.setattr(Trajectory, '_write_native', lambda self, c, b: native[0] and real_write(self, c, b))
+    for cls, variables, precision in ((Trajectory, ['species', 'position'], 6), (Trajectory, ['species', 'pos', 'vel'], 12),
+                                      (TrajectoryRUMD, ['species', 'position', 'velocity'], 9)):
+        texts = []
+        for native[0] in (True, False):
+            path = str(tmp_path / ('f%d.xyz' % native[0]))
+            with cls(path, 'w') as th:
+                th.timestep, th.precision, th.variables = 0.002, precision, variables
+                th.write(s, 0)
+                th.write(s, 3)
+            texts.append(open(path, 'rb').read())
+        assert texts[0] == texts[1] and len(texts[0]) > 256 * 20
+    native[0] = True
+    assert len(calls) == 6                                  # the native path did run, twice per file
+    # columns it does not cover fall back to the block formatter
+    with Trajectory(str(tmp_path / 'r.xyz'), 'w') as th:
+        th.variables = ['species', 'position', 'radius']
+        th.write(s, 0)
+    assert len(calls) == 6
+    # errors: capacity too small, bad precision
+    import ctypes
+    ids = numpy.zeros(4, dtype=numpy.int32)
+    pos = numpy.zeros((4, 3))
+    names = (ctypes.c_char_p * 1)(b'A')
+    need = ctypes.c_int64()
+    dp = lambda a: a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+    ip = ids.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
+    assert oracle_lib.dll.b2_format_xyz(None, 0, ctypes.byref(need), 4, ip, 1, names, dp(pos), None, 6) == 0
+    assert need.value >= 4 * len('A 0.000000 0.000000 0.000000\n')
+    buf = ctypes.create_string_buffer(8)
+    assert oracle_lib.dll.b2_format_xyz(buf, 8, ctypes.byref(need), 4, ip, 1, names, dp(pos), None, 6) != 0
+    assert oracle_lib.dll.b2_format_xyz(None, 0, ctypes.byref(need), 4, ip, 1, names, dp(pos), None, 40) != 0
+
+
 def test_trajectory_fast_path(oracle_lib, tmp_path):
     """block-formatted writer, read mode, RUMD dialect, in-memory snapshots — none of
     them builds Particle objects."""
