@@ -89,7 +89,7 @@ struct b2_ctx {
     int *b8start = nullptr, *tile_base = nullptr, *sbt = nullptr;
     int nb8codes = 0, nsb_total = 0, win_tab_alloc = 0, win_sb_alloc = 0;
     bool win_off = false;            // windows do not fit: this context keeps the global-index list
-    size_t smem_optin = 0;
+    size_t smem_optin = 0, smem_sm = 0;      // shared memory a block may opt into, and of an SM
     // control / reductions / staging
     Ctl *ctl = nullptr, *hctl = nullptr;
     double *partial = nullptr;
@@ -410,7 +410,30 @@ template <typename R> struct Impl {
         CU(cudaFuncSetAttribute(k_step_win<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
         CU(cudaFuncSetAttribute(k_force_win<R, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
         CU(cudaFuncSetAttribute(k_force_win<R, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        CU(cudaFuncSetAttribute(k_build_list_win<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)build_smem(c)));
+        CU(cudaFuncSetAttribute(k_build_list_win<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)build_smem(c)));
         return B2_OK;
+    }
+#ifndef BW_MAXROWS
+#define BW_MAXROWS 128
+#endif
+#ifndef BW_BLOCKS
+#define BW_BLOCKS 2
+#endif
+    // Shared memory of the list build: the window (it reads up to four records past it), then per warp a buffer
+    // of list rows (64 bytes each).  Up to 128 rows, as many as leave room for two blocks per SM.
+    static int build_rows(const b2_ctx *c)
+    {
+        const size_t window = (size_t)c->grid.wcap * sizeof(P4) + 64, fixed = 4096;
+        const size_t half = (c->smem_sm > 1024 * BW_BLOCKS ? c->smem_sm - 1024 * BW_BLOCKS : 0) / BW_BLOCKS;
+        size_t room = half > window + fixed ? half - window - fixed : 0;
+        if (room < 8 * 64 * (WIN_THREADS / 32) && c->smem_optin > window + fixed)          // one block per SM then
+            room = c->smem_optin - window - fixed;
+        return (int)std::min<size_t>(BW_MAXROWS, room / (64 * (WIN_THREADS / 32))) & ~3;
+    }
+    static size_t build_smem(const b2_ctx *c)
+    {
+        return (size_t)c->grid.wcap * sizeof(P4) + 64 + (size_t)build_rows(c) * 64 * (WIN_THREADS / 32);
     }
 
     // ints the list needs for `cap` slots per particle
@@ -508,6 +531,15 @@ template <typename R> struct Impl {
         const Grid &g = c->grid;
         if (g.m == 2 && !g.allpairs && g.nc[0] >= 7 && g.nc[1] >= 7 && g.nc[2] >= 7 && n < (1 << 28) && (!force_walk || g.win)) {
             int codes = 1 << (3 * g.cellbits - 3);
+            static const bool gathered = getenv("B2_BUILD_GATHERED") && atoi(getenv("B2_BUILD_GATHERED")) != 0;   // A/B timing
+            if (g.win && !gathered) {
+                auto kern = c->nsp <= 2 ? k_build_list_win<R, true> : k_build_list_win<R, false>;
+                const int kbuf = std::min(build_rows(c), c->cap & ~3);
+                LAUNCH_SMEM(kern, win_grid(c), WIN_THREADS, build_smem(c), c->ctl, p0, p1, box, c->grid, (const int *)c->sbt,
+                            reinterpret_cast<unsigned short *>(c->nbr), c->nnb, c->cap, kbuf);
+                LAUNCH(k_rebuild_finish, 1, 1, c->ctl);
+                return;
+            }
             auto build = g.win ? (c->nsp <= 2 ? k_build_list_sc<R, true, true> : k_build_list_sc<R, false, true>)
                                : (c->nsp <= 2 ? k_build_list_sc<R, true, false> : k_build_list_sc<R, false, false>);
             // one warp per code (a strided grid of a few blocks per SM was measured 10 % slower:
@@ -1378,6 +1410,9 @@ int b2_create(int device, int precision, b2_ctx **out)
             int optin = 0;
             if ((e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)) != cudaSuccess) break;
             ctx->smem_optin = (size_t)std::max(optin, 0);
+            int per_sm = 0;
+            if ((e = cudaDeviceGetAttribute(&per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device)) != cudaSuccess) break;
+            ctx->smem_sm = (size_t)std::max(per_sm, 0);
         }
         if ((e = cudaMalloc((void **)&ctx->ctl, sizeof(Ctl))) != cudaSuccess) break;
         if ((e = cudaMemset(ctx->ctl, 0, sizeof(Ctl))) != cudaSuccess) break;

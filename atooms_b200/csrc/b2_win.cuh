@@ -372,6 +372,269 @@ __device__ __forceinline__ reld4 to_rel(const double4 &p, const WinOrigin<double
     return r;
 }
 
+// ---- list build on the staged window ------------------------------------------------------------
+// One block per super-block, one warp per 2x2x2 block of cells ("B8") of it.  The window is staged as in
+// the step kernel and turned, in place, into float coordinates relative to the super-block's centre with the
+// species in the fourth lane.  The neighbours of a B8 block lie in the 3x3x3 B8 runs around it, and three
+// runs adjacent along x are ONE stretch of window offsets: a warp walks nine stretches, every lane testing
+// the same record (a broadcast LDS.128) against its own particle, and an entry of the list is the loop
+// index itself.  No candidate is fetched from global memory by the loop (k_build_list_sc gathered its
+// candidates per warp and spent 45 % of its time waiting for them: profiles/r02_ncu_k_build_list_sc_win_fp32.txt).
+// Float test with a band around the threshold, band cases settled with the canonical predicate, as in
+// k_build_list_sc: the list is bit-exact against the oracle's.
+#ifndef BW_MINBLK
+#define BW_MINBLK 2
+#endif
+
+// window records -> float4 (x, y, z relative to the centre; w = species: 0.f / 1.f when FAST2, else its integer bits)
+template <bool FAST2>
+__device__ __forceinline__ float4 bw_record(const relf4 &q)
+{
+    const int t = q.t & 0xff;
+    return make_float4(q.x, q.y, q.z, FAST2 ? (float)t : __int_as_float(t));
+}
+template <bool FAST2>
+__device__ __forceinline__ float4 bw_record(const reld4 &q)
+{
+    const int t = (int)q.t & 0xff;
+    return make_float4((float)q.x, (float)q.y, (float)q.z, FAST2 ? (float)t : __int_as_float(t));
+}
+template <bool FAST2>
+__device__ __forceinline__ void bw_convert(unsigned char *raw, int W, const WinOrigin<float> &org, const Box<float> &box)
+{
+    const int4 *win = reinterpret_cast<const int4 *>(raw);
+    float4 *cand = reinterpret_cast<float4 *>(raw);
+    for (int k = threadIdx.x; k < W; k += WIN_THREADS) cand[k] = bw_record<FAST2>(to_rel(win[k], org, box));   // same address, same thread
+    __syncthreads();
+}
+template <bool FAST2>
+__device__ __forceinline__ void bw_convert(unsigned char *raw, int W, const WinOrigin<double> &org, const Box<double> &box)
+{
+    // 32-byte records become 16-byte ones at the front of the same buffer: a round of WIN_THREADS records is
+    // read, then written behind a barrier; what a round writes lies below everything later rounds read
+    const double4 *win = reinterpret_cast<const double4 *>(raw);
+    float4 *cand = reinterpret_cast<float4 *>(raw);
+    for (int base = 0; base < W; base += WIN_THREADS) {
+        const int k = base + threadIdx.x;
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k < W) q = bw_record<FAST2>(to_rel(win[k], org, box));
+        __syncthreads();
+        if (k < W) cand[k] = q;
+    }
+    __syncthreads();
+}
+
+// entry `off` of a lane into the warp's row buffer (shared-memory address sptr), predicated like sc_append16
+__device__ __forceinline__ void bw_append_s(bool hit, unsigned &sptr, int off)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %1, 0;\n\t"
+                 "@q st.shared.b16 [%0], %2;\n\t@q add.u32 %0, %0, 64;\n\t}"
+                 : "+r"(sptr) : "r"((int)hit), "h"((unsigned short)off) : "memory");
+}
+// the buffered rows of a warp -> the list, one row of 32 lanes per store.  Rows beyond a lane's own count carry
+// leftovers: they land in slots of its row that are rewritten later or never read.
+__device__ __forceinline__ void bw_flush(unsigned sbuf0, int lane, bool valid, int cnt, unsigned short *row16)
+{
+    int kmax = cnt;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+    if (valid) {
+        const unsigned src = sbuf0 + 2u * (unsigned)lane;
+#pragma unroll 4
+        for (int k = 0; k < kmax; k++) {
+            unsigned short v;
+            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(src + 64u * (unsigned)k));
+            row16[(size_t)k * 32] = v;
+        }
+    }
+    __syncwarp();
+}
+
+template <typename R, bool FAST2>
+__global__ void __launch_bounds__(WIN_THREADS, BW_MINBLK)
+k_build_list_win(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0, const typename Pos4<R>::type *pos1,
+                 Box<R> box, Grid g, const int *__restrict__ sbt, unsigned short *__restrict__ nbr16,
+                 int *__restrict__ nnb, int cap, int kbuf)
+{
+    if (!ctl->halt_rebuild) return;
+    typedef typename Pos4<R>::type P4;
+    extern __shared__ __align__(128) unsigned char win_raw[];      // the window, then kbuf rows of 64 bytes per warp
+    __shared__ __align__(8) unsigned long long s_bar;
+    __shared__ int sP[WIN_RUNS + 1], sS[WIN_RUNS];
+    __shared__ R s_rl2[B2_MAXSP * B2_MAXSP];
+    __shared__ float s_hi[B2_MAXSP * B2_MAXSP], s_lo[B2_MAXSP * B2_MAXSP];
+    const P4 *__restrict__ pos = ctl->cur ? pos1 : pos0;
+    const int gi = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    const int *__restrict__ T = sbt + (size_t)gi * SBT_STRIDE;
+    const int W = T[3];
+    if (threadIdx.x == 0) atomicMax(&ctl->win_max, (unsigned)W);
+    if (W > g.wcap || W > 65535) {                   // does not fit the shared memory: the host enlarges it
+        if (threadIdx.x == 0) ctl->overflow = 1u;
+        return;
+    }
+    if (T[1] == 0) return;
+    const WinInfo wi = win_stage<R>(sbt, pos, reinterpret_cast<P4 *>(win_raw), &s_bar);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp == 0) win_layout_load(T, lane, sP, sS);
+    if (threadIdx.x < B2_MAXSP * B2_MAXSP) {
+        const R rl2 = rl2_of(g_pair, threadIdx.x, (R)0);
+        s_rl2[threadIdx.x] = rl2;
+        // half-width of the band, relative to the pair's threshold: a coordinate (at most 4 cells from the
+        // centre) is good to ~5e-7 of the cell width, r^2 to ~2e-6 r_list,max^2 in the worst case
+        const float eps = SC_EPS * fmaxf(1.f, sqrtf(g.reach2 / fmaxf((float)rl2, 1e-30f)));
+        s_hi[threadIdx.x] = (float)rl2 * (1.f + eps);
+        s_lo[threadIdx.x] = (float)rl2 * (1.f - eps);
+    }
+    WinOrigin<R> org;
+    win_origin_load(T, org);
+    win_wait(&s_bar);
+    bw_convert<FAST2>(win_raw, W, org, box);          // ends with a barrier: layout and thresholds are visible too
+    const float4 *__restrict__ cand = reinterpret_cast<const float4 *>(win_raw);
+    const int nsp = g_pair.nsp;
+    const unsigned sbuf0 = smem_u32(win_raw) + (unsigned)g.wcap * (unsigned)sizeof(P4) + 64u + (unsigned)(warp * kbuf) * 64u;
+    for (int b = warp; b < 8; b += WIN_THREADS / 32) {
+        const int ox = b & 1, oy = (b >> 1) & 1, oz = b >> 2;
+        // the last super-block of an axis may be two cells wide
+        if (4 * (int)blockIdx.x + 2 * ox >= g.nc[0] || 4 * (int)blockIdx.y + 2 * oy >= g.nc[1] || 4 * (int)blockIdx.z + 2 * oz >= g.nc[2])
+            continue;
+        const int rx = 1 + ox, ry = 1 + oy, rz = 1 + oz;
+        const int r_own = (rz * 4 + ry) * 4 + rx;
+        const int own0 = sP[r_own], n_own = sP[r_own + 1] - own0, slot0 = sS[r_own];
+        for (int b0 = 0; b0 < n_own; b0 += 32) {          // more than 32 particles in the block: again
+            const bool valid = b0 + lane < n_own;
+            const int self = own0 + (valid ? b0 + lane : 0);
+            const int slot = slot0 + (self - own0);
+            const P4 pi = pos[slot];
+            const bool active = valid && !is_ghost(pi);   // ghosts act as neighbours but own no row
+            const int ti = ptype(pi);
+            const float4 me = cand[self];
+            const float px = me.x, py = me.y, pz = me.z;
+            const float *hi_row = s_hi + ti * nsp, *lo_row = s_lo + ti * nsp;
+            const float hi0 = active ? hi_row[0] : -1.f;
+            const float dhi = active ? hi_row[nsp > 1 ? 1 : 0] - hi_row[0] : 0.f;
+            float bandw = 0.f;                            // widest band of this particle's row of the pair table
+            for (int tj = 0; tj < nsp; tj++) bandw = fmaxf(bandw, hi_row[tj] - lo_row[tj]);
+            if (!active) bandw = -1.f;                    // (its thresholds are negative: t > 0 always)
+            const int li = slot - wi.first;               // rows live in tiles local to the super-block
+            unsigned short *row16 = nbr16 + ((size_t)(wi.tbase + (li >> 5)) * (size_t)cap) * 32 + (li & 31);
+            // The listed pair closest to its threshold, with no select in the loop: t = r^2 - threshold is negative
+            // for a listed pair, and among negative floats the one of smallest magnitude has the smallest bit
+            // pattern read as a signed integer (pairs that are not listed have t >= 0, a non-negative integer).
+            int nearbits = 0;
+            // Entries go to the warp's buffer in shared memory first (rows of 32 lanes, as in the list) and from
+            // there to the list one 64-byte row per store; a 2-byte store per entry straight into the list touches
+            // a sector per lane, and the loop then waits for the store unit to release its operands (a quarter
+            // of the loop's time, profiles/r02_ncu_k_build_list_win_v1.txt).  Once some lane has filled the
+            // buffer, the rows are written out and every lane appends to the list directly (`direct`).
+            const unsigned sptr0 = sbuf0 + 2u * (unsigned)lane;
+            unsigned sptr = sptr0;                        // where this lane's next entry goes
+            const unsigned sfull = sptr0 + 64u * (unsigned)(kbuf - 4);
+            bool direct = kbuf < 8;                       // warp-uniform
+            int cnt = 0;                                  // entries of this lane (direct mode)
+#define BW_R2(Q, IDX, SELF)                                                                    \
+                const float dx = Q.x - px, dy = Q.y - py, dz = Q.z - pz;              \
+                const float r2 = dx * dx + dy * dy + dz * dz;                         \
+                const float hi = FAST2 ? fmaf(Q.w, dhi, hi0)                          \
+                                       : (active ? hi_row[__float_as_int(Q.w)] : -1.f); \
+                const float t = r2 - hi;                                              \
+                const bool hit = SELF ? (t < 0.f && (IDX) != self) : t < 0.f;         \
+                nearbits = min(nearbits, SELF && (IDX) == self ? 0 : __float_as_int(t));
+#define BW_TEST_S(Q, IDX, SELF)   { BW_R2(Q, IDX, SELF) bw_append_s(hit, sptr, (IDX)); }
+#define BW_TEST_G(Q, IDX, SELF)   { BW_R2(Q, IDX, SELF) sc_append16(hit, row16, cnt, cap, (IDX)); }
+            // four records per round, the next four already on their way (reads run up to 4 records past the
+            // stretch: into the next run, or the slack behind the window)
+#define BW_STRETCH(TEST, SELF, GUARD)                                                 \
+            {                                                                         \
+                if (k + 4 <= end) {                                                   \
+                    float4 q0 = cand[k], q1 = cand[k + 1], q2 = cand[k + 2], q3 = cand[k + 3]; \
+                    _Pragma("unroll 1")                                               \
+                    for (; k + 4 <= end; k += 4) {                                    \
+                        GUARD                                                         \
+                        const float4 n0 = cand[k + 4], n1 = cand[k + 5], n2 = cand[k + 6], n3 = cand[k + 7]; \
+                        TEST(q0, k, SELF) TEST(q1, k + 1, SELF) TEST(q2, k + 2, SELF) TEST(q3, k + 3, SELF) \
+                        q0 = n0; q1 = n1; q2 = n2; q3 = n3;                           \
+                    }                                                                 \
+                }                                                                     \
+            }
+#define BW_TAIL(TEST, SELF)                                                           \
+                _Pragma("unroll 1")                                                   \
+                for (; k < end; k++) {                                                \
+                    const float4 q = cand[k];                                         \
+                    TEST(q, k, SELF)                                                  \
+                }
+#define BW_FULL   if (__any_sync(0xffffffffu, sptr > sfull)) break;
+#pragma unroll 1
+            for (int s9 = 0; s9 < 9; s9++) {
+                const int r0 = ((rz - 1 + s9 / 3) * 4 + (ry - 1 + s9 % 3)) * 4 + rx - 1;
+                const int end = sP[r0 + 3];
+                int k = sP[r0];
+                if (!direct) {
+                    if (s9 == 4) BW_STRETCH(BW_TEST_S, true, BW_FULL)        // the stretch that holds the block itself
+                    else BW_STRETCH(BW_TEST_S, false, BW_FULL)
+                    if (k + 4 > end && !__any_sync(0xffffffffu, sptr > sfull)) {      // the last (up to) three
+                        if (s9 == 4) BW_TAIL(BW_TEST_S, true)
+                        else BW_TAIL(BW_TEST_S, false)
+                    } else {
+                        // some lane is within four entries of the buffer's end: rows out, and on in the list
+                        cnt = (int)(sptr - sptr0) >> 6;
+                        bw_flush(sbuf0, lane, valid, cnt, row16);
+                        direct = true;
+                    }
+                }
+                if (direct) {
+                    if (s9 == 4) { BW_STRETCH(BW_TEST_G, true, ) BW_TAIL(BW_TEST_G, true) }
+                    else { BW_STRETCH(BW_TEST_G, false, ) BW_TAIL(BW_TEST_G, false) }
+                }
+            }
+#undef BW_FULL
+#undef BW_TAIL
+#undef BW_STRETCH
+#undef BW_TEST_G
+#undef BW_TEST_S
+#undef BW_R2
+            if (!direct) {
+                cnt = (int)(sptr - sptr0) >> 6;
+                bw_flush(sbuf0, lane, valid, cnt, row16);
+            }
+            if (nearbits < 0 && __int_as_float(nearbits) > -bandw) {
+                // Some listed pair may sit inside the band around its threshold: settle those with the
+                // canonical predicate and close the gaps (about one particle in a thousand).  The row is read
+                // back eight entries at a time: the loads of a batch are in flight together.
+                const int lim = min(cnt, cap);
+                int kept = 0;
+                for (int k0 = 0; k0 < lim; k0 += 8) {
+                    int nm[8];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) nm[u] = k0 + u < lim ? (int)row16[(size_t)(k0 + u) * 32] : 0;
+#pragma unroll
+                    for (int u = 0; u < 8; u++) {
+                        if (k0 + u >= lim) break;
+                        const float4 q = cand[nm[u]];
+                        const int tj = FAST2 ? (int)q.w : __float_as_int(q.w);
+                        const float dx = q.x - px, dy = q.y - py, dz = q.z - pz;
+                        bool keep = true;
+                        if (dx * dx + dy * dy + dz * dz > lo_row[tj])
+                            keep = r2_canon(pi, pos[win_slot_of(sP, sS, nm[u])], box) < s_rl2[ti * nsp + tj];
+                        if (keep) {
+                            row16[(size_t)kept * 32] = (unsigned short)nm[u];     // kept <= k0 + u: behind the reads
+                            kept++;
+                        }
+                    }
+                }
+                if (cnt <= cap) cnt = kept;
+            }
+            if (valid) {
+                nnb[slot] = min(cnt, cap);
+                if (cnt > cap) ctl->overflow = 1u;
+            }
+            int mx = valid ? cnt : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            if (lane == 0) atomicMax(&ctl->max_count, (unsigned)mx);
+        }
+    }
+}
+
 // reciprocal of the step kernels in fp32: the hardware approximation alone (1 ulp; the forces of a step are never
 // reported, and the neighbour's coordinates carry a comparable rounding already).  fp64 keeps the full sequence.
 template <bool FAST> __device__ __forceinline__ float win_rcp(float x)
