@@ -424,7 +424,7 @@ template <typename R> struct Impl {
     // of list rows (64 bytes each).  Up to 128 rows, as many as leave room for two blocks per SM.
     static int build_rows(const b2_ctx *c)
     {
-        const size_t window = (size_t)c->grid.wcap * sizeof(P4) + 64, fixed = 4096;
+        const size_t window = (size_t)c->grid.wcap * sizeof(P4) + 128, fixed = 4096;
         const size_t half = (c->smem_sm > 1024 * BW_BLOCKS ? c->smem_sm - 1024 * BW_BLOCKS : 0) / BW_BLOCKS;
         size_t room = half > window + fixed ? half - window - fixed : 0;
         if (room < 8 * 64 * (WIN_THREADS / 32) && c->smem_optin > window + fixed)          // one block per SM then
@@ -433,7 +433,7 @@ template <typename R> struct Impl {
     }
     static size_t build_smem(const b2_ctx *c)
     {
-        return (size_t)c->grid.wcap * sizeof(P4) + 64 + (size_t)build_rows(c) * 64 * (WIN_THREADS / 32);
+        return (size_t)c->grid.wcap * sizeof(P4) + 128 + (size_t)build_rows(c) * 64 * (WIN_THREADS / 32);
     }
 
     // ints the list needs for `cap` slots per particle

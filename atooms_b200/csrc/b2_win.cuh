@@ -399,29 +399,85 @@ __device__ __forceinline__ float4 bw_record(const reld4 &q)
     const int t = (int)q.t & 0xff;
     return make_float4((float)q.x, (float)q.y, (float)q.z, FAST2 ? (float)t : __int_as_float(t));
 }
+// Records are kept in PAIRS, transposed: records 2p and 2p + 1 are the two float4
+//   (x0, x1, y0, y1)  (z0, z1, w0, w1)
+// so that a 128-bit read yields two register pairs the packed fp32 instructions of sm_100 take as they are
+// (add / mul / fma.f32x2: one issue slot for two candidates).
+struct __align__(16) BwPair { float4 xy, zw; };
+__device__ __forceinline__ BwPair bw_pair(const float4 &a, const float4 &b)
+{
+    BwPair p;
+    p.xy = make_float4(a.x, b.x, a.y, b.y);
+    p.zw = make_float4(a.z, b.z, a.w, b.w);
+    return p;
+}
+#define BW_NOBODY make_float4(1e18f, 0.f, 0.f, 0.f)      // never within reach of anyone
 template <bool FAST2>
 __device__ __forceinline__ void bw_convert(unsigned char *raw, int W, const WinOrigin<float> &org, const Box<float> &box)
 {
+    // a thread takes both records of a pair: they occupy the 32 bytes the pair is written to
     const int4 *win = reinterpret_cast<const int4 *>(raw);
-    float4 *cand = reinterpret_cast<float4 *>(raw);
-    for (int k = threadIdx.x; k < W; k += WIN_THREADS) cand[k] = bw_record<FAST2>(to_rel(win[k], org, box));   // same address, same thread
+    BwPair *cand = reinterpret_cast<BwPair *>(raw);
+    for (int p = threadIdx.x; 2 * p < W; p += WIN_THREADS) {
+        const float4 a = bw_record<FAST2>(to_rel(win[2 * p], org, box));
+        const float4 b = 2 * p + 1 < W ? bw_record<FAST2>(to_rel(win[2 * p + 1], org, box)) : BW_NOBODY;
+        cand[p] = bw_pair(a, b);
+    }
     __syncthreads();
 }
 template <bool FAST2>
 __device__ __forceinline__ void bw_convert(unsigned char *raw, int W, const WinOrigin<double> &org, const Box<double> &box)
 {
-    // 32-byte records become 16-byte ones at the front of the same buffer: a round of WIN_THREADS records is
+    // 64 bytes of records become a 32-byte pair at the front of the same buffer: a round of WIN_THREADS pairs is
     // read, then written behind a barrier; what a round writes lies below everything later rounds read
     const double4 *win = reinterpret_cast<const double4 *>(raw);
-    float4 *cand = reinterpret_cast<float4 *>(raw);
-    for (int base = 0; base < W; base += WIN_THREADS) {
-        const int k = base + threadIdx.x;
-        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (k < W) q = bw_record<FAST2>(to_rel(win[k], org, box));
+    BwPair *cand = reinterpret_cast<BwPair *>(raw);
+    for (int base = 0; 2 * base < W; base += WIN_THREADS) {
+        const int p = base + threadIdx.x;
+        float4 a = BW_NOBODY, b = BW_NOBODY;
+        if (2 * p < W) a = bw_record<FAST2>(to_rel(win[2 * p], org, box));
+        if (2 * p + 1 < W) b = bw_record<FAST2>(to_rel(win[2 * p + 1], org, box));
         __syncthreads();
-        if (k < W) cand[k] = q;
+        if (2 * p < W) cand[p] = bw_pair(a, b);
     }
     __syncthreads();
+}
+// record k of the paired layout
+__device__ __forceinline__ float4 bw_single(const unsigned char *raw, int k)
+{
+    const float *f = reinterpret_cast<const float *>(raw) + (size_t)(k >> 1) * 8 + (k & 1);
+    return make_float4(f[0], f[2], f[4], f[6]);
+}
+
+// packed fp32 (sm_100): two lanes of a 64-bit register pair per instruction
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 x2_pack(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void x2_unpack(f32x2 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 x2_add(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 x2_mul(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 x2_fma(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
 }
 
 // entry `off` of a lane into the warp's row buffer (shared-memory address sptr), predicated like sc_append16
@@ -489,9 +545,9 @@ k_build_list_win(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0, cons
     win_origin_load(T, org);
     win_wait(&s_bar);
     bw_convert<FAST2>(win_raw, W, org, box);          // ends with a barrier: layout and thresholds are visible too
-    const float4 *__restrict__ cand = reinterpret_cast<const float4 *>(win_raw);
+    const ulonglong2 *cand2 = reinterpret_cast<const ulonglong2 *>(win_raw);      // record pair p: entries 2p, 2p + 1
     const int nsp = g_pair.nsp;
-    const unsigned sbuf0 = smem_u32(win_raw) + (unsigned)g.wcap * (unsigned)sizeof(P4) + 64u + (unsigned)(warp * kbuf) * 64u;
+    const unsigned sbuf0 = smem_u32(win_raw) + (unsigned)g.wcap * (unsigned)sizeof(P4) + 128u + (unsigned)(warp * kbuf) * 64u;
     for (int b = warp; b < 8; b += WIN_THREADS / 32) {
         const int ox = b & 1, oy = (b >> 1) & 1, oz = b >> 2;
         // the last super-block of an axis may be two cells wide
@@ -507,11 +563,13 @@ k_build_list_win(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0, cons
             const P4 pi = pos[slot];
             const bool active = valid && !is_ghost(pi);   // ghosts act as neighbours but own no row
             const int ti = ptype(pi);
-            const float4 me = cand[self];
+            const float4 me = bw_single(win_raw, self);
             const float px = me.x, py = me.y, pz = me.z;
             const float *hi_row = s_hi + ti * nsp, *lo_row = s_lo + ti * nsp;
             const float hi0 = active ? hi_row[0] : -1.f;
             const float dhi = active ? hi_row[nsp > 1 ? 1 : 0] - hi_row[0] : 0.f;
+            const f32x2 npx = x2_pack(-px, -px), npy = x2_pack(-py, -py), npz = x2_pack(-pz, -pz);
+            const f32x2 nhi0 = x2_pack(-hi0, -hi0), ndhi = x2_pack(-dhi, -dhi);
             float bandw = 0.f;                            // widest band of this particle's row of the pair table
             for (int tj = 0; tj < nsp; tj++) bandw = fmaxf(bandw, hi_row[tj] - lo_row[tj]);
             if (!active) bandw = -1.f;                    // (its thresholds are negative: t > 0 always)
@@ -531,67 +589,111 @@ k_build_list_win(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0, cons
             const unsigned sfull = sptr0 + 64u * (unsigned)(kbuf - 4);
             bool direct = kbuf < 8;                       // warp-uniform
             int cnt = 0;                                  // entries of this lane (direct mode)
-#define BW_R2(Q, IDX, SELF)                                                                    \
-                const float dx = Q.x - px, dy = Q.y - py, dz = Q.z - pz;              \
-                const float r2 = dx * dx + dy * dy + dz * dz;                         \
-                const float hi = FAST2 ? fmaf(Q.w, dhi, hi0)                          \
-                                       : (active ? hi_row[__float_as_int(Q.w)] : -1.f); \
-                const float t = r2 - hi;                                              \
-                const bool hit = SELF ? (t < 0.f && (IDX) != self) : t < 0.f;         \
-                nearbits = min(nearbits, SELF && (IDX) == self ? 0 : __float_as_int(t));
-#define BW_TEST_S(Q, IDX, SELF)   { BW_R2(Q, IDX, SELF) bw_append_s(hit, sptr, (IDX)); }
-#define BW_TEST_G(Q, IDX, SELF)   { BW_R2(Q, IDX, SELF) sc_append16(hit, row16, cnt, cap, (IDX)); }
-            // four records per round, the next four already on their way (reads run up to 4 records past the
-            // stretch: into the next run, or the slack behind the window)
-#define BW_STRETCH(TEST, SELF, GUARD)                                                 \
+#define BW_HIT(T, IDX, SELF)                                                          \
+                const bool hit = SELF ? (T < 0.f && (IDX) != self) : T < 0.f;         \
+                nearbits = min(nearbits, SELF && (IDX) == self ? 0 : __float_as_int(T));
+#define BW_APPEND_S(IDX)   bw_append_s(hit, sptr, (IDX));
+#define BW_APPEND_G(IDX)   sc_append16(hit, row16, cnt, cap, (IDX));
+            // one record (the odd ends of a stretch)
+#define BW_ONE(APPEND, K, SELF)                                                       \
             {                                                                         \
-                if (k + 4 <= end) {                                                   \
-                    float4 q0 = cand[k], q1 = cand[k + 1], q2 = cand[k + 2], q3 = cand[k + 3]; \
+                const float4 q = bw_single(win_raw, (K));                             \
+                const float dx = q.x - px, dy = q.y - py, dz = q.z - pz;              \
+                const float hi = FAST2 ? fmaf(q.w, dhi, hi0)                          \
+                                       : (active ? hi_row[__float_as_int(q.w)] : -1.f); \
+                const float t = dx * dx + dy * dy + dz * dz - hi;                     \
+                BW_HIT(t, (K), SELF) APPEND((K))                                      \
+            }
+            // the two records of a pair: (xy, zw) as they come from shared memory
+#define BW_TWO(APPEND, XY, ZW, K, SELF)                                               \
+            {                                                                         \
+                const f32x2 dx = x2_add(XY.x, npx), dy = x2_add(XY.y, npy), dz = x2_add(ZW.x, npz); \
+                const f32x2 r2 = x2_fma(dz, dz, x2_fma(dy, dy, x2_mul(dx, dx)));      \
+                float ta, tb;                                                         \
+                if (FAST2) {                                                          \
+                    x2_unpack(x2_fma(ZW.y, ndhi, x2_add(r2, nhi0)), ta, tb);          \
+                } else {                                                              \
+                    float wa, wb;                                                     \
+                    x2_unpack(r2, ta, tb);                                            \
+                    x2_unpack(ZW.y, wa, wb);                                          \
+                    ta -= active ? hi_row[__float_as_int(wa)] : -1.f;                 \
+                    tb -= active ? hi_row[__float_as_int(wb)] : -1.f;                 \
+                }                                                                     \
+                { BW_HIT(ta, (K), SELF) APPEND((K)) }                                 \
+                { BW_HIT(tb, (K) + 1, SELF) APPEND((K) + 1) }                         \
+            }
+            // two pairs per round, the next two already on their way (reads run up to two pairs past the
+            // stretch: into the next run, or the slack behind the window); k is even here.  ROUNDS: how many rounds
+            // may run before the buffer has to be looked at again (a round appends at most four entries per lane).
+#define BW_STRETCH(APPEND, SELF, ROUNDS)                                              \
+            {                                                                         \
+                while (k + 4 <= end) {                                                \
+                    int rounds = (end - k) >> 2;                                      \
+                    ROUNDS                                                            \
+                    const ulonglong2 *pp = cand2 + k;                                 \
+                    ulonglong2 a0 = pp[0], a1 = pp[1], b0_ = pp[2], b1_ = pp[3];      \
+                    k += 4 * rounds;                                                  \
+                    int kk = k - 4 * rounds;                                          \
                     _Pragma("unroll 1")                                               \
-                    for (; k + 4 <= end; k += 4) {                                    \
-                        GUARD                                                         \
-                        const float4 n0 = cand[k + 4], n1 = cand[k + 5], n2 = cand[k + 6], n3 = cand[k + 7]; \
-                        TEST(q0, k, SELF) TEST(q1, k + 1, SELF) TEST(q2, k + 2, SELF) TEST(q3, k + 3, SELF) \
-                        q0 = n0; q1 = n1; q2 = n2; q3 = n3;                           \
+                    for (; kk < k; kk += 4) {                                         \
+                        pp += 4;                                                      \
+                        const ulonglong2 n0 = pp[0], n1 = pp[1], n2 = pp[2], n3 = pp[3]; \
+                        BW_TWO(APPEND, a0, a1, kk, SELF) BW_TWO(APPEND, b0_, b1_, kk + 2, SELF) \
+                        a0 = n0; a1 = n1; b0_ = n2; b1_ = n3;                         \
                     }                                                                 \
                 }                                                                     \
             }
-#define BW_TAIL(TEST, SELF)                                                           \
+#define BW_TAIL(APPEND, SELF)                                                         \
                 _Pragma("unroll 1")                                                   \
-                for (; k < end; k++) {                                                \
-                    const float4 q = cand[k];                                         \
-                    TEST(q, k, SELF)                                                  \
+                for (; k < end; k++) BW_ONE(APPEND, k, SELF)
+            // rounds the fullest lane's buffer still takes: (rows left - 4) / 4 + 1, none once it is within four of the end
+#define BW_ROOM   (sptr > sfull ? 0u : ((sfull - sptr) >> 8) + 1u)
+#define BW_FULL   { const int room = (int)__reduce_min_sync(0xffffffffu, BW_ROOM); if (room == 0) break; rounds = min(rounds, room); }
+#define BW_WALK(APPEND, SELF, GUARD)                                                  \
+                {                                                                     \
+                    if ((k & 1) && k < end) {                                         \
+                        BW_ONE(APPEND, k, SELF)                                       \
+                        k++;                                                          \
+                    }                                                                 \
+                    BW_STRETCH(APPEND, SELF, GUARD)                                   \
                 }
-#define BW_FULL   if (__any_sync(0xffffffffu, sptr > sfull)) break;
 #pragma unroll 1
             for (int s9 = 0; s9 < 9; s9++) {
                 const int r0 = ((rz - 1 + s9 / 3) * 4 + (ry - 1 + s9 % 3)) * 4 + rx - 1;
                 const int end = sP[r0 + 3];
                 int k = sP[r0];
                 if (!direct) {
-                    if (s9 == 4) BW_STRETCH(BW_TEST_S, true, BW_FULL)        // the stretch that holds the block itself
-                    else BW_STRETCH(BW_TEST_S, false, BW_FULL)
-                    if (k + 4 > end && !__any_sync(0xffffffffu, sptr > sfull)) {      // the last (up to) three
-                        if (s9 == 4) BW_TAIL(BW_TEST_S, true)
-                        else BW_TAIL(BW_TEST_S, false)
+                    // (a lane at most four entries short of the buffer's end stops the buffered walk: the checks
+                    // come before the odd record at the front, before every round of four and before the last three)
+                    if (!__any_sync(0xffffffffu, sptr > sfull)) {
+                        if (s9 == 4) BW_WALK(BW_APPEND_S, true, BW_FULL)     // the stretch that holds the block itself
+                        else BW_WALK(BW_APPEND_S, false, BW_FULL)
+                    }
+                    if (k + 4 > end && !__any_sync(0xffffffffu, sptr > sfull)) {
+                        if (s9 == 4) BW_TAIL(BW_APPEND_S, true)
+                        else BW_TAIL(BW_APPEND_S, false)
                     } else {
-                        // some lane is within four entries of the buffer's end: rows out, and on in the list
+                        // rows out, and on in the list itself
                         cnt = (int)(sptr - sptr0) >> 6;
                         bw_flush(sbuf0, lane, valid, cnt, row16);
                         direct = true;
                     }
                 }
                 if (direct) {
-                    if (s9 == 4) { BW_STRETCH(BW_TEST_G, true, ) BW_TAIL(BW_TEST_G, true) }
-                    else { BW_STRETCH(BW_TEST_G, false, ) BW_TAIL(BW_TEST_G, false) }
+                    if (s9 == 4) { BW_WALK(BW_APPEND_G, true, ) BW_TAIL(BW_APPEND_G, true) }
+                    else { BW_WALK(BW_APPEND_G, false, ) BW_TAIL(BW_APPEND_G, false) }
                 }
             }
+#undef BW_WALK
 #undef BW_FULL
+#undef BW_ROOM
 #undef BW_TAIL
 #undef BW_STRETCH
-#undef BW_TEST_G
-#undef BW_TEST_S
-#undef BW_R2
+#undef BW_TWO
+#undef BW_ONE
+#undef BW_APPEND_G
+#undef BW_APPEND_S
+#undef BW_HIT
             if (!direct) {
                 cnt = (int)(sptr - sptr0) >> 6;
                 bw_flush(sbuf0, lane, valid, cnt, row16);
@@ -609,7 +711,7 @@ k_build_list_win(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0, cons
 #pragma unroll
                     for (int u = 0; u < 8; u++) {
                         if (k0 + u >= lim) break;
-                        const float4 q = cand[nm[u]];
+                        const float4 q = bw_single(win_raw, nm[u]);
                         const int tj = FAST2 ? (int)q.w : __float_as_int(q.w);
                         const float dx = q.x - px, dy = q.y - py, dz = q.z - pz;
                         bool keep = true;
