@@ -240,7 +240,8 @@ struct Ctl {
     long long iter;
     // thermostat (b2_run_nvt): v' = th_a v + th_b dt F/m, coefficients renewed every step by the
     // last block from the kinetic energy of the half-step velocities just written
-    int th_kind, th_pad_;        // 0 Berendsen, 1 Nose-Hoover (leap-frog form)
+    int th_kind;                 // 0 Berendsen, 1 Nose-Hoover (leap-frog form)
+    unsigned int region_miss;    // windowed list: a particle lies outside the launched super-blocks (Grid::sb0, sbn)
     double th_T0, th_tau, th_dt, th_xi, th_a, th_b, th_ndof, th_T;
     double red[32];              // reduction results
 };
@@ -272,6 +273,8 @@ struct Grid {
     // windowed list (b2_win.cuh): an even number of cells per axis, in super-blocks of 4x4x4 cells
     int win;           // 1: list entries are 16-bit offsets into the super-block's candidate window
     int nsb[3];        // super-blocks per axis (ceil(nc / 4), nc even)
+    int sb0[3], sbn[3]; // the super-blocks that are launched and tabulated: sbn[d] of them from sb0[d] on, periodically
+                       // (all of them, unless the particles are known to fill only a slab of the box)
     int wcap;          // records a window may hold, the dummy included (shared memory of the step kernel)
 };
 

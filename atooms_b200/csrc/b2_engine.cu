@@ -89,6 +89,9 @@ struct b2_ctx {
     int *b8start = nullptr, *tile_base = nullptr, *sbt = nullptr;
     int nb8codes = 0, nsb_total = 0, win_tab_alloc = 0, win_sb_alloc = 0;
     bool win_off = false;            // windows do not fit: this context keeps the global-index list
+    // the particles fill only the fractions lo <= u < hi (+ wrap) of the box along x: a slab of a decomposed system (b2_peer_refresh)
+    bool region_on = false, region_off = false;
+    double region_lo = 0, region_hi = 0, win_fill = 1.0;
     size_t smem_optin = 0, smem_sm = 0;      // shared memory a block may opt into, and of an SM
     // control / reductions / staging
     Ctl *ctl = nullptr, *hctl = nullptr;
@@ -352,20 +355,46 @@ template <typename R> struct Impl {
             g.nc[0] >= 8 && g.nc[1] >= 8 && g.nc[2] >= 8) {
             double cellvol = 1.0;
             for (int d = 0; d < 3; d++) cellvol *= c->side[d] / (g.nc[d] & ~1);
+            // super-blocks to launch along x when the particles are known to fill a slab only
+            static const bool gathered = getenv("B2_BUILD_GATHERED") && atoi(getenv("B2_BUILD_GATHERED")) != 0;
+            const int nsbx = ((g.nc[0] & ~1) + 3) / 4;
+            int sb_first = 0, sb_count = nsbx;
+            // B2_REGION_X="lo,hi": the same for a single context (timing experiments with a slab-shaped system)
+            if (!c->region_on && getenv("B2_REGION_X") && sscanf(getenv("B2_REGION_X"), "%lf,%lf", &c->region_lo, &c->region_hi) == 2) {
+                c->region_lo = (c->region_lo - c->center[0]) / c->side[0] + 0.5;
+                c->region_hi = (c->region_hi - c->center[0]) / c->side[0] + 0.5;
+                c->region_on = true;
+            }
+            if (c->region_on && !c->region_off && !gathered) {
+                // region_lo / hi: fractions of the box along x from its lower face (may run past 0 or 1)
+                const int ncx = g.nc[0] & ~1;
+                const int c_lo = (int)floor(c->region_lo * ncx), c_hi = (int)floor(c->region_hi * ncx);
+                const int s_lo = (int)floor(c_lo / 4.0) - 1, s_hi = (int)floor(c_hi / 4.0) + 1;     // + one super-block either side
+                if (s_hi - s_lo + 1 < nsbx) {
+                    sb_count = s_hi - s_lo + 1;
+                    sb_first = ((s_lo % nsbx) + nsbx) % nsbx;
+                }
+            }
+            c->win_fill = (double)sb_count / nsbx;
+            cellvol /= c->win_fill;            // the density inside the launched part
             // records of a window (8^3 cells) at the mean density, with room for fluctuations; a slab of a
             // decomposed system is denser than its global mean: the first build reports what it needs
             const double expect = (double)c->n / (c->side[0] * c->side[1] * c->side[2]) * 512.0 * cellvol;
             int wcap = std::max(g.wcap, ((int)(1.25 * expect) + 128 + 7) / 8 * 8);
             const size_t rec = c->precision == B2_FP32 ? 16 : 32;
             const size_t lim = std::min<size_t>((c->smem_optin > 4096 ? c->smem_optin - 4096 : 0) / rec, 65528);
-            const size_t nsbt = (size_t)((g.nc[0] + 3) / 4) * ((g.nc[1] + 3) / 4) * ((g.nc[2] + 3) / 4);
+            const size_t nsbt = (size_t)sb_count * ((g.nc[1] + 3) / 4) * ((g.nc[2] + 3) / 4);
             if ((size_t)wcap <= lim && nsbt <= (size_t)c->ncap / 8 + 64) {
                 g.win = 1;
                 g.wcap = wcap;
                 for (int d = 0; d < 3; d++) {
                     g.nc[d] &= ~1;
                     g.nsb[d] = (g.nc[d] + 3) / 4;
+                    g.sb0[d] = 0;
+                    g.sbn[d] = g.nsb[d];
                 }
+                g.sb0[0] = sb_first;
+                g.sbn[0] = sb_count;
                 mx = 1;
                 for (int d = 0; d < 3; d++) {
                     mx = std::max(mx, g.nc[d]);
@@ -387,7 +416,7 @@ template <typename R> struct Impl {
         if (g.win) {
             int rc;
             c->nb8codes = tab >> 3;
-            c->nsb_total = g.nsb[0] * g.nsb[1] * g.nsb[2];
+            c->nsb_total = g.sbn[0] * g.sbn[1] * g.sbn[2];
             if (c->nb8codes + 2 > c->win_tab_alloc) {
                 if ((rc = dev_alloc(c, &c->b8start, (size_t)c->nb8codes + 2))) return rc;
                 c->win_tab_alloc = c->nb8codes + 2;
@@ -399,6 +428,11 @@ template <typename R> struct Impl {
             }
             if ((rc = win_attributes(c))) return rc;
         }
+        static const bool debug_grid = getenv("B2_DEBUG_GRID") && atoi(getenv("B2_DEBUG_GRID")) != 0;
+        if (debug_grid)
+            fprintf(stderr, "[b2 grid] rank %d n %lld cells %d %d %d m %d win %d super-blocks %d %d %d launched %d+%d wcap %d cap %d region %d (%g, %g) off %d\n",
+                    c->myrank, (long long)c->n, g.nc[0], g.nc[1], g.nc[2], g.m, g.win, g.nsb[0], g.nsb[1], g.nsb[2], g.sb0[0], g.sbn[0],
+                    g.wcap, c->cap, (int)c->region_on, c->region_lo, c->region_hi, (int)c->region_off);
         return B2_OK;
     }
 
@@ -449,6 +483,12 @@ template <typename R> struct Impl {
     {
         int rc;
         Grid &g = c->grid;
+        if (g.win && c->hctl->region_miss) {
+            // a particle outside the slab the caller announced: launch every super-block from now on
+            c->region_off = true;
+            if ((rc = setup_grid(c))) return rc;
+            return ensure_capacity(c, std::max(c->cap, 8));
+        }
         if (g.win && ((int)c->hctl->win_max > g.wcap || c->hctl->win_max >= 65535u)) {
             const size_t rec = sizeof(P4);
             const size_t lim = std::min<size_t>((c->smem_optin > 4096 ? c->smem_optin - 4096 : 0) / rec, 65528);
@@ -458,7 +498,7 @@ template <typename R> struct Impl {
             const bool force_win = getenv("B2_LIST_WINDOWED") && atoi(getenv("B2_LIST_WINDOWED")) != 0;
             const double expect = (double)c->n / (c->side[0] * c->side[1] * c->side[2]) * 512.0 *
                                   (c->side[0] / g.nc[0]) * (c->side[1] / g.nc[1]) * (c->side[2] / g.nc[2]);
-            const bool sparse = (double)c->hctl->win_max > 1.6 * expect + 256.0 && !force_win;
+            const bool sparse = (double)c->hctl->win_max > 1.6 * expect / c->win_fill + 256.0 && !force_win;
             if (want > lim || sparse) {
                 c->win_off = true;
                 c->cap = 0;
@@ -618,7 +658,7 @@ template <typename R> struct Impl {
         LAUNCH(kern, cdiv(c->n, FORCE_THREADS), FORCE_THREADS, a);
     }
 
-    static dim3 win_grid(const b2_ctx *c) { return dim3(c->grid.nsb[0], c->grid.nsb[1], c->grid.nsb[2]); }
+    static dim3 win_grid(const b2_ctx *c) { return dim3(c->grid.sbn[0], c->grid.sbn[1], c->grid.sbn[2]); }
 
     static WinArgs<R> win_args(const b2_ctx *c)
     {
@@ -2826,6 +2866,15 @@ template <typename R> struct ImplDdr {
         c->list_dirty = true;
         c->forces_valid = c->ev_valid = false;
         c->min_resume = false;
+        // owned particles lie in [lo, hi), ghosts within `margin` of it: the windowed list launches that slab only
+        if (!c->region_on && W > 1) {
+            c->region_on = true;
+            c->win_off = false;          // (the first, host-driven upload had to assume the whole box)
+            c->cap = 0;
+        }
+        c->region_lo = lo - margin;
+        c->region_hi = hi + margin;
+        c->region_off = false;
         if (c->mvel) { cudaFree(c->mvel); c->mvel = nullptr; }
         memset(c->hctl, 0, sizeof(Ctl));
         c->hctl->halt_rebuild = 1u;

@@ -14,7 +14,7 @@
 
 // ---- keys -----------------------------------------------------------------
 template <typename R>
-__global__ void k_cell_keys(const Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
+__global__ void k_cell_keys(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
                             const typename Pos4<R>::type *pos1, int n, Box<R> box, Grid g,
                             uint32_t *__restrict__ keys, uint32_t *__restrict__ vals)
 {
@@ -27,6 +27,15 @@ __global__ void k_cell_keys(const Ctl *__restrict__ ctl, const typename Pos4<R>:
     cell_of(box, g, p, cx, cy, cz);
     keys[i] = morton3(cx, cy, cz);
     vals[i] = (uint32_t)i;
+    if (g.win) {
+        // a particle outside the launched super-blocks would have no row: the host then launches them all
+        int lx = (cx >> 2) - g.sb0[0], ly = (cy >> 2) - g.sb0[1], lz = (cz >> 2) - g.sb0[2];
+        lx += lx < 0 ? g.nsb[0] : 0; ly += ly < 0 ? g.nsb[1] : 0; lz += lz < 0 ? g.nsb[2] : 0;
+        if (lx >= g.sbn[0] || ly >= g.sbn[1] || lz >= g.sbn[2]) {
+            ctl->region_miss = 1u;
+            ctl->overflow = 1u;
+        }
+    }
 }
 
 // ---- radix sort, one 8-bit digit per pass -----------------------------------
@@ -727,6 +736,7 @@ __global__ void k_rebuild_begin(Ctl *ctl)
     ctl->max_count = 0u;
     ctl->win_max = 0u;
     ctl->overflow = 0u;
+    ctl->region_miss = 0u;
 }
 
 __global__ void k_rebuild_finish(Ctl *ctl)

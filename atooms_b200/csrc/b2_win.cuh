@@ -127,11 +127,16 @@ __global__ void k_b8_bounds(const Ctl *__restrict__ ctl, const uint32_t *__restr
     b8start[b] = lo;
 }
 
+// super-block of table row gi (= linear block index of the windowed kernels: x fastest over the launched
+// sbn[0] x sbn[1] x sbn[2] super-blocks, which start at sb0 and wrap around the box)
 __device__ __forceinline__ void sb_coords(const Grid &g, int gi, int &sx, int &sy, int &sz)
 {
-    sx = gi % g.nsb[0];
-    sy = (gi / g.nsb[0]) % g.nsb[1];
-    sz = gi / (g.nsb[0] * g.nsb[1]);
+    sx = g.sb0[0] + gi % g.sbn[0];
+    sy = g.sb0[1] + (gi / g.sbn[0]) % g.sbn[1];
+    sz = g.sb0[2] + gi / (g.sbn[0] * g.sbn[1]);
+    sx -= sx >= g.nsb[0] ? g.nsb[0] : 0;
+    sy -= sy >= g.nsb[1] ? g.nsb[1] : 0;
+    sz -= sz >= g.nsb[2] ? g.nsb[2] : 0;
 }
 
 // tile_base[gi] = tiles of 32 lanes before super-block gi (geometric index, x fastest)
@@ -141,7 +146,7 @@ k_sb_tiles(const Ctl *__restrict__ ctl, Grid g, const int *__restrict__ b8start,
     if (!ctl->halt_rebuild) return;
     __shared__ int s_w[32];
     __shared__ int s_run;
-    const int nsb = g.nsb[0] * g.nsb[1] * g.nsb[2];
+    const int nsb = g.sbn[0] * g.sbn[1] * g.sbn[2];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_run = 0;
     __syncthreads();
@@ -329,7 +334,7 @@ k_sb_table(const Ctl *__restrict__ ctl, Grid g, Box<R> box, const int *__restric
     if (!ctl->halt_rebuild) return;
     const int lane = threadIdx.x & 31;
     const int gi = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (gi >= g.nsb[0] * g.nsb[1] * g.nsb[2]) return;
+    if (gi >= g.sbn[0] * g.sbn[1] * g.sbn[2]) return;
     int sx, sy, sz;
     sb_coords(g, gi, sx, sy, sz);
     int p0, st0, ln0, p1, st1, ln1;
@@ -547,12 +552,13 @@ k_build_list_win(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0, cons
     bw_convert<FAST2>(win_raw, W, org, box);          // ends with a barrier: layout and thresholds are visible too
     const ulonglong2 *cand2 = reinterpret_cast<const ulonglong2 *>(win_raw);      // record pair p: entries 2p, 2p + 1
     const int nsp = g_pair.nsp;
+    int sbx, sby, sbz;
+    sb_coords(g, gi, sbx, sby, sbz);
     const unsigned sbuf0 = smem_u32(win_raw) + (unsigned)g.wcap * (unsigned)sizeof(P4) + 128u + (unsigned)(warp * kbuf) * 64u;
     for (int b = warp; b < 8; b += WIN_THREADS / 32) {
         const int ox = b & 1, oy = (b >> 1) & 1, oz = b >> 2;
         // the last super-block of an axis may be two cells wide
-        if (4 * (int)blockIdx.x + 2 * ox >= g.nc[0] || 4 * (int)blockIdx.y + 2 * oy >= g.nc[1] || 4 * (int)blockIdx.z + 2 * oz >= g.nc[2])
-            continue;
+        if (4 * sbx + 2 * ox >= g.nc[0] || 4 * sby + 2 * oy >= g.nc[1] || 4 * sbz + 2 * oz >= g.nc[2]) continue;
         const int rx = 1 + ox, ry = 1 + oy, rz = 1 + oz;
         const int r_own = (rz * 4 + ry) * 4 + rx;
         const int own0 = sP[r_own], n_own = sP[r_own + 1] - own0, slot0 = sS[r_own];
