@@ -265,7 +265,8 @@ __device__ __forceinline__ uint32_t morton3(int cx, int cy, int cz)
 
 struct Grid {
     int nc[3];
-    int cellbits;      // Morton bits per dimension; table has 1 << (3 cellbits) entries
+    int cellbits;      // Morton bits per dimension (what y and z need; x may have more, see grid_key)
+    int keybits;       // bits of a cell key; the cell table has 1 << keybits entries
     int allpairs;      // too few cells along some axis: O(N^2) list build
     int m;             // cells are (r_list,max / m) wide; the stencil reaches m cells (1 or 2)
     float w[3];        // cell widths
@@ -277,6 +278,22 @@ struct Grid {
                        // (all of them, unless the particles are known to fill only a slab of the box)
     int wcap;          // records a window may hold, the dummy included (shared memory of the step kernel)
 };
+
+// Key of cell (x, y, z) at `level` (0: cells, 1: blocks of 2x2x2 cells, 2: super-blocks of 4x4x4): the low
+// (cellbits - level) bits of the three coordinates interleaved, Morton order.  A box much longer along x than
+// along y and z (the box of a slab decomposition) has more cells along x than 2^cellbits: the extra high bits of
+// x go on top of the interleaved part, so the key space stays as small as the grid and blocks, super-blocks
+// and their runs of slots are what they are in a cube.
+__device__ __forceinline__ uint32_t grid_key(const Grid &g, int level, int x, int y, int z)
+{
+    const int b = g.cellbits - level;
+    return (((uint32_t)x >> b) << (3 * b)) | morton3(x & ((1 << b) - 1), y, z);
+}
+// the x part of a cell key alone (y and z contribute spread3(y) << 1 | spread3(z) << 2)
+__device__ __forceinline__ uint32_t grid_key_x(const Grid &g, int x)
+{
+    return (((uint32_t)x >> g.cellbits) << (3 * g.cellbits)) | spread3((uint32_t)x & ((1u << g.cellbits) - 1u));
+}
 
 __device__ __forceinline__ void cell_of(const Box<float> &, const Grid &g, const int4 &p, int &cx, int &cy, int &cz)
 {

@@ -329,7 +329,8 @@ template <typename R> struct Impl {
         for (int m = 2; m >= 1 && g.allpairs; m--) {
             bool ok = true;
             for (int d = 0; d < 3; d++) {
-                int nc = std::min((int)std::floor(c->side[d] / (rl / m)), 256);
+                // at most 256 cells along y and z; x may have up to 4096 (the long axis of a decomposed box: grid_key)
+                int nc = std::min((int)std::floor(c->side[d] / (rl / m)), d == 0 ? 4096 : 256);
                 if (nc < 2 * m + 1) ok = false;
                 g.nc[d] = nc;
             }
@@ -403,10 +404,14 @@ template <typename R> struct Impl {
             }
         }
         g.reach2 = (float)(rl * rl * (1.0 + 1e-3));
+        // Morton bits: what y and z need; further bits of x on top
         g.cellbits = 1;
-        while ((1 << g.cellbits) < mx) g.cellbits++;
-        int tab = 1 << (3 * g.cellbits);
-        c->sort_passes = (3 * g.cellbits + 7) / 8;
+        while ((1 << g.cellbits) < std::max(g.nc[1], g.nc[2])) g.cellbits++;
+        int xbits = 1;
+        while ((1 << xbits) < g.nc[0]) xbits++;
+        g.keybits = 3 * g.cellbits + std::max(0, xbits - g.cellbits);
+        int tab = 1 << g.keybits;
+        c->sort_passes = (g.keybits + 7) / 8;
         if (tab != c->ncelltab || !c->cell_start) {
             int rc;
             if ((rc = dev_alloc(c, &c->cell_start, tab))) return rc;
@@ -570,7 +575,7 @@ template <typename R> struct Impl {
         static const bool force_walk = getenv("B2_LIST_WALK") && atoi(getenv("B2_LIST_WALK")) != 0;
         const Grid &g = c->grid;
         if (g.m == 2 && !g.allpairs && g.nc[0] >= 7 && g.nc[1] >= 7 && g.nc[2] >= 7 && n < (1 << 28) && (!force_walk || g.win)) {
-            int codes = 1 << (3 * g.cellbits - 3);
+            int codes = 1 << (g.keybits - 3);
             static const bool gathered = getenv("B2_BUILD_GATHERED") && atoi(getenv("B2_BUILD_GATHERED")) != 0;   // A/B timing
             if (g.win && !gathered) {
                 auto kern = c->nsp <= 2 ? k_build_list_win<R, true> : k_build_list_win<R, false>;

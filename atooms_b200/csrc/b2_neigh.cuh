@@ -25,7 +25,7 @@ __global__ void k_cell_keys(Ctl *__restrict__ ctl, const typename Pos4<R>::type 
     typename Pos4<R>::type p = pos[i];
     int cx, cy, cz;
     cell_of(box, g, p, cx, cy, cz);
-    keys[i] = morton3(cx, cy, cz);
+    keys[i] = grid_key(g, 0, cx, cy, cz);
     vals[i] = (uint32_t)i;
     if (g.win) {
         // a particle outside the launched super-blocks would have no row: the host then launches them all
@@ -320,7 +320,7 @@ k_build_list(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
         float gx2[2 * M + 1];
 #pragma unroll
         for (int dx = -M; dx <= M; dx++) {
-            sx[dx + M] = spread3((uint32_t)wrap_cell(cx + dx, g.nc[0]));
+            sx[dx + M] = grid_key_x(g, wrap_cell(cx + dx, g.nc[0]));
             const float gx = cell_gap(dx, fx) * g.w[0];
             gx2[dx + M] = gx * gx;
         }
@@ -451,7 +451,10 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
                                          const int *__restrict__ sbt)
 {
     typedef typename Pos4<R>::type P4;
-    const int bx = 2 * (int)compact3(ms), by = 2 * (int)compact3(ms >> 1), bz = 2 * (int)compact3(ms >> 2);
+    // (block key -> block: the interleaved low bits, and the high bits of x above them)
+    const int lowb = 3 * (g.cellbits - 1);
+    const uint32_t mlo = ms & ((1u << lowb) - 1u);
+    const int bx = 2 * (int)(compact3(mlo) | ((ms >> lowb) << (g.cellbits - 1))), by = 2 * (int)compact3(mlo >> 1), bz = 2 * (int)compact3(mlo >> 2);
     if (bx >= g.nc[0] || by >= g.nc[1] || bz >= g.nc[2]) return;
     // the block's own particles: one contiguous run of slots
     int first = 0x7fffffff, len = 0;
@@ -497,7 +500,7 @@ __device__ __forceinline__ void sc_block(uint32_t ms, int lane, ScShared &sh, Sc
             const int cx = wrap_cell(bx - 2 + q % 6, g.nc[0]);
             const int cy = wrap_cell(by - 2 + (q / 6) % 6, g.nc[1]);
             const int cz = wrap_cell(bz - 2 + q / 36, g.nc[2]);
-            const uint32_t key = morton3(cx, cy, cz);
+            const uint32_t key = grid_key(g, 0, cx, cy, cz);
             s0 = cell_start[key];
             l = cell_end[key] - s0;
         }
@@ -722,7 +725,7 @@ k_build_list_sc(Ctl *__restrict__ ctl, const typename Pos4<R>::type *pos0,
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t codes = 1u << (3 * g.cellbits - 3);
+    const uint32_t codes = 1u << (g.keybits - 3);
     for (uint32_t ms = blockIdx.x * SC_WARPS + warp; ms < codes; ms += gridDim.x * SC_WARPS) {
         sc_block<R, FAST2, WIN>(ms, lane, s_warp[warp], s_win[WIN ? warp : 0], s_rl2, s_hi, s_lo, ctl, pos, box, g,
                                 cell_start, cell_end, nbr, nnb, cap, sbt);

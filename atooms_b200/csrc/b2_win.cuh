@@ -55,7 +55,7 @@ __device__ __forceinline__ void win_run(const Grid &g, int sx, int sy, int sz, i
     const int bx = wrap_b8(2 * sx - 1 + (r & 3), g.nc[0] >> 1);
     const int by = wrap_b8(2 * sy - 1 + ((r >> 2) & 3), g.nc[1] >> 1);
     const int bz = wrap_b8(2 * sz - 1 + (r >> 4), g.nc[2] >> 1);
-    const uint32_t code = morton3(bx, by, bz);
+    const uint32_t code = grid_key(g, 1, bx, by, bz);
     start = b8start[code];
     len = b8start[code + 1] - start;
 }
@@ -156,7 +156,7 @@ k_sb_tiles(const Ctl *__restrict__ ctl, Grid g, const int *__restrict__ b8start,
         if (gi < nsb) {
             int sx, sy, sz;
             sb_coords(g, gi, sx, sy, sz);
-            const uint32_t code = morton3(sx, sy, sz);
+            const uint32_t code = grid_key(g, 2, sx, sy, sz);
             t = (b8start[(code + 1) << 3] - b8start[code << 3] + 31) >> 5;
         }
         int incl = t;
@@ -345,7 +345,7 @@ k_sb_table(const Ctl *__restrict__ ctl, Grid g, Box<R> box, const int *__restric
     T[SBT_HEAD + 2 * (lane + 32)] = st1;
     T[SBT_HEAD + 1 + 2 * (lane + 32)] = (p1 & 0xffff) | (ln1 << 16);
     if (lane == 0) {
-        const uint32_t code = morton3(sx, sy, sz);
+        const uint32_t code = grid_key(g, 2, sx, sy, sz);
         const int first = b8start[code << 3];
         T[0] = first;
         T[1] = b8start[(code + 1) << 3] - first;

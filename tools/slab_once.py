@@ -1,7 +1,7 @@
 """Step / refresh times of ONE context whose particles fill a slab of the box (what a rank of the slab
 decomposition holds): the bench system placed in a box twice as long along x.  List format by environment:
 B2_LIST_GLOBAL=1 | B2_LIST_WINDOWED=1 (all super-blocks) | B2_REGION_X=lo,hi (the slab's super-blocks only).
-    python tools/slab_once.py [md_steps]"""
+    python tools/slab_once.py [md_steps] [box length along x in units of the system's]"""
 import json
 import os
 import sys
@@ -14,7 +14,8 @@ from atooms_b200 import capi     # noqa: E402
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 300
 pos, spe, side, vel = bench.ka_workload()
-side = numpy.array(side, dtype=float) * numpy.array([2.0, 1.0, 1.0])
+stretch = float(sys.argv[2]) if len(sys.argv) > 2 else 2.0
+side = numpy.array(side, dtype=float) * numpy.array([stretch, 1.0, 1.0])
 lib = capi.load()
 eng = bench.make_engine(lib, 32, pos, spe, side, vel)
 eng.compute(forces=False)
