@@ -23,8 +23,8 @@ MIN_SD, MIN_FIRE = 0, 1
 NVT_BERENDSEN, NVT_NOSE_HOOVER = 0, 1
 T_KINETIC, T_POTENTIAL, T_VIRIAL, T_FNORM2, T_PX, T_PY, T_PZ, T_MASS, T_MSD, T_LEN = \
     0, 1, 2, 3, 4, 5, 6, 7, 8, 16
-S_STEPS, S_REBUILDS, S_LAUNCHES, S_MAX_NEIGH, S_NEIGH_CAP, S_LIST_MODE, S_NCELLS, S_SMALL_BOX, S_LEN = \
-    0, 1, 2, 3, 4, 5, 6, 7, 16
+S_STEPS, S_REBUILDS, S_LAUNCHES, S_MAX_NEIGH, S_NEIGH_CAP, S_LIST_MODE, S_NCELLS, S_SMALL_BOX, S_WIN_BLOCKS, S_LEN = \
+    0, 1, 2, 3, 4, 5, 6, 7, 8, 16
 
 _ERRORS = {-1: ValueError, -5: NotImplementedError}
 
@@ -450,7 +450,8 @@ class Engine(object):
         return {'steps': int(out[S_STEPS]), 'rebuilds': int(out[S_REBUILDS]),
                 'launches': int(out[S_LAUNCHES]), 'max_neighbors': int(out[S_MAX_NEIGH]),
                 'neighbor_capacity': int(out[S_NEIGH_CAP]), 'list_mode': int(out[S_LIST_MODE]),
-                'ncells': int(out[S_NCELLS]), 'small_box': bool(out[S_SMALL_BOX])}
+                'ncells': int(out[S_NCELLS]), 'small_box': bool(out[S_SMALL_BOX]),
+                'window_blocks': int(out[S_WIN_BLOCKS])}
 
     def last_timing(self):
         ms, launches = _dbl(), _i64()

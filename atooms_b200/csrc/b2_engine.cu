@@ -1763,6 +1763,7 @@ int b2_stats(b2_ctx *c, int64_t out[B2_S_LEN])
     out[B2_S_NEIGH_CAP] = c->cap;
     out[B2_S_LIST_MODE] = c->grid.allpairs ? 1 : (c->grid.win ? 2 : 0);
     out[B2_S_NCELLS] = (int64_t)c->grid.nc[0] * c->grid.nc[1] * c->grid.nc[2];
+    out[B2_S_WIN_BLOCKS] = c->grid.win ? c->nsb_total : 0;
     out[B2_S_SMALL_BOX] = (c->have_box && c->have_table && 2.0 * c->rcut_max > std::min(c->side[0], std::min(c->side[1], c->side[2]))) ? 1 : 0;
     return B2_OK;
 }

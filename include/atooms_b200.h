@@ -85,6 +85,8 @@ extern "C" {
                                 2 = cell list with windowed rows (CUDA engine, >= 8 cells per axis) */
 #define B2_S_NCELLS      6
 #define B2_S_SMALL_BOX   7   /* 1: some side < 2 r_cut,max (single minimum image only) */
+#define B2_S_WIN_BLOCKS  8   /* list mode 2: super-blocks (4x4x4 cells) tabulated and launched: all of the grid,
+                                or those of the slab a rank of the decomposition holds; else 0 */
 #define B2_S_LEN        16
 
 typedef struct b2_ctx b2_ctx;

@@ -178,6 +178,73 @@ def test_neighbor_list_bit_exact_slab_three_species(cuda_lib, oracle_lib, precis
         assert numpy.array_equal(a, b)
 
 
+def long_box(reps_x, keep=None):
+    """ka_N1200 tiled reps_x x 2 x 2 times (a box 10 reps_x long and 20 wide), jittered; `keep`: only the
+    particles with |x| < keep (a slab of matter in an otherwise empty box)."""
+    g = golden('ka_N1200')
+    side = numpy.array(g['side'])
+    shifts = numpy.array([[i, j, k] for i in range(reps_x) for j in range(2) for k in range(2)])
+    pos = (g['position'][None, :, :] + shifts[:, None, :] * side).reshape(-1, 3)
+    pos -= 0.5 * (numpy.array([reps_x, 2, 2]) - 1) * side
+    pos += numpy.random.default_rng(23).uniform(-0.02, 0.02, size=pos.shape)
+    spe = numpy.tile(g['species'], len(shifts))
+    if keep is not None:
+        inside = numpy.abs(pos[:, 0]) < keep
+        pos, spe = pos[inside], spe[inside]
+    n = len(pos)
+    return {'position': pos, 'species': spe, 'side': side * numpy.array([reps_x, 2, 2]), 'center': numpy.zeros(3),
+            'mass': numpy.ones(n), 'velocity': onp.maxwell_boltzmann(n, 0.8, 1.0, 29)}
+
+
+@pytest.mark.parametrize('precision', [64, 32])
+def test_box_with_more_than_256_cells_along_x(cuda_lib, oracle_lib, precision):
+    """The box of a slab decomposition is long along x: cell keys carry the bits of x beyond those y and z need on
+    top of the Morton part (grid_key).  400 x 20 x 20 -> 284 x 14 x 14 cells: single point, bit-exact list, and
+    an NVE stretch with refreshes, on the windowed list (fp32) and the global one (fp64)."""
+    d = rounded(long_box(40), precision)
+    ka = onp.kob_andersen()
+    eng = make_engine(cuda_lib, d, ka, precision)
+    got = eng.compute(per_particle=True, stress=True)
+    st = eng.stats()
+    # (the windowed list takes an even number of cells per axis)
+    assert st['ncells'] == (284 if precision == 32 else 285) * 14 * 14 and st['list_mode'] == (2 if precision == 32 else 0)
+    assert_observables(got, make_engine(oracle_lib, d, ka, 64).compute(per_particle=True, stress=True), precision)
+    for a, b in zip(eng.neighbors(), make_engine(oracle_lib, d, ka, precision).neighbors()):
+        assert numpy.array_equal(a, b)
+    eng.run_nve(200, 0.002)
+    assert eng.stats()['rebuilds'] >= 3
+    pos, vel, _ = eng.download()
+    assert_observables(eng.compute(), make_engine(oracle_lib, dict(d, position=pos, velocity=vel), ka, 64).compute(), precision)
+
+
+def test_windowed_list_over_a_slab_of_the_box(cuda_lib, oracle_lib, monkeypatch):
+    """A rank of the slab decomposition tabulates and launches only the super-blocks its particles can be in
+    (b2_peer_refresh tells the engine; B2_REGION_X does the same for one context).  The list is the oracle's;
+    a particle outside the announced slab makes the engine fall back to all super-blocks, not to a wrong list."""
+    d = rounded(long_box(40, keep=60.0), 32)
+    ka = onp.kob_andersen()
+    ref = make_engine(oracle_lib, d, ka, 32).neighbors()
+    blocks = {}
+    for name, region in (('all', None), ('slab', '-61,61'), ('short', '-30,30')):
+        if region is None:
+            monkeypatch.delenv('B2_REGION_X', raising=False)
+            monkeypatch.setenv('B2_LIST_WINDOWED', '1')       # (or the engine takes a box this empty off the windowed list)
+        else:
+            monkeypatch.setenv('B2_REGION_X', region)
+        eng = make_engine(cuda_lib, d, ka, 32)
+        got = eng.neighbors()
+        st = eng.stats()
+        assert st['list_mode'] == 2
+        blocks[name] = st['window_blocks']
+        for a, b in zip(got, ref):
+            assert numpy.array_equal(a, b)
+        eng.run_nve(100, 0.002)
+        pos, vel, _ = eng.download()
+        assert_observables(eng.compute(), make_engine(oracle_lib, dict(d, position=pos, velocity=vel), ka, 64).compute(), 32)
+    assert blocks['all'] == 71 * 4 * 4 and blocks['short'] == blocks['all']      # fell back
+    assert blocks['slab'] < 0.45 * blocks['all']                                # 120 of 400 along x, + margins
+
+
 def test_nve_trajectory_pin(cuda_lib, oracle_lib, pins):
     """tests/test_lammps.py:33-40 through the CUDA engine, and step-for-step vs the oracle."""
     pin = pins['lj_N1000_nve_x0']
