@@ -562,8 +562,11 @@ template <typename R> struct Impl {
             LAUNCH(k_gather_commit<R>, cdiv(n, 256), 256, c->ctl, n, (const P4 *)c->tpos, (const V4 *)c->tvel,
                    c->torig, (P4 *)c->pos[0], (P4 *)c->pos[1], (V4 *)c->vel, c->orig);
             LAUNCH(k_inverse, cdiv(n, 256), 256, c->ctl, 1, c->orig, n, c->inv);
-            LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
-            LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
+            static const bool gathered_build = getenv("B2_BUILD_GATHERED") && atoi(getenv("B2_BUILD_GATHERED")) != 0;
+            if (!c->grid.win || gathered_build) {       // (the windowed build goes by the runs of the 2x2x2 blocks alone)
+                LAUNCH(k_fill_int, cdiv(c->ncelltab, 256), 256, c->ctl, c->cell_start, c->cell_end, c->ncelltab, 0);
+                LAUNCH(k_cell_bounds, cdiv(n, 256), 256, c->ctl, c->keys[src], n, c->cell_start, c->cell_end);
+            }
             if (c->grid.win) {
                 LAUNCH(k_b8_bounds, cdiv(c->nb8codes + 1, 256), 256, c->ctl, c->keys[src], n, c->nb8codes, c->b8start);
                 LAUNCH(k_sb_tiles, 1, 1024, c->ctl, c->grid, c->b8start, c->tile_base);
@@ -1134,21 +1137,6 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
             long long nrb = c->hctl->rebuilds - rb0;
             if (nrb > 0 && progressed > 0)   // refresh period seen in this round -> batch length
                 c->batch = (int)std::min<int64_t>(std::max<int64_t>(progressed / nrb, 1), 64);
-            // The windowed list pays ~0.25 ms more per refresh and ~0.017 ms less per step (KA N = 1.2M): it wins
-            // when the list lasts longer than ~15 steps.  A run that refreshes more often than every 10 steps
-            // (LJ rho = 0.85 at dt = 0.005: every 7) goes back to the global-index list, once and for good.
-            if (c->grid.win && nrb >= 2 && progressed / nrb < 10 && done < steps &&
-                !(getenv("B2_LIST_WINDOWED") && atoi(getenv("B2_LIST_WINDOWED")) != 0)) {
-                c->win_off = true;
-                c->cap = 0;
-                c->list_dirty = true;
-                if ((rc = ensure_list(c))) return rc;
-                a.nbr = c->nbr;
-                a.cap = c->cap;
-                if ((rc = pull_ctl(c))) return rc;
-                c->hctl->steps_done = done;          // (ensure_list went through the control block)
-                if ((rc = push_ctl(c))) return rc;
-            }
         }
     }
     c->prof[3] = (double)steps;
