@@ -33,8 +33,14 @@ def _save_arrays(path, **arrays):
     meta, blobs = [], []
     for name, a in arrays.items():
         a = numpy.ascontiguousarray(a)
-        meta.append({'name': name, 'dtype': a.dtype.str, 'shape': list(a.shape), 'bytes': int(a.nbytes)})
-        blobs.append(a)
+        m = {'name': name, 'dtype': a.dtype.str, 'shape': list(a.shape), 'bytes': int(a.nbytes)}
+        # an array of one repeated value (masses, radii, image counters of a short run: a quarter of the file)
+        # is stored as that value
+        if a.size > 1024 and a.dtype.kind in 'fiu' and (a.reshape(-1)[::1024] == a.flat[0]).all() and (a == a.flat[0]).all():
+            m['fill'], m['bytes'] = a.flat[0].item(), 0
+        else:
+            blobs.append(a)
+        meta.append(m)
     with open(path, 'wb') as fh:
         fh.write((json.dumps(meta) + '\n').encode())
         for a in blobs:
@@ -49,7 +55,10 @@ def _load_arrays(path):
             return numpy.load(path)
         out = {}
         for m in json.loads(first.decode()):
-            out[m['name']] = numpy.frombuffer(fh.read(m['bytes']), dtype=numpy.dtype(m['dtype'])).reshape(m['shape']).copy()
+            if 'fill' in m:
+                out[m['name']] = numpy.full(m['shape'], m['fill'], dtype=numpy.dtype(m['dtype']))
+            else:
+                out[m['name']] = numpy.frombuffer(fh.read(m['bytes']), dtype=numpy.dtype(m['dtype'])).reshape(m['shape']).copy()
     return out
 
 
