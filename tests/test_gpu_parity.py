@@ -155,6 +155,22 @@ def test_neighbor_list_bit_exact_replicated(cuda_lib, oracle_lib, precision):
         assert numpy.array_equal(a, b)
 
 
+def test_neighbor_list_rows_longer_than_the_build_buffer(cuda_lib, oracle_lib):
+    """The windowed build (k_build_list_win) collects a warp's rows in shared memory, 128 entries per lane, and
+    goes on in the list itself once a lane has filled them: with a skin of 0.7 rows hold up to ~190 entries, so
+    every warp changes over, some of them in the middle of a stretch of candidates."""
+    d = rounded(replicated('ka_N1200', 3, 0.02, 7), 32)            # N = 32400, 18 cells per axis
+    ka = onp.kob_andersen()
+    eng = make_engine(cuda_lib, d, ka, 32, skin=0.7)
+    got = eng.neighbors()
+    st = eng.stats()
+    assert st['list_mode'] == 2 and st['max_neighbors'] > 140
+    ref = make_engine(oracle_lib, d, ka, 32, skin=0.7).neighbors()
+    for a, b in zip(got, ref):
+        assert numpy.array_equal(a, b)
+    assert_observables(eng.compute(), make_engine(oracle_lib, d, ka, 64, skin=0.7).compute(), 32)
+
+
 @pytest.mark.parametrize('precision', [64, 32])
 def test_neighbor_list_bit_exact_slab_three_species(cuda_lib, oracle_lib, precision):
     """A non-cubic box (14 x 7 x 7 cells: even and odd counts, periodic wrap of a half block of
