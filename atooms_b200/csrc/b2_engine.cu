@@ -90,6 +90,14 @@ struct b2_ctx {
     int nb8codes = 0, nsb_total = 0, win_tab_alloc = 0, win_sb_alloc = 0;
     bool win_off = false;            // windows do not fit: this context keeps the global-index list
     // the particles fill only the fractions lo <= u < hi (+ wrap) of the box along x: a slab of a decomposed system (b2_peer_refresh)
+    bool peer_fused = false;         // (b2_peer_run -> dd_step: commit inside the step kernel)
+    // ... and the halo push (StepArgs::halo_map): the map is rebuilt when the list (slots) or the send lists changed
+    bool peer_push_fused = false;
+    int *halo_map = nullptr;
+    int64_t halo_map_cap = 0;
+    long long list_epoch = 0, send_epoch = 0, halo_map_list = -1, halo_map_send = -1;
+    double *halo_out_l[2] = {nullptr, nullptr}, *halo_out_r[2] = {nullptr, nullptr};
+    unsigned long long *halo_flag_l = nullptr, *halo_flag_r = nullptr;
     bool region_on = false, region_off = false;
     double region_lo = 0, region_hi = 0, win_fill = 1.0;
     size_t smem_optin = 0, smem_sm = 0;      // shared memory a block may opt into, and of an SM
@@ -633,6 +641,7 @@ template <typename R> struct Impl {
             CU(cudaGetLastError());
             if (!c->hctl->overflow) {
                 c->list_dirty = false;
+                c->list_epoch++;
                 return B2_OK;
             }
             if ((rc = grow_after_overflow(c))) return rc;
@@ -1089,6 +1098,11 @@ int Impl<R>::run_nve(b2_ctx *c, int64_t steps, double dt, int th_kind, double T0
     a.vmax_out = nullptr;
     a.vmax_mail = nullptr;
     a.peer_state = nullptr;
+    a.peer_commit_state = nullptr;
+    a.peer_mail_in = nullptr;
+    a.peer_gv_out = nullptr;
+    a.peer_drift = 0.0;
+    a.halo_map = nullptr;
     a.nranks = 1;
     a.ke_partial = c->ke_partial;
     int64_t done = 0;
@@ -1285,6 +1299,19 @@ int Impl<R>::dd_step(b2_ctx *c, float *vmax_out)
     a.vmax_mail = c->peer_on ? c->peer_mail : nullptr;
     a.peer_state = c->peer_on ? c->peer_ticket + 2 : nullptr;
     a.nranks = c->nranks;
+    // b2_peer_run: the step kernel's last block settles the step itself (no k_peer_commit launch)
+    const bool fused = c->peer_on && c->peer_fused && n > 0;
+    a.peer_commit_state = fused ? c->peer_ticket + 2 : nullptr;
+    a.peer_mail_in = fused ? (const unsigned long long *)c->peer_buf : nullptr;
+    a.peer_gv_out = fused ? c->dd_vmax + 1 : nullptr;
+    a.peer_drift = c->dd_dt;
+    a.halo_map = fused && c->peer_push_fused ? c->halo_map : nullptr;
+    for (int par = 0; par < 2; par++) {
+        a.halo_out_l[par] = c->halo_out_l[par];
+        a.halo_out_r[par] = c->halo_out_r[par];
+    }
+    a.halo_flag_l = c->halo_flag_l;
+    a.halo_flag_r = c->halo_flag_r;
     a.ke_partial = nullptr;
     if (n > 0) enqueue_step<false>(c, a);
     return B2_OK;
@@ -1471,7 +1498,7 @@ int b2_destroy(b2_ctx *c)
     void *ptrs[] = {c->pos[0], c->pos[1], c->vel, c->frc, c->vir, c->tpos, c->tvel, c->orig, c->torig, c->inv, c->halo_buf, c->dd_vmax,
                     c->img, c->ref, c->mvel, c->ke_partial, c->keys[0], c->keys[1], c->vals[0], c->vals[1], c->hist,
                     c->cell_start, c->cell_end, c->nbr, c->nnb, c->ctl, c->partial, c->stage, c->stage_i, c->b8start,
-                    c->tile_base, c->sbt, c->tab_u, c->tab_w, c->tab_wf};
+                    c->tile_base, c->sbt, c->tab_u, c->tab_w, c->tab_wf, c->halo_map};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
@@ -2253,6 +2280,7 @@ int b2_nccl_set_halo(b2_ctx *c, const int32_t *send_l_dev, int64_t n_send_l, con
     NEED_PARTICLES("b2_nccl_set_halo");
     if (n_send_l < 0 || n_send_r < 0 || n_ghost_l < 0 || n_ghost_r < 0 || n_ghost_l + n_ghost_r > c->n)
         return fail(c, B2_EINVAL, "b2_nccl_set_halo: bad counts");
+    c->send_epoch++;
     c->send_l = send_l_dev; c->send_r = send_r_dev;
     c->n_send_l = (int)n_send_l; c->n_send_r = (int)n_send_r;
     c->n_ghost_l = (int)n_ghost_l; c->n_ghost_r = (int)n_ghost_r;
@@ -2611,11 +2639,49 @@ template <typename R> struct ImplPeer {
             CU(cudaMemsetAsync(c->dd_vmax, 0, 2 * sizeof(float), c->stream));
         }
         char *L = c->peer_map[c->left], *Rt = c->peer_map[c->right];
+        // The step kernel's last block settles the step (B2_PEER_COMMIT_KERNEL=1: k_peer_commit as a launch of its
+        // own, 0.2364 against 0.2341 ms per step at 2 x 1.2M).  B2_PEER_PUSH_FUSED=1: the step kernel also stores
+        // the boundary positions into the neighbours' inboxes (no k_peer_push) — measured SLOWER, 0.2374 ms: the
+        // stores of a block at a face are scattered over its warps and have to be fenced system-wide in its tail,
+        // where k_peer_push writes them as contiguous rows; kept as a switch, off by default.
+        static const bool commit_kernel = getenv("B2_PEER_COMMIT_KERNEL") && atoi(getenv("B2_PEER_COMMIT_KERNEL")) != 0;
+        static const bool push_fused = getenv("B2_PEER_PUSH_FUSED") && atoi(getenv("B2_PEER_PUSH_FUSED")) != 0;
+        const bool fuse_commit = !commit_kernel && n > 0;
+        const bool fuse_push = fuse_commit && push_fused && !c->list_dirty;
+        if (fuse_push) {
+            // the step kernel stores boundary positions into the neighbours' inboxes itself: slot -> send-list entry
+            if (!c->halo_map || c->halo_map_cap < c->ncap) {
+                if (c->halo_map) cudaFree(c->halo_map);
+                c->halo_map = nullptr;
+                CU(cudaMalloc((void **)&c->halo_map, (size_t)c->ncap * sizeof(int)));
+                c->halo_map_cap = c->ncap;
+                c->halo_map_list = -1;
+            }
+            if (c->halo_map_list != c->list_epoch || c->halo_map_send != c->send_epoch) {
+                CU(cudaMemsetAsync(c->halo_map, 0xff, (size_t)n * sizeof(int), c->stream));
+                if (c->n_send_l + c->n_send_r > 0)
+                    LAUNCH(k_halo_map, cdiv(c->n_send_l + c->n_send_r, 256), 256, c->inv, c->send_l, c->n_send_l, c->send_r,
+                           c->n_send_r, c->halo_map);
+                c->halo_map_list = c->list_epoch;
+                c->halo_map_send = c->send_epoch;
+            }
+            for (int par = 0; par < 2; par++) {
+                c->halo_out_l[par] = (double *)(L + peer_inbox(W, c->peer_cap, 1, par));
+                c->halo_out_r[par] = (double *)(Rt + peer_inbox(W, c->peer_cap, 0, par));
+            }
+            c->halo_flag_l = (unsigned long long *)(L + peer_off_flags(W) + 64);
+            c->halo_flag_r = (unsigned long long *)(Rt + peer_off_flags(W));
+        }
         for (int64_t k = 0; k < count; k++) {
+            c->peer_fused = fuse_commit;
+            c->peer_push_fused = fuse_push;
             int rc = Impl<R>::dd_step(c, c->dd_vmax);
+            const bool fused = c->peer_fused;
+            c->peer_fused = c->peer_push_fused = false;
             if (rc) return rc;
-            LAUNCH(k_peer_commit, 1, 32, c->ctl, c->peer_ticket + 2, (const unsigned long long *)c->peer_buf, W, c->dd_dt,
-                   c->dd_vmax + 1);
+            if (!fused)
+                LAUNCH(k_peer_commit, 1, 32, c->ctl, c->peer_ticket + 2, (const unsigned long long *)c->peer_buf, W, c->dd_dt,
+                       c->dd_vmax + 1);
             PeerArgs<R> a;
             a.ctl = c->ctl;
             a.pos[0] = (P4 *)c->pos[0];
@@ -2639,7 +2705,7 @@ template <typename R> struct ImplPeer {
             a.my_flag_r = (const unsigned long long *)(c->peer_buf + peer_off_flags(W) + 64);
             a.ticket = c->peer_ticket;
             a.state = c->peer_ticket + 2;
-            LAUNCH(k_peer_push<R>, std::max(1, cdiv(c->n_send_l + c->n_send_r, 256)), 256, a);
+            if (!fuse_push) LAUNCH(k_peer_push<R>, std::max(1, cdiv(c->n_send_l + c->n_send_r, 256)), 256, a);
             LAUNCH(k_peer_pull<R>, std::max(1, cdiv(c->n_ghost_l + c->n_ghost_r, 256)), 256, a);
         }
         return B2_OK;
@@ -2877,6 +2943,7 @@ template <typename R> struct ImplDdr {
         if (nn > 0)
             LAUNCH(k_ddr_finish<R>, cdiv((int)nn, 256), 256, (const P4 *)c->pos[0], (int)nn, make_box<R>(c),
                    c->orig, c->inv, c->img, c->ref);
+        c->send_epoch++;
         c->send_l = c->ddr_send[0]; c->send_r = c->ddr_send[1];
         c->n_send_l = (int)h[DC_SEND_L]; c->n_send_r = (int)h[DC_SEND_R];
         c->n_ghost_l = (int)h[DC_G_L]; c->n_ghost_r = (int)h[DC_G_R];

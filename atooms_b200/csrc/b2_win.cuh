@@ -845,7 +845,10 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
     extern __shared__ __align__(128) unsigned char win_raw[];
     Ctl *ctl = a.ctl;
     if (ctl->halt_rebuild | ctl->overflow | ctl->done) {
-        if (a.dd && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) *a.vmax_out = 0.f;
+        if (a.dd && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) {
+            *a.vmax_out = 0.f;
+            if (a.peer_commit_state) { a.peer_commit_state[1] = 0u; *a.peer_gv_out = 0.f; }     // (as k_peer_commit)
+        }
         return;
     }
     __shared__ __align__(8) unsigned long long s_bar;
@@ -884,6 +887,7 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
     const R th_a = NVT ? (R)ctl->th_a : (R)1, th_b = NVT ? (R)ctl->th_b : (R)1;
     float v2 = 0.f;
     double mv2 = 0.0;
+    bool pushed = false;
     for (;;) {
         if (valid) {
             if (is_ghost(pi)) {
@@ -904,7 +908,9 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
                     v.x += s * fx; v.y += s * fy; v.z += s * fz;
                 }
                 int kx, ky, kz;
-                posn[i] = advance(pi, a.drift * v.x, a.drift * v.y, a.drift * v.z, a.box, kx, ky, kz);
+                const P4 pnew = advance(pi, a.drift * v.x, a.drift * v.y, a.drift * v.z, a.box, kx, ky, kz);
+                posn[i] = pnew;
+                if (a.halo_map) pushed |= peer_push_one(a, i, pnew);
                 if (kx | ky | kz) {
                     int *im = a.img + 3 * (size_t)a.orig[i];
                     im[0] += kx; im[1] += ky; im[2] += kz;
@@ -924,7 +930,7 @@ k_step_win(StepArgs<R> a, WinArgs<R> wa)
             win_row_begin<U>(row, jj);
         }
     }
-    step_epilogue<R, NVT, WIN_THREADS>(a, ctl, cur, v2, mv2);
+    step_epilogue<R, NVT, WIN_THREADS>(a, ctl, cur, v2, mv2, pushed);
 }
 
 // Forces (+ per-particle energy / virial, + stress partials) on the windowed list: k_force's twin.

@@ -20,6 +20,13 @@ pytestmark = pytest.mark.gpu
 
 
 def _worker(rank, world, port, steps, precision, backend, mode, out, reps_x=2):
+    # variants of the peer-memory step (switches of the CUDA library, read once per process): the commit as a kernel of
+    # its own instead of the step kernel's last block; the halo pushed by the step kernel instead of k_peer_push
+    if mode == 'peer/commit-kernel':
+        os.environ['B2_PEER_COMMIT_KERNEL'] = '1'
+    if mode == 'peer/push-fused':
+        os.environ['B2_PEER_PUSH_FUSED'] = '1'
+    mode = mode.split('/')[0]
     fast, peer = mode != 'torch', mode.startswith('peer')
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
@@ -66,14 +73,14 @@ def test_four_rank_ring_on_cuda(tmp_path, cuda_lib):
     _compare(64, 'peer', tmp_path, cuda_lib, world=4, reps_x=3)
 
 
-@pytest.mark.parametrize('mode', ['torch', 'nccl', 'peer-host', 'peer'])
+@pytest.mark.parametrize('mode', ['torch', 'nccl', 'peer-host', 'peer', 'peer/commit-kernel', 'peer/push-fused'])
 @pytest.mark.parametrize('precision', [64, 32])
 def test_two_rank_slab_run_on_cuda(precision, mode, tmp_path, cuda_lib):
     _compare(precision, mode, tmp_path, cuda_lib)
 
 
 def _compare(precision, mode, tmp_path, cuda_lib, world=2, reps_x=2):
-    fast = mode != 'torch'
+    fast = mode != 'torch'                    # ('peer/...' variants: see _worker)
     from conftest import make_engine
     from oracle import oracle_np as onp
     steps = 120
