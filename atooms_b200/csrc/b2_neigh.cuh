@@ -426,12 +426,6 @@ struct ScWindow {
 __device__ __forceinline__ void sc_append16(bool hit, unsigned short *row, int &cnt, int cap, int off)
 {
     unsigned short *dst = row + (size_t)cnt * 32;
-#ifdef BW_EXPERIMENT_NOSTORE          // timing experiment only (the list is not written)
-    asm volatile("{\n\t.reg .pred q, s;\n\tsetp.ne.s32 q, %1, 0;\n\tsetp.lt.and.s32 s, %0, %2, q;\n\t"
-                 "@q add.s32 %0, %0, 1;\n\t}"
-                 : "+r"(cnt) : "r"((int)hit), "r"(cap), "l"(dst), "h"((unsigned short)off) : "memory");
-    return;
-#endif
     asm volatile("{\n\t.reg .pred q, s;\n\tsetp.ne.s32 q, %1, 0;\n\tsetp.lt.and.s32 s, %0, %2, q;\n\t"
                  "@s st.global.b16 [%3], %4;\n\t@q add.s32 %0, %0, 1;\n\t}"
                  : "+r"(cnt) : "r"((int)hit), "r"(cap), "l"(dst), "h"((unsigned short)off) : "memory");
