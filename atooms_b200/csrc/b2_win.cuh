@@ -488,9 +488,11 @@ __device__ __forceinline__ f32x2 x2_fma(f32x2 a, f32x2 b, f32x2 c)
 // entry `off` of a lane into the warp's row buffer (shared-memory address sptr), predicated like sc_append16
 __device__ __forceinline__ void bw_append_s(bool hit, unsigned &sptr, int off)
 {
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %1, 0;\n\t"
-                 "@q st.shared.b16 [%0], %2;\n\t@q add.u32 %0, %0, 64;\n\t}"
-                 : "+r"(sptr) : "r"((int)hit), "h"((unsigned short)off) : "memory");
+    // the store's address in a register of its own: with `@q st [sptr]; @q add sptr, 64` the add waits until the
+    // store unit has read sptr (short-scoreboard, 15 % of the loop's samples)
+    const unsigned at = sptr;
+    sptr = at + (hit ? 64u : 0u);
+    if (hit) asm volatile("st.shared.b16 [%0], %1;" ::"r"(at), "h"((unsigned short)off) : "memory");
 }
 // the buffered rows of a warp -> the list, one row of 32 lanes per store.  Rows beyond a lane's own count carry
 // leftovers: they land in slots of its row that are rewritten later or never read.
