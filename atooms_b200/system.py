@@ -122,8 +122,10 @@ class _ParticleList(object):
         s = self._system
         p = self._cache.get(i)
         if p is None:
-            p = _particle_class()(position=s._pos_user[i], velocity=s._vel_user[i], species=s._names[s._ids[i]],
-                                  mass=s._mass[i], radius=s._radius[i])
+            p = _bound_particle_class()(position=s._pos_user[i], velocity=s._vel_user[i],
+                                        species=s._pending_species.get(i, s._names[s._ids[i]]),
+                                        mass=s._mass[i], radius=s._radius[i])
+            p.__dict__['_b2_owner'] = (s, i)
             # the reference's Particle takes numpy.asarray of its arguments (particle.py:24-30), which drops
             # the tracking subclass: hand it the tracked row views again
             p.position, p.velocity = s._pos_user[i], s._vel_user[i]
@@ -156,6 +158,34 @@ def _particle_class():
         return P
     except Exception:
         return Particle
+
+
+_BOUND = {}
+
+
+def _bound_particle_class():
+    """The particle class with `species`, `mass` and `radius` that write through to the System they belong to (position and
+    velocity are views already): the reference's trajectory callbacks assign them per particle
+    (atooms/trajectory/decorators.py:33-89 `change_species`)."""
+    base = _particle_class()
+    cls = _BOUND.get(base)
+    if cls is None:
+        def _get(name):
+            return lambda self: self.__dict__['_b2_' + name]
+
+        def _set(name):
+            def setter(self, value):
+                self.__dict__['_b2_' + name] = value
+                owner = self.__dict__.get('_b2_owner')
+                if owner is not None:
+                    owner[0]._assign(owner[1], name, value)
+            return setter
+        cls = type('Particle', (base,), {'species': property(_get('species'), _set('species')),
+                                         'mass': property(_get('mass'), _set('mass')),
+                                         'radius': property(_get('radius'), _set('radius')),
+                                         '__module__': base.__module__})
+        _BOUND[base] = cls
+    return cls
 
 
 class _Tracked(numpy.ndarray):
@@ -223,7 +253,7 @@ def _tracked(array, flag):
 class System(object):
 
     def __init__(self, position, species, cell, velocity=None, mass=None, radius=None,
-                 model='lennard_jones', precision=64, skin=0.3, device=0, library=None):
+                 model='lennard_jones', precision=64, skin=0.3, device=0, library=None, species_order=None):
         position = numpy.array(position, dtype=numpy.float64)
         if position.ndim != 2 or position.shape[1] != 3:
             raise ValueError('position must be (N, 3); only three dimensions are supported')
@@ -242,7 +272,10 @@ class System(object):
         self.model = models.get(model)
         # species names -> 0-based ids in table order
         names = [str(s) for s in species]
-        order = self.model.species if self.model.species is not None else sorted(set(names))
+        if species_order is not None:         # (a system rebuilt from a subset keeps the ids of its species)
+            order = list(species_order) + sorted(set(names) - set(species_order))
+        else:
+            order = self.model.species if self.model.species is not None else sorted(set(names))
         if len(order) > self.model.nsp:
             raise ValueError('system has %d species but the model %s has %d'
                              % (len(order), self.model, self.model.nsp))
@@ -274,6 +307,8 @@ class System(object):
         self._views_out = False          # a mutable handle on the host arrays is in user hands
         self._img_stale = False
         self._img_out = False
+        self._identity_dirty = False     # species or masses were assigned through particle objects
+        self._pending_species = {}       # ... particle -> name, until the next push settles them
         self._touched = {'pos': [False], 'vel': [False]}      # ... and was written through (see _Tracked)
         # 'always': while handles are out, both arrays are pushed before every device operation — right for any
         # writer.  'tracked': only arrays written through numpy since the last push (see _Tracked) are pushed.
@@ -315,6 +350,16 @@ class System(object):
             else:                             # any writer, f2py / C kernels included: push everything
                 self._host_pos_dirty = self._host_vel_dirty = True
             self._touched['pos'][0] = self._touched['vel'][0] = False
+        if self._identity_dirty:
+            # species / masses changed: the device copy is rebuilt from the host arrays (which the holder of the
+            # particle objects owns anyway), the box-crossing counters are kept
+            self._resolve_species()
+            self._engine.upload(self._pos, self._ids, self._vel, self._mass)
+            self._engine.set_images(self._img)
+            self._identity_dirty = self._host_pos_dirty = self._host_vel_dirty = False
+            self._thermo = None
+            if self.interaction is not None:
+                self.interaction._invalidate()
         if self._host_pos_dirty or self._host_vel_dirty:
             self._engine.update(self._pos if self._host_pos_dirty else None,
                                 self._vel if self._host_vel_dirty else None)
@@ -389,6 +434,8 @@ class System(object):
 
     @property
     def species(self):
+        if self._pending_species:
+            return numpy.array(self._labels().tolist())
         return numpy.array(self._names)[self._ids]
 
     @property
@@ -405,16 +452,95 @@ class System(object):
         the whole list on each access)."""
         return self._particle
 
+    @particle.setter
+    def particle(self, particles):
+        """Replace the particles by a list of particle objects, as the reference's System allows and its trajectory
+        callbacks do (`sort`, `filter_species`: atooms/trajectory/decorators.py:91-99).  The device context is
+        rebuilt; cell, model, reservoirs, interaction and synchronisation mode stay."""
+        particles = list(particles)
+        if not particles:
+            raise ValueError('a system needs at least one particle')
+        self._resolve_species()
+        self._pull_image()
+        new = System(position=numpy.array([numpy.asarray(q.position, dtype=numpy.float64) for q in particles]),
+                     species=[str(q.species) for q in particles], cell=self.cell,
+                     velocity=numpy.array([numpy.asarray(q.velocity, dtype=numpy.float64) for q in particles]),
+                     mass=[float(q.mass) for q in particles], radius=[float(getattr(q, 'radius', 0.5)) for q in particles],
+                     model=self.model, precision=self.precision, skin=self._skin(), device=self._engine.device,
+                     library=self._engine.lib, species_order=self._names)
+        images = [getattr(q, 'periodic_image', None) for q in particles]
+        if all(im is not None for im in images):
+            new._img[:] = numpy.array(images, dtype=numpy.int32).reshape(len(particles), 3)
+            new._engine.set_images(new._img)
+        for name in ('thermostat', 'barostat', 'reservoir', 'interaction', 'sync'):
+            setattr(new, name, getattr(self, name))
+        old_engine = self._engine
+        self.__dict__.update(new.__dict__)
+        self._particle._system = self
+        old_engine.close()
+        new.__dict__.clear()                 # (its engine and arrays live on in self)
+        if self.interaction is not None:
+            self.interaction._invalidate()
+
+    def _assign(self, i, name, value):
+        """`particle[i].species = ...` / `.mass = ...` (see _bound_particle_class)."""
+        if name == 'species':
+            self._pending_species[int(i)] = str(value)       # settled by _resolve_species
+        elif name == 'radius':
+            self._radius[i] = float(value)                   # (host side only: the engine has no use for it)
+            return
+        else:
+            self._mass[i] = float(value)
+        self._identity_dirty = True
+        self._thermo = None
+
+    def _labels(self):
+        """Species name of every particle, names assigned through particle objects included."""
+        labels = numpy.array(self._names, dtype=object)[self._ids]
+        for i, name in self._pending_species.items():
+            labels[i] = name
+        return labels
+
+    def _resolve_species(self):
+        """Names assigned particle by particle (`_assign`) -> rows of the model's table.  If every name is one the
+        system has, each particle simply takes that species.  Otherwise the assignment must be a RENAMING: all
+        particles of a species carry one and the same new name (`change_species`: 'A' -> '0', 'B' -> '1', whatever
+        the names meant before), and the species keeps its row.  Anything else does not fit a table of fixed species."""
+        if not self._pending_species:
+            return
+        labels = self._labels()
+        self._pending_species = {}
+        if set(labels.tolist()) <= set(self._names):
+            lookup = {name: k for k, name in enumerate(self._names)}
+            self._ids[:] = [lookup[name] for name in labels]
+            return
+        names = list(self._names)
+        for k in numpy.unique(self._ids):
+            mine = set(labels[self._ids == k].tolist())
+            if len(mine) != 1:
+                raise ValueError('species %s of the model %s (species %s) would be split into %s: only a renaming of '
+                                 'all particles of a species can be taken over' % (names[k], self.model, self._names, sorted(mine)))
+            names[k] = mine.pop()
+        used = [names[k] for k in numpy.unique(self._ids)]
+        if len(set(used)) != len(used):
+            raise ValueError('two species of the model %s were given the same new name %s' % (self.model, used))
+        self._names = names
+
     @property
     def number_of_dimensions(self):
         return 3
 
     @property
     def distinct_species(self):
+        if self._pending_species:
+            return sorted(set(self._labels().tolist()))
         return sorted(set(self._names[i] for i in numpy.unique(self._ids)))
 
     @property
     def composition(self):
+        if self._pending_species:
+            names, counts = numpy.unique(self._labels().astype(str), return_counts=True)
+            return {str(k): int(c) for k, c in zip(names, counts)}
         ids, counts = numpy.unique(self._ids, return_counts=True)
         return {self._names[i]: int(c) for i, c in zip(ids, counts)}
 
@@ -610,6 +736,7 @@ class System(object):
     def __deepcopy__(self, memo):
         """An independent system with its own device context (tests/test_rumd.py:178-194)."""
         self._pull()
+        self._resolve_species()
         new = System(self._pos, [self._names[i] for i in self._ids], Cell(self.cell.side.copy(), self.cell.center.copy()),
                      velocity=self._vel, mass=self._mass, radius=self._radius, model=self.model,
                      precision=self.precision, skin=self._skin(), device=self._engine.device,

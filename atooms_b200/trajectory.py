@@ -91,9 +91,49 @@ class Snapshot(object):
     def particle(self):
         return _Particles(self)
 
+    @particle.setter
+    def particle(self, particles):
+        """A new list of particle objects (the reference's callbacks `sort` / `filter_species` assign one,
+        atooms/trajectory/decorators.py:91-99)."""
+        particles = list(particles)
+        n = len(particles)
+        self.position = numpy.array([q.position for q in particles], dtype=numpy.float64).reshape(n, 3)
+        self.velocity = numpy.array([q.velocity for q in particles], dtype=numpy.float64).reshape(n, 3)
+        self.species = numpy.array([q.species for q in particles])
+        self.mass = numpy.array([q.mass for q in particles], dtype=numpy.float64)
+        self.radius = numpy.array([getattr(q, 'radius', 0.5) for q in particles], dtype=numpy.float64)
+
+    def _assign(self, i, name, value):
+        """`particle[i].species = ...` / `.mass = ...` write through (atooms_b200.system._bound_particle_class)."""
+        if name == 'species':
+            if self.species.dtype != object:
+                self.species = self.species.astype(object)      # (a fixed-width string array would truncate)
+            self.species[i] = value
+        elif name == 'radius':
+            self.radius[i] = float(value)
+        else:
+            self.mass[i] = float(value)
+
     @property
     def distinct_species(self):
         return sorted(set(self.species.tolist()))
+
+    @property
+    def cm_position(self):
+        return (self.mass[:, None] * self.position).sum(axis=0) / self.mass.sum()
+
+    @property
+    def cm_velocity(self):
+        return (self.mass[:, None] * self.velocity).sum(axis=0) / self.mass.sum()
+
+    def kinetic_energy(self, per_particle=False, normed=False):
+        k = 0.5 * float((self.mass[:, None] * self.velocity ** 2).sum())
+        return k / len(self) if (per_particle or normed) else k
+
+    @property
+    def temperature(self):
+        n = len(self)
+        return 2.0 * self.kinetic_energy() / (3 * (n - 1)) if n > 1 else 0.0      # (system.py: ndim (N - 1) degrees of freedom)
 
     @property
     def composition(self):
@@ -135,11 +175,13 @@ class _Particles(object):
         return len(self._f)
 
     def _make(self, i):
-        from .system import _particle_class
+        from .system import _bound_particle_class
         f = self._f
         sp = f.species[i]
-        return _particle_class()(position=f.position[i], velocity=f.velocity[i],
-                                 species=sp.item() if hasattr(sp, 'item') else sp, mass=f.mass[i], radius=f.radius[i])
+        p = _bound_particle_class()(position=f.position[i], velocity=f.velocity[i],
+                                    species=sp.item() if hasattr(sp, 'item') else sp, mass=f.mass[i], radius=f.radius[i])
+        p.__dict__['_b2_owner'] = (f, i)         # species / mass assigned to the object reach the frame's arrays
+        return p
 
     def __getitem__(self, i):
         if isinstance(i, slice):
@@ -197,6 +239,7 @@ class Trajectory(object):
         self.precision = 6
         self.variables = ['species', 'position']
         self._fh = None
+        self.callbacks = []                    # read mode: applied to every frame (atooms/trajectory/base.py:237-249,331-341)
         self._frames = []                      # read mode: (step, offset of the first particle line, n, header dict)
         if mode in ('w', 'a'):
             base = os.path.dirname(filename)
@@ -331,12 +374,24 @@ class Trajectory(object):
         tokens = numpy.array(''.join(self._fh.readline() for _ in range(n)).split())
         ncol = len(tokens) // max(n, 1)
         tokens = tokens.reshape(n, ncol)
-        return self._build(meta, self._read_species(tokens[:, 0]), tokens[:, 1:].astype(numpy.float64), step)
+        frame = self._build(meta, self._read_species(tokens[:, 0]), tokens[:, 1:].astype(numpy.float64), step)
+        for cbk, args, kwargs in list(self.callbacks):
+            frame = cbk(frame, *args, **kwargs)
+        return frame
 
     def _read_species(self, column):
         return column
 
     read = __getitem__
+
+    def register_callback(self, cbk, *args, **kwargs):
+        """A function `cbk(system, *args, **kwargs) -> system` applied to every frame read, the reference's
+        own callbacks included (atooms/trajectory/decorators.py: center, fold, sort, filter_species,
+        change_species, set_density, set_temperature, fix_cm)."""
+        if (cbk, args, kwargs) not in self.callbacks:
+            self.callbacks.append((cbk, args, kwargs))
+
+    add_callback = register_callback
 
 
 class TrajectoryRUMD(Trajectory):

@@ -692,3 +692,65 @@ def test_command_line_driver(oracle_lib, tmp_path, monkeypatch):
 
 def hp_root():
     return os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@needs_ref
+def test_reference_trajectory_callbacks(oracle_lib, tmp_path):
+    """the reference's trajectory callbacks (atooms/trajectory/decorators.py:24-136)
+    work on particle objects — in-place edits of p.position / p.velocity, assignments to p.species, and a new
+    list assigned to system.particle.  They must do to the array-backed System (device copy included) and to a
+    Snapshot read back from a file what they do to the reference's System."""
+    from atooms.trajectory import decorators as deco
+    from atooms_b200 import Snapshot
+
+    def backend():
+        return B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib)
+    u0 = backend().system.potential_energy(per_particle=True)
+    # rigid moves and folds leave the energy alone; the device sees what the callback wrote
+    s = backend().system
+    deco.fold(deco.center(s))
+    assert abs(s.potential_energy(per_particle=True) - u0) < 1e-10
+    assert numpy.all(numpy.abs(s.dump('position')) <= 0.5 * s.cell.side + 1e-12)
+    deco.fix_cm(s)
+    assert numpy.abs(s.cm_position).max() < 1e-12
+    deco.set_temperature(s, 0.7)
+    assert abs(s.temperature - 0.7) < 0.1 and numpy.abs(s.cm_velocity).max() < 1e-12
+    s = backend().system
+    deco.set_density(s, 1.0)
+    assert abs(s.density - 1.0) < 1e-12 and abs(s.potential_energy(per_particle=True) - u0) > 1e-3
+    # relabelling: A, B -> 1, 2 -> 0, 1 -> A, B keeps every particle on its row of the pair table
+    s = backend().system
+    for layout, names in (('F', ['1', '2']), ('C', ['0', '1']), ('A', ['A', 'B'])):
+        deco.change_species(s, layout)
+        assert s.distinct_species == names
+        assert abs(s.potential_energy(per_particle=True) - u0) < 1e-12
+    # a new particle list: sorted by species, then the minority species alone (still species 1 of the model)
+    ids = s._ids.copy()
+    deco.sort(s)
+    assert numpy.array_equal(s._ids, numpy.sort(ids)) and abs(s.potential_energy(per_particle=True) - u0) < 1e-10
+    deco.filter_species(s, 'B')
+    d = golden('ka_N256_rumd')
+    only_b = System(d['position'][d['species'] == 1], ['B'] * int((d['species'] == 1).sum()), Cell(d['side'], d['center']),
+                    model='kob_andersen', library=oracle_lib, species_order=['A', 'B'])
+    ref_b = B200(only_b, 'kob_andersen', library=oracle_lib).system.potential_energy(per_particle=True)
+    assert len(s) == len(only_b) and set(s._ids.tolist()) == {1}
+    assert abs(s.potential_energy(per_particle=True) - ref_b) < 1e-10
+    # a species the model has no row for cannot be taken over
+    s.particle[0].species = 'Q'
+    with pytest.raises(ValueError):
+        s.potential_energy()
+    # the same callbacks on frames read back from a file (array snapshots)
+    path = str(tmp_path / 'cb.xyz')
+    full = backend().system
+    with Trajectory(path, 'w') as th:
+        th.variables = ['species', 'position', 'velocity']
+        th.write(full, 0)
+    with Trajectory(path) as th:
+        th.add_callback(deco.change_species, 'F')
+        th.add_callback(deco.filter_species, '2')
+        th.add_callback(deco.set_density, 0.5)
+        frame = th[0]
+    assert isinstance(frame, Snapshot) and len(frame) == len(only_b) and frame.distinct_species == ['2']
+    assert abs(frame.density - 0.5) < 1e-12
+    x = (len(only_b) / numpy.prod(d['side']) / 0.5) ** (1.0 / 3)
+    assert numpy.abs(frame.position - x * d['position'][d['species'] == 1]).max() < 1e-5
