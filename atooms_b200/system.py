@@ -125,10 +125,10 @@ class _ParticleList(object):
             p = _bound_particle_class()(position=s._pos_user[i], velocity=s._vel_user[i],
                                         species=s._pending_species.get(i, s._names[s._ids[i]]),
                                         mass=s._mass[i], radius=s._radius[i])
-            p.__dict__['_b2_owner'] = (s, i)
             # the reference's Particle takes numpy.asarray of its arguments (particle.py:24-30), which drops
             # the tracking subclass: hand it the tracked row views again
             p.position, p.velocity = s._pos_user[i], s._vel_user[i]
+            p.__dict__['_b2_owner'] = (s, i)
             # numpy.asarray keeps the row views (particle.py:24-30)
             s._pull_image()
             s._img_out = True                # a view of the counters is in user hands from now on
@@ -180,7 +180,18 @@ def _bound_particle_class():
                 if owner is not None:
                     owner[0]._assign(owner[1], name, value)
             return setter
-        cls = type('Particle', (base,), {'species': property(_get('species'), _set('species')),
+        def _set_vector(name):
+            def setter(self, value):
+                owner = self.__dict__.get('_b2_owner')
+                if owner is None:
+                    self.__dict__['_b2_' + name] = value
+                else:           # p.position = array: the values go into the row this particle is a view of
+                    self.__dict__['_b2_' + name][...] = value
+                    owner[0]._assign(owner[1], name, None)
+            return setter
+        cls = type('Particle', (base,), {'position': property(_get('position'), _set_vector('position')),
+                                         'velocity': property(_get('velocity'), _set_vector('velocity')),
+                                         'species': property(_get('species'), _set('species')),
                                          'mass': property(_get('mass'), _set('mass')),
                                          'radius': property(_get('radius'), _set('radius')),
                                          '__module__': base.__module__})
@@ -489,6 +500,8 @@ class System(object):
         elif name == 'radius':
             self._radius[i] = float(value)                   # (host side only: the engine has no use for it)
             return
+        elif name in ('position', 'velocity'):
+            return                                           # (written through the tracked row view already)
         else:
             self._mass[i] = float(value)
         self._identity_dirty = True

@@ -111,6 +111,8 @@ class Snapshot(object):
             self.species[i] = value
         elif name == 'radius':
             self.radius[i] = float(value)
+        elif name in ('position', 'velocity'):
+            pass                                             # (written through the row view already)
         else:
             self.mass[i] = float(value)
 
@@ -335,10 +337,15 @@ class Trajectory(object):
 
     @property
     def steps(self):
-        return [f[0] for f in self._frames]
+        override = self.__dict__.get('_steps')
+        return [f[0] for f in self._frames] if override is None else override
+
+    @steps.setter
+    def steps(self, value):                  # (the reference's `Sliced` decorator narrows them, decorators.py:162-165)
+        self.__dict__['_steps'] = list(value)
 
     def __len__(self):
-        return len(self._frames)
+        return len(self.steps)
 
     def __iter__(self):
         return (self[i] for i in range(len(self)))
@@ -364,20 +371,34 @@ class Trajectory(object):
         snap.extra = {c: v for c, v in got.items() if c not in _WIDTH}
         return snap
 
+    # The template of atooms/trajectory/base.py:209-251, so that the reference's class decorators (`Sliced`,
+    # `Unfolded`: they override read_init / read_system of whatever class they wrap) work on this one:
+    # read(i) = read_init() once, read_system(i), callbacks.
+    def read_init(self):
+        return None
+
     def __getitem__(self, i):
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError('frame %d of %d' % (i, len(self)))
+        if not getattr(self, '_initialized_read', False):
+            self.read_init()
+            self._initialized_read = True
+        frame = self.read_system(i)
+        for cbk, args, kwargs in list(self.callbacks):
+            frame = cbk(frame, *args, **kwargs)
+        return frame
+
+    def read_system(self, i):
         if self._fh is None or self.mode != 'r':
             raise IOError('trajectory %s is not open for reading' % self.filename)
-        if i < 0:
-            i += len(self._frames)
         step, start, n, meta = self._frames[i]
         self._fh.seek(start)
         tokens = numpy.array(''.join(self._fh.readline() for _ in range(n)).split())
         ncol = len(tokens) // max(n, 1)
         tokens = tokens.reshape(n, ncol)
-        frame = self._build(meta, self._read_species(tokens[:, 0]), tokens[:, 1:].astype(numpy.float64), step)
-        for cbk, args, kwargs in list(self.callbacks):
-            frame = cbk(frame, *args, **kwargs)
-        return frame
+        return self._build(meta, self._read_species(tokens[:, 0]), tokens[:, 1:].astype(numpy.float64), step)
 
     def _read_species(self, column):
         return column

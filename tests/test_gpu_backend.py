@@ -26,7 +26,8 @@ PROTOCOL_TESTS = [hp.test_backend_surface, hp.test_nve_pin_through_the_backend, 
 REFERENCE_DRIVER_TESTS = [hp.test_reference_simulation_driver, hp.test_integration_shim, hp.test_reference_optimization_driver,
                           hp.test_interaction_with_reference_system,
                           hp.test_neighbors_export_round_trips_through_the_reference_reader,
-                          hp.test_command_line_driver, hp.test_reference_trajectory_callbacks]
+                          hp.test_command_line_driver, hp.test_reference_trajectory_callbacks,
+                          hp.test_reference_class_decorators_on_the_trajectory]
 
 
 def _call(fn, cuda_lib, pins, tmp_path, monkeypatch):

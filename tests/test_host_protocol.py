@@ -754,3 +754,33 @@ def test_reference_trajectory_callbacks(oracle_lib, tmp_path):
     assert abs(frame.density - 0.5) < 1e-12
     x = (len(only_b) / numpy.prod(d['side']) / 0.5) ** (1.0 / 3)
     assert numpy.abs(frame.position - x * d['position'][d['species'] == 1]).max() < 1e-5
+
+
+@needs_ref
+def test_reference_class_decorators_on_the_trajectory(oracle_lib, tmp_path):
+    """`Sliced` and `Unfolded` (atooms/trajectory/decorators.py:147-241) subclass whatever trajectory they are given
+    and override its read_init / read_system: the reader here follows that template.  Unfolding the frames must
+    reproduce what the engine's own box-crossing counters say."""
+    from atooms.trajectory.decorators import Sliced, Unfolded
+    s = make_system('ka_N256_rumd', oracle_lib, 'kob_andersen')
+    bck = B200(s, 'kob_andersen', dt=0.004, library=oracle_lib)
+    bck.system.set_temperature(3.0, seed=5)
+    path = str(tmp_path / 'u.xyz')
+    unfolded = []
+    with Trajectory(path, 'w') as th:
+        th.precision = 12
+        for _ in range(8):
+            th.write(bck.system, bck.steps)
+            unfolded.append(bck.system.dump('position') + bck.system.image * bck.system.cell.side)
+            bck.run(100)
+    assert numpy.abs(bck.system.image).sum() > 20              # particles did leave the cell
+    with Trajectory(path) as th:
+        sl = Sliced(th, slice(1, 7, 2))
+        assert sl.steps == [100, 300, 500] and len(sl) == 3
+        assert [sl[i].step for i in range(3)] == [100, 300, 500] and sl[-1].step == 500
+        un = Unfolded(th)
+        first = un[0].position.copy()        # (folded as written: compare displacements from it)
+        for k in range(1, 8):
+            assert numpy.abs((un[k].position - first) - (unfolded[k] - unfolded[0])).max() < 1e-9
+        with pytest.raises(ValueError):
+            un[2]                                            # no unfolding backwards (decorators.py:204-206)
