@@ -49,6 +49,12 @@ class Cell(object):
     def volume(self):
         return float(numpy.prod(self.side))
 
+    @property
+    def origin(self):                        # (atooms/system/cell.py:36-39)
+        import warnings
+        warnings.warn('cell origin is deprecated', DeprecationWarning)
+        return numpy.zeros(self.side.size)
+
 
 class Particle(object):
 
@@ -471,17 +477,23 @@ class System(object):
         particles = list(particles)
         if not particles:
             raise ValueError('a system needs at least one particle')
+        n = len(particles)
+        images = [getattr(q, 'periodic_image', None) for q in particles]
+        self._rebuild(numpy.array([numpy.asarray(q.position, dtype=numpy.float64) for q in particles]).reshape(n, 3),
+                      numpy.array([numpy.asarray(q.velocity, dtype=numpy.float64) for q in particles]).reshape(n, 3),
+                      [str(q.species) for q in particles], [float(q.mass) for q in particles],
+                      [float(getattr(q, 'radius', 0.5)) for q in particles],
+                      numpy.array(images, dtype=numpy.int32).reshape(n, 3) if all(im is not None for im in images) else None)
+
+    def _rebuild(self, position, velocity, names, mass, radius, image=None):
+        """This system with another set of particles (any number): a new device context in place of the old one;
+        cell, model, reservoirs, interaction and synchronisation mode stay."""
         self._resolve_species()
-        self._pull_image()
-        new = System(position=numpy.array([numpy.asarray(q.position, dtype=numpy.float64) for q in particles]),
-                     species=[str(q.species) for q in particles], cell=self.cell,
-                     velocity=numpy.array([numpy.asarray(q.velocity, dtype=numpy.float64) for q in particles]),
-                     mass=[float(q.mass) for q in particles], radius=[float(getattr(q, 'radius', 0.5)) for q in particles],
+        new = System(position=position, species=names, cell=self.cell, velocity=velocity, mass=mass, radius=radius,
                      model=self.model, precision=self.precision, skin=self._skin(), device=self._engine.device,
                      library=self._engine.lib, species_order=self._names)
-        images = [getattr(q, 'periodic_image', None) for q in particles]
-        if all(im is not None for im in images):
-            new._img[:] = numpy.array(images, dtype=numpy.int32).reshape(len(particles), 3)
+        if image is not None:
+            new._img[:] = image
             new._engine.set_images(new._img)
         for name in ('thermostat', 'barostat', 'reservoir', 'interaction', 'sync'):
             setattr(new, name, getattr(self, name))
@@ -492,6 +504,85 @@ class System(object):
         new.__dict__.clear()                 # (its engine and arrays live on in self)
         if self.interaction is not None:
             self.interaction._invalidate()
+
+    def replicate(self, times, axis):
+        """`times` copies of the system side by side along `axis`, the cell grown with them, the result centred
+        as before (atooms/system/system.py:381-396) — on the arrays, not particle by particle."""
+        n = int(times)
+        if n <= 1:
+            raise ValueError('replicate: times must be larger than 1')
+        self._pull_image()
+        self._resolve_species()
+        length = float(self.cell.side[axis])
+        shift = (numpy.arange(n) - 0.5 * (n - 1)) * length
+        pos = numpy.tile(self._pos, (n, 1))
+        pos[:, axis] += numpy.repeat(shift, len(self))
+        names = [self._names[i] for i in self._ids] * n
+        side = numpy.array(self.cell.side, dtype=numpy.float64)
+        side[axis] *= n
+        self.cell.side = side
+        self._rebuild(pos, numpy.tile(self._vel, (n, 1)), names, numpy.tile(self._mass, n), numpy.tile(self._radius, n),
+                      numpy.tile(self._img, (n, 1)))
+
+    @property
+    def packing_fraction(self):
+        return float(numpy.pi / 6 * ((2.0 * self._radius) ** 3).sum() / self.cell.volume)      # system.py:160-162
+
+    @property
+    def species_layout(self):
+        """'A' (names), 'C' (integers from 0) or 'F' (integers from 1), as system.py:569-589."""
+        try:
+            lowest = min(int(name) for name in self.distinct_species)
+        except ValueError:
+            return 'A'
+        if lowest not in (0, 1):
+            raise ValueError('Numeric species should start from 0 or 1')
+        return 'C' if lowest == 0 else 'F'
+
+    @species_layout.setter
+    def species_layout(self, layout):
+        """Rename the species (system.py:591-628): a change of names only, every particle keeps its row of the
+        pair table and nothing moves on the device."""
+        if layout[0] not in 'ACF':
+            raise ValueError('layout must be A, C or F (not %s)' % layout)
+        self._resolve_species()
+        current = self.species_layout
+        if layout[0] == current:
+            return
+        import string
+        used = self.distinct_species
+        if layout[0] == 'A':
+            lowest = min(int(name) for name in used)
+            renamed = {name: string.ascii_uppercase[int(name) - lowest] for name in used}
+        elif current == 'A':
+            renamed = {name: str(k + (1 if layout[0] == 'F' else 0)) for k, name in enumerate(used)}
+        else:
+            renamed = {name: str(int(name) + (1 if layout[0] == 'F' else -1)) for name in used}
+        self._names = [renamed.get(name, name) for name in self._names]
+        self._particle._cache.clear()
+
+    def set_composition(self, N):
+        """Assign the species at random so that N[name] particles carry `name` (system.py:210-220)."""
+        import random
+        if sum(N.values()) != len(self):
+            raise ValueError('composition %s does not match N = %d' % (N, len(self)))
+        self._resolve_species()
+        for name in N:
+            if str(name) not in self._names:
+                if len(self._names) >= self.model.nsp:
+                    raise ValueError('species %r: the model %s has %d species (%s)' % (name, self.model, self.model.nsp, self._names))
+                self._names.append(str(name))
+        species = []
+        for name in N:
+            species += [self._names.index(str(name))] * N[name]
+        random.shuffle(species)
+        self._ids[:] = species
+        self._identity_dirty = True
+        self._thermo = None
+        self._particle._cache.clear()
+
+    def show(self, *args, **kwargs):
+        raise NotImplementedError('visualisation backends (atooms/system/system.py:556-567) are unavailable on this box')
 
     def _assign(self, i, name, value):
         """`particle[i].species = ...` / `.mass = ...` (see _bound_particle_class)."""

@@ -27,7 +27,7 @@ REFERENCE_DRIVER_TESTS = [hp.test_reference_simulation_driver, hp.test_integrati
                           hp.test_interaction_with_reference_system,
                           hp.test_neighbors_export_round_trips_through_the_reference_reader,
                           hp.test_command_line_driver, hp.test_reference_trajectory_callbacks,
-                          hp.test_reference_class_decorators_on_the_trajectory]
+                          hp.test_reference_class_decorators_on_the_trajectory, hp.test_system_members_of_the_reference]
 
 
 def _call(fn, cuda_lib, pins, tmp_path, monkeypatch):

@@ -784,3 +784,45 @@ def test_reference_class_decorators_on_the_trajectory(oracle_lib, tmp_path):
             assert numpy.abs((un[k].position - first) - (unfolded[k] - unfolded[0])).max() < 1e-9
         with pytest.raises(ValueError):
             un[2]                                            # no unfolding backwards (decorators.py:204-206)
+
+
+@needs_ref
+def test_system_members_of_the_reference(oracle_lib):
+    """The members of atooms.system.System that change the particles themselves (system.py:160-162, 210-220,
+    381-396, 569-628): replicate, set_composition, species_layout, packing_fraction — on the arrays, with the
+    device copy following, against the reference's own System doing the same particle by particle."""
+    from atooms.system import System as RefSystem, Particle as RefParticle, Cell as RefCell
+    d = golden('ka_N256_rumd')
+    names = d['species_names'][d['species']]
+    s = B200(make_system('ka_N256_rumd', oracle_lib, 'kob_andersen'), 'kob_andersen', library=oracle_lib).system
+    ref = RefSystem([RefParticle(position=x.copy(), velocity=v.copy(), species=n, mass=m)
+                     for x, v, n, m in zip(d['position'], d['velocity'], names, d['mass'])], RefCell(d['side'].copy()))
+    u0, k0 = s.potential_energy(per_particle=True), s.kinetic_energy(per_particle=True)
+    assert abs(s.packing_fraction - ref.packing_fraction) < 1e-12
+    # names only: nothing moves on the device
+    for layout, expect in (('F', ['1', '2']), ('C', ['0', '1']), ('A', ['A', 'B'])):
+        s.species_layout = layout
+        ref.species_layout = layout
+        assert s.species_layout == ref.species_layout == layout and s.distinct_species == expect
+        assert s.particle[7].species == ref.particle[7].species
+        assert abs(s.potential_energy(per_particle=True) - u0) < 1e-12
+    # two periodic copies along x: same energy per particle, the reference's coordinates
+    s.replicate(2, 0)
+    ref.replicate(2, 0)
+    assert len(s) == 512 and numpy.allclose(s.cell.side, ref.cell.side)
+    theirs = numpy.array([p.position for p in ref.particle])
+    assert numpy.abs(numpy.sort(theirs, axis=0) - numpy.sort(s.dump('position'), axis=0)).max() < 1e-12
+    assert abs(s.potential_energy(per_particle=True) - u0) < 1e-12 and abs(s.kinetic_energy(per_particle=True) - k0) < 1e-12
+    assert abs(s.packing_fraction - ref.packing_fraction) < 1e-12
+    with pytest.raises(ValueError):
+        s.replicate(1, 0)
+    # a new composition: the device copy follows (the energy changes, the run goes on)
+    s.set_composition({'A': 500, 'B': 12})
+    assert s.composition == {'A': 500, 'B': 12} and abs(s.concentration['B'] - 12 / 512) < 1e-12
+    assert abs(s.potential_energy(per_particle=True) - u0) > 1e-3
+    with pytest.raises(ValueError):
+        s.set_composition({'A': 3})
+    with pytest.raises(ValueError):
+        s.set_composition({'A': 500, 'B': 6, 'C': 6})       # the model has two species
+    with pytest.raises(NotImplementedError):
+        s.show()
