@@ -73,6 +73,33 @@ class Particle(object):
     def kinetic_energy(self):
         return 0.5 * self.mass * numpy.dot(self.velocity, self.velocity)
 
+    @property
+    def diameter(self):
+        return 2 * self.radius
+
+    def distance(self, particle, cell=None, folded=True):
+        """Separation vector from `particle`, of the nearest periodic image when a cell is given
+        (atooms/system/particle.py:63-82; `folded` only selects between two equivalent reductions there)."""
+        r = self.position - particle.position
+        return r if cell is None else r - numpy.rint(r / cell.side) * cell.side
+
+    def nearest_image(self, particle, cell, copy=False, folded=False):
+        """Move this particle (or a copy of it) to its periodic image nearest to `particle` (particle.py:37-61)."""
+        where = particle.position + self.distance(particle, cell)
+        if copy:
+            import copy as _copy
+            image = _copy.deepcopy(self)
+            image.position = where
+            return image
+        self.position[:] = where
+        return self
+
+    def maxwellian(self, T):
+        """Velocity components drawn from a Gaussian of variance T / m (particle.py:101-107)."""
+        import random
+        for k in range(len(self.velocity)):
+            self.velocity[k] = random.gauss(0, numpy.sqrt(T / self.mass))
+
     def fold(self, cell):
         # atooms/system/particle.py:90-99
         p = self.position - cell.center
@@ -90,9 +117,18 @@ class Thermostat(object):
     (lammps.py:233-235).  Assigning one to `system.thermostat` turns `B200.run`
     into NVT dynamics; `pressure` then uses this temperature (system.py:343-346)."""
 
-    def __init__(self, temperature=None, relaxation_time=1.0):
+    def __init__(self, temperature=None, name='', mass=1.0, coordinate=1.0, momentum=1.0, relaxation_time=1.0,
+                 collision_period=None):
+        self.name = name
         self.temperature = temperature
-        self.relaxation_time = relaxation_time
+        self.coordinate = numpy.asarray(coordinate)
+        self.momentum = numpy.asarray(momentum)
+        self.mass = numpy.asarray(mass)
+        self.relaxation_time = relaxation_time if collision_period is None else collision_period
+
+    @property
+    def collision_period(self):
+        return self.relaxation_time
 
 
 class Barostat(object):

@@ -226,7 +226,110 @@ def _arrays_of(system, columns):
     return [numpy.asarray(system.dump(c)) for c in columns]
 
 
-class Trajectory(object):
+def block_size_of(steps):
+    """Frames per block: the period after which the increments between steps recur (1 for equally spaced frames,
+    the whole trajectory when nothing recurs) — what atooms/trajectory/utils.py:98-133 finds for exponentially
+    spaced samples like 1, 2, 4, 11, 12, 14, ..."""
+    steps = list(steps)
+    if len(steps) < 2:
+        return 1
+    inc = [b - a for a, b in zip(steps[:-1], steps[1:])]
+    if all(d == inc[0] for d in inc):
+        return 1
+    for period in range(1, len(inc)):
+        if all(d == inc[k % period] for k, d in enumerate(inc)):
+            return period
+    return len(steps)
+
+
+class _BaseMembers(object):
+
+    """The members of atooms/trajectory/base.py:212-527 that analysis code built on the reference uses besides
+    read / write: time axis, block size, the read_* / write_* hooks, append and copy."""
+
+    def append(self, system):
+        self.write(system)
+
+    def _next_step(self, step):
+        steps = self.steps
+        return (steps[-1] + 1 if len(steps) else 0) if step is None else step
+
+    @property
+    def times(self):
+        dt = self.timestep if self.timestep is not None else 1.0
+        return [step * dt for step in self.steps]
+
+    @property
+    def total_time(self):
+        dt = self.timestep if self.timestep is not None else 1.0
+        return (self.steps[-1] - self.steps[0]) * dt
+
+    @property
+    def block_size(self):
+        fixed = self.__dict__.get('_block_size')
+        return block_size_of(self.steps) if fixed is None else fixed
+
+    @block_size.setter
+    def block_size(self, value):
+        self.__dict__['_block_size'] = value
+
+    @property
+    def grandcanonical(self):
+        return False
+
+    @property
+    def fields(self):
+        return self.variables
+
+    @fields.setter
+    def fields(self, value):
+        self.variables = value
+
+    def read_len(self):
+        return len(self)
+
+    def read_steps(self):
+        return list(self.steps)
+
+    def read_timestep(self):
+        return self.timestep if self.timestep is not None else 1.0
+
+    def read_block_size(self):
+        return None
+
+    def write_init(self, system):
+        pass
+
+    def write_system(self, system, step):
+        self.write(system, step)
+
+    def write_timestep(self, value):
+        self.timestep = value
+
+    def write_block_size(self, value):
+        pass
+
+    def copy(self, cls=None, fout=None, steps=None, **ignored):
+        """The frames (those at `steps`, if given) written to another trajectory of class `cls`; returns it, closed
+        (base.py:384-443)."""
+        cls = self.__class__ if cls is None else cls
+        if fout is None:
+            root, ext = os.path.splitext(getattr(self, 'filename', None) or 'trajectory')
+            fout = root + '.copy.' + getattr(cls, 'suffix', ext.lstrip('.') or 'xyz')
+        if fout == getattr(self, 'filename', None):
+            raise IOError('copy: trying to overwrite the input trajectory')
+        out = cls(fout, 'w')
+        out.variables, out.timestep = list(self.variables), self.timestep
+        if getattr(self, 'precision', None) is not None:
+            out.precision = self.precision
+        for k, step in enumerate(self.steps):
+            if steps is None or step in steps:
+                out.write(self[k], step)
+        out.close()
+        return out
+
+
+class Trajectory(_BaseMembers):
 
     """xyz trajectory in the reference's layout (atooms/trajectory/xyz.py:135-474)."""
 
@@ -243,6 +346,7 @@ class Trajectory(object):
         self._fh = None
         self.callbacks = []                    # read mode: applied to every frame (atooms/trajectory/base.py:237-249,331-341)
         self._frames = []                      # read mode: (step, offset of the first particle line, n, header dict)
+        self._written = []                     # write mode: steps written so far
         if mode in ('w', 'a'):
             base = os.path.dirname(filename)
             if base and not os.path.exists(base):
@@ -275,9 +379,11 @@ class Trajectory(object):
     def _species_column(self, names):
         return names.astype(object) if names.dtype.kind in 'US' else names
 
-    def write(self, system, step):
+    def write(self, system, step=None):
         if self._fh is None or self.mode == 'r':
             raise IOError('trajectory %s is not open for writing' % self.filename)
+        step = self._next_step(step)           # (base.py:267-275: one past the last step when none is given)
+        self._written.append(step)
         columns = _columns(self.variables)
         blocks = _arrays_of(system, columns)
         n = len(blocks[0]) if blocks else 0
@@ -338,7 +444,9 @@ class Trajectory(object):
     @property
     def steps(self):
         override = self.__dict__.get('_steps')
-        return [f[0] for f in self._frames] if override is None else override
+        if override is not None:
+            return override
+        return [f[0] for f in self._frames] if self.mode == 'r' else self._written
 
     @steps.setter
     def steps(self, value):                  # (the reference's `Sliced` decorator narrows them, decorators.py:162-165)
@@ -460,7 +568,7 @@ class TrajectoryRUMD(Trajectory):
         return out
 
 
-class TrajectoryRam(object):
+class TrajectoryRam(_BaseMembers):
 
     """Frames kept in memory as array snapshots: the interface of atooms/trajectory/ram.py:7-47 (write
     replaces the frame of a step already present, `th[i]` returns a copy, `th[i] = system` writes)
@@ -483,7 +591,8 @@ class TrajectoryRam(object):
     def close(self):
         pass
 
-    def write(self, system, step):
+    def write(self, system, step=None):
+        step = self._next_step(step)
         frame = Snapshot.of(system, step)
         if step in self.steps:
             self._frames[self.steps.index(step)] = frame
@@ -494,10 +603,26 @@ class TrajectoryRam(object):
     def __len__(self):
         return len(self._frames)
 
-    def __getitem__(self, i):
+    def read_init(self):
+        return None
+
+    def read_system(self, i):
         return copy.deepcopy(self._frames[i])
 
+    def __getitem__(self, i):
+        frame = self.read_system(i)
+        for cbk, args, kwargs in list(self.__dict__.get('callbacks', ())):
+            frame = cbk(frame, *args, **kwargs)
+        return frame
+
     read = __getitem__
+
+    def register_callback(self, cbk, *args, **kwargs):
+        callbacks = self.__dict__.setdefault('callbacks', [])
+        if (cbk, args, kwargs) not in callbacks:
+            callbacks.append((cbk, args, kwargs))
+
+    add_callback = register_callback
 
     def __setitem__(self, i, value):
         try:

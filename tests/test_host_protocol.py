@@ -826,3 +826,64 @@ def test_system_members_of_the_reference(oracle_lib):
         s.set_composition({'A': 500, 'B': 6, 'C': 6})       # the model has two species
     with pytest.raises(NotImplementedError):
         s.show()
+
+
+def test_trajectory_base_members(oracle_lib, tmp_path):
+    """What analysis code written against atooms/trajectory/base.py:212-527 uses besides read and write: a default
+    step, append, the time axis, the block size of exponentially spaced frames, the read_* hooks, copy."""
+    from atooms_b200 import TrajectoryRam
+    from atooms_b200.trajectory import block_size_of
+    s = make_system('ka_N256_rumd', oracle_lib, 'kob_andersen')
+    path = str(tmp_path / 'b.xyz')
+    steps = [0, 1, 2, 4, 8, 16, 17, 18, 20, 24, 32]
+    with Trajectory(path, 'w') as th:
+        th.timestep = 0.002
+        for step in steps:
+            th.write(s, step)
+        th.append(s)                                         # one past the last step
+        assert th.steps == steps + [33]
+    with Trajectory(path) as th:
+        assert th.read_len() == 12 and th.read_steps() == steps + [33] and th.read_timestep() == 0.002
+        assert th.times[4] == 8 * 0.002 and abs(th.total_time - 33 * 0.002) < 1e-15
+        assert th.block_size == 5 and not th.grandcanonical
+        out = th.copy(cls=TrajectoryRam, steps=[0, 8, 32])
+        assert out.steps == [0, 8, 32] and numpy.abs(out[1].position - th[4].position).max() == 0.0
+        twin = th.copy(fout=str(tmp_path / 'c.xyz'))
+    with Trajectory(twin.filename) as th:
+        assert th.steps == steps + [33] and th.timestep == 0.002
+    ram = TrajectoryRam()
+    ram.write(s)
+    ram.append(s)
+    assert ram.steps == [0, 1] and ram.block_size == 1
+    for seq, size in (([0, 1, 2, 3], 1), ([1, 2, 4, 11, 12, 14, 21, 22, 24], 3), ([0, 1, 3, 7], 4), ([5], 1),
+                      ([0, 1, 10, 11, 20, 21, 30], 2)):
+        assert block_size_of(seq) == size
+        if HAVE_REF:
+            from atooms.trajectory.utils import get_block_size
+            assert get_block_size(seq) == size
+
+
+def test_standalone_particle_and_reservoirs():
+    """The stand-ins used when atooms itself is not importable carry the members of the originals
+    (atooms/system/particle.py:32-107, reservoir.py:22-40)."""
+    from atooms_b200.system import Particle as Own, Cell as OwnCell
+    from atooms_b200 import Thermostat
+    cell = OwnCell([4.0, 4.0, 4.0])
+    a = Own(numpy.array([1.9, 0.0, -1.9]), numpy.zeros(3), 'A', mass=2.0, radius=0.6)
+    b = Own(numpy.array([-1.9, 0.5, 1.9]), numpy.zeros(3), 'B')
+    assert a.diameter == 1.2
+    assert numpy.allclose(a.distance(b), [3.8, -0.5, -3.8]) and numpy.allclose(a.distance(b, cell), [-0.2, -0.5, 0.2])
+    image = a.nearest_image(b, cell, copy=True)
+    assert numpy.allclose(image.position, [-2.1, 0.0, 2.1]) and numpy.allclose(a.position, [1.9, 0.0, -1.9])
+    a.nearest_image(b, cell)
+    assert numpy.allclose(a.position, [-2.1, 0.0, 2.1])
+    a.maxwellian(1.0)
+    assert numpy.abs(a.velocity).max() > 0
+    if HAVE_REF:
+        from atooms.system.particle import Particle as Ref
+        from atooms.system.cell import Cell as RefCell
+        ra, rb = Ref(position=[1.9, 0.0, -1.9], radius=0.6), Ref(position=[-1.9, 0.5, 1.9])
+        assert numpy.allclose(ra.distance(rb, RefCell([4.0, 4.0, 4.0])), [-0.2, -0.5, 0.2]) and ra.diameter == 1.2
+        assert numpy.allclose(ra.nearest_image(rb, RefCell([4.0, 4.0, 4.0]), copy=True).position, image.position)
+    th = Thermostat(2.0, collision_period=0.3)
+    assert th.relaxation_time == 0.3 and th.collision_period == 0.3 and Thermostat(1.0, relaxation_time=0.5).collision_period == 0.5
