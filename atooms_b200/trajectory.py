@@ -351,12 +351,25 @@ class Trajectory(_BaseMembers):
             base = os.path.dirname(filename)
             if base and not os.path.exists(base):
                 os.makedirs(base)
-            self._fh = open(filename, mode)
+            self._fh = self._open(filename, mode)
         elif mode == 'r':
-            self._fh = open(filename, 'r')
+            self._fh = self._open(filename, 'r')
             self._index()
         else:
             raise ValueError('unknown mode %r' % mode)
+
+    @staticmethod
+    def _open(filename, mode):
+        """Plain text, or gzip when the name says so (RUMD keeps its configurations as .xyz.gz,
+        atooms/trajectory/rumd.py:10-98): read in one go, the frame index then works on the text in memory."""
+        if not filename.endswith('.gz'):
+            return open(filename, mode)
+        import gzip
+        import io
+        if mode == 'r':
+            with gzip.open(filename, 'rt') as fh:
+                return io.StringIO(fh.read())
+        return gzip.open(filename, mode + 't')
 
     def __enter__(self):
         return self
@@ -422,6 +435,12 @@ class Trajectory(_BaseMembers):
             if ':' in token:
                 key, value = token.split(':', 1)
                 meta[key] = value
+        # RUMD's second header format (atooms/trajectory/rumd.py:56-67): the time step is the second field of
+        # `integrator=`, the cell follows the box type in `sim_box=`
+        if 'integrator' in meta and 'dt' not in meta:
+            meta['dt'] = meta['integrator'].split(',')[1]
+        if 'sim_box' in meta and 'cell' not in meta:
+            meta['cell'] = ','.join(meta['sim_box'].split(',')[1:])
         return meta
 
     def _index(self):

@@ -887,3 +887,41 @@ def test_standalone_particle_and_reservoirs():
         assert numpy.allclose(ra.nearest_image(rb, RefCell([4.0, 4.0, 4.0]), copy=True).position, image.position)
     th = Thermostat(2.0, collision_period=0.3)
     assert th.relaxation_time == 0.3 and th.collision_period == 0.3 and Thermostat(1.0, relaxation_time=0.5).collision_period == 0.5
+
+
+def test_rumd_configurations_gzipped_and_second_header_format(oracle_lib, tmp_path):
+    """RUMD keeps configurations as .xyz.gz and has two header dialects (atooms/trajectory/rumd.py:56-67, 79-98):
+    `boxLengths= dt=` and `sim_box=<type>,Lx,Ly,Lz integrator=<name>,dt,...`."""
+    import gzip
+    from atooms_b200 import TrajectoryRUMD
+    s = make_system('ka_N256_rumd', oracle_lib, 'kob_andersen')
+    path = str(tmp_path / 'conf.xyz.gz')
+    with TrajectoryRUMD(path, 'w') as th:                   # written compressed, by the native formatter too
+        th.timestep = 0.005
+        th.write(s, 0)
+        th.write(s, 40)
+    assert gzip.open(path, 'rt').readline().strip() == '256'
+    with TrajectoryRUMD(path) as th:
+        assert th.steps == [0, 40] and th.timestep == 0.005
+        assert numpy.abs(th[1].position - s.dump('position')).max() < 1e-8
+    second = str(tmp_path / 'second.xyz.gz')
+    with gzip.open(second, 'wt') as fh:
+        for step in (0, 8):
+            fh.write('3\nioformat=2 timeStepIndex=%d numTypes=2 integrator=IntegratorNVT,0.004,0.5,0.4,0 '
+                     'sim_box=RectangularSimulationBox,10.03,10.03,12.5 mass=1.0,1.0 columns=type,x,y,z,imx,imy,imz,pe,vir\n' % step)
+            fh.write('0 4.2019 -0.8430 -0.7399 0 0 0 -5.3925 28.4504\n1 1.0 2.0 3.0 0 1 0 -4.0 20.0\n0 -1.5 0.25 4.0 -1 0 0 -6.0 30.0\n')
+    with TrajectoryRUMD(second) as th:
+        frame = th[1]
+        assert th.steps == [0, 8] and th.timestep == 0.004 and numpy.allclose(frame.cell.side, [10.03, 10.03, 12.5])
+        assert frame.distinct_species == ['0', '1'] and numpy.allclose(frame.position[2], [-1.5, 0.25, 4.0])
+        assert numpy.allclose(frame.extra['pe'][:, 0], [-5.3925, -4.0, -6.0]) and frame.extra['imy'][1, 0] == 1
+    data = '/root/reference/data/ka_rumd_N1200.xyz.gz'      # the reference's own file, where the tree is at hand
+    if HAVE_REF and os.path.exists(data):
+        from atooms.trajectory import TrajectoryRUMD as RefRUMD
+        ref = RefRUMD(data)
+        with TrajectoryRUMD(data) as th:
+            assert th.steps == ref.steps and th.timestep == ref.timestep and th.block_size == ref.block_size
+            mine, theirs = th[3], ref[3]
+            assert numpy.allclose(mine.cell.side, theirs.cell.side)
+            assert numpy.abs(mine.position - numpy.array([p.position for p in theirs.particle])).max() == 0.0
+        ref.close()
