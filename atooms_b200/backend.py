@@ -70,6 +70,12 @@ def _last_frame(inp):
     if hasattr(inp, '__getitem__') and hasattr(inp, 'steps'):
         return inp[-1]
     if isinstance(inp, str) and os.path.exists(inp):
+        # xyz and RUMD configurations: the readers of this package (arrays, no Particle objects)
+        if inp.endswith('.xyz.gz') or inp.endswith('.xyz'):
+            from .trajectory import TrajectoryRUMD
+            with (TrajectoryRUMD if inp.endswith('.gz') else Trajectory)(inp) as th:
+                if len(th):
+                    return th[-1]
         try:
             from atooms import trajectory
         except ImportError:
