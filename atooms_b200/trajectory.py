@@ -137,6 +137,47 @@ class Snapshot(object):
         n = len(self)
         return 2.0 * self.kinetic_energy() / (3 * (n - 1)) if n > 1 else 0.0      # (system.py: ndim (N - 1) degrees of freedom)
 
+    @temperature.setter
+    def temperature(self, T):
+        self.set_temperature(T)
+
+    # the host-side members of atooms/system/system.py:186-208, 227-230, 330-379 — on the arrays
+    @property
+    def concentration(self):
+        return {k: v / float(len(self)) for k, v in self.composition.items()}
+
+    @property
+    def packing_fraction(self):
+        return float(numpy.pi / 6 * ((2.0 * self.radius) ** 3).sum() / self.cell.volume)
+
+    def cm(self, what):
+        return (self.mass[:, None] * getattr(self, what)).sum(axis=0) / self.mass.sum()
+
+    def scale_velocities(self, factor):
+        self.velocity *= factor
+
+    def fix_momentum(self):
+        self.velocity -= self.cm_velocity
+
+    def fold(self):
+        center = getattr(self.cell, 'center', 0.0)
+        r = self.position - center
+        self.position[:] = r - numpy.rint(r / self.cell.side) * self.cell.side + center
+
+    def set_density(self, rho):
+        factor = (self.density / rho) ** (1.0 / 3)
+        self.position *= factor
+        self.cell.side = self.cell.side * factor
+
+    def set_temperature(self, temperature, seed=None):
+        """Maxwell-Boltzmann velocities at `temperature`, total momentum zero, rescaled to it exactly."""
+        rng = numpy.random.default_rng(seed)
+        self.velocity[:] = rng.normal(size=self.velocity.shape) * numpy.sqrt(temperature / self.mass)[:, None]
+        self.fix_momentum()
+        current = self.temperature
+        if current > 0:
+            self.velocity *= numpy.sqrt(temperature / current)
+
     @property
     def composition(self):
         names, counts = numpy.unique(self.species, return_counts=True)

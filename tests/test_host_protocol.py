@@ -925,3 +925,28 @@ def test_rumd_configurations_gzipped_and_second_header_format(oracle_lib, tmp_pa
             assert numpy.allclose(mine.cell.side, theirs.cell.side)
             assert numpy.abs(mine.position - numpy.array([p.position for p in theirs.particle])).max() == 0.0
         ref.close()
+
+
+def test_snapshot_host_side_members(oracle_lib):
+    """A frame read back from a trajectory answers the host-side questions a System answers
+    (atooms/system/system.py:160-230, 330-379), without a device context."""
+    from atooms_b200 import Snapshot
+    s = make_system('ka_N256_rumd', oracle_lib, 'kob_andersen')
+    f = Snapshot.of(s)
+    assert abs(f.temperature - s.temperature) < 1e-12 and abs(f.kinetic_energy() - s.kinetic_energy()) < 1e-9
+    assert numpy.allclose(f.cm_position, s.cm_position) and numpy.allclose(f.cm_velocity, s.cm_velocity)
+    assert numpy.allclose(f.cm('position'), s.cm_position) and abs(f.packing_fraction - s.packing_fraction) < 1e-12
+    assert f.concentration == s.concentration and f.composition == s.composition
+    f.position += 3.0 * f.cell.side
+    f.fold()
+    assert numpy.abs(f.position - s.dump('position')).max() < 1e-9
+    f.set_density(1.0)
+    assert abs(f.density - 1.0) < 1e-12
+    f.set_temperature(0.8, seed=3)
+    assert abs(f.temperature - 0.8) < 1e-12 and numpy.abs(f.cm_velocity).max() < 1e-12
+    f.scale_velocities(2.0)
+    assert abs(f.temperature - 3.2) < 1e-12
+    f.temperature = 1.0
+    assert abs(f.temperature - 1.0) < 1e-12
+    # and starts a backend like any other system
+    assert len(B200(f, 'kob_andersen', library=oracle_lib).system) == 256
